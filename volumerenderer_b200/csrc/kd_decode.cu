@@ -1,0 +1,82 @@
+// kd_decode.cu -- stage 1 of the hot path on the GPU: batched kd-tree stream decode into 8-bit
+// bricks placed inside a device slab.  Replaces the reference's CPU
+// VolumeKdtree::levelCut (/root/reference/volume_renderer/VolumeKdTree_recover.cpp:726-835) and the
+// brick placement of VolumeReader::LoadBricksToTexture (VolumeReader.h:184-205).
+//
+// Launch shape: one CTA per (brick, tile); a tile is the box of a depth-Dt tree node (32x32x16 for
+// a 256x256x128 brick), at most 2^14 voxels.  256 parser threads, one per depth-Dl leaf subtree
+// (4x4x4 voxels), walk their stream segments independently (kd_decode_core.h), writing path-ordered
+// strips in shared memory; the CTA then gathers the strips into 16-byte row segments and stores
+// them with 128-bit writes, so every 32-byte DRAM sector of the slab is written exactly once.
+#include <cuda_runtime.h>
+
+#include "kd_decode.h"
+#include "kd_decode_core.h"
+
+namespace vr {
+
+struct DecodeParams {
+  vr_kd_geom g;
+  const vr_kd_job* jobs;
+  uint8_t* dst;
+  int64_t rowPitch;    // slab X
+  int64_t slicePitch;  // slab X*Y
+  int vec16;
+};
+
+__global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
+  extern __shared__ __align__(16) uint8_t strips[];
+  __shared__ int64_t sTileBase;
+  const vr_kd_geom& g = p.g;
+  const uint32_t brick = blockIdx.x >> g.Dt;
+  const uint32_t tile = blockIdx.x & ((1u << g.Dt) - 1u);
+  const vr_kd_job& job = p.jobs[brick];
+  const uint32_t blk = __ldg(job.tileLeafBlock + tile);
+  if (threadIdx.x == 0) {
+    int ox, oy, oz;
+    vr_tile_origin(g, tile, &ox, &oy, &oz);
+    sTileBase = job.dstOffset + (int64_t)oz * p.slicePitch + (int64_t)oy * p.rowPitch + ox;
+  }
+  const uint32_t items = vr_tile_items(g);
+  if (blk == VR_PRUNED) {  // constant tile: pure fill
+    const int val = job.tileVal[tile];
+    __syncthreads();
+    uint8_t* dst = p.dst + sTileBase;
+    for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
+      vr_tile_fill_item(g, it, val, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
+    return;
+  }
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  if (threadIdx.x < lpt) vr_tile_phase1(job, g, blk, threadIdx.x, strips);
+  __syncthreads();
+  uint8_t* dst = p.dst + sTileBase;
+  for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
+    vr_tile_phase2_item(g, it, strips, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
+}
+
+size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
+  const size_t lpt = size_t(1) << (g.tileBits - g.leafBits);
+  return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
+}
+
+cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int nBricks, uint8_t* dst,
+                             int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream) {
+  if (nBricks <= 0) return cudaSuccess;
+  DecodeParams p;
+  p.g = g;
+  p.jobs = jobsDev;
+  p.dst = dst;
+  p.rowPitch = rowPitch;
+  p.slicePitch = slicePitch;
+  p.vec16 = vec16 ? 1 : 0;
+  const size_t smem = kd_decode_smem_bytes(g);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const unsigned grid = (unsigned)nBricks << g.Dt;
+  kd_decode_tiles_kernel<<<grid, 256, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace vr

@@ -1,0 +1,13 @@
+// kd_decode.h -- launch interface of the CUDA stream decoder (kd_decode.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include "kd_common.h"
+#include "kd_decode_core.h"
+
+namespace vr {
+size_t kd_decode_smem_bytes(const vr_kd_geom& g);
+// Decodes nBricks prepared streams (jobsDev[i]) into dst (slab, x fastest; rowPitch = slab X,
+// slicePitch = slab X*Y).  Asynchronous on `stream`.
+cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int nBricks, uint8_t* dst,
+                             int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream);
+}  // namespace vr

@@ -1,0 +1,264 @@
+// kd_decode_core.h -- the per-thread pieces of the GPU stream decoder, written as host/device
+// code so the same source is exercised thread-by-thread on the CPU by tests/emu (test harness only)
+// and compiled into kd_decode.cu for the device.
+//
+// What it decodes: the preorder 2-bit stream consumed by the reference's
+// VolumeKdtree::levelCut (/root/reference/volume_renderer/VolumeKdTree_recover.cpp:726-835):
+//   node above origTreeDepth : 3 = constant box, else two children follow (left then right)
+//   node at origTreeDepth    : 3 = voxel equals parent, else a refinement chain follows
+//   chain (<= 7 symbols)     : 3 terminates, else saturating +/- distanceMap[depth]
+// One parser thread owns one "leaf subtree" (root at depth Dl, 2^leafBits voxels) whose start
+// offset and root value come from the side index (kd_stream.h).  It writes its voxels in PATH
+// order into a private, padded shared-memory strip; a second phase gathers strips into x-fastest
+// 16-byte row segments of the destination slab.
+#pragma once
+#include "kd_common.h"
+
+#if defined(__CUDA_ARCH__)
+#define VR_CTZ32(x) (__ffs((int)(x)) - 1)
+#define VR_LDG32(p) __ldg(p)
+#else
+#define VR_CTZ32(x) __builtin_ctz((unsigned)(x))
+#define VR_LDG32(p) (*(p))
+#endif
+
+#define VR_LEAF_PITCH_PAD 4  // strip pitch = 2^leafBits + 4 bytes (keeps strips on distinct banks)
+
+// Per-brick decode job, resident in device memory.
+typedef struct vr_kd_job {
+  const uint32_t* words;         // packed stream, 4-byte aligned, padded by >= 16 readable bytes
+  const uint32_t* tileLeafBlock; // [2^Dt]
+  const uint8_t* tileVal;        // [2^Dt]
+  const uint32_t* leafOff;       // [liveTiles * leavesPerTile]
+  const uint8_t* leafVal;        // [liveTiles * leavesPerTile]
+  uint64_t treeDist;             // byte h = distanceMap[D0 - h] for h = 0..leafBits (levels inside a leaf subtree)
+  uint64_t chainDist;            // byte k-1 = distanceMap[D0 + k] for k = 1..7
+  int64_t dstOffset;             // voxel offset of the brick's (0,0,0) inside the destination slab
+} vr_kd_job;
+
+// Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
+struct VrBitReader {
+  const uint32_t* w;
+  uint64_t win;
+  int have;
+  uint32_t idx;
+  VR_HD void init(const uint32_t* words, uint32_t sym) {
+    w = words;
+    idx = sym >> 4;
+    int sh = (int)(sym & 15) * 2;
+    win = (uint64_t)VR_LDG32(w + idx) >> sh;
+    have = 32 - sh;
+    ++idx;
+    win |= (uint64_t)VR_LDG32(w + idx) << have;
+    have += 32;
+    ++idx;
+  }
+  VR_HD int take() {
+    int c = (int)(win & 3);
+    win >>= 2;
+    have -= 2;
+    if (have <= 32) {
+      win |= (uint64_t)VR_LDG32(w + idx) << have;
+      have += 32;
+      ++idx;
+    }
+    return c;
+  }
+};
+
+// Path-ordered byte sink with 4-byte packing.  Voxels arrive in increasing path index.
+struct VrStripSink {
+  uint8_t* buf;  // 4-byte aligned
+  uint32_t acc;
+  VR_HD void init(uint8_t* b) { buf = b; acc = 0; }
+  VR_HD void put(uint32_t v, int val) {
+    acc |= (uint32_t)val << (8 * (v & 3));
+    if ((v & 3) == 3) {
+      *reinterpret_cast<uint32_t*>(buf + (v & ~3u)) = acc;
+      acc = 0;
+    }
+  }
+  VR_HD void fill(uint32_t v, uint32_t cnt, int val) {
+    if (cnt >= 4) {  // v is a multiple of cnt, hence of 4
+      uint32_t word = (uint32_t)val * 0x01010101u;
+      for (uint32_t i = 0; i < cnt; i += 4) *reinterpret_cast<uint32_t*>(buf + v + i) = word;
+    } else {
+      for (uint32_t i = 0; i < cnt; ++i) put(v + i, val);
+    }
+  }
+  VR_HD void finish(uint32_t total) {  // strips shorter than one word
+    if (total < 4)
+      for (uint32_t i = 0; i < total; ++i) buf[i] = (uint8_t)(acc >> (8 * i));
+  }
+};
+
+// Refinement chain below a depth-D0 node whose own value is `val` (VolumeKdTree_recover.cpp:806-833
+// for depth >= origTreeDepth): up to 7 symbols, 3 terminates, no terminator after the 7th.
+template <typename Reader>
+VR_HD int vr_decode_chain(Reader& rd, int val, uint64_t chainDist) {
+#pragma unroll 1
+  for (int k = 0; k < VR_ADD_LEVELS; ++k) {
+    int c = rd.take();
+    if (c == 3) break;
+    val = vr_apply(val, c, (int)((chainDist >> (8 * k)) & 0xFF));
+  }
+  return val;
+}
+
+// Decodes the leaf subtree whose root symbol the reader is positioned on.  The root is known to be
+// an internal node (symbol != 3) with decoded value `ownVal`.
+template <typename Reader, typename Sink>
+VR_HD void vr_decode_leaf(Reader& rd, int leafBits, int ownVal, uint64_t treeDist, uint64_t chainDist,
+                          Sink& sink) {
+  const uint32_t total = 1u << leafBits;
+  (void)rd.take();  // the root's own symbol; its effect is already in ownVal
+  if (leafBits == 0) {
+    sink.put(0, vr_decode_chain(rd, ownVal, chainDist));
+    sink.finish(total);
+    return;
+  }
+  uint64_t vals = (uint64_t)ownVal << (8 * leafBits);  // byte h = value of the path node at height h
+  int h = leafBits - 1;
+  uint32_t v = 0;
+  for (;;) {
+    const int c = rd.take();
+    const int pv = (int)((vals >> (8 * (h + 1))) & 0xFF);
+    if (c == 3) {
+      sink.fill(v, 1u << h, pv);
+      v += 1u << h;
+    } else {
+      const int val = vr_apply(pv, c, (int)((treeDist >> (8 * h)) & 0xFF));
+      if (h > 0) {
+        vals = (vals & ~((uint64_t)0xFF << (8 * h))) | ((uint64_t)val << (8 * h));
+        --h;
+        continue;
+      }
+      sink.put(v, vr_decode_chain(rd, val, chainDist));
+      v += 1;
+    }
+    if (v == total) break;
+    h = VR_CTZ32(v);
+  }
+  sink.finish(total);
+}
+
+// ---- phase 1: one parser thread ----------------------------------------------------------------
+// strips: shared memory, leavesPerTile strips of pitch (2^leafBits + VR_LEAF_PITCH_PAD) bytes.
+VR_HD void vr_tile_phase1(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf,
+                          uint8_t* strips) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  VrStripSink sink;
+  sink.init(strips + (size_t)leaf * pitch);
+  if (off == VR_PRUNED) {
+    sink.fill(0, 1u << g.leafBits, val);
+    sink.finish(1u << g.leafBits);
+    return;
+  }
+  VrBitReader rd;
+  rd.init(job.words, off);
+  vr_decode_leaf(rd, g.leafBits, val, job.treeDist, job.chainDist, sink);
+}
+
+// Tile-local path index of tile-local voxel (x,y,z).
+VR_HD uint32_t vr_path_of(const vr_kd_geom& g, int x, int y, int z) {
+  uint32_t p = 0;
+  for (int j = 0; (1 << j) < g.tx; ++j) p |= (uint32_t)((x >> j) & 1) << g.pathBit[0][j];
+  for (int j = 0; (1 << j) < g.ty; ++j) p |= (uint32_t)((y >> j) & 1) << g.pathBit[1][j];
+  for (int j = 0; (1 << j) < g.tz; ++j) p |= (uint32_t)((z >> j) & 1) << g.pathBit[2][j];
+  return p;
+}
+
+// Tile origin (brick-local voxel coordinates) of tile slot t (path prefix of Dt bits).
+VR_HD void vr_tile_origin(const vr_kd_geom& g, uint32_t t, int* ox, int* oy, int* oz) {
+  int o[3] = {0, 0, 0};
+  for (int d = 0; d < g.Dt; ++d)
+    if ((t >> (g.Dt - 1 - d)) & 1) o[g.splitDim[d]] += g.childOff[d];
+  *ox = o[0]; *oy = o[1]; *oz = o[2];
+}
+
+VR_HD uint32_t vr_strip_addr(const vr_kd_geom& g, uint32_t path) {
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  return (path >> g.leafBits) * pitch + (path & ((1u << g.leafBits) - 1));
+}
+
+// Strip-address contribution of tile path bit b (strip address is linear over path bits).
+VR_HD uint32_t vr_bit_addr(const vr_kd_geom& g, int b) {
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  return b < g.leafBits ? (1u << b) : (pitch << (b - g.leafBits));
+}
+
+// ---- phase 2: gather strips into x-fastest rows of the destination ------------------------------
+// Work item `item` of a tile: a run of `seg` (= min(16, tx)) voxels along x at tile-local (x0,y,z).
+// dst points at the tile origin inside the slab; rowPitch / slicePitch are the slab's y and z strides.
+// When vec16 is set (seg == 16 and every address 16-byte aligned) one 128-bit store is issued.
+VR_HD void vr_tile_phase2_item(const vr_kd_geom& g, uint32_t item, const uint8_t* strips, uint8_t* dst,
+                               int64_t rowPitch, int64_t slicePitch, bool vec16) {
+  const int seg = g.tx < 16 ? g.tx : 16;
+  const int segsPerRow = g.tx / seg;
+  const int x0 = (int)(item % (uint32_t)segsPerRow) * seg;
+  const int y = (int)((item / (uint32_t)segsPerRow) % (uint32_t)g.ty);
+  const int z = (int)(item / (uint32_t)(segsPerRow * g.ty));
+  uint32_t base = 0;
+  for (int j = 4; (1 << j) < g.tx; ++j) base += ((x0 >> j) & 1) ? vr_bit_addr(g, g.pathBit[0][j]) : 0u;
+  for (int j = 0; (1 << j) < g.ty; ++j) base += ((y >> j) & 1) ? vr_bit_addr(g, g.pathBit[1][j]) : 0u;
+  for (int j = 0; (1 << j) < g.tz; ++j) base += ((z >> j) & 1) ? vr_bit_addr(g, g.pathBit[2][j]) : 0u;
+  uint32_t a[4] = {0, 0, 0, 0};
+  for (int j = 0; j < 4 && (1 << j) < g.tx; ++j) a[j] = vr_bit_addr(g, g.pathBit[0][j]);
+  uint8_t* out = dst + (int64_t)z * slicePitch + (int64_t)y * rowPitch + x0;
+  if (vec16) {
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t r = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int xi = q * 4 + i;
+        const uint32_t ad = base + ((xi & 1) ? a[0] : 0u) + ((xi & 2) ? a[1] : 0u) + ((xi & 4) ? a[2] : 0u) +
+                            ((xi & 8) ? a[3] : 0u);
+        r |= (uint32_t)strips[ad] << (8 * i);
+      }
+      w[q] = r;
+    }
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<uint4*>(out) = make_uint4(w[0], w[1], w[2], w[3]);
+#else
+    for (int q = 0; q < 4; ++q)
+      for (int i = 0; i < 4; ++i) out[q * 4 + i] = (uint8_t)(w[q] >> (8 * i));
+#endif
+  } else {
+    for (int xi = 0; xi < seg; ++xi) {
+      const uint32_t ad = base + ((xi & 1) ? a[0] : 0u) + ((xi & 2) ? a[1] : 0u) + ((xi & 4) ? a[2] : 0u) +
+                          ((xi & 8) ? a[3] : 0u);
+      out[xi] = strips[ad];
+    }
+  }
+}
+
+// Constant tile: same work items, value `val`.
+VR_HD void vr_tile_fill_item(const vr_kd_geom& g, uint32_t item, int val, uint8_t* dst, int64_t rowPitch,
+                             int64_t slicePitch, bool vec16) {
+  const int seg = g.tx < 16 ? g.tx : 16;
+  const int segsPerRow = g.tx / seg;
+  const int x0 = (int)(item % (uint32_t)segsPerRow) * seg;
+  const int y = (int)((item / (uint32_t)segsPerRow) % (uint32_t)g.ty);
+  const int z = (int)(item / (uint32_t)(segsPerRow * g.ty));
+  uint8_t* out = dst + (int64_t)z * slicePitch + (int64_t)y * rowPitch + x0;
+  if (vec16) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t w = (uint32_t)val * 0x01010101u;
+    *reinterpret_cast<uint4*>(out) = make_uint4(w, w, w, w);
+#else
+    for (int i = 0; i < 16; ++i) out[i] = (uint8_t)val;
+#endif
+  } else {
+    for (int xi = 0; xi < seg; ++xi) out[xi] = (uint8_t)val;
+  }
+}
+
+VR_HD uint32_t vr_tile_items(const vr_kd_geom& g) {
+  const int seg = g.tx < 16 ? g.tx : 16;
+  return (uint32_t)((g.tx / seg) * g.ty * g.tz);
+}
