@@ -1,0 +1,120 @@
+/* vr_b200.h -- C ABI of the B200-native VolumeRenderer hot path (libvr_b200.so).
+ *
+ * Drop-in boundary for the reference's three C++ surfaces; every entry point cites
+ * the reference interface it replaces (paths relative to /root/reference/volume_renderer/).
+ * Conventions: plain pointers and sizes only; every function returns an int status (VR_OK = 0,
+ * never throws or exits across the boundary -- the reference exit(-1)s on a missing tree file,
+ * VolumeKdTree_recover.cpp:560-565, and throws on a brick size mismatch, VolumeReader.h:258-260);
+ * host buffers are caller-owned; device buffers are library-owned unless wrapped; one CUDA stream
+ * per context; handles are not thread-safe.  There is no CPU fallback: decode and render fail with
+ * VR_ERR_CUDA when no device is usable.
+ */
+#ifndef VR_B200_H
+#define VR_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VR_OK 0
+#define VR_ERR_ARG 1
+#define VR_ERR_IO 2
+#define VR_ERR_FORMAT 3
+#define VR_ERR_CUDA 4
+#define VR_ERR_UNSUPPORTED 5
+#define VR_ERR_STATE 6
+
+typedef struct vr_context vr_context; /* device ordinal + CUDA stream                          */
+typedef struct vr_stream vr_stream;   /* one kd-tree stream = state of a reference VolumeKdtree */
+typedef struct vr_volume vr_volume;   /* device slab, x fastest = the reference's 3-D texture   */
+typedef struct vr_decode_plan vr_decode_plan;
+
+/* 88-byte container header exactly as VolumeKdtree::save writes it (VolumeKdTree_recover.cpp:535-542) */
+#pragma pack(push, 1)
+typedef struct vr_stream_header {
+  int64_t rootMin[3];
+  int64_t rootMax[3];
+  int32_t maxTreeDepth;
+  int32_t origTreeDepth;
+  int64_t X, Y, Z;
+  int64_t numActiveNodes;
+} vr_stream_header;
+#pragma pack(pop)
+
+typedef struct vr_build_stats {
+  int32_t maxErrorBeforeGrowth; /* "Before branch growth, Maximum Error" VolumeKdTree_recover.cpp:76 */
+  int32_t maxError;             /* "Maximum Error" :120 */
+  double meanL1, meanL2;        /* :129 */
+  int64_t zeroRunRewrites;      /* firings of the zeroStartIdx rewrite (:684-689); expected 0 */
+} vr_build_stats;
+
+const char* vr_last_error(void); /* message of the last failing call on this thread */
+const char* vr_version(void);
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* Replaces the GL context + window set-up of main.cpp:84-135 with a headless CUDA device binding. */
+int vr_context_create(int device, vr_context** out);
+int vr_context_destroy(vr_context* ctx);
+/* Use an externally created cudaStream_t (e.g. torch's current stream) for all later calls. */
+int vr_context_set_stream(vr_context* ctx, void* cuda_stream);
+int vr_context_synchronize(vr_context* ctx);
+
+/* ---- stream container: VolumeKdtree::save / open (VolumeKdTree_recover.cpp:521-594) ---------- */
+int vr_stream_from_memory(const vr_stream_header* hdr, const uint8_t* distanceMap, const uint8_t* bits,
+                          int64_t nbytes, vr_stream** out);
+int vr_stream_open(const char* path, vr_stream** out); /* accepts exact and +8-byte-slack files (SURVEY C-3) */
+int vr_stream_save(const vr_stream* s, const char* path);
+int vr_stream_destroy(vr_stream* s);
+/* public fields of class VolumeKdtree (VolumeKdtree_recover.h:57-79) */
+int vr_stream_get_header(const vr_stream* s, vr_stream_header* hdr);
+int vr_stream_get_distance_map(const vr_stream* s, uint8_t* out, int32_t cap); /* maxTreeDepth+1 bytes */
+int vr_stream_get_bits(const vr_stream* s, const uint8_t** bits, int64_t* nbytes); /* TwoBitArray::bits */
+/* full grammar walk: VR_OK iff exactly numActiveNodes symbols parse */
+int vr_stream_validate(const vr_stream* s, int64_t* nodesConsumed);
+/* builds the derived decode index (side table of subtree offsets); idempotent */
+int vr_stream_prepare(vr_stream* s);
+/* bytes of the device image: [0] stream words, [1] index */
+int vr_stream_device_bytes(const vr_stream* s, int64_t out[2]);
+/* page-lock the host image so uploads run at full PCIe rate */
+int vr_stream_pin(vr_stream* s);
+/* H2D copy of stream + index (asynchronous on the context stream); implies prepare */
+int vr_stream_upload(vr_context* ctx, vr_stream* s);
+
+/* ---- codec: VolumeKdtree(in,x,y,z) + setErrorTolerance + setMaxEpochs + build ----------------- */
+/* (VolumeKdtree_recover.h:103,126,167,175; VolumeKdTree_recover.cpp:17-140).  CPU, reference
+ * algorithm, byte-identical streams; `brick` is not modified (the reference empties its input). */
+int vr_kd_compress(const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tolerance, int maxEpochs,
+                   vr_stream** out, vr_build_stats* stats);
+
+/* ---- volume (device slab) --------------------------------------------------------------------- */
+/* Replaces VolumeReader::data + textureId (VolumeReader.h:42-51): an SX*SY*SZ uint8 array. */
+int vr_volume_create(vr_context* ctx, int64_t SX, int64_t SY, int64_t SZ, vr_volume** out);
+int vr_volume_wrap(vr_context* ctx, void* device_ptr, int64_t SX, int64_t SY, int64_t SZ, vr_volume** out);
+int vr_volume_destroy(vr_volume* v);
+int vr_volume_device_ptr(const vr_volume* v, void** ptr);
+int vr_volume_dims(const vr_volume* v, int64_t dims[3]);
+int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host); /* synchronous */
+/* LoadBrickToTexture / LoadBricksToTexture raw path (VolumeReader.h:91-107,151-223): place one raw
+ * brick (BX*BY*BZ, x fastest) at voxel origin (ox,oy,oz) of the slab; 64-bit indexing (SURVEY C-12). */
+int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, int64_t BX, int64_t BY,
+                           int64_t BZ, int64_t ox, int64_t oy, int64_t oz);
+
+/* ---- stage 1: decode = VolumeKdtree::levelCut (VolumeKdTree_recover.cpp:726-835) --------------- */
+/* Plan a batched decode of n uploaded streams (all of one brick shape) into `dst`; origins holds
+ * 3*n voxel coordinates (brick b of the reference grid sits at (i*X, j*Y, k*Z), main.cpp:599-619). */
+int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n, const int64_t* origins,
+                          vr_volume* dst, vr_decode_plan** out);
+int vr_decode_plan_run(vr_decode_plan* plan); /* one kernel launch, asynchronous */
+int vr_decode_plan_destroy(vr_decode_plan* plan);
+/* algorithmic bytes of one run: [0] stream bytes read, [1] voxel bytes written, [2] index bytes read */
+int vr_decode_plan_bytes(const vr_decode_plan* plan, int64_t out[3]);
+/* End-to-end levelCut: host stream -> host voxels (upload, decode, download; synchronous).
+ * cutDepth must equal maxTreeDepth: any other depth crashes the reference and is
+ * rejected with VR_ERR_UNSUPPORTED. */
+int vr_kd_levelcut(vr_context* ctx, vr_stream* s, int32_t cutDepth, uint8_t* out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VR_B200_H */

@@ -1,0 +1,76 @@
+// TEST HARNESS ONLY.  Runs the device decode logic of volumerenderer_b200/csrc/kd_decode_core.h on the
+// CPU, CTA by CTA and thread by thread (phase 1 for every thread, then phase 2), so the parser and
+// the strip->row gather can be checked against the oracle without a GPU.  Never linked into the
+// product library.
+#include <cstring>
+#include <vector>
+#include "../../volumerenderer_b200/csrc/kd_stream.h"
+#include "../../volumerenderer_b200/csrc/kd_decode_core.h"
+
+using namespace vr;
+
+extern "C" {
+// compress with the product's CPU compressor; returns a heap KdStream*
+void* emu_compress(const uint8_t* vol, long long X, long long Y, long long Z, int tol, int epochs, long long* zeroRewrites) {
+  KdStream* s = new KdStream;
+  KdBuildStats st;
+  if (kd_compress(vol, X, Y, Z, tol, epochs, s, &st) != VR_OK) { delete s; return nullptr; }
+  if (zeroRewrites) *zeroRewrites = st.zeroRunRewrites;
+  return s;
+}
+void* emu_from_memory(const vr_kd_header* h, const uint8_t* dm, const uint8_t* bits, long long n) {
+  KdStream* s = new KdStream;
+  if (kd_from_memory(h, dm, bits, n, s) != VR_OK) { delete s; return nullptr; }
+  return s;
+}
+void emu_free(void* p) { delete static_cast<KdStream*>(p); }
+void emu_meta(void* p, long long* m) {
+  KdStream* s = static_cast<KdStream*>(p);
+  m[0] = s->hdr.maxTreeDepth; m[1] = s->hdr.origTreeDepth; m[2] = s->hdr.X; m[3] = s->hdr.Y; m[4] = s->hdr.Z;
+  m[5] = s->hdr.numActiveNodes; m[6] = (long long)s->bits.size();
+}
+void emu_get(void* p, uint8_t* dm, uint8_t* bits) {
+  KdStream* s = static_cast<KdStream*>(p);
+  std::memcpy(dm, s->distanceMap.data(), s->distanceMap.size());
+  std::memcpy(bits, s->bits.data(), s->bits.size());
+}
+int emu_validate(void* p, long long* nodes) {
+  int64_t n = 0; int rc = kd_validate(*static_cast<KdStream*>(p), &n); *nodes = n; return rc;
+}
+// prepare + emulate the tile kernel into a slab of dims (SX,SY,SZ) at origin (ox,oy,oz)
+int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ, long long ox, long long oy, long long oz, int vec16) {
+  KdStream* s = static_cast<KdStream*>(p);
+  int rc = kd_prepare(s);
+  if (rc != VR_OK) return rc;
+  const vr_kd_geom& g = s->geom;
+  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 4, 0);
+  std::memcpy(words.data(), s->bits.data(), s->bits.size());
+  vr_kd_job job;
+  job.words = words.data();
+  job.tileLeafBlock = s->index.tileLeafBlock.data();
+  job.tileVal = s->index.tileVal.data();
+  job.leafOff = s->index.leafOff.data();
+  job.leafVal = s->index.leafVal.data();
+  job.treeDist = 0; job.chainDist = 0;
+  for (int h = 0; h <= g.leafBits && h < 8; ++h) job.treeDist |= (uint64_t)s->distanceMap[g.D0 - h] << (8 * h);
+  for (int k = 1; k <= 7; ++k) job.chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
+  job.dstOffset = (oz * SY + oy) * SX + ox;
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  std::vector<uint8_t> strips(lpt * ((1u << g.leafBits) + VR_LEAF_PITCH_PAD));
+  const uint32_t items = vr_tile_items(g);
+  for (uint32_t tile = 0; tile < (1u << g.Dt); ++tile) {
+    int tox, toy, toz;
+    vr_tile_origin(g, tile, &tox, &toy, &toz);
+    uint8_t* dst = slab + job.dstOffset + ((int64_t)toz * SY + toy) * SX + tox;
+    uint32_t blk = job.tileLeafBlock[tile];
+    if (blk == VR_PRUNED) {
+      for (uint32_t it = 0; it < items; ++it) vr_tile_fill_item(g, it, job.tileVal[tile], dst, SX, SX * SY, vec16 != 0);
+      continue;
+    }
+    std::fill(strips.begin(), strips.end(), 0xEE);
+    for (uint32_t t = 0; t < lpt; ++t) vr_tile_phase1(job, g, blk, t, strips.data());
+    for (uint32_t it = 0; it < items; ++it) vr_tile_phase2_item(g, it, strips.data(), dst, SX, SX * SY, vec16 != 0);
+  }
+  return VR_OK;
+}
+}

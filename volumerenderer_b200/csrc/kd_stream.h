@@ -42,15 +42,15 @@ struct KdStream {
   int64_t streamBytes() const { return (hdr.numActiveNodes + 3) / 4; }
 };
 
-enum {
-  VR_OK = 0,
-  VR_ERR_ARG = 1,        // bad argument / null pointer
-  VR_ERR_IO = 2,         // file missing or short
-  VR_ERR_FORMAT = 3,     // header inconsistent, non power-of-two extents, grammar violation
-  VR_ERR_CUDA = 4,       // CUDA runtime error (see vr_last_error)
-  VR_ERR_UNSUPPORTED = 5,// e.g. levelCut with cutDepth != maxTreeDepth (crashes in the reference)
-  VR_ERR_STATE = 6       // call order (decode before prepare, render before volume, ...)
-};
+#ifndef VR_OK  // same values as include/vr_b200.h
+#define VR_OK 0
+#define VR_ERR_ARG 1          // bad argument / null pointer
+#define VR_ERR_IO 2           // file missing or short
+#define VR_ERR_FORMAT 3       // header inconsistent, non power-of-two extents, grammar violation
+#define VR_ERR_CUDA 4         // CUDA runtime error (see vr_last_error)
+#define VR_ERR_UNSUPPORTED 5  // e.g. levelCut with cutDepth != maxTreeDepth (crashes in the reference)
+#define VR_ERR_STATE 6        // call order (decode before prepare, render before volume, ...)
+#endif
 
 // Container -----------------------------------------------------------------------------------
 int kd_from_memory(const vr_kd_header* hdr, const uint8_t* distanceMap, const uint8_t* bits,

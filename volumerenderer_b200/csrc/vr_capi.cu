@@ -1,0 +1,143 @@
+// vr_capi.cu -- the C ABI (include/vr_b200.h) over the C++/CUDA implementation.  No CPU fallback:
+// every decode/render entry point needs a usable CUDA device and reports VR_ERR_CUDA otherwise.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vr_b200.h"
+#include "kd_decode.h"
+#include "kd_stream.h"
+#include "vr_internal.h"
+
+using namespace vr;
+
+static thread_local std::string g_err;
+namespace vr {
+int fail(int code, const char* msg) { g_err = msg ? msg : ""; return code; }
+int fail_cuda(cudaError_t e, const char* where) {
+  g_err = std::string(where) + ": " + cudaGetErrorString(e);
+  return VR_ERR_CUDA;
+}
+}  // namespace vr
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
+
+static_assert(sizeof(vr_stream_header) == sizeof(vr_kd_header) && sizeof(vr_kd_header) == 88, "container header is 88 bytes");
+
+extern "C" {
+
+const char* vr_last_error(void) { return g_err.c_str(); }
+const char* vr_version(void) { return "vr_b200 0.1 (sm_100a)"; }
+
+// ---- context ------------------------------------------------------------------------------------
+int vr_context_create(int device, vr_context** out) {
+  if (!out) return fail(VR_ERR_ARG, "vr_context_create: null out");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceCount");
+  if (device < 0 || device >= n) return fail(VR_ERR_CUDA, "vr_context_create: no such CUDA device");
+  CU(cudaSetDevice(device));
+  vr_context* c = new vr_context;
+  c->device = device;
+  c->ownsStream = true;
+  e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete c; return fail_cuda(e, "cudaStreamCreate"); }
+  *out = c;
+  return VR_OK;
+}
+int vr_context_destroy(vr_context* c) {
+  if (!c) return VR_OK;
+  cudaSetDevice(c->device);
+  if (c->ownsStream) cudaStreamDestroy(c->stream);
+  delete c;
+  return VR_OK;
+}
+int vr_context_set_stream(vr_context* c, void* s) {
+  if (!c) return fail(VR_ERR_ARG, "null context");
+  if (c->ownsStream) cudaStreamDestroy(c->stream);
+  c->ownsStream = false;
+  c->stream = (cudaStream_t)s;
+  return VR_OK;
+}
+int vr_context_synchronize(vr_context* c) {
+  if (!c) return fail(VR_ERR_ARG, "null context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+
+// ---- stream container -----------------------------------------------------------------------------
+int vr_stream_from_memory(const vr_stream_header* hdr, const uint8_t* dm, const uint8_t* bits, int64_t nbytes,
+                          vr_stream** out) {
+  if (!out) return fail(VR_ERR_ARG, "null out");
+  vr_stream* s = new vr_stream;
+  int rc = kd_from_memory(reinterpret_cast<const vr_kd_header*>(hdr), dm, bits, nbytes, &s->kd);
+  if (rc != VR_OK) { delete s; return fail(rc, "vr_stream_from_memory: bad header or short bit array"); }
+  *out = s;
+  return VR_OK;
+}
+int vr_stream_open(const char* path, vr_stream** out) {
+  if (!out) return fail(VR_ERR_ARG, "null out");
+  vr_stream* s = new vr_stream;
+  int rc = kd_open(path, &s->kd);
+  if (rc != VR_OK) { delete s; return fail(rc, rc == VR_ERR_IO ? "Tree File does not exist or is short" : "bad tree file"); }
+  *out = s;
+  return VR_OK;
+}
+int vr_stream_save(const vr_stream* s, const char* path) {
+  if (!s) return fail(VR_ERR_ARG, "null stream");
+  int rc = kd_save(s->kd, path);
+  return rc == VR_OK ? VR_OK : fail(rc, "vr_stream_save failed (no tree to save, or I/O error)");
+}
+int vr_stream_destroy(vr_stream* s) {
+  if (!s) return VR_OK;
+  s->release();
+  delete s;
+  return VR_OK;
+}
+int vr_stream_get_header(const vr_stream* s, vr_stream_header* hdr) {
+  if (!s || !hdr) return fail(VR_ERR_ARG, "null");
+  std::memcpy(hdr, &s->kd.hdr, sizeof(*hdr));
+  return VR_OK;
+}
+int vr_stream_get_distance_map(const vr_stream* s, uint8_t* out, int32_t cap) {
+  if (!s || !out) return fail(VR_ERR_ARG, "null");
+  if (cap < (int32_t)s->kd.distanceMap.size()) return fail(VR_ERR_ARG, "distance map buffer too small");
+  std::memcpy(out, s->kd.distanceMap.data(), s->kd.distanceMap.size());
+  return VR_OK;
+}
+int vr_stream_get_bits(const vr_stream* s, const uint8_t** bits, int64_t* nbytes) {
+  if (!s || !bits || !nbytes) return fail(VR_ERR_ARG, "null");
+  *bits = s->kd.bits.data();
+  *nbytes = (int64_t)s->kd.bits.size();
+  return VR_OK;
+}
+int vr_stream_validate(const vr_stream* s, int64_t* nodes) {
+  if (!s) return fail(VR_ERR_ARG, "null stream");
+  int64_t n = 0;
+  int rc = kd_validate(s->kd, &n);
+  if (nodes) *nodes = n;
+  return rc == VR_OK ? VR_OK : fail(rc, "stream does not parse to numActiveNodes symbols");
+}
+
+int vr_kd_compress(const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tol, int epochs, vr_stream** out,
+                   vr_build_stats* stats) {
+  if (!brick || !out) return fail(VR_ERR_ARG, "null");
+  vr_stream* s = new vr_stream;
+  KdBuildStats st;
+  int rc = kd_compress(brick, X, Y, Z, tol, epochs, &s->kd, &st);
+  if (rc != VR_OK) { delete s; return fail(rc, "vr_kd_compress: extents must be powers of two"); }
+  if (stats) {
+    stats->maxErrorBeforeGrowth = st.maxErrorBeforeGrowth;
+    stats->maxError = st.maxError;
+    stats->meanL1 = st.meanL1;
+    stats->meanL2 = st.meanL2;
+    stats->zeroRunRewrites = st.zeroRunRewrites;
+  }
+  *out = s;
+  return VR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,230 @@
+// vr_capi_device.cu -- device-side half of the C ABI: stream upload, volumes, decode plans, levelCut.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <new>
+
+#include "../../include/vr_b200.h"
+#include "kd_decode.h"
+#include "vr_internal.h"
+
+using namespace vr;
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
+
+static inline size_t align16(size_t v) { return (v + 15) & ~size_t(15); }
+
+void vr_stream::release() {
+  if (devImage) { if (device >= 0) cudaSetDevice(device); cudaFree(devImage); devImage = nullptr; }
+  if (hostImage) { if (pinned) cudaFreeHost(hostImage); else delete[] hostImage; hostImage = nullptr; }
+  pinned = false;
+}
+
+namespace vr {
+int stream_build_image(vr_stream* s) {
+  if (s->hostImage) return VR_OK;
+  if (!s->kd.index.built) {
+    int rc = kd_prepare(&s->kd);
+    if (rc != VR_OK) return fail(rc, "vr_stream_prepare: stream does not parse");
+  }
+  const KdIndex& ix = s->kd.index;
+  s->wordsBytes = align16((size_t)s->kd.streamBytes() + 16);
+  s->offWords = 0;
+  s->offTile = s->wordsBytes;
+  s->offLeafOff = s->offTile + align16(ix.tileLeafBlock.size() * 4);
+  s->offTileVal = s->offLeafOff + align16(ix.leafOff.size() * 4);
+  s->offLeafVal = s->offTileVal + align16(ix.tileVal.size());
+  s->imageBytes = s->offLeafVal + align16(ix.leafVal.size());
+  s->hostImage = new (std::nothrow) uint8_t[s->imageBytes];
+  if (!s->hostImage) return fail(VR_ERR_ARG, "out of host memory");
+  std::memset(s->hostImage, 0, s->imageBytes);
+  std::memcpy(s->hostImage + s->offWords, s->kd.bits.data(), (size_t)s->kd.streamBytes());
+  std::memcpy(s->hostImage + s->offTile, ix.tileLeafBlock.data(), ix.tileLeafBlock.size() * 4);
+  if (!ix.leafOff.empty()) std::memcpy(s->hostImage + s->offLeafOff, ix.leafOff.data(), ix.leafOff.size() * 4);
+  std::memcpy(s->hostImage + s->offTileVal, ix.tileVal.data(), ix.tileVal.size());
+  if (!ix.leafVal.empty()) std::memcpy(s->hostImage + s->offLeafVal, ix.leafVal.data(), ix.leafVal.size());
+  return VR_OK;
+}
+}  // namespace vr
+
+extern "C" {
+
+int vr_stream_prepare(vr_stream* s) {
+  if (!s) return fail(VR_ERR_ARG, "null stream");
+  return stream_build_image(s);
+}
+int vr_stream_device_bytes(const vr_stream* s, int64_t out[2]) {
+  if (!s || !out) return fail(VR_ERR_ARG, "null");
+  if (!s->hostImage) return fail(VR_ERR_STATE, "stream not prepared");
+  out[0] = (int64_t)s->wordsBytes;
+  out[1] = (int64_t)(s->imageBytes - s->wordsBytes);
+  return VR_OK;
+}
+int vr_stream_pin(vr_stream* s) {
+  if (!s) return fail(VR_ERR_ARG, "null stream");
+  int rc = stream_build_image(s);
+  if (rc != VR_OK) return rc;
+  if (s->pinned) return VR_OK;
+  uint8_t* p = nullptr;
+  CU(cudaHostAlloc((void**)&p, s->imageBytes, cudaHostAllocDefault));
+  std::memcpy(p, s->hostImage, s->imageBytes);
+  delete[] s->hostImage;
+  s->hostImage = p;
+  s->pinned = true;
+  return VR_OK;
+}
+int vr_stream_upload(vr_context* ctx, vr_stream* s) {
+  if (!ctx || !s) return fail(VR_ERR_ARG, "null");
+  int rc = stream_build_image(s);
+  if (rc != VR_OK) return rc;
+  CU(cudaSetDevice(ctx->device));
+  if (s->devImage && s->device != ctx->device) { cudaSetDevice(s->device); cudaFree(s->devImage); s->devImage = nullptr; cudaSetDevice(ctx->device); }
+  if (!s->devImage) { CU(cudaMalloc((void**)&s->devImage, s->imageBytes)); s->device = ctx->device; }
+  CU(cudaMemcpyAsync(s->devImage, s->hostImage, s->imageBytes, cudaMemcpyHostToDevice, ctx->stream));
+  return VR_OK;
+}
+
+// ---- volume ---------------------------------------------------------------------------------------
+int vr_volume_create(vr_context* ctx, int64_t SX, int64_t SY, int64_t SZ, vr_volume** out) {
+  if (!ctx || !out || SX <= 0 || SY <= 0 || SZ <= 0) return fail(VR_ERR_ARG, "vr_volume_create: bad argument");
+  CU(cudaSetDevice(ctx->device));
+  vr_volume* v = new vr_volume;
+  v->SX = SX; v->SY = SY; v->SZ = SZ; v->owned = true; v->device = ctx->device;
+  cudaError_t e = cudaMalloc((void**)&v->dev, (size_t)(SX * SY * SZ));
+  if (e != cudaSuccess) { delete v; return fail_cuda(e, "cudaMalloc(volume)"); }
+  *out = v;
+  return VR_OK;
+}
+int vr_volume_wrap(vr_context* ctx, void* p, int64_t SX, int64_t SY, int64_t SZ, vr_volume** out) {
+  if (!ctx || !out || !p || SX <= 0 || SY <= 0 || SZ <= 0) return fail(VR_ERR_ARG, "vr_volume_wrap: bad argument");
+  vr_volume* v = new vr_volume;
+  v->dev = (uint8_t*)p; v->SX = SX; v->SY = SY; v->SZ = SZ; v->owned = false; v->device = ctx->device;
+  *out = v;
+  return VR_OK;
+}
+int vr_volume_destroy(vr_volume* v) {
+  if (!v) return VR_OK;
+  if (v->owned && v->dev) { cudaSetDevice(v->device); cudaFree(v->dev); }
+  delete v;
+  return VR_OK;
+}
+int vr_volume_device_ptr(const vr_volume* v, void** p) {
+  if (!v || !p) return fail(VR_ERR_ARG, "null");
+  *p = v->dev;
+  return VR_OK;
+}
+int vr_volume_dims(const vr_volume* v, int64_t d[3]) {
+  if (!v || !d) return fail(VR_ERR_ARG, "null");
+  d[0] = v->SX; d[1] = v->SY; d[2] = v->SZ;
+  return VR_OK;
+}
+int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host) {
+  if (!ctx || !v || !host) return fail(VR_ERR_ARG, "null");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(host, v->dev, (size_t)(v->SX * v->SY * v->SZ), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return VR_OK;
+}
+int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, int64_t BX, int64_t BY, int64_t BZ,
+                           int64_t ox, int64_t oy, int64_t oz) {
+  if (!ctx || !v || !brick) return fail(VR_ERR_ARG, "null");
+  if (ox < 0 || oy < 0 || oz < 0 || ox + BX > v->SX || oy + BY > v->SY || oz + BZ > v->SZ)
+    return fail(VR_ERR_ARG, "brick does not fit inside the volume");
+  CU(cudaSetDevice(ctx->device));
+  cudaMemcpy3DParms p;
+  std::memset(&p, 0, sizeof(p));
+  p.srcPtr = make_cudaPitchedPtr((void*)brick, (size_t)BX, (size_t)BX, (size_t)BY);
+  p.dstPtr = make_cudaPitchedPtr((void*)v->dev, (size_t)v->SX, (size_t)v->SX, (size_t)v->SY);
+  p.dstPos = make_cudaPos((size_t)ox, (size_t)oy, (size_t)oz);
+  p.extent = make_cudaExtent((size_t)BX, (size_t)BY, (size_t)BZ);
+  p.kind = cudaMemcpyHostToDevice;
+  CU(cudaMemcpy3DAsync(&p, ctx->stream));
+  return VR_OK;
+}
+
+}  // extern "C"
+
+// ---- stage 1: decode plans ----------------------------------------------------------------------------
+extern "C" {
+
+int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n, const int64_t* origins,
+                          vr_volume* dst, vr_decode_plan** out) {
+  if (!ctx || !streams || n <= 0 || !origins || !dst || !out) return fail(VR_ERR_ARG, "vr_decode_plan_create: bad argument");
+  CU(cudaSetDevice(ctx->device));
+  const vr_kd_geom& g = streams[0]->kd.geom;
+  std::vector<vr_kd_job> jobs((size_t)n);
+  bool vec16 = (g.tx >= 16) && (dst->SX % 16 == 0) && (((uintptr_t)dst->dev) % 16 == 0);
+  vr_decode_plan* p = new vr_decode_plan;
+  p->ctx = ctx; p->geom = g; p->n = n; p->dst = dst;
+  for (int i = 0; i < n; ++i) {
+    vr_stream* s = streams[i];
+    if (!s || !s->devImage || s->device != ctx->device) { delete p; return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
+    const vr_kd_header& h = s->kd.hdr;
+    if (h.X != g.X || h.Y != g.Y || h.Z != g.Z) { delete p; return fail(VR_ERR_ARG, "all streams of a plan must share one brick shape"); }
+    const int64_t ox = origins[3 * i], oy = origins[3 * i + 1], oz = origins[3 * i + 2];
+    if (ox < 0 || oy < 0 || oz < 0 || ox + h.X > dst->SX || oy + h.Y > dst->SY || oz + h.Z > dst->SZ) {
+      delete p; return fail(VR_ERR_ARG, "brick placement outside the destination volume");
+    }
+    if (ox % 16) vec16 = false;
+    vr_kd_job& j = jobs[(size_t)i];
+    j.words = reinterpret_cast<const uint32_t*>(s->devImage + s->offWords);
+    j.tileLeafBlock = reinterpret_cast<const uint32_t*>(s->devImage + s->offTile);
+    j.leafOff = reinterpret_cast<const uint32_t*>(s->devImage + s->offLeafOff);
+    j.tileVal = s->devImage + s->offTileVal;
+    j.leafVal = s->devImage + s->offLeafVal;
+    j.treeDist = 0; j.chainDist = 0;
+    for (int hh = 0; hh <= g.leafBits && hh < 8; ++hh) j.treeDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 - hh)] << (8 * hh);
+    for (int k = 1; k <= VR_ADD_LEVELS; ++k) j.chainDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 + k)] << (8 * (k - 1));
+    j.dstOffset = (oz * dst->SY + oy) * dst->SX + ox;
+    p->bytesStream += s->kd.streamBytes() + 88 + h.maxTreeDepth + 1;
+    p->bytesVoxels += h.X * h.Y * h.Z;
+    p->bytesIndex += (int64_t)(s->imageBytes - s->wordsBytes);
+  }
+  p->vec16 = vec16;
+  cudaError_t e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
+  if (e != cudaSuccess) { delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
+  e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // jobs is a stack-lifetime buffer
+  if (e != cudaSuccess) { cudaFree(p->jobsDev); delete p; return fail_cuda(e, "upload jobs"); }
+  *out = p;
+  return VR_OK;
+}
+int vr_decode_plan_run(vr_decode_plan* p) {
+  if (!p) return fail(VR_ERR_ARG, "null plan");
+  CU(cudaSetDevice(p->ctx->device));
+  CU(kd_decode_launch(p->geom, p->jobsDev, p->n, p->dst->dev, p->dst->SX, p->dst->SX * p->dst->SY, p->vec16, p->ctx->stream));
+  return VR_OK;
+}
+int vr_decode_plan_destroy(vr_decode_plan* p) {
+  if (!p) return VR_OK;
+  cudaSetDevice(p->ctx->device);
+  cudaFree(p->jobsDev);
+  delete p;
+  return VR_OK;
+}
+int vr_decode_plan_bytes(const vr_decode_plan* p, int64_t out[3]) {
+  if (!p || !out) return fail(VR_ERR_ARG, "null");
+  out[0] = p->bytesStream; out[1] = p->bytesVoxels; out[2] = p->bytesIndex;
+  return VR_OK;
+}
+
+int vr_kd_levelcut(vr_context* ctx, vr_stream* s, int32_t cutDepth, uint8_t* out_host) {
+  if (!ctx || !s || !out_host) return fail(VR_ERR_ARG, "null");
+  if (cutDepth != s->kd.hdr.maxTreeDepth)
+    return fail(VR_ERR_UNSUPPORTED, "levelCut: only cutDepth == maxTreeDepth is decodable (the reference crashes otherwise)");
+  int rc = vr_stream_upload(ctx, s);
+  if (rc != VR_OK) return rc;
+  vr_volume* v = nullptr;
+  rc = vr_volume_create(ctx, s->kd.hdr.X, s->kd.hdr.Y, s->kd.hdr.Z, &v);
+  if (rc != VR_OK) return rc;
+  const int64_t origin[3] = {0, 0, 0};
+  vr_decode_plan* p = nullptr;
+  vr_stream* arr[1] = {s};
+  rc = vr_decode_plan_create(ctx, arr, 1, origin, v, &p);
+  if (rc == VR_OK) rc = vr_decode_plan_run(p);
+  if (rc == VR_OK) rc = vr_volume_download(ctx, v, out_host);
+  vr_decode_plan_destroy(p);
+  vr_volume_destroy(v);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,49 @@
+// vr_internal.h -- handle definitions behind the opaque C ABI types.
+#pragma once
+#include <cuda_runtime.h>
+#include <vector>
+#include "kd_decode_core.h"
+#include "kd_stream.h"
+
+struct vr_context {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool ownsStream = false;
+};
+
+// Device image of a prepared stream: one arena, sections 16-byte aligned:
+//   [words (+16 B zero pad) | tileLeafBlock | leafOff | tileVal | leafVal]
+struct vr_stream {
+  vr::KdStream kd;
+  uint8_t* hostImage = nullptr;   // pageable (new[]) or pinned (cudaHostAlloc)
+  bool pinned = false;
+  size_t imageBytes = 0;
+  size_t offWords = 0, offTile = 0, offLeafOff = 0, offTileVal = 0, offLeafVal = 0;
+  size_t wordsBytes = 0;          // stream section (algorithmic stream bytes, padded)
+  uint8_t* devImage = nullptr;
+  int device = -1;
+  void release();
+};
+
+struct vr_volume {
+  uint8_t* dev = nullptr;
+  int64_t SX = 0, SY = 0, SZ = 0;
+  bool owned = false;
+  int device = 0;
+};
+
+struct vr_decode_plan {
+  vr_context* ctx = nullptr;
+  vr_kd_geom geom;
+  vr_kd_job* jobsDev = nullptr;
+  int n = 0;
+  vr_volume* dst = nullptr;
+  bool vec16 = false;
+  int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
+};
+
+namespace vr {
+int fail(int code, const char* msg);
+int fail_cuda(cudaError_t e, const char* where);
+int stream_build_image(vr_stream* s);  // prepare + pack host image
+}

@@ -1,0 +1,286 @@
+"""Host-side mirror of the reference codec interface on top of the C ABI.
+
+`VolumeKdtree` keeps the reference's method names and argument meaning
+(/root/reference/volume_renderer/VolumeKdtree_recover.h:103-175): build, levelCut, save, open,
+setErrorTolerance, setMaxEpochs, measureMaxError, measureMeanError, queryError, and the public
+fields tree / distanceMap / maxTreeDepth / origTreeDepth / numActiveNodes / X / Y / Z.
+levelCut runs on the GPU (stage 1 of the hot path); build is the CPU reference algorithm.
+"""
+import ctypes
+from ctypes import byref, c_int64, c_void_p
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, lib
+
+
+class Context:
+    """One device + CUDA stream (vr_context)."""
+
+    def __init__(self, device=0, cuda_stream=None):
+        self.h = c_void_p()
+        check(lib.vr_context_create(int(device), byref(self.h)))
+        self.device = int(device)
+        if cuda_stream is not None:
+            check(lib.vr_context_set_stream(self.h, c_void_p(int(cuda_stream))))
+
+    def synchronize(self):
+        check(lib.vr_context_synchronize(self.h))
+
+    def close(self):
+        if self.h:
+            lib.vr_context_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Stream:
+    """One kd-tree stream (vr_stream): container fields + derived decode index."""
+
+    def __init__(self, handle):
+        self.h = handle
+
+    @classmethod
+    def from_memory(cls, header, distance_map, bits):
+        dm = np.ascontiguousarray(distance_map, dtype=np.uint8)
+        b = np.ascontiguousarray(bits, dtype=np.uint8)
+        h = c_void_p()
+        check(lib.vr_stream_from_memory(byref(header), dm.ctypes.data, b.ctypes.data, b.size, byref(h)))
+        return cls(h)
+
+    @classmethod
+    def open(cls, path):
+        h = c_void_p()
+        check(lib.vr_stream_open(str(path).encode(), byref(h)))
+        return cls(h)
+
+    @classmethod
+    def compress(cls, brick, tolerance=6, max_epochs=5):
+        """brick: uint8 array shaped (Z, Y, X) (x fastest).  Returns (Stream, BuildStats)."""
+        a = np.ascontiguousarray(brick, dtype=np.uint8)
+        assert a.ndim == 3
+        Z, Y, X = a.shape
+        h = c_void_p()
+        st = _lib.BuildStats()
+        check(lib.vr_kd_compress(a.ctypes.data, X, Y, Z, int(tolerance), int(max_epochs), byref(h), byref(st)))
+        return cls(h), st
+
+    def save(self, path):
+        check(lib.vr_stream_save(self.h, str(path).encode()))
+
+    @property
+    def header(self):
+        hd = _lib.StreamHeader()
+        check(lib.vr_stream_get_header(self.h, byref(hd)))
+        return hd
+
+    @property
+    def distance_map(self):
+        out = np.zeros(self.header.maxTreeDepth + 1, np.uint8)
+        check(lib.vr_stream_get_distance_map(self.h, out.ctypes.data, out.size))
+        return out
+
+    @property
+    def bits(self):
+        p = c_void_p()
+        n = c_int64()
+        check(lib.vr_stream_get_bits(self.h, byref(p), byref(n)))
+        return np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8)), shape=(n.value,)).copy()
+
+    def validate(self):
+        n = c_int64()
+        check(lib.vr_stream_validate(self.h, byref(n)))
+        return n.value
+
+    def prepare(self):
+        check(lib.vr_stream_prepare(self.h))
+        return self
+
+    def pin(self):
+        check(lib.vr_stream_pin(self.h))
+        return self
+
+    def device_bytes(self):
+        out = (c_int64 * 2)()
+        check(lib.vr_stream_device_bytes(self.h, out))
+        return out[0], out[1]
+
+    def upload(self, ctx):
+        check(lib.vr_stream_upload(ctx.h, self.h))
+        return self
+
+    def close(self):
+        if self.h:
+            lib.vr_stream_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Volume:
+    """Device slab (vr_volume), x fastest; numpy view order is (Z, Y, X)."""
+
+    def __init__(self, ctx, SX, SY, SZ, device_ptr=None):
+        self.ctx = ctx
+        self.h = c_void_p()
+        self.dims = (int(SX), int(SY), int(SZ))
+        if device_ptr is None:
+            check(lib.vr_volume_create(ctx.h, SX, SY, SZ, byref(self.h)))
+        else:
+            check(lib.vr_volume_wrap(ctx.h, c_void_p(int(device_ptr)), SX, SY, SZ, byref(self.h)))
+
+    @property
+    def device_ptr(self):
+        p = c_void_p()
+        check(lib.vr_volume_device_ptr(self.h, byref(p)))
+        return p.value
+
+    def download(self):
+        SX, SY, SZ = self.dims
+        out = np.empty((SZ, SY, SX), np.uint8)
+        check(lib.vr_volume_download(self.ctx.h, self.h, out.ctypes.data))
+        return out
+
+    def upload_brick(self, brick, origin):
+        a = np.ascontiguousarray(brick, dtype=np.uint8)
+        BZ, BY, BX = a.shape
+        check(lib.vr_volume_upload_brick(self.ctx.h, self.h, a.ctypes.data, BX, BY, BZ, *[int(o) for o in origin]))
+        self.ctx.synchronize()  # `a` may be a temporary
+
+    def close(self):
+        if self.h:
+            lib.vr_volume_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DecodePlan:
+    """Batched stage-1 decode of uploaded streams into a Volume (one kernel launch per run)."""
+
+    def __init__(self, ctx, streams, origins, volume):
+        self.ctx, self.streams, self.volume = ctx, list(streams), volume
+        n = len(self.streams)
+        arr = (c_void_p * n)(*[s.h for s in self.streams])
+        org = (c_int64 * (3 * n))(*[int(v) for o in origins for v in o])
+        self.h = c_void_p()
+        check(lib.vr_decode_plan_create(ctx.h, arr, n, org, volume.h, byref(self.h)))
+
+    def run(self):
+        check(lib.vr_decode_plan_run(self.h))
+
+    def bytes(self):
+        out = (c_int64 * 3)()
+        check(lib.vr_decode_plan_bytes(self.h, out))
+        return {"stream": out[0], "voxels": out[1], "index": out[2]}
+
+    def close(self):
+        if self.h:
+            lib.vr_decode_plan_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class VolumeKdtree:
+    """Reference-shaped codec object (VolumeKdtree_recover.h:49-176)."""
+
+    def __init__(self, inData=None, x=0, y=0, z=0, ctx=None):
+        self._data = None if inData is None else np.ascontiguousarray(inData, dtype=np.uint8).reshape(z, y, x)
+        self.X, self.Y, self.Z = int(x), int(y), int(z)
+        self.tolerance, self.maxEpochs = 6, 5  # defaults VolumeKdtree_recover.h:92-93,110-111
+        self._stream = None
+        self._ctx = ctx
+        self._output = None
+        self.stats = None
+
+    # -- knobs (VolumeKdTree_recover.cpp:9-15)
+    def setErrorTolerance(self, errorTolerance):
+        self.tolerance = int(errorTolerance)
+
+    def setMaxEpochs(self, epochs):
+        self.maxEpochs = int(epochs)
+
+    # -- build (VolumeKdTree_recover.cpp:17); the input array is left intact (SURVEY C-11)
+    def build(self, useThreads=True):
+        if self._data is None:
+            raise _lib.VrError(_lib.VR_ERR_STATE, "build: no input volume")
+        self._stream, self.stats = Stream.compress(self._data, self.tolerance, self.maxEpochs)
+        return self
+
+    def _need(self):
+        if self._stream is None:
+            raise _lib.VrError(_lib.VR_ERR_STATE, "no tree: call build() or open() first")
+        return self._stream
+
+    # -- public fields of the reference class
+    @property
+    def stream(self):
+        return self._need()
+
+    @property
+    def tree(self):
+        return self._need().bits
+
+    @property
+    def distanceMap(self):
+        return self._need().distance_map
+
+    @property
+    def maxTreeDepth(self):
+        return self._need().header.maxTreeDepth
+
+    @property
+    def origTreeDepth(self):
+        return self._need().header.origTreeDepth
+
+    @property
+    def numActiveNodes(self):
+        return self._need().header.numActiveNodes
+
+    def save(self, filename):
+        self._need().save(filename)
+
+    def open(self, filename):
+        self._stream = Stream.open(filename)
+        hd = self._stream.header
+        self.X, self.Y, self.Z = hd.X, hd.Y, hd.Z
+        return self
+
+    # -- stage 1 on the GPU (VolumeKdTree_recover.cpp:726)
+    def levelCut(self, cutDepth, outData=None):
+        s = self._need()
+        if self._ctx is None:
+            self._ctx = Context(0)
+        out = np.empty((self.Z, self.Y, self.X), np.uint8) if outData is None else outData
+        check(lib.vr_kd_levelcut(self._ctx.h, s.h, int(cutDepth), out.ctypes.data))
+        self._output = out
+        return out
+
+    # -- error queries (VolumeKdTree_recover.cpp:386-411); usable here because build keeps the input
+    def measureMaxError(self):
+        return int(np.abs(self._output.astype(np.int16) - self._data.astype(np.int16)).max())
+
+    def measureMeanError(self):
+        return float(np.abs(self._output.astype(np.int16) - self._data.astype(np.int16)).mean())
+
+    def queryError(self):
+        return np.abs(self._output.astype(np.int16) - self._data.astype(np.int16)).astype(np.uint8)
