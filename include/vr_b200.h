@@ -60,6 +60,12 @@ int vr_context_destroy(vr_context* ctx);
 int vr_context_set_stream(vr_context* ctx, void* cuda_stream);
 int vr_context_synchronize(vr_context* ctx);
 
+/* CUDA-event timing on the context stream (replaces DebugTimer::Begin/End, DebugTimer.cpp:6-35).
+ * slot in [0,16): begin/end record events asynchronously; elapsed synchronises on the end event. */
+int vr_timer_begin(vr_context* ctx, int slot);
+int vr_timer_end(vr_context* ctx, int slot);
+int vr_timer_elapsed_ms(vr_context* ctx, int slot, float* ms);
+
 /* ---- stream container: VolumeKdtree::save / open (VolumeKdTree_recover.cpp:521-594) ---------- */
 int vr_stream_from_memory(const vr_stream_header* hdr, const uint8_t* distanceMap, const uint8_t* bits,
                           int64_t nbytes, vr_stream** out);

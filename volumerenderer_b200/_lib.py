@@ -45,6 +45,9 @@ _SIGS = {
     "vr_context_destroy": (c_int, [c_void_p]),
     "vr_context_set_stream": (c_int, [c_void_p, c_void_p]),
     "vr_context_synchronize": (c_int, [c_void_p]),
+    "vr_timer_begin": (c_int, [c_void_p, c_int]),
+    "vr_timer_end": (c_int, [c_void_p, c_int]),
+    "vr_timer_elapsed_ms": (c_int, [c_void_p, c_int, POINTER(ctypes.c_float)]),
     "vr_stream_from_memory": (c_int, [POINTER(StreamHeader), c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),
     "vr_stream_open": (c_int, [c_char_p, POINTER(c_void_p)]),
     "vr_stream_save": (c_int, [c_void_p, c_char_p]),

@@ -51,6 +51,7 @@ int vr_context_destroy(vr_context* c) {
   if (!c) return VR_OK;
   cudaSetDevice(c->device);
   if (c->ownsStream) cudaStreamDestroy(c->stream);
+  for (auto& e : c->ev) for (auto& k : e) if (k) cudaEventDestroy(k);
   delete c;
   return VR_OK;
 }
@@ -65,6 +66,26 @@ int vr_context_synchronize(vr_context* c) {
   if (!c) return fail(VR_ERR_ARG, "null context");
   CU(cudaSetDevice(c->device));
   CU(cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+
+int vr_timer_begin(vr_context* c, int slot) {
+  if (!c || slot < 0 || slot >= 16) return fail(VR_ERR_ARG, "bad timer slot");
+  CU(cudaSetDevice(c->device));
+  for (int k = 0; k < 2; ++k)
+    if (!c->ev[slot][k]) CU(cudaEventCreate(&c->ev[slot][k]));
+  CU(cudaEventRecord(c->ev[slot][0], c->stream));
+  return VR_OK;
+}
+int vr_timer_end(vr_context* c, int slot) {
+  if (!c || slot < 0 || slot >= 16 || !c->ev[slot][1]) return fail(VR_ERR_ARG, "bad timer slot");
+  CU(cudaEventRecord(c->ev[slot][1], c->stream));
+  return VR_OK;
+}
+int vr_timer_elapsed_ms(vr_context* c, int slot, float* ms) {
+  if (!c || !ms || slot < 0 || slot >= 16 || !c->ev[slot][1]) return fail(VR_ERR_ARG, "bad timer slot");
+  CU(cudaEventSynchronize(c->ev[slot][1]));
+  CU(cudaEventElapsedTime(ms, c->ev[slot][0], c->ev[slot][1]));
   return VR_OK;
 }
 

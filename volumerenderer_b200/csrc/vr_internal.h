@@ -9,6 +9,7 @@ struct vr_context {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
+  cudaEvent_t ev[16][2] = {};
 };
 
 // Device image of a prepared stream: one arena, sections 16-byte aligned:

@@ -28,6 +28,17 @@ class Context:
     def synchronize(self):
         check(lib.vr_context_synchronize(self.h))
 
+    def timer_begin(self, slot=0):
+        check(lib.vr_timer_begin(self.h, slot))
+
+    def timer_end(self, slot=0):
+        check(lib.vr_timer_end(self.h, slot))
+
+    def timer_ms(self, slot=0):
+        ms = ctypes.c_float()
+        check(lib.vr_timer_elapsed_ms(self.h, slot, byref(ms)))
+        return ms.value
+
     def close(self):
         if self.h:
             lib.vr_context_destroy(self.h)
