@@ -120,6 +120,39 @@ int vr_decode_plan_bytes(const vr_decode_plan* plan, int64_t out[3]);
  * rejected with VR_ERR_UNSUPPORTED. */
 int vr_kd_levelcut(vr_context* ctx, vr_stream* s, int32_t cutDepth, uint8_t* out_host);
 
+/* ---- stage 2: ray marching = the reference's shader-selectable renderer -------------------------- */
+/* Mode = which fragment shader main.cpp:71-74 would load. */
+#define VR_MODE_COMPOSITE 0             /* raycaster.frag */
+#define VR_MODE_ISOSURFACE 1            /* isosurface.frag */
+#define VR_MODE_ISOSURFACE_COMPRESSED 2 /* isosurface_compressed.frag (a stub in the reference):
+                                           defined here as isosurface.frag evaluated on the volume that
+                                           levelCut produces from the streams, decoded on the device */
+
+/* Uniforms + camera of main.cpp:33-40,52,319-341,396-397.  The whole volume maps to the unit cube. */
+typedef struct vr_render_params {
+  float eye[3], front[3], up[3]; /* camPos, camFront, camUp */
+  float vfov_deg, znear, zfar;   /* perspectiveFov(radians(fov), w, h, 0.1, 100) */
+  float step_size[3];            /* uniform step_size */
+  float isoValue;                /* uniform isoValue */
+  int32_t width, height;         /* framebuffer size */
+  int32_t mode;
+} vr_render_params;
+int vr_render_defaults(vr_render_params* p); /* the reference's constants */
+/* derived camera: eye[3], right[3], up[3], forward[3], tw, th, znear, zfar, step[3], iso (20 floats) */
+int vr_camera_basis(const vr_render_params* p, float out[20]);
+/* One frame = one UnitBrick::Draw() (main.cpp:404).  Output: width*height RGBA float32 in [0,1], row 0
+ * = bottom row (GL convention), written to DEVICE memory; hit_dev (optional) = sample index of the
+ * iso hit or -1; samples_dev (optional) += number of texture-fetching march steps.  Asynchronous. */
+int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev,
+              int32_t* hit_dev, uint64_t* samples_dev);
+/* Same, result copied to HOST buffers; synchronous. */
+int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_host,
+                      int32_t* hit_host, uint64_t* samples_host);
+/* ISOSURFACE_COMPRESSED / any mode straight from streams: run the decode plan, then march its
+ * destination volume, all on the device with no host round trip. */
+int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
+                         int32_t* hit_dev, uint64_t* samples_dev);
+
 #ifdef __cplusplus
 }
 #endif
