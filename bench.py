@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- contract benchmark of the hot path (kd-tree decode -> ray-march), one process per GPU.
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W  # the reference's CPU path on the host cores
+
+Workload `rm_yslab` (BASELINE config 4 shape): the synthetic Richtmyer-Meshkov field on the
+reference's brick grid (256x256x128 bricks, grid 8x8x15).  Rank r owns the y-slab j = r: 120 bricks =
+2048x256x1920 voxels (0.94 GiB); N = 8 is exactly the full 2048x2048x1920 volume (weak scaling, no
+data-path collective for decode).  A step = stage 1 (one batched decode launch of the rank's 120 streams
+into its slab) + stage 2 (one 1024^2 colour-compositing frame of that slab).  Inputs are larger than L2
+(the slab alone is 8x the 126 MB L2), so no explicit flush is needed between iterations.
+metric: decoded GVoxel/s through the whole step (decode + frame); frames/s and G samples/s are extra keys.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BX, BY, BZ = 256, 256, 128
+GI, GK = 8, 15
+IMG = 1024
+
+
+def peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
+        self.p.terminate()
+        sel = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.05] or [r for (_, r) in self.rows[-3:]]
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in sel:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+                for nme, val in zip(names, f[2:6]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples_in_region": len([1 for (t, _) in self.rows if t0 <= t <= t1 + 0.05])}
+
+
+def slab_bricks(rank):
+    """(i, j, k) of the rank's 120 bricks, k-major so constant layers interleave with the mixing layer."""
+    return [(i, rank, k) for k in range(GK) for i in range(GI)]
+
+
+def build_streams(vr, rank, threads, want_volumes=False):
+    """Synthesise and compress the rank's bricks (CPU, untimed set-up).  Identical constant bricks are
+    compressed once and share a stream (memoised deterministic set-up, not part of any timed region)."""
+    from volumerenderer_b200 import synth
+    bricks = slab_bricks(rank)
+    const_cache, const_lock = {}, threading.Lock()
+
+    def one(ijk):
+        i, j, k = ijk
+        cv = synth.rm_brick_constant_value(i, j, k, 0)
+        if cv is not None:
+            with const_lock:
+                if cv not in const_cache:
+                    s, _ = vr.Stream.compress(synth.constant_brick(value=cv), 1, 2)
+                    const_cache[cv] = s.prepare()
+            return const_cache[cv], (synth.constant_brick(value=cv) if want_volumes else None)
+        vol = synth.rm_brick(i, j, k, 0)
+        s, _ = vr.Stream.compress(vol, 1, 2)  # tolerance 1, 2 epochs: main.cpp:253-254
+        return s.prepare(), (vol if want_volumes else None)
+
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        res = list(ex.map(one, bricks))
+    return bricks, [r[0] for r in res], [r[1] for r in res]
+
+
+def dist_setup(n_gpus):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import volumerenderer_b200 as vr
+    from volumerenderer_b200 import render
+    rank, world, local = dist_setup(args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    threads = max(1, (os.cpu_count() or 8) // max(1, world))
+    ctx = vr.Context(local)
+    t_setup = time.time()
+    bricks, streams, _ = build_streams(vr, rank, threads)
+    uniq = {id(s): s for s in streams}
+    for s in uniq.values():
+        s.pin()
+        s.upload(ctx)
+    vol = vr.Volume(ctx, GI * BX, BY, GK * BZ)
+    origins = [(i * BX, 0, k * BZ) for (i, j, k) in bricks]
+    plan = vr.DecodePlan(ctx, streams, origins, vol)
+    by = plan.bytes()
+    p = render.default_params(IMG, IMG, render.COMPOSITE)
+    out = torch.empty((IMG, IMG, 4), dtype=torch.float32, device=f"cuda:{local}")
+    cnt = torch.zeros(1, dtype=torch.int64, device=f"cuda:{local}")
+    host_img = torch.empty((IMG, IMG, 4), dtype=torch.float32).pin_memory()
+    torch.cuda.synchronize()
+    t_setup = time.time() - t_setup
+
+    def step(slot=None):
+        # slot != None: bracket each launch with its own CUDA-event pair (read back after the region)
+        if slot is None:
+            plan.run()
+            render.render_device(ctx, vol, p, out.data_ptr())
+        else:
+            ctx.timer_begin(slot); plan.run(); ctx.timer_end(slot)
+            ctx.timer_begin(slot + 1); render.render_device(ctx, vol, p, out.data_ptr()); ctx.timer_end(slot + 1)
+
+    def barrier():
+        ctx.synchronize(); torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ctx.synchronize(); torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(1)
+    # samples per frame (effective march steps reaching the fetch), counted once outside the timed region
+    cnt.zero_(); torch.cuda.synchronize()
+    render.render_device(ctx, vol, p, out.data_ptr(), None, cnt.data_ptr()); ctx.synchronize()
+    samples = int(cnt.item())
+
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t0 = time.time()
+    ctx.timer_begin(0)
+    n_probe = min(args.steps, 7)  # per-kernel event pairs on the last n_probe steps of the timed region
+    for it in range(args.steps):
+        k = it - (args.steps - n_probe)
+        step(1 + 2 * k if k >= 0 else None)
+    ctx.timer_end(0)
+    total_ms = ctx.timer_ms(0)
+    dec_ms = [ctx.timer_ms(1 + 2 * k) for k in range(n_probe)]
+    mar_ms = [ctx.timer_ms(2 + 2 * k) for k in range(n_probe)]
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    if world > 1:
+        t = torch.tensor([total_ms], device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_step = total_ms / args.steps
+    voxels_rank = by["voxels"]
+    voxels_all = voxels_rank * world
+
+    # ---- end to end through the C ABI with host buffers: H2D of the streams (pinned images), decode,
+    # frame, D2H of the RGBA frame, every step
+    h2d = sum(sum(s.device_bytes()) for s in uniq.values())
+    d2h = IMG * IMG * 16
+    e2e_steps = max(3, min(args.steps, 20))
+
+    def e2e_step():
+        for s in uniq.values():
+            s.upload(ctx)
+        plan.run()
+        render.render_device(ctx, vol, p, out.data_ptr())
+        ctx.synchronize()
+        host_img.copy_(out, non_blocking=False)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    te = time.time()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = (time.time() - te) * 1e3 / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_ms], device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier(); dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    d_ms, m_ms = float(np.mean(dec_ms)), float(np.mean(mar_ms))
+    dec_bytes = by["stream"] + by["voxels"]
+    mar_bytes = 8 * samples + 16 * IMG * IMG
+    roof_dec = {"kernel": "kd_decode_tiles_kernel", "bound": "hbm", "achieved": dec_bytes / d_ms / 1e6, "peak": peak, "unit": "GB/s",
+                "frac": dec_bytes / d_ms / 1e6 / peak, "traffic": None, "ms": d_ms, "algorithmic_bytes": dec_bytes,
+                "index_bytes": by["index"], "peak_source": peak_src}
+    roof_mar = {"kernel": "march_kernel<composite>", "bound": "hbm", "achieved": mar_bytes / m_ms / 1e6, "peak": peak, "unit": "GB/s",
+                "frac": mar_bytes / m_ms / 1e6 / peak, "traffic": None, "ms": m_ms, "algorithmic_bytes": mar_bytes,
+                "peak_source": peak_src}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            t = json.load(open(tr))
+            roof_dec["traffic"] = t.get("decode"); roof_mar["traffic"] = t.get("march")
+        except Exception:
+            pass
+    dominant = roof_dec if d_ms >= m_ms else roof_mar
+    nodes = sum(s.header.numActiveNodes for s in streams)
+    line = {
+        "metric": "decoded_gvoxels_per_s", "value": voxels_all / ms_step / 1e6, "unit": "GVoxel/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8 decode / f32 march", "data": "synthetic",
+        "config": {"workload": "rm_yslab: per GPU 120 bricks 256x256x128 (y-slab 2048x256x1920 of the synthetic "
+                               "Richtmyer-Meshkov volume, tolerance 1, 2 epochs) decoded then one 1024x1024 "
+                               "colour-compositing frame (reference camera); N=8 is the full 2048x2048x1920 volume",
+                   "bricks_per_gpu": len(streams), "image": [IMG, IMG], "bits_per_voxel": 2.0 * nodes / voxels_rank,
+                   "l2": "inputs+outputs per step (>= 1 GB) exceed the 126 MB L2; no explicit flush",
+                   "multi_gpu": "bricks sharded by y-slab, no data-path collective for decode; frames are per-slab"},
+        "stages": {"decode_ms": d_ms, "march_ms": m_ms, "decode_gvoxels_per_s": voxels_rank / d_ms / 1e6,
+                   "frames_per_s": 1e3 / m_ms, "gsamples_per_s": samples / m_ms / 1e6, "samples_per_frame": samples},
+        "roofline": dominant, "roofline_decode": roof_dec, "roofline_march": roof_mar,
+        "e2e": {"value": voxels_all / e2e_ms / 1e6, "unit": "GVoxel/s", "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps},
+        "gpu_launches": 2 * args.steps, "clocks": clocks, "setup_s": t_setup,
+    }
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU side: the reference's own levelCut (oracle/_ref, unmodified reference code) brick-parallel over
+# the host cores + the scalar shader restatement (the reference has no CPU renderer) for the frame.
+def _cpu_setup(rank, threads):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_api as oa
+    import volumerenderer_b200 as vr  # compressor only (CPU, reference algorithm); never the decode path
+    from volumerenderer_b200 import render
+    bricks, streams, _ = build_streams(vr, rank, threads)
+    handles = []  # one reference object per brick: levelCut keeps per-call state in members (not re-entrant)
+    kind = "reference" if oa.REF is not None else "port"
+    import tempfile
+    paths = {}
+    for s in streams:
+        hd = s.header
+        if kind == "reference":
+            if id(s) not in paths:
+                with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+                    paths[id(s)] = f.name
+                s.save(paths[id(s)])  # container written by our save(), opened by the reference's open()
+            handles.append(oa.REF.ref_kd_open(paths[id(s)].encode()))
+        else:
+            handles.append((s.bits, hd.numActiveNodes, s.distance_map, hd.origTreeDepth, hd.maxTreeDepth))
+    for pth in paths.values():
+        os.remove(pth)
+    return oa, render, bricks, streams, handles, kind
+
+
+def _cpu_decode(oa, kind, handles, streams, idx, threads, reps=1):
+    """levelCut of bricks idx (one brick per thread at a time); returns seconds."""
+    if kind == "reference":
+        import ctypes
+        arr = (ctypes.c_void_p * len(idx))(*[handles[b] for b in idx])
+        return oa.REF.ref_kd_levelcut_bench(arr, len(idx), reps, threads)
+    t0 = time.time()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(lambda b: oa.oracle_levelcut(*handles[b], BX, BY, BZ), idx * reps))
+    return time.time() - t0
+
+
+def _cpu_full_volume(oa, kind, handles, streams, bricks):
+    """Host copy of the decoded slab (input of the CPU frame), decoded by the oracle, untimed."""
+    slab = np.empty((GK * BZ, BY, GI * BX), np.uint8)
+    cache = {}
+    for b, (i, j, k) in enumerate(bricks):
+        key = id(streams[b])
+        if key not in cache:
+            s = streams[b]
+            hd = s.header
+            rc, dec = oa.oracle_levelcut(s.bits, hd.numActiveNodes, s.distance_map, hd.origTreeDepth, hd.maxTreeDepth, BX, BY, BZ)
+            assert rc == 0
+            cache[key] = dec
+        slab[k * BZ:(k + 1) * BZ, :, i * BX:(i + 1) * BX] = cache[key]
+    return slab
+
+
+def cpu_baseline(budget_s=20.0, steps=1, warmup=0, as_line=False, args=None):
+    threads = os.cpu_count() or 1
+    oa, render, bricks, streams, handles, kind = _cpu_setup(0, threads)
+    slab = _cpu_full_volume(oa, kind, handles, streams, bricks)
+    p = render.default_params(IMG, IMG, render.COMPOSITE)
+    blob = render.oracle_param_blob(p)
+    img = np.zeros((IMG, IMG, 4), np.float32)
+    import ctypes
+    buf = ctypes.create_string_buffer(blob, len(blob))
+
+    def one_step(m):
+        idx = list(range(0, len(bricks), m))
+        td = _cpu_decode(oa, kind, handles, streams, idx, threads)
+        t0 = time.time()
+        oa.ORACLE.oracle_render_rows(slab.ctypes.data, GI * BX, BY, GK * BZ, buf, img.ctypes.data, None, threads, m)
+        tr = time.time() - t0
+        return td, tr, len(idx)
+
+    # choose the sample stride m so that (warmup + steps) passes fit the budget
+    td, tr, _ = one_step(8)
+    est_full = (td + tr) * 8
+    m = 1
+    while est_full / m * (steps + warmup) > budget_s and m < 8:
+        m += 1
+    for _ in range(warmup):
+        one_step(m)
+    tds, trs, nb = [], [], 0
+    for _ in range(steps):
+        td, tr, nb = one_step(m)
+        tds.append(td); trs.append(tr)
+    t_step = float(np.mean(tds) + np.mean(trs))
+    vox = nb * BX * BY * BZ
+    sample = (f"every {m}th brick of the rank-0 slab ({nb} of {len(bricks)} bricks, reference levelCut, one brick per thread) + "
+              f"every {m}th row of the 1024x1024 composite frame (C++ shader restatement, rows over threads)")
+    base = {"value": vox / t_step / 1e9, "unit": "GVoxel/s", "cores": threads, "kind": kind, "sample": sample,
+            "decode_s": float(np.mean(tds)), "frame_s": float(np.mean(trs)),
+            "decode_mvoxels_per_s": vox / float(np.mean(tds)) / 1e6, "frames_per_s_full_frame": 1.0 / (float(np.mean(trs)) * m)}
+    if not as_line:
+        return base
+    line = {"impl": "reference", "metric": "decoded_gvoxels_per_s", "value": base["value"], "unit": "GVoxel/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8 decode / f32 march", "data": "synthetic",
+            "config": {"workload": "rm_yslab (see the GPU arm): bounded sample of the rank-0 slab per step", "image": [IMG, IMG]},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "GVoxel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        print(json.dumps(cpu_baseline(budget_s=150.0, steps=args.steps, warmup=args.warmup, as_line=True, args=args)), flush=True)
+        return
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

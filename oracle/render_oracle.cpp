@@ -172,8 +172,15 @@ static void shade_pixel(const Params& P, const Vol& vol, int px, int py, float* 
 extern "C" {
 // params: 29 floats then W,H,mode as int32 (see Params).  out: H*W*4 floats, row 0 = bottom row (GL).
 // hit (optional): H*W int32 sample index of the iso hit, -1 = none.  Returns samples fetched (S).
+int64_t oracle_render_rows(const uint8_t* volume, int64_t X, int64_t Y, int64_t Z, const void* params, float* out,
+                           int32_t* hit, int threads, int rowStep);
 int64_t oracle_render(const uint8_t* volume, int64_t X, int64_t Y, int64_t Z, const void* params, float* out,
                       int32_t* hit, int threads) {
+  return oracle_render_rows(volume, X, Y, Z, params, out, hit, threads, 1);
+}
+// Bounded sample for the timed CPU baseline: only rows with py % rowStep == 0 are shaded.
+int64_t oracle_render_rows(const uint8_t* volume, int64_t X, int64_t Y, int64_t Z, const void* params, float* out,
+                           int32_t* hit, int threads, int rowStep) {
   Params P;
   std::memcpy(&P, params, sizeof(P));
   Vol vol = {volume, X, Y, Z};
@@ -183,7 +190,7 @@ int64_t oracle_render(const uint8_t* volume, int64_t X, int64_t Y, int64_t Z, co
   for (int w = 0; w < threads; ++w)
     pool.emplace_back([&, w]() {
       int64_t n = 0;
-      for (int py = w; py < P.H; py += threads)
+      for (int py = w * rowStep; py < P.H; py += threads * rowStep)
         for (int px = 0; px < P.W; ++px)
           shade_pixel(P, vol, px, py, out + 4 * ((int64_t)py * P.W + px), &n, hit ? hit + (int64_t)py * P.W + px : nullptr);
       counts[(size_t)w] = n;

@@ -23,6 +23,8 @@ ORACLE.oracle_parse_container.restype = c_int
 ORACLE.oracle_parse_container.argtypes = [c_void_p, c_int64, c_void_p]
 ORACLE.oracle_render.restype = c_int64
 ORACLE.oracle_render.argtypes = [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int]
+ORACLE.oracle_render_rows.restype = c_int64
+ORACLE.oracle_render_rows.argtypes = [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int]
 
 if REF is not None:
     LL = c_longlong

@@ -74,3 +74,16 @@ def shell_brick(brick, noise=0, seed=1):
         v = v + np.random.default_rng(seed).integers(-noise, noise + 1, v.shape)
     v[r > X * 0.45] = 0
     return np.ascontiguousarray(np.clip(v, 0, 255).astype(np.uint8))
+
+
+def rm_brick_constant_value(i, j, k, t=0, brick=BRICK):
+    """0 / 230 when the whole brick lies below / above the mixing layer for every (x, y), else None
+    (bound from |H - 960| <= 60 + 40 t and half-width w = 8 + 6 t)."""
+    Z = brick[2]
+    amp, w = 60.0 + 40.0 * t, 8.0 + 6.0 * t
+    z0, z1 = k * Z, k * Z + Z - 1
+    if z1 <= 960.0 - amp - w:
+        return 0
+    if z0 >= 960.0 + amp + w:
+        return 230
+    return None
