@@ -34,6 +34,26 @@ void emu_get(void* p, uint8_t* dm, uint8_t* bits) {
   std::memcpy(dm, s->distanceMap.data(), s->distanceMap.size());
   std::memcpy(bits, s->bits.data(), s->bits.size());
 }
+// brute force: the chain table equals the sequential saturating chain for every start value
+long long emu_check_chain_lut(unsigned long long chainDist) {
+  long long bad = 0;
+  for (uint32_t codes = 0; codes < (1u << 14); ++codes) {
+    const uint32_t e = vr_chain_lut_entry(codes, chainDist);
+    for (int x = 0; x < 256; ++x) {
+      int val = x, L = 7;
+      for (int k = 0; k < 7; ++k) {
+        int c = (codes >> (2 * k)) & 3;
+        if (c == 3) { L = k + 1; break; }
+        val = vr_apply(val, c, (int)((chainDist >> (8 * k)) & 0xFF));
+      }
+      int y = x + (int)(int8_t)(e & 0xFF);
+      const int lo = (e >> 8) & 0xFF, hi = (e >> 16) & 0xFF;
+      y = y < lo ? lo : y; y = y > hi ? hi : y;
+      if (y != val || (int)(e >> 24) != L) ++bad;
+    }
+  }
+  return bad;
+}
 int emu_validate(void* p, long long* nodes) {
   int64_t n = 0; int rc = kd_validate(*static_cast<KdStream*>(p), &n); *nodes = n; return rc;
 }
@@ -55,6 +75,9 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   for (int h = 0; h <= g.leafBits && h < 8; ++h) job.treeDist |= (uint64_t)s->distanceMap[g.D0 - h] << (8 * h);
   for (int k = 1; k <= 7; ++k) job.chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
   job.dstOffset = (oz * SY + oy) * SX + ox;
+  std::vector<uint32_t> lut(1u << 14);
+  for (uint32_t i = 0; i < (1u << 14); ++i) lut[i] = vr_chain_lut_entry(i, job.chainDist);
+  job.chainLut = lut.data();
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   std::vector<uint8_t> strips(lpt * ((1u << g.leafBits) + VR_LEAF_PITCH_PAD));
   const uint32_t items = vr_tile_items(g);
@@ -68,6 +91,12 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
       continue;
     }
     std::fill(strips.begin(), strips.end(), 0xEE);
+    if (g.fastPath && vec16) {  // mirrors the fast path of kd_decode_tiles_kernel
+      for (uint32_t t = 0; t < 256; ++t) vr_tile_phase1_v2(job, g, blk, t, strips.data());
+      for (uint32_t warp = 0; warp < 8; ++warp)
+        for (uint32_t q = 0; q < (1u << g.fbUnit); ++q) vr_unit_phase2_item(g, warp, q, strips.data(), dst, SX, SX * SY);
+      continue;
+    }
     for (uint32_t t = 0; t < lpt; ++t) vr_tile_phase1(job, g, blk, t, strips.data());
     for (uint32_t it = 0; it < items; ++it) vr_tile_phase2_item(g, it, strips.data(), dst, SX, SX * SY, vec16 != 0);
   }

@@ -126,3 +126,27 @@ def test_emulated_device_decode_matches_golden(path):
     slab[2:2 + Z, 1:1 + Y, ox:ox + X] = 0xAB
     assert (slab == 0xAB).all(), "decode wrote outside its brick"
     oa.EMU.emu_free(h)
+
+
+def test_chain_table_equals_sequential_chain_for_all_inputs():
+    """16384 chains x 256 start values: the reference's distances 64..1 and two other sets whose sum
+    fits the table's signed 8-bit offset (larger sums take the loop-based parser)."""
+    for dist in ([64, 32, 16, 8, 4, 2, 1], [100, 0, 13, 7, 3, 3, 1], [1, 2, 4, 8, 16, 32, 64]):
+        assert oa.EMU.emu_check_chain_lut(sum(d << (8 * k) for k, d in enumerate(dist))) == 0
+
+
+def test_emulated_fast_path_full_size_brick():
+    """256x256x128 (tiles of 2^14 voxels): exercises the table-driven parser and the warp-unit gather."""
+    vol = synth.rm_brick(3, 4, 7)
+    s, _ = vr.Stream.compress(vol, 1, 2)
+    hd = s.header
+    dm, bits = s.distance_map, s.bits
+    h = oa.EMU.emu_from_memory(ctypes.byref(hd), dm.ctypes.data, bits.ctypes.data, bits.size)
+    slab = np.full((128 + 2, 256 + 1, 256 + 32), 0xAB, np.uint8)
+    assert oa.EMU.emu_decode(h, slab.ctypes.data, 256 + 32, 256 + 1, 128 + 2, 16, 1, 1, 1) == 0
+    rc, want = oa.oracle_levelcut(bits, hd.numActiveNodes, dm, hd.origTreeDepth, hd.maxTreeDepth, 256, 256, 128)
+    assert rc == 0
+    assert np.array_equal(slab[1:129, 1:257, 16:272], want)
+    slab[1:129, 1:257, 16:272] = 0xAB
+    assert (slab == 0xAB).all()
+    oa.EMU.emu_free(h)

@@ -48,6 +48,18 @@ typedef struct vr_kd_geom {
   // pathBit[a][j]: which bit of a tile-local path index (tileBits wide, MSB = first split below
   // the tile root) carries bit j of the tile-local coordinate along axis a
   uint8_t pathBit[3][16];
+  // inverse map: tile path bit b carries coordinate bit pbCoordBit[b] of axis pbAxis[b]
+  uint8_t pbAxis[16];
+  uint8_t pbCoordBit[16];
+  // gather tables of the fast decode path (valid when fastPath != 0): strip-address contribution of the
+  // 4 low x bits, and of the other tileBits-4 path bits in increasing path-bit order with their axis and
+  // coordinate bit; fbUnit = how many of those lie inside a warp's unit (path bits < leafBits+5)
+  int32_t fastPath;
+  int32_t fbUnit;
+  uint16_t xa[4];
+  uint16_t fbAddr[12];
+  uint8_t fbAxis[12];
+  uint8_t fbCb[12];
 } vr_kd_geom;
 
 static VR_HD int vr_ilog2_exact(int64_t v) {  // returns -1 when v is not a power of two
@@ -70,6 +82,7 @@ static inline int vr_kd_make_geom(int64_t X, int64_t Y, int64_t Z, vr_kd_geom* g
   int64_t ext[3] = {X, Y, Z};
   for (int d = 0; d < VR_MAX_DEPTH; ++d) { g->splitDim[d] = 0; g->childOff[d] = 0; }
   for (int a = 0; a < 3; ++a) for (int j = 0; j < 16; ++j) g->pathBit[a][j] = 0;
+  for (int j = 0; j < 16; ++j) { g->pbAxis[j] = 0; g->pbCoordBit[j] = 0; }
   g->tileBits = g->D0 < VR_TILE_BITS_MAX ? g->D0 : VR_TILE_BITS_MAX;
   g->leafBits = g->tileBits > VR_LEAF_THREADS_LOG2 ? g->tileBits - VR_LEAF_THREADS_LOG2 : 0;
   g->Dt = g->D0 - g->tileBits;
@@ -82,9 +95,32 @@ static inline int vr_kd_make_geom(int64_t X, int64_t Y, int64_t Z, vr_kd_geom* g
     g->splitDim[d] = (uint8_t)s;
     g->childOff[d] = (int32_t)ext[s];
     if (d + 1 == g->Dt) { g->tx = (int32_t)ext[0]; g->ty = (int32_t)ext[1]; g->tz = (int32_t)ext[2]; }
-    if (d >= g->Dt) g->pathBit[s][vr_ilog2_exact(ext[s])] = (uint8_t)(g->D0 - 1 - d);
+    if (d >= g->Dt) {
+      const int b = g->D0 - 1 - d, cb = vr_ilog2_exact(ext[s]);
+      g->pathBit[s][cb] = (uint8_t)b;
+      g->pbAxis[b] = (uint8_t)s;
+      g->pbCoordBit[b] = (uint8_t)cb;
+    }
   }
   if (g->Dt == 0) { g->tx = (int32_t)X; g->ty = (int32_t)Y; g->tz = (int32_t)Z; }
+  // fast-path gather tables
+  g->fastPath = 0; g->fbUnit = 0;
+  for (int j = 0; j < 4; ++j) g->xa[j] = 0;
+  for (int j = 0; j < 12; ++j) { g->fbAddr[j] = 0; g->fbAxis[j] = 0; g->fbCb[j] = 0; }
+  if (g->tileBits == VR_TILE_BITS_MAX && g->tx >= 16) {
+    const int unitBits = g->leafBits + 5;
+    const int pitch = (1 << g->leafBits) + 4;  // VR_LEAF_PITCH_PAD
+    int ok = 1, n = 0;
+    for (int j = 0; j < 4; ++j) if (g->pathBit[0][j] >= unitBits) ok = 0;
+    for (int b = 0; b < g->tileBits && ok; ++b) {
+      const int addr = b < g->leafBits ? (1 << b) : (pitch << (b - g->leafBits));
+      if (g->pbAxis[b] == 0 && g->pbCoordBit[b] < 4) { g->xa[g->pbCoordBit[b]] = (uint16_t)addr; continue; }
+      g->fbAddr[n] = (uint16_t)addr; g->fbAxis[n] = g->pbAxis[b]; g->fbCb[n] = g->pbCoordBit[b];
+      if (b < unitBits) g->fbUnit = n + 1;
+      ++n;
+    }
+    g->fastPath = ok;
+  }
   return 0;
 }
 

@@ -46,6 +46,22 @@ __global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_const
       vr_tile_fill_item(g, it, val, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
     return;
   }
+  if (g.fastPath && p.vec16) {
+    // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
+    vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
+    __syncwarp();
+    int64_t tb = job.dstOffset;  // tile origin, recomputed per thread (no CTA barrier on this path)
+    for (int d = 0; d < g.Dt; ++d)
+      if ((tile >> (g.Dt - 1 - d)) & 1) {
+        const int64_t st = g.splitDim[d] == 0 ? (int64_t)1 : (g.splitDim[d] == 1 ? p.rowPitch : p.slicePitch);
+        tb += st * g.childOff[d];
+      }
+    uint8_t* dstw = p.dst + tb;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t perUnit = 1u << g.fbUnit;
+    for (uint32_t q = lane; q < perUnit; q += 32) vr_unit_phase2_item(g, warp, q, strips, dstw, p.rowPitch, p.slicePitch);
+    return;
+  }
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   if (threadIdx.x < lpt) vr_tile_phase1(job, g, blk, threadIdx.x, strips);
   __syncthreads();

@@ -34,6 +34,7 @@ typedef struct vr_kd_job {
   uint64_t treeDist;             // byte h = distanceMap[D0 - h] for h = 0..leafBits (levels inside a leaf subtree)
   uint64_t chainDist;            // byte k-1 = distanceMap[D0 + k] for k = 1..7
   int64_t dstOffset;             // voxel offset of the brick's (0,0,0) inside the destination slab
+  const uint32_t* chainLut;      // [16384] refinement-chain table for this stream's chainDist (vr_chain_lut_entry)
 } vr_kd_job;
 
 // Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
@@ -173,10 +174,13 @@ VR_HD uint32_t vr_path_of(const vr_kd_geom& g, int x, int y, int z) {
 
 // Tile origin (brick-local voxel coordinates) of tile slot t (path prefix of Dt bits).
 VR_HD void vr_tile_origin(const vr_kd_geom& g, uint32_t t, int* ox, int* oy, int* oz) {
-  int o[3] = {0, 0, 0};
+  int o0 = 0, o1 = 0, o2 = 0;
   for (int d = 0; d < g.Dt; ++d)
-    if ((t >> (g.Dt - 1 - d)) & 1) o[g.splitDim[d]] += g.childOff[d];
-  *ox = o[0]; *oy = o[1]; *oz = o[2];
+    if ((t >> (g.Dt - 1 - d)) & 1) {
+      const int s = g.splitDim[d], c = g.childOff[d];
+      o0 += s == 0 ? c : 0; o1 += s == 1 ? c : 0; o2 += s == 2 ? c : 0;
+    }
+  *ox = o0; *oy = o1; *oz = o2;
 }
 
 VR_HD uint32_t vr_strip_addr(const vr_kd_geom& g, uint32_t path) {
@@ -262,3 +266,149 @@ VR_HD uint32_t vr_tile_items(const vr_kd_geom& g) {
   const int seg = g.tx < 16 ? g.tx : 16;
   return (uint32_t)((g.tx / seg) * g.ty * g.tz);
 }
+
+// =================================================================================================
+// v2 fast path (full tiles of 256 leaf subtrees, 16-byte aligned destination)
+// =================================================================================================
+
+// Refinement-chain table.  A chain is <= 7 symbols (14 bits, LSB first); its effect on the voxel value
+// is a composition of saturating +/- steps, which is always of the form x -> min(max(x + A, lo), hi).
+// Entry = A (int8) | lo << 8 | hi << 16 | symbols consumed << 24.
+VR_HD uint32_t vr_chain_lut_entry(uint32_t codes14, uint64_t chainDist) {
+  int A = 0, lo = 0, hi = 255, L = VR_ADD_LEVELS;
+  for (int k = 0; k < VR_ADD_LEVELS; ++k) {
+    const int c = (int)((codes14 >> (2 * k)) & 3);
+    if (c == 3) { L = k + 1; break; }
+    const int d = (int)((chainDist >> (8 * k)) & 0xFF);
+    const int a = c == 1 ? d : (c == 2 ? -d : 0);
+    A += a;
+    lo += a; lo = lo < 0 ? 0 : (lo > 255 ? 255 : lo);
+    hi += a; hi = hi < 0 ? 0 : (hi > 255 ? 255 : hi);
+  }
+  return (uint32_t)(A & 0xFF) | ((uint32_t)lo << 8) | ((uint32_t)hi << 16) | ((uint32_t)L << 24);
+}
+
+// Bit window: low bits of `win` are the next symbols; > 32 valid bits after every skip().
+struct VrWindow {
+  const uint32_t* w;  // next word to load
+  uint64_t win;
+  int have;
+  VR_HD void init(const uint32_t* words, uint32_t sym) {
+    w = words + (sym >> 4);
+    const int sh = (int)(sym & 15) * 2;
+    win = (uint64_t)VR_LDG32(w) >> sh;
+    have = 32 - sh;
+    win |= (uint64_t)VR_LDG32(w + 1) << have;
+    have += 32;
+    w += 2;
+  }
+  VR_HD void skip(int nbits) {
+    win >>= nbits;
+    have -= nbits;
+    if (have <= 32) {
+      win |= (uint64_t)VR_LDG32(w) << have;
+      have += 32;
+      ++w;
+    }
+  }
+};
+
+// Leaf-subtree parser, v2: value stack as a byte shift register (top = parent of the next node), whole
+// refinement chains resolved by one table look-up.  Same contract as vr_decode_leaf.
+template <typename Sink>
+VR_HD void vr_decode_leaf_v2(VrWindow& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut, Sink& sink) {
+  const uint32_t total = 1u << leafBits;
+  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
+  uint64_t stack = (uint64_t)ownVal;
+  int h = leafBits - 1;
+  uint32_t v = 0;
+  for (;;) {
+    const int c = (int)(rd.win & 3);
+    const int pv = (int)(stack & 0xFF);
+    if (h > 0) {
+      if (c == 3) {  // constant box of 2^h voxels
+        sink.fill(v, 1u << h, pv);
+        v += 1u << h;
+        rd.skip(2);
+      } else {
+        const int val = vr_apply(pv, c, (int)((treeDist >> (8 * h)) & 0xFF));
+        stack = (stack << 8) | (uint64_t)val;
+        --h;
+        rd.skip(2);
+        continue;
+      }
+    } else {  // voxel + refinement chain
+      const uint32_t e = VR_LDG32(lut + ((uint32_t)(rd.win >> 2) & 0x3FFFu));
+      int val = vr_apply(pv, c, (int)(treeDist & 0xFF));
+      val += (int)(int8_t)(e & 0xFF);
+      const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
+      val = val < lo ? lo : val;
+      val = val > hi ? hi : val;
+      const bool leaf = c == 3;
+      sink.put(v, leaf ? pv : val);
+      v += 1;
+      rd.skip(leaf ? 2 : 2 + 2 * (int)(e >> 24));
+    }
+    if (v == total) break;
+    const int nh = VR_CTZ32(v);
+    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
+    h = nh;
+  }
+  sink.finish(total);
+}
+
+VR_HD void vr_tile_phase1_v2(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, uint8_t* strips) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  VrStripSink sink;
+  sink.init(strips + (size_t)leaf * pitch);
+  if (off == VR_PRUNED) {
+    sink.fill(0, 1u << g.leafBits, val);
+    return;
+  }
+  VrWindow rd;
+  rd.init(job.words, off);
+  vr_decode_leaf_v2(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
+}
+
+// Phase 2 over a "unit" = the 2^unitBits voxels whose tile path index shares the top bits `unit`
+// (a warp's 32 leaf subtrees when unitBits = leafBits + 5).  Item q = one 16-byte x-run; the other
+// unitBits-4 free path bits are enumerated by the bits of q in increasing path-bit order.
+// Requires the 4 low x bits to map to path bits < unitBits (checked on the host).
+VR_HD void vr_unit_phase2_item(const vr_kd_geom& g, uint32_t unit, uint32_t q, const uint8_t* strips,
+                               uint8_t* dstTile, int64_t rowPitch, int64_t slicePitch) {
+  const uint32_t m = q | (unit << g.fbUnit);  // one bit per free path bit, increasing path-bit order
+  uint32_t sAddr = 0;
+  int64_t gOff = 0;
+#pragma unroll
+  for (int k = 0; k < VR_TILE_BITS_MAX - 4; ++k) {
+    if ((m >> k) & 1u) {
+      sAddr += g.fbAddr[k];
+      const int64_t st = g.fbAxis[k] == 0 ? (int64_t)1 : (g.fbAxis[k] == 1 ? rowPitch : slicePitch);
+      gOff += st << g.fbCb[k];
+    }
+  }
+  const uint32_t a[4] = {g.xa[0], g.xa[1], g.xa[2], g.xa[3]};
+  uint32_t w[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int xi = k * 4 + i;
+      const uint32_t ad = sAddr + ((xi & 1) ? a[0] : 0u) + ((xi & 2) ? a[1] : 0u) + ((xi & 4) ? a[2] : 0u) + ((xi & 8) ? a[3] : 0u);
+      r |= (uint32_t)strips[ad] << (8 * i);
+    }
+    w[k] = r;
+  }
+  uint8_t* out = dstTile + gOff;
+#if defined(__CUDA_ARCH__)
+  *reinterpret_cast<uint4*>(out) = make_uint4(w[0], w[1], w[2], w[3]);
+#else
+  for (int k = 0; k < 4; ++k)
+    for (int i = 0; i < 4; ++i) out[k * 4 + i] = (uint8_t)(w[k] >> (8 * i));
+#endif
+}
+

@@ -52,6 +52,7 @@ int vr_context_destroy(vr_context* c) {
   cudaSetDevice(c->device);
   if (c->ownsStream) cudaStreamDestroy(c->stream);
   for (auto& e : c->ev) for (auto& k : e) if (k) cudaEventDestroy(k);
+  for (auto& kv : c->chainLuts) cudaFree(kv.second);
   delete c;
   return VR_OK;
 }

@@ -46,6 +46,23 @@ int stream_build_image(vr_stream* s) {
 }
 }  // namespace vr
 
+namespace vr {
+int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out) {
+  auto it = ctx->chainLuts.find(chainDist);
+  if (it != ctx->chainLuts.end()) { *out = it->second; return VR_OK; }
+  std::vector<uint32_t> host(1u << 14);
+  for (uint32_t i = 0; i < (1u << 14); ++i) host[i] = vr_chain_lut_entry(i, chainDist);
+  uint32_t* dev = nullptr;
+  CU(cudaMalloc((void**)&dev, host.size() * 4));
+  cudaError_t e = cudaMemcpyAsync(dev, host.data(), host.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) { cudaFree(dev); return fail_cuda(e, "upload chain table"); }
+  ctx->chainLuts[chainDist] = dev;
+  *out = dev;
+  return VR_OK;
+}
+}  // namespace vr
+
 extern "C" {
 
 int vr_stream_prepare(vr_stream* s) {
@@ -175,6 +192,10 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     for (int hh = 0; hh <= g.leafBits && hh < 8; ++hh) j.treeDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 - hh)] << (8 * hh);
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) j.chainDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 + k)] << (8 * (k - 1));
     j.dstOffset = (oz * dst->SY + oy) * dst->SX + ox;
+    { int rc = context_chain_lut(ctx, j.chainDist, &j.chainLut); if (rc != VR_OK) { delete p; return rc; } }
+    int chainSum = 0;  // the table packs the net offset in 8 signed bits: 64+32+...+1 = 127 for every reference stream
+    for (int k = 1; k <= VR_ADD_LEVELS; ++k) chainSum += s->kd.distanceMap[(size_t)(g.D0 + k)];
+    if (chainSum > 127) p->geom.fastPath = 0;
     p->bytesStream += s->kd.streamBytes() + 88 + h.maxTreeDepth + 1;
     p->bytesVoxels += h.X * h.Y * h.Z;
     p->bytesIndex += (int64_t)(s->imageBytes - s->wordsBytes);

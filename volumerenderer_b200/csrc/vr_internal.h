@@ -1,6 +1,7 @@
 // vr_internal.h -- handle definitions behind the opaque C ABI types.
 #pragma once
 #include <cuda_runtime.h>
+#include <map>
 #include <vector>
 #include "kd_decode_core.h"
 #include "kd_stream.h"
@@ -10,6 +11,7 @@ struct vr_context {
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
   cudaEvent_t ev[16][2] = {};
+  std::map<uint64_t, uint32_t*> chainLuts;  // chainDist -> device table of 16384 entries
 };
 
 // Device image of a prepared stream: one arena, sections 16-byte aligned:
@@ -47,4 +49,5 @@ namespace vr {
 int fail(int code, const char* msg);
 int fail_cuda(cudaError_t e, const char* where);
 int stream_build_image(vr_stream* s);  // prepare + pack host image
+int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out);
 }
