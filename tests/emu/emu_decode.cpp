@@ -58,6 +58,8 @@ int emu_validate(void* p, long long* nodes) {
   int64_t n = 0; int rc = kd_validate(*static_cast<KdStream*>(p), &n); *nodes = n; return rc;
 }
 // prepare + emulate the tile kernel into a slab of dims (SX,SY,SZ) at origin (ox,oy,oz)
+static int g_variant = 0;
+void emu_set_variant(int v) { g_variant = v; }
 int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ, long long ox, long long oy, long long oz, int vec16) {
   KdStream* s = static_cast<KdStream*>(p);
   int rc = kd_prepare(s);
@@ -92,7 +94,11 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
     }
     std::fill(strips.begin(), strips.end(), 0xEE);
     if (g.fastPath && vec16) {  // mirrors the fast path of kd_decode_tiles_kernel
-      for (uint32_t t = 0; t < 256; ++t) vr_tile_phase1_v2(job, g, blk, t, strips.data());
+      for (uint32_t t = 0; t < 256; ++t) {
+        if (g_variant == 1) vr_tile_phase1_v3<true>(job, g, blk, t, strips.data());
+        else if (g_variant == 2) vr_tile_phase1_v2(job, g, blk, t, strips.data());
+        else vr_tile_phase1_v3<false>(job, g, blk, t, strips.data());
+      }
       for (uint32_t warp = 0; warp < 8; ++warp)
         for (uint32_t q = 0; q < (1u << g.fbUnit); ++q) vr_unit_phase2_item(g, warp, q, strips.data(), dst, SX, SX * SY);
       continue;

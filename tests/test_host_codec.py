@@ -135,9 +135,12 @@ def test_chain_table_equals_sequential_chain_for_all_inputs():
         assert oa.EMU.emu_check_chain_lut(sum(d << (8 * k) for k, d in enumerate(dist))) == 0
 
 
-def test_emulated_fast_path_full_size_brick():
-    """256x256x128 (tiles of 2^14 voxels): exercises the table-driven parser and the warp-unit gather."""
-    vol = synth.rm_brick(3, 4, 7)
+@pytest.mark.parametrize("variant,kind", [(0, "rm"), (1, "rm"), (2, "rm"), (0, "noise"), (1, "shell")])
+def test_emulated_fast_path_full_size_brick(variant, kind):
+    """256x256x128 (tiles of 2^14 voxels): exercises the table-driven parsers and the warp-unit gather."""
+    oa.EMU.emu_set_variant(variant)
+    vol = {"rm": lambda: synth.rm_brick(3, 4, 7), "noise": synth.noise_brick,
+           "shell": lambda: synth.shell_brick((256, 256, 128), noise=3)}[kind]()
     s, _ = vr.Stream.compress(vol, 1, 2)
     hd = s.header
     dm, bits = s.distance_map, s.bits
@@ -150,3 +153,4 @@ def test_emulated_fast_path_full_size_brick():
     slab[1:129, 1:257, 16:272] = 0xAB
     assert (slab == 0xAB).all()
     oa.EMU.emu_free(h)
+    oa.EMU.emu_set_variant(0)

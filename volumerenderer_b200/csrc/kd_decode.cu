@@ -10,6 +10,8 @@
 // them with 128-bit writes, so every 32-byte DRAM sector of the slab is written exactly once.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "kd_decode.h"
 #include "kd_decode_core.h"
 
@@ -22,14 +24,17 @@ struct DecodeParams {
   int64_t rowPitch;    // slab X
   int64_t slicePitch;  // slab X*Y
   int vec16;
+  int nBricks;
+  int order;  // 1 = brick-major (default; measured 0.44 ms vs 0.60 ms tile-major on the rm_yslab batch), 0 = tile-major
+  int variant;  // parser variant of the fast path: 0 = v3 (chain length from the table), 1 = v3 (length by ALU), 2 = v2
 };
 
 __global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
   extern __shared__ __align__(16) uint8_t strips[];
   __shared__ int64_t sTileBase;
   const vr_kd_geom& g = p.g;
-  const uint32_t brick = blockIdx.x >> g.Dt;
-  const uint32_t tile = blockIdx.x & ((1u << g.Dt) - 1u);
+  const uint32_t brick = p.order ? blockIdx.x >> g.Dt : blockIdx.x % (uint32_t)p.nBricks;
+  const uint32_t tile = p.order ? blockIdx.x & ((1u << g.Dt) - 1u) : blockIdx.x / (uint32_t)p.nBricks;
   const vr_kd_job& job = p.jobs[brick];
   const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   if (threadIdx.x == 0) {
@@ -48,7 +53,10 @@ __global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_const
   }
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
-    vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
+    if (p.variant == 1) vr_tile_phase1_v3<true>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 2) vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
+    else vr_tile_phase1_v3<false>(job, g, blk, threadIdx.x, sbase);
     __syncwarp();
     int64_t tb = job.dstOffset;  // tile origin, recomputed per thread (no CTA barrier on this path)
     for (int d = 0; d < g.Dt; ++d)
@@ -85,6 +93,15 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int 
   p.rowPitch = rowPitch;
   p.slicePitch = slicePitch;
   p.vec16 = vec16 ? 1 : 0;
+  p.nBricks = nBricks;
+  {
+    static int variant = -1;
+    if (variant < 0) { const char* e = getenv("VR_DECODE_VARIANT"); variant = e ? atoi(e) : 0; }
+    p.variant = variant;
+    static int order = -1;
+    if (order < 0) { const char* e = getenv("VR_DECODE_ORDER"); order = e ? atoi(e) : 1; }
+    p.order = order;
+  }
   const size_t smem = kd_decode_smem_bytes(g);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -412,3 +412,150 @@ VR_HD void vr_unit_phase2_item(const vr_kd_geom& g, uint32_t unit, uint32_t q, c
 #endif
 }
 
+
+// =================================================================================================
+// v3 parser: 32-bit funnel-shift bit window, branch-free value update, shared-space strip stores,
+// left/right voxel items handled as a pair.
+// =================================================================================================
+// Strip address type SA: uint32_t = shared-window byte address (device), uint8_t* = plain pointer (host emulation).
+VR_HD void vr_st32(uint32_t addr, uint32_t val) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(val) : "memory");
+#else
+  (void)addr; (void)val;
+#endif
+}
+VR_HD void vr_st32(uint8_t* addr, uint32_t val) { *reinterpret_cast<uint32_t*>(addr) = val; }
+#define VR_ST32(addr, val) vr_st32((addr), (val))
+#if defined(__CUDA_ARCH__)
+#define VR_FUNNEL_R(lo, hi, sh) __funnelshift_r((lo), (hi), (sh))
+#else
+#define VR_FUNNEL_R(lo, hi, sh) ((uint32_t)(((((uint64_t)(hi)) << 32) | (uint64_t)(lo)) >> ((sh) & 31)))
+#endif
+
+struct VrWin32 {
+  const uint32_t* w;  // next word to load
+  uint32_t cur, nxt;
+  int bo;             // bit offset into cur, 0..31
+  VR_HD void init(const uint32_t* words, uint32_t sym) {
+    w = words + (sym >> 4);
+    cur = VR_LDG32(w);
+    nxt = VR_LDG32(w + 1);
+    w += 2;
+    bo = (int)(sym & 15) * 2;
+  }
+  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }  // 32 valid bits
+  VR_HD void skip(int nbits) {
+    bo += nbits;
+    if (bo >= 32) {
+      cur = nxt;
+      nxt = VR_LDG32(w);
+      ++w;
+      bo -= 32;
+    }
+  }
+};
+
+// 1 = saturating add, 2 = saturating subtract, 0/3 = unchanged; no branches.
+VR_HD int vr_apply_bf(int parent, int code, int dist) {
+  const int s = (code & 1) - (code >> 1);
+  int v = parent + s * dist;
+  v = v < 0 ? 0 : v;
+  return v > 255 ? 255 : v;
+}
+
+template <typename SA>
+struct VrStripSink3 {
+  SA base;
+  uint32_t acc;
+  VR_HD void init(SA b) { base = b; acc = 0; }
+  VR_HD void put(uint32_t v, int val) {
+    acc |= (uint32_t)val << (8 * (v & 3));
+    if ((v & 3) == 3) {
+      VR_ST32(base + (v & ~3u), acc);
+      acc = 0;
+    }
+  }
+  VR_HD void fill(uint32_t v, uint32_t cnt, int val) {
+    const uint32_t word = (uint32_t)val * 0x01010101u;
+    if (cnt >= 4) {
+      for (uint32_t i = 0; i < cnt; i += 4) VR_ST32(base + v + i, word);
+    } else {  // cnt == 2 (cnt == 1 never reaches fill on this path): v is even
+      acc |= (word & 0xFFFFu) << (8 * (v & 3));
+      if (v & 2) { VR_ST32(base + (v & ~3u), acc); acc = 0; }
+    }
+  }
+};
+
+// CHAIN_LEN_ALU: take the chain length from the symbol bits (position of the first 3) instead of the
+// table entry, so the table load is off the parser's critical path.
+template <bool CHAIN_LEN_ALU, typename SA>
+VR_HD void vr_decode_leaf_v3(VrWin32& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
+                             VrStripSink3<SA>& sink) {
+  const uint32_t total = 1u << leafBits;  // leafBits >= 2 on this path
+  const int d0 = (int)(treeDist & 0xFF);
+  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
+  uint64_t stack = (uint64_t)ownVal;
+  int h = leafBits - 1;
+  uint32_t v = 0;
+  for (;;) {
+    uint32_t bits = rd.peek();
+    int c = (int)(bits & 3);
+    const int pv = (int)(stack & 0xFF);
+    if (h > 0) {
+      if (c == 3) {  // constant box of 2^h voxels
+        sink.fill(v, 1u << h, pv);
+        v += 1u << h;
+        rd.skip(2);
+      } else {
+        const int val = vr_apply_bf(pv, c, (int)((treeDist >> (8 * h)) & 0xFF));
+        stack = (stack << 8) | (uint64_t)val;
+        --h;
+        rd.skip(2);
+        continue;
+      }
+    } else {  // left and right voxel of one height-1 node, each with its refinement chain
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (t) { bits = rd.peek(); c = (int)(bits & 3); }
+        const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
+        int L;
+        if (CHAIN_LEN_ALU) {
+          const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;
+          L = (VR_CTZ32(m) >> 1) + 1;
+        } else {
+          L = (int)(e >> 24);
+        }
+        const bool leaf = c == 3;
+        rd.skip(leaf ? 2 : 2 + 2 * L);
+        int val = vr_apply_bf(pv, c, d0) + (int)(int8_t)(e & 0xFF);
+        const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
+        val = val < lo ? lo : val;
+        val = val > hi ? hi : val;
+        sink.put(v, leaf ? pv : val);
+        v += 1;
+      }
+    }
+    if (v == total) break;
+    const int nh = VR_CTZ32(v);
+    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
+    h = nh;
+  }
+}
+
+template <bool CHAIN_LEN_ALU, typename SA>
+VR_HD void vr_tile_phase1_v3(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  VrStripSink3<SA> sink;
+  sink.init(strips + leaf * pitch);
+  if (off == VR_PRUNED) {
+    sink.fill(0, 1u << g.leafBits, val);
+    return;
+  }
+  VrWin32 rd;
+  rd.init(job.words, off);
+  vr_decode_leaf_v3<CHAIN_LEN_ALU, SA>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
+}

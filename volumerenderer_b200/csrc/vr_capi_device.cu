@@ -1,6 +1,8 @@
 // vr_capi_device.cu -- device-side half of the C ABI: stream upload, volumes, decode plans, levelCut.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -201,6 +203,16 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     p->bytesIndex += (int64_t)(s->imageBytes - s->wordsBytes);
   }
   p->vec16 = vec16;
+  if (const char* ev = getenv("VR_DECODE_SORT")) {
+    if (atoi(ev)) {  // experiment: bricks with the most live tiles first
+      std::vector<std::pair<int64_t, int>> key;
+      for (int i = 0; i < n; ++i) key.push_back({-streams[i]->kd.index.numLiveTiles, i});
+      std::stable_sort(key.begin(), key.end());
+      std::vector<vr_kd_job> sorted;
+      for (auto& k : key) sorted.push_back(jobs[(size_t)k.second]);
+      jobs.swap(sorted);
+    }
+  }
   cudaError_t e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
   if (e != cudaSuccess) { delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
   e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
