@@ -153,6 +153,51 @@ int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_par
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
                          int32_t* hit_dev, uint64_t* samples_dev);
 
+/* ---- sort-last rendering of a volume sharded over GPUs (no counterpart in the reference, which
+ * renders one texture on one GPU, main.cpp:290,404) ------------------------------------
+ * One process per GPU; rank r holds a box of the whole texture (its bricks, decoded in place, plus a
+ * halo) and renders the samples of the reference's ray lattice whose base texel lies in its owned
+ * box.  The exchange between the passes (all-gather / all-reduce of image-sized buffers) is the
+ * caller's: NCCL via torch.distributed in volumerenderer_b200/sortlast.py, or any other transport. */
+typedef struct vr_slab_desc {
+  int64_t global[3]; /* extent of the whole texture (what the unit cube maps to) */
+  int64_t origin[3]; /* global coordinate of voxel (0,0,0) of the device slab (owned box minus halo) */
+  int64_t own_lo[3]; /* owned box [own_lo, own_hi) in global coordinates; the boxes of all ranks   */
+  int64_t own_hi[3]; /* partition the texture as a grid (slabs along one axis are the usual case)  */
+} vr_slab_desc;
+typedef struct vr_sortlast vr_sortlast;
+/* ctx may be NULL (host-side queries only: vr_sortlast_order); the device tables are made on first use */
+int vr_sortlast_create(vr_context* ctx, const vr_slab_desc* slabs, int32_t n, int32_t rank, vr_sortlast** out);
+int vr_sortlast_destroy(vr_sortlast* sl);
+/* front-to-back order of the n slabs for rays whose direction signs are octant (bit0: x<0, bit1: y<0, bit2: z<0) */
+int vr_sortlast_order(const vr_sortlast* sl, int32_t octant, int32_t* out_ranks);
+/* halo (voxels per axis and side) the device slab must hold around its owned box for `params`:
+ * 1 for the trilinear taps of raycaster.frag:60; isosurface.frag additionally reaches one step ahead
+ * (:121) and DELTA = 0.01 texture units around the hit (:18,52-59). */
+int vr_sortlast_halo(const vr_render_params* params, const int64_t global[3], int64_t halo[3]);
+/* pass 1 (asynchronous).  composite: cseg/tseg = W*H floats, the segment's premultiplied colour and
+ * transmittance.  isosurface: rgba = W*H*4 floats (0 where no hit), hit = W*H sample indices
+ * (VR_HIT_NONE where no hit). */
+#define VR_HIT_NONE 0x7FFFFFFF
+int vr_partial_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                         float* cseg_dev, float* tseg_dev, uint64_t* samples_dev);
+int vr_partial_iso(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                   float* rgba_dev, int32_t* hit_dev, uint64_t* samples_dev);
+/* pass 2, composite: tseg_all_dev = the n ranks' tseg buffers, rank-major (all-gather); contrib_dev =
+ * W*H*2 floats, this rank's (C, A) term.  The element-wise SUM of the terms over ranks goes to
+ * vr_finish_composite, which applies the colour map of raycaster.frag:82-85. */
+int vr_resolve_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                         const float* tseg_all_dev, const float* cseg_dev, float* contrib_dev, uint64_t* samples_dev);
+int vr_finish_composite(vr_context* ctx, const vr_render_params* params, const float* contrib_sum_dev, float* out_rgba_dev);
+/* pass 2, isosurface: hit_min_dev = element-wise MIN of the ranks' hit buffers; rgba_dev is masked in
+ * place so that the element-wise SUM over ranks is the finished frame. */
+int vr_resolve_iso(vr_context* ctx, const vr_sortlast* sl, const vr_render_params* params, const int32_t* hit_mine_dev,
+                   const int32_t* hit_min_dev, float* rgba_dev);
+/* halo exchange helpers: copy a box of the slab (slab-local voxel coordinates) to / from a dense
+ * x-fastest device buffer (asynchronous on the context stream). */
+int vr_volume_pack_box(vr_context* ctx, const vr_volume* v, const int64_t origin[3], const int64_t extent[3], uint8_t* dst_dev);
+int vr_volume_unpack_box(vr_context* ctx, vr_volume* v, const int64_t origin[3], const int64_t extent[3], const uint8_t* src_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -202,3 +202,164 @@ int64_t oracle_render_rows(const uint8_t* volume, int64_t X, int64_t Y, int64_t 
 }
 int oracle_render_params_size(void) { return (int)sizeof(Params); }
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Sort-last restatement (no reference counterpart: the reference renders one texture on one GPU).
+// CPU stand-in for the product's slab kernels, used by the world_size-2 gloo tests of the host-side
+// exchange logic; ground truth for the composited frame stays oracle_render on the whole volume.
+namespace {
+struct Slab { const uint8_t* d; int G[3], o[3], S[3], lo[3], hi[3]; };
+static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+static inline float slab_texel(const Slab& v, int x, int y, int z) {
+  x = clampi(clampi(x, 0, v.G[0] - 1) - v.o[0], 0, v.S[0] - 1);
+  y = clampi(clampi(y, 0, v.G[1] - 1) - v.o[1], 0, v.S[1] - 1);
+  z = clampi(clampi(z, 0, v.G[2] - 1) - v.o[2], 0, v.S[2] - 1);
+  return (float)v.d[x + (int64_t)v.S[0] * (y + (int64_t)v.S[1] * z)];
+}
+static inline float slab_tex(const Slab& v, V3 p) {
+  float cx = p.x * (float)v.G[0] - 0.5f, cy = p.y * (float)v.G[1] - 0.5f, cz = p.z * (float)v.G[2] - 0.5f;
+  float fx = std::floor(cx), fy = std::floor(cy), fz = std::floor(cz);
+  float wx = cx - fx, wy = cy - fy, wz = cz - fz;
+  int x0 = (int)fx, y0 = (int)fy, z0 = (int)fz;
+  float c000 = slab_texel(v, x0, y0, z0), c100 = slab_texel(v, x0 + 1, y0, z0);
+  float c010 = slab_texel(v, x0, y0 + 1, z0), c110 = slab_texel(v, x0 + 1, y0 + 1, z0);
+  float c001 = slab_texel(v, x0, y0, z0 + 1), c101 = slab_texel(v, x0 + 1, y0, z0 + 1);
+  float c011 = slab_texel(v, x0, y0 + 1, z0 + 1), c111 = slab_texel(v, x0 + 1, y0 + 1, z0 + 1);
+  float c00 = std::fmaf(wx, c100 - c000, c000), c10 = std::fmaf(wx, c110 - c010, c010);
+  float c01 = std::fmaf(wx, c101 - c001, c001), c11 = std::fmaf(wx, c111 - c011, c011);
+  float c0 = std::fmaf(wy, c10 - c00, c00), c1 = std::fmaf(wy, c11 - c01, c01);
+  return std::fmaf(wz, c1 - c0, c0) * (1.0f / 255.0f);
+}
+static inline bool slab_owned(const Slab& v, V3 p) {
+  int b[3] = {clampi((int)std::floor(p.x * (float)v.G[0] - 0.5f), 0, v.G[0] - 1),
+              clampi((int)std::floor(p.y * (float)v.G[1] - 0.5f), 0, v.G[1] - 1),
+              clampi((int)std::floor(p.z * (float)v.G[2] - 0.5f), 0, v.G[2] - 1)};
+  for (int a = 0; a < 3; ++a) if (b[a] < v.lo[a] || b[a] >= v.hi[a]) return false;
+  return true;
+}
+static Slab make_slab(const uint8_t* d, const int32_t* geom) {
+  Slab v; v.d = d;
+  for (int a = 0; a < 3; ++a) { v.G[a] = geom[a]; v.o[a] = geom[3 + a]; v.S[a] = geom[6 + a]; v.lo[a] = geom[9 + a]; v.hi[a] = geom[12 + a]; }
+  return v;
+}
+static void segment(const Slab& v, V3 p, V3 dirStep, float* C, float* A) {
+  bool started = false;
+  for (int i = 0; i < 300; ++i) {
+    p = add(p, dirStep);
+    if (!inside(p)) break;
+    if (!slab_owned(v, p)) { if (started) break; continue; }
+    started = true;
+    float smp = slab_tex(v, p);
+    float prev_alpha = smp - (smp * *A);
+    *C = prev_alpha * smp + *C;
+    *A += prev_alpha * 0.6f;
+    if (*A > 0.99f) break;
+  }
+}
+static void ray_dirs(const Params& P, V3 vUV, V3* dir, V3* dirStep) {
+  V3 eye = {P.eye[0], P.eye[1], P.eye[2]};
+  *dir = normalize(sub(sub(vUV, V3{0.5f, 0.5f, 0.5f}), eye));
+  *dirStep = mul(*dir, V3{P.step[0], P.step[1], P.step[2]});
+}
+template <class F> static void for_pixels(const Params& P, int threads, F f) {
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int w = 0; w < threads; ++w)
+    pool.emplace_back([&, w]() { for (int py = w; py < P.H; py += threads) for (int px = 0; px < P.W; ++px) f(px, py); });
+  for (auto& t : pool) t.join();
+}
+}  // namespace
+
+extern "C" {
+// geom: 15 int32 = G[3], o[3], S[3], lo[3], hi[3]
+void oracle_partial_composite(const uint8_t* slab, const int32_t* geom, const void* params, float* cseg, float* tseg, int threads) {
+  Params P; std::memcpy(&P, params, sizeof(P));
+  Slab v = make_slab(slab, geom);
+  for_pixels(P, threads, [&](int px, int py) {
+    float C = 0.0f, A = 0.0f; V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) { V3 dir, ds; ray_dirs(P, vUV, &dir, &ds); segment(v, vUV, ds, &C, &A); }
+    cseg[(int64_t)py * P.W + px] = C; tseg[(int64_t)py * P.W + px] = 1.0f - A;
+  });
+}
+void oracle_partial_iso(const uint8_t* slab, const int32_t* geom, const void* params, float* rgba, int32_t* hit, int threads) {
+  Params P; std::memcpy(&P, params, sizeof(P));
+  Slab v = make_slab(slab, geom);
+  for_pixels(P, threads, [&](int px, int py) {
+    float* o = rgba + 4 * ((int64_t)py * P.W + px);
+    o[0] = o[1] = o[2] = o[3] = 0.0f;
+    int32_t h = 0x7FFFFFFF; V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      V3 dir, dirStep; ray_dirs(P, vUV, &dir, &dirStep);
+      V3 p = vUV; bool started = false;
+      for (int i = 0; i < 300; ++i) {
+        p = add(p, dirStep);
+        if (!inside(p)) break;
+        if (!slab_owned(v, p)) { if (started) break; continue; }
+        started = true;
+        float smp = slab_tex(v, p), smp2 = slab_tex(v, add(p, dirStep));
+        if ((smp - P.iso) < 0.0f && (smp2 - P.iso) >= 0.0f) {
+          V3 left = p, right = add(p, dirStep);
+          for (int b = 0; b < 4; ++b) { V3 mid = scale(add(right, left), 0.5f); if (slab_tex(v, mid) < P.iso) left = mid; else right = mid; }
+          V3 tc = scale(add(right, left), 0.5f);
+          const float D = 0.01f;
+          V3 s1 = {slab_tex(v, sub(tc, V3{D, 0, 0})), slab_tex(v, sub(tc, V3{0, D, 0})), slab_tex(v, sub(tc, V3{0, 0, D}))};
+          V3 s2 = {slab_tex(v, add(tc, V3{D, 0, 0})), slab_tex(v, add(tc, V3{0, D, 0})), slab_tex(v, add(tc, V3{0, 0, D}))};
+          V3 g = sub(s1, s2);
+          V3 N = normalize(V3{g.x / 2.0f, g.y / 2.0f, g.z / 2.0f});
+          V3 L = {-dir.x, -dir.y, -dir.z};
+          float diffuse = std::fmax(dot(L, N), 0.0f);
+          V3 halfVec = normalize(add(L, L));
+          float specular = std::pow(std::fmax(0.00001f, dot(halfVec, N)), 250.0f);
+          o[0] = clamp01(diffuse * 0.39f + specular); o[1] = clamp01(diffuse * 0.58f + specular);
+          o[2] = clamp01(diffuse * 0.93f + specular); o[3] = 1.0f;
+          h = i;
+          break;
+        }
+      }
+    }
+    hit[(int64_t)py * P.W + px] = h;
+  });
+}
+// order: 8 x n visibility orders; contrib: W*H*2 floats
+void oracle_resolve_composite(const uint8_t* slab, const int32_t* geom, const void* params, const float* tsegAll, int n, int rank,
+                              const int32_t* order, const float* cseg, float* contrib, int threads) {
+  Params P; std::memcpy(&P, params, sizeof(P));
+  Slab v = make_slab(slab, geom);
+  const int64_t npix = (int64_t)P.W * P.H;
+  for_pixels(P, threads, [&](int px, int py) {
+    const int64_t pix = (int64_t)py * P.W + px;
+    float tC = 0.0f, tA = 0.0f; V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      V3 dir, ds; ray_dirs(P, vUV, &dir, &ds);
+      const int oct = (ds.x < 0.0f ? 1 : 0) | (ds.y < 0.0f ? 2 : 0) | (ds.z < 0.0f ? 4 : 0);
+      const int32_t* ord = order + oct * n;
+      float T = 1.0f, Tin = 1.0f; int myPos = -1, crossPos = -1;
+      for (int k = 0; k < n; ++k) {
+        int r = ord[k];
+        if (r == rank) { myPos = k; Tin = T; }
+        T = T * tsegAll[(int64_t)r * npix + pix];
+        if (crossPos < 0 && (1.0f - T) > 0.99f) crossPos = k;
+      }
+      if (crossPos >= 0 && crossPos < myPos) {
+      } else if (crossPos == myPos) {
+        float C = 0.0f, A = 1.0f - Tin;
+        segment(v, vUV, ds, &C, &A);
+        tC = C; tA = A;
+      } else {
+        tC = Tin * cseg[pix];
+        if (crossPos < 0 && myPos == n - 1) tA = 1.0f - T;
+      }
+    }
+    contrib[2 * pix] = tC; contrib[2 * pix + 1] = tA;
+  });
+}
+void oracle_finish_composite(const void* params, const float* sum, float* out, int threads) {
+  Params P; std::memcpy(&P, params, sizeof(P));
+  for_pixels(P, threads, [&](int px, int py) {
+    const int64_t pix = (int64_t)py * P.W + px;
+    float* o = out + 4 * pix; V3 vUV;
+    o[0] = o[1] = o[2] = o[3] = 1.0f;
+    if (ray_setup(P, px, py, &vUV)) { o[0] = o[1] = clamp01(1.0f - sum[2 * pix]); o[2] = 1.0f; o[3] = clamp01(sum[2 * pix + 1]); }
+  });
+}
+}

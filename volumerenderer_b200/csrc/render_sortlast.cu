@@ -1,0 +1,227 @@
+// render_sortlast.cu -- stage 2 on a volume sharded over GPUs: every rank marches the
+// samples of the reference's ray lattice that fall into its own slab, and the per-slab segment
+// partials are combined front to back ("sort-last").  The reference renders one texture on one GPU
+// (main.cpp:404); the arithmetic per sample is unchanged (raycaster.frag:60-77, isosurface.frag:120-157).
+//
+// Lattice: every rank replays p_i = p_{i-1} + dirStep from the same entry point with the same fp32
+// additions (raycaster.frag:39), so sample positions, the 300-sample budget and the exit test are
+// identical on all ranks; a rank only fetches at the samples it owns (dev::owned).
+//
+// Composite: with T = 1 - A the recurrence a = s - s*A; C += a*s; A += 0.6*a is T *= (1 - 0.6 s),
+// C += T_before * s^2, so a segment that starts with transmittance T_in contributes T_in * C_seg and
+// hands on T_in * T_seg.  Early ray termination (A > 0.99, raycaster.frag:77) is a property of the whole
+// ray: pass 1 stops only when the segment alone is opaque (always safe), pass 2 knows T_in from the
+// other ranks' T_seg and re-marches the one segment in which the ray really terminates, with the
+// reference recurrence started at A_in = 1 - T_in, so that the stop sample is the reference's.
+// Isosurface: the first hit over the whole ray is the hit with the smallest sample index.
+#include "render_common.cuh"
+
+namespace vr {
+
+using namespace dev;
+
+namespace {
+
+__device__ __forceinline__ bool pixel_of_thread(const RenderParams& P, int* px, int* py) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  *px = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
+  *py = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+  return *px < P.W && *py < P.H;
+}
+
+__device__ __forceinline__ void count_samples(unsigned long long* sampleCount, unsigned n) {
+  if (sampleCount) {
+    unsigned tot = __reduce_add_sync(0xFFFFFFFFu, n);
+    if ((threadIdx.x & 31) == 0 && tot) atomicAdd(sampleCount, (unsigned long long)tot);
+  }
+}
+
+// Reference recurrence over the owned samples of one ray, started at (C, A).  A slab is convex, so the
+// owned samples are one run of the lattice: stop at the first sample after it.
+__device__ __forceinline__ void march_segment(const Vol& v, V3 p, V3 dirStep, float* C, float* A, unsigned* n) {
+  float c = *C, a = *A;
+  bool started = false;
+  for (int i = 0; i < 300; ++i) {
+    p = add(p, dirStep);
+    if (!inside(p)) break;
+    if (!owned(v, p)) {
+      if (started) break;
+      continue;
+    }
+    started = true;
+    float smp = tex<true>(v, p);
+    ++*n;
+    float prev_alpha = fsub(smp, fmul(smp, a));
+    c = fadd(fmul(prev_alpha, smp), c);
+    a = fadd(a, fmul(prev_alpha, 0.6f));
+    if (a > 0.99f) break;
+  }
+  *C = c; *A = a;
+}
+
+__global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_constant__ RenderParams P,
+                                                                const __grid_constant__ SlabGeom g,
+                                                                const uint8_t* __restrict__ vol, float* __restrict__ cseg,
+                                                                float* __restrict__ tseg,
+                                                                unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    float C = 0.0f, A = 0.0f;
+    V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      Vol v = make_vol(g, vol);
+      V3 dir, dirStep;
+      ray_dir(P, vUV, &dir, &dirStep);
+      march_segment(v, vUV, dirStep, &C, &A, &n);
+    }
+    cseg[(long long)py * P.W + px] = C;
+    tseg[(long long)py * P.W + px] = fsub(1.0f, A);
+  }
+  count_samples(sampleCount, n);
+}
+
+__global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant__ RenderParams P,
+                                                          const __grid_constant__ SlabGeom g, const uint8_t* __restrict__ vol,
+                                                          float4* __restrict__ rgbaOut, int* __restrict__ hitOut,
+                                                          unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    float4 rgba = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    int hit = VR_HIT_NONE;
+    V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      Vol v = make_vol(g, vol);
+      V3 dir, dirStep;
+      ray_dir(P, vUV, &dir, &dirStep);
+      V3 p = vUV;
+      bool started = false;
+      for (int i = 0; i < 300; ++i) {
+        p = add(p, dirStep);
+        if (!inside(p)) break;
+        if (!owned(v, p)) {
+          if (started) break;
+          continue;
+        }
+        started = true;
+        float smp = tex<true>(v, p);
+        float smp2 = tex<true>(v, add(p, dirStep));
+        ++n;
+        if (fsub(smp, P.iso) < 0.0f && fsub(smp2, P.iso) >= 0.0f) {
+          rgba = iso_shade<true>(v, P, p, dir, dirStep);
+          hit = i;
+          break;
+        }
+      }
+    }
+    rgbaOut[(long long)py * P.W + px] = rgba;
+    hitOut[(long long)py * P.W + px] = hit;
+  }
+  count_samples(sampleCount, n);
+}
+
+__global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_constant__ RenderParams P,
+                                                                const __grid_constant__ SlabGeom g,
+                                                                const uint8_t* __restrict__ vol, const float* __restrict__ tsegAll,
+                                                                int nRanks, int rank, const int* __restrict__ order,
+                                                                const float* __restrict__ cseg, float2* __restrict__ contrib,
+                                                                unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    const long long pix = (long long)py * P.W + px, npix = (long long)P.W * P.H;
+    float2 term = make_float2(0.0f, 0.0f);
+    V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      V3 dir, dirStep;
+      ray_dir(P, vUV, &dir, &dirStep);
+      // visibility order of the slabs for this ray's direction octant
+      const int oct = (dirStep.x < 0.0f ? 1 : 0) | (dirStep.y < 0.0f ? 2 : 0) | (dirStep.z < 0.0f ? 4 : 0);
+      const int* ord = order + oct * nRanks;
+      // walk the segments front to back: every rank evaluates the same chain in the same order
+      float T = 1.0f, Tin = 1.0f;
+      int myPos = -1, crossPos = -1;
+      for (int k = 0; k < nRanks; ++k) {
+        const int r = __ldg(ord + k);
+        if (r == rank) { myPos = k; Tin = T; }
+        T = fmul(T, __ldg(tsegAll + (long long)r * npix + pix));
+        if (crossPos < 0 && fsub(1.0f, T) > 0.99f) crossPos = k;
+      }
+      if (crossPos >= 0 && crossPos < myPos) {
+        // the ray terminated in a slab in front of this one
+      } else if (crossPos == myPos) {
+        // the ray terminates inside this segment: replay it with the reference recurrence from A_in
+        Vol v = make_vol(g, vol);
+        float C = 0.0f, A = fsub(1.0f, Tin);
+        march_segment(v, vUV, dirStep, &C, &A, &n);
+        term = make_float2(C, A);
+      } else {
+        term.x = fmul(Tin, __ldg(cseg + pix));
+        if (crossPos < 0 && myPos == nRanks - 1) term.y = fsub(1.0f, T);  // no termination anywhere: last slab closes alpha
+      }
+    }
+    contrib[pix] = term;
+  }
+  count_samples(sampleCount, n);
+}
+
+__global__ void __launch_bounds__(256) finish_composite_kernel(const __grid_constant__ RenderParams P,
+                                                               const float2* __restrict__ sum, float4* __restrict__ out) {
+  int px, py;
+  if (pixel_of_thread(P, &px, &py)) {
+    const long long pix = (long long)py * P.W + px;
+    float4 rgba = make_float4(1.0f, 1.0f, 1.0f, 1.0f);  // clear colour (main.cpp:392)
+    V3 vUV;
+    if (ray_setup(P, px, py, &vUV)) {
+      float2 s = sum[pix];
+      rgba = make_float4(clamp01(fsub(1.0f, s.x)), clamp01(fsub(1.0f, s.x)), 1.0f, clamp01(s.y));  // raycaster.frag:82-85
+    }
+    out[pix] = rgba;
+  }
+}
+
+__global__ void __launch_bounds__(256) resolve_iso_kernel(long long npix, int rank, const int* __restrict__ hitMine,
+                                                          const int* __restrict__ hitMin, float4* __restrict__ rgba) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const int hm = hitMin[i], h = hitMine[i];
+  if (hm == VR_HIT_NONE) {
+    const float w = rank == 0 ? 1.0f : 0.0f;  // miss: vec4(255,255,255,1) clamped (isosurface.frag:79), supplied once
+    rgba[i] = make_float4(w, w, w, w);
+  } else if (h != hm) {
+    rgba[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  }
+}
+
+dim3 pixel_grid(const RenderParams& P) { return dim3((P.W + 31) / 32, (P.H + 7) / 8); }
+
+}  // namespace
+
+cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float* cseg, float* tseg,
+                                     unsigned long long* sampleCount, cudaStream_t stream) {
+  partial_composite_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, cseg, tseg, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float4* rgba, int* hit,
+                               unsigned long long* sampleCount, cudaStream_t stream) {
+  partial_iso_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, rgba, hit, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, const float* tsegAll, int n,
+                                     int rank, const int* order, const float* cseg, float2* contrib,
+                                     unsigned long long* sampleCount, cudaStream_t stream) {
+  resolve_composite_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, float4* out, cudaStream_t stream) {
+  finish_composite_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, sum, out);
+  return cudaGetLastError();
+}
+cudaError_t resolve_iso_launch(int W, int H, int rank, const int* hitMine, const int* hitMin, float4* rgba, cudaStream_t stream) {
+  long long npix = (long long)W * H;
+  resolve_iso_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, stream>>>(npix, rank, hitMine, hitMin, rgba);
+  return cudaGetLastError();
+}
+
+}  // namespace vr

@@ -12,7 +12,8 @@
 using namespace vr;
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
 
-static int make_params(const vr_render_params* in, RenderParams* P) {
+namespace vr {
+int make_render_params(const vr_render_params* in, RenderParams* P) {
   if (in->width <= 0 || in->height <= 0) return VR_ERR_ARG;
   double f[3] = {in->front[0], in->front[1], in->front[2]}, up[3] = {in->up[0], in->up[1], in->up[2]};
   double fl = std::sqrt(f[0] * f[0] + f[1] * f[1] + f[2] * f[2]);
@@ -36,6 +37,7 @@ static int make_params(const vr_render_params* in, RenderParams* P) {
   P->mode = in->mode == VR_MODE_COMPOSITE ? 0 : 1;
   return VR_OK;
 }
+}  // namespace vr
 
 extern "C" {
 
@@ -57,7 +59,7 @@ int vr_render_defaults(vr_render_params* p) {
 int vr_camera_basis(const vr_render_params* in, float out[20]) {
   if (!in || !out) return fail(VR_ERR_ARG, "null");
   RenderParams P;
-  if (make_params(in, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  if (make_render_params(in, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
   std::memcpy(out, &P, 20 * sizeof(float));
   return VR_OK;
 }
@@ -68,7 +70,7 @@ int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* par
   if (params->mode != VR_MODE_COMPOSITE && params->mode != VR_MODE_ISOSURFACE && params->mode != VR_MODE_ISOSURFACE_COMPRESSED)
     return fail(VR_ERR_ARG, "vr_render: unknown mode");
   RenderParams P;
-  if (make_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
   if (vol->SX > 0x7FFFFFFF || vol->SY > 0x7FFFFFFF || vol->SZ > 0x7FFFFFFF) return fail(VR_ERR_UNSUPPORTED, "volume extent too large");
   CU(cudaSetDevice(ctx->device));
   CU(render_launch(P, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,

@@ -1,0 +1,199 @@
+// vr_capi_sortlast.cu -- C ABI of the sort-last renderer (include/vr_b200.h, "sort-last rendering"):
+// slab geometry and visibility orders on the host, kernels of render_sortlast.cu on the device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "../../include/vr_b200.h"
+#include "render_march.h"
+#include "vr_internal.h"
+
+using namespace vr;
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
+
+struct vr_sortlast {
+  int device = 0;
+  int n = 0, rank = 0;
+  std::vector<vr_slab_desc> slabs;
+  int order[8][VR_MAX_RANKS];
+  int* orderDev = nullptr;  // 8 x n
+};
+
+namespace vr { int make_render_params(const vr_render_params* in, RenderParams* P); }
+
+static int slab_geom(const vr_sortlast* sl, const vr_volume* v, SlabGeom* g) {
+  const vr_slab_desc& d = sl->slabs[(size_t)sl->rank];
+  const int64_t S[3] = {v->SX, v->SY, v->SZ};
+  for (int a = 0; a < 3; ++a) {
+    if (d.global[a] > 0x7FFFFFFF) return fail(VR_ERR_UNSUPPORTED, "volume extent too large");
+    if (d.origin[a] < 0 || d.origin[a] + S[a] > d.global[a]) return fail(VR_ERR_ARG, "slab does not lie inside the global volume");
+    if (d.own_lo[a] < d.origin[a] || d.own_hi[a] > d.origin[a] + S[a]) return fail(VR_ERR_ARG, "owned box is not inside the device slab");
+    g->G[a] = (int)d.global[a]; g->o[a] = (int)d.origin[a]; g->S[a] = (int)S[a];
+    g->lo[a] = (int)d.own_lo[a]; g->hi[a] = (int)d.own_hi[a];
+  }
+  return VR_OK;
+}
+
+extern "C" {
+
+int vr_sortlast_create(vr_context* ctx, const vr_slab_desc* slabs, int32_t n, int32_t rank, vr_sortlast** out) {
+  if (!slabs || !out || n < 1 || n > VR_MAX_RANKS || rank < 0 || rank >= n) return fail(VR_ERR_ARG, "vr_sortlast_create: bad argument");
+  for (int r = 0; r < n; ++r)
+    for (int a = 0; a < 3; ++a) {
+      if (slabs[r].global[a] != slabs[0].global[a] || slabs[r].global[a] <= 0) return fail(VR_ERR_ARG, "slabs disagree on the global extent");
+      if (slabs[r].own_lo[a] < 0 || slabs[r].own_hi[a] > slabs[r].global[a] || slabs[r].own_lo[a] >= slabs[r].own_hi[a])
+        return fail(VR_ERR_ARG, "empty or out-of-range owned box");
+    }
+  // the owned boxes must tile the texture: equal total volume and pairwise disjoint
+  long double vol = 0, tot = (long double)slabs[0].global[0] * slabs[0].global[1] * slabs[0].global[2];
+  for (int r = 0; r < n; ++r) {
+    vol += (long double)(slabs[r].own_hi[0] - slabs[r].own_lo[0]) * (slabs[r].own_hi[1] - slabs[r].own_lo[1]) * (slabs[r].own_hi[2] - slabs[r].own_lo[2]);
+    for (int q = 0; q < r; ++q) {
+      bool overlap = true;
+      for (int a = 0; a < 3; ++a)
+        overlap = overlap && slabs[r].own_lo[a] < slabs[q].own_hi[a] && slabs[q].own_lo[a] < slabs[r].own_hi[a];
+      if (overlap) return fail(VR_ERR_ARG, "owned boxes overlap");
+    }
+  }
+  if (vol != tot) return fail(VR_ERR_ARG, "owned boxes do not cover the texture");
+  vr_sortlast* sl = new vr_sortlast;
+  sl->device = ctx ? ctx->device : -1; sl->n = n; sl->rank = rank;
+  sl->slabs.assign(slabs, slabs + n);
+  // Front-to-back order per direction octant.  For a grid partition any lexicographic order of the box
+  // corners, each axis taken in the ray's direction of travel, is a visibility order: two boxes are
+  // separated by an axis-aligned plane that spans the volume, and the ray crosses it in that sense.
+  for (int oct = 0; oct < 8; ++oct) {
+    std::vector<int> idx((size_t)n);
+    for (int r = 0; r < n; ++r) idx[(size_t)r] = r;
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) {
+      for (int ax = 0; ax < 3; ++ax) {
+        int64_t ka = (oct >> ax) & 1 ? -slabs[a].own_lo[ax] : slabs[a].own_lo[ax];
+        int64_t kb = (oct >> ax) & 1 ? -slabs[b].own_lo[ax] : slabs[b].own_lo[ax];
+        if (ka != kb) return ka < kb;
+      }
+      return false;
+    });
+    for (int r = 0; r < n; ++r) sl->order[oct][r] = idx[(size_t)r];
+  }
+  *out = sl;  // the device copy of the orders is made by the first vr_resolve_composite (ctx may be NULL here)
+  return VR_OK;
+}
+
+static int order_on_device(vr_context* ctx, vr_sortlast* sl) {
+  if (sl->orderDev && sl->device == ctx->device) return VR_OK;
+  if (sl->orderDev) return fail(VR_ERR_STATE, "vr_sortlast used with two devices");
+  std::vector<int> flat((size_t)8 * sl->n);
+  for (int oct = 0; oct < 8; ++oct) std::memcpy(&flat[(size_t)oct * sl->n], sl->order[oct], sizeof(int) * (size_t)sl->n);
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMalloc((void**)&sl->orderDev, flat.size() * sizeof(int)));
+  CU(cudaMemcpy(sl->orderDev, flat.data(), flat.size() * sizeof(int), cudaMemcpyHostToDevice));
+  sl->device = ctx->device;
+  return VR_OK;
+}
+
+int vr_sortlast_destroy(vr_sortlast* sl) {
+  if (!sl) return VR_OK;
+  if (sl->orderDev) { cudaSetDevice(sl->device); cudaFree(sl->orderDev); }
+  delete sl;
+  return VR_OK;
+}
+
+int vr_sortlast_order(const vr_sortlast* sl, int32_t octant, int32_t* out) {
+  if (!sl || !out || octant < 0 || octant > 7) return fail(VR_ERR_ARG, "vr_sortlast_order: bad argument");
+  for (int r = 0; r < sl->n; ++r) out[r] = sl->order[octant][r];
+  return VR_OK;
+}
+
+int vr_sortlast_halo(const vr_render_params* p, const int64_t global[3], int64_t halo[3]) {
+  if (!p || !global || !halo) return fail(VR_ERR_ARG, "null");
+  for (int a = 0; a < 3; ++a) {
+    if (p->mode == VR_MODE_COMPOSITE) { halo[a] = 1; continue; }
+    // base texel -> taps of tex(p + dirStep) and of the gradient probes tc +- 0.01 (tc within the step)
+    double reach = (std::fabs((double)p->step_size[a]) + 0.01) * (double)global[a];
+    halo[a] = (int64_t)std::ceil(reach) + 2;
+  }
+  return VR_OK;
+}
+
+#define SL_PROLOGUE(need_slab)                                                                      \
+  if (!ctx || !sl || !params) return fail(VR_ERR_ARG, "null argument");                             \
+  RenderParams P;                                                                                   \
+  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size"); \
+  SlabGeom g;                                                                                       \
+  std::memset(&g, 0, sizeof(g));                                                                    \
+  if (need_slab) { if (!slab) return fail(VR_ERR_ARG, "null slab"); int rc_ = slab_geom(sl, slab, &g); if (rc_ != VR_OK) return rc_; } \
+  CU(cudaSetDevice(ctx->device));
+
+int vr_partial_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                         float* cseg, float* tseg, uint64_t* samples) {
+  if (!cseg || !tseg) return fail(VR_ERR_ARG, "null output");
+  SL_PROLOGUE(true)
+  CU(partial_composite_launch(P, g, slab->dev, cseg, tseg, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
+int vr_partial_iso(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                   float* rgba, int32_t* hit, uint64_t* samples) {
+  if (!rgba || !hit) return fail(VR_ERR_ARG, "null output");
+  SL_PROLOGUE(true)
+  CU(partial_iso_launch(P, g, slab->dev, reinterpret_cast<float4*>(rgba), hit, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
+int vr_resolve_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                         const float* tseg_all, const float* cseg, float* contrib, uint64_t* samples) {
+  if (!tseg_all || !cseg || !contrib) return fail(VR_ERR_ARG, "null buffer");
+  SL_PROLOGUE(true)
+  { int rc_ = order_on_device(ctx, const_cast<vr_sortlast*>(sl)); if (rc_ != VR_OK) return rc_; }
+  CU(resolve_composite_launch(P, g, slab->dev, tseg_all, sl->n, sl->rank, sl->orderDev, cseg, reinterpret_cast<float2*>(contrib),
+                              reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
+int vr_finish_composite(vr_context* ctx, const vr_render_params* params, const float* sum, float* out) {
+  if (!ctx || !params || !sum || !out) return fail(VR_ERR_ARG, "null argument");
+  RenderParams P;
+  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  CU(cudaSetDevice(ctx->device));
+  CU(finish_composite_launch(P, reinterpret_cast<const float2*>(sum), reinterpret_cast<float4*>(out), ctx->stream));
+  return VR_OK;
+}
+
+int vr_resolve_iso(vr_context* ctx, const vr_sortlast* sl, const vr_render_params* params, const int32_t* hit_mine,
+                   const int32_t* hit_min, float* rgba) {
+  if (!ctx || !sl || !params || !hit_mine || !hit_min || !rgba) return fail(VR_ERR_ARG, "null argument");
+  if (params->width <= 0 || params->height <= 0) return fail(VR_ERR_ARG, "bad image size");
+  CU(cudaSetDevice(ctx->device));
+  CU(resolve_iso_launch(params->width, params->height, sl->rank, hit_mine, hit_min, reinterpret_cast<float4*>(rgba), ctx->stream));
+  return VR_OK;
+}
+
+static int box_copy(vr_context* ctx, const vr_volume* v, const int64_t o[3], const int64_t e[3], uint8_t* dense, bool pack) {
+  if (!ctx || !v || !o || !e || !dense) return fail(VR_ERR_ARG, "null argument");
+  const int64_t S[3] = {v->SX, v->SY, v->SZ};
+  for (int a = 0; a < 3; ++a)
+    if (o[a] < 0 || e[a] <= 0 || o[a] + e[a] > S[a]) return fail(VR_ERR_ARG, "box outside the slab");
+  CU(cudaSetDevice(ctx->device));
+  cudaMemcpy3DParms p;
+  std::memset(&p, 0, sizeof(p));
+  cudaPitchedPtr slab = make_cudaPitchedPtr(v->dev, (size_t)v->SX, (size_t)v->SX, (size_t)v->SY);
+  cudaPitchedPtr buf = make_cudaPitchedPtr(dense, (size_t)e[0], (size_t)e[0], (size_t)e[1]);
+  cudaPos at = make_cudaPos((size_t)o[0], (size_t)o[1], (size_t)o[2]), zero = make_cudaPos(0, 0, 0);
+  p.srcPtr = pack ? slab : buf; p.srcPos = pack ? at : zero;
+  p.dstPtr = pack ? buf : slab; p.dstPos = pack ? zero : at;
+  p.extent = make_cudaExtent((size_t)e[0], (size_t)e[1], (size_t)e[2]);
+  p.kind = cudaMemcpyDeviceToDevice;
+  CU(cudaMemcpy3DAsync(&p, ctx->stream));
+  return VR_OK;
+}
+int vr_volume_pack_box(vr_context* ctx, const vr_volume* v, const int64_t origin[3], const int64_t extent[3], uint8_t* dst) {
+  return box_copy(ctx, v, origin, extent, dst, true);
+}
+int vr_volume_unpack_box(vr_context* ctx, vr_volume* v, const int64_t origin[3], const int64_t extent[3], const uint8_t* src) {
+  return box_copy(ctx, v, origin, extent, const_cast<uint8_t*>(src), false);
+}
+
+}  // extern "C"

@@ -1,0 +1,302 @@
+"""Sort-last rendering of a volume sharded over GPUs: host-side logic above the C ABI.
+
+The reference renders one 3-D texture on one GPU (main.cpp:290,404).  Here every rank (one process per
+GPU) holds a box of that texture -- its own bricks decoded in place plus a halo -- and a frame is
+
+  composite  (raycaster.frag):  pass 1 per-slab segment partials (C_seg, T_seg)  ->  all-gather of T_seg
+                                ->  pass 2 per-rank (C, A) term  ->  all-reduce(sum)  ->  colour map
+  isosurface (isosurface.frag): pass 1 first hit among the slab's samples  ->  all-reduce(min) of the hit
+                                index  ->  mask  ->  all-reduce(sum) of the colours
+
+The kernels are the C ABI's vr_partial_* / vr_resolve_* / vr_finish_* (csrc/render_sortlast.cu); the
+exchange is torch.distributed (NCCL on GPUs; the same code runs over gloo with CPU tensors in the tests,
+with a CPU stand-in for the kernels supplied by the test).  Nothing here touches the oracle.
+"""
+import ctypes
+from ctypes import byref, c_int32, c_int64, c_void_p
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, lib
+from .render import COMPOSITE, RenderParams
+
+HIT_NONE = 0x7FFFFFFF
+
+
+class SlabDesc(ctypes.Structure):
+    """vr_slab_desc: where a rank's device slab sits in the whole texture."""
+    _fields_ = [("global_", c_int64 * 3), ("origin", c_int64 * 3), ("own_lo", c_int64 * 3), ("own_hi", c_int64 * 3)]
+
+    def stored(self, halo):
+        """(origin, extent) of the device slab for a halo of `halo` voxels per axis and side."""
+        o = [max(0, self.own_lo[a] - halo[a]) for a in range(3)]
+        e = [min(self.global_[a], self.own_hi[a] + halo[a]) - o[a] for a in range(3)]
+        return o, e
+
+
+_P = ctypes.POINTER
+_SIGS = {
+    "vr_sortlast_create": [c_void_p, _P(SlabDesc), c_int32, c_int32, _P(c_void_p)],
+    "vr_sortlast_destroy": [c_void_p],
+    "vr_sortlast_order": [c_void_p, c_int32, _P(c_int32)],
+    "vr_sortlast_halo": [_P(RenderParams), _P(c_int64), _P(c_int64)],
+    "vr_partial_composite": [c_void_p, c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p],
+    "vr_partial_iso": [c_void_p, c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p],
+    "vr_resolve_composite": [c_void_p, c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p, c_void_p],
+    "vr_finish_composite": [c_void_p, _P(RenderParams), c_void_p, c_void_p],
+    "vr_resolve_iso": [c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p],
+    "vr_volume_pack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
+    "vr_volume_unpack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
+}
+for _n, _a in _SIGS.items():
+    getattr(lib, _n).restype = ctypes.c_int
+    getattr(lib, _n).argtypes = _a
+_lib.EXPORTED[:] = sorted(set(_lib.EXPORTED) | set(_SIGS))
+
+
+# ---------------------------------------------------------------------------------------------------
+# layout
+def required_halo(params, global_dims):
+    """Voxels per axis and side a slab must hold around its owned box (vr_sortlast_halo)."""
+    g = (c_int64 * 3)(*[int(v) for v in global_dims])
+    h = (c_int64 * 3)()
+    check(lib.vr_sortlast_halo(byref(params), g, h))
+    return [int(v) for v in h]
+
+
+def slab_layout(global_dims, n_ranks, axis=1, halo=(1, 1, 1)):
+    """Partition the texture into n_ranks slabs along `axis` (y-slabs by brick row).
+    Returns (descs, stored) with stored[r] = (origin, extent) of rank r's device slab."""
+    G = [int(v) for v in global_dims]
+    if G[axis] % n_ranks:
+        raise ValueError(f"extent {G[axis]} along axis {axis} does not divide into {n_ranks} slabs")
+    w = G[axis] // n_ranks
+    descs, stored = [], []
+    for r in range(n_ranks):
+        d = SlabDesc()
+        lo, hi = [0, 0, 0], list(G)
+        lo[axis], hi[axis] = r * w, (r + 1) * w
+        d.global_[:] = G
+        d.own_lo[:] = lo
+        d.own_hi[:] = hi
+        o, e = d.stored(halo)
+        d.origin[:] = o
+        descs.append(d)
+        stored.append((o, e))
+    return descs, stored
+
+
+def halo_transfers(descs, stored):
+    """Boxes that must travel between ranks so every device slab is complete: for each ordered pair
+    (src, dst) the part of dst's stored box that src owns.  Returns [(src, dst, global_lo, extent)]."""
+    out = []
+    for dst, (o, e) in enumerate(stored):
+        for src, d in enumerate(descs):
+            if src == dst:
+                continue
+            lo = [max(o[a], d.own_lo[a]) for a in range(3)]
+            hi = [min(o[a] + e[a], d.own_hi[a]) for a in range(3)]
+            if all(hi[a] > lo[a] for a in range(3)):
+                out.append((src, dst, lo, [hi[a] - lo[a] for a in range(3)]))
+    return out
+
+
+class SortLast:
+    """vr_sortlast: the slab geometry of all ranks + the visibility orders, bound to one rank."""
+
+    def __init__(self, ctx, descs, rank):
+        self.ctx, self.n, self.rank = ctx, len(descs), int(rank)
+        arr = (SlabDesc * self.n)(*descs)
+        self.h = c_void_p()
+        check(lib.vr_sortlast_create(ctx.h if ctx is not None else None, arr, self.n, self.rank, byref(self.h)))
+
+    def order(self, octant):
+        out = (c_int32 * self.n)()
+        check(lib.vr_sortlast_order(self.h, int(octant), out))
+        return list(out)
+
+    def close(self):
+        if self.h:
+            lib.vr_sortlast_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------------------------
+# device ops: the C ABI on torch CUDA tensors (torch is plumbing: memory + streams + collectives)
+class CudaSlabOps:
+    def __init__(self, ctx, sortlast, volume, width, height, count_samples=False):
+        import torch
+        self.torch, self.ctx, self.sl, self.vol = torch, ctx, sortlast, volume
+        self.W, self.H = int(width), int(height)
+        dev = torch.device("cuda", ctx.device)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.cseg = torch.empty((self.H, self.W), **f32)
+        self.tseg = torch.empty((self.H, self.W), **f32)
+        self.contrib = torch.empty((self.H, self.W, 2), **f32)
+        self.rgba = torch.empty((self.H, self.W, 4), **f32)
+        self.hit = torch.empty((self.H, self.W), dtype=torch.int32, device=dev)
+        self.samples = torch.zeros(1, dtype=torch.int64, device=dev) if count_samples else None
+
+    def _cnt(self):
+        return c_void_p(self.samples.data_ptr()) if self.samples is not None else None
+
+    def partial_composite(self, p):
+        check(lib.vr_partial_composite(self.ctx.h, self.sl.h, self.vol.h, byref(p), c_void_p(self.cseg.data_ptr()),
+                                       c_void_p(self.tseg.data_ptr()), self._cnt()))
+        return self.cseg, self.tseg
+
+    def resolve_composite(self, p, tseg_all, cseg):
+        assert tseg_all.is_contiguous() and tseg_all.shape[0] == self.sl.n
+        check(lib.vr_resolve_composite(self.ctx.h, self.sl.h, self.vol.h, byref(p), c_void_p(tseg_all.data_ptr()),
+                                       c_void_p(cseg.data_ptr()), c_void_p(self.contrib.data_ptr()), self._cnt()))
+        return self.contrib
+
+    def finish_composite(self, p, total):
+        check(lib.vr_finish_composite(self.ctx.h, byref(p), c_void_p(total.data_ptr()), c_void_p(self.rgba.data_ptr())))
+        return self.rgba
+
+    def partial_iso(self, p):
+        check(lib.vr_partial_iso(self.ctx.h, self.sl.h, self.vol.h, byref(p), c_void_p(self.rgba.data_ptr()),
+                                 c_void_p(self.hit.data_ptr()), self._cnt()))
+        return self.rgba, self.hit
+
+    def resolve_iso(self, p, hit, hit_min, rgba):
+        check(lib.vr_resolve_iso(self.ctx.h, self.sl.h, byref(p), c_void_p(hit.data_ptr()), c_void_p(hit_min.data_ptr()),
+                                 c_void_p(rgba.data_ptr())))
+        return rgba
+
+    # halo boxes <-> dense buffers
+    def pack_box(self, origin, extent):
+        buf = self.torch.empty((extent[2], extent[1], extent[0]), dtype=self.torch.uint8, device=self.cseg.device)
+        check(lib.vr_volume_pack_box(self.ctx.h, self.vol.h, (c_int64 * 3)(*origin), (c_int64 * 3)(*extent), c_void_p(buf.data_ptr())))
+        return buf
+
+    def unpack_box(self, origin, extent, buf):
+        assert buf.is_contiguous()
+        check(lib.vr_volume_unpack_box(self.ctx.h, self.vol.h, (c_int64 * 3)(*origin), (c_int64 * 3)(*extent), c_void_p(buf.data_ptr())))
+
+    def empty_box(self, extent):
+        return self.torch.empty((extent[2], extent[1], extent[0]), dtype=self.torch.uint8, device=self.cseg.device)
+
+
+# ---------------------------------------------------------------------------------------------------
+# exchange
+class TorchDistExchange:
+    """The frame's collectives over torch.distributed (NCCL over NVLink on GPUs, gloo in CPU tests)."""
+
+    def __init__(self, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.group = torch, dist, group
+        self.n = dist.get_world_size(group)
+        self._gather = None
+
+    def all_gather(self, t):
+        if self._gather is None or self._gather.shape[1:] != t.shape or self._gather.device != t.device:
+            self._gather = self.torch.empty((self.n,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        self.dist.all_gather_into_tensor(self._gather.view(-1), t.contiguous().view(-1), group=self.group)
+        return self._gather
+
+    def all_reduce_sum(self, t):
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    def all_reduce_min(self, t):
+        out = t.clone()
+        self.dist.all_reduce(out, op=self.dist.ReduceOp.MIN, group=self.group)
+        return out
+
+
+def frame_steps(ops, params):
+    """One sort-last frame of one rank as a coroutine: yields (collective, tensor) requests, receives the
+    collective's result, returns the finished RGBA frame [H, W, 4] (row 0 = bottom row)."""
+    if params.mode == COMPOSITE:
+        cseg, tseg = ops.partial_composite(params)
+        tseg_all = yield ("all_gather", tseg)
+        contrib = ops.resolve_composite(params, tseg_all, cseg)
+        total = yield ("all_reduce_sum", contrib)
+        return ops.finish_composite(params, total)
+    rgba, hit = ops.partial_iso(params)
+    hit_min = yield ("all_reduce_min", hit)
+    rgba = ops.resolve_iso(params, hit, hit_min, rgba)
+    total = yield ("all_reduce_sum", rgba)
+    return total
+
+
+def render_frame(ops, exchange, params):
+    """Drive frame_steps with real collectives (one process per GPU)."""
+    gen = frame_steps(ops, params)
+    try:
+        req = next(gen)
+        while True:
+            kind, t = req
+            req = gen.send(getattr(exchange, kind)(t))
+    except StopIteration as fin:
+        return fin.value
+
+
+def render_frame_lockstep(ops_list, params):
+    """All ranks in ONE process (virtual ranks on one device, or CPU stand-ins): the collectives are done
+    locally on the list of tensors.  Returns every rank's finished frame."""
+    import torch
+    gens = [frame_steps(o, params) for o in ops_list]
+    reqs = [next(g) for g in gens]
+    done = [None] * len(gens)
+    while any(d is None for d in done):
+        kind = reqs[0][0]
+        assert all(r[0] == kind for r in reqs)
+        ts = [r[1] for r in reqs]
+        if kind == "all_gather":
+            res = [torch.stack(ts).contiguous()] * len(ts)
+        elif kind == "all_reduce_sum":
+            tot = torch.stack(ts).sum(0)
+            res = [tot.clone() for _ in ts]
+        elif kind == "all_reduce_min":
+            tot = torch.stack(ts).amin(0)
+            res = [tot.clone() for _ in ts]
+        else:
+            raise ValueError(kind)
+        for i, g in enumerate(gens):
+            try:
+                reqs[i] = g.send(res[i])
+            except StopIteration as fin:
+                done[i] = fin.value
+    return done
+
+
+# ---------------------------------------------------------------------------------------------------
+# halo exchange (once per decoded timestep, not per frame)
+def exchange_halos(ops, descs, stored, rank, dist=None, group=None):
+    """Fill rank's halo from the ranks that own it and serve the others' halos (grouped point-to-point
+    sends: ncclSend/ncclRecv under torch.distributed.batch_isend_irecv)."""
+    import torch.distributed as tdist
+    dist = dist or tdist
+    my_o = stored[rank][0]
+    p2p, recvs = [], []
+    for src, dst, lo, ext in halo_transfers(descs, stored):
+        if src == rank:
+            o_src = [lo[a] - stored[src][0][a] for a in range(3)]
+            p2p.append(dist.P2POp(dist.isend, ops.pack_box(o_src, ext), dst, group=group))
+        elif dst == rank:
+            buf = ops.empty_box(ext)
+            recvs.append(([lo[a] - my_o[a] for a in range(3)], ext, buf))
+            p2p.append(dist.P2POp(dist.irecv, buf, src, group=group))
+    if p2p:
+        for w in dist.batch_isend_irecv(p2p):
+            w.wait()
+    for o, ext, buf in recvs:
+        ops.unpack_box(o, ext, buf)
+
+
+def exchange_halos_lockstep(ops_list, descs, stored):
+    """Same for virtual ranks living in one process."""
+    for src, dst, lo, ext in halo_transfers(descs, stored):
+        buf = ops_list[src].pack_box([lo[a] - stored[src][0][a] for a in range(3)], ext)
+        ops_list[dst].unpack_box([lo[a] - stored[dst][0][a] for a in range(3)], ext, buf)
