@@ -8,7 +8,10 @@ Workload `rm_yslab` (BASELINE config 4 shape): the synthetic Richt
 reference's brick grid (256x256x128 bricks, grid 8x8x15).  Rank r owns the y-slab j = r: 120 bricks =
 2048x256x1920 voxels (0.94 GiB); N = 8 is exactly the full 2048x2048x1920 volume (weak scaling, no
 data-path collective for decode).  A step = stage 1 (one batched decode launch of the rank's 120 streams
-into its slab) + stage 2 (one 1024^2 colour-compositing frame of that slab).  Inputs are larger than L2
+into its slab) + stage 2 (one 1024^2 colour-compositing frame).  At N = 1 the frame is the plain march of the
+rank's slab; at N > 1 the texture is the N slabs side by side (2048 x 256N x 1920) and the frame is the
+sort-last composite over NCCL (halo rows exchanged after the decode, segment partials, all-gather of
+T_seg, resolve, all-reduce, colour map: volumerenderer_b200/sortlast.py).  Inputs are larger than L2
 (the slab alone is 8x the 126 MB L2), so no explicit flush is needed between iterations.
 metric: decoded GVoxel/s through the whole step (decode + frame); frames/s and G samples/s are extra keys.
 """
@@ -128,32 +131,51 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     threads = max(1, (os.cpu_count() or 8) // max(1, world))
-    ctx = vr.Context(local)
+    # the library launches on torch's current stream so NCCL collectives and kernels are ordered
+    ctx = vr.Context(local, cuda_stream=torch.cuda.current_stream().cuda_stream)
     t_setup = time.time()
     bricks, streams, _ = build_streams(vr, rank, threads)
     uniq = {id(s): s for s in streams}
     for s in uniq.values():
         s.pin()
         s.upload(ctx)
-    vol = vr.Volume(ctx, GI * BX, BY, GK * BZ)
-    origins = [(i * BX, 0, k * BZ) for (i, j, k) in bricks]
+    p = render.default_params(IMG, IMG, render.COMPOSITE)
+    if world > 1:
+        from volumerenderer_b200 import sortlast
+        G = (GI * BX, BY * world, GK * BZ)
+        descs, stored = sortlast.slab_layout(G, world, axis=1, halo=sortlast.required_halo(p, G))
+        so, se = stored[rank]
+        vol = vr.Volume(ctx, *se).set_cell_origin(so)  # owned rows + one halo row per interior side
+        origins = [(i * BX - so[0], rank * BY - so[1], k * BZ - so[2]) for (i, j, k) in bricks]
+        sl = sortlast.SortLast(ctx, descs, rank)
+        ops = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=True)
+        exch = sortlast.TorchDistExchange()
+    else:
+        vol = vr.Volume(ctx, GI * BX, BY, GK * BZ)
+        origins = [(i * BX, 0, k * BZ) for (i, j, k) in bricks]
     plan = vr.DecodePlan(ctx, streams, origins, vol)
     by = plan.bytes()
-    p = render.default_params(IMG, IMG, render.COMPOSITE)
     out = torch.empty((IMG, IMG, 4), dtype=torch.float32, device=f"cuda:{local}")
     cnt = torch.zeros(1, dtype=torch.int64, device=f"cuda:{local}")
     host_img = torch.empty((IMG, IMG, 4), dtype=torch.float32).pin_memory()
     torch.cuda.synchronize()
     t_setup = time.time() - t_setup
 
+    def frame():
+        if world > 1:
+            sortlast.exchange_halos(ops, descs, stored, rank)
+            return sortlast.render_frame(ops, exch, p)
+        render.render_device(ctx, vol, p, out.data_ptr())
+        return out
+
     def step(slot=None):
-        # slot != None: bracket each launch with its own CUDA-event pair (read back after the region)
+        # slot != None: bracket each stage with its own CUDA-event pair (read back after the region)
         if slot is None:
             plan.run()
-            render.render_device(ctx, vol, p, out.data_ptr())
+            frame()
         else:
             ctx.timer_begin(slot); plan.run(); ctx.timer_end(slot)
-            ctx.timer_begin(slot + 1); render.render_device(ctx, vol, p, out.data_ptr()); ctx.timer_end(slot + 1)
+            ctx.timer_begin(slot + 1); frame(); ctx.timer_end(slot + 1)
 
     def barrier():
         ctx.synchronize(); torch.cuda.synchronize()
@@ -164,9 +186,16 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step(1)
     # samples per frame (effective march steps reaching the fetch), counted once outside the timed region
-    cnt.zero_(); torch.cuda.synchronize()
-    render.render_device(ctx, vol, p, out.data_ptr(), None, cnt.data_ptr()); ctx.synchronize()
-    samples = int(cnt.item())
+    torch.cuda.synchronize()
+    if world > 1:
+        ops.samples.zero_(); frame(); torch.cuda.synchronize()
+        t = ops.samples.clone(); dist.all_reduce(t)
+        samples = int(t.item())  # fetches of all ranks, both passes
+        ops.samples = None       # not counted inside the timed region
+    else:
+        cnt.zero_(); torch.cuda.synchronize()
+        render.render_device(ctx, vol, p, out.data_ptr(), None, cnt.data_ptr()); ctx.synchronize()
+        samples = int(cnt.item())
 
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
@@ -201,9 +230,10 @@ def run_ours(args):
         for s in uniq.values():
             s.upload(ctx)
         plan.run()
-        render.render_device(ctx, vol, p, out.data_ptr())
+        img = frame()
         ctx.synchronize()
-        host_img.copy_(out, non_blocking=False)
+        if rank == 0:
+            host_img.copy_(img, non_blocking=False)
 
     for _ in range(2):
         e2e_step()
@@ -225,11 +255,11 @@ def run_ours(args):
     peak, peak_src = peaks()
     d_ms, m_ms = float(np.mean(dec_ms)), float(np.mean(mar_ms))
     dec_bytes = by["stream"] + by["voxels"]
-    mar_bytes = 8 * samples + 16 * IMG * IMG
+    mar_bytes = 8 * samples // world + 16 * IMG * IMG  # per rank (N > 1: an even share of all ranks' fetches)
     roof_dec = {"kernel": "kd_decode_tiles_kernel", "bound": "hbm", "achieved": dec_bytes / d_ms / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": dec_bytes / d_ms / 1e6 / peak, "traffic": None, "ms": d_ms, "algorithmic_bytes": dec_bytes,
                 "index_bytes": by["index"], "peak_source": peak_src}
-    roof_mar = {"kernel": "march_kernel<composite>", "bound": "hbm", "achieved": mar_bytes / m_ms / 1e6, "peak": peak, "unit": "GB/s",
+    roof_mar = {"kernel": "march_kernel<composite>" if world == 1 else "sort-last frame (halo + partial + all-gather + resolve + all-reduce + finish)", "bound": "hbm", "achieved": mar_bytes / m_ms / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": mar_bytes / m_ms / 1e6 / peak, "traffic": None, "ms": m_ms, "algorithmic_bytes": mar_bytes,
                 "peak_source": peak_src}
     tr = os.path.join(ROOT, "profiles", "traffic.json")
@@ -250,13 +280,15 @@ def run_ours(args):
                                "colour-compositing frame (reference camera); N=8 is the full 2048x2048x1920 volume",
                    "bricks_per_gpu": len(streams), "image": [IMG, IMG], "bits_per_voxel": 2.0 * nodes / voxels_rank,
                    "l2": "inputs+outputs per step (>= 1 GB) exceed the 126 MB L2; no explicit flush",
-                   "multi_gpu": "bricks sharded by y-slab, no data-path collective for decode; frames are per-slab"},
+                   "multi_gpu": ("single slab, plain march" if world == 1 else
+                                 f"texture = {world} y-slabs (2048x{256 * world}x1920); decode has no collective; frame = sort-last composite "
+                                 "over NCCL (halo send/recv, all-gather T_seg 4 MiB/rank, all-reduce (C,A) 8 MiB)")},
         "stages": {"decode_ms": d_ms, "march_ms": m_ms, "decode_gvoxels_per_s": voxels_rank / d_ms / 1e6,
                    "frames_per_s": 1e3 / m_ms, "gsamples_per_s": samples / m_ms / 1e6, "samples_per_frame": samples},
         "roofline": dominant, "roofline_decode": roof_dec, "roofline_march": roof_mar,
         "e2e": {"value": voxels_all / e2e_ms / 1e6, "unit": "GVoxel/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps},
-        "gpu_launches": 2 * args.steps, "clocks": clocks, "setup_s": t_setup,
+        "gpu_launches": (2 if world == 1 else 4) * args.steps,  # own kernels per step (N > 1: decode, partial, resolve, finish) "clocks": clocks, "setup_s": t_setup,
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)

@@ -341,6 +341,8 @@ void oracle_resolve_composite(const uint8_t* slab, const int32_t* geom, const vo
         if (crossPos < 0 && (1.0f - T) > 0.99f) crossPos = k;
       }
       if (crossPos >= 0 && crossPos < myPos) {
+      } else if (crossPos == myPos && Tin == 1.0f) {
+        tC = cseg[pix]; tA = 1.0f - tsegAll[(int64_t)rank * npix + pix];
       } else if (crossPos == myPos) {
         float C = 0.0f, A = 1.0f - Tin;
         segment(v, vUV, ds, &C, &A);

@@ -44,7 +44,7 @@ def _make_ranks(ctx, full, n, axis, p, fill_halo_by_exchange=True):
     ops = []
     for r in range(n):
         o, e = stored[r]
-        vol = vr.Volume(ctx, *e)
+        vol = vr.Volume(ctx, *e).set_cell_origin(o)
         lo = [descs[r].own_lo[a] for a in range(3)]; hi = [descs[r].own_hi[a] for a in range(3)]
         own = np.ascontiguousarray(full[lo[2]:hi[2], lo[1]:hi[1], lo[0]:hi[0]])
         torch.cuda.synchronize()
@@ -112,7 +112,7 @@ def test_compressed_bricks_decode_into_slabs(ctx):
     ops = []
     for r in range(2):
         o, e = stored[r]
-        vol = vr.Volume(ctx, *e)
+        vol = vr.Volume(ctx, *e).set_cell_origin(o)
         vol.upload_brick(np.zeros((e[2], e[1], e[0]), np.uint8), (0, 0, 0))
         streams, origins = [], []
         for k in range(2):

@@ -68,6 +68,10 @@ _SIGS = {
     "vr_volume_dims": (c_int, [c_void_p, POINTER(c_int64)]),
     "vr_volume_download": (c_int, [c_void_p, c_void_p, c_void_p]),
     "vr_volume_upload_brick": (c_int, [c_void_p, c_void_p, c_void_p] + [c_int64] * 6),
+    "vr_volume_set_cell_origin": (c_int, [c_void_p, POINTER(c_int64)]),
+    "vr_volume_set_skipping": (c_int, [c_void_p, c_int]),
+    "vr_volume_invalidate": (c_int, [c_void_p]),
+    "vr_volume_occupancy_download": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, POINTER(c_int32)]),
     "vr_decode_plan_create": (c_int, [c_void_p, POINTER(c_void_p), c_int32, POINTER(c_int64), c_void_p, POINTER(c_void_p)]),
     "vr_decode_plan_run": (c_int, [c_void_p]),
     "vr_decode_plan_destroy": (c_int, [c_void_p]),

@@ -35,6 +35,7 @@ typedef struct vr_kd_job {
   uint64_t chainDist;            // byte k-1 = distanceMap[D0 + k] for k = 1..7
   int64_t dstOffset;             // voxel offset of the brick's (0,0,0) inside the destination slab
   const uint32_t* chainLut;      // [16384] refinement-chain table for this stream's chainDist (vr_chain_lut_entry)
+  int64_t occBase;               // occupancy cell of the brick's (0,0,0) in the destination's grid, < 0 = tiles are not cells
 } vr_kd_job;
 
 // Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
@@ -377,8 +378,18 @@ VR_HD void vr_tile_phase1_v2(const vr_kd_job& job, const vr_kd_geom& g, uint32_t
 // (a warp's 32 leaf subtrees when unitBits = leafBits + 5).  Item q = one 16-byte x-run; the other
 // unitBits-4 free path bits are enumerated by the bits of q in increasing path-bit order.
 // Requires the 4 low x bits to map to path bits < unitBits (checked on the host).
-VR_HD void vr_unit_phase2_item(const vr_kd_geom& g, uint32_t unit, uint32_t q, const uint8_t* strips,
-                               uint8_t* dstTile, int64_t rowPitch, int64_t slicePitch) {
+VR_HD uint32_t vr_bmax4(uint32_t a, uint32_t b) {  // per-byte unsigned max
+#if defined(__CUDA_ARCH__)
+  return __vmaxu4(a, b);
+#else
+  uint32_t r = 0;
+  for (int i = 0; i < 4; ++i) { uint32_t x = (a >> (8 * i)) & 0xFF, y = (b >> (8 * i)) & 0xFF; r |= (x > y ? x : y) << (8 * i); }
+  return r;
+#endif
+}
+// Returns the per-byte maximum of the 16 voxels written (for the occupancy bound of the tile).
+VR_HD uint32_t vr_unit_phase2_item(const vr_kd_geom& g, uint32_t unit, uint32_t q, const uint8_t* strips,
+                                   uint8_t* dstTile, int64_t rowPitch, int64_t slicePitch) {
   const uint32_t m = q | (unit << g.fbUnit);  // one bit per free path bit, increasing path-bit order
   uint32_t sAddr = 0;
   int64_t gOff = 0;
@@ -410,6 +421,7 @@ VR_HD void vr_unit_phase2_item(const vr_kd_geom& g, uint32_t unit, uint32_t q, c
   for (int k = 0; k < 4; ++k)
     for (int i = 0; i < 4; ++i) out[k * 4 + i] = (uint8_t)(w[k] >> (8 * i));
 #endif
+  return vr_bmax4(vr_bmax4(w[0], w[1]), vr_bmax4(w[2], w[3]));
 }
 
 

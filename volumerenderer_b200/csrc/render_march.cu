@@ -20,9 +20,9 @@ using namespace dev;
 
 namespace {
 
-template <int MODE>
-__global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ RenderParams P, const uint8_t* __restrict__ vol,
-                                                    int X, int Y, int Z, float4* __restrict__ out,
+template <int MODE, bool OCC>
+__global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ RenderParams P, const __grid_constant__ OccView occ,
+                                                    const uint8_t* __restrict__ vol, int X, int Y, int Z, float4* __restrict__ out,
                                                     int* __restrict__ hitIndex, unsigned long long* __restrict__ sampleCount) {
   // block = 32x8 pixels = 8 warps; warp w covers an 8x4 tile
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -43,6 +43,14 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
         for (int i = 0; i < 300; ++i) {
           p = add(p, dirStep);
           if (!inside(p)) break;
+          if (OCC) {  // void cell: the sample is exactly 0 and leaves (C, A) unchanged
+            const int k = occ_skip<false>(occ, v, p, dirStep, 299 - i);
+            if (k >= 0) {
+              for (int j = 0; j < k; ++j) p = add(p, dirStep);
+              i += k; n += 1 + k;
+              continue;
+            }
+          }
           float smp = tex<false>(v, p);
           ++n;
           float prev_alpha = fsub(smp, fmul(smp, A));
@@ -55,8 +63,17 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
         for (int i = 0; i < 300; ++i) {
           p = add(p, dirStep);
           if (!inside(p)) break;
+          const V3 pn = add(p, dirStep);
+          if (OCC) {  // every tap of the look-ahead sample is below the iso value: no crossing can be detected here
+            const int k = occ_skip<false>(occ, v, pn, dirStep, 299 - i);
+            if (k >= 0) {
+              for (int j = 0; j < k; ++j) p = add(p, dirStep);
+              i += k; n += 1 + k;
+              continue;
+            }
+          }
           float smp = tex<false>(v, p);
-          float smp2 = tex<false>(v, add(p, dirStep));
+          float smp2 = tex<false>(v, pn);
           ++n;
           if (fsub(smp, P.iso) < 0.0f && fsub(smp2, P.iso) >= 0.0f) {
             rgba = iso_shade<false>(v, P, p, dir, dirStep);
@@ -77,13 +94,16 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
 
 }  // namespace
 
-cudaError_t render_launch(const RenderParams& P, const uint8_t* vol, int X, int Y, int Z, float4* out, int* hitIndex,
-                          unsigned long long* sampleCount, cudaStream_t stream) {
+cudaError_t render_launch(const RenderParams& P, const OccView& occ, const uint8_t* vol, int X, int Y, int Z, float4* out,
+                          int* hitIndex, unsigned long long* sampleCount, cudaStream_t stream) {
   dim3 grid((P.W + 31) / 32, (P.H + 7) / 8), block(256);
-  if (P.mode == 0)
-    march_kernel<0><<<grid, block, 0, stream>>>(P, vol, X, Y, Z, out, hitIndex, sampleCount);
-  else
-    march_kernel<1><<<grid, block, 0, stream>>>(P, vol, X, Y, Z, out, hitIndex, sampleCount);
+  if (P.mode == 0) {
+    if (occ.dil) march_kernel<0, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+    else march_kernel<0, false><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+  } else {
+    if (occ.dil) march_kernel<1, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+    else march_kernel<1, false><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+  }
   return cudaGetLastError();
 }
 

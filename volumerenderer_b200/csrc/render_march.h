@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "occupancy.h"
+
 namespace vr {
 // Same field order as the oracle's Params (oracle/render_oracle.cpp): camera basis precomputed on the host.
 struct RenderParams {
@@ -12,8 +14,9 @@ struct RenderParams {
   float iso;
   int W, H, mode;  // mode 0 composite, 1 isosurface
 };
-cudaError_t render_launch(const RenderParams& P, const uint8_t* vol, int X, int Y, int Z, float4* out, int* hitIndex,
-                          unsigned long long* sampleCount, cudaStream_t stream);
+// occ.dil == null: march every sample; otherwise skip void cells (occupancy.h), same frame bit for bit
+cudaError_t render_launch(const RenderParams& P, const OccView& occ, const uint8_t* vol, int X, int Y, int Z, float4* out,
+                          int* hitIndex, unsigned long long* sampleCount, cudaStream_t stream);
 
 // ---- sort-last: one device slab of a volume sharded over ranks -----------------------
 // G = extent of the whole texture, o/S = origin and extent of the stored box (owned box + halo),
@@ -22,16 +25,16 @@ struct SlabGeom { int G[3], o[3], S[3], lo[3], hi[3]; };
 #define VR_MAX_RANKS 64
 #define VR_HIT_NONE 0x7FFFFFFF
 // pass 1, composite: per pixel the segment partial (C_seg, T_seg) over the samples this slab owns
-cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float* cseg, float* tseg,
-                                     unsigned long long* sampleCount, cudaStream_t stream);
+cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float* cseg,
+                                     float* tseg, unsigned long long* sampleCount, cudaStream_t stream);
 // pass 1, isosurface: first hit among the owned samples: colour (0 if none) and global sample index (VR_HIT_NONE)
-cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float4* rgba, int* hit,
+cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float4* rgba, int* hit,
                                unsigned long long* sampleCount, cudaStream_t stream);
 // pass 2, composite: tsegAll = n x (W*H) segment transmittances of all ranks; order = 8 x n visibility
 // orders (device), one per direction octant.  contrib = per pixel (C, A) term of this rank; the sum of
 // the terms over ranks is the frame's (C, A).
-cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, const float* tsegAll, int n,
-                                     int rank, const int* order, const float* cseg, float2* contrib,
+cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
+                                     const float* tsegAll, int n, int rank, const int* order, const float* cseg, float2* contrib,
                                      unsigned long long* sampleCount, cudaStream_t stream);
 // colour map of raycaster.frag:82-85 on the summed terms; white where the view ray misses the cube
 cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, float4* out, cudaStream_t stream);

@@ -38,7 +38,8 @@ __device__ __forceinline__ void count_samples(unsigned long long* sampleCount, u
 
 // Reference recurrence over the owned samples of one ray, started at (C, A).  A slab is convex, so the
 // owned samples are one run of the lattice: stop at the first sample after it.
-__device__ __forceinline__ void march_segment(const Vol& v, V3 p, V3 dirStep, float* C, float* A, unsigned* n) {
+template <bool OCC>
+__device__ __forceinline__ void march_segment(const Vol& v, const OccView& occ, V3 p, V3 dirStep, float* C, float* A, unsigned* n) {
   float c = *C, a = *A;
   bool started = false;
   for (int i = 0; i < 300; ++i) {
@@ -49,6 +50,14 @@ __device__ __forceinline__ void march_segment(const Vol& v, V3 p, V3 dirStep, fl
       continue;
     }
     started = true;
+    if (OCC) {  // void cell: exactly-zero samples change nothing (skipped positions need no ownership test either)
+      const int k = occ_skip<true>(occ, v, p, dirStep, 299 - i);
+      if (k >= 0) {
+        for (int j = 0; j < k; ++j) p = add(p, dirStep);
+        i += k; *n += 1 + k;
+        continue;
+      }
+    }
     float smp = tex<true>(v, p);
     ++*n;
     float prev_alpha = fsub(smp, fmul(smp, a));
@@ -59,8 +68,10 @@ __device__ __forceinline__ void march_segment(const Vol& v, V3 p, V3 dirStep, fl
   *C = c; *A = a;
 }
 
+template <bool OCC>
 __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_constant__ RenderParams P,
                                                                 const __grid_constant__ SlabGeom g,
+                                                                const __grid_constant__ OccView occ,
                                                                 const uint8_t* __restrict__ vol, float* __restrict__ cseg,
                                                                 float* __restrict__ tseg,
                                                                 unsigned long long* __restrict__ sampleCount) {
@@ -73,7 +84,7 @@ __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_con
       Vol v = make_vol(g, vol);
       V3 dir, dirStep;
       ray_dir(P, vUV, &dir, &dirStep);
-      march_segment(v, vUV, dirStep, &C, &A, &n);
+      march_segment<OCC>(v, occ, vUV, dirStep, &C, &A, &n);
     }
     cseg[(long long)py * P.W + px] = C;
     tseg[(long long)py * P.W + px] = fsub(1.0f, A);
@@ -81,8 +92,10 @@ __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_con
   count_samples(sampleCount, n);
 }
 
+template <bool OCC>
 __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant__ RenderParams P,
-                                                          const __grid_constant__ SlabGeom g, const uint8_t* __restrict__ vol,
+                                                          const __grid_constant__ SlabGeom g,
+                                                          const __grid_constant__ OccView occ, const uint8_t* __restrict__ vol,
                                                           float4* __restrict__ rgbaOut, int* __restrict__ hitOut,
                                                           unsigned long long* __restrict__ sampleCount) {
   int px, py;
@@ -105,8 +118,17 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
           continue;
         }
         started = true;
+        const V3 pn = add(p, dirStep);
+        if (OCC) {
+          const int k = occ_skip<true>(occ, v, pn, dirStep, 299 - i);
+          if (k >= 0) {
+            for (int j = 0; j < k; ++j) p = add(p, dirStep);
+            i += k; n += 1 + k;
+            continue;
+          }
+        }
         float smp = tex<true>(v, p);
-        float smp2 = tex<true>(v, add(p, dirStep));
+        float smp2 = tex<true>(v, pn);
         ++n;
         if (fsub(smp, P.iso) < 0.0f && fsub(smp2, P.iso) >= 0.0f) {
           rgba = iso_shade<true>(v, P, p, dir, dirStep);
@@ -121,8 +143,10 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
   count_samples(sampleCount, n);
 }
 
+template <bool OCC>
 __global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_constant__ RenderParams P,
                                                                 const __grid_constant__ SlabGeom g,
+                                                                const __grid_constant__ OccView occ,
                                                                 const uint8_t* __restrict__ vol, const float* __restrict__ tsegAll,
                                                                 int nRanks, int rank, const int* __restrict__ order,
                                                                 const float* __restrict__ cseg, float2* __restrict__ contrib,
@@ -150,11 +174,14 @@ __global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_con
       }
       if (crossPos >= 0 && crossPos < myPos) {
         // the ray terminated in a slab in front of this one
+      } else if (crossPos == myPos && Tin == 1.0f) {
+        // nothing in front of this slab: pass 1 already ran the reference recurrence from A = 0
+        term = make_float2(__ldg(cseg + pix), fsub(1.0f, __ldg(tsegAll + (long long)rank * npix + pix)));
       } else if (crossPos == myPos) {
         // the ray terminates inside this segment: replay it with the reference recurrence from A_in
         Vol v = make_vol(g, vol);
         float C = 0.0f, A = fsub(1.0f, Tin);
-        march_segment(v, vUV, dirStep, &C, &A, &n);
+        march_segment<OCC>(v, occ, vUV, dirStep, &C, &A, &n);
         term = make_float2(C, A);
       } else {
         term.x = fmul(Tin, __ldg(cseg + pix));
@@ -198,20 +225,23 @@ dim3 pixel_grid(const RenderParams& P) { return dim3((P.W + 31) / 32, (P.H + 7) 
 
 }  // namespace
 
-cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float* cseg, float* tseg,
-                                     unsigned long long* sampleCount, cudaStream_t stream) {
-  partial_composite_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, cseg, tseg, sampleCount);
+cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float* cseg,
+                                     float* tseg, unsigned long long* sampleCount, cudaStream_t stream) {
+  if (occ.dil) partial_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, tseg, sampleCount);
+  else partial_composite_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, tseg, sampleCount);
   return cudaGetLastError();
 }
-cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, float4* rgba, int* hit,
+cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float4* rgba, int* hit,
                                unsigned long long* sampleCount, cudaStream_t stream) {
-  partial_iso_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, rgba, hit, sampleCount);
+  if (occ.dil) partial_iso_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, rgba, hit, sampleCount);
+  else partial_iso_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, rgba, hit, sampleCount);
   return cudaGetLastError();
 }
-cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const uint8_t* vol, const float* tsegAll, int n,
-                                     int rank, const int* order, const float* cseg, float2* contrib,
+cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
+                                     const float* tsegAll, int n, int rank, const int* order, const float* cseg, float2* contrib,
                                      unsigned long long* sampleCount, cudaStream_t stream) {
-  resolve_composite_kernel<<<pixel_grid(P), 256, 0, stream>>>(P, g, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
+  if (occ.dil) resolve_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
+  else resolve_composite_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
   return cudaGetLastError();
 }
 cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, float4* out, cudaStream_t stream) {

@@ -122,6 +122,7 @@ int vr_volume_wrap(vr_context* ctx, void* p, int64_t SX, int64_t SY, int64_t SZ,
 }
 int vr_volume_destroy(vr_volume* v) {
   if (!v) return VR_OK;
+  v->occ_free();
   if (v->owned && v->dev) { cudaSetDevice(v->device); cudaFree(v->dev); }
   delete v;
   return VR_OK;
@@ -157,6 +158,8 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
   p.extent = make_cudaExtent((size_t)BX, (size_t)BY, (size_t)BZ);
   p.kind = cudaMemcpyHostToDevice;
   CU(cudaMemcpy3DAsync(&p, ctx->stream));
+  const int64_t lo[3] = {ox, oy, oz}, ext[3] = {BX, BY, BZ};
+  volume_occ_written(ctx, v, lo, ext);
   return VR_OK;
 }
 
@@ -174,6 +177,8 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   bool vec16 = (g.tx >= 16) && (dst->SX % 16 == 0) && (((uintptr_t)dst->dev) % 16 == 0);
   vr_decode_plan* p = new vr_decode_plan;
   p->ctx = ctx; p->geom = g; p->n = n; p->dst = dst;
+  // the kernel keeps the occupancy grid current when every decode tile is exactly one cell (32x32x16)
+  bool occFused = dst->skipping && g.fastPath && g.tx == 32 && g.ty == 32 && g.tz == 16 && volume_occ_alloc(dst) == VR_OK;
   for (int i = 0; i < n; ++i) {
     vr_stream* s = streams[i];
     if (!s || !s->devImage || s->device != ctx->device) { delete p; return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
@@ -194,6 +199,12 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     for (int hh = 0; hh <= g.leafBits && hh < 8; ++hh) j.treeDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 - hh)] << (8 * hh);
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) j.chainDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 + k)] << (8 * (k - 1));
     j.dstOffset = (oz * dst->SY + oy) * dst->SX + ox;
+    j.occBase = -1;
+    if (occFused) {
+      const int64_t l[3] = {ox + dst->shift[0], oy + dst->shift[1], oz + dst->shift[2]};
+      if ((l[0] & 31) || (l[1] & 31) || (l[2] & 15)) occFused = false;
+      else j.occBase = (l[0] >> 5) + (int64_t)dst->nc[0] * ((l[1] >> 5) + (int64_t)dst->nc[1] * (l[2] >> 4));
+    }
     { int rc = context_chain_lut(ctx, j.chainDist, &j.chainLut); if (rc != VR_OK) { delete p; return rc; } }
     int chainSum = 0;  // the table packs the net offset in 8 signed bits: 64+32+...+1 = 127 for every reference stream
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) chainSum += s->kd.distanceMap[(size_t)(g.D0 + k)];
@@ -203,6 +214,9 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     p->bytesIndex += (int64_t)(s->imageBytes - s->wordsBytes);
   }
   p->vec16 = vec16;
+  p->occFused = occFused && vec16 && p->geom.fastPath;
+  p->occEpoch = dst->occEpoch;
+  if (!p->occFused) for (auto& j : jobs) j.occBase = -1;
   if (const char* ev = getenv("VR_DECODE_SORT")) {
     if (atoi(ev)) {  // experiment: bricks with the most live tiles first
       std::vector<std::pair<int64_t, int>> key;
@@ -224,7 +238,12 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
 int vr_decode_plan_run(vr_decode_plan* p) {
   if (!p) return fail(VR_ERR_ARG, "null plan");
   CU(cudaSetDevice(p->ctx->device));
-  CU(kd_decode_launch(p->geom, p->jobsDev, p->n, p->dst->dev, p->dst->SX, p->dst->SX * p->dst->SY, p->vec16, p->ctx->stream));
+  vr_volume* d = p->dst;
+  const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
+  CU(kd_decode_launch(p->geom, p->jobsDev, p->n, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
+                      d->nc[0], d->nc[0] * d->nc[1]));
+  if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
+  else d->occValid = false;
   return VR_OK;
 }
 int vr_decode_plan_destroy(vr_decode_plan* p) {

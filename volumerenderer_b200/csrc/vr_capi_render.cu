@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "../../include/vr_b200.h"
+#include "occupancy.h"
 #include "render_march.h"
 #include "vr_internal.h"
 
@@ -36,6 +37,19 @@ int make_render_params(const vr_render_params* in, RenderParams* P) {
   P->W = in->width; P->H = in->height;
   P->mode = in->mode == VR_MODE_COMPOSITE ? 0 : 1;
   return VR_OK;
+}
+// Largest voxel value m whose sample can never reach the mode's threshold (occupancy.h): composite skips
+// exactly-zero cells; isosurface skips cells where even the maximum tap stays below isoValue
+// (smp2 <= m/255 in the kernel's own arithmetic, so `smp2 - iso >= 0` of isosurface.frag:126 cannot hold).
+int skip_threshold(const RenderParams& P) {
+  if (P.mode == 0) return 0;
+  int thr = -1;
+  for (int m = 0; m < 256; ++m) {
+    volatile float s = (float)m * (1.0f / 255.0f);
+    volatile float d = s - P.iso;
+    if (d < 0.0f) thr = m; else break;
+  }
+  return thr;
 }
 }  // namespace vr
 
@@ -73,7 +87,9 @@ int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* par
   if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
   if (vol->SX > 0x7FFFFFFF || vol->SY > 0x7FFFFFFF || vol->SZ > 0x7FFFFFFF) return fail(VR_ERR_UNSUPPORTED, "volume extent too large");
   CU(cudaSetDevice(ctx->device));
-  CU(render_launch(P, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,
+  OccView occ;
+  { int rc = volume_occ_view(ctx, vol, skip_threshold(P), &occ); if (rc != VR_OK) return rc; }
+  CU(render_launch(P, occ, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,
                    reinterpret_cast<unsigned long long*>(samples_dev), ctx->stream));
   return VR_OK;
 }

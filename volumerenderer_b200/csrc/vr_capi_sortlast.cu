@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/vr_b200.h"
+#include "occupancy.h"
 #include "render_march.h"
 #include "vr_internal.h"
 
@@ -22,7 +23,7 @@ struct vr_sortlast {
   int* orderDev = nullptr;  // 8 x n
 };
 
-namespace vr { int make_render_params(const vr_render_params* in, RenderParams* P); }
+namespace vr { int make_render_params(const vr_render_params* in, RenderParams* P); int skip_threshold(const RenderParams& P); }
 
 static int slab_geom(const vr_sortlast* sl, const vr_volume* v, SlabGeom* g) {
   const vr_slab_desc& d = sl->slabs[(size_t)sl->rank];
@@ -125,13 +126,16 @@ int vr_sortlast_halo(const vr_render_params* p, const int64_t global[3], int64_t
   SlabGeom g;                                                                                       \
   std::memset(&g, 0, sizeof(g));                                                                    \
   if (need_slab) { if (!slab) return fail(VR_ERR_ARG, "null slab"); int rc_ = slab_geom(sl, slab, &g); if (rc_ != VR_OK) return rc_; } \
-  CU(cudaSetDevice(ctx->device));
+  CU(cudaSetDevice(ctx->device));                                                                   \
+  OccView occ;                                                                                      \
+  std::memset(&occ, 0, sizeof(occ));                                                                \
+  if (need_slab) { int rc_ = volume_occ_view(ctx, slab, skip_threshold(P), &occ); if (rc_ != VR_OK) return rc_; }
 
 int vr_partial_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
                          float* cseg, float* tseg, uint64_t* samples) {
   if (!cseg || !tseg) return fail(VR_ERR_ARG, "null output");
   SL_PROLOGUE(true)
-  CU(partial_composite_launch(P, g, slab->dev, cseg, tseg, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  CU(partial_composite_launch(P, g, occ, slab->dev, cseg, tseg, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
   return VR_OK;
 }
 
@@ -139,7 +143,7 @@ int vr_partial_iso(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab
                    float* rgba, int32_t* hit, uint64_t* samples) {
   if (!rgba || !hit) return fail(VR_ERR_ARG, "null output");
   SL_PROLOGUE(true)
-  CU(partial_iso_launch(P, g, slab->dev, reinterpret_cast<float4*>(rgba), hit, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  CU(partial_iso_launch(P, g, occ, slab->dev, reinterpret_cast<float4*>(rgba), hit, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
   return VR_OK;
 }
 
@@ -148,7 +152,7 @@ int vr_resolve_composite(vr_context* ctx, const vr_sortlast* sl, const vr_volume
   if (!tseg_all || !cseg || !contrib) return fail(VR_ERR_ARG, "null buffer");
   SL_PROLOGUE(true)
   { int rc_ = order_on_device(ctx, const_cast<vr_sortlast*>(sl)); if (rc_ != VR_OK) return rc_; }
-  CU(resolve_composite_launch(P, g, slab->dev, tseg_all, sl->n, sl->rank, sl->orderDev, cseg, reinterpret_cast<float2*>(contrib),
+  CU(resolve_composite_launch(P, g, occ, slab->dev, tseg_all, sl->n, sl->rank, sl->orderDev, cseg, reinterpret_cast<float2*>(contrib),
                               reinterpret_cast<unsigned long long*>(samples), ctx->stream));
   return VR_OK;
 }
@@ -187,6 +191,7 @@ static int box_copy(vr_context* ctx, const vr_volume* v, const int64_t o[3], con
   p.extent = make_cudaExtent((size_t)e[0], (size_t)e[1], (size_t)e[2]);
   p.kind = cudaMemcpyDeviceToDevice;
   CU(cudaMemcpy3DAsync(&p, ctx->stream));
+  if (!pack) volume_occ_written(ctx, const_cast<vr_volume*>(v), o, e);
   return VR_OK;
 }
 int vr_volume_pack_box(vr_context* ctx, const vr_volume* v, const int64_t origin[3], const int64_t extent[3], uint8_t* dst) {

@@ -33,6 +33,16 @@ struct vr_volume {
   int64_t SX = 0, SY = 0, SZ = 0;
   bool owned = false;
   int device = 0;
+  // occupancy for empty-space skipping (occupancy.h); grids are allocated on first use
+  bool skipping = true;           // vr_volume_set_skipping
+  int64_t cellOrigin[3] = {0, 0, 0};  // global voxel coordinate of voxel (0,0,0): cells align to the global grid
+  int shift[3] = {0, 0, 0};       // cellOrigin mod cell size
+  int nc[3] = {0, 0, 0}, nm[3] = {0, 0, 0};
+  uint8_t *occRaw = nullptr, *occDil = nullptr, *occMacro = nullptr;
+  bool occValid = false;          // occRaw bounds every stored voxel
+  bool occDilDirty = true;        // occDil / occMacro need recomputing from occRaw
+  int occEpoch = 0;               // bumped whenever the grids are freed (plans remember the epoch they were built for)
+  void occ_free();
 };
 
 struct vr_decode_plan {
@@ -42,6 +52,8 @@ struct vr_decode_plan {
   int n = 0;
   vr_volume* dst = nullptr;
   bool vec16 = false;
+  bool occFused = false;  // every tile of every job is one occupancy cell: the kernel keeps occRaw current
+  int occEpoch = 0;
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
 };
 
@@ -50,4 +62,8 @@ int fail(int code, const char* msg);
 int fail_cuda(cudaError_t e, const char* where);
 int stream_build_image(vr_stream* s);  // prepare + pack host image
 int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out);
+struct OccView;
+int volume_occ_alloc(vr_volume* v);                       // allocate the grids for the current cellOrigin
+int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out);  // build / refresh as needed; out->dil = null when off
+void volume_occ_written(vr_context* ctx, vr_volume* v, const int64_t lo[3], const int64_t ext[3]);  // a box of voxels was overwritten
 }

@@ -162,6 +162,27 @@ class Volume:
         check(lib.vr_volume_download(self.ctx.h, self.h, out.ctypes.data))
         return out
 
+    def set_cell_origin(self, origin):
+        """Global voxel coordinate of this slab's voxel (0,0,0): occupancy cells align to the global grid."""
+        check(lib.vr_volume_set_cell_origin(self.h, (c_int64 * 3)(*[int(o) for o in origin])))
+        return self
+
+    def set_skipping(self, enable=True):
+        """Empty-space skipping in the march (default on); frames are identical either way."""
+        check(lib.vr_volume_set_skipping(self.h, 1 if enable else 0))
+        return self
+
+    def invalidate(self):
+        check(lib.vr_volume_invalidate(self.h))
+
+    def occupancy(self, which=0):
+        """Per-cell maxima as numpy (nz, ny, nx): 0 raw (cells of 32x32x16), 1 dilated, 2 macro."""
+        dims = (ctypes.c_int32 * 3)()
+        check(lib.vr_volume_occupancy_download(self.ctx.h, self.h, int(which), None, 0, dims))
+        out = np.empty((dims[2], dims[1], dims[0]), np.uint8)
+        check(lib.vr_volume_occupancy_download(self.ctx.h, self.h, int(which), out.ctypes.data, out.size, dims))
+        return out
+
     def upload_brick(self, brick, origin):
         a = np.ascontiguousarray(brick, dtype=np.uint8)
         BZ, BY, BX = a.shape
