@@ -108,7 +108,7 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 
 /* ---- empty-space skipping (north_star; no usable bound structure exists in the reference) --
  * Every volume carries a grid of exact per-cell maxima (cells of 32x32x16 voxels aligned to the global
- * voxel grid, plus a dilated copy and a 256x256x128 macro level).  The decode kernel maintains it for the
+ * voxel grid, plus a dilated copy and an octree of maxima above it).  The decode kernel maintains it for the
  * bricks it writes; raw uploads are reduced lazily at the next render.  The march skips the fetch where
  * the bound proves the sample is exactly 0 (composite: contributes nothing, raycaster.frag:69-72) or
  * below the iso value (isosurface.frag:126 cannot fire); sample positions are still produced by the
@@ -116,7 +116,8 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 int vr_volume_set_cell_origin(vr_volume* v, const int64_t origin[3]); /* global coordinate of voxel (0,0,0); default 0 */
 int vr_volume_set_skipping(vr_volume* v, int enable);                 /* default on */
 int vr_volume_invalidate(vr_volume* v); /* the caller wrote voxels behind the library's back (wrapped memory) */
-/* which: 0 raw maxima, 1 dilated, 2 macro; out_host may be NULL to query dims only */
+/* which: 0 raw cell maxima, 1 + l = level l of the octree of dilated maxima (VR_ERR_ARG past the root);
+ * out_host may be NULL to query dims only */
 int vr_volume_occupancy_download(vr_context* ctx, const vr_volume* v, int32_t which, uint8_t* out_host, int64_t cap, int32_t dims[3]);
 
 /* ---- stage 1: decode = VolumeKdtree::levelCut (VolumeKdTree_recover.cpp:726-835) --------------- */

@@ -1,4 +1,4 @@
-"""GPU (-m gpu): empty-space skipping.  (1) the occupancy grids (exact per-cell maxima, dilated, macro) equal
+"""GPU (-m gpu): empty-space skipping.  (1) the occupancy grids (exact per-cell maxima, dilated, octree of maxima) equal
 a numpy reduction of the same voxels, whether produced by the lazy reduction kernel (raw uploads, odd
 extents, shifted cell origin) or by the decode kernel itself (fused, 256x256x128 bricks); (2) frames and
 sample counts are bit-identical with skipping on and off, and match the scalar oracle."""
@@ -21,7 +21,7 @@ def ctx():
 
 
 def np_grids(a, origin=(0, 0, 0)):
-    """raw / dilated / macro maxima of a (Z, Y, X) array with cells aligned to the global grid."""
+    """raw / dilated / octree maxima of a (Z, Y, X) array with cells aligned to the global grid."""
     Z, Y, X = a.shape
     sh = [origin[i] % CS[i] for i in range(3)]
     n = [(s + h - 1) // c + 1 for s, h, c in zip((X, Y, Z), sh, CS)]
@@ -39,13 +39,18 @@ def np_grids(a, origin=(0, 0, 0)):
         for dy in range(2):
             for dx in range(2):
                 dil = np.maximum(dil, pad[dz:dz + n[2], dy:dy + n[1], dx:dx + n[0]])
-    m = [(c - 1) // 8 + 1 for c in n]
-    macro = np.zeros((m[2], m[1], m[0]), np.uint8)
-    for z in range(m[2]):
-        for y in range(m[1]):
-            for x in range(m[0]):
-                macro[z, y, x] = dil[8 * z:8 * z + 8, 8 * y:8 * y + 8, 8 * x:8 * x + 8].max()
-    return raw, dil, macro
+    out = [raw, dil]  # which = 0 raw, 1 = level 0 (dilated), 2.. = octree of maxima above it
+    cur = dil
+    while cur.size > 1:
+        m = [(c - 1) // 2 + 1 for c in cur.shape]
+        nxt = np.zeros(m, np.uint8)
+        for z in range(m[0]):
+            for y in range(m[1]):
+                for x in range(m[2]):
+                    nxt[z, y, x] = cur[2 * z:2 * z + 2, 2 * y:2 * y + 2, 2 * x:2 * x + 2].max()
+        out.append(nxt)
+        cur = nxt
+    return out
 
 
 @pytest.mark.parametrize("shape,origin", [((256, 96, 128), (0, 0, 0)), ((70, 50, 100), (0, 0, 0)), ((96, 66, 128), (0, 31, 0)),

@@ -28,18 +28,17 @@ struct DecodeParams {
   int order;  // 1 = brick-major (default; measured 0.44 ms vs 0.60 ms tile-major on the rm_yslab batch), 0 = tile-major
   int variant;  // parser variant of the fast path: 0 = v3 (chain length from the table), 1 = v3 (length by ALU), 2 = v2
   // occupancy (occupancy.h): when a decode tile is exactly one cell the kernel stores the tile's maximum
-  uint8_t* occ;  // null = off
-  int occNX, occNXY;
+  // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
+  uint8_t* occ;             // null = off
+  const int32_t* tileCell;  // [2^Dt] cell of the tile relative to the cell of the brick's (0,0,0)
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
 __device__ __forceinline__ int64_t tile_cell(const DecodeParams& p, const vr_kd_job& job, uint32_t tile) {
-  int ox, oy, oz;
-  vr_tile_origin(p.g, tile, &ox, &oy, &oz);
-  return job.occBase + (ox >> 5) + (int64_t)(oy >> 5) * p.occNX + (int64_t)(oz >> 4) * p.occNXY;
+  return job.occBase + __ldg(p.tileCell + tile);
 }
 
-__global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
+__global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
   extern __shared__ __align__(16) uint8_t strips[];
   __shared__ int64_t sTileBase;
   const vr_kd_geom& g = p.g;
@@ -55,7 +54,10 @@ __global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_const
   const uint32_t items = vr_tile_items(g);
   if (blk == VR_PRUNED) {  // constant tile: pure fill
     const int val = job.tileVal[tile];
-    if (p.occ && job.occBase >= 0 && threadIdx.x == 0) p.occ[tile_cell(p, job, tile)] = (uint8_t)val;
+    if (p.occ && job.occBase >= 0 && threadIdx.x == 0) {
+      const uint32_t w = (uint32_t)val * 0x01010101u;
+      *reinterpret_cast<uint2*>(p.occ + tile_cell(p, job, tile) * 8) = make_uint2(w, w);
+    }
     __syncthreads();
     uint8_t* dst = p.dst + sTileBase;
     for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
@@ -80,16 +82,10 @@ __global__ void __launch_bounds__(256) kd_decode_tiles_kernel(const __grid_const
     const uint32_t perUnit = 1u << g.fbUnit;
     uint32_t m4 = 0;
     for (uint32_t q = lane; q < perUnit; q += 32) m4 = __vmaxu4(m4, vr_unit_phase2_item(g, warp, q, strips, dstw, p.rowPitch, p.slicePitch));
-    if (p.occ && job.occBase >= 0) {  // tile maximum -> occupancy cell (trailing barrier: every warp is done storing)
-      __shared__ uint32_t sMax[8];
+    if (p.occ && job.occBase >= 0) {  // this warp's maximum -> its slot of the tile's occupancy cell
       uint32_t m = max(max(m4 & 0xFF, (m4 >> 8) & 0xFF), max((m4 >> 16) & 0xFF, m4 >> 24));
       m = __reduce_max_sync(0xFFFFFFFFu, m);
-      if (lane == 0) sMax[warp] = m;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        for (int w = 1; w < 8; ++w) m = max(m, sMax[w]);
-        p.occ[tile_cell(p, job, tile)] = (uint8_t)m;
-      }
+      if (lane == 0) p.occ[tile_cell(p, job, tile) * 8 + warp] = (uint8_t)m;
     }
     return;
   }
@@ -107,8 +103,8 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
 }
 
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int nBricks, uint8_t* dst,
-                             int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ, int occNX,
-                             int occNXY) {
+                             int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
+                             const int32_t* tileCell) {
   if (nBricks <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -118,7 +114,7 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int 
   p.slicePitch = slicePitch;
   p.vec16 = vec16 ? 1 : 0;
   p.nBricks = nBricks;
-  p.occ = occ; p.occNX = occNX; p.occNXY = occNXY;
+  p.occ = tileCell ? occ : nullptr; p.tileCell = tileCell;
   {
     static int variant = -1;
     if (variant < 0) { const char* e = getenv("VR_DECODE_VARIANT"); variant = e ? atoi(e) : 0; }

@@ -40,43 +40,100 @@ __global__ void __launch_bounds__(256) occ_reduce_box_kernel(const uint8_t* __re
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int w = 1; w < 8; ++w) m = max(m, sm[w]);
-    raw[((long long)cz * ny + cy) * nx + cx] = (uint8_t)m;
+    const unsigned w = m * 0x01010101u;  // all writer slots
+    *reinterpret_cast<uint2*>(raw + (((long long)cz * ny + cy) * nx + cx) * VR_OCC_SLOTS) = make_uint2(w, w);
   }
 }
 
-__global__ void occ_dilate_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ dil, int nx, int ny, int nz) {
-  const long long n = (long long)nx * ny * nz;
+__device__ __forceinline__ unsigned raw_max(const uint8_t* __restrict__ raw, long long cell) {
+  const uint2 w = __ldg(reinterpret_cast<const uint2*>(raw + cell * VR_OCC_SLOTS));
+  const unsigned m = __vmaxu4(w.x, w.y);
+  return max(max(m & 0xFF, (m >> 8) & 0xFF), max((m >> 16) & 0xFF, m >> 24));
+}
+
+// One CTA per level-3 cell = 8x8x8 level-0 cells: dilate raw into level 0, then reduce to levels 1..3.
+__global__ void __launch_bounds__(512) occ_pyr_low_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ pyr,
+                                                          const __grid_constant__ OccView L) {
+  __shared__ uint8_t s0[512], s1[64], s2[8];
+  const int t = threadIdx.x;
+  const int cx = (blockIdx.x << 3) + (t & 7), cy = (blockIdx.y << 3) + ((t >> 3) & 7), cz = (blockIdx.z << 3) + (t >> 6);
+  unsigned m = 0;
+  if (cx < L.nx && cy < L.ny && cz < L.nz) {
+    for (int dz = 0; dz < 2; ++dz)
+      for (int dy = 0; dy < 2; ++dy)
+        for (int dx = 0; dx < 2; ++dx) {
+          const int x = min(cx + dx, L.nx - 1), y = min(cy + dy, L.ny - 1), z = min(cz + dz, L.nz - 1);
+          m = max(m, raw_max(raw, ((long long)z * L.ny + y) * L.nx + x));
+        }
+    pyr[L.off[0] + ((long long)cz * L.ny + cy) * L.nx + cx] = (uint8_t)m;
+  }
+  s0[t] = (uint8_t)m;
+  __syncthreads();
+  for (int l = 1; l <= 3; ++l) {
+    if (l >= L.nlev) break;
+    const int w = 8 >> l, cells = w * w * w;  // cells of level l inside this CTA's region
+    uint8_t* dst = l == 1 ? s1 : s2;
+    const uint8_t* src = l == 1 ? s0 : (l == 2 ? s1 : s2);
+    unsigned mm = 0;
+    int x = 0, y = 0, z = 0;
+    if (t < cells) {
+      x = t % w; y = (t / w) % w; z = t / (w * w);
+      const int ws = w * 2;
+      for (int c = 0; c < 8; ++c) mm = max(mm, (unsigned)src[((2 * z + (c >> 2)) * ws + (2 * y + ((c >> 1) & 1))) * ws + 2 * x + (c & 1)]);
+    }
+    __syncthreads();  // src fully read before a level that aliases it is written (s2 serves levels 2 and 3)
+    if (t < cells) {
+      if (l < 3) dst[t] = (uint8_t)mm;
+      const int nxl = ((L.nx - 1) >> l) + 1, nyl = ((L.ny - 1) >> l) + 1, nzl = ((L.nz - 1) >> l) + 1;
+      const int gx = (blockIdx.x << (3 - l)) + x, gy = (blockIdx.y << (3 - l)) + y, gz = (blockIdx.z << (3 - l)) + z;
+      if (gx < nxl && gy < nyl && gz < nzl) pyr[L.off[l] + ((long long)gz * nyl + gy) * nxl + gx] = (uint8_t)mm;
+    }
+    __syncthreads();
+  }
+}
+
+// One CTA: levels 4.. from level 3, one level after the other.
+__global__ void __launch_bounds__(256) occ_pyr_high_kernel(uint8_t* __restrict__ pyr, const __grid_constant__ OccView L) {
+  for (int l = 4; l < L.nlev; ++l) {
+    const int nxl = ((L.nx - 1) >> l) + 1, nyl = ((L.ny - 1) >> l) + 1, nzl = ((L.nz - 1) >> l) + 1;
+    const int nxp = ((L.nx - 1) >> (l - 1)) + 1, nyp = ((L.ny - 1) >> (l - 1)) + 1, nzp = ((L.nz - 1) >> (l - 1)) + 1;
+    for (int i = threadIdx.x; i < nxl * nyl * nzl; i += blockDim.x) {
+      const int x = i % nxl, y = (i / nxl) % nyl, z = i / (nxl * nyl);
+      unsigned m = 0;
+      for (int c = 0; c < 8; ++c) {
+        const int px = 2 * x + (c & 1), py = 2 * y + ((c >> 1) & 1), pz = 2 * z + (c >> 2);
+        if (px < nxp && py < nyp && pz < nzp) m = max(m, (unsigned)pyr[L.off[l - 1] + ((long long)pz * nyp + py) * nxp + px]);
+      }
+      pyr[L.off[l] + i] = (uint8_t)m;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void occ_levels_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ lvl, const __grid_constant__ OccView L) {
+  const long long n = (long long)L.nx * L.ny * L.nz;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const int cx = (int)(i % nx), cy = (int)((i / nx) % ny), cz = (int)(i / ((long long)nx * ny));
-  unsigned m = 0;
-  for (int dz = 0; dz < 2; ++dz)
-    for (int dy = 0; dy < 2; ++dy)
-      for (int dx = 0; dx < 2; ++dx) {
-        const int x = min(cx + dx, nx - 1), y = min(cy + dy, ny - 1), z = min(cz + dz, nz - 1);
-        m = max(m, (unsigned)__ldg(raw + ((long long)z * ny + y) * nx + x));
-      }
-  dil[i] = (uint8_t)m;
-}
-
-// one warp per macro cell
-__global__ void occ_macro_kernel(const uint8_t* __restrict__ dil, uint8_t* __restrict__ macro, int nx, int ny, int nz, int mx, int my,
-                                 int mz) {
-  const int warp = (int)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-  if (warp >= mx * my * mz) return;
-  const int bx = warp % mx, by = (warp / mx) % my, bz = warp / (mx * my);
-  const int W = 1 << VR_OCC_MACRO;
-  unsigned m = 0;
-  for (int it = lane; it < W * W * W; it += 32) {
-    const int x = (bx << VR_OCC_MACRO) + (it & (W - 1)), y = (by << VR_OCC_MACRO) + ((it >> VR_OCC_MACRO) & (W - 1)),
-              z = (bz << VR_OCC_MACRO) + (it >> (2 * VR_OCC_MACRO));
-    if (x < nx && y < ny && z < nz) m = max(m, (unsigned)__ldg(dil + ((long long)z * ny + y) * nx + x));
+  const int cx = (int)(i % L.nx), cy = (int)((i / L.nx) % L.ny), cz = (int)(i / ((long long)L.nx * L.ny));
+  int out = VR_OCC_SOLID;
+  if ((int)pyr[L.off[0] + i] <= L.thr) {
+    out = 0;
+    for (int s = 1; s < L.nlev; ++s) {
+      const int nxl = ((L.nx - 1) >> s) + 1, nyl = ((L.ny - 1) >> s) + 1;
+      if ((int)pyr[L.off[s] + ((long long)(cz >> s) * nyl + (cy >> s)) * nxl + (cx >> s)] > L.thr) break;
+      out = s;
+    }
   }
-  m = __reduce_max_sync(0xFFFFFFFFu, m);
-  if (lane == 0) macro[warp] = (uint8_t)m;
+  lvl[i] = (uint8_t)out;
 }
 
 }  // namespace
+
+cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& L, cudaStream_t stream) {
+  const long long n = (long long)L.nx * L.ny * L.nz;
+  occ_levels_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(pyr, lvl, L);
+  return cudaGetLastError();
+}
 
 cudaError_t occ_reduce_box_launch(const uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, const int64_t lo[3], const int64_t ext[3],
                                   uint8_t* raw, int nx, int ny, int nz, const int shift[3], cudaStream_t stream) {
@@ -91,12 +148,10 @@ cudaError_t occ_reduce_box_launch(const uint8_t* vol, int64_t SX, int64_t SY, in
   return cudaGetLastError();
 }
 
-cudaError_t occ_dilate_launch(const uint8_t* raw, uint8_t* dil, uint8_t* macro, int nx, int ny, int nz, int mx, int my, int mz,
-                              cudaStream_t stream) {
-  const long long n = (long long)nx * ny * nz;
-  occ_dilate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(raw, dil, nx, ny, nz);
-  const long long threads = (long long)mx * my * mz * 32;
-  occ_macro_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(dil, macro, nx, ny, nz, mx, my, mz);
+cudaError_t occ_pyramid_launch(const uint8_t* raw, uint8_t* pyr, const OccView& L, cudaStream_t stream) {
+  dim3 grid((unsigned)(((L.nx - 1) >> 3) + 1), (unsigned)(((L.ny - 1) >> 3) + 1), (unsigned)(((L.nz - 1) >> 3) + 1));
+  occ_pyr_low_kernel<<<grid, 512, 0, stream>>>(raw, pyr, L);
+  if (L.nlev > 4) occ_pyr_high_kernel<<<1, 256, 0, stream>>>(pyr, L);
   return cudaGetLastError();
 }
 

@@ -139,37 +139,40 @@ __device__ __forceinline__ bool ray_setup(const RenderParams& P, int px, int py,
 // ---- empty-space skipping (occupancy.h) -------------------------------------------------------------
 // q = position whose 8 taps decide the sample (composite: the sample itself; isosurface: the look-ahead
 // p + dirStep).  Returns -1 when the cell's bound does not prove the sample void; otherwise the number
-// k >= 0 of FURTHER lattice steps q + j*d (j = 1..k) that provably stay inside the same void macro cell
-// (and inside the texture), capped by `budget`.  The estimate uses real-number geometry with a margin far
-// above the accumulated rounding of the lattice (300 additions of magnitude <= 1: < 2e-5).
+// k >= 0 of FURTHER lattice steps q + j*d (j = 1..k) that provably stay inside the largest void octree
+// cell around q (and inside the texture), capped by `budget`.  inv = 1/d per axis.  The estimate uses
+// real-number geometry with a margin far above the accumulated rounding of the lattice (300 additions of
+// magnitude <= 1: < 2e-5); the positions themselves are still produced by the caller's repeated additions.
 template <bool SLAB>
-__device__ __forceinline__ int occ_skip(const OccView& o, const Vol& v, V3 q, V3 d, int budget) {
+__device__ __forceinline__ int occ_skip(const OccView& o, const Vol& v, V3 q, V3 d, V3 inv, int budget) {
   int bx = clampi((int)floorf(fsub(fmul(q.x, v.fX), 0.5f)), 0, v.GX - 1);
   int by = clampi((int)floorf(fsub(fmul(q.y, v.fY), 0.5f)), 0, v.GY - 1);
   int bz = clampi((int)floorf(fsub(fmul(q.z, v.fZ), 0.5f)), 0, v.GZ - 1);
   if (SLAB) { bx = clampi(bx - v.ox, 0, v.SX - 1); by = clampi(by - v.oy, 0, v.SY - 1); bz = clampi(bz - v.oz, 0, v.SZ - 1); }
   const int cx = (bx + o.sx) >> VR_OCC_LX, cy = (by + o.sy) >> VR_OCC_LY, cz = (bz + o.sz) >> VR_OCC_LZ;
-  if ((int)__ldg(o.dil + ((long long)cz * o.ny + cy) * o.nx + cx) > o.thr) return -1;
-  const int mx = cx >> VR_OCC_MACRO, my = cy >> VR_OCC_MACRO, mz = cz >> VR_OCC_MACRO;
-  if ((int)__ldg(o.macro + ((long long)mz * o.my + my) * o.mx + mx) > o.thr) return 0;
-  // macro cell as a box of base texels in global voxel coordinates, clipped to the stored box
+  const int l = (int)__ldg(o.lvl + (cz * o.ny + cy) * o.nx + cx);  // highest void octree level around the cell
+  if (l == VR_OCC_SOLID) return -1;
+  if (l < 2) return 0;  // a cell or two: about one step, not worth the geometry
+  // the level-l cell as a box of base texels in global voxel coordinates, clipped to the stored box
   const float kMargin = 1.0e-4f;
   float t = 1.0e9f;
-  const int ml[3] = {mx, my, mz}, sh[3] = {o.sx, o.sy, o.sz}, lg[3] = {VR_OCC_LX + VR_OCC_MACRO, VR_OCC_LY + VR_OCC_MACRO, VR_OCC_LZ + VR_OCC_MACRO};
+  const int cl[3] = {cx >> l, cy >> l, cz >> l}, sh[3] = {o.sx, o.sy, o.sz}, lg[3] = {VR_OCC_LX + l, VR_OCC_LY + l, VR_OCC_LZ + l};
   const int S[3] = {v.SX, v.SY, v.SZ}, org[3] = {SLAB ? v.ox : 0, SLAB ? v.oy : 0, SLAB ? v.oz : 0}, G[3] = {v.GX, v.GY, v.GZ};
-  const float qq[3] = {q.x, q.y, q.z}, dd[3] = {d.x, d.y, d.z}, fG[3] = {v.fX, v.fY, v.fZ};
+  const float qq[3] = {q.x, q.y, q.z}, dd[3] = {d.x, d.y, d.z}, ii[3] = {inv.x, inv.y, inv.z}, rG[3] = {1.0f / v.fX, 1.0f / v.fY, 1.0f / v.fZ};
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
-    const int lo = max((ml[a] << lg[a]) - sh[a], 0) + org[a], hi = min(((ml[a] + 1) << lg[a]) - sh[a], S[a]) + org[a];
-    const float plo = lo == 0 ? 0.0f : ((float)lo + 0.5f) / fG[a];
-    const float phi = hi >= G[a] ? 1.0f : ((float)hi + 0.5f) / fG[a];
-    if (dd[a] > 0.0f) t = fminf(t, (phi - kMargin - qq[a]) / dd[a]);
-    else if (dd[a] < 0.0f) t = fminf(t, (plo + kMargin - qq[a]) / dd[a]);
+    const int lo = max((cl[a] << lg[a]) - sh[a], 0) + org[a];
+    const int hi = (int)min((long long)((cl[a] + 1ll) << lg[a]) - sh[a], (long long)S[a]) + org[a];
+    const float plo = lo == 0 ? 0.0f : ((float)lo + 0.5f) * rG[a];
+    const float phi = hi >= G[a] ? 1.0f : ((float)hi + 0.5f) * rG[a];
+    if (dd[a] > 0.0f) t = fminf(t, (phi - kMargin - qq[a]) * ii[a]);
+    else if (dd[a] < 0.0f) t = fminf(t, (plo + kMargin - qq[a]) * ii[a]);
     else if (!(qq[a] > plo + kMargin && qq[a] < phi - kMargin)) t = 0.0f;
   }
   const int k = (int)floorf(t) - 1;
   return min(max(k, 0), budget);
 }
+__device__ __forceinline__ V3 recip(V3 d) { return {1.0f / d.x, 1.0f / d.y, 1.0f / d.z}; }
 
 // dir and dirStep of the fragment (raycaster.frag:27,31 / isosurface.frag:88,92)
 __device__ __forceinline__ void ray_dir(const RenderParams& P, V3 vUV, V3* dir, V3* dirStep) {

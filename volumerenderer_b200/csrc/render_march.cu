@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
     if (ray_setup(P, px, py, &vUV)) {
       V3 dir, dirStep;
       ray_dir(P, vUV, &dir, &dirStep);
+      const V3 inv = recip(dirStep);
       V3 p = vUV;
       if (MODE == 0) {
         float C = 0.0f, A = 0.0f;
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
           p = add(p, dirStep);
           if (!inside(p)) break;
           if (OCC) {  // void cell: the sample is exactly 0 and leaves (C, A) unchanged
-            const int k = occ_skip<false>(occ, v, p, dirStep, 299 - i);
+            const int k = occ_skip<false>(occ, v, p, dirStep, inv, 299 - i);
             if (k >= 0) {
               for (int j = 0; j < k; ++j) p = add(p, dirStep);
               i += k; n += 1 + k;
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
           if (!inside(p)) break;
           const V3 pn = add(p, dirStep);
           if (OCC) {  // every tap of the look-ahead sample is below the iso value: no crossing can be detected here
-            const int k = occ_skip<false>(occ, v, pn, dirStep, 299 - i);
+            const int k = occ_skip<false>(occ, v, pn, dirStep, inv, 299 - i);
             if (k >= 0) {
               for (int j = 0; j < k; ++j) p = add(p, dirStep);
               i += k; n += 1 + k;
@@ -98,10 +99,10 @@ cudaError_t render_launch(const RenderParams& P, const OccView& occ, const uint8
                           int* hitIndex, unsigned long long* sampleCount, cudaStream_t stream) {
   dim3 grid((P.W + 31) / 32, (P.H + 7) / 8), block(256);
   if (P.mode == 0) {
-    if (occ.dil) march_kernel<0, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+    if (occ.pyr) march_kernel<0, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
     else march_kernel<0, false><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
   } else {
-    if (occ.dil) march_kernel<1, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
+    if (occ.pyr) march_kernel<1, true><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
     else march_kernel<1, false><<<grid, block, 0, stream>>>(P, occ, vol, X, Y, Z, out, hitIndex, sampleCount);
   }
   return cudaGetLastError();

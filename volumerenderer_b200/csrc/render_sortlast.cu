@@ -41,6 +41,7 @@ __device__ __forceinline__ void count_samples(unsigned long long* sampleCount, u
 template <bool OCC>
 __device__ __forceinline__ void march_segment(const Vol& v, const OccView& occ, V3 p, V3 dirStep, float* C, float* A, unsigned* n) {
   float c = *C, a = *A;
+  const V3 inv = recip(dirStep);
   bool started = false;
   for (int i = 0; i < 300; ++i) {
     p = add(p, dirStep);
@@ -51,7 +52,7 @@ __device__ __forceinline__ void march_segment(const Vol& v, const OccView& occ, 
     }
     started = true;
     if (OCC) {  // void cell: exactly-zero samples change nothing (skipped positions need no ownership test either)
-      const int k = occ_skip<true>(occ, v, p, dirStep, 299 - i);
+      const int k = occ_skip<true>(occ, v, p, dirStep, inv, 299 - i);
       if (k >= 0) {
         for (int j = 0; j < k; ++j) p = add(p, dirStep);
         i += k; *n += 1 + k;
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
       Vol v = make_vol(g, vol);
       V3 dir, dirStep;
       ray_dir(P, vUV, &dir, &dirStep);
+      const V3 inv = recip(dirStep);
       V3 p = vUV;
       bool started = false;
       for (int i = 0; i < 300; ++i) {
@@ -120,7 +122,7 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
         started = true;
         const V3 pn = add(p, dirStep);
         if (OCC) {
-          const int k = occ_skip<true>(occ, v, pn, dirStep, 299 - i);
+          const int k = occ_skip<true>(occ, v, pn, dirStep, inv, 299 - i);
           if (k >= 0) {
             for (int j = 0; j < k; ++j) p = add(p, dirStep);
             i += k; n += 1 + k;
@@ -227,20 +229,20 @@ dim3 pixel_grid(const RenderParams& P) { return dim3((P.W + 31) / 32, (P.H + 7) 
 
 cudaError_t partial_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float* cseg,
                                      float* tseg, unsigned long long* sampleCount, cudaStream_t stream) {
-  if (occ.dil) partial_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, tseg, sampleCount);
+  if (occ.pyr) partial_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, tseg, sampleCount);
   else partial_composite_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, tseg, sampleCount);
   return cudaGetLastError();
 }
 cudaError_t partial_iso_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float4* rgba, int* hit,
                                unsigned long long* sampleCount, cudaStream_t stream) {
-  if (occ.dil) partial_iso_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, rgba, hit, sampleCount);
+  if (occ.pyr) partial_iso_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, rgba, hit, sampleCount);
   else partial_iso_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, rgba, hit, sampleCount);
   return cudaGetLastError();
 }
 cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
                                      const float* tsegAll, int n, int rank, const int* order, const float* cseg, float2* contrib,
                                      unsigned long long* sampleCount, cudaStream_t stream) {
-  if (occ.dil) resolve_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
+  if (occ.pyr) resolve_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
   else resolve_composite_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
   return cudaGetLastError();
 }

@@ -227,11 +227,22 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
       jobs.swap(sorted);
     }
   }
+  if (p->occFused) {
+    std::vector<int32_t> tc(size_t(1) << g.Dt);
+    for (uint32_t t = 0; t < tc.size(); ++t) {
+      int ox, oy, oz;
+      vr_tile_origin(g, t, &ox, &oy, &oz);
+      tc[t] = (ox >> 5) + dst->nc[0] * ((oy >> 5) + dst->nc[1] * (oz >> 4));
+    }
+    cudaError_t et = cudaMalloc((void**)&p->tileCellDev, tc.size() * 4);
+    if (et == cudaSuccess) et = cudaMemcpy(p->tileCellDev, tc.data(), tc.size() * 4, cudaMemcpyHostToDevice);
+    if (et != cudaSuccess) { cudaFree(p->tileCellDev); delete p; return fail_cuda(et, "upload tile cells"); }
+  }
   cudaError_t e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
-  if (e != cudaSuccess) { delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
+  if (e != cudaSuccess) { cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
   e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // jobs is a stack-lifetime buffer
-  if (e != cudaSuccess) { cudaFree(p->jobsDev); delete p; return fail_cuda(e, "upload jobs"); }
+  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
   *out = p;
   return VR_OK;
 }
@@ -241,7 +252,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
   CU(kd_decode_launch(p->geom, p->jobsDev, p->n, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
-                      d->nc[0], d->nc[0] * d->nc[1]));
+                      occ ? p->tileCellDev : nullptr));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   return VR_OK;
@@ -250,6 +261,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   if (!p) return VR_OK;
   cudaSetDevice(p->ctx->device);
   cudaFree(p->jobsDev);
+  cudaFree(p->tileCellDev);
   delete p;
   return VR_OK;
 }

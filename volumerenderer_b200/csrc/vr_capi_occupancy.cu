@@ -15,9 +15,9 @@ using namespace vr;
 static const int kLg[3] = {VR_OCC_LX, VR_OCC_LY, VR_OCC_LZ};
 
 void vr_volume::occ_free() {
-  if (occRaw || occDil || occMacro) cudaSetDevice(device);
-  cudaFree(occRaw); cudaFree(occDil); cudaFree(occMacro);
-  occRaw = occDil = occMacro = nullptr;
+  if (occRaw || occPyr || occLvl) cudaSetDevice(device);
+  cudaFree(occRaw); cudaFree(occPyr); cudaFree(occLvl);
+  occRaw = occPyr = occLvl = nullptr; occLvlThr = -2;
   occValid = false; occDilDirty = true; ++occEpoch;
 }
 
@@ -29,13 +29,22 @@ int volume_occ_alloc(vr_volume* v) {
   for (int a = 0; a < 3; ++a) {
     v->shift[a] = (int)(v->cellOrigin[a] & ((1 << kLg[a]) - 1));
     v->nc[a] = (int)((S[a] + v->shift[a] - 1) >> kLg[a]) + 1;
-    v->nm[a] = ((v->nc[a] - 1) >> VR_OCC_MACRO) + 1;
   }
-  const size_t n = (size_t)v->nc[0] * v->nc[1] * v->nc[2], m = (size_t)v->nm[0] * v->nm[1] * v->nm[2];
+  const size_t n = (size_t)v->nc[0] * v->nc[1] * v->nc[2];
+  size_t total = 0;
+  v->occLevels = 0;
+  for (int l = 0; l < VR_OCC_MAX_LEVELS; ++l) {
+    const size_t nl = (size_t)(((v->nc[0] - 1) >> l) + 1) * (((v->nc[1] - 1) >> l) + 1) * (((v->nc[2] - 1) >> l) + 1);
+    if (total + nl > 0x7FFFFFFF) break;
+    v->occOff[l] = (int)total;
+    total += (nl + 15) & ~size_t(15);
+    v->occLevels = l + 1;
+    if (nl == 1) break;
+  }
   CU(cudaSetDevice(v->device));
-  CU(cudaMalloc((void**)&v->occRaw, n));
-  CU(cudaMalloc((void**)&v->occDil, n));
-  CU(cudaMalloc((void**)&v->occMacro, m));
+  CU(cudaMalloc((void**)&v->occRaw, n * VR_OCC_SLOTS));
+  CU(cudaMalloc((void**)&v->occPyr, total));
+  CU(cudaMalloc((void**)&v->occLvl, n));
   v->occValid = false; v->occDilDirty = true;
   return VR_OK;
 }
@@ -52,15 +61,22 @@ int volume_occ_view(vr_context* ctx, const vr_volume* cv, int thr, OccView* out)
     CU(occ_reduce_box_launch(v->dev, v->SX, v->SY, v->SZ, lo, ext, v->occRaw, v->nc[0], v->nc[1], v->nc[2], v->shift, ctx->stream));
     v->occValid = true; v->occDilDirty = true;
   }
-  if (v->occDilDirty) {
-    CU(occ_dilate_launch(v->occRaw, v->occDil, v->occMacro, v->nc[0], v->nc[1], v->nc[2], v->nm[0], v->nm[1], v->nm[2], ctx->stream));
-    v->occDilDirty = false;
-  }
-  out->dil = v->occDil; out->macro = v->occMacro;
+  out->nlev = v->occLevels;
+  for (int l = 0; l < v->occLevels; ++l) out->off[l] = v->occOff[l];
   out->nx = v->nc[0]; out->ny = v->nc[1]; out->nz = v->nc[2];
-  out->mx = v->nm[0]; out->my = v->nm[1]; out->mz = v->nm[2];
   out->sx = v->shift[0]; out->sy = v->shift[1]; out->sz = v->shift[2];
   out->thr = thr;
+  if (v->occDilDirty) {
+    CU(occ_pyramid_launch(v->occRaw, v->occPyr, *out, ctx->stream));
+    v->occDilDirty = false;
+    v->occLvlThr = -2;
+  }
+  if (v->occLvlThr != thr) {
+    CU(occ_levels_launch(v->occPyr, v->occLvl, *out, ctx->stream));
+    v->occLvlThr = thr;
+  }
+  out->pyr = v->occPyr;
+  out->lvl = v->occLvl;
   return VR_OK;
 }
 
@@ -114,14 +130,25 @@ int vr_volume_occupancy_download(vr_context* ctx, const vr_volume* v, int32_t wh
   OccView ov;
   int rc = volume_occ_view(ctx, v, 0, &ov);
   if (rc != VR_OK) return rc;
-  if (!ov.dil) return fail(VR_ERR_STATE, "skipping is disabled for this volume");
-  const bool macro = which == 2;
-  dims[0] = macro ? ov.mx : ov.nx; dims[1] = macro ? ov.my : ov.ny; dims[2] = macro ? ov.mz : ov.nz;
+  if (!ov.pyr) return fail(VR_ERR_STATE, "skipping is disabled for this volume");
+  if (which < 0 || which > ov.nlev) return fail(VR_ERR_ARG, "no such level");
+  const int l = which == 0 ? 0 : which - 1;
+  dims[0] = ((ov.nx - 1) >> l) + 1; dims[1] = ((ov.ny - 1) >> l) + 1; dims[2] = ((ov.nz - 1) >> l) + 1;
   const int64_t n = (int64_t)dims[0] * dims[1] * dims[2];
   if (!out_host) return VR_OK;
   if (cap < n) return fail(VR_ERR_ARG, "buffer too small");
-  const uint8_t* src = which == 0 ? v->occRaw : (which == 1 ? v->occDil : v->occMacro);
-  CU(cudaMemcpyAsync(out_host, src, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (which == 0) {  // raw: max over the writer slots
+    std::vector<uint8_t> slots((size_t)n * VR_OCC_SLOTS);
+    CU(cudaMemcpyAsync(slots.data(), v->occRaw, slots.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int64_t i = 0; i < n; ++i) {
+      uint8_t m = 0;
+      for (int k = 0; k < VR_OCC_SLOTS; ++k) m = slots[(size_t)i * VR_OCC_SLOTS + k] > m ? slots[(size_t)i * VR_OCC_SLOTS + k] : m;
+      out_host[i] = m;
+    }
+    return VR_OK;
+  }
+  CU(cudaMemcpyAsync(out_host, v->occPyr + ov.off[l], (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return VR_OK;
 }

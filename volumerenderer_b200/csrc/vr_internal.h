@@ -37,10 +37,14 @@ struct vr_volume {
   bool skipping = true;           // vr_volume_set_skipping
   int64_t cellOrigin[3] = {0, 0, 0};  // global voxel coordinate of voxel (0,0,0): cells align to the global grid
   int shift[3] = {0, 0, 0};       // cellOrigin mod cell size
-  int nc[3] = {0, 0, 0}, nm[3] = {0, 0, 0};
-  uint8_t *occRaw = nullptr, *occDil = nullptr, *occMacro = nullptr;
+  int nc[3] = {0, 0, 0};          // level-0 cells per axis
+  int occLevels = 0;              // pyramid levels (level l has ((nc - 1) >> l) + 1 cells per axis)
+  int occOff[12] = {0};           // byte offset of each level inside occPyr
+  uint8_t *occRaw = nullptr, *occPyr = nullptr;  // raw: 8 writer slots per cell; pyr: dilated level 0 + octree of maxima
   bool occValid = false;          // occRaw bounds every stored voxel
-  bool occDilDirty = true;        // occDil / occMacro need recomputing from occRaw
+  bool occDilDirty = true;        // occPyr needs recomputing from occRaw
+  uint8_t* occLvl = nullptr;      // per level-0 cell: highest void level for threshold occLvlThr (occupancy.h)
+  int occLvlThr = -2;             // -2 = occLvl is stale
   int occEpoch = 0;               // bumped whenever the grids are freed (plans remember the epoch they were built for)
   void occ_free();
 };
@@ -54,6 +58,7 @@ struct vr_decode_plan {
   bool vec16 = false;
   bool occFused = false;  // every tile of every job is one occupancy cell: the kernel keeps occRaw current
   int occEpoch = 0;
+  int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
 };
 

@@ -176,7 +176,8 @@ class Volume:
         check(lib.vr_volume_invalidate(self.h))
 
     def occupancy(self, which=0):
-        """Per-cell maxima as numpy (nz, ny, nx): 0 raw (cells of 32x32x16), 1 dilated, 2 macro."""
+        """Per-cell maxima as numpy (nz, ny, nx): 0 raw (cells of 32x32x16), 1 + l = level l of the octree of
+        dilated maxima (level 0 = dilated cells; each level halves the grid)."""
         dims = (ctypes.c_int32 * 3)()
         check(lib.vr_volume_occupancy_download(self.ctx.h, self.h, int(which), None, 0, dims))
         out = np.empty((dims[2], dims[1], dims[0]), np.uint8)
