@@ -201,11 +201,12 @@ VR_HD uint32_t vr_bit_addr(const vr_kd_geom& g, int b) {
 // When vec16 is set (seg == 16 and every address 16-byte aligned) one 128-bit store is issued.
 VR_HD void vr_tile_phase2_item(const vr_kd_geom& g, uint32_t item, const uint8_t* strips, uint8_t* dst,
                                int64_t rowPitch, int64_t slicePitch, bool vec16) {
+  // tile extents are powers of two: shifts and masks instead of integer division
   const int seg = g.tx < 16 ? g.tx : 16;
-  const int segsPerRow = g.tx / seg;
-  const int x0 = (int)(item % (uint32_t)segsPerRow) * seg;
-  const int y = (int)((item / (uint32_t)segsPerRow) % (uint32_t)g.ty);
-  const int z = (int)(item / (uint32_t)(segsPerRow * g.ty));
+  const int lsr = g.tx < 16 ? 0 : VR_CTZ32((uint32_t)g.tx) - 4, lty = VR_CTZ32((uint32_t)g.ty);
+  const int x0 = (int)(item & ((1u << lsr) - 1u)) * seg;
+  const int y = (int)((item >> lsr) & (uint32_t)(g.ty - 1));
+  const int z = (int)(item >> (lsr + lty));
   uint32_t base = 0;
   for (int j = 4; (1 << j) < g.tx; ++j) base += ((x0 >> j) & 1) ? vr_bit_addr(g, g.pathBit[0][j]) : 0u;
   for (int j = 0; (1 << j) < g.ty; ++j) base += ((y >> j) & 1) ? vr_bit_addr(g, g.pathBit[1][j]) : 0u;
@@ -245,11 +246,12 @@ VR_HD void vr_tile_phase2_item(const vr_kd_geom& g, uint32_t item, const uint8_t
 // Constant tile: same work items, value `val`.
 VR_HD void vr_tile_fill_item(const vr_kd_geom& g, uint32_t item, int val, uint8_t* dst, int64_t rowPitch,
                              int64_t slicePitch, bool vec16) {
+  // tile extents are powers of two: shifts and masks instead of integer division
   const int seg = g.tx < 16 ? g.tx : 16;
-  const int segsPerRow = g.tx / seg;
-  const int x0 = (int)(item % (uint32_t)segsPerRow) * seg;
-  const int y = (int)((item / (uint32_t)segsPerRow) % (uint32_t)g.ty);
-  const int z = (int)(item / (uint32_t)(segsPerRow * g.ty));
+  const int lsr = g.tx < 16 ? 0 : VR_CTZ32((uint32_t)g.tx) - 4, lty = VR_CTZ32((uint32_t)g.ty);
+  const int x0 = (int)(item & ((1u << lsr) - 1u)) * seg;
+  const int y = (int)((item >> lsr) & (uint32_t)(g.ty - 1));
+  const int z = (int)(item >> (lsr + lty));
   uint8_t* out = dst + (int64_t)z * slicePitch + (int64_t)y * rowPitch + x0;
   if (vec16) {
 #if defined(__CUDA_ARCH__)
@@ -264,8 +266,7 @@ VR_HD void vr_tile_fill_item(const vr_kd_geom& g, uint32_t item, int val, uint8_
 }
 
 VR_HD uint32_t vr_tile_items(const vr_kd_geom& g) {
-  const int seg = g.tx < 16 ? g.tx : 16;
-  return (uint32_t)((g.tx / seg) * g.ty * g.tz);
+  return (uint32_t)((g.tx < 16 ? 1 : (g.tx >> 4)) * g.ty * g.tz);
 }
 
 // =================================================================================================
