@@ -59,6 +59,12 @@ int vr_context_destroy(vr_context* ctx);
 /* Use an externally created cudaStream_t (e.g. torch's current stream) for all later calls. */
 int vr_context_set_stream(vr_context* ctx, void* cuda_stream);
 int vr_context_synchronize(vr_context* ctx);
+/* Cross-stream ordering for pipelines (e.g. a copy context uploading timestep t+1 while the render context
+ * decodes and draws timestep t): work submitted to `ctx` after this call starts only after everything
+ * submitted to `other` before this call has finished.  Device-side wait; the host does not block. */
+int vr_context_wait_for(vr_context* ctx, vr_context* other);
+/* Asynchronous device -> pinned/pageable host copy on the context stream (frame read-back in a pipeline). */
+int vr_context_download(vr_context* ctx, void* dst_host, const void* src_dev, int64_t nbytes);
 
 /* CUDA-event timing on the context stream (replaces DebugTimer::Begin/End, DebugTimer.cpp:6-35).
  * slot in [0,16): begin/end record events asynchronously; elapsed synchronises on the end event. */

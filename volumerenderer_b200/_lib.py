@@ -45,6 +45,8 @@ _SIGS = {
     "vr_context_destroy": (c_int, [c_void_p]),
     "vr_context_set_stream": (c_int, [c_void_p, c_void_p]),
     "vr_context_synchronize": (c_int, [c_void_p]),
+    "vr_context_wait_for": (c_int, [c_void_p, c_void_p]),
+    "vr_context_download": (c_int, [c_void_p, c_void_p, c_void_p, c_int64]),
     "vr_timer_begin": (c_int, [c_void_p, c_int]),
     "vr_timer_end": (c_int, [c_void_p, c_int]),
     "vr_timer_elapsed_ms": (c_int, [c_void_p, c_int, POINTER(ctypes.c_float)]),

@@ -52,6 +52,7 @@ int vr_context_destroy(vr_context* c) {
   cudaSetDevice(c->device);
   if (c->ownsStream) cudaStreamDestroy(c->stream);
   for (auto& e : c->ev) for (auto& k : e) if (k) cudaEventDestroy(k);
+  if (c->evOrder) cudaEventDestroy(c->evOrder);
   for (auto& kv : c->chainLuts) cudaFree(kv.second);
   delete c;
   return VR_OK;
@@ -67,6 +68,23 @@ int vr_context_synchronize(vr_context* c) {
   if (!c) return fail(VR_ERR_ARG, "null context");
   CU(cudaSetDevice(c->device));
   CU(cudaStreamSynchronize(c->stream));
+  return VR_OK;
+}
+
+int vr_context_wait_for(vr_context* c, vr_context* other) {
+  if (!c || !other) return fail(VR_ERR_ARG, "null context");
+  if (c == other || c->stream == other->stream) return VR_OK;  // same stream: already ordered
+  CU(cudaSetDevice(other->device));
+  if (!other->evOrder) CU(cudaEventCreateWithFlags(&other->evOrder, cudaEventDisableTiming));
+  CU(cudaEventRecord(other->evOrder, other->stream));
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamWaitEvent(c->stream, other->evOrder, 0));
+  return VR_OK;
+}
+int vr_context_download(vr_context* c, void* dst, const void* src, int64_t nbytes) {
+  if (!c || !dst || !src || nbytes < 0) return fail(VR_ERR_ARG, "vr_context_download: bad argument");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(dst, src, (size_t)nbytes, cudaMemcpyDeviceToHost, c->stream));
   return VR_OK;
 }
 

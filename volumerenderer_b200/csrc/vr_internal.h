@@ -11,6 +11,7 @@ struct vr_context {
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
   cudaEvent_t ev[16][2] = {};
+  cudaEvent_t evOrder = nullptr;  // recorded by vr_context_wait_for(other = this)
   std::map<uint64_t, uint32_t*> chainLuts;  // chainDist -> device table of 16384 entries
 };
 

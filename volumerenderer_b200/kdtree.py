@@ -28,6 +28,14 @@ class Context:
     def synchronize(self):
         check(lib.vr_context_synchronize(self.h))
 
+    def wait_for(self, other):
+        """Later work on this context waits (on the device) for everything already submitted to `other`."""
+        check(lib.vr_context_wait_for(self.h, other.h))
+
+    def download(self, dst_host_ptr, src_dev_ptr, nbytes):
+        """Asynchronous device -> host copy on this context's stream."""
+        check(lib.vr_context_download(self.h, c_void_p(int(dst_host_ptr)), c_void_p(int(src_dev_ptr)), int(nbytes)))
+
     def timer_begin(self, slot=0):
         check(lib.vr_timer_begin(self.h, slot))
 
