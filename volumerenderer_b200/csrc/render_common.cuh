@@ -174,6 +174,37 @@ __device__ __forceinline__ int occ_skip(const OccView& o, const Vol& v, V3 q, V3
 }
 __device__ __forceinline__ V3 recip(V3 d) { return {1.0f / d.x, 1.0f / d.y, 1.0f / d.z}; }
 
+
+// Sort-last: conservative index of the first lattice sample a slab can own.  Samples i < first_owned() are
+// certainly not owned (real-number geometry with a margin far above the lattice's accumulated rounding, and
+// one extra step), so the caller replays them with the three additions only -- no ownership or inside
+// test: once a coordinate has left (0,1) it never returns, so the regular loop's inside test still ends
+// the ray correctly when it resumes.  300 = the ray never meets the slab.
+__device__ __forceinline__ int first_owned(const Vol& v, V3 p0, V3 d) {
+  const float kMargin = 1.0e-4f;
+  const float pp[3] = {p0.x, p0.y, p0.z}, dd[3] = {d.x, d.y, d.z}, fG[3] = {v.fX, v.fY, v.fZ};
+  const int lo[3] = {v.lox, v.loy, v.loz}, hi[3] = {v.hix, v.hiy, v.hiz}, G[3] = {v.GX, v.GY, v.GZ};
+  float first = 0.0f;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    if (lo[a] <= 0 && hi[a] >= G[a]) continue;  // the slab spans this axis
+    const float a0 = lo[a] <= 0 ? -1.0f : ((float)lo[a] + 0.5f) / fG[a];   // owned  <=>  a0 <= p < a1 (up to rounding)
+    const float a1 = hi[a] >= G[a] ? 2.0f : ((float)hi[a] + 0.5f) / fG[a];
+    if (dd[a] > 0.0f) {
+      if (pp[a] > a1 + kMargin) return 300;
+      first = fmaxf(first, (a0 - kMargin - pp[a]) / dd[a]);
+    } else if (dd[a] < 0.0f) {
+      if (pp[a] < a0 - kMargin) return 300;
+      first = fmaxf(first, (a1 + kMargin - pp[a]) / dd[a]);
+    } else if (pp[a] < a0 - kMargin || pp[a] > a1 + kMargin) {
+      return 300;
+    }
+  }
+  // sample i sits at p0 + (i + 1) * d
+  const int i = (int)floorf(fminf(first, 400.0f)) - 2;
+  return min(max(i, 0), 300);
+}
+
 // dir and dirStep of the fragment (raycaster.frag:27,31 / isosurface.frag:88,92)
 __device__ __forceinline__ void ray_dir(const RenderParams& P, V3 vUV, V3* dir, V3* dirStep) {
   V3 eye = {P.eye[0], P.eye[1], P.eye[2]};

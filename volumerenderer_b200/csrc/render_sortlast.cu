@@ -43,7 +43,9 @@ __device__ __forceinline__ void march_segment(const Vol& v, const OccView& occ, 
   float c = *C, a = *A;
   const V3 inv = recip(dirStep);
   bool started = false;
-  for (int i = 0; i < 300; ++i) {
+  const int i0 = first_owned(v, p, dirStep);
+  for (int j = 0; j < i0 && i0 < 300; ++j) p = add(p, dirStep);  // lattice replay up to the slab, additions only
+  for (int i = i0; i < 300; ++i) {
     p = add(p, dirStep);
     if (!inside(p)) break;
     if (!owned(v, p)) {
@@ -112,7 +114,9 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
       const V3 inv = recip(dirStep);
       V3 p = vUV;
       bool started = false;
-      for (int i = 0; i < 300; ++i) {
+      const int i0 = first_owned(v, p, dirStep);
+      for (int j = 0; j < i0 && i0 < 300; ++j) p = add(p, dirStep);
+      for (int i = i0; i < 300; ++i) {
         p = add(p, dirStep);
         if (!inside(p)) break;
         if (!owned(v, p)) {
