@@ -131,8 +131,11 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     threads = max(1, (os.cpu_count() or 8) // max(1, world))
-    # the library launches on torch's current stream so NCCL collectives and kernels are ordered
-    ctx = vr.Context(local, cuda_stream=torch.cuda.current_stream().cuda_stream)
+    # one non-default stream for everything (capturable into a CUDA graph); the library launches on torch's
+    # current stream so NCCL collectives and kernels are ordered
+    main_stream = torch.cuda.Stream()
+    torch.cuda.set_stream(main_stream)
+    ctx = vr.Context(local, cuda_stream=main_stream.cuda_stream)
     t_setup = time.time()
     bricks, streams, _ = build_streams(vr, rank, threads)
     uniq = {id(s): s for s in streams}
@@ -197,20 +200,44 @@ def run_ours(args):
         render.render_device(ctx, vol, p, out.data_ptr(), None, cnt.data_ptr()); ctx.synchronize()
         samples = int(cnt.item())
 
+    # The step (decode launch, occupancy refresh, march / sort-last frame with its NCCL collectives) is
+    # captured once into a CUDA graph and replayed: one host call per step instead of ~10-30.
+    # (N = 1 only: capturing the NCCL point-to-point halo exchange together with the collectives hung in
+    # this torch/NCCL combination, so multi-GPU steps are launched eagerly.)
+    graph = None
+    if not args.no_graph and world == 1:
+        try:
+            barrier()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=main_stream):
+                step(None)
+            graph = g
+            graph.replay(); barrier()
+        except Exception as e:  # stay measurable: eager launches
+            graph = None
+            sys.stderr.write(f"bench.py: CUDA graph capture failed ({type(e).__name__}: {e}); eager launches\n")
+            torch.cuda.synchronize()
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     t0 = time.time()
     ctx.timer_begin(0)
-    n_probe = min(args.steps, 7)  # per-kernel event pairs on the last n_probe steps of the timed region
     for it in range(args.steps):
-        k = it - (args.steps - n_probe)
-        step(1 + 2 * k if k >= 0 else None)
+        if graph is not None:
+            graph.replay()
+        else:
+            step(None)
     ctx.timer_end(0)
     total_ms = ctx.timer_ms(0)
+    barrier()
+    t1 = time.time()
+    # per-stage CUDA-event pairs on extra eager steps right after the timed region (events cannot be read
+    # back from inside a captured graph); same kernels, same inputs
+    n_probe = 7
+    for k in range(n_probe):
+        step(1 + 2 * k)
     dec_ms = [ctx.timer_ms(1 + 2 * k) for k in range(n_probe)]
     mar_ms = [ctx.timer_ms(2 + 2 * k) for k in range(n_probe)]
     barrier()
-    t1 = time.time()
     clocks = sampler.stop(t0, t1) if sampler else None
     if world > 1:
         t = torch.tensor([total_ms], device=f"cuda:{local}")
@@ -334,7 +361,8 @@ def run_ours(args):
                 "mode": "streaming: timesteps t=0/t=1 alternate, H2D of the next timestep overlaps decode+frame of the current",
                 "serial": {"value": voxels_all / serial_ms / 1e6, "ms_per_step": serial_ms,
                            "h2d_bytes_per_step": int(h2d_sets[0])}},
-        "gpu_launches": (2 if world == 1 else 4) * args.steps,  # own kernels per step (N > 1: decode, partial, resolve, finish) "clocks": clocks, "setup_s": t_setup,
+        # own kernels per step: decode, 3 occupancy refresh, march (N > 1: partial, resolve, finish instead of march)
+        "cuda_graph": graph is not None, "gpu_launches": (5 if world == 1 else 7) * args.steps, "clocks": clocks, "setup_s": t_setup,
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)
@@ -455,6 +483,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of replaying a captured CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
