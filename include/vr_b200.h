@@ -93,6 +93,19 @@ int vr_stream_pin(vr_stream* s);
 /* H2D copy of stream + index (asynchronous on the context stream); implies prepare */
 int vr_stream_upload(vr_context* ctx, vr_stream* s);
 
+/* ---- MidRangeTree's 4-bit/node shader stream (MidRangeTree::convertToByteArray, MidRangeTree.cpp:1095-1128) ----
+ * byte k = tree[2k]<<6 | range[2k]<<4 | tree[2k+1]<<2 | range[2k+1]; length = next power of two >= ceil(n/2),
+ * zero tail.  tree / range are TwoBitArray bit arrays (LSB first) of n symbols.  Returns the packed length
+ * through *out_len; out may be NULL to query it. */
+int vr_nibbles_pack(const uint8_t* tree, const uint8_t* range, int64_t n, uint8_t* out, int64_t cap, int64_t* out_len);
+/* Inverse: split n nodes of a 4-bit stream into the two TwoBitArray bit arrays (ceil(n/4) bytes each). */
+int vr_nibbles_unpack(const uint8_t* nibbles, int64_t nbytes, int64_t n, uint8_t* tree_out, uint8_t* range_out);
+/* A decodable stream straight from the 4-bit shader stream: the midpoint codes are the codes levelCut walks
+ * (MidRangeTree::levelCut decodes the midpoint tree only, MidRangeTree.cpp:984); range_out (optional,
+ * ceil(numActiveNodes/4) bytes) receives the half-range codes. */
+int vr_stream_from_nibbles(const vr_stream_header* hdr, const uint8_t* distanceMap, const uint8_t* nibbles, int64_t nbytes,
+                           vr_stream** out, uint8_t* range_out);
+
 /* ---- codec: VolumeKdtree(in,x,y,z) + setErrorTolerance + setMaxEpochs + build ----------------- */
 /* (VolumeKdtree_recover.h:103,126,167,175; VolumeKdTree_recover.cpp:17-140).  CPU, reference
  * algorithm, byte-identical streams; `brick` is not modified (the reference empties its input). */

@@ -62,6 +62,9 @@ _SIGS = {
     "vr_stream_device_bytes": (c_int, [c_void_p, POINTER(c_int64)]),
     "vr_stream_pin": (c_int, [c_void_p]),
     "vr_stream_upload": (c_int, [c_void_p, c_void_p]),
+    "vr_nibbles_pack": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, POINTER(c_int64)]),
+    "vr_nibbles_unpack": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "vr_stream_from_nibbles": (c_int, [POINTER(StreamHeader), c_void_p, c_void_p, c_int64, POINTER(c_void_p), c_void_p]),
     "vr_kd_compress": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
     "vr_volume_create": (c_int, [c_void_p, c_int64, c_int64, c_int64, POINTER(c_void_p)]),
     "vr_volume_wrap": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, POINTER(c_void_p)]),

@@ -162,6 +162,49 @@ int vr_stream_validate(const vr_stream* s, int64_t* nodes) {
   return rc == VR_OK ? VR_OK : fail(rc, "stream does not parse to numActiveNodes symbols");
 }
 
+// ---- MidRangeTree 4-bit shader stream ------------------------------------------------------------------
+static inline int sym2(const uint8_t* bits, int64_t i) { return (bits[i >> 2] >> (2 * (int)(i & 3))) & 3; }
+
+int vr_nibbles_pack(const uint8_t* tree, const uint8_t* range, int64_t n, uint8_t* out, int64_t cap, int64_t* out_len) {
+  if (!tree || !range || n < 0 || !out_len) return fail(VR_ERR_ARG, "vr_nibbles_pack: bad argument");
+  const int64_t need = (n + 1) / 2;
+  int64_t len = 1;
+  while (len < need) len <<= 1;  // MidRangeTree.cpp:1098-1106: buffer length rounded up to a power of two
+  *out_len = len;
+  if (!out) return VR_OK;
+  if (cap < len) return fail(VR_ERR_ARG, "vr_nibbles_pack: buffer too small");
+  std::memset(out, 0, (size_t)len);
+  for (int64_t i = 0; i < n; ++i) {
+    const int nib = (sym2(tree, i) << 2) | sym2(range, i);
+    out[i >> 1] |= (uint8_t)((i & 1) ? nib : nib << 4);  // even node in the high nibble (:1124)
+  }
+  return VR_OK;
+}
+
+int vr_nibbles_unpack(const uint8_t* nib, int64_t nbytes, int64_t n, uint8_t* tree_out, uint8_t* range_out) {
+  if (!nib || n < 0 || (n + 1) / 2 > nbytes || (!tree_out && !range_out)) return fail(VR_ERR_ARG, "vr_nibbles_unpack: bad argument");
+  const size_t nb = (size_t)((n + 3) / 4);
+  if (tree_out) std::memset(tree_out, 0, nb);
+  if (range_out) std::memset(range_out, 0, nb);
+  for (int64_t i = 0; i < n; ++i) {
+    const int v = (i & 1) ? (nib[i >> 1] & 15) : (nib[i >> 1] >> 4);
+    if (tree_out) tree_out[i >> 2] |= (uint8_t)((v >> 2) << (2 * (int)(i & 3)));
+    if (range_out) range_out[i >> 2] |= (uint8_t)((v & 3) << (2 * (int)(i & 3)));
+  }
+  return VR_OK;
+}
+
+int vr_stream_from_nibbles(const vr_stream_header* hdr, const uint8_t* dm, const uint8_t* nib, int64_t nbytes, vr_stream** out,
+                           uint8_t* range_out) {
+  if (!hdr || !dm || !nib || !out) return fail(VR_ERR_ARG, "vr_stream_from_nibbles: null argument");
+  const int64_t n = hdr->numActiveNodes;
+  if (n <= 0 || (n + 1) / 2 > nbytes) return fail(VR_ERR_FORMAT, "4-bit stream shorter than numActiveNodes");
+  std::vector<uint8_t> mid((size_t)((n + 3) / 4));
+  int rc = vr_nibbles_unpack(nib, nbytes, n, mid.data(), range_out);
+  if (rc != VR_OK) return rc;
+  return vr_stream_from_memory(hdr, dm, mid.data(), (int64_t)mid.size(), out);
+}
+
 int vr_kd_compress(const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tol, int epochs, vr_stream** out,
                    vr_build_stats* stats) {
   if (!brick || !out) return fail(VR_ERR_ARG, "null");

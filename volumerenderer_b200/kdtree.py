@@ -74,6 +74,16 @@ class Stream:
         return cls(h)
 
     @classmethod
+    def from_nibbles(cls, header, distance_map, nibbles):
+        """MidRangeTree's 4-bit/node shader stream (convertToByteArray) -> (decodable midpoint Stream, range bits)."""
+        dm = np.ascontiguousarray(distance_map, dtype=np.uint8)
+        nb = np.ascontiguousarray(nibbles, dtype=np.uint8)
+        rng = np.zeros((header.numActiveNodes + 3) // 4, np.uint8)
+        h = c_void_p()
+        check(lib.vr_stream_from_nibbles(byref(header), dm.ctypes.data, nb.ctypes.data, nb.size, byref(h), rng.ctypes.data))
+        return cls(h), rng
+
+    @classmethod
     def open(cls, path):
         h = c_void_p()
         check(lib.vr_stream_open(str(path).encode(), byref(h)))
@@ -144,6 +154,23 @@ class Stream:
             self.close()
         except Exception:
             pass
+
+
+def nibbles_pack(tree_bits, range_bits, n):
+    """MidRangeTree::convertToByteArray (MidRangeTree.cpp:1095-1128): the 4-bit/node stream of n nodes."""
+    t = np.ascontiguousarray(tree_bits, np.uint8); r = np.ascontiguousarray(range_bits, np.uint8)
+    L = c_int64()
+    check(lib.vr_nibbles_pack(t.ctypes.data, r.ctypes.data, int(n), None, 0, byref(L)))
+    out = np.zeros(L.value, np.uint8)
+    check(lib.vr_nibbles_pack(t.ctypes.data, r.ctypes.data, int(n), out.ctypes.data, out.size, byref(L)))
+    return out
+
+
+def nibbles_unpack(nibbles, n):
+    nb = np.ascontiguousarray(nibbles, np.uint8)
+    t = np.zeros((n + 3) // 4, np.uint8); r = np.zeros((n + 3) // 4, np.uint8)
+    check(lib.vr_nibbles_unpack(nb.ctypes.data, nb.size, int(n), t.ctypes.data, r.ctypes.data))
+    return t, r
 
 
 class Volume:
