@@ -97,7 +97,9 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
       for (uint32_t t = 0; t < 256; ++t) {
         if (g_variant == 1) vr_tile_phase1_v3<true>(job, g, blk, t, strips.data());
         else if (g_variant == 2) vr_tile_phase1_v2(job, g, blk, t, strips.data());
-        else vr_tile_phase1_v3<false>(job, g, blk, t, strips.data());
+        else if (g_variant == 3) vr_tile_phase1_v3<false>(job, g, blk, t, strips.data());
+        else if (g_variant == 4) vr_tile_phase1_v4<true>(job, g, blk, t, strips.data());
+        else vr_tile_phase1_v4<false>(job, g, blk, t, strips.data());
       }
       for (uint32_t warp = 0; warp < 8; ++warp)
         for (uint32_t q = 0; q < (1u << g.fbUnit); ++q) vr_unit_phase2_item(g, warp, q, strips.data(), dst, SX, SX * SY);

@@ -3,6 +3,6 @@ AugmentariumLab/VolumeRenderer) behind a C ABI (include/vr_b200.h, libvr_b200.so
 
 Importing this package loads the CUDA library; it raises if the library was not built.
 """
-from . import _lib, render, synth  # noqa: F401
+from . import _lib, render, sortlast, synth  # noqa: F401
 from ._lib import VrError  # noqa: F401
 from .kdtree import Context, DecodePlan, Stream, Volume, VolumeKdtree, nibbles_pack, nibbles_unpack  # noqa: F401

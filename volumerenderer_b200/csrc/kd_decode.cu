@@ -26,7 +26,7 @@ struct DecodeParams {
   int vec16;
   int nBricks;
   int order;  // 1 = brick-major (default; measured 0.44 ms vs 0.60 ms tile-major on the rm_yslab batch), 0 = tile-major
-  int variant;  // parser variant of the fast path: 0 = v3 (chain length from the table), 1 = v3 (length by ALU), 2 = v2
+  int variant;  // parser variant of the fast path: 0 = v4 (default), 1 = v3 (chain length by ALU), 2 = v2, 3 = v3, 4 = v4 (length by ALU)
   // occupancy (occupancy.h): when a decode tile is exactly one cell the kernel stores the tile's maximum
   // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
   uint8_t* occ;             // null = off
@@ -67,9 +67,11 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
-    if (p.variant == 1) vr_tile_phase1_v3<true>(job, g, blk, threadIdx.x, sbase);
+    if (p.variant == 0) vr_tile_phase1_v4<false>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 1) vr_tile_phase1_v3<true>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 2) vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
-    else vr_tile_phase1_v3<false>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 3) vr_tile_phase1_v3<false>(job, g, blk, threadIdx.x, sbase);
+    else vr_tile_phase1_v4<true>(job, g, blk, threadIdx.x, sbase);
     __syncwarp();
     int64_t tb = job.dstOffset;  // tile origin, recomputed per thread (no CTA barrier on this path)
     for (int d = 0; d < g.Dt; ++d)

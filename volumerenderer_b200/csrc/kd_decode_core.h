@@ -556,6 +556,83 @@ VR_HD void vr_decode_leaf_v3(VrWin32& rd, int leafBits, int ownVal, uint64_t tre
   }
 }
 
+// v4: same arithmetic as v3, different control flow.  In v3 a loop iteration handles EITHER one inner node OR
+// one voxel pair, so the lanes of a warp (each at its own place in its own subtree) sit in different
+// branches most of the time and the warp pays for both bodies every iteration (profile: 20-28 of 32 lanes
+// active, 128 SASS instructions per iteration).  Here every iteration first runs a short descent loop over
+// inner nodes (the cheap body; lanes differ only in trip count, 1-5), after which all lanes are at a leaf
+// event -- a voxel pair, or occasionally a pruned box -- and execute the expensive pair body together.
+template <bool CHAIN_LEN_ALU, typename SA>
+VR_HD void vr_decode_leaf_v4(VrWin32& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
+                             VrStripSink3<SA>& sink) {
+  const uint32_t total = 1u << leafBits;  // leafBits >= 2 on this path
+  const int d0 = (int)(treeDist & 0xFF);
+  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
+  uint64_t stack = (uint64_t)ownVal;
+  int h = leafBits - 1;
+  uint32_t v = 0;
+  for (;;) {
+    uint32_t bits = rd.peek();
+    int c = (int)(bits & 3);
+    while (h > 0 && c != 3) {  // descend through inner nodes
+      const int val = vr_apply_bf((int)(stack & 0xFF), c, (int)((treeDist >> (8 * h)) & 0xFF));
+      stack = (stack << 8) | (uint64_t)val;
+      --h;
+      rd.skip(2);
+      bits = rd.peek();
+      c = (int)(bits & 3);
+    }
+    const int pv = (int)(stack & 0xFF);
+    if (h > 0) {  // constant box of 2^h voxels
+      sink.fill(v, 1u << h, pv);
+      v += 1u << h;
+      rd.skip(2);
+    } else {  // left and right voxel of one height-1 node, each with its refinement chain
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (t) { bits = rd.peek(); c = (int)(bits & 3); }
+        const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
+        int L;
+        if (CHAIN_LEN_ALU) {
+          const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;
+          L = (VR_CTZ32(m) >> 1) + 1;
+        } else {
+          L = (int)(e >> 24);
+        }
+        const bool leaf = c == 3;
+        rd.skip(leaf ? 2 : 2 + 2 * L);
+        int val = vr_apply_bf(pv, c, d0) + (int)(int8_t)(e & 0xFF);
+        const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
+        val = val < lo ? lo : val;
+        val = val > hi ? hi : val;
+        sink.put(v, leaf ? pv : val);
+        v += 1;
+      }
+    }
+    if (v == total) break;
+    const int nh = VR_CTZ32(v);
+    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
+    h = nh;
+  }
+}
+
+template <bool CHAIN_LEN_ALU, typename SA>
+VR_HD void vr_tile_phase1_v4(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  VrStripSink3<SA> sink;
+  sink.init(strips + leaf * pitch);
+  if (off == VR_PRUNED) {
+    sink.fill(0, 1u << g.leafBits, val);
+    return;
+  }
+  VrWin32 rd;
+  rd.init(job.words, off);
+  vr_decode_leaf_v4<CHAIN_LEN_ALU, SA>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
+}
+
 template <bool CHAIN_LEN_ALU, typename SA>
 VR_HD void vr_tile_phase1_v3(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
