@@ -6,6 +6,7 @@
 #include <vector>
 #include "../../volumerenderer_b200/csrc/kd_stream.h"
 #include "../../volumerenderer_b200/csrc/kd_decode_core.h"
+#include "../../volumerenderer_b200/csrc/kd_worklist.h"
 
 using namespace vr;
 
@@ -83,15 +84,24 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   std::vector<uint8_t> strips(lpt * ((1u << g.leafBits) + VR_LEAF_PITCH_PAD));
   const uint32_t items = vr_tile_items(g);
-  for (uint32_t tile = 0; tile < (1u << g.Dt); ++tile) {
+  // the launch's CTA list, exactly as the device path builds it (kd_worklist.h)
+  std::vector<vr_kd_work> work;
+  const KdIndex* idx = &s->index;
+  kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work);
+  for (const vr_kd_work& wk : work) {
+    const uint32_t tile = wk.id & ((1u << g.Dt) - 1u);
     int tox, toy, toz;
     vr_tile_origin(g, tile, &tox, &toy, &toz);
     uint8_t* dst = slab + job.dstOffset + ((int64_t)toz * SY + toy) * SX + tox;
-    uint32_t blk = job.tileLeafBlock[tile];
-    if (blk == VR_PRUNED) {
-      for (uint32_t it = 0; it < items; ++it) vr_tile_fill_item(g, it, job.tileVal[tile], dst, SX, SX * SY, vec16 != 0);
+    if (wk.L != VR_WORK_PARSE) {
+      if (vec16) {
+        for (uint32_t t = 0; t < 256; ++t) vr_group_fill(g, (int)wk.L, wk.vals, dst, SX, SX * SY, t, 256);
+      } else {
+        for (uint32_t it = 0; it < items; ++it) vr_tile_fill_item(g, it, (int)(wk.vals & 0xFF), dst, SX, SX * SY, false);
+      }
       continue;
     }
+    const uint32_t blk = job.tileLeafBlock[tile];
     std::fill(strips.begin(), strips.end(), 0xEE);
     if (g.fastPath && vec16) {  // mirrors the fast path of kd_decode_tiles_kernel
       for (uint32_t t = 0; t < 256; ++t) {

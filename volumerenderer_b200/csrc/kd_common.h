@@ -56,6 +56,10 @@ typedef struct vr_kd_geom {
   // coordinate bit; fbUnit = how many of those lie inside a warp's unit (path bits < leafBits+5)
   int32_t fastPath;
   int32_t fbUnit;
+  // constant-tile fills: tile-index bits of the (up to 3) finest x splits above the tile roots, finest
+  // first -- tiles that differ only in these bits are x-neighbours inside the brick
+  int32_t nxr;
+  uint8_t xrBit[4];
   uint16_t xa[4];
   uint16_t fbAddr[12];
   uint8_t fbAxis[12];
@@ -103,6 +107,10 @@ static inline int vr_kd_make_geom(int64_t X, int64_t Y, int64_t Z, vr_kd_geom* g
     }
   }
   if (g->Dt == 0) { g->tx = (int32_t)X; g->ty = (int32_t)Y; g->tz = (int32_t)Z; }
+  g->nxr = 0;
+  for (int j = 0; j < 4; ++j) g->xrBit[j] = 0;
+  for (int d = g->Dt - 1; d >= 0 && g->nxr < 3; --d)
+    if (g->splitDim[d] == 0) g->xrBit[g->nxr++] = (uint8_t)(g->Dt - 1 - d);
   // fast-path gather tables
   g->fastPath = 0; g->fbUnit = 0;
   for (int j = 0; j < 4; ++j) g->xa[j] = 0;

@@ -24,8 +24,7 @@ struct DecodeParams {
   int64_t rowPitch;    // slab X
   int64_t slicePitch;  // slab X*Y
   int vec16;
-  int nBricks;
-  int order;  // 1 = brick-major (default; measured 0.44 ms vs 0.60 ms tile-major on the rm_yslab batch), 0 = tile-major
+  const vr_kd_work* work;  // one entry per CTA (kd_worklist.h)
   int variant;  // parser variant of the fast path: 0 = v4 (default), 1 = v3 (chain length by ALU), 2 = v2, 3 = v3, 4 = v4 (length by ALU)
   // occupancy (occupancy.h): when a decode tile is exactly one cell the kernel stores the tile's maximum
   // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
@@ -42,28 +41,37 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   extern __shared__ __align__(16) uint8_t strips[];
   __shared__ int64_t sTileBase;
   const vr_kd_geom& g = p.g;
-  const uint32_t brick = p.order ? blockIdx.x >> g.Dt : blockIdx.x % (uint32_t)p.nBricks;
-  const uint32_t tile = p.order ? blockIdx.x & ((1u << g.Dt) - 1u) : blockIdx.x / (uint32_t)p.nBricks;
+  const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + blockIdx.x);  // {id, L, vals}
+  const uint32_t brick = wk.x >> g.Dt;
+  const uint32_t tile = wk.x & ((1u << g.Dt) - 1u);
   const vr_kd_job& job = p.jobs[brick];
-  const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   if (threadIdx.x == 0) {
     int ox, oy, oz;
     vr_tile_origin(g, tile, &ox, &oy, &oz);
     sTileBase = job.dstOffset + (int64_t)oz * p.slicePitch + (int64_t)oy * p.rowPitch + ox;
   }
-  const uint32_t items = vr_tile_items(g);
-  if (blk == VR_PRUNED) {  // constant tile: pure fill
-    const int val = job.tileVal[tile];
-    if (p.occ && job.occBase >= 0 && threadIdx.x == 0) {
-      const uint32_t w = (uint32_t)val * 0x01010101u;
-      *reinterpret_cast<uint2*>(p.occ + tile_cell(p, job, tile) * 8) = make_uint2(w, w);
+  if (wk.y != VR_WORK_PARSE) {  // constant tiles: pure fill
+    const uint64_t vals = (uint64_t)wk.z | ((uint64_t)wk.w << 32);
+    const int L = (int)wk.y;
+    if (p.occ && job.occBase >= 0 && threadIdx.x < (1u << L)) {  // one thread per member tile
+      uint32_t t = tile;
+      for (int j = 0; j < L; ++j) t |= ((threadIdx.x >> j) & 1u) << g.xrBit[j];
+      const uint32_t w = (uint32_t)((vals >> (8 * threadIdx.x)) & 0xFF) * 0x01010101u;
+      *reinterpret_cast<uint2*>(p.occ + tile_cell(p, job, t) * 8) = make_uint2(w, w);
     }
     __syncthreads();
     uint8_t* dst = p.dst + sTileBase;
-    for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
-      vr_tile_fill_item(g, it, val, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
+    if (p.vec16) {
+      vr_group_fill(g, L, vals, dst, p.rowPitch, p.slicePitch, threadIdx.x, blockDim.x);
+    } else {
+      const uint32_t items = vr_tile_items(g);
+      for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
+        vr_tile_fill_item(g, it, (int)(vals & 0xFF), dst, p.rowPitch, p.slicePitch, false);
+    }
     return;
   }
+  const uint32_t blk = __ldg(job.tileLeafBlock + tile);
+  const uint32_t items = vr_tile_items(g);
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
@@ -104,34 +112,30 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
   return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
 }
 
-cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, int nBricks, uint8_t* dst,
+cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
                              const int32_t* tileCell) {
-  if (nBricks <= 0) return cudaSuccess;
+  if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
   p.jobs = jobsDev;
+  p.work = workDev;
   p.dst = dst;
   p.rowPitch = rowPitch;
   p.slicePitch = slicePitch;
   p.vec16 = vec16 ? 1 : 0;
-  p.nBricks = nBricks;
   p.occ = tileCell ? occ : nullptr; p.tileCell = tileCell;
   {
     static int variant = -1;
     if (variant < 0) { const char* e = getenv("VR_DECODE_VARIANT"); variant = e ? atoi(e) : 0; }
     p.variant = variant;
-    static int order = -1;
-    if (order < 0) { const char* e = getenv("VR_DECODE_ORDER"); order = e ? atoi(e) : 1; }
-    p.order = order;
   }
   const size_t smem = kd_decode_smem_bytes(g);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  const unsigned grid = (unsigned)nBricks << g.Dt;
-  kd_decode_tiles_kernel<<<grid, 256, smem, stream>>>(p);
+  kd_decode_tiles_kernel<<<(unsigned)nWork, 256, smem, stream>>>(p);
   return cudaGetLastError();
 }
 

@@ -38,6 +38,16 @@ typedef struct vr_kd_job {
   int64_t occBase;               // occupancy cell of the brick's (0,0,0) in the destination's grid, < 0 = tiles are not cells
 } vr_kd_job;
 
+// One CTA of the decode launch (host: kd_worklist.h).  id = brick << Dt | tile.  L = VR_WORK_PARSE: the tile is
+// parsed; otherwise the CTA fills the 2^L x-neighbouring constant tiles starting at `tile`, byte j of vals =
+// value of the j-th of them.
+#define VR_WORK_PARSE 0xFFFFFFFFu
+typedef struct vr_kd_work {
+  uint32_t id;
+  uint32_t L;
+  uint64_t vals;
+} vr_kd_work;
+
 // Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
 struct VrBitReader {
   const uint32_t* w;
@@ -262,6 +272,77 @@ VR_HD void vr_tile_fill_item(const vr_kd_geom& g, uint32_t item, int val, uint8_
 #endif
   } else {
     for (int xi = 0; xi < seg; ++xi) out[xi] = (uint8_t)val;
+  }
+}
+
+// ---- grouped constant fills -----------------------------------------------------------------------
+// A tile row is only tx (32) bytes wide, and a fill made of 32-byte pieces runs at ~4.2 TB/s on B200 where
+// full 128-byte lines reach 6.3-7 TB/s (tools/fill_probe.cu: every warp store then touches 16 L2 lines
+// instead of 4).  So constant tiles that are x-neighbours inside their brick are filled together: the tile
+// with the lowest x of the largest aligned all-constant group (1, 2, 4 or 8 tiles) writes rows of
+// n * tx bytes for the whole group, the other members write nothing.
+#define VR_FILL_GROUP_MAX_ROW 4096  // bytes; rows are cut into 16-byte pieces, one per thread of a 256-thread CTA
+
+// Returns log2 of the group size if `tile` (a constant tile) leads its group, -1 if another tile fills it.
+// Byte j of *vals = value of the j-th tile of the group (in x order).
+VR_HD int vr_fill_group_of(const vr_kd_geom& g, const vr_kd_job& job, uint32_t tile, uint64_t* vals) {
+  int nb = g.nxr;
+  while (nb > 0 && ((int64_t)g.tx << nb) > VR_FILL_GROUP_MAX_ROW) --nb;
+  if (g.tx < 16) nb = 0;
+  uint32_t xi = 0, rest = tile;
+  for (int j = 0; j < nb; ++j) {
+    xi |= ((tile >> g.xrBit[j]) & 1u) << j;
+    rest &= ~(1u << g.xrBit[j]);
+  }
+  uint32_t m = 0;
+  uint64_t v = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 8; ++i) {
+    if (i < (1u << nb)) {
+      uint32_t t = rest;
+      for (int j = 0; j < nb; ++j) t |= ((i >> j) & 1u) << g.xrBit[j];
+      if (job.tileLeafBlock[t] == VR_PRUNED) {
+        m |= 1u << i;
+        v |= (uint64_t)job.tileVal[t] << (8 * i);
+      }
+    }
+  }
+  int L = 0;
+  for (int l = nb; l >= 1; --l) {
+    const uint32_t lo = xi & ~((1u << l) - 1u);
+    const uint32_t gm = ((1u << (1u << l)) - 1u) << lo;
+    if ((m & gm) == gm) { L = l; break; }
+  }
+  if (xi & ((1u << L) - 1u)) return -1;
+  *vals = v >> (8 * xi);
+  return L;
+}
+
+VR_HD void vr_store16_const(uint8_t* out, int val) {
+#if defined(__CUDA_ARCH__)
+  const uint32_t w = (uint32_t)val * 0x01010101u;
+  *reinterpret_cast<uint4*>(out) = make_uint4(w, w, w, w);
+#else
+  for (int i = 0; i < 16; ++i) out[i] = (uint8_t)val;
+#endif
+}
+
+// Thread `tid` of `nthreads` (a power of two >= pieces per row) fills its share of a group of 2^L tiles whose
+// first tile has its origin at dst (16-byte aligned destination).  A thread keeps one 16-byte column of the
+// group, so its value and x offset are fixed and a store costs one address update.
+VR_HD void vr_group_fill(const vr_kd_geom& g, int L, uint64_t vals, uint8_t* dst, int64_t rowPitch, int64_t slicePitch,
+                         uint32_t tid, uint32_t nthreads) {
+  const int lpt = VR_CTZ32((uint32_t)g.tx) - 4;  // log2 pieces per tile row
+  const int lR = lpt + L;                        // log2 pieces per group row
+  const uint32_t piece = tid & ((1u << lR) - 1u);
+  const uint32_t rstep = nthreads >> lR;
+  const int val = (int)((vals >> (8 * (piece >> lpt))) & 0xFF);
+  const int lty = VR_CTZ32((uint32_t)g.ty);
+  const uint32_t rows = (uint32_t)(g.ty * g.tz);
+  uint8_t* base = dst + (size_t)piece * 16;
+  for (uint32_t row = tid >> lR; row < rows; row += rstep) {
+    const uint32_t y = row & (uint32_t)(g.ty - 1), z = row >> lty;
+    vr_store16_const(base + (int64_t)z * slicePitch + (int64_t)y * rowPitch, val);
   }
 }
 

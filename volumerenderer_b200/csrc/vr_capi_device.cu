@@ -8,6 +8,7 @@
 
 #include "../../include/vr_b200.h"
 #include "kd_decode.h"
+#include "kd_worklist.h"
 #include "vr_internal.h"
 
 using namespace vr;
@@ -217,16 +218,7 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   p->occFused = occFused && vec16 && p->geom.fastPath;
   p->occEpoch = dst->occEpoch;
   if (!p->occFused) for (auto& j : jobs) j.occBase = -1;
-  if (const char* ev = getenv("VR_DECODE_SORT")) {
-    if (atoi(ev)) {  // experiment: bricks with the most live tiles first
-      std::vector<std::pair<int64_t, int>> key;
-      for (int i = 0; i < n; ++i) key.push_back({-streams[i]->kd.index.numLiveTiles, i});
-      std::stable_sort(key.begin(), key.end());
-      std::vector<vr_kd_job> sorted;
-      for (auto& k : key) sorted.push_back(jobs[(size_t)k.second]);
-      jobs.swap(sorted);
-    }
-  }
+  std::vector<vr_stream*> jobStream(streams, streams + n);
   if (p->occFused) {
     std::vector<int32_t> tc(size_t(1) << g.Dt);
     for (uint32_t t = 0; t < tc.size(); ++t) {
@@ -238,11 +230,24 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     if (et == cudaSuccess) et = cudaMemcpy(p->tileCellDev, tc.data(), tc.size() * 4, cudaMemcpyHostToDevice);
     if (et != cudaSuccess) { cudaFree(p->tileCellDev); delete p; return fail_cuda(et, "upload tile cells"); }
   }
-  cudaError_t e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
-  if (e != cudaSuccess) { cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
+  cudaError_t e;
+  {
+    std::vector<const KdIndex*> idx((size_t)n);
+    std::vector<int64_t> offs((size_t)n);
+    for (int i = 0; i < n; ++i) { idx[(size_t)i] = &jobStream[(size_t)i]->kd.index; offs[(size_t)i] = jobs[(size_t)i].dstOffset; }
+    std::vector<vr_kd_work> work;
+    const char* eo = getenv("VR_DECODE_ORDER");
+    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, eo ? atoi(eo) : 0, &work);
+    p->nWork = (int)work.size();
+    e = cudaMalloc((void**)&p->workDev, sizeof(vr_kd_work) * std::max<size_t>(work.size(), 1));
+    if (e == cudaSuccess) e = cudaMemcpy(p->workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload work list"); }
+  }
+  e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
+  if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
   e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // jobs is a stack-lifetime buffer
-  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
+  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
   *out = p;
   return VR_OK;
 }
@@ -251,7 +256,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
-  CU(kd_decode_launch(p->geom, p->jobsDev, p->n, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
+  CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
                       occ ? p->tileCellDev : nullptr));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
@@ -261,6 +266,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   if (!p) return VR_OK;
   cudaSetDevice(p->ctx->device);
   cudaFree(p->jobsDev);
+  cudaFree(p->workDev);
   cudaFree(p->tileCellDev);
   delete p;
   return VR_OK;

@@ -54,6 +54,8 @@ struct vr_decode_plan {
   vr_context* ctx = nullptr;
   vr_kd_geom geom;
   vr_kd_job* jobsDev = nullptr;
+  vr_kd_work* workDev = nullptr;  // CTA work list of the launch (kd_worklist.h)
+  int nWork = 0;
   int n = 0;
   vr_volume* dst = nullptr;
   bool vec16 = false;
