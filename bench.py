@@ -323,24 +323,15 @@ def run_ours(args):
             dist.barrier(); dist.destroy_process_group()
         return
     peak, peak_src = peaks()
-    # write-only ceiling of this device, measured live (1 GiB fill, best of 10): 96 % of the decode's bytes are writes
-    wbuf = torch.empty(1 << 30, dtype=torch.uint8, device=f"cuda:{local}")
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    wbest = 1e9
-    for _ in range(12):
-        e0.record(); wbuf.fill_(3); e1.record(); torch.cuda.synchronize()
-        wbest = min(wbest, e0.elapsed_time(e1))
-    write_only = wbuf.numel() / wbest / 1e6
-    del wbuf
     d_ms, m_ms = float(np.mean(dec_ms)), float(np.mean(mar_ms))
     dec_bytes = by["stream"] + by["voxels"]
     mar_bytes = 8 * samples // world + 16 * IMG * IMG  # per rank (N > 1: an even share of all ranks' fetches)
     roof_dec = {"kernel": "kd_decode_tiles_kernel", "bound": "hbm", "achieved": dec_bytes / d_ms / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": dec_bytes / d_ms / 1e6 / peak, "traffic": None, "ms": d_ms, "algorithmic_bytes": dec_bytes,
                 "index_bytes": by["index"], "peak_source": peak_src,
-                "write_only_gbs": write_only, "write_fraction": by["voxels"] / dec_bytes,
-                "note": "peak = measured read+write copy bandwidth; write_only_gbs = 1 GiB device fill timed in this run "
-                        "(the decode's bytes are write_fraction writes)"}
+                "write_fraction": by["voxels"] / dec_bytes,
+                "note": "peak = measured read+write copy bandwidth; a write-only fill of full 128-byte lines reaches the same "
+                        "figure on this part (tools/fill_probe.cu, profiles/r1_fill_probe.txt)"}
     roof_mar = {"kernel": "march_kernel<composite>" if world == 1 else "sort-last frame (halo + partial + all-gather + resolve + all-reduce + finish)", "bound": "hbm", "achieved": mar_bytes / m_ms / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": mar_bytes / m_ms / 1e6 / peak, "traffic": None, "ms": m_ms, "algorithmic_bytes": mar_bytes,
                 "peak_source": peak_src}

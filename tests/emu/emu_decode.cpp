@@ -87,7 +87,9 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   // the launch's CTA list, exactly as the device path builds it (kd_worklist.h)
   std::vector<vr_kd_work> work;
   const KdIndex* idx = &s->index;
-  kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work);
+  std::vector<vr_fill_job> fills;
+  const int64_t org[3] = {ox, oy, oz};
+  kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work, &fills, 4, org);
   for (const vr_kd_work& wk : work) {
     const uint32_t tile = wk.id & ((1u << g.Dt) - 1u);
     int tox, toy, toz;
@@ -101,6 +103,11 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
       }
       continue;
     }
+    for (uint32_t k = 0; k < ((uint32_t)(wk.vals >> 32) & 0x7FFFFFFFu); ++k) {  // constant groups attached to this parse CTA
+      const vr_fill_job& fj = fills[(size_t)(uint32_t)wk.vals + k];
+      for (uint32_t t = 0; t < 256; ++t)
+        vr_group_fill(g, (int)fj.L, fj.vals, slab + ((int64_t)fj.z * SY + fj.y) * SX + fj.x, SX, SX * SY, t, 256);
+    }
     const uint32_t blk = job.tileLeafBlock[tile];
     std::fill(strips.begin(), strips.end(), 0xEE);
     if (g.fastPath && vec16) {  // mirrors the fast path of kd_decode_tiles_kernel
@@ -109,7 +116,11 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
         else if (g_variant == 2) vr_tile_phase1_v2(job, g, blk, t, strips.data());
         else if (g_variant == 3) vr_tile_phase1_v3<false>(job, g, blk, t, strips.data());
         else if (g_variant == 4) vr_tile_phase1_v4<true>(job, g, blk, t, strips.data());
-        else vr_tile_phase1_v4<false>(job, g, blk, t, strips.data());
+        else if (g_variant == 5) vr_tile_phase1_v4<false, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
+        else if (g_variant == 6) vr_tile_phase1_v4<false>(job, g, blk, t, strips.data());
+        else if (g_variant == 11) vr_tile_phase1_v4<true, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
+        else if (g_variant == 10) vr_tile_phase1_v5<false, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
+        else vr_tile_phase1_v5<true, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
       }
       for (uint32_t warp = 0; warp < 8; ++warp)
         for (uint32_t q = 0; q < (1u << g.fbUnit); ++q) vr_unit_phase2_item(g, warp, q, strips.data(), dst, SX, SX * SY);

@@ -25,7 +25,8 @@ struct DecodeParams {
   int64_t slicePitch;  // slab X*Y
   int vec16;
   const vr_kd_work* work;  // one entry per CTA (kd_worklist.h)
-  int variant;  // parser variant of the fast path: 0 = v4 (default), 1 = v3 (chain length by ALU), 2 = v2, 3 = v3, 4 = v4 (length by ALU)
+  const vr_fill_job* fills;  // constant groups attached to parse CTAs
+  int variant;  // parser variant of the fast path: 0 = v4 with 3-word window, chain length by ALU (default), 1 = v3 (length by ALU), 2 = v2, 3 = v3, 4 = v4 (length by ALU), 5 = v4 3-word window, 6 = v4
   // occupancy (occupancy.h): when a decode tile is exactly one cell the kernel stores the tile's maximum
   // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
   uint8_t* occ;             // null = off
@@ -35,6 +36,22 @@ struct DecodeParams {
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
 __device__ __forceinline__ int64_t tile_cell(const DecodeParams& p, const vr_kd_job& job, uint32_t tile) {
   return job.occBase + __ldg(p.tileCell + tile);
+}
+
+__device__ __forceinline__ void attached_fills(const DecodeParams& p, uint32_t first, uint32_t count) {
+  for (uint32_t k = 0; k < count; ++k) {
+    const vr_fill_job* fj = p.fills + first + k;
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(fj));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(fj) + 1);
+    const uint64_t vals = (uint64_t)b.x | ((uint64_t)b.y << 32);
+    const int64_t cell = (int64_t)((uint64_t)b.z | ((uint64_t)b.w << 32));
+    if (p.occ && cell >= 0 && threadIdx.x < (1u << a.w)) {
+      const uint32_t w = (uint32_t)((vals >> (8 * threadIdx.x)) & 0xFF) * 0x01010101u;
+      *reinterpret_cast<uint2*>(p.occ + (cell + threadIdx.x) * 8) = make_uint2(w, w);
+    }
+    vr_group_fill(p.g, (int)a.w, vals, p.dst + (int64_t)(int)a.z * p.slicePitch + (int64_t)(int)a.y * p.rowPitch + (int)a.x, p.rowPitch,
+                  p.slicePitch, threadIdx.x, blockDim.x);
+  }
 }
 
 __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
@@ -70,12 +87,24 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
     }
     return;
   }
+  // constant groups that ride along with this parse CTA (wk.z = first, wk.w = count | late << 31): half of the CTAs
+  // store them before parsing, the other half afterwards, so that at any time some CTAs of an SM write (HBM bound)
+  // while the others parse (issue bound); with one order for all, the CTAs of a wave would fill and parse in step.
+  const bool late = (wk.w >> 31) != 0;
+  if (!late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
   const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   const uint32_t items = vr_tile_items(g);
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
-    if (p.variant == 0) vr_tile_phase1_v4<false>(job, g, blk, threadIdx.x, sbase);
+    if (p.variant == 0) vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 10) vr_tile_phase1_v5<false, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 11) vr_tile_phase1_v4<true, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 5) vr_tile_phase1_v4<false, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 7) vr_tile_phase1_v4<true, uint32_t, VrWin96, 0>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 8) vr_tile_phase1_v4<true, uint32_t, VrWin96, 1>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 9) vr_tile_phase1_v4<true, uint32_t, VrWin96, 4>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 6) vr_tile_phase1_v4<false>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 1) vr_tile_phase1_v3<true>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 2) vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
     else if (p.variant == 3) vr_tile_phase1_v3<false>(job, g, blk, threadIdx.x, sbase);
@@ -97,6 +126,7 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
       m = __reduce_max_sync(0xFFFFFFFFu, m);
       if (lane == 0) p.occ[tile_cell(p, job, tile) * 8 + warp] = (uint8_t)m;
     }
+    if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
     return;
   }
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
@@ -105,6 +135,7 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   uint8_t* dst = p.dst + sTileBase;
   for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
     vr_tile_phase2_item(g, it, strips, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
+  if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
 }
 
 size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
@@ -114,12 +145,13 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
 
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
-                             const int32_t* tileCell) {
+                             const int32_t* tileCell, const vr_fill_job* fillsDev) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
   p.jobs = jobsDev;
   p.work = workDev;
+  p.fills = fillsDev;
   p.dst = dst;
   p.rowPitch = rowPitch;
   p.slicePitch = slicePitch;

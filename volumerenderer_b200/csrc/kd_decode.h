@@ -9,8 +9,9 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 // Decodes the prepared streams jobsDev[] into dst (slab, x fastest; rowPitch = slab X, slicePitch = slab X*Y),
 // one CTA per entry of workDev (kd_worklist.h).  Asynchronous on `stream`.  occ (optional): raw occupancy grid
 // of the slab (occupancy.h, 8 slots per cell); tileCell[tile] = cell of the tile relative to the brick's first
-// cell; jobs with occBase >= 0 store their tile maxima into it.
+// cell; jobs with occBase >= 0 store their tile maxima into it.  fillsDev: the constant groups that parse entries
+// refer to (vals = first | count << 32).
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ = nullptr,
-                             const int32_t* tileCell = nullptr);
+                             const int32_t* tileCell = nullptr, const vr_fill_job* fillsDev = nullptr);
 }  // namespace vr

@@ -22,6 +22,9 @@
 #define VR_LDG32(p) (*(p))
 #endif
 
+#ifndef VR_PREFETCH_LINES
+#define VR_PREFETCH_LINES 2  // 128-byte lines requested ahead per leaf subtree (kd_decode.cu, parse path)
+#endif
 #define VR_LEAF_PITCH_PAD 4  // strip pitch = 2^leafBits + 4 bytes (keeps strips on distinct banks)
 
 // Per-brick decode job, resident in device memory.
@@ -47,6 +50,15 @@ typedef struct vr_kd_work {
   uint32_t L;
   uint64_t vals;
 } vr_kd_work;
+
+// One group of 2^L x-neighbouring constant tiles stored by the TMA fill kernel (kd_fill.h); 32 bytes, read as two
+// 16-byte words.
+typedef struct vr_fill_job {
+  int32_t x, y, z;   // voxel coordinates of the group's origin in the destination volume
+  uint32_t L;
+  uint64_t vals;     // byte j = value of the j-th tile
+  int64_t occCell;   // occupancy cell of the first tile (members follow at +1), < 0 = none
+} vr_fill_job;
 
 // Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
 struct VrBitReader {
@@ -338,11 +350,18 @@ VR_HD void vr_group_fill(const vr_kd_geom& g, int L, uint64_t vals, uint8_t* dst
   const uint32_t rstep = nthreads >> lR;
   const int val = (int)((vals >> (8 * (piece >> lpt))) & 0xFF);
   const int lty = VR_CTZ32((uint32_t)g.ty);
-  const uint32_t rows = (uint32_t)(g.ty * g.tz);
+  const uint32_t row0 = tid >> lR;
   uint8_t* base = dst + (size_t)piece * 16;
-  for (uint32_t row = tid >> lR; row < rows; row += rstep) {
-    const uint32_t y = row & (uint32_t)(g.ty - 1), z = row >> lty;
-    vr_store16_const(base + (int64_t)z * slicePitch + (int64_t)y * rowPitch, val);
+  if (rstep <= (uint32_t)g.ty) {  // a pass covers rstep rows of one slice: walk y inside z with a fixed pointer step
+    const int64_t ystep = (int64_t)rstep * rowPitch;
+    for (int z = 0; z < g.tz; ++z) {
+      uint8_t* q = base + (int64_t)z * slicePitch + (int64_t)row0 * rowPitch;
+      for (uint32_t y = row0; y < (uint32_t)g.ty; y += rstep, q += ystep) vr_store16_const(q, val);
+    }
+  } else {  // a pass covers whole slices: this thread keeps its y
+    const uint32_t zstep = rstep >> lty;
+    uint8_t* q = base + (int64_t)(row0 >> lty) * slicePitch + (int64_t)(row0 & (uint32_t)(g.ty - 1)) * rowPitch;
+    for (uint32_t z = row0 >> lty; z < (uint32_t)g.tz; z += zstep, q += (int64_t)zstep * slicePitch) vr_store16_const(q, val);
   }
 }
 
@@ -550,6 +569,35 @@ struct VrWin32 {
   }
 };
 
+// Same window with one more word of look-ahead: the word loaded by a refill is not part of the window until
+// the NEXT refill (16 symbols later), so the load latency never sits on the parser's dependent chain
+// (profile of VrWin32: a third of the parser's stall samples were on the funnel shift that follows a refill).
+// Reads at most 3 words past the word that holds the last symbol consumed.
+struct VrWin96 {
+  const uint32_t* w;
+  uint32_t cur, nxt, nn;
+  int bo;
+  VR_HD void init(const uint32_t* words, uint32_t sym) {
+    w = words + (sym >> 4);
+    cur = VR_LDG32(w);
+    nxt = VR_LDG32(w + 1);
+    nn = VR_LDG32(w + 2);
+    w += 3;
+    bo = (int)(sym & 15) * 2;
+  }
+  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
+  VR_HD void skip(int nbits) {
+    bo += nbits;
+    if (bo >= 32) {
+      cur = nxt;
+      nxt = nn;
+      nn = VR_LDG32(w);
+      ++w;
+      bo -= 32;
+    }
+  }
+};
+
 // 1 = saturating add, 2 = saturating subtract, 0/3 = unchanged; no branches.
 VR_HD int vr_apply_bf(int parent, int code, int dist) {
   const int s = (code & 1) - (code >> 1);
@@ -643,8 +691,8 @@ VR_HD void vr_decode_leaf_v3(VrWin32& rd, int leafBits, int ownVal, uint64_t tre
 // active, 128 SASS instructions per iteration).  Here every iteration first runs a short descent loop over
 // inner nodes (the cheap body; lanes differ only in trip count, 1-5), after which all lanes are at a leaf
 // event -- a voxel pair, or occasionally a pruned box -- and execute the expensive pair body together.
-template <bool CHAIN_LEN_ALU, typename SA>
-VR_HD void vr_decode_leaf_v4(VrWin32& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
+template <bool CHAIN_LEN_ALU, typename SA, typename WIN>
+VR_HD void vr_decode_leaf_v4(WIN& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
                              VrStripSink3<SA>& sink) {
   const uint32_t total = 1u << leafBits;  // leafBits >= 2 on this path
   const int d0 = (int)(treeDist & 0xFF);
@@ -697,7 +745,112 @@ VR_HD void vr_decode_leaf_v4(VrWin32& rd, int leafBits, int ownVal, uint64_t tre
   }
 }
 
-template <bool CHAIN_LEN_ALU, typename SA>
+// v5: the three lowest levels of a leaf subtree (7 inner nodes, 8 voxels: an "octet") as straight-line code.
+// v4 still pays ~31 instructions per inner node (dynamic height: 64-bit shifts for the value stack and the level
+// distance, loop control) and ~12 per voxel pair for the pop.  Below height 3 the shape of the tree is fixed, so
+// node values live in registers, level distances and strip byte positions are compile-time constants, and only
+// the symbols decide: 3 at an inner node skips its subtree (the lanes that do not skip it keep the warp busy).
+// Heights >= 3 keep v4's dynamic loop (at most 7 such nodes per leaf subtree).
+template <int H, int POS, bool CHAIN_LEN_ALU, typename SA, typename WIN>
+struct VrSub {
+  static VR_HD void run(WIN& rd, int pv, uint64_t treeDist, const uint32_t* lut, SA base, uint32_t& acc) {
+    const uint32_t bits = rd.peek();
+    const int c = (int)(bits & 3);
+    rd.skip(2);
+    if (c == 3) {  // constant box of 2^H voxels, H = 1 or 2
+      if (H == 2) {
+        VR_ST32(base + POS, (uint32_t)pv * 0x01010101u);
+      } else {
+        acc |= ((uint32_t)pv * 0x0101u) << (8 * (POS & 3));
+        if ((POS & 3) == 2) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
+      }
+    } else {
+      const int val = vr_apply_bf(pv, c, (int)((treeDist >> (8 * H)) & 0xFF));
+      VrSub<H - 1, POS, CHAIN_LEN_ALU, SA, WIN>::run(rd, val, treeDist, lut, base, acc);
+      VrSub<H - 1, POS + (1 << (H - 1)), CHAIN_LEN_ALU, SA, WIN>::run(rd, val, treeDist, lut, base, acc);
+    }
+  }
+};
+template <int POS, bool CHAIN_LEN_ALU, typename SA, typename WIN>
+struct VrSub<0, POS, CHAIN_LEN_ALU, SA, WIN> {  // one voxel with its refinement chain
+  static VR_HD void run(WIN& rd, int pv, uint64_t treeDist, const uint32_t* lut, SA base, uint32_t& acc) {
+    const uint32_t bits = rd.peek();
+    const int c = (int)(bits & 3);
+    const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
+    int L;
+    if (CHAIN_LEN_ALU) {
+      const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;
+      L = (VR_CTZ32(m) >> 1) + 1;
+    } else {
+      L = (int)(e >> 24);
+    }
+    const bool leaf = c == 3;
+    rd.skip(leaf ? 2 : 2 + 2 * L);
+    int val = vr_apply_bf(pv, c, (int)(treeDist & 0xFF)) + (int)(int8_t)(e & 0xFF);
+    const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
+    val = val < lo ? lo : val;
+    val = val > hi ? hi : val;
+    acc |= (uint32_t)(leaf ? pv : val) << (8 * (POS & 3));
+    if ((POS & 3) == 3) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
+  }
+};
+
+template <bool CHAIN_LEN_ALU, typename SA, typename WIN>
+VR_HD void vr_decode_leaf_v5(WIN& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut, SA base) {
+  const uint32_t total = 1u << leafBits;  // leafBits >= 4 on this path
+  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
+  uint64_t stack = (uint64_t)ownVal;
+  int h = leafBits - 1;
+  uint32_t v = 0;
+  for (;;) {
+    uint32_t bits = rd.peek();
+    int c = (int)(bits & 3);
+    while (h > 3 && c != 3) {  // inner nodes above the octets
+      const int val = vr_apply_bf((int)(stack & 0xFF), c, (int)((treeDist >> (8 * h)) & 0xFF));
+      stack = (stack << 8) | (uint64_t)val;
+      --h;
+      rd.skip(2);
+      bits = rd.peek();
+      c = (int)(bits & 3);
+    }
+    const int pv = (int)(stack & 0xFF);
+    rd.skip(2);
+    if (c == 3) {  // constant box of 2^h >= 8 voxels
+      const uint32_t word = (uint32_t)pv * 0x01010101u;
+      for (uint32_t i = 0; i < (1u << h); i += 4) VR_ST32(base + v + i, word);
+      v += 1u << h;
+    } else {  // h == 3: an octet
+      const int val = vr_apply_bf(pv, c, (int)((treeDist >> 24) & 0xFF));
+      uint32_t acc = 0;
+      VrSub<2, 0, CHAIN_LEN_ALU, SA, WIN>::run(rd, val, treeDist, lut, base + v, acc);
+      VrSub<2, 4, CHAIN_LEN_ALU, SA, WIN>::run(rd, val, treeDist, lut, base + v, acc);
+      v += 8;
+    }
+    if (v == total) break;
+    const int nh = VR_CTZ32(v);
+    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
+    h = nh;
+  }
+}
+
+template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32, int PF = VR_PREFETCH_LINES>
+VR_HD void vr_tile_phase1_v5(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  const SA base = strips + leaf * pitch;
+  if (off == VR_PRUNED) {
+    const uint32_t word = (uint32_t)val * 0x01010101u;
+    for (uint32_t i = 0; i < (1u << g.leafBits); i += 4) VR_ST32(base + i, word);
+    return;
+  }
+  WIN rd;
+  rd.init(job.words, off);
+  vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
+}
+
+template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32, int PF = VR_PREFETCH_LINES>
 VR_HD void vr_tile_phase1_v4(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
@@ -709,9 +862,18 @@ VR_HD void vr_tile_phase1_v4(const vr_kd_job& job, const vr_kd_geom& g, uint32_t
     sink.fill(0, 1u << g.leafBits, val);
     return;
   }
-  VrWin32 rd;
+#if defined(__CUDA_ARCH__)
+  // The segment of one leaf subtree is 50-160 bytes of the stream that nobody has touched yet: without help every
+  // 32-byte sector is a DRAM round trip in the middle of the dependent parse (a warp paid ~50 of them per tile, one
+  // after the other).  Ask for the lines now, all lanes at once, so that they are under way while the parse starts.
+  {
+    const char* q = reinterpret_cast<const char*>(job.words + (off >> 4));
+    for (int k = 0; k < PF; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + 128 * k));
+  }
+#endif
+  WIN rd;
   rd.init(job.words, off);
-  vr_decode_leaf_v4<CHAIN_LEN_ALU, SA>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
+  vr_decode_leaf_v4<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
 }
 
 template <bool CHAIN_LEN_ALU, typename SA>

@@ -15,12 +15,23 @@
 
 namespace vr {
 
-// order: 0 = address order, 1 = parse tiles first, 2 = parse tiles last (each class in address order)
+// order: 0 = address order, 1 = parse tiles first, 2 = parse tiles last (each class in address order).
+// attach > 0 (needs fills != null): up to `attach` constant groups ride along with every parse CTA, which stores
+// them before it starts parsing -- the fills (pure HBM writes) then overlap the parsing (issue bound) of the other
+// CTAs on the same SM instead of forming a phase of their own.  Groups are dealt out evenly in address order;
+// what does not fit stays a CTA of its own.  fills receives the attached groups; origins = voxel origin of every
+// brick in the destination (3 per brick), occBase / tileCell as in the decode kernel (null = no occupancy).
 inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* idx, const int64_t* dstOffset, int64_t rowPitch,
-                              int64_t slicePitch, bool vec16, int order, std::vector<vr_kd_work>* out) {
+                              int64_t slicePitch, bool vec16, int order, std::vector<vr_kd_work>* out,
+                              std::vector<vr_fill_job>* fills = nullptr, int attach = 0, const int64_t* origins = nullptr,
+                              int lateMode = 0,
+                              const int64_t* occBase = nullptr, const int32_t* tileCell = nullptr) {
   struct Item { int64_t key; vr_kd_work w; };
+  struct FItem { int64_t key; vr_kd_work w; vr_fill_job f; };
   std::vector<Item> items;
+  std::vector<FItem> fitems;
   const uint32_t nt = 1u << g.Dt;
+  const bool split = fills && attach > 0 && vec16 && origins;
   items.reserve((size_t)n * nt / 4 + 16);
   for (int b = 0; b < n; ++b) {
     vr_kd_job hj{};  // host view of the two tile tables, which is all vr_fill_group_of reads
@@ -45,12 +56,38 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
       int ox, oy, oz;
       vr_tile_origin(g, t, &ox, &oy, &oz);
       int64_t key = dstOffset[b] + (int64_t)oz * slicePitch + (int64_t)oy * rowPitch + ox;
+      if (!parse && split) {
+        vr_fill_job f;
+        f.x = (int32_t)(origins[3 * b] + ox);
+        f.y = (int32_t)(origins[3 * b + 1] + oy);
+        f.z = (int32_t)(origins[3 * b + 2] + oz);
+        f.L = w.L;
+        f.vals = w.vals;
+        f.occCell = (occBase && tileCell && occBase[b] >= 0) ? occBase[b] + tileCell[t] : -1;
+        fitems.push_back({key, w, f});
+        continue;
+      }
       if (order == 1 && !parse) key += int64_t(1) << 60;
       if (order == 2 && parse) key += int64_t(1) << 60;
       items.push_back({key, w});
     }
   }
   std::sort(items.begin(), items.end(), [](const Item& a, const Item& b) { return a.key < b.key; });
+  if (fills) fills->clear();
+  if (split) {
+    std::sort(fitems.begin(), fitems.end(), [](const FItem& a, const FItem& b) { return a.key < b.key; });
+    const size_t P = items.size(), F = fitems.size();
+    size_t next = 0;
+    for (size_t i = 0; i < P && next < F; ++i) {  // even deal: parse CTA i gets groups [i*F/P, (i+1)*F/P), capped
+      size_t want = std::min<size_t>((F * (i + 1)) / P - (F * i) / P, (size_t)attach);
+      want = std::min(want, F - next);
+      // bit 63 = store the groups after parsing instead of before (every other parse CTA, see kd_decode.cu)
+      const uint64_t late = lateMode == 1 ? (i & 1) : (lateMode == 2 ? 1 : 0);
+      items[i].w.vals = (uint64_t)fills->size() | ((uint64_t)want << 32) | (late << 63);
+      for (size_t k = 0; k < want; ++k) fills->push_back(fitems[next++].f);
+    }
+    for (; next < F; ++next) items.push_back({fitems[next].key, fitems[next].w});  // leftovers: CTAs of their own, after the parse CTAs
+  }
   out->resize(items.size());
   for (size_t i = 0; i < items.size(); ++i) (*out)[i] = items[i].w;
 }

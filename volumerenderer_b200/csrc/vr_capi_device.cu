@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -169,6 +170,11 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
 extern "C" {
 
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
 int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n, const int64_t* origins,
                           vr_volume* dst, vr_decode_plan** out) {
   if (!ctx || !streams || n <= 0 || !origins || !dst || !out) return fail(VR_ERR_ARG, "vr_decode_plan_create: bad argument");
@@ -219,8 +225,10 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   p->occEpoch = dst->occEpoch;
   if (!p->occFused) for (auto& j : jobs) j.occBase = -1;
   std::vector<vr_stream*> jobStream(streams, streams + n);
+  std::vector<int32_t> tileCellHost;
   if (p->occFused) {
-    std::vector<int32_t> tc(size_t(1) << g.Dt);
+    std::vector<int32_t>& tc = tileCellHost;
+    tc.resize(size_t(1) << g.Dt);
     for (uint32_t t = 0; t < tc.size(); ++t) {
       int ox, oy, oz;
       vr_tile_origin(g, t, &ox, &oy, &oz);
@@ -236,18 +244,27 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     std::vector<int64_t> offs((size_t)n);
     for (int i = 0; i < n; ++i) { idx[(size_t)i] = &jobStream[(size_t)i]->kd.index; offs[(size_t)i] = jobs[(size_t)i].dstOffset; }
     std::vector<vr_kd_work> work;
-    const char* eo = getenv("VR_DECODE_ORDER");
-    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, eo ? atoi(eo) : 0, &work);
+    std::vector<vr_fill_job> fills;
+    std::vector<int64_t> ob((size_t)n);
+    for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
+    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
+                      env_int("VR_FILL_ATTACH", 2), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
+                      p->occFused ? tileCellHost.data() : nullptr);
     p->nWork = (int)work.size();
+    p->nFill = (int)fills.size();
     e = cudaMalloc((void**)&p->workDev, sizeof(vr_kd_work) * std::max<size_t>(work.size(), 1));
     if (e == cudaSuccess) e = cudaMemcpy(p->workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload work list"); }
+    if (e == cudaSuccess && p->nFill) {
+      e = cudaMalloc((void**)&p->fillJobsDev, sizeof(vr_fill_job) * fills.size());
+      if (e == cudaSuccess) e = cudaMemcpy(p->fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload work list"); }
   }
   e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
-  if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
+  if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
   e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // jobs is a stack-lifetime buffer
-  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->workDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
+  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
   *out = p;
   return VR_OK;
 }
@@ -256,8 +273,8 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
-  CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
-                      occ ? p->tileCellDev : nullptr));
+  CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
+                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   return VR_OK;
@@ -267,6 +284,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaSetDevice(p->ctx->device);
   cudaFree(p->jobsDev);
   cudaFree(p->workDev);
+  cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
   delete p;
   return VR_OK;

@@ -56,6 +56,8 @@ struct vr_decode_plan {
   vr_kd_job* jobsDev = nullptr;
   vr_kd_work* workDev = nullptr;  // CTA work list of the launch (kd_worklist.h)
   int nWork = 0;
+  vr_fill_job* fillJobsDev = nullptr;  // constant groups attached to parse CTAs (kd_worklist.h)
+  int nFill = 0;
   int n = 0;
   vr_volume* dst = nullptr;
   bool vec16 = false;
