@@ -188,6 +188,8 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step(1)
+    # nvidia-smi needs a few hundred ms to start printing: launch it now so that it is sampling when the timed region runs
+    sampler = ClockSampler(local) if rank == 0 else None
     # samples per frame (effective march steps reaching the fetch), counted once outside the timed region
     torch.cuda.synchronize()
     if world > 1:
@@ -218,7 +220,6 @@ def run_ours(args):
             sys.stderr.write(f"bench.py: CUDA graph capture failed ({type(e).__name__}: {e}); eager launches\n")
             torch.cuda.synchronize()
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
     t0 = time.time()
     ctx.timer_begin(0)
     for it in range(args.steps):
