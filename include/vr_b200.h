@@ -111,6 +111,12 @@ int vr_stream_from_nibbles(const vr_stream_header* hdr, const uint8_t* distanceM
  * algorithm, byte-identical streams; `brick` is not modified (the reference empties its input). */
 int vr_kd_compress(const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tolerance, int maxEpochs,
                    vr_stream** out, vr_build_stats* stats);
+/* The same producer on the GPU (csrc/kd_build.cu): level-parallel kernels, byte-identical streams
+ * (the two sequential steps of build -- the running-mean estimate of encodeNodeEstimate :415-455 and the
+ * order-dependent double accumulation of compressGradientDescent :206-384 -- are reproduced exactly, see
+ * csrc/kd_build_core.h).  `brick` is host memory (uploaded); synchronous. */
+int vr_kd_compress_device(vr_context* ctx, const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tolerance, int maxEpochs,
+                          vr_stream** out, vr_build_stats* stats);
 
 /* ---- volume (device slab) --------------------------------------------------------------------- */
 /* Replaces VolumeReader::data + textureId (VolumeReader.h:42-51): an SX*SY*SZ uint8 array. */
@@ -124,6 +130,11 @@ int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host); /* s
  * brick (BX*BY*BZ, x fastest) at voxel origin (ox,oy,oz) of the slab; 64-bit indexing (SURVEY C-12). */
 int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, int64_t BX, int64_t BY,
                            int64_t BZ, int64_t ox, int64_t oy, int64_t oz);
+/* GPU producer on a brick that already lives in a device volume (e.g. one just decoded, simulated or uploaded):
+ * compresses the X*Y*Z box at `origin` without a host round trip of the voxels.  fixed_point_iterations (optional,
+ * 2 entries): scan passes of the running-mean fixed point, total and worst level. */
+int vr_kd_compress_volume(vr_context* ctx, const vr_volume* vol, const int64_t origin[3], int64_t X, int64_t Y, int64_t Z,
+                          int tolerance, int maxEpochs, vr_stream** out, vr_build_stats* stats, int64_t* fixed_point_iterations);
 
 /* ---- empty-space skipping (north_star; no usable bound structure exists in the reference) --
  * Every volume carries a grid of exact per-cell maxima (cells of 32x32x16 voxels aligned to the global

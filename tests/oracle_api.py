@@ -50,6 +50,10 @@ if REF is not None:
 
 if EMU is not None:
     LL = c_longlong
+    if hasattr(EMU, "emu_build"):
+        EMU.emu_build.argtypes = [c_void_p, LL, LL, LL, c_int, c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(LL)]
+        EMU.emu_build_matches_host.argtypes = [c_void_p, c_void_p, LL, LL, LL, c_int, c_int]
+        EMU.emu_accumulate_check.argtypes = [ctypes.c_double, c_void_p, LL]
     EMU.emu_compress.restype = c_void_p
     EMU.emu_compress.argtypes = [c_void_p, LL, LL, LL, c_int, c_int, c_void_p]
     EMU.emu_from_memory.restype = c_void_p

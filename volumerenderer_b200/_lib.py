@@ -66,6 +66,9 @@ _SIGS = {
     "vr_nibbles_unpack": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "vr_stream_from_nibbles": (c_int, [POINTER(StreamHeader), c_void_p, c_void_p, c_int64, POINTER(c_void_p), c_void_p]),
     "vr_kd_compress": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
+    "vr_kd_compress_device": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
+    "vr_kd_compress_volume": (c_int, [c_void_p, c_void_p, POINTER(c_int64), c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p),
+                                      POINTER(BuildStats), POINTER(c_int64)]),
     "vr_volume_create": (c_int, [c_void_p, c_int64, c_int64, c_int64, POINTER(c_void_p)]),
     "vr_volume_wrap": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, POINTER(c_void_p)]),
     "vr_volume_destroy": (c_int, [c_void_p]),

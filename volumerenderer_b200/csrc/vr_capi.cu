@@ -54,6 +54,7 @@ int vr_context_destroy(vr_context* c) {
   for (auto& e : c->ev) for (auto& k : e) if (k) cudaEventDestroy(k);
   if (c->evOrder) cudaEventDestroy(c->evOrder);
   for (auto& kv : c->chainLuts) cudaFree(kv.second);
+  vr::kd_builder_destroy(c->builder);
   delete c;
   return VR_OK;
 }

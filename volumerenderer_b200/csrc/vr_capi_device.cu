@@ -8,6 +8,7 @@
 #include <new>
 
 #include "../../include/vr_b200.h"
+#include "kd_build.h"
 #include "kd_decode.h"
 #include "kd_worklist.h"
 #include "vr_internal.h"
@@ -313,6 +314,55 @@ int vr_kd_levelcut(vr_context* ctx, vr_stream* s, int32_t cutDepth, uint8_t* out
   vr_decode_plan_destroy(p);
   vr_volume_destroy(v);
   return rc;
+}
+
+// ---- GPU stream producer (kd_build.cu) ---------------------------------------------------------------
+static int build_common(vr_context* ctx, const uint8_t* volDev, int64_t X, int64_t Y, int64_t Z, int64_t rowPitch, int64_t slicePitch,
+                        int tol, int epochs, vr_stream** out, vr_build_stats* stats, int64_t* iters) {
+  if (!ctx->builder) ctx->builder = kd_builder_create();
+  vr_stream* s = new vr_stream;
+  KdBuildStats st;
+  cudaError_t ce = cudaSuccess;
+  int rc = kd_build_device(ctx->builder, volDev, X, Y, Z, rowPitch, slicePitch, tol, epochs, ctx->stream, &s->kd, &st, &ce, iters);
+  if (rc != VR_OK) {
+    delete s;
+    if (rc == VR_ERR_CUDA) return fail_cuda(ce, "vr_kd_compress_device");
+    return fail(rc, "vr_kd_compress_device: extents must be powers of two");
+  }
+  if (stats) {
+    stats->maxErrorBeforeGrowth = st.maxErrorBeforeGrowth;
+    stats->maxError = st.maxError;
+    stats->meanL1 = st.meanL1;
+    stats->meanL2 = st.meanL2;
+    stats->zeroRunRewrites = st.zeroRunRewrites;
+  }
+  *out = s;
+  return VR_OK;
+}
+
+int vr_kd_compress_device(vr_context* ctx, const uint8_t* brick_host, int64_t X, int64_t Y, int64_t Z, int tol, int epochs,
+                          vr_stream** out, vr_build_stats* stats) {
+  if (!ctx || !brick_host || !out || X <= 0 || Y <= 0 || Z <= 0) return fail(VR_ERR_ARG, "vr_kd_compress_device: bad argument");
+  CU(cudaSetDevice(ctx->device));
+  uint8_t* dev = nullptr;
+  const size_t bytes = (size_t)X * (size_t)Y * (size_t)Z;
+  CU(cudaMalloc((void**)&dev, bytes));
+  cudaError_t e = cudaMemcpyAsync(dev, brick_host, bytes, cudaMemcpyHostToDevice, ctx->stream);
+  if (e != cudaSuccess) { cudaFree(dev); return fail_cuda(e, "upload brick"); }
+  int rc = build_common(ctx, dev, X, Y, Z, X, X * Y, tol, epochs, out, stats, nullptr);
+  cudaFree(dev);
+  return rc;
+}
+
+int vr_kd_compress_volume(vr_context* ctx, const vr_volume* vol, const int64_t origin[3], int64_t X, int64_t Y, int64_t Z, int tol,
+                          int epochs, vr_stream** out, vr_build_stats* stats, int64_t* fixed_point_iterations) {
+  if (!ctx || !vol || !origin || !out) return fail(VR_ERR_ARG, "vr_kd_compress_volume: bad argument");
+  if (origin[0] < 0 || origin[1] < 0 || origin[2] < 0 || X <= 0 || Y <= 0 || Z <= 0 || origin[0] + X > vol->SX || origin[1] + Y > vol->SY ||
+      origin[2] + Z > vol->SZ)
+    return fail(VR_ERR_ARG, "vr_kd_compress_volume: brick outside the volume");
+  CU(cudaSetDevice(ctx->device));
+  const uint8_t* p = vol->dev + (origin[2] * vol->SY + origin[1]) * vol->SX + origin[0];
+  return build_common(ctx, p, X, Y, Z, vol->SX, vol->SX * vol->SY, tol, epochs, out, stats, fixed_point_iterations);
 }
 
 }  // extern "C"

@@ -6,12 +6,15 @@
 #include "kd_decode_core.h"
 #include "kd_stream.h"
 
+namespace vr { struct KdBuilder; void kd_builder_destroy(KdBuilder*); }
+
 struct vr_context {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
   cudaEvent_t ev[16][2] = {};
   cudaEvent_t evOrder = nullptr;  // recorded by vr_context_wait_for(other = this)
+  vr::KdBuilder* builder = nullptr;  // scratch of the GPU stream producer (kd_build.h), created on first use
   std::map<uint64_t, uint32_t*> chainLuts;  // chainDist -> device table of 16384 entries
 };
 

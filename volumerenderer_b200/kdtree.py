@@ -100,6 +100,30 @@ class Stream:
         check(lib.vr_kd_compress(a.ctypes.data, X, Y, Z, int(tolerance), int(max_epochs), byref(h), byref(st)))
         return cls(h), st
 
+    @classmethod
+    def compress_device(cls, ctx, brick, tolerance=6, max_epochs=5):
+        """Same stream as compress(), produced on the GPU (csrc/kd_build.cu); brick is a host array (Z, Y, X)."""
+        a = np.ascontiguousarray(brick, dtype=np.uint8)
+        assert a.ndim == 3
+        Z, Y, X = a.shape
+        h = c_void_p()
+        st = _lib.BuildStats()
+        check(lib.vr_kd_compress_device(ctx.h, a.ctypes.data, X, Y, Z, int(tolerance), int(max_epochs), byref(h), byref(st)))
+        return cls(h), st
+
+    @classmethod
+    def compress_volume(cls, ctx, volume, origin, shape, tolerance=6, max_epochs=5):
+        """GPU producer on the (X, Y, Z) box at voxel `origin` (x, y, z) of a device Volume.
+        Returns (Stream, BuildStats, (scan passes of the running-mean fixed point: total, worst level))."""
+        import ctypes
+        org = (ctypes.c_int64 * 3)(*[int(v) for v in origin])
+        it = (ctypes.c_int64 * 2)(0, 0)
+        h = c_void_p()
+        st = _lib.BuildStats()
+        X, Y, Z = [int(v) for v in shape]
+        check(lib.vr_kd_compress_volume(ctx.h, volume.h, org, X, Y, Z, int(tolerance), int(max_epochs), byref(h), byref(st), it))
+        return cls(h), st, (int(it[0]), int(it[1]))
+
     def save(self, path):
         check(lib.vr_stream_save(self.h, str(path).encode()))
 
