@@ -50,6 +50,14 @@ int main(int argc, char** argv) {
     catch (const vr::Error& e) { std::printf("open_missing=error%d\n", e.code); }
     if (!gpu) return 0;
 
+    {  // the same build on the GPU gives the same stream
+      vr::VolumeKdtree gpuTree(volume.data, volume.dataDims[0], volume.dataDims[1], volume.dataDims[2]);
+      gpuTree.setMaxEpochs(2);
+      gpuTree.setErrorTolerance(1);
+      gpuTree.build(*ctx);
+      std::printf("gpu_build_equal=%d\n", (int)(gpuTree.tree == myTree.tree && gpuTree.distanceMap == myTree.distanceMap &&
+                                                 gpuTree.numActiveNodes == myTree.numActiveNodes && gpuTree.stats.maxError == myTree.stats.maxError));
+    }
     std::vector<vr::byte> treeData;
     myTree.levelCut(myTree.maxTreeDepth, treeData, *ctx);  // main.cpp:280-281
     std::printf("decoded=%u maxerr_measured=%d\n", fnv(treeData.data(), treeData.size()), myTree.measureMaxError());

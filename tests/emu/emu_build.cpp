@@ -2,7 +2,10 @@
 // kernel by kernel as plain loops over the same host/device element functions (csrc/kd_build_core.h) and with the
 // same parallel formulations (fixed-point running mean over prefix sums, hierarchical order-exact accumulation,
 // subtree sizes -> offsets -> scatter), so that its exactness can be checked where there is no GPU.
+#include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -57,6 +60,17 @@ int emu_build(const uint8_t* volume, long long X, long long Y, long long Z, int 
     uint8_t* code = codes.data() + (n - 1);
     int epoch = 0;
     recon.assign((size_t)n, 0);
+    if (const char* dd = getenv("EMU_DUMP_LEVELS")) {  // level inputs of the running-mean estimate, for convergence studies
+      char path[512];
+      snprintf(path, sizeof(path), "%s/level_%02d.bin", dd, depth);
+      if (FILE* f = fopen(path, "wb")) {
+        long long nn = n;
+        std::vector<uint8_t> par((size_t)n);
+        for (int64_t i = 0; i < n; ++i) par[(size_t)i] = (uint8_t)parent_of(parents, depth, i);
+        fwrite(&nn, 8, 1, f); fwrite(&depth, 4, 1, f); fwrite(par.data(), 1, (size_t)n, f); fwrite(truth, 1, (size_t)n, f);
+        fclose(f);
+      }
+    }
     // running mean as a fixed point over prefix sums (est_init / scan / est_iter of kd_build.cu)
     double distanceSum = 0.0, distanceCount = 0.0;
     {
@@ -72,6 +86,7 @@ int emu_build(const uint8_t* volume, long long X, long long Y, long long Z, int 
         uint64_t run = 0;
         for (int64_t i = 0; i < n; ++i) { prefix[(size_t)i] = run; run += items[(size_t)i]; }
         unsigned changed = 0;
+        int64_t first = -1;
         for (int64_t i = 0; i < n; ++i) {
           const int parent = parent_of(parents, depth, i), t = truth[i];
           const uint64_t st = prefix[(size_t)i];
@@ -80,9 +95,22 @@ int emu_build(const uint8_t* volume, long long X, long long Y, long long Z, int 
             dec[(size_t)i] = d;
             items[(size_t)i] = d ? (((uint64_t)std::abs(parent - t) << 32) | 1u) : 0;
             ++changed;
+            if (first < 0) first = i;
           }
         }
         if (!changed) break;
+        if (changed < 256) {  // est_window_kernel
+          const uint64_t st = prefix[(size_t)first];
+          double sum = (double)(st >> 32), count = (double)(uint32_t)st;
+          const int64_t end = std::min<int64_t>(first + 4096, n);
+          for (int64_t i = first; i < end; ++i) {
+            const int parent = parent_of(parents, depth, i), t = truth[i];
+            const bool d = vr_estimate_counts(parent, t, sum, count);
+            dec[(size_t)i] = d;
+            items[(size_t)i] = d ? (((uint64_t)std::abs(parent - t) << 32) | 1u) : 0;
+            if (d) { sum += (double)std::abs(parent - t); count += 1.0; }
+          }
+        }
       }
       itTotal += it + 1;
       if (it + 1 > itWorst) itWorst = it + 1;

@@ -88,6 +88,7 @@ def test_cpp_pipeline_gpu(exe, scene):
     assert rc == 0 and int(kv["decoded"]) == fnv_fast(want)
     assert int(kv["maxerr_measured"]) == int(np.abs(want.astype(int) - full.astype(int)).max())
     assert kv["cut10"] == "error5"                         # VR_ERR_UNSUPPORTED; the reference segfaults
+    assert kv["gpu_build_equal"] == "1"                    # VolumeKdtree::build(Context&): GPU producer, same stream
     p = render.default_params(96, 72, render.COMPOSITE, step=(1 / 64, 1 / 64, 1 / 32))
     img, S, _ = oa.oracle_render(want, render.oracle_param_blob(p), 4)
     assert int(kv["composite_samples"]) == S

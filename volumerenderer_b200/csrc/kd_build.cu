@@ -71,6 +71,23 @@ __global__ void est_iter_kernel(const uint8_t* parents, const uint8_t* truth, in
     dec[i] = d;
     items[i] = d ? (((uint64_t)abs(parent - t) << 32) | 1u) : 0;
     atomicAdd(changed, 1u);
+    atomicMin(changed + 1, (unsigned int)i);  // everything in front of the first change is final
+  }
+}
+// A pass that changes only a handful of decisions is usually a chain reaction creeping forward a few nodes per
+// pass (runs of nodes that sit exactly on the threshold).  Everything in front of the first change is final and
+// prefix[first] is exact, so one thread replays the next `len` nodes sequentially and leaves them final.
+__global__ void est_window_kernel(const uint8_t* parents, const uint8_t* truth, int depth, int64_t n, const uint64_t* prefix, uint64_t* items,
+                                  uint8_t* dec, int64_t first, int64_t len) {
+  const uint64_t st = prefix[first];
+  double sum = (double)(st >> 32), count = (double)(uint32_t)st;
+  const int64_t end = first + len < n ? first + len : n;
+  for (int64_t i = first; i < end; ++i) {
+    const int parent = parent_of(parents, depth, i), t = truth[i];
+    const bool d = vr_estimate_counts(parent, t, sum, count);
+    dec[i] = d;
+    items[i] = d ? (((uint64_t)abs(parent - t) << 32) | 1u) : 0;
+    if (d) { sum += (double)abs(parent - t); count += 1.0; }
   }
 }
 __global__ void est_seq_kernel(const uint8_t* parents, const uint8_t* truth, int depth, int64_t n, double* out) {
@@ -320,12 +337,15 @@ int kd_build_device(KdBuilder* b, const uint8_t* volDev, int64_t X, int64_t Y, i
         size_t tb = b->cubBytes;
         KB_CHECK(cub::DeviceScan::ExclusiveSum(b->cubTemp, tb, b->items, b->prefix, (int)n, stream));
         KB_CHECK(cudaMemsetAsync(changedDev, 0, sizeof(unsigned int), stream));
+        KB_CHECK(cudaMemsetAsync(changedDev + 1, 0xFF, sizeof(unsigned int), stream));
         est_iter_kernel<<<grid_for(n), TB, 0, stream>>>(parents, truth, depth, n, b->prefix, b->items, b->dec, changedDev);
         KB_CHECK(fetch(b, 3, stream));
-        unsigned int changed;
-        std::memcpy(&changed, b->scalarsHost + 2, sizeof(changed));
-        if (changed == 0) break;
+        unsigned int changed[2];
+        std::memcpy(changed, b->scalarsHost + 2, sizeof(changed));
+        if (changed[0] == 0) break;
         if (it >= 400) break;  // not converging: replay the level with one thread below
+        if (changed[0] < 256)   // a creeping chain reaction: settle the next stretch sequentially
+          est_window_kernel<<<1, 1, 0, stream>>>(parents, truth, depth, n, b->prefix, b->items, b->dec, (int64_t)changed[1], 4096);
       }
       itTotal += it + 1;
       if (it + 1 > itWorst) itWorst = it + 1;

@@ -312,10 +312,17 @@ class VolumeKdtree:
         self.maxEpochs = int(epochs)
 
     # -- build (VolumeKdTree_recover.cpp:17); the input array is left intact (SURVEY C-11)
-    def build(self, useThreads=True):
+    def build(self, useThreads=True, device=False):
+        """VolumeKdtree::build (VolumeKdtree_recover.h:126).  device=True runs the GPU producer (csrc/kd_build.cu) on
+        this object's context; both give the byte-identical stream of the reference."""
         if self._data is None:
             raise _lib.VrError(_lib.VR_ERR_STATE, "build: no input volume")
-        self._stream, self.stats = Stream.compress(self._data, self.tolerance, self.maxEpochs)
+        if device:
+            if self._ctx is None:
+                raise _lib.VrError(_lib.VR_ERR_STATE, "build(device=True) needs a Context")
+            self._stream, self.stats = Stream.compress_device(self._ctx, self._data, self.tolerance, self.maxEpochs)
+        else:
+            self._stream, self.stats = Stream.compress(self._data, self.tolerance, self.maxEpochs)
         return self
 
     def _need(self):
