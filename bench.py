@@ -370,7 +370,7 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
 
@@ -480,6 +480,17 @@ def cpu_baseline(budget_s=20.0, steps=1, warmup=0, as_line=False, args=None):
     return line
 
 
+_RESULT_FD = None
+
+
+def emit(obj):
+    data = (json.dumps(obj) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -489,10 +500,16 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of replaying a captured CUDA graph")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON result: libraries that print to fd 1 (NCCL's version banner, ...) are
+    # sent to stderr for the duration of the run and the result is written to the saved descriptor at the end
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
             return
-        print(json.dumps(cpu_baseline(budget_s=150.0, steps=args.steps, warmup=args.warmup, as_line=True, args=args)), flush=True)
+        emit(cpu_baseline(budget_s=150.0, steps=args.steps, warmup=args.warmup, as_line=True, args=args))
         return
     run_ours(args)
 
