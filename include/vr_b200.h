@@ -242,6 +242,37 @@ int vr_resolve_iso(vr_context* ctx, const vr_sortlast* sl, const vr_render_param
 int vr_volume_pack_box(vr_context* ctx, const vr_volume* v, const int64_t origin[3], const int64_t extent[3], uint8_t* dst_dev);
 int vr_volume_unpack_box(vr_context* ctx, vr_volume* v, const int64_t origin[3], const int64_t extent[3], const uint8_t* src_dev);
 
+/* ---- peer-memory exchange for the sort-last frame (NVLink / NVSwitch, one process per GPU) ----------------------
+ * The frame's exchange steps (halo planes, all-gather of segment transmittances, sum of the ranks' terms) move a few
+ * MB between ranks that sit on one NVSwitch: as NCCL calls they cost 80-250 us each, mostly latency.  A vr_peer is a
+ * window of device memory per rank that every other rank maps (CUDA IPC); data moves with ONE kernel per step that
+ * stores straight into the destination windows over NVLink and then raises a flag there; the consumer waits on its own
+ * flags with a one-warp kernel on its stream (bounded: a missing peer ends the wait after ~0.5 s and sets the error
+ * flag instead of hanging the GPU).  No host synchronisation, no staging copies, no NCCL on this path.
+ * Protocol: every put to (dst, slot) is matched by one wait on (slot, src) at dst, in the same order on both sides. */
+typedef struct vr_peer vr_peer;
+#define VR_PEER_HANDLE_BYTES 64
+#define VR_PEER_SLOTS 8
+int vr_peer_create(vr_context* ctx, int32_t rank, int32_t n, int64_t window_bytes, vr_peer** out);
+int vr_peer_destroy(vr_peer* p);
+int vr_peer_handle(const vr_peer* p, uint8_t out[VR_PEER_HANDLE_BYTES]);      /* to be all-gathered by the caller */
+int vr_peer_open(vr_peer* p, const uint8_t* handles /* n * VR_PEER_HANDLE_BYTES, rank-major */);
+/* same-process ranks (tests, one process driving several devices): raw pointers instead of IPC handles */
+int vr_peer_raw(const vr_peer* p, void** window);
+int vr_peer_open_raw(vr_peer* p, void* const* windows /* n, rank-major */);
+int vr_peer_window(const vr_peer* p, int32_t rank, void** ptr);               /* rank's window as mapped in this process */
+/* One kernel: for k < count copies bytes[k] from src_dev[k] (local memory) to window(dst_rank[k]) + dst_off[k], then
+ * raises flag (slot, my rank) at every distinct destination.  16-byte aligned pointers, offsets and sizes. */
+int vr_peer_put(vr_peer* p, int32_t slot, int32_t count, const int32_t* dst_rank, const int64_t* dst_off, const void* const* src_dev,
+                const int64_t* bytes);
+/* Waits (on the context's stream) until the ranks in src_rank[] have raised (slot, rank) once more. */
+int vr_peer_wait(vr_peer* p, int32_t slot, int32_t count, const int32_t* src_rank);
+/* out[j] = in[0][j] op in[1][j] op ... in[n-1][j] for j < count 4-byte elements, combined in index order
+ * (deterministic); op 0 = float sum, 1 = int32 min.  in[] are device pointers (typically n stripes inside this rank's
+ * window), count a multiple of 4. */
+int vr_peer_reduce(vr_peer* p, int32_t op, int32_t n, const void* const* in, void* out, int64_t count);
+int vr_peer_error(vr_peer* p, int32_t* timed_out); /* synchronises the stream; 0 = fine, else 0x10000 | slot << 8 | source rank of a wait that expired */
+
 #ifdef __cplusplus
 }
 #endif

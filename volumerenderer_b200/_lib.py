@@ -66,6 +66,17 @@ _SIGS = {
     "vr_nibbles_unpack": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "vr_stream_from_nibbles": (c_int, [POINTER(StreamHeader), c_void_p, c_void_p, c_int64, POINTER(c_void_p), c_void_p]),
     "vr_kd_compress": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
+    "vr_peer_create": (c_int, [c_void_p, c_int32, c_int32, c_int64, POINTER(c_void_p)]),
+    "vr_peer_destroy": (c_int, [c_void_p]),
+    "vr_peer_handle": (c_int, [c_void_p, c_void_p]),
+    "vr_peer_open": (c_int, [c_void_p, c_void_p]),
+    "vr_peer_raw": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "vr_peer_open_raw": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "vr_peer_window": (c_int, [c_void_p, c_int32, POINTER(c_void_p)]),
+    "vr_peer_put": (c_int, [c_void_p, c_int32, c_int32, POINTER(c_int32), POINTER(c_int64), POINTER(c_void_p), POINTER(c_int64)]),
+    "vr_peer_wait": (c_int, [c_void_p, c_int32, c_int32, POINTER(c_int32)]),
+    "vr_peer_reduce": (c_int, [c_void_p, c_int32, c_int32, POINTER(c_void_p), c_void_p, c_int64]),
+    "vr_peer_error": (c_int, [c_void_p, POINTER(c_int32)]),
     "vr_kd_compress_device": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
     "vr_kd_compress_volume": (c_int, [c_void_p, c_void_p, POINTER(c_int64), c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p),
                                       POINTER(BuildStats), POINTER(c_int64)]),

@@ -173,10 +173,17 @@ class CudaSlabOps:
         return rgba
 
     # halo boxes <-> dense buffers
-    def pack_box(self, origin, extent):
-        buf = self.torch.empty((extent[2], extent[1], extent[0]), dtype=self.torch.uint8, device=self.cseg.device)
+    def pack_box(self, origin, extent, pad16=False):
+        if pad16:  # flat buffer rounded up to 16 bytes (peer puts move 16-byte words)
+            n = int(extent[0]) * int(extent[1]) * int(extent[2])
+            buf = self.torch.empty(((n + 15) // 16 * 16,), dtype=self.torch.uint8, device=self.cseg.device)
+        else:
+            buf = self.torch.empty((extent[2], extent[1], extent[0]), dtype=self.torch.uint8, device=self.cseg.device)
         check(lib.vr_volume_pack_box(self.ctx.h, self.vol.h, (c_int64 * 3)(*origin), (c_int64 * 3)(*extent), c_void_p(buf.data_ptr())))
         return buf
+
+    def unpack_box_ptr(self, origin, extent, dev_ptr):
+        check(lib.vr_volume_unpack_box(self.ctx.h, self.vol.h, (c_int64 * 3)(*origin), (c_int64 * 3)(*extent), c_void_p(int(dev_ptr))))
 
     def unpack_box(self, origin, extent, buf):
         assert buf.is_contiguous()
@@ -214,6 +221,167 @@ class TorchDistExchange:
         return out
 
 
+class _DevMem:
+    """Device memory owned by the library, exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class PeerExchange:
+    """The frame's exchange steps over peer memory (vr_peer_*, include/vr_b200.h): every rank owns a window that all
+    ranks of the node map; a step is ONE store kernel over NVLink plus a flag, the consumer waits on the device.
+    Same interface as TorchDistExchange (tensors in, tensors out), plus exchange_halos().
+
+    Window layout for P pixels and n ranks (bytes):  gather n*4P | stripes-in n*(16P/n) | total 16P | halo staging.
+    handles: callable(bytes64) -> list of the n ranks' 64-byte handles (e.g. an all-gather over torch.distributed);
+    None = raw mode, call open_raw() with the windows of same-process ranks."""
+
+    GATHER, RED_IN, RED_OUT, HALO = 0, 1, 2, 3
+
+    def __init__(self, ctx, rank, n, W, H, halo_bytes=0, handles=None):
+        import torch
+        self.torch, self.ctx, self.rank, self.n, self.P = torch, ctx, int(rank), int(n), int(W) * int(H)
+        P = self.P
+        assert (4 * P) % (16 * n) == 0, "image size must split into 16-byte aligned stripes"
+        self.off_gather = 0
+        self.off_red_in = self.off_gather + 4 * P * n
+        self.off_total = self.off_red_in + 16 * P          # n stripes of 16P/n bytes (largest payload: rgba float4)
+        self.off_halo = self.off_total + 16 * P
+        self.halo_bytes = (int(halo_bytes) + 15) // 16 * 16
+        self.bytes = self.off_halo + self.halo_bytes
+        self.h = c_void_p()
+        check(lib.vr_peer_create(ctx.h, self.rank, self.n, self.bytes, byref(self.h)))
+        self.device = torch.device("cuda", ctx.device if hasattr(ctx, "device") else torch.cuda.current_device())
+        self._scratch = {}
+        if handles is not None:
+            mine = (ctypes.c_uint8 * 64)()
+            check(lib.vr_peer_handle(self.h, mine))
+            allh = handles(bytes(mine))
+            blob = (ctypes.c_uint8 * (64 * self.n)).from_buffer_copy(b"".join(allh))
+            check(lib.vr_peer_open(self.h, blob))
+        self.base = None
+
+    def raw(self):
+        w = c_void_p()
+        check(lib.vr_peer_raw(self.h, byref(w)))
+        return w.value
+
+    def open_raw(self, windows):
+        check(lib.vr_peer_open_raw(self.h, (c_void_p * self.n)(*windows)))
+
+    def _base(self):
+        if self.base is None:
+            w = c_void_p()
+            check(lib.vr_peer_window(self.h, self.rank, byref(w)))
+            self.base = w.value
+        return self.base
+
+    def _view(self, off, shape, dtype):
+        ts = {self.torch.float32: "<f4", self.torch.int32: "<i4", self.torch.uint8: "|u1"}[dtype]
+        return self.torch.as_tensor(_DevMem(self._base() + off, shape, ts), device=self.device)
+
+    def _put(self, slot, copies):
+        k = len(copies)
+        check(lib.vr_peer_put(self.h, slot, k, (c_int32 * k)(*[c[0] for c in copies]), (c_int64 * k)(*[c[1] for c in copies]),
+                              (c_void_p * k)(*[c[2] for c in copies]), (c_int64 * k)(*[c[3] for c in copies])))
+
+    def _wait(self, slot, ranks):
+        check(lib.vr_peer_wait(self.h, slot, len(ranks), (c_int32 * len(ranks))(*ranks)))
+
+    # Every collective is a short sequence of stages; a stage never depends on a peer's work of the same stage, so
+    # same-process ranks can be driven stage by stage (render_frame_peer_lockstep) while one-process-per-GPU ranks
+    # simply run them back to back.
+    def stages(self, kind, t):
+        """Generator: runs one stage per next(); the last value is the collective's result."""
+        assert t.is_contiguous() and t.element_size() == 4
+        if kind == "all_gather":
+            assert t.numel() == self.P
+            nb = 4 * self.P
+            self._put(self.GATHER, [(r, self.off_gather + self.rank * nb, t.data_ptr(), nb) for r in range(self.n)])
+            yield None
+            self._wait(self.GATHER, list(range(self.n)))
+            yield self._view(self.off_gather, (self.n,) + tuple(t.shape), t.dtype)
+            return
+        # reduce-scatter + all-gather over the windows: rank j combines stripe j of every rank (fixed order), then
+        # stores the finished stripe into every window
+        op = {"all_reduce_sum": 0, "all_reduce_min": 1}[kind]
+        nbytes = t.numel() * 4
+        assert nbytes <= 16 * self.P and nbytes % (16 * self.n) == 0
+        sb = nbytes // self.n
+        base = t.data_ptr()
+        self._put(self.RED_IN, [(j, self.off_red_in + self.rank * sb, base + j * sb, sb) for j in range(self.n)])
+        yield None
+        self._wait(self.RED_IN, list(range(self.n)))
+        key = (sb, t.dtype)
+        if key not in self._scratch:
+            self._scratch[key] = self.torch.empty(sb // 4, dtype=t.dtype, device=t.device)
+        red = self._scratch[key]
+        ins = (c_void_p * self.n)(*[self._base() + self.off_red_in + k * sb for k in range(self.n)])
+        check(lib.vr_peer_reduce(self.h, op, self.n, ins, c_void_p(red.data_ptr()), sb // 4))
+        self._put(self.RED_OUT, [(r, self.off_total + self.rank * sb, red.data_ptr(), sb) for r in range(self.n)])
+        yield None
+        self._wait(self.RED_OUT, list(range(self.n)))
+        yield self._view(self.off_total, tuple(t.shape), t.dtype)
+
+    def _run(self, kind, t):
+        res = None
+        for res in self.stages(kind, t):
+            pass
+        return res
+
+    def all_gather(self, t):
+        return self._run("all_gather", t)
+
+    def all_reduce_sum(self, t):
+        return self._run("all_reduce_sum", t)
+
+    def all_reduce_min(self, t):
+        return self._run("all_reduce_min", t)
+
+    def exchange_halos(self, ops, descs, stored, defer_receive=False):
+        """Halo boxes: the owner packs a box and stores it into the staging area of the rank that needs it; that rank
+        waits on the device and unpacks into its slab (which also refreshes the occupancy of the box)."""
+        rank, my_o = self.rank, stored[self.rank][0]
+        offs = {}            # running staging offset per destination, identical on all ranks
+        copies, keep, recvs = [], [], []
+        for src, dst, lo, ext in halo_transfers(descs, stored):
+            nb = (int(ext[0]) * int(ext[1]) * int(ext[2]) + 15) // 16 * 16
+            o = offs.get(dst, 0)
+            offs[dst] = o + nb
+            assert o + nb <= self.halo_bytes, "halo staging area too small"
+            if src == rank:
+                buf = ops.pack_box([lo[a] - stored[src][0][a] for a in range(3)], ext, pad16=True)
+                keep.append(buf)
+                copies.append((dst, self.off_halo + o, buf.data_ptr(), nb))
+            elif dst == rank:
+                recvs.append((src, [lo[a] - my_o[a] for a in range(3)], ext, o))
+        if copies:
+            self._put(self.HALO, copies)
+        self._keep = keep  # until the next call: the put kernel reads them asynchronously
+        if defer_receive:
+            return recvs
+        self.receive_halos(ops, recvs)
+        return None
+
+    def receive_halos(self, ops, recvs):
+        if recvs:
+            self._wait(self.HALO, sorted({r[0] for r in recvs}))
+            for _, o3, ext, o in recvs:
+                ops.unpack_box_ptr(o3, ext, self._base() + self.off_halo + o)
+
+    def timed_out(self):
+        e = c_int32(0)
+        check(lib.vr_peer_error(self.h, byref(e)))
+        self.last_error = e.value
+        return bool(e.value)
+
+    def close(self):
+        if self.h:
+            lib.vr_peer_destroy(self.h)
+            self.h = c_void_p()
+
+
 def frame_steps(ops, params):
     """One sort-last frame of one rank as a coroutine: yields (collective, tensor) requests, receives the
     collective's result, returns the finished RGBA frame [H, W, 4] (row 0 = bottom row)."""
@@ -242,6 +410,34 @@ def render_frame(ops, exchange, params):
         return fin.value
 
 
+def render_frame_peer_lockstep(ops_list, ex_list, params):
+    """Virtual ranks of ONE process over PeerExchange windows: every collective is driven stage by stage over all
+    ranks, so no rank's device-side wait is queued before the put it waits for."""
+    gens = [frame_steps(o, params) for o in ops_list]
+    reqs = [next(g) for g in gens]
+    done = [None] * len(gens)
+    while any(d is None for d in done):
+        kind = reqs[0][0]
+        assert all(r[0] == kind for r in reqs)
+        st = [ex.stages(kind, r[1]) for ex, r in zip(ex_list, reqs)]
+        res = [None] * len(st)
+        alive = True
+        while alive:
+            alive = False
+            for i, g in enumerate(st):
+                try:
+                    res[i] = next(g)
+                    alive = True
+                except StopIteration:
+                    pass
+        for i, g in enumerate(gens):
+            try:
+                reqs[i] = g.send(res[i])
+            except StopIteration as fin:
+                done[i] = fin.value
+    return done
+
+
 def render_frame_lockstep(ops_list, params):
     """All ranks in ONE process (virtual ranks on one device, or CPU stand-ins): the collectives are done
     locally on the list of tensors.  Returns every rank's finished frame."""
@@ -253,6 +449,8 @@ def render_frame_lockstep(ops_list, params):
         kind = reqs[0][0]
         assert all(r[0] == kind for r in reqs)
         ts = [r[1] for r in reqs]
+        if ts[0].is_cuda:  # the ranks' kernels may run on streams of their own; the local collective runs on torch's
+            torch.cuda.synchronize()
         if kind == "all_gather":
             res = [torch.stack(ts).contiguous()] * len(ts)
         elif kind == "all_reduce_sum":
@@ -263,6 +461,8 @@ def render_frame_lockstep(ops_list, params):
             res = [tot.clone() for _ in ts]
         else:
             raise ValueError(kind)
+        if ts[0].is_cuda:
+            torch.cuda.synchronize()
         for i, g in enumerate(gens):
             try:
                 reqs[i] = g.send(res[i])
