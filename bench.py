@@ -152,7 +152,18 @@ def run_ours(args):
         origins = [(i * BX - so[0], rank * BY - so[1], k * BZ - so[2]) for (i, j, k) in bricks]
         sl = sortlast.SortLast(ctx, descs, rank)
         ops = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=True)
-        exch = sortlast.TorchDistExchange()
+        # exchange steps over peer memory (NVLink stores + flags, sortlast.PeerExchange); --exchange nccl = torch.distributed
+        peer = None
+        if args.exchange == "peer":
+            def gather_handles(mine):
+                allh = [None] * world
+                dist.all_gather_object(allh, mine)
+                return allh
+            peer = sortlast.PeerExchange(ctx, rank, world, IMG, IMG, halo_bytes=sortlast.halo_staging_bytes(descs, stored),
+                                         handles=gather_handles)
+            exch = peer
+        else:
+            exch = sortlast.TorchDistExchange()
     else:
         vol = vr.Volume(ctx, GI * BX, BY, GK * BZ)
         origins = [(i * BX, 0, k * BZ) for (i, j, k) in bricks]
@@ -166,7 +177,10 @@ def run_ours(args):
 
     def frame():
         if world > 1:
-            sortlast.exchange_halos(ops, descs, stored, rank)
+            if peer is not None:
+                peer.exchange_halos(ops, descs, stored)
+            else:
+                sortlast.exchange_halos(ops, descs, stored, rank)
             return sortlast.render_frame(ops, exch, p)
         render.render_device(ctx, vol, p, out.data_ptr())
         return out
@@ -498,6 +512,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="N > 1: sort-last exchange over peer-memory windows or NCCL")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of replaying a captured CUDA graph")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that print to fd 1 (NCCL's version banner, ...) are

@@ -1,5 +1,5 @@
 """TEST SCRIPT (launched by torchrun on >= 2 GPUs, see test_gpu_sortlast_nccl.py): the sort-last frame over
-real NCCL collectives, one process per GPU, against the single-texture oracle of the whole volume."""
+real NCCL collectives and over peer-memory windows, one process per GPU, against the single-texture oracle of the whole volume."""
 import os
 import sys
 
@@ -37,6 +37,25 @@ def main():
             torch.cuda.synchronize()
             assert np.array_equal(vol.download(), full[o[2]:o[2] + e[2], o[1]:o[1] + e[1], o[0]:o[0] + e[0]]), "halo exchange"
             got = sortlast.render_frame(ops, sortlast.TorchDistExchange(), p).cpu().numpy()
+            # the same frame with the exchange over peer-memory windows (CUDA IPC + NVLink stores + flags)
+            def gather_handles(mine):
+                allh = [None] * world
+                dist.all_gather_object(allh, mine)
+                return allh
+            peer = sortlast.PeerExchange(ctx, rank, world, W, H, halo_bytes=sortlast.halo_staging_bytes(descs, stored), handles=gather_handles)
+            vol.upload_brick(np.zeros((e[2], e[1], e[0]), np.uint8), (0, 0, 0))  # wipe the halo, exchange it again over the windows
+            vol.upload_brick(np.ascontiguousarray(full[lo[2]:hi[2], lo[1]:hi[1], lo[0]:hi[0]]), [lo[a] - o[a] for a in range(3)])
+            peer.exchange_halos(ops, descs, stored)
+            torch.cuda.synchronize()
+            assert np.array_equal(vol.download(), full[o[2]:o[2] + e[2], o[1]:o[1] + e[1], o[0]:o[0] + e[0]]), "halo exchange over peer windows"
+            for rep in range(3):
+                got_peer = sortlast.render_frame(ops, peer, p)
+                torch.cuda.synchronize()
+                assert not peer.timed_out(), hex(peer.last_error)
+                d = float(np.nanmax(np.abs(got_peer.cpu().numpy() - got)))
+                assert d <= (2e-6 if mode == render.COMPOSITE else 0.0), (rank, mode, rep, d)
+            dist.barrier()
+            peer.close()
             want, _, _ = oa.oracle_render(full, render.oracle_param_blob(p), 4)
             err = float(np.nanmax(np.abs(got - want)))
             worst = max(worst, err)

@@ -102,6 +102,14 @@ def halo_transfers(descs, stored):
     return out
 
 
+def halo_staging_bytes(descs, stored):
+    """Bytes of halo staging a PeerExchange window needs (the largest sum of incoming boxes over the ranks)."""
+    need = {}
+    for src, dst, lo, ext in halo_transfers(descs, stored):
+        need[dst] = need.get(dst, 0) + (int(ext[0]) * int(ext[1]) * int(ext[2]) + 15) // 16 * 16
+    return max(need.values()) if need else 0
+
+
 class SortLast:
     """vr_sortlast: the slab geometry of all ranks + the visibility orders, bound to one rank."""
 
