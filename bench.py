@@ -143,6 +143,7 @@ def run_ours(args):
         s.pin()
         s.upload(ctx)
     p = render.default_params(IMG, IMG, render.COMPOSITE)
+    peer = None
     if world > 1:
         from volumerenderer_b200 import sortlast
         G = (GI * BX, BY * world, GK * BZ)
@@ -153,7 +154,6 @@ def run_ours(args):
         sl = sortlast.SortLast(ctx, descs, rank)
         ops = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=True)
         # exchange steps over peer memory (NVLink stores + flags, sortlast.PeerExchange); --exchange nccl = torch.distributed
-        peer = None
         if args.exchange == "peer":
             def gather_handles(mine):
                 allh = [None] * world
@@ -179,8 +179,8 @@ def run_ours(args):
         if world > 1:
             if peer is not None:
                 peer.exchange_halos(ops, descs, stored)
-            else:
-                sortlast.exchange_halos(ops, descs, stored, rank)
+                return peer.render_frame(ops, p)  # composite passes fused with their exchange step
+            sortlast.exchange_halos(ops, descs, stored, rank)
             return sortlast.render_frame(ops, exch, p)
         render.render_device(ctx, vol, p, out.data_ptr())
         return out
@@ -218,10 +218,11 @@ def run_ours(args):
 
     # The step (decode launch, occupancy refresh, march / sort-last frame with its NCCL collectives) is
     # captured once into a CUDA graph and replayed: one host call per step instead of ~10-30.
-    # (N = 1 only: capturing the NCCL point-to-point halo exchange together with the collectives hung in
-    # this torch/NCCL combination, so multi-GPU steps are launched eagerly.)
+    # (N > 1: only with the peer-memory exchange, whose steps are plain kernels with device-side epoch counters;
+    # capturing the NCCL point-to-point halo exchange together with the collectives hung in this torch/NCCL
+    # combination, so --exchange nccl launches eagerly.)
     graph = None
-    if not args.no_graph and world == 1:
+    if not args.no_graph and (world == 1 or peer is not None):
         try:
             barrier()
             g = torch.cuda.CUDAGraph()
@@ -379,8 +380,10 @@ def run_ours(args):
                 "mode": "streaming: timesteps t=0/t=1 alternate, H2D of the next timestep overlaps decode+frame of the current",
                 "serial": {"value": voxels_all / serial_ms / 1e6, "ms_per_step": serial_ms,
                            "h2d_bytes_per_step": int(h2d_sets[0])}},
-        # own kernels per step: decode, 3 occupancy refresh, march (N > 1: partial, resolve, finish instead of march)
-        "cuda_graph": graph is not None, "gpu_launches": (5 if world == 1 else 7) * args.steps, "clocks": clocks, "setup_s": t_setup,
+        # own kernels per step: decode, 3 occupancy refresh, march; N > 1 over NCCL: partial, resolve, finish instead of march;
+        # N > 1 over peer windows (rank 0, one neighbour): decode, halo put + wait + box reduce, 3 occupancy, partial, gather put +
+        # wait, resolve, reduce-scatter put + wait + combine, all-gather put + wait, finish = 17
+        "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)

@@ -247,7 +247,7 @@ int vr_volume_unpack_box(vr_context* ctx, vr_volume* v, const int64_t origin[3],
  * MB between ranks that sit on one NVSwitch: as NCCL calls they cost 80-250 us each, mostly latency.  A vr_peer is a
  * window of device memory per rank that every other rank maps (CUDA IPC); data moves with ONE kernel per step that
  * stores straight into the destination windows over NVLink and then raises a flag there; the consumer waits on its own
- * flags with a one-warp kernel on its stream (bounded: a missing peer ends the wait after ~0.5 s and sets the error
+ * flags with a one-warp kernel on its stream (bounded: a missing peer ends the wait after ~1 s and sets the error
  * flag instead of hanging the GPU).  No host synchronisation, no staging copies, no NCCL on this path.
  * Protocol: every put to (dst, slot) is matched by one wait on (slot, src) at dst, in the same order on both sides. */
 typedef struct vr_peer vr_peer;
@@ -272,6 +272,22 @@ int vr_peer_wait(vr_peer* p, int32_t slot, int32_t count, const int32_t* src_ran
  * window), count a multiple of 4. */
 int vr_peer_reduce(vr_peer* p, int32_t op, int32_t n, const void* const* in, void* out, int64_t count);
 int vr_peer_error(vr_peer* p, int32_t* timed_out); /* synchronises the stream; 0 = fine, else 0x10000 | slot << 8 | source rank of a wait that expired */
+
+/* The composite passes of the sort-last frame FUSED with their exchange step: the march kernels store their per-pixel
+ * results straight into the windows of the ranks that need them and raise `slot` there from their last CTA (no staging
+ * buffers, no copy kernels).  Offsets are bytes inside the windows (16-byte aligned), identical on all ranks:
+ *   pass 1: T_seg of this rank -> every window at gather_off + rank * 4*W*H      (then vr_peer_wait(slot, all ranks))
+ *   pass 2: reads the n T_seg at gather_off of the own window; this rank's (C, A) term of pixel p goes to the owner of
+ *           p's stripe, j = p / (W*H/n): window j at red_off + rank * 8*W*H/n     (then wait)
+ *   pass 3: the stripe owner sums the n terms in rank order, applies the colour map of raycaster.frag:82-85 and stores
+ *           the RGBA stripe into every window at frame_off                        (then wait: frame_off holds the frame) */
+int vr_peer_partial_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_volume* slab,
+                              const vr_render_params* params, float* cseg_dev, int64_t gather_off, uint64_t* samples_dev);
+int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_volume* slab,
+                              const vr_render_params* params, int64_t gather_off, const float* cseg_dev, int64_t red_off,
+                              uint64_t* samples_dev);
+int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off,
+                             int64_t frame_off);
 
 #ifdef __cplusplus
 }

@@ -77,6 +77,16 @@ def test_frame_over_peer_windows(full, n, axis, mode):
                 assert torch.equal(frames[r], want[r]), (rep, r)
             else:  # the ranks' terms are summed in rank order here, in torch's reduction order in the lock-step frame
                 assert (frames[r] - want[r]).abs().max().item() <= 2e-6, (rep, r)
+    if mode == render.COMPOSITE:
+        # the exchange fused into the march kernels: same arithmetic as the staged peer frame, bit for bit
+        staged = [f.clone() for f in frames]
+        for rep in range(3):
+            fused = sortlast.render_frame_fused_lockstep(ops, ex, p)
+            for c in ctxs:
+                c.synchronize()
+            assert not any(e.timed_out() for e in ex), [hex(e.last_error) for e in ex]
+            for r in range(n):
+                assert torch.equal(fused[r], staged[r]), (rep, r)
     for e in ex:
         e.close()
     for c in ctxs:

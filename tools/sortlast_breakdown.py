@@ -25,7 +25,15 @@ so, se = stored[rank]
 vol = vr.Volume(ctx, *se).set_cell_origin(so)
 plan = vr.DecodePlan(ctx, streams, [(i * 256 - so[0], rank * 256 - so[1], k * 128 - so[2]) for (i, j, k) in bricks], vol)
 ops = sortlast.CudaSlabOps(ctx, sortlast.SortLast(ctx, descs, rank), vol, 1024, 1024, count_samples=False)
-exch = sortlast.TorchDistExchange()
+mode = sys.argv[2] if len(sys.argv) > 2 else "nccl"
+if mode == "peer":
+    def gather_handles(mine):
+        allh = [None] * world
+        dist.all_gather_object(allh, mine)
+        return allh
+    exch = sortlast.PeerExchange(ctx, rank, world, 1024, 1024, halo_bytes=sortlast.halo_staging_bytes(descs, stored), handles=gather_handles)
+else:
+    exch = sortlast.TorchDistExchange()
 
 def ev():
     e = torch.cuda.Event(enable_timing=True); e.record(); return e
@@ -37,7 +45,11 @@ for it in range(25):
     t0 = time.perf_counter()
     e = [ev()]
     plan.run(); e.append(ev())
-    sortlast.exchange_halos(ops, descs, stored, rank); e.append(ev())
+    if mode == "peer":
+        exch.exchange_halos(ops, descs, stored)
+    else:
+        sortlast.exchange_halos(ops, descs, stored, rank)
+    e.append(ev())
     cseg, tseg = ops.partial_composite(p); e.append(ev())
     ta = exch.all_gather(tseg); e.append(ev())
     c = ops.resolve_composite(p, ta, cseg); e.append(ev())
@@ -54,5 +66,5 @@ allr = [None] * world
 dist.all_gather_object(allr, res)
 if rank == 0:
     for r, x in enumerate(allr):
-        print(f"rank {r} view {view}: " + " ".join(f"{k}={v:.3f}" for k, v in x.items()))
+        print(f"rank {r} view {view} {mode}: " + " ".join(f"{k}={v:.3f}" for k, v in x.items()))
 dist.barrier(); dist.destroy_process_group()

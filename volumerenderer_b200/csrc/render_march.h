@@ -41,4 +41,26 @@ cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, fl
 // pass 2, isosurface: keep this rank's colour only where its hit is the frame's first hit (hitMin =
 // element-wise min over ranks); rank 0 supplies white where no rank hit.  Sum over ranks = the frame.
 cudaError_t resolve_iso_launch(int W, int H, int rank, const int* hitMine, const int* hitMin, float4* rgba, cudaStream_t stream);
+
+// ---- the same passes fused with their exchange step over peer-memory windows (vr_peer, include/vr_b200.h) --------
+// A kernel stores its per-pixel result straight into the windows of the ranks that need it (NVLink stores from the
+// compute kernel, no staging buffer, no copy kernel) and its last CTA raises the arrival flags.
+#define VR_MAX_PEERS 32
+struct PeerTargets {
+  uint8_t* base[VR_MAX_PEERS];    // every rank's window as mapped here
+  uint32_t* flag[VR_MAX_PEERS];   // arrival counter (slot, this rank) inside every rank's flag area
+  uint32_t* sent[VR_MAX_PEERS];   // this rank's count of signals to that rank on this slot (device-side epoch)
+  unsigned int* ticket;           // local CTA ticket
+  int n, rank;
+};
+// pass 1: T_seg of this rank -> window[r] + gatherOff + rank * 4 * W*H for every r; C_seg stays local
+cudaError_t partial_composite_peer_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float* cseg,
+                                          const PeerTargets& t, long long gatherOff, unsigned long long* sampleCount, cudaStream_t stream);
+// pass 2: this rank's (C, A) term of pixel p -> stripe owner j = p / (W*H/n): window[j] + redOff + rank * 8 * W*H/n
+cudaError_t resolve_composite_peer_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
+                                          const float* tsegAll, const int* order, const float* cseg, const PeerTargets& t,
+                                          long long redOff, unsigned long long* sampleCount, cudaStream_t stream);
+// pass 3 (stripe owner): sum of the n terms in rank order + colour map -> RGBA of the stripe into every window + frameOff
+cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff,
+                                         cudaStream_t stream);
 }  // namespace vr

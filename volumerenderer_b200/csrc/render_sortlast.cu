@@ -72,6 +72,21 @@ __device__ __forceinline__ void march_segment(const Vol& v, const OccView& occ, 
 }
 
 template <bool OCC>
+__device__ __forceinline__ void partial_pixel(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, int px, int py,
+                                              float* C, float* T, unsigned* n) {
+  float c = 0.0f, a = 0.0f;
+  V3 vUV;
+  if (ray_setup(P, px, py, &vUV)) {
+    Vol v = make_vol(g, vol);
+    V3 dir, dirStep;
+    ray_dir(P, vUV, &dir, &dirStep);
+    march_segment<OCC>(v, occ, vUV, dirStep, &c, &a, n);
+  }
+  *C = c;
+  *T = fsub(1.0f, a);
+}
+
+template <bool OCC>
 __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_constant__ RenderParams P,
                                                                 const __grid_constant__ SlabGeom g,
                                                                 const __grid_constant__ OccView occ,
@@ -81,18 +96,51 @@ __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_con
   int px, py;
   unsigned n = 0;
   if (pixel_of_thread(P, &px, &py)) {
-    float C = 0.0f, A = 0.0f;
-    V3 vUV;
-    if (ray_setup(P, px, py, &vUV)) {
-      Vol v = make_vol(g, vol);
-      V3 dir, dirStep;
-      ray_dir(P, vUV, &dir, &dirStep);
-      march_segment<OCC>(v, occ, vUV, dirStep, &C, &A, &n);
-    }
+    float C, T;
+    partial_pixel<OCC>(P, g, occ, vol, px, py, &C, &T, &n);
     cseg[(long long)py * P.W + px] = C;
-    tseg[(long long)py * P.W + px] = fsub(1.0f, A);
+    tseg[(long long)py * P.W + px] = T;
   }
   count_samples(sampleCount, n);
+}
+
+// Last CTA of the grid publishes: every CTA has fenced its stores (system scope: they go to peer memory) before it
+// takes a ticket, so whoever draws the last ticket knows all of them are visible before the flags are.
+__device__ __forceinline__ void peer_signal(const PeerTargets& t) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned total = gridDim.x * gridDim.y;
+    if (atomicAdd(t.ticket, 1u) == total - 1) {
+      *t.ticket = 0;
+      __threadfence_system();
+      for (int r = 0; r < t.n; ++r) {
+        const uint32_t v = *t.sent[r] + 1u;
+        *t.sent[r] = v;
+        *reinterpret_cast<volatile uint32_t*>(t.flag[r]) = v;
+      }
+    }
+  }
+}
+
+template <bool OCC>
+__global__ void __launch_bounds__(256) partial_composite_peer_kernel(const __grid_constant__ RenderParams P,
+                                                                     const __grid_constant__ SlabGeom g,
+                                                                     const __grid_constant__ OccView occ,
+                                                                     const uint8_t* __restrict__ vol, float* __restrict__ cseg,
+                                                                     const __grid_constant__ PeerTargets t, long long gatherOff,
+                                                                     unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    float C, T;
+    partial_pixel<OCC>(P, g, occ, vol, px, py, &C, &T, &n);
+    const long long pix = (long long)py * P.W + px, npix = (long long)P.W * P.H;
+    cseg[pix] = C;
+    for (int r = 0; r < t.n; ++r) reinterpret_cast<float*>(t.base[r] + gatherOff)[(long long)t.rank * npix + pix] = T;
+  }
+  count_samples(sampleCount, n);
+  peer_signal(t);
 }
 
 template <bool OCC>
@@ -150,16 +198,9 @@ __global__ void __launch_bounds__(256) partial_iso_kernel(const __grid_constant_
 }
 
 template <bool OCC>
-__global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_constant__ RenderParams P,
-                                                                const __grid_constant__ SlabGeom g,
-                                                                const __grid_constant__ OccView occ,
-                                                                const uint8_t* __restrict__ vol, const float* __restrict__ tsegAll,
-                                                                int nRanks, int rank, const int* __restrict__ order,
-                                                                const float* __restrict__ cseg, float2* __restrict__ contrib,
-                                                                unsigned long long* __restrict__ sampleCount) {
-  int px, py;
-  unsigned n = 0;
-  if (pixel_of_thread(P, &px, &py)) {
+__device__ __forceinline__ float2 resolve_pixel(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* __restrict__ vol,
+                                                const float* __restrict__ tsegAll, int nRanks, int rank, const int* __restrict__ order,
+                                                const float* __restrict__ cseg, int px, int py, unsigned& n) {
     const long long pix = (long long)py * P.W + px, npix = (long long)P.W * P.H;
     float2 term = make_float2(0.0f, 0.0f);
     V3 vUV;
@@ -194,9 +235,64 @@ __global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_con
         if (crossPos < 0 && myPos == nRanks - 1) term.y = fsub(1.0f, T);  // no termination anywhere: last slab closes alpha
       }
     }
-    contrib[pix] = term;
+    return term;
+}
+
+template <bool OCC>
+__global__ void __launch_bounds__(256) resolve_composite_kernel(const __grid_constant__ RenderParams P,
+                                                                const __grid_constant__ SlabGeom g,
+                                                                const __grid_constant__ OccView occ,
+                                                                const uint8_t* __restrict__ vol, const float* __restrict__ tsegAll,
+                                                                int nRanks, int rank, const int* __restrict__ order,
+                                                                const float* __restrict__ cseg, float2* __restrict__ contrib,
+                                                                unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) contrib[(long long)py * P.W + px] = resolve_pixel<OCC>(P, g, occ, vol, tsegAll, nRanks, rank, order, cseg, px, py, n);
+  count_samples(sampleCount, n);
+}
+
+template <bool OCC>
+__global__ void __launch_bounds__(256) resolve_composite_peer_kernel(const __grid_constant__ RenderParams P,
+                                                                     const __grid_constant__ SlabGeom g,
+                                                                     const __grid_constant__ OccView occ,
+                                                                     const uint8_t* __restrict__ vol, const float* __restrict__ tsegAll,
+                                                                     const int* __restrict__ order, const float* __restrict__ cseg,
+                                                                     const __grid_constant__ PeerTargets t, long long redOff,
+                                                                     unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    const float2 term = resolve_pixel<OCC>(P, g, occ, vol, tsegAll, t.n, t.rank, order, cseg, px, py, n);
+    const long long pix = (long long)py * P.W + px, stripe = ((long long)P.W * P.H) / t.n;
+    const long long j = pix / stripe;  // owner of the pixel's stripe
+    reinterpret_cast<float2*>(t.base[j] + redOff)[(long long)t.rank * stripe + (pix - j * stripe)] = term;
   }
   count_samples(sampleCount, n);
+  peer_signal(t);
+}
+
+// One thread per pixel of this rank's stripe: the ranks' terms in rank order, then the colour map (finish_composite_kernel).
+__global__ void __launch_bounds__(256) finish_composite_peer_kernel(const __grid_constant__ RenderParams P,
+                                                                    const __grid_constant__ PeerTargets t, long long redOff, long long frameOff) {
+  const long long stripe = ((long long)P.W * P.H) / t.n;
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < stripe) {
+    const float2* in = reinterpret_cast<const float2*>(t.base[t.rank] + redOff);
+    float2 s = in[k];
+    for (int r = 1; r < t.n; ++r) {
+      const float2 b = in[(long long)r * stripe + k];
+      s.x = fadd(s.x, b.x);
+      s.y = fadd(s.y, b.y);
+    }
+    const long long pix = (long long)t.rank * stripe + k;
+    float4 rgba = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    V3 vUV;
+    if (ray_setup(P, (int)(pix % P.W), (int)(pix / P.W), &vUV))
+      rgba = make_float4(clamp01(fsub(1.0f, s.x)), clamp01(fsub(1.0f, s.x)), 1.0f, clamp01(s.y));
+    for (int r = 0; r < t.n; ++r) reinterpret_cast<float4*>(t.base[r] + frameOff)[pix] = rgba;
+  }
+  peer_signal(t);
 }
 
 __global__ void __launch_bounds__(256) finish_composite_kernel(const __grid_constant__ RenderParams P,
@@ -248,6 +344,25 @@ cudaError_t resolve_composite_launch(const RenderParams& P, const SlabGeom& g, c
                                      unsigned long long* sampleCount, cudaStream_t stream) {
   if (occ.pyr) resolve_composite_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
   else resolve_composite_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, n, rank, order, cseg, contrib, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t partial_composite_peer_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, float* cseg,
+                                          const PeerTargets& t, long long gatherOff, unsigned long long* sampleCount, cudaStream_t stream) {
+  if (occ.pyr) partial_composite_peer_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, t, gatherOff, sampleCount);
+  else partial_composite_peer_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, cseg, t, gatherOff, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t resolve_composite_peer_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
+                                          const float* tsegAll, const int* order, const float* cseg, const PeerTargets& t,
+                                          long long redOff, unsigned long long* sampleCount, cudaStream_t stream) {
+  if (occ.pyr) resolve_composite_peer_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, order, cseg, t, redOff, sampleCount);
+  else resolve_composite_peer_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, order, cseg, t, redOff, sampleCount);
+  return cudaGetLastError();
+}
+cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff,
+                                         cudaStream_t stream) {
+  const long long stripe = ((long long)P.W * P.H) / t.n;
+  finish_composite_peer_kernel<<<dim3((unsigned)((stripe + 255) / 256), 1), 256, 0, stream>>>(P, t, redOff, frameOff);
   return cudaGetLastError();
 }
 cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, float4* out, cudaStream_t stream) {

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../../include/vr_b200.h"
+#include "render_march.h"
 #include "vr_internal.h"
 
 using namespace vr;
@@ -15,16 +16,22 @@ using namespace vr;
 namespace {
 
 constexpr int MAX_PEERS = 32;
-constexpr int FLAG_BYTES = 4096;  // [VR_PEER_SLOTS][MAX_PEERS] uint32 counters, then error word and tickets
-constexpr int ERR_WORD = VR_PEER_SLOTS * MAX_PEERS;
+// Flag area behind every window (uint32 words): [slot][src] arrival counters written by the peers, then this rank's own
+// bookkeeping: puts issued per (slot, dst), waits issued per (slot, src), error word, ticket.  All counters live on
+// the device and are advanced by the kernels themselves, so a captured CUDA graph of a step can be replayed.
+constexpr int FLAG_BYTES = 4096;
+constexpr int SENT_WORD = VR_PEER_SLOTS * MAX_PEERS;
+constexpr int SEEN_WORD = 2 * VR_PEER_SLOTS * MAX_PEERS;
+constexpr int ERR_WORD = 3 * VR_PEER_SLOTS * MAX_PEERS;
 constexpr int TICKET_WORD = ERR_WORD + 1;
+static_assert((TICKET_WORD + 1) * 4 <= FLAG_BYTES, "flag area");
 
 struct PutParams {
   uint8_t* dst[MAX_PEERS];
   const uint8_t* src[MAX_PEERS];
   int64_t bytes[MAX_PEERS];
   uint32_t* flag[MAX_PEERS];  // one per distinct destination
-  uint32_t flagVal[MAX_PEERS];
+  uint32_t* sent[MAX_PEERS];  // local counter of puts to that destination on this slot
   int count, nFlags, ctasPerCopy;
   unsigned int* ticket;  // local
 };
@@ -43,14 +50,18 @@ __global__ void __launch_bounds__(256) peer_put_kernel(const __grid_constant__ P
     if (t == gridDim.x - 1) {  // every CTA has stored and fenced: publish
       *p.ticket = 0;
       __threadfence_system();
-      for (int f = 0; f < p.nFlags; ++f) *reinterpret_cast<volatile uint32_t*>(p.flag[f]) = p.flagVal[f];
+      for (int f = 0; f < p.nFlags; ++f) {
+        const uint32_t v = *p.sent[f] + 1u;
+        *p.sent[f] = v;
+        *reinterpret_cast<volatile uint32_t*>(p.flag[f]) = v;
+      }
     }
   }
 }
 
 struct WaitParams {
   const uint32_t* flag[MAX_PEERS];  // in this rank's own window
-  uint32_t want[MAX_PEERS];
+  uint32_t* seen[MAX_PEERS];        // local counter of waits on that source and slot
   int src[MAX_PEERS];
   int count, slot;
   unsigned int* err;
@@ -59,7 +70,8 @@ struct WaitParams {
 __global__ void peer_wait_kernel(const __grid_constant__ WaitParams p) {
   if ((int)threadIdx.x < p.count) {
     const volatile uint32_t* f = p.flag[threadIdx.x];
-    const uint32_t want = p.want[threadIdx.x];
+    const uint32_t want = *p.seen[threadIdx.x] + 1u;
+    *p.seen[threadIdx.x] = want;
     const long long t0 = clock64();
     while ((int32_t)(*f - want) < 0) {
       if (clock64() - t0 > p.limit) { atomicExch(p.err, 0x10000u | ((unsigned)p.slot << 8) | (unsigned)p.src[threadIdx.x]); break; }  // which wait expired
@@ -105,11 +117,27 @@ struct vr_peer {
   uint8_t* mapped[MAX_PEERS] = {};
   bool ipc[MAX_PEERS] = {};
   bool opened = false;
-  uint32_t sent[VR_PEER_SLOTS][MAX_PEERS] = {};  // puts issued to (slot, dst)
-  uint32_t seen[VR_PEER_SLOTS][MAX_PEERS] = {};  // waits issued on (slot, src)
-  long long limit = 1000000000LL;
+  long long limit = 2000000000LL;
   uint32_t* flags_of(int r) const { return reinterpret_cast<uint32_t*>(mapped[r] + windowBytes); }
 };
+
+namespace vr {
+int peer_targets(vr_peer* p, int slot, PeerTargets* t, int64_t* windowBytes) {
+  if (!p || !t || slot < 0 || slot >= VR_PEER_SLOTS) return fail(VR_ERR_ARG, "peer_targets: bad argument");
+  if (!p->opened) return fail(VR_ERR_STATE, "peer windows not opened");
+  static_assert(VR_MAX_PEERS == MAX_PEERS, "peer table size");
+  std::memset(t, 0, sizeof(*t));
+  t->n = p->n; t->rank = p->rank;
+  for (int r = 0; r < p->n; ++r) {
+    t->base[r] = p->mapped[r];
+    t->flag[r] = p->flags_of(r) + slot * MAX_PEERS + p->rank;
+    t->sent[r] = p->flags_of(p->rank) + SENT_WORD + slot * MAX_PEERS + r;
+  }
+  t->ticket = reinterpret_cast<unsigned int*>(p->flags_of(p->rank) + TICKET_WORD);
+  if (windowBytes) *windowBytes = p->windowBytes;
+  return VR_OK;
+}
+}  // namespace vr
 
 extern "C" {
 
@@ -123,7 +151,7 @@ int vr_peer_create(vr_context* ctx, int32_t rank, int32_t n, int64_t window_byte
   if (e == cudaSuccess) e = cudaMemset(p->window + window_bytes, 0, FLAG_BYTES);
   if (e != cudaSuccess) { cudaFree(p->window); delete p; return fail_cuda(e, "vr_peer_create"); }
   int khz = 0;
-  if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) == cudaSuccess && khz > 0) p->limit = (long long)khz * 500;  // 0.5 s
+  if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) == cudaSuccess && khz > 0) p->limit = (long long)khz * 1000;  // 1 s
   p->mapped[rank] = p->window;
   *out = p;
   return VR_OK;
@@ -209,7 +237,7 @@ int vr_peer_put(vr_peer* p, int32_t slot, int32_t count, const int32_t* dst_rank
     if (!flagged[d]) {
       flagged[d] = true;
       q.flag[q.nFlags] = p->flags_of(d) + slot * MAX_PEERS + p->rank;
-      q.flagVal[q.nFlags] = ++p->sent[slot][d];
+      q.sent[q.nFlags] = p->flags_of(p->rank) + SENT_WORD + slot * MAX_PEERS + d;
       ++q.nFlags;
     }
   }
@@ -235,7 +263,7 @@ int vr_peer_wait(vr_peer* p, int32_t slot, int32_t count, const int32_t* src_ran
     const int s = src_rank[k];
     if (s < 0 || s >= p->n) return fail(VR_ERR_ARG, "vr_peer_wait: bad rank");
     q.flag[k] = p->flags_of(p->rank) + slot * MAX_PEERS + s;
-    q.want[k] = ++p->seen[slot][s];
+    q.seen[k] = p->flags_of(p->rank) + SEEN_WORD + slot * MAX_PEERS + s;
     q.src[k] = s;
   }
   q.slot = slot;

@@ -201,4 +201,52 @@ int vr_volume_unpack_box(vr_context* ctx, vr_volume* v, const int64_t origin[3],
   return box_copy(ctx, v, origin, extent, const_cast<uint8_t*>(src), false);
 }
 
+// ---- composite passes fused with their exchange step over peer windows (render_march.h, PeerTargets) --------------
+int vr_peer_partial_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_volume* slab,
+                              const vr_render_params* params, float* cseg, int64_t gather_off, uint64_t* samples) {
+  if (!cseg || !peer) return fail(VR_ERR_ARG, "null argument");
+  SL_PROLOGUE(true)
+  PeerTargets t;
+  int64_t wb = 0;
+  { int rc_ = peer_targets(peer, slot, &t, &wb); if (rc_ != VR_OK) return rc_; }
+  const int64_t npix = (int64_t)P.W * P.H;
+  if (t.n != sl->n || t.rank != sl->rank || gather_off < 0 || (gather_off & 15) || gather_off + 4 * npix * t.n > wb)
+    return fail(VR_ERR_ARG, "vr_peer_partial_composite: window too small or ranks differ");
+  CU(partial_composite_peer_launch(P, g, occ, slab->dev, cseg, t, gather_off, reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
+int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_volume* slab,
+                              const vr_render_params* params, int64_t gather_off, const float* cseg, int64_t red_off, uint64_t* samples) {
+  if (!cseg || !peer) return fail(VR_ERR_ARG, "null argument");
+  SL_PROLOGUE(true)
+  { int rc_ = order_on_device(ctx, const_cast<vr_sortlast*>(sl)); if (rc_ != VR_OK) return rc_; }
+  PeerTargets t;
+  int64_t wb = 0;
+  { int rc_ = peer_targets(peer, slot, &t, &wb); if (rc_ != VR_OK) return rc_; }
+  const int64_t npix = (int64_t)P.W * P.H;
+  if (t.n != sl->n || t.rank != sl->rank || npix % t.n || ((8 * npix / t.n) & 15) || gather_off < 0 || red_off < 0 || (red_off & 15) ||
+      gather_off + 4 * npix * t.n > wb || red_off + 8 * npix > wb)
+    return fail(VR_ERR_ARG, "vr_peer_resolve_composite: window too small, ranks differ or image not divisible into stripes");
+  const float* tsegAll = reinterpret_cast<const float*>(t.base[t.rank] + gather_off);
+  CU(resolve_composite_peer_launch(P, g, occ, slab->dev, tsegAll, sl->orderDev, cseg, t, red_off,
+                                   reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
+int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off, int64_t frame_off) {
+  if (!ctx || !peer || !params) return fail(VR_ERR_ARG, "null argument");
+  RenderParams P;
+  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  CU(cudaSetDevice(ctx->device));
+  PeerTargets t;
+  int64_t wb = 0;
+  { int rc_ = peer_targets(peer, slot, &t, &wb); if (rc_ != VR_OK) return rc_; }
+  const int64_t npix = (int64_t)P.W * P.H;
+  if (npix % t.n || red_off < 0 || frame_off < 0 || (frame_off & 15) || red_off + 8 * npix > wb || frame_off + 16 * npix > wb)
+    return fail(VR_ERR_ARG, "vr_peer_finish_composite: window too small or image not divisible into stripes");
+  CU(finish_composite_peer_launch(P, t, red_off, frame_off, ctx->stream));
+  return VR_OK;
+}
+
 }  // extern "C"

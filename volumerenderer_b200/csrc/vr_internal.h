@@ -8,6 +8,8 @@
 
 namespace vr { struct KdBuilder; void kd_builder_destroy(KdBuilder*); }
 
+struct vr_peer;
+
 struct vr_context {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -76,6 +78,9 @@ int fail_cuda(cudaError_t e, const char* where);
 int stream_build_image(vr_stream* s);  // prepare + pack host image
 int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out);
 struct OccView;
+struct PeerTargets;
+// fills t for a fused kernel that signals `slot` at every rank (vr_capi_peer.cu); windowBytes = usable window size
+int peer_targets(struct ::vr_peer* p, int slot, PeerTargets* t, int64_t* windowBytes);
 int volume_occ_alloc(vr_volume* v);                       // allocate the grids for the current cellOrigin
 int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out);  // build / refresh as needed; out->dil = null when off
 void volume_occ_written(vr_context* ctx, vr_volume* v, const int64_t lo[3], const int64_t ext[3]);  // a box of voxels was overwritten

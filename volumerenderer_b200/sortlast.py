@@ -347,6 +347,34 @@ class PeerExchange:
     def all_reduce_min(self, t):
         return self._run("all_reduce_min", t)
 
+    def frame_stages(self, ops, params):
+        """One COMPOSITE frame with the exchange fused into the march kernels (vr_peer_*_composite): three compute
+        kernels that store into the peers' windows, three device-side waits.  Generator like stages(); the last value
+        is the finished frame [H, W, 4] (a view of this rank's window)."""
+        assert params.mode == COMPOSITE
+        everyone = list(range(self.n))
+        check(lib.vr_peer_partial_composite(self.ctx.h, self.h, self.GATHER, ops.sl.h, ops.vol.h, byref(params),
+                                            c_void_p(ops.cseg.data_ptr()), self.off_gather, ops._cnt()))
+        yield None
+        self._wait(self.GATHER, everyone)
+        check(lib.vr_peer_resolve_composite(self.ctx.h, self.h, self.RED_IN, ops.sl.h, ops.vol.h, byref(params), self.off_gather,
+                                            c_void_p(ops.cseg.data_ptr()), self.off_red_in, ops._cnt()))
+        yield None
+        self._wait(self.RED_IN, everyone)
+        check(lib.vr_peer_finish_composite(self.ctx.h, self.h, self.RED_OUT, byref(params), self.off_red_in, self.off_total))
+        yield None
+        self._wait(self.RED_OUT, everyone)
+        yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
+
+    def render_frame(self, ops, params):
+        """The frame of one rank (one process per GPU): fused path for COMPOSITE, staged collectives for ISOSURFACE."""
+        if params.mode != COMPOSITE:
+            return render_frame(ops, self, params)
+        res = None
+        for res in self.frame_stages(ops, params):
+            pass
+        return res
+
     def exchange_halos(self, ops, descs, stored, defer_receive=False):
         """Halo boxes: the owner packs a box and stores it into the staging area of the rank that needs it; that rank
         waits on the device and unpacks into its slab (which also refreshes the occupancy of the box)."""
@@ -444,6 +472,22 @@ def render_frame_peer_lockstep(ops_list, ex_list, params):
             except StopIteration as fin:
                 done[i] = fin.value
     return done
+
+
+def render_frame_fused_lockstep(ops_list, ex_list, params):
+    """Virtual ranks of one process: PeerExchange.frame_stages of all ranks, stage by stage."""
+    st = [ex.frame_stages(o, params) for ex, o in zip(ex_list, ops_list)]
+    res = [None] * len(st)
+    alive = True
+    while alive:
+        alive = False
+        for i, g in enumerate(st):
+            try:
+                res[i] = next(g)
+                alive = True
+            except StopIteration:
+                pass
+    return res
 
 
 def render_frame_lockstep(ops_list, params):
