@@ -154,7 +154,7 @@ def run_ours(args):
         sl = sortlast.SortLast(ctx, descs, rank)
         ops = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=True)
         # exchange steps over peer memory (NVLink stores + flags, sortlast.PeerExchange); --exchange nccl = torch.distributed
-        if args.exchange == "peer":
+        if args.exchange in ("peer", "peer-fused"):
             def gather_handles(mine):
                 allh = [None] * world
                 dist.all_gather_object(allh, mine)
@@ -179,7 +179,7 @@ def run_ours(args):
         if world > 1:
             if peer is not None:
                 peer.exchange_halos(ops, descs, stored)
-                return peer.render_frame(ops, p)  # composite passes fused with their exchange step
+                return peer.render_frame(ops, p, fused=args.exchange == "peer-fused")
             sortlast.exchange_halos(ops, descs, stored, rank)
             return sortlast.render_frame(ops, exch, p)
         render.render_device(ctx, vol, p, out.data_ptr())
@@ -515,7 +515,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="N > 1: sort-last exchange over peer-memory windows or NCCL")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "peer-fused", "nccl"],
+                    help="N > 1: sort-last exchange over peer-memory windows (copy kernels, or fused into the march kernels) or NCCL")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of replaying a captured CUDA graph")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that print to fd 1 (NCCL's version banner, ...) are

@@ -50,7 +50,7 @@ def main():
             assert np.array_equal(vol.download(), full[o[2]:o[2] + e[2], o[1]:o[1] + e[1], o[0]:o[0] + e[0]]), "halo exchange over peer windows"
             for rep in range(4):
                 # staged collectives over the windows, then (composite) the passes fused with their exchange step
-                got_peer = sortlast.render_frame(ops, peer, p) if rep < 2 else peer.render_frame(ops, p)
+                got_peer = peer.render_frame(ops, p, fused=rep >= 2)
                 torch.cuda.synchronize()
                 assert not peer.timed_out(), hex(peer.last_error)
                 d = float(np.nanmax(np.abs(got_peer.cpu().numpy() - got)))
