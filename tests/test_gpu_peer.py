@@ -80,8 +80,8 @@ def test_frame_over_peer_windows(full, n, axis, mode):
     if mode == render.COMPOSITE:
         # the exchange fused into the march kernels: same arithmetic as the staged peer frame, bit for bit
         staged = [f.clone() for f in frames]
-        for rep in range(3):
-            fused = sortlast.render_frame_fused_lockstep(ops, ex, p)
+        for rep in range(4):
+            fused = sortlast.render_frame_fused_lockstep(ops, ex, p, hybrid=rep % 2 == 1)
             for c in ctxs:
                 c.synchronize()
             assert not any(e.timed_out() for e in ex), [hex(e.last_error) for e in ex]

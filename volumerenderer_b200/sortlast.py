@@ -366,15 +366,36 @@ class PeerExchange:
         self._wait(self.RED_OUT, everyone)
         yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
 
+    def frame_stages_hybrid(self, ops, params):
+        """COMPOSITE frame, the default: plain march kernels, the two image-sized hand-overs as coalesced copy kernels
+        into the peers' windows, and the last pass (sum of the ranks' terms + colour map) as ONE kernel that stores the
+        finished stripe into every window: 3 compute + 2 copy + 3 wait launches."""
+        assert params.mode == COMPOSITE
+        everyone = list(range(self.n))
+        cseg, tseg = ops.partial_composite(params)
+        nb = 4 * self.P
+        self._put(self.GATHER, [(r, self.off_gather + self.rank * nb, tseg.data_ptr(), nb) for r in everyone])
+        yield None
+        self._wait(self.GATHER, everyone)
+        contrib = ops.resolve_composite(params, self._view(self.off_gather, (self.n,) + tuple(tseg.shape), tseg.dtype), cseg)
+        sb = 8 * self.P // self.n
+        self._put(self.RED_IN, [(j, self.off_red_in + self.rank * sb, contrib.data_ptr() + j * sb, sb) for j in everyone])
+        yield None
+        self._wait(self.RED_IN, everyone)
+        check(lib.vr_peer_finish_composite(self.ctx.h, self.h, self.RED_OUT, byref(params), self.off_red_in, self.off_total))
+        yield None
+        self._wait(self.RED_OUT, everyone)
+        yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
+
     def render_frame(self, ops, params, fused=False):
         """The frame of one rank (one process per GPU).  fused=True (COMPOSITE only) lets the march kernels store into
         the peers' windows themselves; measured slower than the staged copies on 2 x B200 (0.334 vs 0.287 ms per
         1024^2 frame: 32-byte stores in the 8x4 pixel-tile order and a system-scope fence per CTA inside the compute
         kernels cost more than the separate coalesced copy kernel), so the staged exchange is the default."""
-        if params.mode != COMPOSITE or not fused:
+        if params.mode != COMPOSITE:
             return render_frame(ops, self, params)
         res = None
-        for res in self.frame_stages(ops, params):
+        for res in (self.frame_stages(ops, params) if fused else self.frame_stages_hybrid(ops, params)):
             pass
         return res
 
@@ -477,9 +498,9 @@ def render_frame_peer_lockstep(ops_list, ex_list, params):
     return done
 
 
-def render_frame_fused_lockstep(ops_list, ex_list, params):
-    """Virtual ranks of one process: PeerExchange.frame_stages of all ranks, stage by stage."""
-    st = [ex.frame_stages(o, params) for ex, o in zip(ex_list, ops_list)]
+def render_frame_fused_lockstep(ops_list, ex_list, params, hybrid=False):
+    """Virtual ranks of one process: PeerExchange.frame_stages (or frame_stages_hybrid) of all ranks, stage by stage."""
+    st = [(ex.frame_stages_hybrid if hybrid else ex.frame_stages)(o, params) for ex, o in zip(ex_list, ops_list)]
     res = [None] * len(st)
     alive = True
     while alive:
