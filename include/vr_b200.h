@@ -197,6 +197,30 @@ int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_par
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
                          int32_t* hit_dev, uint64_t* samples_dev);
 
+/* Compressed-domain frame with a view-dependent ("lazy") decode -- the intent behind the reference's stub
+ * isosurface_compressed.frag:23-29 (`node{idx, boundMin, boundMax, scalarMin, scalarMax}`) and the never-enabled
+ * stream-as-SSBO path of main.cpp:203-237.  The stream index carries the exact maximum of every
+ * 32x32x16 tile (vr_stream_tile_bounds), so before anything is decoded the library knows which tiles a frame of
+ * `params` can read: the march skips every lattice position whose occupancy cell is void for the mode's threshold
+ * (composite: maximum 0; isosurface: maximum below isoValue), and what it reads otherwise lies within a fixed reach
+ * of a non-void cell (csrc/kd_cull.h).  Only those tiles are decoded; the others are not written at all and only their
+ * maxima enter the occupancy grid.  The frame is bit-identical to vr_render_compressed.  Afterwards the destination
+ * volume is PARTIAL (valid where this frame could read): vr_render on it fails with VR_ERR_STATE until
+ * vr_decode_plan_run has decoded the plan in full again.  The culled work list is cached in the plan per
+ * (threshold, step_size).  stats (optional): [0] tiles of the plan, [1] tiles written, [2] voxel bytes written,
+ * [3] stream bytes read. */
+int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
+                              int32_t* hit_dev, uint64_t* samples_dev, int64_t stats[4]);
+/* Host-only view of the same decision (no device needed): needed_out[b * tiles + t] = 1 iff a frame of `params` over a
+ * volume of dims[] can read tile t of brick b placed at origins[3b..] (multiples of the 32x32x16 cell).
+ * tile_boxes_out (optional) = voxel origin of every tile in the volume, 3 int32 per tile; tiles_per_brick (optional).
+ * needed_out may be NULL to query tiles_per_brick only. */
+int vr_lazy_tile_mask(vr_stream* const* streams, int32_t n, const int64_t* origins, const int64_t dims[3], const vr_render_params* params,
+                      uint8_t* needed_out, int32_t* tile_boxes_out, int32_t* tiles_per_brick);
+/* Exact minimum / maximum of the voxels levelCut would produce in every decode tile, read off the stream index
+ * (implies prepare; nothing is decoded).  2^Dt entries each in tile (kd path) order; tile_dims (optional) = tile extent. */
+int vr_stream_tile_bounds(vr_stream* s, uint8_t* mins, uint8_t* maxs, int64_t cap, int32_t tile_dims[3]);
+
 /* ---- sort-last rendering of a volume sharded over GPUs (no counterpart in the reference, which
  * renders one texture on one GPU, main.cpp:290,404) ------------------------------------
  * One process per GPU; rank r holds a box of the whole texture (its bricks, decoded in place, plus a

@@ -60,6 +60,12 @@ typedef struct vr_fill_job {
   int64_t occCell;   // occupancy cell of the first tile (members follow at +1), < 0 = none
 } vr_fill_job;
 
+// A tile the lazy decode leaves out (kd_cull.h): its occupancy cell and the exact maximum of its voxels.
+typedef struct vr_occ_set {
+  int64_t cell;
+  int64_t value;
+} vr_occ_set;
+
 // Sequential 2-bit reader over 32-bit words; always holds >= 32 valid bits after a refill.
 struct VrBitReader {
   const uint32_t* w;

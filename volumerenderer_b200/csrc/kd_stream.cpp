@@ -76,6 +76,8 @@ int kd_save(const KdStream& s, const char* path) {
 // Grammar walk.  A node at height h (= D0 - depth) starts at voxel path index v with v % 2^h == 0;
 // after a subtree ends, the next node's height is ctz(v).  Visitor hooks:
 //   node(pos, depth, h, v, code, value)  every tree node at depth <= D0 (not chain symbols)
+//   leaf(v, h, value)                    every decoded box: 2^h voxels from path index v take `value` (what levelCut
+//                                        writes at VolumeKdTree_recover.cpp:759-766), chains already applied
 //   done_item(v, endPos)                 after a depth-D0 item (voxel + chain) was consumed
 template <typename V>
 static int walk(const KdStream& s, V& vis, int64_t* consumed) {
@@ -98,6 +100,7 @@ static int walk(const KdStream& s, V& vis, int64_t* consumed) {
     vis.node(pos, depth, h, v, c, val);
     ++pos;
     if (c == 3) {
+      vis.leaf(v, h, val);
       v += uint64_t(1) << h;
     } else if (h > 0) {
       vals[h] = val;
@@ -111,6 +114,7 @@ static int walk(const KdStream& s, V& vis, int64_t* consumed) {
         if (ck == 3) break;
         val = vr_apply(val, ck, dm[D0 + k]);
       }
+      vis.leaf(v, 0, val);
       v += 1;
     }
     if (v == total) break;
@@ -123,6 +127,7 @@ static int walk(const KdStream& s, V& vis, int64_t* consumed) {
 namespace {
 struct CountVisitor {
   void node(int64_t, int, int, uint64_t, int, int) {}
+  void leaf(uint64_t, int, int) {}
 };
 
 struct IndexVisitor {
@@ -160,6 +165,13 @@ struct IndexVisitor {
       ix.leafVal[base + (inTile >> g.leafBits)] = (uint8_t)val;
     }
   }
+  void leaf(uint64_t v, int h, int val) {  // exact bounds of the decoded voxels per tile (kd_cull.h)
+    const uint64_t t0 = v >> g.tileBits, cnt = h > g.tileBits ? uint64_t(1) << (h - g.tileBits) : 1;
+    for (uint64_t t = t0; t < t0 + cnt; ++t) {
+      if (val > ix.tileMax[t]) ix.tileMax[t] = (uint8_t)val;
+      if (val < ix.tileMin[t]) ix.tileMin[t] = (uint8_t)val;
+    }
+  }
 };
 }  // namespace
 
@@ -177,6 +189,8 @@ int kd_prepare(KdStream* s) {
   uint64_t nTiles = uint64_t(1) << g.Dt;
   ix.tileLeafBlock.assign(nTiles, VR_PRUNED);
   ix.tileVal.assign(nTiles, 0);
+  ix.tileMax.assign(nTiles, 0);
+  ix.tileMin.assign(nTiles, 255);
   IndexVisitor iv(g, ix);
   int64_t consumed = 0;
   int rc = walk(*s, iv, &consumed);

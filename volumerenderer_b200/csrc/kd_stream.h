@@ -24,6 +24,7 @@ struct KdIndex {
   std::vector<uint8_t> tileVal;
   std::vector<uint32_t> leafOff;
   std::vector<uint8_t> leafVal;
+  std::vector<uint8_t> tileMax, tileMin;  // exact bounds of the decoded voxels of every tile (host only; kd_cull.h)
   std::vector<uint32_t> blockSymBegin;  // per live tile: first symbol of the tile subtree
   std::vector<uint32_t> blockSymEnd;    // per live tile: one past its last symbol
   int64_t numLiveTiles = 0;

@@ -21,11 +21,15 @@ namespace vr {
 // CTAs on the same SM instead of forming a phase of their own.  Groups are dealt out evenly in address order;
 // what does not fit stays a CTA of its own.  fills receives the attached groups; origins = voxel origin of every
 // brick in the destination (3 per brick), occBase / tileCell as in the decode kernel (null = no occupancy).
+// needed (n * 2^Dt bytes, kd_cull.h; needs occBase, tileCell and culled): tiles a frame cannot read get no work --
+// a parse tile is dropped when it is not needed, a constant group when none of its members is -- and their exact
+// maxima go to `culled` instead, to be written into the occupancy grid without decoding anything.
 inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* idx, const int64_t* dstOffset, int64_t rowPitch,
                               int64_t slicePitch, bool vec16, int order, std::vector<vr_kd_work>* out,
                               std::vector<vr_fill_job>* fills = nullptr, int attach = 0, const int64_t* origins = nullptr,
                               int lateMode = 0,
-                              const int64_t* occBase = nullptr, const int32_t* tileCell = nullptr) {
+                              const int64_t* occBase = nullptr, const int32_t* tileCell = nullptr,
+                              const uint8_t* needed = nullptr, std::vector<vr_occ_set>* culled = nullptr) {
   struct Item { int64_t key; vr_kd_work w; };
   struct FItem { int64_t key; vr_kd_work w; vr_fill_job f; };
   std::vector<Item> items;
@@ -51,6 +55,21 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
         } else {
           w.L = 0;
           w.vals = hj.tileVal[t];
+        }
+      }
+      if (needed && culled && occBase && tileCell && occBase[b] >= 0) {
+        const uint32_t members = parse ? 1u : (1u << w.L);
+        uint32_t mt[8];
+        bool any = false;
+        for (uint32_t i = 0; i < members; ++i) {  // member i of a group: x index of the leader + i, scattered to the x path bits
+          uint32_t tm = t;
+          for (uint32_t j = 0; j < w.L && !parse; ++j) tm |= ((i >> j) & 1u) << g.xrBit[j];
+          mt[i] = tm;
+          any = any || needed[(size_t)b * nt + tm];
+        }
+        if (!any) {
+          for (uint32_t i = 0; i < members; ++i) culled->push_back({occBase[b] + tileCell[mt[i]], (int64_t)idx[b]->tileMax[mt[i]]});
+          continue;
         }
       }
       int ox, oy, oz;

@@ -129,6 +129,22 @@ __global__ void occ_levels_kernel(const uint8_t* __restrict__ pyr, uint8_t* __re
 
 }  // namespace
 
+namespace {
+// pairs[2i] = cell, pairs[2i+1] = exact maximum of the cell's voxels: slot 0 takes the value, the other writer slots 0
+__global__ void __launch_bounds__(256) occ_set_cells_kernel(uint8_t* __restrict__ raw, const long long* __restrict__ pairs, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const longlong2 e = __ldg(reinterpret_cast<const longlong2*>(pairs) + i);
+  *reinterpret_cast<uint2*>(raw + e.x * VR_OCC_SLOTS) = make_uint2((unsigned)e.y & 0xFFu, 0u);
+}
+}  // namespace
+
+cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  occ_set_cells_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(raw, reinterpret_cast<const long long*>(pairsDev), n);
+  return cudaGetLastError();
+}
+
 cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& L, cudaStream_t stream) {
   const long long n = (long long)L.nx * L.ny * L.nz;
   occ_levels_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(pyr, lvl, L);

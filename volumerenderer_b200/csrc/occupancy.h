@@ -36,6 +36,8 @@ struct OccView {        // what the march kernels read (null pyr = no skipping)
 // raw[cell][0..7] = max over (cell ∩ box) for every cell the box touches
 cudaError_t occ_reduce_box_launch(const uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, const int64_t lo[3], const int64_t ext[3],
                                   uint8_t* raw, int nx, int ny, int nz, const int shift[3], cudaStream_t stream);
+// raw[cell] = value for n (cell, value) pairs of 2 x int64: cells whose voxels are known without being stored (lazy decode, kd_cull.h)
+cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, cudaStream_t stream);
 // all pyramid levels from raw (two launches)
 cudaError_t occ_pyramid_launch(const uint8_t* raw, uint8_t* pyr, const OccView& layout, cudaStream_t stream);
 // lvl[c] for layout.thr (one thread per level-0 cell climbs the octree once, instead of every ray doing it)

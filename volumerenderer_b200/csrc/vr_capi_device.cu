@@ -10,7 +10,9 @@
 #include "../../include/vr_b200.h"
 #include "kd_build.h"
 #include "kd_decode.h"
+#include "kd_cull.h"
 #include "kd_worklist.h"
+#include "occupancy.h"
 #include "vr_internal.h"
 
 using namespace vr;
@@ -169,6 +171,89 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 }  // extern "C"
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
+void vr_decode_plan::lazy_free() {
+  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev) cudaSetDevice(ctx->device);
+  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev);
+  lazy = Lazy();
+}
+
+extern "C" { static int env_int(const char* name, int dflt); }
+
+namespace vr {
+int plan_lazy_prepare(vr_decode_plan* p, int thr, const int reach[3]) {
+  vr_decode_plan::Lazy& lz = p->lazy;
+  if (lz.built && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2]) return VR_OK;
+  if (!p->occFused) return fail(VR_ERR_STATE, "lazy decode needs tiles that coincide with occupancy cells");
+  p->lazy_free();
+  const vr_kd_geom& g = p->geom;
+  const vr_volume* d = p->dst;
+  const uint32_t nt = 1u << g.Dt;
+  const int n = p->n;
+  std::vector<const KdIndex*> idx((size_t)n);
+  for (int i = 0; i < n; ++i) idx[(size_t)i] = &p->streams[(size_t)i]->kd.index;
+  CullGrid cg;
+  for (int a = 0; a < 3; ++a) cg.nc[a] = d->nc[a];
+  cg.lg[0] = VR_OCC_LX; cg.lg[1] = VR_OCC_LY; cg.lg[2] = VR_OCC_LZ;
+  std::vector<uint8_t> needed((size_t)n * nt);
+  const std::vector<int64_t>& ob = p->occBase;
+  const std::vector<int32_t>& tc = p->tileCellHost;
+  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, thr, reach,
+             needed.data());
+  std::vector<vr_kd_work> work;
+  std::vector<vr_fill_job> fills;
+  std::vector<vr_occ_set> culled;
+  kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
+                    env_int("VR_FILL_ATTACH", 2), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled);
+  lz.tilesTotal = (int64_t)n * nt;
+  lz.tilesWritten = lz.tilesTotal - (int64_t)culled.size();
+  lz.bytesVoxels = lz.tilesWritten * ((int64_t)g.tx * g.ty * g.tz);
+  lz.bytesStream = 0;
+  for (const vr_kd_work& w : work)
+    if (w.L == VR_WORK_PARSE) {
+      const KdIndex& ix = *idx[(size_t)(w.id >> g.Dt)];
+      const uint32_t blk = ix.tileLeafBlock[w.id & (nt - 1u)];
+      lz.bytesStream += ((int64_t)ix.blockSymEnd[blk] - (int64_t)ix.blockSymBegin[blk] + 3) / 4;
+    }
+  if (cudaSetDevice(p->ctx->device) != cudaSuccess) return fail(VR_ERR_CUDA, "cudaSetDevice");
+  cudaError_t e = cudaSuccess;
+  lz.nWork = (int)work.size(); lz.nFill = (int)fills.size(); lz.nOccSet = (int)culled.size();
+  if (lz.nWork) {
+    e = cudaMalloc((void**)&lz.workDev, sizeof(vr_kd_work) * work.size());
+    if (e == cudaSuccess) e = cudaMemcpy(lz.workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess && lz.nFill) {
+    e = cudaMalloc((void**)&lz.fillJobsDev, sizeof(vr_fill_job) * fills.size());
+    if (e == cudaSuccess) e = cudaMemcpy(lz.fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess && lz.nOccSet) {
+    static_assert(sizeof(vr_occ_set) == 16, "pairs of int64");
+    e = cudaMalloc((void**)&lz.occSetDev, sizeof(vr_occ_set) * culled.size());
+    if (e == cudaSuccess) e = cudaMemcpy(lz.occSetDev, culled.data(), sizeof(vr_occ_set) * culled.size(), cudaMemcpyHostToDevice);
+  }
+  if (e != cudaSuccess) { p->lazy_free(); return fail_cuda(e, "upload lazy work list"); }
+  lz.thr = thr; lz.reach[0] = reach[0]; lz.reach[1] = reach[1]; lz.reach[2] = reach[2];
+  lz.built = true;
+  return VR_OK;
+}
+
+// One lazy pass: decode what the frame can read, record the maxima of the rest.
+int plan_lazy_run(vr_decode_plan* p) {
+  vr_decode_plan::Lazy& lz = p->lazy;
+  vr_volume* d = p->dst;
+  if (!lz.built) return fail(VR_ERR_STATE, "lazy work list not built");
+  if (!(d->occRaw && d->occEpoch == p->occEpoch && d->skipping)) return fail(VR_ERR_STATE, "occupancy grid of the destination changed");
+  cudaError_t e = cudaSetDevice(p->ctx->device);
+  if (e == cudaSuccess)
+    e = kd_decode_launch(p->geom, p->jobsDev, lz.workDev, lz.nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, d->occRaw,
+                         p->tileCellDev, lz.fillJobsDev);
+  if (e == cudaSuccess) e = occ_set_cells_launch(d->occRaw, lz.occSetDev, lz.nOccSet, p->ctx->stream);
+  if (e != cudaSuccess) return fail_cuda(e, "lazy decode launch");
+  d->occDilDirty = true;
+  if (lz.nOccSet) d->partialOwner = p;
+  return VR_OK;
+}
+}  // namespace vr
+
 extern "C" {
 
 static int env_int(const char* name, int dflt) {
@@ -253,6 +338,8 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
                       p->occFused ? tileCellHost.data() : nullptr);
     p->nWork = (int)work.size();
     p->nFill = (int)fills.size();
+    p->streams = jobStream; p->origins.assign(origins, origins + 3 * (size_t)n); p->dstOffset = offs; p->occBase = ob;
+    p->tileCellHost = tileCellHost;
     e = cudaMalloc((void**)&p->workDev, sizeof(vr_kd_work) * std::max<size_t>(work.size(), 1));
     if (e == cudaSuccess) e = cudaMemcpy(p->workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && p->nFill) {
@@ -278,6 +365,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
                       occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
+  if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again
   return VR_OK;
 }
 int vr_decode_plan_destroy(vr_decode_plan* p) {
@@ -287,6 +375,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->workDev);
   cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
+  p->lazy_free();
   delete p;
   return VR_OK;
 }

@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "../../include/vr_b200.h"
+#include "kd_cull.h"
 #include "occupancy.h"
 #include "render_march.h"
 #include "vr_internal.h"
@@ -51,6 +52,31 @@ int skip_threshold(const RenderParams& P) {
   }
   return thr;
 }
+int skip_threshold_of(const vr_render_params* params, int* thr, int* mode) {
+  RenderParams P;
+  if (make_render_params(params, &P) != VR_OK) return VR_ERR_ARG;
+  *thr = skip_threshold(P);
+  *mode = P.mode;
+  return VR_OK;
+}
+
+int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev, int32_t* hit_dev,
+                  uint64_t* samples_dev, bool allowPartial) {
+  if (!ctx || !vol || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render: null argument");
+  if (params->mode != VR_MODE_COMPOSITE && params->mode != VR_MODE_ISOSURFACE && params->mode != VR_MODE_ISOSURFACE_COMPRESSED)
+    return fail(VR_ERR_ARG, "vr_render: unknown mode");
+  if (vol->partialOwner && !allowPartial)
+    return fail(VR_ERR_STATE, "vr_render: the volume was decoded lazily for one frame (vr_render_compressed_lazy); run its plan in full first");
+  RenderParams P;
+  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  if (vol->SX > 0x7FFFFFFF || vol->SY > 0x7FFFFFFF || vol->SZ > 0x7FFFFFFF) return fail(VR_ERR_UNSUPPORTED, "volume extent too large");
+  CU(cudaSetDevice(ctx->device));
+  OccView occ;
+  { int rc = volume_occ_view(ctx, vol, skip_threshold(P), &occ); if (rc != VR_OK) return rc; }
+  CU(render_launch(P, occ, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,
+                   reinterpret_cast<unsigned long long*>(samples_dev), ctx->stream));
+  return VR_OK;
+}
 }  // namespace vr
 
 extern "C" {
@@ -80,18 +106,7 @@ int vr_camera_basis(const vr_render_params* in, float out[20]) {
 
 int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev,
               int32_t* hit_dev, uint64_t* samples_dev) {
-  if (!ctx || !vol || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render: null argument");
-  if (params->mode != VR_MODE_COMPOSITE && params->mode != VR_MODE_ISOSURFACE && params->mode != VR_MODE_ISOSURFACE_COMPRESSED)
-    return fail(VR_ERR_ARG, "vr_render: unknown mode");
-  RenderParams P;
-  if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
-  if (vol->SX > 0x7FFFFFFF || vol->SY > 0x7FFFFFFF || vol->SZ > 0x7FFFFFFF) return fail(VR_ERR_UNSUPPORTED, "volume extent too large");
-  CU(cudaSetDevice(ctx->device));
-  OccView occ;
-  { int rc = volume_occ_view(ctx, vol, skip_threshold(P), &occ); if (rc != VR_OK) return rc; }
-  CU(render_launch(P, occ, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,
-                   reinterpret_cast<unsigned long long*>(samples_dev), ctx->stream));
-  return VR_OK;
+  return render_volume(ctx, vol, params, out_rgba_dev, hit_dev, samples_dev, false);
 }
 
 int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_host,
@@ -124,6 +139,101 @@ int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_
   int rc = vr_decode_plan_run(plan);
   if (rc != VR_OK) return rc;
   return vr_render(ctx, plan->dst, params, out_rgba_dev, hit_dev, samples_dev);
+}
+
+int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
+                              int32_t* hit_dev, uint64_t* samples_dev, int64_t stats[4]) {
+  if (!ctx || !plan || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render_compressed_lazy: null argument");
+  if (ctx != plan->ctx) return fail(VR_ERR_ARG, "vr_render_compressed_lazy: the plan belongs to another context");
+  vr_volume* d = plan->dst;
+  int thr = 0, mode = 0;
+  if (skip_threshold_of(params, &thr, &mode) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  const bool lazy = plan->occFused && d->skipping && d->occRaw && d->occEpoch == plan->occEpoch && thr >= 0;
+  if (!lazy) {  // tiles do not coincide with occupancy cells (odd placement) or skipping is off: every tile is needed
+    int rc = vr_decode_plan_run(plan);
+    if (rc != VR_OK) return rc;
+    if (stats) { stats[0] = stats[1] = (int64_t)plan->n << plan->geom.Dt; stats[2] = plan->bytesVoxels; stats[3] = plan->bytesStream; }
+    return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, false);
+  }
+  const int64_t G[3] = {d->SX, d->SY, d->SZ};
+  int reach[3];
+  cull_reach(mode, params->step_size, G, reach);
+  int rc = plan_lazy_prepare(plan, thr, reach);
+  if (rc != VR_OK) return rc;
+  if (!d->occValid) {
+    if (plan->bytesVoxels == d->SX * d->SY * d->SZ) {
+      d->occValid = true;  // the plan covers the volume: after this pass every cell carries an exact maximum
+    } else {  // cells outside the plan: bound what is stored there now, before this pass leaves stale voxels behind
+      OccView tmp;
+      rc = volume_occ_view(ctx, d, thr, &tmp);
+      if (rc != VR_OK) return rc;
+    }
+  }
+  rc = plan_lazy_run(plan);
+  if (rc != VR_OK) return rc;
+  if (stats) { stats[0] = plan->lazy.tilesTotal; stats[1] = plan->lazy.tilesWritten; stats[2] = plan->lazy.bytesVoxels; stats[3] = plan->lazy.bytesStream; }
+  return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, true);
+}
+
+/* host only: the tiles a frame of `params` can read (kd_cull.h), for bricks placed on the cell grid of a volume of dims[] */
+int vr_lazy_tile_mask(vr_stream* const* streams, int32_t n, const int64_t* origins, const int64_t dims[3], const vr_render_params* params,
+                      uint8_t* needed_out, int32_t* tile_boxes_out, int32_t* tiles_per_brick) {
+  if (!streams || n <= 0 || !origins || !dims || !params) return fail(VR_ERR_ARG, "vr_lazy_tile_mask: null argument");
+  int thr = 0, mode = 0;
+  if (skip_threshold_of(params, &thr, &mode) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
+  for (int i = 0; i < n; ++i) {
+    if (!streams[i]) return fail(VR_ERR_ARG, "null stream");
+    if (!streams[i]->kd.index.built) { int rc = kd_prepare(&streams[i]->kd); if (rc != VR_OK) return fail(rc, "prepare"); }
+  }
+  const vr_kd_geom& g = streams[0]->kd.geom;
+  const uint32_t nt = 1u << g.Dt;
+  if (tiles_per_brick) *tiles_per_brick = (int32_t)nt;
+  if (!needed_out) return VR_OK;
+  if (g.tx != (1 << VR_OCC_LX) || g.ty != (1 << VR_OCC_LY) || g.tz != (1 << VR_OCC_LZ))
+    return fail(VR_ERR_UNSUPPORTED, "tiles do not coincide with occupancy cells for this brick shape");
+  CullGrid cg;
+  cg.lg[0] = VR_OCC_LX; cg.lg[1] = VR_OCC_LY; cg.lg[2] = VR_OCC_LZ;
+  for (int a = 0; a < 3; ++a) cg.nc[a] = (int)((dims[a] - 1) >> cg.lg[a]) + 1;
+  std::vector<const KdIndex*> idx((size_t)n);
+  std::vector<int64_t> base((size_t)n);
+  for (int i = 0; i < n; ++i) {
+    const vr_kd_header& h = streams[i]->kd.hdr;
+    if (h.X != g.X || h.Y != g.Y || h.Z != g.Z) return fail(VR_ERR_ARG, "all streams must share one brick shape");
+    const int64_t* o = origins + 3 * i;
+    if ((o[0] & 31) || (o[1] & 31) || (o[2] & 15) || o[0] < 0 || o[1] < 0 || o[2] < 0 || o[0] + h.X > dims[0] || o[1] + h.Y > dims[1] ||
+        o[2] + h.Z > dims[2])
+      return fail(VR_ERR_ARG, "brick placement off the cell grid or outside the volume");
+    idx[(size_t)i] = &streams[i]->kd.index;
+    base[(size_t)i] = (o[0] >> 5) + (int64_t)cg.nc[0] * ((o[1] >> 5) + (int64_t)cg.nc[1] * (o[2] >> 4));
+  }
+  std::vector<int32_t> tc(nt);
+  for (uint32_t t = 0; t < nt; ++t) {
+    int ox, oy, oz;
+    vr_tile_origin(g, t, &ox, &oy, &oz);
+    tc[t] = (ox >> 5) + cg.nc[0] * ((oy >> 5) + cg.nc[1] * (oz >> 4));
+    if (tile_boxes_out)
+      for (int i = 0; i < n; ++i) {
+        int32_t* b = tile_boxes_out + ((size_t)i * nt + t) * 3;
+        b[0] = (int32_t)origins[3 * i] + ox; b[1] = (int32_t)origins[3 * i + 1] + oy; b[2] = (int32_t)origins[3 * i + 2] + oz;
+      }
+  }
+  int reach[3];
+  cull_reach(mode, params->step_size, dims, reach);
+  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return base[(size_t)b] + tc[t]; }, thr, reach, needed_out);
+  return VR_OK;
+}
+
+/* exact bounds of the decoded voxels per tile, from the stream index (no decode): 2^Dt entries each */
+int vr_stream_tile_bounds(vr_stream* s, uint8_t* mins, uint8_t* maxs, int64_t cap, int32_t tile_dims[3]) {
+  if (!s) return fail(VR_ERR_ARG, "null");
+  if (!s->kd.index.built) { int rc = kd_prepare(&s->kd); if (rc != VR_OK) return fail(rc, "prepare"); }
+  const int64_t nt = int64_t(1) << s->kd.geom.Dt;
+  if (tile_dims) { tile_dims[0] = s->kd.geom.tx; tile_dims[1] = s->kd.geom.ty; tile_dims[2] = s->kd.geom.tz; }
+  if (!mins && !maxs) return VR_OK;
+  if (cap < nt) return fail(VR_ERR_ARG, "buffer too small");
+  if (mins) std::memcpy(mins, s->kd.index.tileMin.data(), (size_t)nt);
+  if (maxs) std::memcpy(maxs, s->kd.index.tileMax.data(), (size_t)nt);
+  return VR_OK;
 }
 
 }  // extern "C"

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <map>
 #include <vector>
+#include "../../include/vr_b200.h"
 #include "kd_decode_core.h"
 #include "kd_stream.h"
 
@@ -52,6 +53,9 @@ struct vr_volume {
   uint8_t* occLvl = nullptr;      // per level-0 cell: highest void level for threshold occLvlThr (occupancy.h)
   int occLvlThr = -2;             // -2 = occLvl is stale
   int occEpoch = 0;               // bumped whenever the grids are freed (plans remember the epoch they were built for)
+  // set by a lazy decode (vr_render_compressed_lazy): only the tiles that frame could read hold valid voxels, so
+  // vr_render refuses the volume until the owning plan has been run in full again
+  const void* partialOwner = nullptr;
   void occ_free();
 };
 
@@ -70,6 +74,19 @@ struct vr_decode_plan {
   int occEpoch = 0;
   int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
+  // host copies kept for the lazy (view-dependent) work list, kd_cull.h
+  std::vector<vr_stream*> streams;
+  std::vector<int64_t> origins, dstOffset, occBase;
+  std::vector<int32_t> tileCellHost;
+  struct Lazy {
+    bool built = false;
+    int thr = 0, reach[3] = {0, 0, 0};   // cache key
+    vr_kd_work* workDev = nullptr; int nWork = 0;
+    vr_fill_job* fillJobsDev = nullptr; int nFill = 0;
+    int64_t* occSetDev = nullptr; int nOccSet = 0;  // (cell, max) pairs of the tiles left out
+    int64_t tilesTotal = 0, tilesWritten = 0, bytesVoxels = 0, bytesStream = 0;
+  } lazy;
+  void lazy_free();
 };
 
 namespace vr {
@@ -83,5 +100,12 @@ struct PeerTargets;
 int peer_targets(struct ::vr_peer* p, int slot, PeerTargets* t, int64_t* windowBytes);
 int volume_occ_alloc(vr_volume* v);                       // allocate the grids for the current cellOrigin
 int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out);  // build / refresh as needed; out->dil = null when off
+// the march of vr_render without the partial-volume check (lazy path)
+int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev, int32_t* hit_dev,
+                  uint64_t* samples_dev, bool allowPartial);
+int skip_threshold_of(const vr_render_params* params, int* thr, int* mode);  // occupancy threshold of the frame's mode
+// (re)builds plan->lazy for (thr, reach): the work list without the tiles the frame cannot read (kd_cull.h)
+int plan_lazy_prepare(vr_decode_plan* plan, int thr, const int reach[3]);
+int plan_lazy_run(vr_decode_plan* plan);  // decode launch over the lazy list + maxima of the tiles left out
 void volume_occ_written(vr_context* ctx, vr_volume* v, const int64_t lo[3], const int64_t ext[3]);  // a box of voxels was overwritten
 }

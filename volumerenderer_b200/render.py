@@ -25,8 +25,17 @@ _lib.lib.vr_camera_basis.argtypes = [ctypes.POINTER(RenderParams), ctypes.POINTE
 for _n in ("vr_render", "vr_render_to_host", "vr_render_compressed"):
     getattr(_lib.lib, _n).restype = ctypes.c_int
     getattr(_lib.lib, _n).argtypes = [c_void_p, c_void_p, ctypes.POINTER(RenderParams), c_void_p, c_void_p, c_void_p]
+_lib.lib.vr_render_compressed_lazy.restype = ctypes.c_int
+_lib.lib.vr_render_compressed_lazy.argtypes = [c_void_p, c_void_p, ctypes.POINTER(RenderParams), c_void_p, c_void_p, c_void_p,
+                                               ctypes.POINTER(ctypes.c_int64)]
+_lib.lib.vr_lazy_tile_mask.restype = ctypes.c_int
+_lib.lib.vr_lazy_tile_mask.argtypes = [ctypes.POINTER(c_void_p), c_int32, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64),
+                                       ctypes.POINTER(RenderParams), c_void_p, c_void_p, ctypes.POINTER(c_int32)]
+_lib.lib.vr_stream_tile_bounds.restype = ctypes.c_int
+_lib.lib.vr_stream_tile_bounds.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, ctypes.POINTER(c_int32)]
 _lib.EXPORTED[:] = sorted(set(_lib.EXPORTED) | {"vr_render_defaults", "vr_camera_basis", "vr_render",
-                                                "vr_render_to_host", "vr_render_compressed"})
+                                                "vr_render_to_host", "vr_render_compressed", "vr_render_compressed_lazy",
+                                                "vr_lazy_tile_mask", "vr_stream_tile_bounds"})
 
 
 def default_params(width=1600, height=1200, mode=COMPOSITE, eye=None, front=None, up=None, iso=None, step=None):
@@ -85,6 +94,44 @@ def render_device(ctx, volume, p, out_ptr, hit_ptr=None, samples_ptr=None):
 def render_compressed_device(ctx, plan, p, out_ptr, hit_ptr=None, samples_ptr=None):
     check(lib.vr_render_compressed(ctx.h, plan.h, byref(p), c_void_p(out_ptr), c_void_p(hit_ptr) if hit_ptr else None,
                                    c_void_p(samples_ptr) if samples_ptr else None))
+
+
+def render_compressed_lazy_device(ctx, plan, p, out_ptr, hit_ptr=None, samples_ptr=None):
+    """Frame straight from the streams, decoding only the tiles the frame can read (vr_render_compressed_lazy).
+    Returns {tiles, tiles_written, voxel_bytes, stream_bytes}."""
+    st = (ctypes.c_int64 * 4)()
+    check(lib.vr_render_compressed_lazy(ctx.h, plan.h, byref(p), c_void_p(out_ptr), c_void_p(hit_ptr) if hit_ptr else None,
+                                        c_void_p(samples_ptr) if samples_ptr else None, st))
+    return {"tiles": st[0], "tiles_written": st[1], "voxel_bytes": st[2], "stream_bytes": st[3]}
+
+
+def lazy_tile_mask(streams, origins, dims, p):
+    """Host-only: (needed uint8 [n, tiles], tile origins int32 [n, tiles, 3]) for a frame of `p` over a volume of `dims`
+    (x, y, z) with brick b at origins[b] (vr_lazy_tile_mask)."""
+    n = len(streams)
+    hs = (c_void_p * n)(*[s.h for s in streams])
+    org = np.ascontiguousarray(np.asarray(origins, np.int64).reshape(n, 3))
+    dm = (ctypes.c_int64 * 3)(*[int(v) for v in dims])
+    nt = c_int32(0)
+    check(lib.vr_lazy_tile_mask(hs, n, org.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)), dm, byref(p), None, None, byref(nt)))
+    needed = np.zeros((n, nt.value), np.uint8)
+    boxes = np.zeros((n, nt.value, 3), np.int32)
+    check(lib.vr_lazy_tile_mask(hs, n, org.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)), dm, byref(p), needed.ctypes.data,
+                                boxes.ctypes.data, byref(nt)))
+    return needed, boxes
+
+
+def stream_tile_bounds(stream):
+    """(mins, maxs, tile_dims): exact bounds of the decoded voxels of every decode tile, from the index alone."""
+    td = (c_int32 * 3)()
+    check(lib.vr_stream_tile_bounds(stream.h, None, None, 0, td))
+    # number of tiles = brick voxels / tile voxels
+    hdr = stream.header
+    nt = int(hdr.X * hdr.Y * hdr.Z) // (td[0] * td[1] * td[2])
+    mins = np.empty(nt, np.uint8)
+    maxs = np.empty(nt, np.uint8)
+    check(lib.vr_stream_tile_bounds(stream.h, mins.ctypes.data, maxs.ctypes.data, nt, td))
+    return mins, maxs, tuple(td)
 
 
 def smoke_check(vr, oa, decoded):
