@@ -93,6 +93,12 @@ int vr_stream_pin(vr_stream* s);
 /* H2D copy of stream + index (asynchronous on the context stream); implies prepare */
 int vr_stream_upload(vr_context* ctx, vr_stream* s);
 
+/* VolumeKdtree::open for a whole timestep (main.cpp:276-284 opens one tree per brick): `threads` host threads (0 = all
+ * cores) open and parse the n container files and build their decode index while the calling thread pins and uploads
+ * the streams in order as they become ready (ctx may be NULL: open + prepare only).  out receives n streams; on any
+ * failure every stream is destroyed and the first error is returned (VR_ERR_IO missing / short file, VR_ERR_FORMAT). */
+int vr_streams_load(vr_context* ctx, const char* const* paths, int32_t n, int32_t threads, vr_stream** out);
+
 /* ---- MidRangeTree's 4-bit/node shader stream (MidRangeTree::convertToByteArray, MidRangeTree.cpp:1095-1128) ----
  * byte k = tree[2k]<<6 | range[2k]<<4 | tree[2k+1]<<2 | range[2k+1]; length = next power of two >= ceil(n/2),
  * zero tail.  tree / range are TwoBitArray bit arrays (LSB first) of n symbols.  Returns the packed length
@@ -130,6 +136,18 @@ int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host); /* s
  * brick (BX*BY*BZ, x fastest) at voxel origin (ox,oy,oz) of the slab; 64-bit indexing (SURVEY C-12). */
 int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, int64_t BX, int64_t BY,
                            int64_t BZ, int64_t ox, int64_t oy, int64_t oz);
+/* LoadBricksToTexture (VolumeReader.h:151-223) as one call: brick b of `numBricks` raw files (one X*Y*Z uint8 file per
+ * brick, path = find(b, timestep, user) = the reference's findSourceFile, main.cpp:580-597) goes to grid position
+ * brick_ijk[3b..] (NULL = fillVolumeBrickMap's b -> (b % I, (b / I) % J, b / (I*J)), main.cpp:599-619) of the slab, 64-bit
+ * offsets (SURVEY C-12).  Pipelined: a reader thread fills a ring of pinned staging buffers while the context's stream
+ * copies each brick straight to its place (no assembled host array).  host_data (optional, I*X * J*Y * K*Z bytes)
+ * receives the assembled array as well (= VolumeReader::data).  Synchronous.  A missing file gives VR_ERR_IO (the
+ * reference returns false), a file whose size is not X*Y*Z gives VR_ERR_FORMAT (the reference throws, :258-260).
+ * stats (optional): [0] bricks copied, [1] bytes copied. */
+typedef const char* (*vr_find_source_file)(int32_t brick, int32_t timestep, void* user);
+int vr_volume_load_bricks(vr_context* ctx, vr_volume* v, int64_t numBricks, int64_t I, int64_t J, int64_t K, int32_t timestep,
+                          const int64_t brick_dims[3], vr_find_source_file find, void* user, const int64_t* brick_ijk,
+                          uint8_t* host_data, int64_t stats[2]);
 /* GPU producer on a brick that already lives in a device volume (e.g. one just decoded, simulated or uploaded):
  * compresses the X*Y*Z box at `origin` without a host round trip of the voxels.  fixed_point_iterations (optional,
  * 2 entries): scan passes of the running-mean fixed point, total and worst level. */

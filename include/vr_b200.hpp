@@ -170,19 +170,37 @@ class VolumeReader {
   bool LoadBricksToTexture(int64_t numBricks, int64_t I, int64_t J, int64_t K, int timestep, bool dealloc, bool toGPU = true) {
     const int64_t X = brickDims[0], Y = brickDims[1], Z = brickDims[2];
     const int64_t GX = I * X, GY = J * Y;
-    data.assign((size_t)(X * Y * Z * numBricks), T(0));
+    std::vector<int64_t> ijk((size_t)numBricks * 3);
     for (int b = 0; b < (int)numBricks; ++b) {
       if (!brickMap || !brickMap->count(b)) throw std::runtime_error("brick map has no entry for brick " + std::to_string(b));
-      const std::vector<int64_t>& ijk = (*brickMap)[b];
+      for (int a = 0; a < 3; ++a) ijk[(size_t)b * 3 + a] = (*brickMap)[b][a];
+    }
+    dataDims[0] = GX; dataDims[1] = GY; dataDims[2] = K * Z;
+    if (toGPU && ctx_) {
+      // pipelined path (vr_volume_load_bricks): file reads overlap the H2D copies, bricks go straight to their place in
+      // the slab; the assembled host array (`data`) is only filled when the caller keeps it (dealloc == false)
+      static_assert(sizeof(T) == 1, "the device slab is 8-bit (GL_RED / GL_UNSIGNED_BYTE in the reference)");
+      vr_volume_destroy(volume); volume = nullptr;
+      check(vr_volume_create(ctx_->handle(), dataDims[0], dataDims[1], dataDims[2], &volume));
+      if (dealloc) std::vector<T>().swap(data); else data.assign((size_t)(GX * GY * K * Z), T(0));
+      const int64_t bd[3] = {X, Y, Z};
+      const int rc = vr_volume_load_bricks(ctx_->handle(), volume, numBricks, I, J, K, timestep, bd, &VolumeReader::find_trampoline, this,
+                                           ijk.data(), dealloc ? nullptr : reinterpret_cast<uint8_t*>(data.data()), nullptr);
+      if (rc == VR_ERR_IO) return false;                                  // missing file: the reference returns false
+      if (rc == VR_ERR_FORMAT) throw std::runtime_error(vr_last_error());  // size mismatch: the reference throws (:258-260)
+      check(rc);
+      return true;
+    }
+    data.assign((size_t)(X * Y * Z * numBricks), T(0));
+    for (int b = 0; b < (int)numBricks; ++b) {
       if (!read_brick(findSourceFile(b, timestep))) return false;
       for (int64_t z = 0; z < Z; ++z)
         for (int64_t y = 0; y < Y; ++y) {
           const T* src = temp_.data() + (z * Y + y) * X;
-          T* dst = data.data() + ((ijk[2] * Z + z) * GY + (ijk[1] * Y + y)) * GX + ijk[0] * X;
+          T* dst = data.data() + ((ijk[(size_t)b * 3 + 2] * Z + z) * GY + (ijk[(size_t)b * 3 + 1] * Y + y)) * GX + ijk[(size_t)b * 3] * X;
           for (int64_t x = 0; x < X; ++x) dst[x] = src[x];
         }
     }
-    dataDims[0] = GX; dataDims[1] = GY; dataDims[2] = K * Z;
     if (toGPU) transferToGPU(dealloc);
     return true;
   }
@@ -213,7 +231,13 @@ class VolumeReader {
     std::fclose(f);
     return got == (size_t)want;
   }
+  static const char* find_trampoline(int32_t brick, int32_t timestep, void* self) {
+    VolumeReader* r = static_cast<VolumeReader*>(self);
+    r->path_ = r->findSourceFile(brick, timestep);
+    return r->path_.c_str();
+  }
   std::vector<T> temp_;
+  std::string path_;
   Context* ctx_ = nullptr;
 };
 

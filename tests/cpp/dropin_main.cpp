@@ -50,6 +50,20 @@ int main(int argc, char** argv) {
     catch (const vr::Error& e) { std::printf("open_missing=error%d\n", e.code); }
     if (!gpu) return 0;
 
+    {  // LoadBricksToTexture with toGPU: pipelined file reads + H2D copies straight into the slab (vr_volume_load_bricks)
+      vr::VolumeReader<vr::byte> streamed(BRICK_DIM, VOLUME_GRID, findBrickBinaryFile, &brickMap, ctx);
+      bool ok = streamed.LoadBricksToTexture(8, 2, 2, 2, 7, /*dealloc*/ false, /*toGPU*/ true);
+      std::vector<vr::byte> dev(64u * 64u * 32u);
+      if (ok) vr::check(vr_volume_download(ctx->handle(), streamed.volume, dev.data()));
+      std::printf("streamed_ok=%d streamed_host=%u streamed_device=%u\n", ok ? 1 : 0, fnv(streamed.data.data(), streamed.data.size()),
+                  fnv(dev.data(), dev.size()));
+      ok = streamed.LoadBricksToTexture(8, 2, 2, 2, 7, /*dealloc*/ true, /*toGPU*/ true);
+      if (ok) vr::check(vr_volume_download(ctx->handle(), streamed.volume, dev.data()));
+      std::printf("streamed_dealloc=%d,%u,%u\n", ok ? 1 : 0, (unsigned)streamed.data.size(), fnv(dev.data(), dev.size()));
+      bool gone = !streamed.LoadBricksToTexture(8, 2, 2, 2, /*timestep*/ 8, true, true);  // no files for timestep 8
+      std::printf("streamed_missing_returns_false=%d\n", gone ? 1 : 0);
+    }
+
     {  // the same build on the GPU gives the same stream
       vr::VolumeKdtree gpuTree(volume.data, volume.dataDims[0], volume.dataDims[1], volume.dataDims[2]);
       gpuTree.setMaxEpochs(2);

@@ -89,6 +89,9 @@ def test_cpp_pipeline_gpu(exe, scene):
     assert int(kv["maxerr_measured"]) == int(np.abs(want.astype(int) - full.astype(int)).max())
     assert kv["cut10"] == "error5"                         # VR_ERR_UNSUPPORTED; the reference segfaults
     assert kv["gpu_build_equal"] == "1"                    # VolumeKdtree::build(Context&): GPU producer, same stream
+    # LoadBricksToTexture(toGPU=true): pipelined loader, same placement on the host copy and in the device slab
+    assert kv["streamed_ok"] == "1" and int(kv["streamed_host"]) == fnv_fast(full) and int(kv["streamed_device"]) == fnv_fast(full)
+    assert kv["streamed_dealloc"] == f"1,0,{fnv_fast(full)}" and kv["streamed_missing_returns_false"] == "1"
     p = render.default_params(96, 72, render.COMPOSITE, step=(1 / 64, 1 / 64, 1 / 32))
     img, S, _ = oa.oracle_render(want, render.oracle_param_blob(p), 4)
     assert int(kv["composite_samples"]) == S

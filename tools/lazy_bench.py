@@ -62,7 +62,7 @@ def run(ctx, name, streams, origins, dims, img, iters, emit):
             emit({"workload": name, "mode": mname, "view": vname, "image": [img, img], "bricks": len(streams),
                   "full_ms": full_ms, "full_min_ms": full_min, "full_decode_ms": dec_ms, "lazy_ms": lazy_ms, "lazy_min_ms": lazy_min,
                   "speedup": full_ms / lazy_ms, "tiles": stats["tiles"], "tiles_written": stats["tiles_written"],
-                  "voxel_bytes_full": by[1], "voxel_bytes_lazy": stats["voxel_bytes"], "stream_bytes_full": by[0],
+                  "voxel_bytes_full": by["voxels"], "voxel_bytes_lazy": stats["voxel_bytes"], "stream_bytes_full": by["stream"],
                   "stream_bytes_lazy": stats["stream_bytes"], "frames_bit_identical": same,
                   "hits": int((hit2 >= 0).sum().item())})
     plan.close()

@@ -99,7 +99,11 @@ _SIGS = {
     "vr_decode_plan_destroy": (c_int, [c_void_p]),
     "vr_decode_plan_bytes": (c_int, [c_void_p, POINTER(c_int64)]),
     "vr_kd_levelcut": (c_int, [c_void_p, c_void_p, c_int32, c_void_p]),
+    "vr_volume_load_bricks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, POINTER(c_int64), c_void_p, c_void_p,
+                                      POINTER(c_int64), c_void_p, POINTER(c_int64)]),
+    "vr_streams_load": (c_int, [c_void_p, POINTER(c_char_p), c_int32, c_int32, POINTER(c_void_p)]),
 }
+FIND_SOURCE_FILE = ctypes.CFUNCTYPE(c_void_p, c_int32, c_int32, c_void_p)  # returns the address of a NUL-terminated path
 
 EXPORTED = sorted(_SIGS)
 for _name, (_res, _args) in _SIGS.items():

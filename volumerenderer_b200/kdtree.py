@@ -180,6 +180,16 @@ class Stream:
             pass
 
 
+def load_streams(paths, ctx=None, threads=0):
+    """VolumeKdtree::open for many files at once (vr_streams_load): worker threads open + index the containers while the
+    calling thread pins and uploads them to ctx's device in order.  ctx=None: open + prepare only."""
+    n = len(paths)
+    arr = (ctypes.c_char_p * n)(*[str(p).encode() for p in paths])
+    out = (c_void_p * n)()
+    check(lib.vr_streams_load(ctx.h if ctx is not None else None, arr, n, int(threads), out))
+    return [Stream(c_void_p(out[i])) for i in range(n)]
+
+
 def nibbles_pack(tree_bits, range_bits, n):
     """MidRangeTree::convertToByteArray (MidRangeTree.cpp:1095-1128): the 4-bit/node stream of n nodes."""
     t = np.ascontiguousarray(tree_bits, np.uint8); r = np.ascontiguousarray(range_bits, np.uint8)
@@ -242,6 +252,27 @@ class Volume:
         out = np.empty((dims[2], dims[1], dims[0]), np.uint8)
         check(lib.vr_volume_occupancy_download(self.ctx.h, self.h, int(which), out.ctypes.data, out.size, dims))
         return out
+
+    def load_bricks(self, numBricks, I, J, K, timestep, brick_dims, find_source_file, brick_map=None, want_host=False):
+        """VolumeReader::LoadBricksToTexture (VolumeReader.h:151-223): brick b's raw file find_source_file(b, timestep)
+        goes to grid position brick_map[b] (default: fillVolumeBrickMap's b -> (b % I, (b // I) % J, b // (I*J))),
+        file reads and H2D copies pipelined (vr_volume_load_bricks).  Returns (bricks, bytes[, host array (Z, Y, X)])."""
+        keep = []
+
+        def _find(b, t, _user):
+            keep.append(ctypes.create_string_buffer(str(find_source_file(b, t)).encode()))
+            return ctypes.addressof(keep[-1])
+
+        cb = _lib.FIND_SOURCE_FILE(_find)
+        bd = (c_int64 * 3)(*[int(v) for v in brick_dims])
+        ijk = None
+        if brick_map is not None:
+            ijk = (c_int64 * (3 * numBricks))(*[int(v) for b in range(numBricks) for v in brick_map[b]])
+        host = np.zeros((K * brick_dims[2], J * brick_dims[1], I * brick_dims[0]), np.uint8) if want_host else None
+        st = (c_int64 * 2)()
+        check(lib.vr_volume_load_bricks(self.ctx.h, self.h, int(numBricks), int(I), int(J), int(K), int(timestep), bd,
+                                        ctypes.cast(cb, c_void_p), None, ijk, host.ctypes.data if want_host else None, st))
+        return (st[0], st[1], host) if want_host else (st[0], st[1])
 
     def upload_brick(self, brick, origin):
         a = np.ascontiguousarray(brick, dtype=np.uint8)
