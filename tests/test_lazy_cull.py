@@ -66,12 +66,20 @@ def test_culled_tiles_cannot_influence_an_iso_frame(layered, iso):
         thr = int(np.ceil(iso * 255.0)) - 1  # largest voxel value strictly below the iso value
         assert 0 < needed.sum() < needed.size  # something is culled, something is kept
         poisoned = dec.copy()
+        kinds = set()
         for b in range(needed.shape[0]):
             for t in np.flatnonzero(needed[b] == 0):
                 ox, oy, oz = boxes[b, t]
-                assert dec[oz:oz + 16, oy:oy + 32, ox:ox + 32].max() <= thr  # only void tiles are ever left out
-                poisoned[oz:oz + 16, oy:oy + 32, ox:ox + 32] = rng.integers(0, thr + 1, (16, 32, 32), dtype=np.uint8)
+                box = dec[oz:oz + 16, oy:oy + 32, ox:ox + 32]
+                if box.max() <= thr:     # void: below the iso value whatever is stored there
+                    poisoned[oz:oz + 16, oy:oy + 32, ox:ox + 32] = rng.integers(0, thr + 1, (16, 32, 32), dtype=np.uint8)
+                    kinds.add("void")
+                else:                    # solid-high: at or above it whatever is stored there
+                    assert box.min() >= thr + 2
+                    poisoned[oz:oz + 16, oy:oy + 32, ox:ox + 32] = rng.integers(thr + 2, 256, (16, 32, 32), dtype=np.uint8)
+                    kinds.add("solid")
         assert (poisoned != dec).any()
+        assert kinds == {"void", "solid"}
         want, S, hits = oa.oracle_render(dec, render.oracle_param_blob(p), 8, want_hits=True)
         got, S2, hits2 = oa.oracle_render(poisoned, render.oracle_param_blob(p), 8, want_hits=True)
         assert (hits >= 0).any()

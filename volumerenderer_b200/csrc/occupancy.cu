@@ -139,6 +139,19 @@ __global__ void __launch_bounds__(256) occ_set_cells_kernel(uint8_t* __restrict_
 }
 }  // namespace
 
+namespace {
+__global__ void __launch_bounds__(256) occ_merge_solid_kernel(uint8_t* __restrict__ lvl, const uint8_t* __restrict__ solid, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && __ldg(solid + i) && lvl[i] == VR_OCC_SOLID) lvl[i] = 0;  // skip this lattice position only (level 0)
+}
+}  // namespace
+
+cudaError_t occ_merge_solid_launch(uint8_t* lvl, const uint8_t* solidDev, int n, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  occ_merge_solid_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(lvl, solidDev, n);
+  return cudaGetLastError();
+}
+
 cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   occ_set_cells_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(raw, reinterpret_cast<const long long*>(pairsDev), n);

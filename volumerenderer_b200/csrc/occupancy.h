@@ -38,6 +38,9 @@ cudaError_t occ_reduce_box_launch(const uint8_t* vol, int64_t SX, int64_t SY, in
                                   uint8_t* raw, int nx, int ny, int nz, const int shift[3], cudaStream_t stream);
 // raw[cell] = value for n (cell, value) pairs of 2 x int64: cells whose voxels are known without being stored (lazy decode, kd_cull.h)
 cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, cudaStream_t stream);
+// lvl[c] = 0 (skip the fetch at this lattice position) where solid[c] != 0 and the cell is not void already: look-up cells
+// of the isosurface march in which the crossing test cannot fire because every reachable voxel is >= isoValue (kd_cull.h)
+cudaError_t occ_merge_solid_launch(uint8_t* lvl, const uint8_t* solidDev, int n, cudaStream_t stream);
 // all pyramid levels from raw (two launches)
 cudaError_t occ_pyramid_launch(const uint8_t* raw, uint8_t* pyr, const OccView& layout, cudaStream_t stream);
 // lvl[c] for layout.thr (one thread per level-0 cell climbs the octree once, instead of every ray doing it)

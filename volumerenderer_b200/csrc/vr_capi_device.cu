@@ -172,17 +172,19 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
 void vr_decode_plan::lazy_free() {
-  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev) cudaSetDevice(ctx->device);
-  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev);
+  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev) cudaSetDevice(ctx->device);
+  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev);
   lazy = Lazy();
 }
 
 extern "C" { static int env_int(const char* name, int dflt); }
 
 namespace vr {
-int plan_lazy_prepare(vr_decode_plan* p, int thr, const int reach[3]) {
+int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], const int stepReach[3]) {
   vr_decode_plan::Lazy& lz = p->lazy;
-  if (lz.built && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2]) return VR_OK;
+  if (lz.built && lz.mode == mode && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2] &&
+      lz.stepReach[0] == stepReach[0] && lz.stepReach[1] == stepReach[1] && lz.stepReach[2] == stepReach[2])
+    return VR_OK;
   if (!p->occFused) return fail(VR_ERR_STATE, "lazy decode needs tiles that coincide with occupancy cells");
   p->lazy_free();
   const vr_kd_geom& g = p->geom;
@@ -197,8 +199,9 @@ int plan_lazy_prepare(vr_decode_plan* p, int thr, const int reach[3]) {
   std::vector<uint8_t> needed((size_t)n * nt);
   const std::vector<int64_t>& ob = p->occBase;
   const std::vector<int32_t>& tc = p->tileCellHost;
-  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, thr, reach,
-             needed.data());
+  std::vector<uint8_t> solid;
+  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, mode, thr,
+             reach, stepReach, needed.data(), &solid);
   std::vector<vr_kd_work> work;
   std::vector<vr_fill_job> fills;
   std::vector<vr_occ_set> culled;
@@ -230,8 +233,13 @@ int plan_lazy_prepare(vr_decode_plan* p, int thr, const int reach[3]) {
     e = cudaMalloc((void**)&lz.occSetDev, sizeof(vr_occ_set) * culled.size());
     if (e == cudaSuccess) e = cudaMemcpy(lz.occSetDev, culled.data(), sizeof(vr_occ_set) * culled.size(), cudaMemcpyHostToDevice);
   }
+  if (e == cudaSuccess && !solid.empty()) {
+    e = cudaMalloc((void**)&lz.solidDev, solid.size());
+    if (e == cudaSuccess) e = cudaMemcpy(lz.solidDev, solid.data(), solid.size(), cudaMemcpyHostToDevice);
+  }
   if (e != cudaSuccess) { p->lazy_free(); return fail_cuda(e, "upload lazy work list"); }
-  lz.thr = thr; lz.reach[0] = reach[0]; lz.reach[1] = reach[1]; lz.reach[2] = reach[2];
+  lz.mode = mode; lz.thr = thr;
+  for (int a = 0; a < 3; ++a) { lz.reach[a] = reach[a]; lz.stepReach[a] = stepReach[a]; }
   lz.built = true;
   return VR_OK;
 }

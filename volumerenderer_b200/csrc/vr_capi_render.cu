@@ -61,7 +61,7 @@ int skip_threshold_of(const vr_render_params* params, int* thr, int* mode) {
 }
 
 int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev, int32_t* hit_dev,
-                  uint64_t* samples_dev, bool allowPartial) {
+                  uint64_t* samples_dev, bool allowPartial, const uint8_t* solidMaskDev) {
   if (!ctx || !vol || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render: null argument");
   if (params->mode != VR_MODE_COMPOSITE && params->mode != VR_MODE_ISOSURFACE && params->mode != VR_MODE_ISOSURFACE_COMPRESSED)
     return fail(VR_ERR_ARG, "vr_render: unknown mode");
@@ -73,6 +73,10 @@ int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params*
   CU(cudaSetDevice(ctx->device));
   OccView occ;
   { int rc = volume_occ_view(ctx, vol, skip_threshold(P), &occ); if (rc != VR_OK) return rc; }
+  if (solidMaskDev && occ.lvl && P.mode != 0) {  // this frame only: the cached per-cell levels are recomputed for the next one
+    CU(occ_merge_solid_launch(const_cast<uint8_t*>(occ.lvl), solidMaskDev, occ.nx * occ.ny * occ.nz, ctx->stream));
+    const_cast<vr_volume*>(vol)->occLvlThr = -2;
+  }
   CU(render_launch(P, occ, vol->dev, (int)vol->SX, (int)vol->SY, (int)vol->SZ, reinterpret_cast<float4*>(out_rgba_dev), hit_dev,
                    reinterpret_cast<unsigned long long*>(samples_dev), ctx->stream));
   return VR_OK;
@@ -156,9 +160,10 @@ int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_re
     return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, false);
   }
   const int64_t G[3] = {d->SX, d->SY, d->SZ};
-  int reach[3];
+  int reach[3], stepReach[3];
   cull_reach(mode, params->step_size, G, reach);
-  int rc = plan_lazy_prepare(plan, thr, reach);
+  cull_step_reach(params->step_size, G, stepReach);
+  int rc = plan_lazy_prepare(plan, mode, thr, reach, stepReach);
   if (rc != VR_OK) return rc;
   if (!d->occValid) {
     if (plan->bytesVoxels == d->SX * d->SY * d->SZ) {
@@ -172,7 +177,7 @@ int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_re
   rc = plan_lazy_run(plan);
   if (rc != VR_OK) return rc;
   if (stats) { stats[0] = plan->lazy.tilesTotal; stats[1] = plan->lazy.tilesWritten; stats[2] = plan->lazy.bytesVoxels; stats[3] = plan->lazy.bytesStream; }
-  return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, true);
+  return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, true, plan->lazy.solidDev);
 }
 
 /* host only: the tiles a frame of `params` can read (kd_cull.h), for bricks placed on the cell grid of a volume of dims[] */
@@ -217,9 +222,11 @@ int vr_lazy_tile_mask(vr_stream* const* streams, int32_t n, const int64_t* origi
         b[0] = (int32_t)origins[3 * i] + ox; b[1] = (int32_t)origins[3 * i + 1] + oy; b[2] = (int32_t)origins[3 * i + 2] + oz;
       }
   }
-  int reach[3];
+  int reach[3], stepReach[3];
   cull_reach(mode, params->step_size, dims, reach);
-  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return base[(size_t)b] + tc[t]; }, thr, reach, needed_out);
+  cull_step_reach(params->step_size, dims, stepReach);
+  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return base[(size_t)b] + tc[t]; }, mode, thr, reach, stepReach,
+             needed_out, nullptr);
   return VR_OK;
 }
 

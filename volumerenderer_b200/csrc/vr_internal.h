@@ -80,7 +80,8 @@ struct vr_decode_plan {
   std::vector<int32_t> tileCellHost;
   struct Lazy {
     bool built = false;
-    int thr = 0, reach[3] = {0, 0, 0};   // cache key
+    int mode = 0, thr = 0, reach[3] = {0, 0, 0}, stepReach[3] = {0, 0, 0};   // cache key
+    uint8_t* solidDev = nullptr;  // per occupancy cell of dst: 1 = "solid-high" look-up cell (kd_cull.h), isosurface only
     vr_kd_work* workDev = nullptr; int nWork = 0;
     vr_fill_job* fillJobsDev = nullptr; int nFill = 0;
     int64_t* occSetDev = nullptr; int nOccSet = 0;  // (cell, max) pairs of the tiles left out
@@ -101,11 +102,13 @@ int peer_targets(struct ::vr_peer* p, int slot, PeerTargets* t, int64_t* windowB
 int volume_occ_alloc(vr_volume* v);                       // allocate the grids for the current cellOrigin
 int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out);  // build / refresh as needed; out->dil = null when off
 // the march of vr_render without the partial-volume check (lazy path)
+// solidMaskDev (optional, one byte per occupancy cell): look-up cells where the iso crossing test cannot fire because
+// every reachable voxel is >= isoValue (kd_cull.h); the march skips the fetch there as it does in void cells
 int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_dev, int32_t* hit_dev,
-                  uint64_t* samples_dev, bool allowPartial);
+                  uint64_t* samples_dev, bool allowPartial, const uint8_t* solidMaskDev = nullptr);
 int skip_threshold_of(const vr_render_params* params, int* thr, int* mode);  // occupancy threshold of the frame's mode
 // (re)builds plan->lazy for (thr, reach): the work list without the tiles the frame cannot read (kd_cull.h)
-int plan_lazy_prepare(vr_decode_plan* plan, int thr, const int reach[3]);
+int plan_lazy_prepare(vr_decode_plan* plan, int mode, int thr, const int reach[3], const int stepReach[3]);
 int plan_lazy_run(vr_decode_plan* plan);  // decode launch over the lazy list + maxima of the tiles left out
 void volume_occ_written(vr_context* ctx, vr_volume* v, const int64_t lo[3], const int64_t ext[3]);  // a box of voxels was overwritten
 }
