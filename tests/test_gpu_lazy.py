@@ -99,7 +99,9 @@ def test_lazy_frame_is_bit_identical_and_leaves_culled_tiles_untouched(ctx, laye
         assert np.array_equal(out.cpu().numpy(), out2.cpu().numpy())
         assert np.array_equal(hit.cpu().numpy(), hit2.cpu().numpy())
         assert int(smp.item()) == int(smp2.item())
-        render.render_to_host(ctx, vol, p)  # complete again: allowed
+        # complete again: the plain march (no bounds from the index, no solid-high mask) is allowed and gives the same frame
+        plain, S3, hits3 = render.render_to_host(ctx, vol, p, want_hits=True)
+        assert np.array_equal(plain, out2.cpu().numpy()) and np.array_equal(hits3, hit2.cpu().numpy()) and S3 == int(smp2.item())
         if mode != render.COMPOSITE:
             assert (hit2.cpu().numpy() >= 0).any()
     plan.close()
@@ -154,6 +156,8 @@ def test_config3_full_size_64_bricks_1024(ctx):
     ctx.synchronize()
     assert torch.equal(out, out2) and torch.equal(hit, hit2) and int(smp.item()) == int(smp2.item())
     assert int((hit2 >= 0).sum().item()) > 1000
+    plain, S3, hits3 = render.render_to_host(ctx, vol, p, want_hits=True)  # plain march of the decoded volume, no index bounds
+    assert np.array_equal(plain, out2.cpu().numpy()) and np.array_equal(hits3, hit2.cpu().numpy()) and S3 == int(smp2.item())
     dec = vol.download()
     for b in (0, 27, 63):  # decode parity on a sample of bricks
         s = streams[b]

@@ -139,10 +139,23 @@ int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_par
 
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
                          int32_t* hit_dev, uint64_t* samples_dev) {
-  if (!plan) return fail(VR_ERR_ARG, "null plan");
+  if (!plan || !params) return fail(VR_ERR_ARG, "null plan");
   int rc = vr_decode_plan_run(plan);
   if (rc != VR_OK) return rc;
-  return vr_render(ctx, plan->dst, params, out_rgba_dev, hit_dev, samples_dev);
+  // the stream index bounds every tile from both sides, so the isosurface march can also skip look-up cells in which
+  // every reachable voxel is >= isoValue (kd_cull.h); the mask is cached in the plan per (isoValue, step_size)
+  const uint8_t* solid = nullptr;
+  vr_volume* d = plan->dst;
+  int thr = 0, mode = 0;
+  if (ctx == plan->ctx && skip_threshold_of(params, &thr, &mode) == VR_OK && mode != 0 && thr >= 0 && plan->occFused && d->skipping &&
+      d->occRaw && d->occEpoch == plan->occEpoch) {
+    const int64_t G[3] = {d->SX, d->SY, d->SZ};
+    int reach[3], stepReach[3];
+    cull_reach(mode, params->step_size, G, reach);
+    cull_step_reach(params->step_size, G, stepReach);
+    if (plan_lazy_prepare(plan, mode, thr, reach, stepReach) == VR_OK) solid = plan->lazy.solidDev;
+  }
+  return render_volume(ctx, d, params, out_rgba_dev, hit_dev, samples_dev, false, solid);
 }
 
 int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
