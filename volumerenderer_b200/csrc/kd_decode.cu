@@ -31,6 +31,10 @@ struct DecodeParams {
   // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
   uint8_t* occ;             // null = off
   const int32_t* tileCell;  // [2^Dt] cell of the tile relative to the cell of the brick's (0,0,0)
+  // stream staging (VrWinStage): ranges[cta] = {first 16-byte chunk, chunks} of the tile's stream segment, copied to
+  // shared memory at byte offset stripBytes by the whole CTA with 128-bit loads before the parsers start
+  const vr_stage_range* ranges;      // null = off
+  uint32_t stripBytes;
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
@@ -97,7 +101,18 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
-    if (p.variant == 0) vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
+    uint2 rg = make_uint2(0u, 0u);
+    if (p.ranges) rg = __ldg(reinterpret_cast<const uint2*>(p.ranges) + blockIdx.x);
+    if (rg.y) {  // CTA-uniform: stage the tile's stream segment, then parse out of shared memory
+      const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
+      const uint32_t stage = sbase + p.stripBytes;
+      for (uint32_t j = threadIdx.x; j < rg.y; j += blockDim.x) {
+        const uint4 v = __ldg(src + j);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + 16u * j), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+      }
+      __syncthreads();
+      vr_tile_phase1_v5_staged<true, uint32_t>(job, g, blk, threadIdx.x, sbase, stage - 16u * rg.x);
+    } else if (p.variant == 0) vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 10) vr_tile_phase1_v5<false, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 11) vr_tile_phase1_v4<true, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 5) vr_tile_phase1_v4<false, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
@@ -145,7 +160,7 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
 
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
-                             const int32_t* tileCell, const vr_fill_job* fillsDev) {
+                             const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -162,7 +177,9 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
     if (variant < 0) { const char* e = getenv("VR_DECODE_VARIANT"); variant = e ? atoi(e) : 0; }
     p.variant = variant;
   }
-  const size_t smem = kd_decode_smem_bytes(g);
+  p.ranges = stageBytes > 0 ? rangesDev : nullptr;
+  p.stripBytes = (uint32_t)kd_decode_smem_bytes(g);
+  const size_t smem = kd_decode_smem_bytes(g) + (p.ranges ? (size_t)stageBytes : 0);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -13,5 +13,8 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 // refer to (vals = first | count << 32).
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ = nullptr,
-                             const int32_t* tileCell = nullptr, const vr_fill_job* fillsDev = nullptr);
+                             const int32_t* tileCell = nullptr, const vr_fill_job* fillsDev = nullptr,
+                             const vr_stage_range* rangesDev = nullptr, int stageBytes = 0);
+// rangesDev (optional, one entry per CTA, kd_worklist.h): the stream segment a parse CTA copies into shared memory
+// before parsing (stageBytes of dynamic shared memory behind the strips); null / stageBytes 0 = parse from global memory.
 }  // namespace vr

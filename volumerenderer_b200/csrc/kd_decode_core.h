@@ -60,6 +60,12 @@ typedef struct vr_fill_job {
   int64_t occCell;   // occupancy cell of the first tile (members follow at +1), < 0 = none
 } vr_fill_job;
 
+// Stream segment a parse CTA stages in shared memory (VrWinStage): first 16-byte chunk of the brick's stream and the
+// number of chunks; {0, 0} = not staged.  Read as one 8-byte word by the kernel.
+typedef struct vr_stage_range {
+  uint32_t first, count;
+} vr_stage_range;
+
 // A tile the lazy decode leaves out (kd_cull.h): its occupancy cell and the exact maximum of its voxels.
 typedef struct vr_occ_set {
   int64_t cell;
@@ -604,6 +610,46 @@ struct VrWin96 {
   }
 };
 
+// The tile's whole stream segment staged in shared memory by the CTA (kd_decode.cu): the window refills from shared
+// memory, so the parser's dependent chain never waits on a global load -- its latency under a memory system that the
+// constant fills of the other CTAs keep saturated with writes is what made parsing and filling run one after the other
+// instead of side by side.  sbase = shared byte address of (virtual) word 0 of the stream, i.e. staged address - 4 * first
+// staged word; every word the parser can touch (the segment plus 3 words of look-ahead) is staged.
+struct VrWinStage {
+  uint32_t sbase;
+  uint32_t wi;  // next word to load
+  uint32_t cur, nxt;
+  int bo;
+  VR_HD static uint32_t lds(uint32_t addr) {
+#if defined(__CUDA_ARCH__)
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+#else
+    (void)addr;
+    return 0;
+#endif
+  }
+  VR_HD void init_staged(uint32_t sb, uint32_t sym) {
+    sbase = sb;
+    wi = sym >> 4;
+    cur = lds(sbase + 4u * wi);
+    nxt = lds(sbase + 4u * wi + 4u);
+    wi += 2;
+    bo = (int)(sym & 15) * 2;
+  }
+  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
+  VR_HD void skip(int nbits) {
+    bo += nbits;
+    if (bo >= 32) {
+      cur = nxt;
+      nxt = lds(sbase + 4u * wi);
+      ++wi;
+      bo -= 32;
+    }
+  }
+};
+
 // 1 = saturating add, 2 = saturating subtract, 0/3 = unchanged; no branches.
 VR_HD int vr_apply_bf(int parent, int code, int dist) {
   const int s = (code & 1) - (code >> 1);
@@ -854,6 +900,24 @@ VR_HD void vr_tile_phase1_v5(const vr_kd_job& job, const vr_kd_geom& g, uint32_t
   WIN rd;
   rd.init(job.words, off);
   vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
+}
+
+// v5 parser over a staged segment (VrWinStage): stageBase = shared byte address of virtual word 0
+template <bool CHAIN_LEN_ALU, typename SA>
+VR_HD void vr_tile_phase1_v5_staged(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips, uint32_t stageBase) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  const SA base = strips + leaf * pitch;
+  if (off == VR_PRUNED) {
+    const uint32_t word = (uint32_t)val * 0x01010101u;
+    for (uint32_t i = 0; i < (1u << g.leafBits); i += 4) VR_ST32(base + i, word);
+    return;
+  }
+  VrWinStage rd;
+  rd.init_staged(stageBase, off);
+  vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, VrWinStage>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
 }
 
 template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32, int PF = VR_PREFETCH_LINES>

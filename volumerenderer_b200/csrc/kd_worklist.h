@@ -29,7 +29,8 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
                               std::vector<vr_fill_job>* fills = nullptr, int attach = 0, const int64_t* origins = nullptr,
                               int lateMode = 0,
                               const int64_t* occBase = nullptr, const int32_t* tileCell = nullptr,
-                              const uint8_t* needed = nullptr, std::vector<vr_occ_set>* culled = nullptr) {
+                              const uint8_t* needed = nullptr, std::vector<vr_occ_set>* culled = nullptr,
+                              std::vector<vr_stage_range>* ranges = nullptr, int64_t stageBytes = 0) {
   struct Item { int64_t key; vr_kd_work w; };
   struct FItem { int64_t key; vr_kd_work w; vr_fill_job f; };
   std::vector<Item> items;
@@ -109,6 +110,23 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
   }
   out->resize(items.size());
   for (size_t i = 0; i < items.size(); ++i) (*out)[i] = items[i].w;
+  // ranges[i] = {first 16-byte chunk, chunks} of the stream segment parse CTA i stages in shared memory (VrWinStage):
+  // from the word of the tile's first symbol to 3 words past the word of its last one (the window's look-ahead);
+  // {0, 0} = not staged (constant group, or a segment larger than the staging area: that CTA parses from global memory)
+  if (ranges) {
+    ranges->assign(items.size(), vr_stage_range{0u, 0u});
+    const uint32_t tmask = (1u << g.Dt) - 1u;
+    for (size_t i = 0; i < items.size() && stageBytes > 0; ++i) {
+      const vr_kd_work& w = items[i].w;
+      if (w.L != VR_WORK_PARSE) continue;
+      const KdIndex& ix = *idx[w.id >> g.Dt];
+      const uint32_t blk = ix.tileLeafBlock[w.id & tmask];
+      const uint64_t begin = ix.blockSymBegin[blk], end = ix.blockSymEnd[blk];
+      if (end <= begin) continue;
+      const uint64_t c0 = (begin >> 4) >> 2, c1 = ((((end - 1) >> 4) + 3) >> 2) + 1;
+      if ((int64_t)(c1 - c0) * 16 <= stageBytes) (*ranges)[i] = vr_stage_range{(uint32_t)c0, (uint32_t)(c1 - c0)};
+    }
+  }
 }
 
 }  // namespace vr

@@ -172,8 +172,8 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
 void vr_decode_plan::lazy_free() {
-  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev) cudaSetDevice(ctx->device);
-  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev);
+  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.rangesDev) cudaSetDevice(ctx->device);
+  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev); cudaFree(lazy.rangesDev);
   lazy = Lazy();
 }
 
@@ -205,8 +205,10 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
   std::vector<vr_kd_work> work;
   std::vector<vr_fill_job> fills;
   std::vector<vr_occ_set> culled;
+  std::vector<vr_stage_range> ranges;
   kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                    env_int("VR_FILL_ATTACH", 2), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled);
+                    env_int("VR_FILL_ATTACH", 2), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
+                    &ranges, p->stageBytes);
   lz.tilesTotal = (int64_t)n * nt;
   lz.tilesWritten = lz.tilesTotal - (int64_t)culled.size();
   lz.bytesVoxels = lz.tilesWritten * ((int64_t)g.tx * g.ty * g.tz);
@@ -227,6 +229,10 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
   if (e == cudaSuccess && lz.nFill) {
     e = cudaMalloc((void**)&lz.fillJobsDev, sizeof(vr_fill_job) * fills.size());
     if (e == cudaSuccess) e = cudaMemcpy(lz.fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess && p->stageBytes > 0 && !ranges.empty()) {
+    e = cudaMalloc((void**)&lz.rangesDev, sizeof(vr_stage_range) * ranges.size());
+    if (e == cudaSuccess) e = cudaMemcpy(lz.rangesDev, ranges.data(), sizeof(vr_stage_range) * ranges.size(), cudaMemcpyHostToDevice);
   }
   if (e == cudaSuccess && lz.nOccSet) {
     static_assert(sizeof(vr_occ_set) == 16, "pairs of int64");
@@ -253,7 +259,7 @@ int plan_lazy_run(vr_decode_plan* p) {
   cudaError_t e = cudaSetDevice(p->ctx->device);
   if (e == cudaSuccess)
     e = kd_decode_launch(p->geom, p->jobsDev, lz.workDev, lz.nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, d->occRaw,
-                         p->tileCellDev, lz.fillJobsDev);
+                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes);
   if (e == cudaSuccess) e = occ_set_cells_launch(d->occRaw, lz.occSetDev, lz.nOccSet, p->ctx->stream);
   if (e != cudaSuccess) return fail_cuda(e, "lazy decode launch");
   d->occDilDirty = true;
@@ -339,11 +345,17 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     for (int i = 0; i < n; ++i) { idx[(size_t)i] = &jobStream[(size_t)i]->kd.index; offs[(size_t)i] = jobs[(size_t)i].dstOffset; }
     std::vector<vr_kd_work> work;
     std::vector<vr_fill_job> fills;
+    std::vector<vr_stage_range> ranges;
+    // experiment, off by default (VR_STAGE_KB = 8 / 16 turns it on): parse CTAs copy their tile's stream segment into shared
+    // memory first (VrWinStage).  Measured on the 120-brick slab: 8 KB 0.263 ms, 16 KB 0.275 ms against 0.267 ms without --
+    // the parser is bound by instruction issue, not by the latency of its stream loads, and the larger shared-memory
+    // footprint costs L1 hits of the chain table (profiles/r1_ab_stage.txt)
+    p->stageBytes = (vec16 && p->geom.fastPath && (kd_decode_smem_bytes(g) % 16) == 0) ? 1024 * env_int("VR_STAGE_KB", 0) : 0;
     std::vector<int64_t> ob((size_t)n);
     for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
     kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
                       env_int("VR_FILL_ATTACH", 2), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
-                      p->occFused ? tileCellHost.data() : nullptr);
+                      p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes);
     p->nWork = (int)work.size();
     p->nFill = (int)fills.size();
     p->streams = jobStream; p->origins.assign(origins, origins + 3 * (size_t)n); p->dstOffset = offs; p->occBase = ob;
@@ -354,7 +366,11 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
       e = cudaMalloc((void**)&p->fillJobsDev, sizeof(vr_fill_job) * fills.size());
       if (e == cudaSuccess) e = cudaMemcpy(p->fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
     }
-    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload work list"); }
+    if (e == cudaSuccess && p->stageBytes > 0 && !ranges.empty()) {
+      e = cudaMalloc((void**)&p->rangesDev, sizeof(vr_stage_range) * ranges.size());
+      if (e == cudaSuccess) e = cudaMemcpy(p->rangesDev, ranges.data(), sizeof(vr_stage_range) * ranges.size(), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); cudaFree(p->rangesDev); delete p; return fail_cuda(e, "upload work list"); }
   }
   e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
   if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
@@ -370,7 +386,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
   CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
-                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev));
+                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again
@@ -383,6 +399,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->workDev);
   cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
+  cudaFree(p->rangesDev);
   p->lazy_free();
   delete p;
   return VR_OK;

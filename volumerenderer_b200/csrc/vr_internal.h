@@ -73,6 +73,8 @@ struct vr_decode_plan {
   bool occFused = false;  // every tile of every job is one occupancy cell: the kernel keeps occRaw current
   int occEpoch = 0;
   int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
+  vr_stage_range* rangesDev = nullptr;      // per CTA: stream segment staged in shared memory (kd_worklist.h); null = off
+  int stageBytes = 0;
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
   // host copies kept for the lazy (view-dependent) work list, kd_cull.h
   std::vector<vr_stream*> streams;
@@ -84,6 +86,7 @@ struct vr_decode_plan {
     uint8_t* solidDev = nullptr;  // per occupancy cell of dst: 1 = "solid-high" look-up cell (kd_cull.h), isosurface only
     vr_kd_work* workDev = nullptr; int nWork = 0;
     vr_fill_job* fillJobsDev = nullptr; int nFill = 0;
+    vr_stage_range* rangesDev = nullptr;
     int64_t* occSetDev = nullptr; int nOccSet = 0;  // (cell, max) pairs of the tiles left out
     int64_t tilesTotal = 0, tilesWritten = 0, bytesVoxels = 0, bytesStream = 0;
   } lazy;
