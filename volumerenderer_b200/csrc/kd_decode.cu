@@ -8,6 +8,7 @@
 // (4x4x4 voxels), walk their stream segments independently (kd_decode_core.h), writing path-ordered
 // strips in shared memory; the CTA then gathers the strips into 16-byte row segments and stores
 // them with 128-bit writes, so every 32-byte DRAM sector of the slab is written exactly once.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstdlib>
@@ -35,6 +36,11 @@ struct DecodeParams {
   // shared memory at byte offset stripBytes by the whole CTA with 128-bit loads before the parsers start
   const vr_stage_range* ranges;      // null = off
   uint32_t stripBytes;
+  // attached constant groups stored by the TMA unit (kd_decode.h): row images live at byte offset tmaOff of the dynamic
+  // shared memory, VR_TMA_MAX_ATTACH images of (tx << 3) * VR_TMA_BOX_ROWS bytes
+  int useTma;
+  uint32_t tmaOff;
+  VrFillMaps maps;
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
@@ -58,8 +64,57 @@ __device__ __forceinline__ void attached_fills(const DecodeParams& p, uint32_t f
   }
 }
 
+// TMA variant of attached_fills: the CTA writes one row image per group ((tx << L) x 8 bytes) into shared memory, warp 0
+// issues the tensor stores (64 per group: 16 slices x 4 row blocks, two per lane) and everybody goes on to parse; the
+// issuing lanes wait for their bulk groups right before the CTA exits.  Must be called by all threads of the CTA.
+__device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32_t first, uint32_t count, uint32_t smemBase) {
+  const uint32_t imgBytes = (uint32_t)(p.g.tx << 3) * VR_TMA_BOX_ROWS;
+  const uint32_t ltx = (uint32_t)(31 - __clz(p.g.tx));
+  for (uint32_t k = 0; k < count; ++k) {
+    const vr_fill_job* fj = p.fills + first + k;
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(fj));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(fj) + 1);
+    const uint64_t vals = (uint64_t)b.x | ((uint64_t)b.y << 32);
+    const int64_t cell = (int64_t)((uint64_t)b.z | ((uint64_t)b.w << 32));
+    if (p.occ && cell >= 0 && threadIdx.x < (1u << a.w)) {
+      const uint32_t w = (uint32_t)((vals >> (8 * threadIdx.x)) & 0xFF) * 0x01010101u;
+      *reinterpret_cast<uint2*>(p.occ + (cell + threadIdx.x) * 8) = make_uint2(w, w);
+    }
+    const uint32_t lW = ltx + a.w;                                  // log2 row bytes of the group
+    const uint32_t pieces = ((uint32_t)VR_TMA_BOX_ROWS << lW) >> 4;  // 16-byte pieces of the image
+    const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
+    for (uint32_t q = threadIdx.x; q < pieces; q += blockDim.x) {
+      const uint32_t xb = (q << 4) & ((1u << lW) - 1u);
+      const uint32_t w = (uint32_t)((vals >> (8 * (xb >> ltx))) & 0xFF) * 0x01010101u;
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(img + 16u * q), "r"(w) : "memory");
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const uint32_t rowBlocks = (uint32_t)p.g.ty / VR_TMA_BOX_ROWS;
+    const uint32_t per = (uint32_t)p.g.tz * rowBlocks;  // stores per group
+    for (uint32_t k = 0; k < count; ++k) {
+      const vr_fill_job* fj = p.fills + first + k;
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(fj));
+      const void* tm = &p.maps.m[a.w][0];
+      const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
+      for (uint32_t s = threadIdx.x; s < per; s += 32) {
+        const int z = (int)a.z + (int)(s / rowBlocks), y = (int)a.y + (int)(s % rowBlocks) * VR_TMA_BOX_ROWS;
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tm), "r"((int)a.x), "r"(y), "r"(z),
+                     "r"(img)
+                     : "memory");
+      }
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+}
+__device__ __forceinline__ void attached_fills_tma_wait() {
+  if (threadIdx.x < 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
-  extern __shared__ __align__(16) uint8_t strips[];
+  extern __shared__ __align__(128) uint8_t strips[];
   __shared__ int64_t sTileBase;
   const vr_kd_geom& g = p.g;
   const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + blockIdx.x);  // {id, L, vals}
@@ -95,7 +150,9 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   // store them before parsing, the other half afterwards, so that at any time some CTAs of an SM write (HBM bound)
   // while the others parse (issue bound); with one order for all, the CTAs of a wave would fill and parse in step.
   const bool late = (wk.w >> 31) != 0;
-  if (!late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
+  const bool tma = p.useTma && (wk.w & 0x7FFFFFFFu) != 0;  // CTA-uniform
+  if (tma) attached_fills_tma(p, wk.z, wk.w & 0x7FFFFFFFu, (uint32_t)__cvta_generic_to_shared(strips));
+  else if (!late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
   const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   const uint32_t items = vr_tile_items(g);
   if (g.fastPath && p.vec16) {
@@ -141,7 +198,8 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
       m = __reduce_max_sync(0xFFFFFFFFu, m);
       if (lane == 0) p.occ[tile_cell(p, job, tile) * 8 + warp] = (uint8_t)m;
     }
-    if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
+    if (tma) attached_fills_tma_wait();
+    else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
     return;
   }
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
@@ -150,7 +208,8 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
   uint8_t* dst = p.dst + sTileBase;
   for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
     vr_tile_phase2_item(g, it, strips, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
-  if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
+  if (tma) attached_fills_tma_wait();
+  else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
 }
 
 size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
@@ -158,9 +217,39 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
   return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
 }
 
+typedef CUresult (*VrEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, VrFillMaps* out) {
+  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
+  static VrEncodeFn enc = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      f = nullptr;
+    }
+    return (VrEncodeFn)f;
+  }();
+  if (!enc || tx < 16 || (tx << 3) > 256 || ty % VR_TMA_BOX_ROWS) return false;
+  if (SX % 16 || ((uintptr_t)vol) % 16 || SX >= (int64_t(1) << 32) || SY >= (int64_t(1) << 32) || SZ >= (int64_t(1) << 32)) return false;
+  for (int L = 0; L <= 3; ++L) {
+    cuuint64_t dims[3] = {(cuuint64_t)SX, (cuuint64_t)SY, (cuuint64_t)SZ};
+    cuuint64_t strides[2] = {(cuuint64_t)SX, (cuuint64_t)SX * (cuuint64_t)SY};
+    cuuint32_t box[3] = {(cuuint32_t)(tx << L), (cuuint32_t)VR_TMA_BOX_ROWS, 1};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = enc(reinterpret_cast<CUtensorMap*>(&out->m[L][0]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+  }
+  return true;
+}
+
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
-                             const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes) {
+                             const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes,
+                             const VrFillMaps* tmaMaps) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -179,7 +268,14 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
   }
   p.ranges = stageBytes > 0 ? rangesDev : nullptr;
   p.stripBytes = (uint32_t)kd_decode_smem_bytes(g);
-  const size_t smem = kd_decode_smem_bytes(g) + (p.ranges ? (size_t)stageBytes : 0);
+  size_t smem = kd_decode_smem_bytes(g) + (p.ranges ? (size_t)stageBytes : 0);
+  p.useTma = 0; p.tmaOff = 0;
+  if (tmaMaps && fillsDev && vec16 && g.tx >= 16 && (g.tx << 3) <= 256 && g.ty % VR_TMA_BOX_ROWS == 0) {
+    p.useTma = 1;
+    p.maps = *tmaMaps;
+    p.tmaOff = (uint32_t)((smem + 127) & ~size_t(127));
+    smem = p.tmaOff + (size_t)VR_TMA_MAX_ATTACH * (size_t)(g.tx << 3) * VR_TMA_BOX_ROWS;
+  }
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

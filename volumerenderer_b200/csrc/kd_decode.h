@@ -5,6 +5,15 @@
 #include "kd_decode_core.h"
 
 namespace vr {
+// Four CUtensorMap over the destination slab (uint8, 3-D), box = (tx << L) x VR_TMA_BOX_ROWS x 1 for L = 0..3: the
+// constant groups attached to a parse CTA are stored by the TMA unit (cp.async.bulk.tensor) from a small row image in
+// shared memory while all eight warps of the CTA parse -- the fills then cost the parser neither issue slots nor CTA
+// slots (it needs all six CTAs per SM to hide its latency).
+#define VR_TMA_BOX_ROWS 8
+#define VR_TMA_MAX_ATTACH 4
+struct VrFillMaps { alignas(64) unsigned char m[4][128]; };
+// false when the driver entry point is missing or the slab cannot be described (fills then use ordinary stores)
+bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, VrFillMaps* out);
 size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 // Decodes the prepared streams jobsDev[] into dst (slab, x fastest; rowPitch = slab X, slicePitch = slab X*Y),
 // one CTA per entry of workDev (kd_worklist.h).  Asynchronous on `stream`.  occ (optional): raw occupancy grid
@@ -14,7 +23,8 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ = nullptr,
                              const int32_t* tileCell = nullptr, const vr_fill_job* fillsDev = nullptr,
-                             const vr_stage_range* rangesDev = nullptr, int stageBytes = 0);
+                             const vr_stage_range* rangesDev = nullptr, int stageBytes = 0,
+                             const VrFillMaps* tmaMaps = nullptr);
 // rangesDev (optional, one entry per CTA, kd_worklist.h): the stream segment a parse CTA copies into shared memory
 // before parsing (stageBytes of dynamic shared memory behind the strips); null / stageBytes 0 = parse from global memory.
 }  // namespace vr

@@ -30,7 +30,8 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
                               int lateMode = 0,
                               const int64_t* occBase = nullptr, const int32_t* tileCell = nullptr,
                               const uint8_t* needed = nullptr, std::vector<vr_occ_set>* culled = nullptr,
-                              std::vector<vr_stage_range>* ranges = nullptr, int64_t stageBytes = 0) {
+                              std::vector<vr_stage_range>* ranges = nullptr, int64_t stageBytes = 0,
+                              int only = 0 /* timing experiments: 1 = parse tiles only, 2 = constant fills only */) {
   struct Item { int64_t key; vr_kd_work w; };
   struct FItem { int64_t key; vr_kd_work w; vr_fill_job f; };
   std::vector<Item> items;
@@ -73,6 +74,7 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
           continue;
         }
       }
+      if ((only == 1 && !parse) || (only == 2 && parse)) continue;
       int ox, oy, oz;
       vr_tile_origin(g, t, &ox, &oy, &oz);
       int64_t key = dstOffset[b] + (int64_t)oz * slicePitch + (int64_t)oy * rowPitch + ox;

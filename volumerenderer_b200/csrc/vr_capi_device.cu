@@ -207,7 +207,7 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
   std::vector<vr_occ_set> culled;
   std::vector<vr_stage_range> ranges;
   kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                    env_int("VR_FILL_ATTACH", 2), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
+                    std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
                     &ranges, p->stageBytes);
   lz.tilesTotal = (int64_t)n * nt;
   lz.tilesWritten = lz.tilesTotal - (int64_t)culled.size();
@@ -259,7 +259,7 @@ int plan_lazy_run(vr_decode_plan* p) {
   cudaError_t e = cudaSetDevice(p->ctx->device);
   if (e == cudaSuccess)
     e = kd_decode_launch(p->geom, p->jobsDev, lz.workDev, lz.nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, d->occRaw,
-                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes);
+                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr);
   if (e == cudaSuccess) e = occ_set_cells_launch(d->occRaw, lz.occSetDev, lz.nOccSet, p->ctx->stream);
   if (e != cudaSuccess) return fail_cuda(e, "lazy decode launch");
   d->occDilDirty = true;
@@ -351,11 +351,15 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     // the parser is bound by instruction issue, not by the latency of its stream loads, and the larger shared-memory
     // footprint costs L1 hits of the chain table (profiles/r1_ab_stage.txt)
     p->stageBytes = (vec16 && p->geom.fastPath && (kd_decode_smem_bytes(g) % 16) == 0) ? 1024 * env_int("VR_STAGE_KB", 0) : 0;
+    // experiment VR_FILL_TMA = 1: the constant groups attached to parse CTAs are stored by the TMA unit
+    p->tma = env_int("VR_FILL_TMA", 0) != 0 && vec16 && p->geom.fastPath &&
+             kd_fill_maps_create(dst->dev, dst->SX, dst->SY, dst->SZ, g.tx, g.ty, &p->tmaMaps);
     std::vector<int64_t> ob((size_t)n);
     for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
     kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                      env_int("VR_FILL_ATTACH", 2), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
-                      p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes);
+                      std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
+                      p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes,
+                      env_int("VR_DECODE_ONLY", 0));
     p->nWork = (int)work.size();
     p->nFill = (int)fills.size();
     p->streams = jobStream; p->origins.assign(origins, origins + 3 * (size_t)n); p->dstOffset = offs; p->occBase = ob;
@@ -386,7 +390,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
   CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
-                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes));
+                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again

@@ -4,6 +4,7 @@
 #include <map>
 #include <vector>
 #include "../../include/vr_b200.h"
+#include "kd_decode.h"
 #include "kd_decode_core.h"
 #include "kd_stream.h"
 
@@ -73,6 +74,8 @@ struct vr_decode_plan {
   bool occFused = false;  // every tile of every job is one occupancy cell: the kernel keeps occRaw current
   int occEpoch = 0;
   int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
+  bool tma = false;                // attached constant groups go through the TMA unit (kd_decode.h)
+  vr::VrFillMaps tmaMaps;
   vr_stage_range* rangesDev = nullptr;      // per CTA: stream segment staged in shared memory (kd_worklist.h); null = off
   int stageBytes = 0;
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
