@@ -217,6 +217,19 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
   return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
 }
 
+__global__ void __launch_bounds__(256) kd_prefetch_l2_kernel(const uint8_t* const* __restrict__ ptrs, const uint32_t* __restrict__ lines) {
+  const uint8_t* base = ptrs[blockIdx.y];
+  const uint32_t n = lines[blockIdx.y];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(base + (size_t)i * 128));
+}
+
+cudaError_t kd_prefetch_l2_launch(const uint8_t* const* ptrsDev, const uint32_t* linesDev, int n, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  kd_prefetch_l2_kernel<<<dim3(32, (unsigned)n), 256, 0, stream>>>(ptrsDev, linesDev);
+  return cudaGetLastError();
+}
+
 typedef CUresult (*VrEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 

@@ -15,6 +15,9 @@ struct VrFillMaps { alignas(64) unsigned char m[4][128]; };
 // false when the driver entry point is missing or the slab cannot be described (fills then use ordinary stores)
 bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, VrFillMaps* out);
 size_t kd_decode_smem_bytes(const vr_kd_geom& g);
+// Pulls n device arenas (ptrs[i], lines[i] x 128 bytes) into L2 with evict-last priority: the prepared streams of a
+// plan (tens of MB, the L2 holds 126 MB) are then read by the parsers from L2 instead of DRAM.
+cudaError_t kd_prefetch_l2_launch(const uint8_t* const* ptrsDev, const uint32_t* linesDev, int n, cudaStream_t stream);
 // Decodes the prepared streams jobsDev[] into dst (slab, x fastest; rowPitch = slab X, slicePitch = slab X*Y),
 // one CTA per entry of workDev (kd_worklist.h).  Asynchronous on `stream`.  occ (optional): raw occupancy grid
 // of the slab (occupancy.h, 8 slots per cell); tileCell[tile] = cell of the tile relative to the brick's first

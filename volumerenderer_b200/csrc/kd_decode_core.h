@@ -345,7 +345,11 @@ VR_HD int vr_fill_group_of(const vr_kd_geom& g, const vr_kd_job& job, uint32_t t
 VR_HD void vr_store16_const(uint8_t* out, int val) {
 #if defined(__CUDA_ARCH__)
   const uint32_t w = (uint32_t)val * 0x01010101u;
+#if !defined(VR_FILL_PLAIN_STORES)  // streaming stores (st.global.cs, evict-first in L2): measured 0.256 vs 0.262 ms per slab
+  __stcs(reinterpret_cast<uint4*>(out), make_uint4(w, w, w, w));
+#else
   *reinterpret_cast<uint4*>(out) = make_uint4(w, w, w, w);
+#endif
 #else
   for (int i = 0; i < 16; ++i) out[i] = (uint8_t)val;
 #endif

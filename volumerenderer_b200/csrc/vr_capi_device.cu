@@ -376,6 +376,21 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     }
     if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); cudaFree(p->rangesDev); delete p; return fail_cuda(e, "upload work list"); }
   }
+  if (env_int("VR_L2_PREFETCH", 0)) {  // experiment: pull the plan's streams into L2 (evict-last) before every decode launch
+    std::vector<const uint8_t*> ptrs;
+    std::vector<uint32_t> lines;
+    for (vr_stream* s : jobStream) {
+      bool seen = false;
+      for (const uint8_t* q : ptrs) seen = seen || q == s->devImage;
+      if (!seen) { ptrs.push_back(s->devImage); lines.push_back((uint32_t)((s->imageBytes + 127) / 128)); }
+    }
+    p->nPrefetch = (int)ptrs.size();
+    e = cudaMalloc((void**)&p->pfPtrsDev, sizeof(void*) * ptrs.size());
+    if (e == cudaSuccess) e = cudaMemcpy(p->pfPtrsDev, ptrs.data(), sizeof(void*) * ptrs.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->pfLinesDev, 4 * lines.size());
+    if (e == cudaSuccess) e = cudaMemcpy(p->pfLinesDev, lines.data(), 4 * lines.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { p->nPrefetch = 0; (void)cudaGetLastError(); }
+  }
   e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
   if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
   e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
@@ -389,6 +404,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
+  if (p->nPrefetch) CU(kd_prefetch_l2_launch(p->pfPtrsDev, p->pfLinesDev, p->nPrefetch, p->ctx->stream));
   CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
                       occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
@@ -404,6 +420,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
   cudaFree(p->rangesDev);
+  cudaFree(p->pfPtrsDev); cudaFree(p->pfLinesDev);
   p->lazy_free();
   delete p;
   return VR_OK;
