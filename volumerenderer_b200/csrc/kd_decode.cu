@@ -41,6 +41,9 @@ struct DecodeParams {
   int useTma;
   uint32_t tmaOff;
   VrFillMaps maps;
+  // persistent launch with SM roles (kd_decode_persistent_kernel)
+  int nWork, nParse, fillEvery;
+  uint32_t* queue;
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
@@ -113,11 +116,10 @@ __device__ __forceinline__ void attached_fills_tma_wait() {
   if (threadIdx.x < 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
-__global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
-  extern __shared__ __align__(128) uint8_t strips[];
-  __shared__ int64_t sTileBase;
+// One work-list entry, executed by a whole CTA (strips = the CTA's dynamic shared memory, sTileBase = one shared word).
+__device__ __forceinline__ void decode_work_item(const DecodeParams& p, const uint32_t item, uint8_t* strips, int64_t& sTileBase) {
   const vr_kd_geom& g = p.g;
-  const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + blockIdx.x);  // {id, L, vals}
+  const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + item);  // {id, L, vals}
   const uint32_t brick = wk.x >> g.Dt;
   const uint32_t tile = wk.x & ((1u << g.Dt) - 1u);
   const vr_kd_job& job = p.jobs[brick];
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_co
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
     uint2 rg = make_uint2(0u, 0u);
-    if (p.ranges) rg = __ldg(reinterpret_cast<const uint2*>(p.ranges) + blockIdx.x);
+    if (p.ranges) rg = __ldg(reinterpret_cast<const uint2*>(p.ranges) + item);
     if (rg.y) {  // CTA-uniform: stage the tile's stream segment, then parse out of shared memory
       const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
       const uint32_t stage = sbase + p.stripBytes;
@@ -217,6 +219,44 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
   return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
 }
 
+__global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t strips[];
+  __shared__ int64_t sTileBase;
+  decode_work_item(p, blockIdx.x, strips, sTileBase);
+}
+
+// Persistent variant with SM roles: the work list holds the parse entries first ([0, nParse)) and the constant groups
+// behind them; CTAs on every fillEvery-th SM (by %smid) drain the fill queue first, all others the parse queue first, and
+// either kind helps the other once its own queue is empty.  While HBM is write-saturated a parse CTA's own 16 KB of voxel
+// stores wait behind whatever its SM has queued; confining the fills to a subset of the SMs keeps the other SMs' store
+// queues short (profiles/r1_decode_overlap.md).  queue[0] / queue[1] = next parse / fill entry, zeroed before the launch.
+__global__ void __launch_bounds__(256, 6) kd_decode_persistent_kernel(const __grid_constant__ DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t strips[];
+  __shared__ int64_t sTileBase;
+  __shared__ uint32_t sItem;
+  uint32_t smid;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  const uint32_t mine = (smid % (uint32_t)p.fillEvery) == 0 ? 1u : 0u;
+  const uint32_t base[2] = {0u, (uint32_t)p.nParse}, count[2] = {(uint32_t)p.nParse, (uint32_t)(p.nWork - p.nParse)};
+  for (;;) {
+    if (threadIdx.x == 0) {
+      uint32_t it = 0xFFFFFFFFu;
+      for (uint32_t t = 0; t < 2 && it == 0xFFFFFFFFu; ++t) {
+        const uint32_t q = mine ^ t;
+        if (count[q] == 0) continue;
+        const uint32_t k = atomicAdd(p.queue + q, 1u);
+        if (k < count[q]) it = base[q] + k;
+      }
+      sItem = it;
+    }
+    __syncthreads();
+    const uint32_t it = sItem;
+    __syncthreads();
+    if (it == 0xFFFFFFFFu) return;
+    decode_work_item(p, it, strips, sTileBase);
+  }
+}
+
 __global__ void __launch_bounds__(256) kd_prefetch_l2_kernel(const uint8_t* const* __restrict__ ptrs, const uint32_t* __restrict__ lines) {
   const uint8_t* base = ptrs[blockIdx.y];
   const uint32_t n = lines[blockIdx.y];
@@ -262,7 +302,7 @@ bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int t
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
                              const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes,
-                             const VrFillMaps* tmaMaps) {
+                             const VrFillMaps* tmaMaps, int nParse, int fillEvery, uint32_t* queueDev) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -292,6 +332,20 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+  }
+  p.nWork = nWork; p.nParse = nParse; p.fillEvery = fillEvery; p.queue = queueDev;
+  if (fillEvery > 0 && queueDev && nParse >= 0 && nParse <= nWork) {
+    static int numSMs = 0;
+    if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); }
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(kd_decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    cudaError_t e = cudaMemsetAsync(queueDev, 0, 2 * sizeof(uint32_t), stream);
+    if (e != cudaSuccess) return e;
+    const int ctas = numSMs * 6 < nWork ? numSMs * 6 : nWork;
+    kd_decode_persistent_kernel<<<(unsigned)ctas, 256, smem, stream>>>(p);
+    return cudaGetLastError();
   }
   kd_decode_tiles_kernel<<<(unsigned)nWork, 256, smem, stream>>>(p);
   return cudaGetLastError();

@@ -27,7 +27,9 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ = nullptr,
                              const int32_t* tileCell = nullptr, const vr_fill_job* fillsDev = nullptr,
                              const vr_stage_range* rangesDev = nullptr, int stageBytes = 0,
-                             const VrFillMaps* tmaMaps = nullptr);
+                             const VrFillMaps* tmaMaps = nullptr, int nParse = -1, int fillEvery = 0, uint32_t* queueDev = nullptr);
+// fillEvery > 0 (needs queueDev = 2 counters and a work list with its nParse parse entries first): persistent launch in which
+// every fillEvery-th SM works on the constant groups and the others on the parse tiles (kd_decode.cu).
 // rangesDev (optional, one entry per CTA, kd_worklist.h): the stream segment a parse CTA copies into shared memory
 // before parsing (stageBytes of dynamic shared memory behind the strips); null / stageBytes 0 = parse from global memory.
 }  // namespace vr

@@ -356,12 +356,17 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
              kd_fill_maps_create(dst->dev, dst->SX, dst->SY, dst->SZ, g.tx, g.ty, &p->tmaMaps);
     std::vector<int64_t> ob((size_t)n);
     for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
-    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                      std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
+    p->persistFillEvery = (vec16 && p->geom.fastPath) ? env_int("VR_DECODE_PERSIST", 0) : 0;
+    const bool persist = p->persistFillEvery > 0;  // parse entries first, no attached groups: two queues
+    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, persist ? 1 : env_int("VR_DECODE_ORDER", 0), &work, &fills,
+                      persist ? 0 : std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
                       p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes,
                       env_int("VR_DECODE_ONLY", 0));
     p->nWork = (int)work.size();
     p->nFill = (int)fills.size();
+    p->nParse = 0;
+    for (const vr_kd_work& w : work) p->nParse += w.L == VR_WORK_PARSE ? 1 : 0;
+    if (persist && cudaMalloc((void**)&p->queueDev, 2 * sizeof(uint32_t)) != cudaSuccess) { (void)cudaGetLastError(); p->persistFillEvery = 0; }
     p->streams = jobStream; p->origins.assign(origins, origins + 3 * (size_t)n); p->dstOffset = offs; p->occBase = ob;
     p->tileCellHost = tileCellHost;
     e = cudaMalloc((void**)&p->workDev, sizeof(vr_kd_work) * std::max<size_t>(work.size(), 1));
@@ -406,7 +411,8 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
   if (p->nPrefetch) CU(kd_prefetch_l2_launch(p->pfPtrsDev, p->pfLinesDev, p->nPrefetch, p->ctx->stream));
   CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
-                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr));
+                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr, p->nParse,
+                      p->queueDev ? p->persistFillEvery : 0, p->queueDev));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again
@@ -420,7 +426,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
   cudaFree(p->rangesDev);
-  cudaFree(p->pfPtrsDev); cudaFree(p->pfLinesDev);
+  cudaFree(p->pfPtrsDev); cudaFree(p->pfLinesDev); cudaFree(p->queueDev);
   p->lazy_free();
   delete p;
   return VR_OK;
