@@ -38,7 +38,8 @@ struct DecodeParams {
   uint32_t stripBytes;
   // attached constant groups stored by the TMA unit (kd_decode.h): row images live at byte offset tmaOff of the dynamic
   // shared memory, VR_TMA_MAX_ATTACH images of (tx << 3) * VR_TMA_BOX_ROWS bytes
-  int useTma;
+  int useTma;       // rows of a TMA box (0 = ordinary stores)
+  int skipParse;    // timing experiments: parse entries only issue their attached groups
   uint32_t tmaOff;
   VrFillMaps maps;
   // persistent launch with SM roles (kd_decode_persistent_kernel)
@@ -71,7 +72,8 @@ __device__ __forceinline__ void attached_fills(const DecodeParams& p, uint32_t f
 // issues the tensor stores (64 per group: 16 slices x 4 row blocks, two per lane) and everybody goes on to parse; the
 // issuing lanes wait for their bulk groups right before the CTA exits.  Must be called by all threads of the CTA.
 __device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32_t first, uint32_t count, uint32_t smemBase) {
-  const uint32_t imgBytes = (uint32_t)(p.g.tx << 3) * VR_TMA_BOX_ROWS;
+  const uint32_t boxRows = (uint32_t)p.useTma;
+  const uint32_t imgBytes = (uint32_t)(p.g.tx << 3) * boxRows;
   const uint32_t ltx = (uint32_t)(31 - __clz(p.g.tx));
   for (uint32_t k = 0; k < count; ++k) {
     const vr_fill_job* fj = p.fills + first + k;
@@ -84,7 +86,7 @@ __device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32
       *reinterpret_cast<uint2*>(p.occ + (cell + threadIdx.x) * 8) = make_uint2(w, w);
     }
     const uint32_t lW = ltx + a.w;                                  // log2 row bytes of the group
-    const uint32_t pieces = ((uint32_t)VR_TMA_BOX_ROWS << lW) >> 4;  // 16-byte pieces of the image
+    const uint32_t pieces = (boxRows << lW) >> 4;  // 16-byte pieces of the image
     const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
     for (uint32_t q = threadIdx.x; q < pieces; q += blockDim.x) {
       const uint32_t xb = (q << 4) & ((1u << lW) - 1u);
@@ -95,7 +97,7 @@ __device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
   if (threadIdx.x < 32) {
-    const uint32_t rowBlocks = (uint32_t)p.g.ty / VR_TMA_BOX_ROWS;
+    const uint32_t rowBlocks = (uint32_t)p.g.ty / boxRows;
     const uint32_t per = (uint32_t)p.g.tz * rowBlocks;  // stores per group
     for (uint32_t k = 0; k < count; ++k) {
       const vr_fill_job* fj = p.fills + first + k;
@@ -103,7 +105,7 @@ __device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32
       const void* tm = &p.maps.m[a.w][0];
       const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
       for (uint32_t s = threadIdx.x; s < per; s += 32) {
-        const int z = (int)a.z + (int)(s / rowBlocks), y = (int)a.y + (int)(s % rowBlocks) * VR_TMA_BOX_ROWS;
+        const int z = (int)a.z + (int)(s / rowBlocks), y = (int)a.y + (int)((s % rowBlocks) * boxRows);
         asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tm), "r"((int)a.x), "r"(y), "r"(z),
                      "r"(img)
                      : "memory");
@@ -155,6 +157,7 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
   const bool tma = p.useTma && (wk.w & 0x7FFFFFFFu) != 0;  // CTA-uniform
   if (tma) attached_fills_tma(p, wk.z, wk.w & 0x7FFFFFFFu, (uint32_t)__cvta_generic_to_shared(strips));
   else if (!late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
+  if (p.skipParse) { if (tma) attached_fills_tma_wait(); else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu); return; }
   const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   const uint32_t items = vr_tile_items(g);
   if (g.fastPath && p.vec16) {
@@ -273,7 +276,7 @@ cudaError_t kd_prefetch_l2_launch(const uint8_t* const* ptrsDev, const uint32_t*
 typedef CUresult (*VrEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, VrFillMaps* out) {
+bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, int rows, VrFillMaps* out) {
   static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
   static VrEncodeFn enc = [] {
     void* f = nullptr;
@@ -284,12 +287,12 @@ bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int t
     }
     return (VrEncodeFn)f;
   }();
-  if (!enc || tx < 16 || (tx << 3) > 256 || ty % VR_TMA_BOX_ROWS) return false;
+  if (!enc || tx < 16 || (tx << 3) > 256 || rows <= 0 || ty % rows) return false;
   if (SX % 16 || ((uintptr_t)vol) % 16 || SX >= (int64_t(1) << 32) || SY >= (int64_t(1) << 32) || SZ >= (int64_t(1) << 32)) return false;
   for (int L = 0; L <= 3; ++L) {
     cuuint64_t dims[3] = {(cuuint64_t)SX, (cuuint64_t)SY, (cuuint64_t)SZ};
     cuuint64_t strides[2] = {(cuuint64_t)SX, (cuuint64_t)SX * (cuuint64_t)SY};
-    cuuint32_t box[3] = {(cuuint32_t)(tx << L), (cuuint32_t)VR_TMA_BOX_ROWS, 1};
+    cuuint32_t box[3] = {(cuuint32_t)(tx << L), (cuuint32_t)rows, 1};
     cuuint32_t es[3] = {1, 1, 1};
     CUresult r = enc(reinterpret_cast<CUtensorMap*>(&out->m[L][0]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, es,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
@@ -302,7 +305,7 @@ bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int t
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
                              const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes,
-                             const VrFillMaps* tmaMaps, int nParse, int fillEvery, uint32_t* queueDev) {
+                             const VrFillMaps* tmaMaps, int nParse, int fillEvery, uint32_t* queueDev, int tmaRows) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -323,11 +326,16 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
   p.stripBytes = (uint32_t)kd_decode_smem_bytes(g);
   size_t smem = kd_decode_smem_bytes(g) + (p.ranges ? (size_t)stageBytes : 0);
   p.useTma = 0; p.tmaOff = 0;
-  if (tmaMaps && fillsDev && vec16 && g.tx >= 16 && (g.tx << 3) <= 256 && g.ty % VR_TMA_BOX_ROWS == 0) {
-    p.useTma = 1;
+  {
+    static int skip = -1;
+    if (skip < 0) { const char* e = getenv("VR_DECODE_ONLY"); skip = (e && atoi(e) == 3) ? 1 : 0; }
+    p.skipParse = skip;
+  }
+  if (tmaMaps && tmaRows > 0 && fillsDev && vec16 && g.tx >= 16 && (g.tx << 3) <= 256 && g.ty % tmaRows == 0) {
+    p.useTma = tmaRows;
     p.maps = *tmaMaps;
     p.tmaOff = (uint32_t)((smem + 127) & ~size_t(127));
-    smem = p.tmaOff + (size_t)VR_TMA_MAX_ATTACH * (size_t)(g.tx << 3) * VR_TMA_BOX_ROWS;
+    smem = p.tmaOff + (size_t)VR_TMA_MAX_ATTACH * (size_t)(g.tx << 3) * (size_t)tmaRows;
   }
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

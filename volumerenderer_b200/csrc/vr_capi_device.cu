@@ -207,7 +207,7 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
   std::vector<vr_occ_set> culled;
   std::vector<vr_stage_range> ranges;
   kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                    std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
+                    std::min(env_int("VR_FILL_ATTACH", 2), p->tma ? VR_TMA_MAX_ATTACH : 64), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
                     &ranges, p->stageBytes);
   lz.tilesTotal = (int64_t)n * nt;
   lz.tilesWritten = lz.tilesTotal - (int64_t)culled.size();
@@ -259,7 +259,8 @@ int plan_lazy_run(vr_decode_plan* p) {
   cudaError_t e = cudaSetDevice(p->ctx->device);
   if (e == cudaSuccess)
     e = kd_decode_launch(p->geom, p->jobsDev, lz.workDev, lz.nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, d->occRaw,
-                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr);
+                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr, -1, 0, nullptr,
+                         p->tmaRows);
   if (e == cudaSuccess) e = occ_set_cells_launch(d->occRaw, lz.occSetDev, lz.nOccSet, p->ctx->stream);
   if (e != cudaSuccess) return fail_cuda(e, "lazy decode launch");
   d->occDilDirty = true;
@@ -352,14 +353,15 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     // footprint costs L1 hits of the chain table (profiles/r1_ab_stage.txt)
     p->stageBytes = (vec16 && p->geom.fastPath && (kd_decode_smem_bytes(g) % 16) == 0) ? 1024 * env_int("VR_STAGE_KB", 0) : 0;
     // experiment VR_FILL_TMA = 1: the constant groups attached to parse CTAs are stored by the TMA unit
+    p->tmaRows = env_int("VR_TMA_ROWS", 8);
     p->tma = env_int("VR_FILL_TMA", 0) != 0 && vec16 && p->geom.fastPath &&
-             kd_fill_maps_create(dst->dev, dst->SX, dst->SY, dst->SZ, g.tx, g.ty, &p->tmaMaps);
+             kd_fill_maps_create(dst->dev, dst->SX, dst->SY, dst->SZ, g.tx, g.ty, p->tmaRows, &p->tmaMaps);
     std::vector<int64_t> ob((size_t)n);
     for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
     p->persistFillEvery = (vec16 && p->geom.fastPath) ? env_int("VR_DECODE_PERSIST", 0) : 0;
     const bool persist = p->persistFillEvery > 0;  // parse entries first, no attached groups: two queues
     kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, persist ? 1 : env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                      persist ? 0 : std::min(env_int("VR_FILL_ATTACH", p->tma ? 3 : 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
+                      persist ? 0 : std::min(env_int("VR_FILL_ATTACH", 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
                       p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes,
                       env_int("VR_DECODE_ONLY", 0));
     p->nWork = (int)work.size();
@@ -412,7 +414,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   if (p->nPrefetch) CU(kd_prefetch_l2_launch(p->pfPtrsDev, p->pfLinesDev, p->nPrefetch, p->ctx->stream));
   CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
                       occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr, p->nParse,
-                      p->queueDev ? p->persistFillEvery : 0, p->queueDev));
+                      p->queueDev ? p->persistFillEvery : 0, p->queueDev, p->tmaRows));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again

@@ -76,6 +76,7 @@ struct vr_decode_plan {
   int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
   const uint8_t** pfPtrsDev = nullptr; uint32_t* pfLinesDev = nullptr; int nPrefetch = 0;  // unique stream arenas (L2 prefetch)
   int persistFillEvery = 0, nParse = 0; uint32_t* queueDev = nullptr;  // persistent launch with SM roles (kd_decode.h)
+  int tmaRows = 8;
   bool tma = false;                // attached constant groups go through the TMA unit (kd_decode.h)
   vr::VrFillMaps tmaMaps;
   vr_stage_range* rangesDev = nullptr;      // per CTA: stream segment staged in shared memory (kd_worklist.h); null = off
