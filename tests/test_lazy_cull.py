@@ -101,3 +101,54 @@ def test_composite_keeps_every_tile_next_to_a_nonzero_one(layered):
             # hot cell H marks [H - 1, H + 1] for composite, so tile c is needed iff some cell in [c - 1, c + 1] is nonzero
             nb = cellmax[max(cz - 1, 0):cz + 2, max(cy - 1, 0):cy + 2, max(cx - 1, 0):cx + 2]
             assert bool(needed[b, t]) == bool(nb.max() > 0), (b, t)
+
+
+def _window_any(grid, below, above):
+    """out[k] = any grid[k - below .. k + above] per axis (axes z, y, x of a (cz, cy, cx) array), clipped to the grid."""
+    out = grid.copy()
+    for axis, (b, a) in zip((2, 1, 0), zip(below, above)):  # x, y, z
+        src = out
+        acc = np.zeros_like(src)
+        n = src.shape[axis]
+        for d in range(-b, a + 1):
+            lo, hi = max(0, -d), min(n, n - d)
+            if lo >= hi:
+                continue
+            dst_sl = [slice(None)] * 3
+            src_sl = [slice(None)] * 3
+            dst_sl[axis] = slice(lo, hi)
+            src_sl[axis] = slice(lo + d, hi + d)
+            acc[tuple(dst_sl)] |= src[tuple(src_sl)]
+        out = acc
+    return out
+
+
+@pytest.mark.parametrize("iso,step", [(40 / 255, (1 / 256, 1 / 256, 1 / 256)), (120 / 255, (1 / 64, 1 / 128, 1 / 32)),
+                                      (200 / 255, (1 / 512, 1 / 512, 1 / 512))])
+def test_iso_rule_equals_a_numpy_restatement(layered, iso, step):
+    """The separable window code of kd_cull.h against a direct numpy restatement of the rule:
+    fetch = (some cell of c + {0,1}^3 has max > thr) and (some voxel <= thr + 1 within stepReach of c);
+    needed = some fetching cell c with the tile in [c - ceil(reach/cs), c + ceil((reach+1)/cs)]."""
+    dims, streams, origins, dec = layered
+    X, Y, Z = dims
+    p = render.default_params(64, 64, render.ISOSURFACE, iso=iso, step=step)
+    needed, boxes = render.lazy_tile_mask(streams, origins, dims, p)
+    thr = int(np.ceil(iso * 255.0)) - 1
+    cs = (32, 32, 16)
+    G = (X, Y, Z)
+    cmax = dec.reshape(Z // 16, 16, Y // 32, 32, X // 32, 32).max(axis=(1, 3, 5))
+    cmin = dec.reshape(Z // 16, 16, Y // 32, 32, X // 32, 32).min(axis=(1, 3, 5))
+    ceil_div = lambda a, b: -(-a // b)
+    reach = [int(np.ceil((abs(s) + 0.01) * g)) + 1 for s, g in zip(step, G)]
+    sreach = [int(np.ceil(abs(s) * g)) + 1 for s, g in zip(step, G)]
+    hot, low = cmax > thr, cmin <= thr + 1
+    fetch = _window_any(hot, (0, 0, 0), (1, 1, 1))
+    fetch &= _window_any(low, [ceil_div(r, c) for r, c in zip(sreach, cs)], [ceil_div(r + 1, c) for r, c in zip(sreach, cs)])
+    want = _window_any(fetch, [ceil_div(r + 1, c) for r, c in zip(reach, cs)], [ceil_div(r, c) for r, c in zip(reach, cs)])
+    got = np.zeros_like(want)
+    for b in range(needed.shape[0]):
+        for t in range(needed.shape[1]):
+            cx, cy, cz = boxes[b, t] // np.array(cs)
+            got[cz, cy, cx] = bool(needed[b, t])
+    assert np.array_equal(got, want)
+    assert 0 < got.sum() < got.size
