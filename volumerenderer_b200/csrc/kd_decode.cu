@@ -175,6 +175,7 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
       __syncthreads();
       vr_tile_phase1_v5_staged<true, uint32_t>(job, g, blk, threadIdx.x, sbase, stage - 16u * rg.x);
     } else if (p.variant == 0) vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
+    else if (p.variant == 12) vr_tile_phase1_v5<true, uint32_t, VrWin128>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 10) vr_tile_phase1_v5<false, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 11) vr_tile_phase1_v4<true, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
     else if (p.variant == 5) vr_tile_phase1_v4<false, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);

@@ -614,6 +614,58 @@ struct VrWin96 {
   }
 };
 
+// 128-bit refills: the window proper is still (cur, nxt), but nxt is fed from a four-word register queue that one
+// 16-byte load fills when its last word has moved on -- a whole refill (16 symbols) before the first of the new
+// words is needed, so the load's latency is off the dependent chain, and every 32-byte sector of the stream is requested
+// twice instead of eight times (profiles/r1_decode_overlap.md: the 4-byte refills thrash L1 and wait on L2).
+// words must be 16-byte aligned; reads to the end of the 16-byte chunk after the one holding the last symbol.
+struct VrWin128 {
+  const uint4* w;  // next chunk to load
+  uint32_t cur, nxt;
+  uint32_t b0, b1, b2, b3;  // queue, b0 = next word
+  int left;                 // words left in the queue
+  int bo;
+  VR_HD static uint4 ld(const uint4* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+  }
+  VR_HD uint32_t pop() {
+    const uint32_t r = b0;
+    b0 = b1; b1 = b2; b2 = b3;
+    if (--left == 0) {
+      const uint4 q = ld(w);
+      ++w;
+      b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
+      left = 4;
+    }
+    return r;
+  }
+  VR_HD void init(const uint32_t* words, uint32_t sym) {
+    const uint32_t w0 = sym >> 4;
+    w = reinterpret_cast<const uint4*>(words) + (w0 >> 2);
+    const uint4 q = ld(w);
+    ++w;
+    b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
+    left = 4;
+    for (uint32_t k = 0; k < (w0 & 3u); ++k) (void)pop();
+    cur = pop();
+    nxt = pop();
+    bo = (int)(sym & 15) * 2;
+  }
+  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
+  VR_HD void skip(int nbits) {
+    bo += nbits;
+    if (bo >= 32) {
+      cur = nxt;
+      nxt = pop();
+      bo -= 32;
+    }
+  }
+};
+
 // The tile's whole stream segment staged in shared memory by the CTA (kd_decode.cu): the window refills from shared
 // memory, so the parser's dependent chain never waits on a global load -- its latency under a memory system that the
 // constant fills of the other CTAs keep saturated with writes is what made parsing and filling run one after the other
