@@ -619,15 +619,17 @@ struct VrWin96 {
 // words is needed, so the load's latency is off the dependent chain, and every 32-byte sector of the stream is requested
 // twice instead of eight times (profiles/r1_decode_overlap.md: the 4-byte refills thrash L1 and wait on L2).
 // words must be 16-byte aligned; reads to the end of the 16-byte chunk after the one holding the last symbol.
+struct alignas(16) VrChunk16 { uint32_t x, y, z, w; };  // uint4 without the CUDA headers (this file also compiles as plain C++)
 struct VrWin128 {
-  const uint4* w;  // next chunk to load
+  const VrChunk16* w;  // next chunk to load
   uint32_t cur, nxt;
   uint32_t b0, b1, b2, b3;  // queue, b0 = next word
   int left;                 // words left in the queue
   int bo;
-  VR_HD static uint4 ld(const uint4* p) {
+  VR_HD static VrChunk16 ld(const VrChunk16* p) {
 #if defined(__CUDA_ARCH__)
-    return __ldg(p);
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    return VrChunk16{v.x, v.y, v.z, v.w};
 #else
     return *p;
 #endif
@@ -636,7 +638,7 @@ struct VrWin128 {
     const uint32_t r = b0;
     b0 = b1; b1 = b2; b2 = b3;
     if (--left == 0) {
-      const uint4 q = ld(w);
+      const VrChunk16 q = ld(w);
       ++w;
       b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
       left = 4;
@@ -645,8 +647,8 @@ struct VrWin128 {
   }
   VR_HD void init(const uint32_t* words, uint32_t sym) {
     const uint32_t w0 = sym >> 4;
-    w = reinterpret_cast<const uint4*>(words) + (w0 >> 2);
-    const uint4 q = ld(w);
+    w = reinterpret_cast<const VrChunk16*>(words) + (w0 >> 2);
+    const VrChunk16 q = ld(w);
     ++w;
     b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
     left = 4;
