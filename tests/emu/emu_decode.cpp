@@ -66,7 +66,7 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   int rc = kd_prepare(s);
   if (rc != VR_OK) return rc;
   const vr_kd_geom& g = s->geom;
-  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 4, 0);
+  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 16, 0);  // the windows read a few words (VrWin128: two 16-byte chunks) past the end
   std::memcpy(words.data(), s->bits.data(), s->bits.size());
   vr_kd_job job;
   job.words = words.data();
@@ -120,6 +120,7 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
         else if (g_variant == 6) vr_tile_phase1_v4<false>(job, g, blk, t, strips.data());
         else if (g_variant == 11) vr_tile_phase1_v4<true, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
         else if (g_variant == 10) vr_tile_phase1_v5<false, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
+        else if (g_variant == 12) vr_tile_phase1_v5<true, uint8_t*, VrWin128>(job, g, blk, t, strips.data());
         else vr_tile_phase1_v5<true, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
       }
       for (uint32_t warp = 0; warp < 8; ++warp)
