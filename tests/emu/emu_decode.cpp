@@ -61,6 +61,13 @@ int emu_validate(void* p, long long* nodes) {
 // prepare + emulate the tile kernel into a slab of dims (SX,SY,SZ) at origin (ox,oy,oz)
 static int g_variant = 0;
 void emu_set_variant(int v) { g_variant = v; }
+// lazy (view-dependent) decode: the next emu_decode call drops the tiles whose byte in `needed` (2^Dt entries) is 0, as the
+// device path does (kd_worklist.h with a kd_cull.h mask), and reports the (cell, max) pairs of the dropped tiles
+static const uint8_t* g_needed = nullptr;
+static long long* g_culled_out = nullptr;
+static long long g_culled_cap = 0, g_culled_n = 0;
+void emu_set_lazy(const uint8_t* needed, long long* culled_out, long long cap) { g_needed = needed; g_culled_out = culled_out; g_culled_cap = cap; g_culled_n = 0; }
+long long emu_culled_count(void) { return g_culled_n; }
 int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ, long long ox, long long oy, long long oz, int vec16) {
   KdStream* s = static_cast<KdStream*>(p);
   int rc = kd_prepare(s);
@@ -89,7 +96,24 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   const KdIndex* idx = &s->index;
   std::vector<vr_fill_job> fills;
   const int64_t org[3] = {ox, oy, oz};
-  kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work, &fills, 4, org);
+  if (g_needed) {  // cells of 32x32x16 voxels on the slab's grid, the brick on a cell boundary (as vr_decode_plan_create requires)
+    if (g.tx != 32 || g.ty != 32 || g.tz != 16 || (ox & 31) || (oy & 31) || (oz & 15)) return VR_ERR_UNSUPPORTED;
+    const int64_t ncx = (SX + 31) >> 5, ncy = (SY + 31) >> 5;
+    const int64_t occBase = (ox >> 5) + ncx * ((oy >> 5) + ncy * (oz >> 4));
+    std::vector<int32_t> tileCell(size_t(1) << g.Dt);
+    for (uint32_t t = 0; t < tileCell.size(); ++t) {
+      int tx0, ty0, tz0;
+      vr_tile_origin(g, t, &tx0, &ty0, &tz0);
+      tileCell[t] = (int32_t)((tx0 >> 5) + ncx * ((ty0 >> 5) + ncy * (tz0 >> 4)));
+    }
+    std::vector<vr_occ_set> culled;
+    kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work, &fills, 2, org, 0, &occBase, tileCell.data(), g_needed,
+                      &culled);
+    g_culled_n = (long long)culled.size();
+    for (size_t i = 0; i < culled.size() && (long long)i < g_culled_cap; ++i) { g_culled_out[2 * i] = culled[i].cell; g_culled_out[2 * i + 1] = culled[i].value; }
+  } else {
+    kd_build_worklist(g, 1, &idx, &job.dstOffset, SX, SX * SY, vec16 != 0, 0, &work, &fills, 4, org);
+  }
   for (const vr_kd_work& wk : work) {
     const uint32_t tile = wk.id & ((1u << g.Dt) - 1u);
     int tox, toy, toz;

@@ -64,6 +64,9 @@ if EMU is not None:
     EMU.emu_validate.argtypes = [c_void_p, c_void_p]
     EMU.emu_decode.argtypes = [c_void_p, c_void_p] + [LL] * 6 + [c_int]
     EMU.emu_set_variant.argtypes = [c_int]
+    if hasattr(EMU, "emu_set_lazy"):
+        EMU.emu_set_lazy.argtypes = [c_void_p, c_void_p, LL]
+        EMU.emu_culled_count.restype = LL
     EMU.emu_check_chain_lut.restype = LL
     EMU.emu_check_chain_lut.argtypes = [ctypes.c_ulonglong]
 

@@ -152,3 +152,49 @@ def test_iso_rule_equals_a_numpy_restatement(layered, iso, step):
             got[cz, cy, cx] = bool(needed[b, t])
     assert np.array_equal(got, want)
     assert 0 < got.sum() < got.size
+
+
+def test_culled_work_list_on_the_cpu_emulation():
+    """The device path's work-list builder with a cull mask (kd_worklist.h), run by the CPU emulation of the decode
+    kernel (tests/emu): tiles the mask keeps are decoded bit-exactly, every member of a kept constant group too, all
+    other tiles are never written, and their (cell, exact maximum) pairs are reported for the occupancy grid."""
+    import ctypes
+    if oa.EMU is None or not hasattr(oa.EMU, "emu_set_lazy"):
+        pytest.skip("emulation harness not built")
+    X, Y, Z = 256, 256, 128
+    brick = synth.rm_brick(3, 4, 7)  # straddles the mixing layer: void, mixed and solid tiles
+    s, _ = vr.Stream.compress(brick, 1, 2)
+    p = render.default_params(64, 64, render.ISOSURFACE, iso=40 / 255)
+    needed, boxes = render.lazy_tile_mask([s], [(0, 0, 0)], (X, Y, Z), p)
+    needed = np.ascontiguousarray(needed[0])
+    assert 0 < needed.sum() < needed.size
+    mins, maxs, _ = render.stream_tile_bounds(s)
+    hd, dm, bits = s.header, s.distance_map, s.bits
+    rc, want = oa.oracle_levelcut(bits, hd.numActiveNodes, dm, hd.origTreeDepth, hd.maxTreeDepth, X, Y, Z)
+    assert rc == 0
+    h = oa.EMU.emu_from_memory(ctypes.byref(hd), dm.ctypes.data, bits.ctypes.data, bits.size)
+    slab = np.full((Z, Y, X), 0xEE, np.uint8)
+    culled = np.zeros((needed.size, 2), np.int64)
+    oa.EMU.emu_set_lazy(needed.ctypes.data, culled.ctypes.data, needed.size)
+    try:
+        assert oa.EMU.emu_decode(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 1) == 0
+        n = oa.EMU.emu_culled_count()
+    finally:
+        oa.EMU.emu_set_lazy(None, None, 0)
+        oa.EMU.emu_free(h)
+    cells = {}
+    for t, (ox, oy, oz) in enumerate(boxes[0]):
+        cells[(ox >> 5) + 8 * ((oy >> 5) + 8 * (oz >> 4))] = t
+    dropped = set()
+    for cell, value in culled[:n]:
+        t = cells[int(cell)]
+        assert not needed[t] and int(value) == int(maxs[t])
+        dropped.add(t)
+    assert len(dropped) == n > 0
+    for t, (ox, oy, oz) in enumerate(boxes[0]):
+        got = slab[oz:oz + 16, oy:oy + 32, ox:ox + 32]
+        if t in dropped:
+            assert (got == 0xEE).all(), t
+        else:  # needed, or a member of a constant group that has a needed member
+            assert np.array_equal(got, want[oz:oz + 16, oy:oy + 32, ox:ox + 32]), t
+    assert not any(needed[t] for t in dropped)
