@@ -51,6 +51,18 @@ long long emu_check_chain_lut(unsigned long long chainDist) {
       const int lo = (e >> 8) & 0xFF, hi = (e >> 16) & 0xFF;
       y = y < lo ? lo : y; y = y > hi ? hi : y;
       if (y != val || (int)(e >> 24) != L) ++bad;
+      // the same chain through the two-level table of variant 13 (symbols 0..4, then 5..6 or the identity)
+      const uint32_t m = (codes & (codes >> 1) & 0x1555u) | 0x1000u;
+      const uint32_t e1 = vr_chain_lut_entry((codes & 0x3FFu) | 0x3C00u, chainDist);
+      const uint32_t i2 = (m & 0x155u) ? 0xFu : ((codes >> 10) & 0xFu);
+      const uint32_t e2 = vr_chain_lut_entry(i2 | 0x30u, chainDist >> 40);
+      int z = x + (int)(int8_t)(e1 & 0xFF);
+      const int lo1 = (e1 >> 8) & 0xFF, hi1 = (e1 >> 16) & 0xFF;
+      z = z < lo1 ? lo1 : z; z = z > hi1 ? hi1 : z;
+      z += (int)(int8_t)(e2 & 0xFF);
+      const int lo2 = (e2 >> 8) & 0xFF, hi2 = (e2 >> 16) & 0xFF;
+      z = z < lo2 ? lo2 : z; z = z > hi2 ? hi2 : z;
+      if (z != val || (int)(((unsigned)__builtin_ctz(m)) >> 1) + 1 != L) ++bad;
     }
   }
   return bad;
@@ -85,8 +97,10 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   for (int h = 0; h <= g.leafBits && h < 8; ++h) job.treeDist |= (uint64_t)s->distanceMap[g.D0 - h] << (8 * h);
   for (int k = 1; k <= 7; ++k) job.chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
   job.dstOffset = (oz * SY + oy) * SX + ox;
-  std::vector<uint32_t> lut(1u << 14);
+  std::vector<uint32_t> lut((1u << 14) + VR_LUT2_ENTRIES);
   for (uint32_t i = 0; i < (1u << 14); ++i) lut[i] = vr_chain_lut_entry(i, job.chainDist);
+  for (uint32_t i = 0; i < 1024u; ++i) lut[VR_LUT2_OFF + i] = vr_chain_lut_entry(i | 0x3C00u, job.chainDist);
+  for (uint32_t i = 0; i < 16u; ++i) lut[VR_LUT2_OFF + 1024u + i] = vr_chain_lut_entry(i | 0x30u, job.chainDist >> 40);
   job.chainLut = lut.data();
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   std::vector<uint8_t> strips(lpt * ((1u << g.leafBits) + VR_LEAF_PITCH_PAD));
@@ -145,6 +159,7 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
         else if (g_variant == 11) vr_tile_phase1_v4<true, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
         else if (g_variant == 10) vr_tile_phase1_v5<false, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
         else if (g_variant == 12) vr_tile_phase1_v5<true, uint8_t*, VrWin128>(job, g, blk, t, strips.data());
+        else if (g_variant == 13) vr_tile_phase1_v5_l2<uint8_t*, VrWin32L>(job, g, blk, t, strips.data(), lut.data() + VR_LUT2_OFF, 0u);
         else vr_tile_phase1_v5<true, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
       }
       for (uint32_t warp = 0; warp < 8; ++warp)

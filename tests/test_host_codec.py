@@ -135,7 +135,7 @@ def test_chain_table_equals_sequential_chain_for_all_inputs():
         assert oa.EMU.emu_check_chain_lut(sum(d << (8 * k) for k, d in enumerate(dist))) == 0
 
 
-@pytest.mark.parametrize("variant,kind", [(0, "rm"), (1, "rm"), (2, "rm"), (3, "rm"), (4, "rm"), (5, "rm"), (6, "rm"), (10, "rm"), (11, "rm"), (12, "rm"), (12, "noise"), (0, "noise"), (0, "shell"), (4, "noise")])
+@pytest.mark.parametrize("variant,kind", [(0, "rm"), (1, "rm"), (2, "rm"), (3, "rm"), (4, "rm"), (5, "rm"), (6, "rm"), (10, "rm"), (11, "rm"), (12, "rm"), (12, "noise"), (13, "rm"), (13, "noise"), (13, "shell"), (0, "noise"), (0, "shell"), (4, "noise")])
 def test_emulated_fast_path_full_size_brick(variant, kind):
     """256x256x128 (tiles of 2^14 voxels): exercises the table-driven parsers and the warp-unit gather."""
     oa.EMU.emu_set_variant(variant)

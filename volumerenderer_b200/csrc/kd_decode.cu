@@ -45,6 +45,7 @@ struct DecodeParams {
   // persistent launch with SM roles (kd_decode_persistent_kernel)
   int nWork, nParse, fillEvery;
   uint32_t* queue;
+  uint32_t lutOff;  // variant 13: byte offset of the two-level chain table in the dynamic shared memory
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
@@ -165,7 +166,25 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
     uint2 rg = make_uint2(0u, 0u);
     if (p.ranges) rg = __ldg(reinterpret_cast<const uint2*>(p.ranges) + item);
-    if (rg.y) {  // CTA-uniform: stage the tile's stream segment, then parse out of shared memory
+    if (p.variant == 13) {  // two-level chain table in shared memory, stream staged when the segment fits
+      const uint32_t lutS = sbase + p.lutOff;
+      for (uint32_t i = threadIdx.x; i < VR_LUT2_ENTRIES; i += blockDim.x) {
+        const uint32_t v = __ldg(job.chainLut + VR_LUT2_OFF + i);
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(lutS + 4u * i), "r"(v) : "memory");
+      }
+      const uint32_t stage = sbase + p.stripBytes;
+      if (rg.y) {
+        const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
+        for (uint32_t j = threadIdx.x; j < rg.y; j += blockDim.x) {
+          const uint4 v = __ldg(src + j);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + 16u * j), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+        }
+      }
+      __syncthreads();
+      const uint32_t* lut2 = reinterpret_cast<const uint32_t*>((uintptr_t)lutS);
+      if (rg.y) vr_tile_phase1_v5_l2<uint32_t, VrWinStageL>(job, g, blk, threadIdx.x, sbase, lut2, stage - 16u * rg.x);
+      else vr_tile_phase1_v5_l2<uint32_t, VrWin32L>(job, g, blk, threadIdx.x, sbase, lut2, 0u);
+    } else if (rg.y) {  // CTA-uniform: stage the tile's stream segment, then parse out of shared memory
       const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
       const uint32_t stage = sbase + p.stripBytes;
       for (uint32_t j = threadIdx.x; j < rg.y; j += blockDim.x) {
@@ -337,6 +356,11 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
     p.maps = *tmaMaps;
     p.tmaOff = (uint32_t)((smem + 127) & ~size_t(127));
     smem = p.tmaOff + (size_t)VR_TMA_MAX_ATTACH * (size_t)(g.tx << 3) * (size_t)tmaRows;
+  }
+  p.lutOff = 0;
+  if (p.variant == 13) {
+    p.lutOff = (uint32_t)((smem + 15) & ~size_t(15));
+    smem = p.lutOff + 4u * VR_LUT2_ENTRIES + 64;
   }
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -563,6 +563,7 @@ VR_HD void vr_st32(uint8_t* addr, uint32_t val) { *reinterpret_cast<uint32_t*>(a
 #endif
 
 struct VrWin32 {
+  static constexpr bool kSmemLut = false;
   const uint32_t* w;  // next word to load
   uint32_t cur, nxt;
   int bo;             // bit offset into cur, 0..31
@@ -590,6 +591,7 @@ struct VrWin32 {
 // (profile of VrWin32: a third of the parser's stall samples were on the funnel shift that follows a refill).
 // Reads at most 3 words past the word that holds the last symbol consumed.
 struct VrWin96 {
+  static constexpr bool kSmemLut = false;
   const uint32_t* w;
   uint32_t cur, nxt, nn;
   int bo;
@@ -621,6 +623,7 @@ struct VrWin96 {
 // words must be 16-byte aligned; reads to the end of the 16-byte chunk after the one holding the last symbol.
 struct alignas(16) VrChunk16 { uint32_t x, y, z, w; };  // uint4 without the CUDA headers (this file also compiles as plain C++)
 struct VrWin128 {
+  static constexpr bool kSmemLut = false;
   const VrChunk16* w;  // next chunk to load
   uint32_t cur, nxt;
   uint32_t b0, b1, b2, b3;  // queue, b0 = next word
@@ -674,6 +677,7 @@ struct VrWin128 {
 // instead of side by side.  sbase = shared byte address of (virtual) word 0 of the stream, i.e. staged address - 4 * first
 // staged word; every word the parser can touch (the segment plus 3 words of look-ahead) is staged.
 struct VrWinStage {
+  static constexpr bool kSmemLut = false;
   uint32_t sbase;
   uint32_t wi;  // next word to load
   uint32_t cur, nxt;
@@ -706,6 +710,32 @@ struct VrWinStage {
       bo -= 32;
     }
   }
+};
+
+// Two-level chain table (variant 13): the 64 KB table above lives in L1/L2, and under the fills every look-up that misses
+// L1 waits on a busy L2.  A chain's effect x -> min(max(x + A, lo), hi) is closed under composition, so the 7-symbol
+// table splits into symbols 0..4 (1 024 entries) and symbols 5..6 (16 entries, used as the identity when the chain ended
+// earlier): 4 160 bytes that each parse CTA copies into its shared memory.  Layout behind the 16 384-entry table:
+// [VR_LUT2_OFF, +1024) level 1, [+1024, +1040) level 2; entries as vr_chain_lut_entry.
+#define VR_LUT2_OFF 16384u
+#define VR_LUT2_ENTRIES 1040u
+// lut = host pointer to the 1 040 entries (emulation) or, on the device, the shared byte address cast to a pointer
+VR_HD uint32_t vr_lut2_load(const uint32_t* lut, uint32_t idx) {
+#if defined(__CUDA_ARCH__)
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"((uint32_t)(uintptr_t)lut + 4u * idx));
+  return v;
+#else
+  return lut[idx];
+#endif
+}
+struct VrWin32L : VrWin32 {
+  static constexpr bool kSmemLut = true;
+  VR_HD void init2(const uint32_t* words, uint32_t, uint32_t sym) { init(words, sym); }
+};
+struct VrWinStageL : VrWinStage {
+  static constexpr bool kSmemLut = true;
+  VR_HD void init2(const uint32_t*, uint32_t stageBase, uint32_t sym) { init_staged(stageBase, sym); }
 };
 
 // 1 = saturating add, 2 = saturating subtract, 0/3 = unchanged; no branches.
@@ -886,6 +916,25 @@ struct VrSub<0, POS, CHAIN_LEN_ALU, SA, WIN> {  // one voxel with its refinement
   static VR_HD void run(WIN& rd, int pv, uint64_t treeDist, const uint32_t* lut, SA base, uint32_t& acc) {
     const uint32_t bits = rd.peek();
     const int c = (int)(bits & 3);
+    if constexpr (WIN::kSmemLut) {  // two-level table in shared memory (VR_LUT2_*)
+      const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;  // bit 2k: chain symbol k is a terminator
+      const int L = (VR_CTZ32(m) >> 1) + 1;
+      const uint32_t e1 = vr_lut2_load(lut, (bits >> 2) & 0x3FFu);
+      const uint32_t i2 = (m & 0x155u) ? 0xFu : ((bits >> 12) & 0xFu);  // chain ended within symbols 0..4: identity
+      const uint32_t e2 = vr_lut2_load(lut, 1024u + i2);
+      const bool leaf = c == 3;
+      rd.skip(leaf ? 2 : 2 + 2 * L);
+      int val = vr_apply_bf(pv, c, (int)(treeDist & 0xFF)) + (int)(int8_t)(e1 & 0xFF);
+      const int lo1 = (int)((e1 >> 8) & 0xFF), hi1 = (int)((e1 >> 16) & 0xFF);
+      val = val < lo1 ? lo1 : val;
+      val = val > hi1 ? hi1 : val;
+      val += (int)(int8_t)(e2 & 0xFF);
+      const int lo2 = (int)((e2 >> 8) & 0xFF), hi2 = (int)((e2 >> 16) & 0xFF);
+      val = val < lo2 ? lo2 : val;
+      val = val > hi2 ? hi2 : val;
+      acc |= (uint32_t)(leaf ? pv : val) << (8 * (POS & 3));
+      if ((POS & 3) == 3) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
+    } else {
     const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
     int L;
     if (CHAIN_LEN_ALU) {
@@ -902,6 +951,7 @@ struct VrSub<0, POS, CHAIN_LEN_ALU, SA, WIN> {  // one voxel with its refinement
     val = val > hi ? hi : val;
     acc |= (uint32_t)(leaf ? pv : val) << (8 * (POS & 3));
     if ((POS & 3) == 3) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
+    }
   }
 };
 
@@ -958,6 +1008,26 @@ VR_HD void vr_tile_phase1_v5(const vr_kd_job& job, const vr_kd_geom& g, uint32_t
   WIN rd;
   rd.init(job.words, off);
   vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
+}
+
+// v5 parser with the two-level chain table in shared memory; WIN = VrWin32L (stream from global memory) or VrWinStageL
+// (staged segment, stageBase as below); lut2 = the 1 040 entries (vr_lut2_load)
+template <typename SA, typename WIN>
+VR_HD void vr_tile_phase1_v5_l2(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips, const uint32_t* lut2,
+                                uint32_t stageBase) {
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
+  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
+  const int val = job.leafVal[(size_t)blk * lpt + leaf];
+  const SA base = strips + leaf * pitch;
+  if (off == VR_PRUNED) {
+    const uint32_t word = (uint32_t)val * 0x01010101u;
+    for (uint32_t i = 0; i < (1u << g.leafBits); i += 4) VR_ST32(base + i, word);
+    return;
+  }
+  WIN rd;
+  rd.init2(job.words, stageBase, off);
+  vr_decode_leaf_v5<true, SA, WIN>(rd, g.leafBits, val, job.treeDist, lut2, base);
 }
 
 // v5 parser over a staged segment (VrWinStage): stageBase = shared byte address of virtual word 0

@@ -57,8 +57,10 @@ namespace vr {
 int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out) {
   auto it = ctx->chainLuts.find(chainDist);
   if (it != ctx->chainLuts.end()) { *out = it->second; return VR_OK; }
-  std::vector<uint32_t> host(1u << 14);
+  std::vector<uint32_t> host((1u << 14) + VR_LUT2_ENTRIES);
   for (uint32_t i = 0; i < (1u << 14); ++i) host[i] = vr_chain_lut_entry(i, chainDist);
+  for (uint32_t i = 0; i < 1024u; ++i) host[VR_LUT2_OFF + i] = vr_chain_lut_entry(i | 0x3C00u, chainDist);         // symbols 0..4
+  for (uint32_t i = 0; i < 16u; ++i) host[VR_LUT2_OFF + 1024u + i] = vr_chain_lut_entry(i | 0x30u, chainDist >> 40);  // symbols 5..6
   uint32_t* dev = nullptr;
   CU(cudaMalloc((void**)&dev, host.size() * 4));
   cudaError_t e = cudaMemcpyAsync(dev, host.data(), host.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
