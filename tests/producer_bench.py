@@ -1,6 +1,7 @@
 """Stream producer timings on the GPU box: GPU producer (csrc/kd_build.cu) vs the host compressor (kd_compress.cpp)
 vs the UNMODIFIED reference build() (oracle/_ref, useThreads as main.cpp does), same bricks, streams compared.
-Usage: python tools/build_bench.py [reps]      (prints one JSON line per brick kind)"""
+Usage: python tests/producer_bench.py [reps]      (prints one JSON line per brick kind)
+TEST INFRASTRUCTURE (lives under tests/ because it times the oracle's reference build next to the product's producers)."""
 import json
 import os
 import sys
@@ -10,7 +11,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import volumerenderer_b200 as vr  # noqa: E402
 from volumerenderer_b200 import synth  # noqa: E402
 
