@@ -119,6 +119,65 @@ def dist_setup(n_gpus):
     return rank, world, local
 
 
+def frame_check_multi(args, ctx, vol, ops, descs, stored, frame, peers, p, rank, world, local):
+    """N > 1, after the timed region: the sort-last frame the step draws (same kernels, same exchange, same decoded
+    slabs) against the plain single-texture march -- the N = 1 kernel, itself parity-tested against the shader
+    restatement in tests/ -- of the WHOLE texture, which rank 0 assembles from every rank's owned box (NCCL send /
+    recv, outside every timed region).  Also reads every rank's peer-window error word (a wait that timed out).
+    Returns the dict emitted as `frame_check`; raises SystemExit above 1/255 or after a time-out."""
+    import torch
+    import torch.distributed as dist
+    import volumerenderer_b200 as vr
+    from volumerenderer_b200 import render
+    from volumerenderer_b200._lib import check, lib
+    from ctypes import c_int64, c_void_p
+    dev = torch.device("cuda", local)
+    img = frame().clone()
+    ctx.synchronize(); torch.cuda.synchronize()
+    to = torch.tensor([max([int(bool(q.timed_out())) for q in peers if q is not None] or [0])], device=dev)
+    dist.all_reduce(to, op=dist.ReduceOp.MAX)
+    d, (so, se) = descs[rank], stored[rank]
+    ext = [int(d.own_hi[a] - d.own_lo[a]) for a in range(3)]
+    own = ops.pack_box([int(d.own_lo[a] - so[a]) for a in range(3)], ext)
+    ctx.synchronize(); torch.cuda.synchronize()
+    res = None
+    if rank == 0:
+        G = [int(v) for v in descs[0].global_]
+        full = vr.Volume(ctx, *G)
+        tmp = torch.empty_like(own)
+        for r in range(world):
+            src = own
+            if r != 0:
+                dist.recv(tmp, src=r)
+                torch.cuda.synchronize()
+                src = tmp
+            lo = [int(descs[r].own_lo[a]) for a in range(3)]
+            er = [int(descs[r].own_hi[a] - descs[r].own_lo[a]) for a in range(3)]
+            check(lib.vr_volume_unpack_box(ctx.h, full.h, (c_int64 * 3)(*lo), (c_int64 * 3)(*er), c_void_p(src.data_ptr())))
+            ctx.synchronize()
+        ref = torch.empty((IMG, IMG, 4), dtype=torch.float32, device=dev)
+        render.render_device(ctx, full, p, ref.data_ptr())
+        ctx.synchronize(); torch.cuda.synchronize()
+        diff = (img.view(IMG, IMG, 4) - ref).abs()
+        diff = torch.where(torch.isnan(diff), torch.zeros_like(diff), diff)
+        res = {"max_abs": float(diff.max().item()), "rows": IMG, "pixels_differing_above_1e-4": int((diff.amax(-1) > 1e-4).sum().item()),
+               "timed_out": int(to.item()), "tolerance": 1.0 / 255.0,
+               "against": f"plain single-texture march (march_kernel, N=1 path) of the whole {G[0]}x{G[1]}x{G[2]} texture gathered on rank 0",
+               "nontrivial_pixels": int(((ref[..., :3] - 1.0).abs().amax(-1) > 1e-3).sum().item())}
+        del full, tmp
+    else:
+        dist.send(own, dst=0)
+    ok = torch.tensor([1 if (res is None or (res["max_abs"] <= 1.0 / 255.0 and res["timed_out"] == 0 and res["nontrivial_pixels"] > 0)) else 0],
+                      device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if int(ok.item()) == 0 or int(to.item()) != 0:
+        if rank == 0:
+            sys.stderr.write(f"bench.py: frame_check FAILED: {res}\n")
+        dist.barrier()
+        raise SystemExit(3)
+    return res
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -239,6 +298,7 @@ def run_ours(args):
     # issue-bound and (N > 1) the frame spends much of its time waiting for peers, so the two overlap well.  Every step
     # still decodes its 120 bricks and draws one frame of a freshly decoded slab; a pair of steps is one graph replay.
     pair = None
+    peerF = None
     if args.pipeline and (world == 1 or peer is not None):
         try:
             f_stream = torch.cuda.Stream(priority=-1)
@@ -313,6 +373,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_step = total_ms / args.steps
+    frame_check = frame_check_multi(args, ctx, vol, ops, descs, stored, frame, [peer, peerF], p, rank, world, local) if world > 1 else None
     voxels_rank = by["voxels"]
     voxels_all = voxels_rank * world
 
@@ -441,7 +502,7 @@ def run_ours(args):
         # own kernels per step: decode, 3 occupancy refresh, march; N > 1 over NCCL: partial, resolve, finish instead of march;
         # N > 1 over peer windows (rank 0, one neighbour): decode, halo put + wait + box reduce, 3 occupancy, partial, gather put +
         # wait, resolve, reduce-scatter put + wait + combine, all-gather put + wait, finish = 17
-        "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
+        "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "frame_check": frame_check, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)

@@ -7,6 +7,7 @@
 #include "../../volumerenderer_b200/csrc/kd_stream.h"
 #include "../../volumerenderer_b200/csrc/kd_decode_core.h"
 #include "../../volumerenderer_b200/csrc/kd_worklist.h"
+#include "../../volumerenderer_b200/csrc/kd_parse6.h"
 
 using namespace vr;
 
@@ -170,5 +171,126 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
     for (uint32_t it = 0; it < items; ++it) vr_tile_phase2_item(g, it, strips.data(), dst, SX, SX * SY, vec16 != 0);
   }
   return VR_OK;
+}
+
+// ---- the persistent kernel's parser (kd_parse6.h), thread by thread -------------------------------------------------------
+// stageChunks: capacity of the staging area in 16-byte chunks (tiles with longer segments go through WinGlobal, as on the
+// device); needed/culled as in emu_set_lazy.  stats (optional, 4 values): parse tiles, tiles parsed from global memory,
+// constant groups, shared-memory bank-conflict wavefronts of the chain-table look-ups are NOT modelled here.
+}  // extern "C"
+template <int ROT>
+static void emu6_tile(const vr_kd_job& job, const vr_parse_item& it, const vr6::P6Geom& pg, const vr6::Dist& d, std::vector<uint8_t>& smem,
+                      uint32_t lutOff, uint32_t stripOff, uint32_t stageOff, uint8_t* slab, int64_t SX, int64_t SY) {
+  vr6::Mem::base() = smem.data();
+  const uint32_t stageBase = stageOff - 16u * it.seg0;  // shared address of virtual word 0 (wraps)
+  if (it.segChunks) std::memcpy(smem.data() + stageOff, reinterpret_cast<const uint8_t*>(job.words) + 16ull * it.seg0, 16ull * it.segChunks);
+  std::fill(smem.begin() + stripOff, smem.begin() + stripOff + VR6_STRIPS_BYTES, 0xEE);
+  for (uint32_t t = 0; t < 256; ++t) {
+    const uint32_t off = job.leafOff[(size_t)it.blk * 256 + t];
+    const uint32_t val = job.leafVal[(size_t)it.blk * 256 + t];
+    const uint32_t strip = stripOff + t * VR6_STRIP_PITCH;
+    if (off == VR_PRUNED) { vr6::fill_leaf(strip, val); continue; }
+    if (it.segChunks) {
+      vr6::WinShared w;
+      w.init(stageBase, nullptr, off);
+      vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
+    } else {
+      vr6::WinGlobal w;
+      w.init(0, job.words, off);
+      vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
+    }
+  }
+  for (uint32_t w = 0; w < 8; ++w)
+    for (uint32_t m = 0; m < 128; ++m) {
+      uint32_t sOff; int64_t gOff;
+      vr6::p6_run_addr(pg, w, m, SX, SX * SY, &sOff, &gOff);
+      uint8_t* out = slab + it.dst + gOff;
+      for (uint32_t j = 0; j < 4; ++j) {
+        const uint32_t a = stripOff + sOff + ((j & 1u) ? pg.xs[0] : 0u) + ((j & 2u) ? pg.xs[1] : 0u);
+        std::memcpy(out + 4 * j, smem.data() + a, 4);
+      }
+    }
+}
+extern "C" {
+static long long g6_stats[4];
+void emu_decode6_stats(long long* out) { std::memcpy(out, g6_stats, sizeof(g6_stats)); }
+int emu_decode6(void* p, uint8_t* slab, long long SX, long long SY, long long SZ, long long ox, long long oy, long long oz, int stageChunks) {
+  KdStream* s = static_cast<KdStream*>(p);
+  int rc = kd_prepare(s);
+  if (rc != VR_OK) return rc;
+  const vr_kd_geom& g = s->geom;
+  vr6::P6Geom pg;
+  if (!vr6::p6_make_geom(g, &pg) || (SX % 16) || (ox % 16)) return VR_ERR_UNSUPPORTED;
+  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 16, 0);
+  std::memcpy(words.data(), s->bits.data(), s->bits.size());
+  vr_kd_job job{};
+  job.words = words.data();
+  job.tileLeafBlock = s->index.tileLeafBlock.data();
+  job.tileVal = s->index.tileVal.data();
+  job.leafOff = s->index.leafOff.data();
+  job.leafVal = s->index.leafVal.data();
+  uint64_t chainDist = 0;
+  for (int k = 1; k <= 7; ++k) chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
+  job.dstOffset = (oz * SY + oy) * SX + ox;
+  vr6::Dist d{s->distanceMap[g.D0], s->distanceMap[g.D0 - 1], s->distanceMap[g.D0 - 2], s->distanceMap[g.D0 - 3], s->distanceMap[g.D0 - 4],
+              s->distanceMap[g.D0 - 5]};
+  const uint32_t lutOff = 0, stripOff = VR6_LUT_BYTES, stageOff = VR6_LUT_BYTES + ((VR6_STRIPS_BYTES + 15u) & ~15u);
+  std::vector<uint8_t> smem(stageOff + 16ull * (size_t)(stageChunks > 0 ? stageChunks : 1) + 64);
+  for (uint32_t i = 0; i < VR6_LUT_ENTRIES; ++i) { const uint32_t e = vr6::chain_entry(i, chainDist); std::memcpy(smem.data() + lutOff + 4 * i, &e, 4); }
+  const KdIndex* idx = &s->index;
+  const int64_t org[3] = {ox, oy, oz};
+  std::vector<vr_parse_item> parse;
+  std::vector<vr_fill_job> fills;
+  std::vector<vr_occ_set> culled;
+  int64_t occBase = -1;
+  std::vector<int32_t> tileCell;
+  if (g_needed) {
+    if (g.tx != 32 || g.ty != 32 || g.tz != 16 || (ox & 31) || (oy & 31) || (oz & 15)) return VR_ERR_UNSUPPORTED;
+    const int64_t ncx = (SX + 31) >> 5, ncy = (SY + 31) >> 5;
+    occBase = (ox >> 5) + ncx * ((oy >> 5) + ncy * (oz >> 4));
+    tileCell.resize(size_t(1) << g.Dt);
+    for (uint32_t t = 0; t < tileCell.size(); ++t) {
+      int tx0, ty0, tz0;
+      vr_tile_origin(g, t, &tx0, &ty0, &tz0);
+      tileCell[t] = (int32_t)((tx0 >> 5) + ncx * ((ty0 >> 5) + ncy * (tz0 >> 4)));
+    }
+  }
+  kd_build_worklist6(g, 1, &idx, &job.dstOffset, SX, SX * SY, org, g_needed ? &occBase : nullptr, g_needed ? tileCell.data() : nullptr, g_needed,
+                     g_needed ? &culled : nullptr, (uint32_t)(stageChunks > 0 ? stageChunks : 0), &parse, &fills);
+  g_culled_n = (long long)culled.size();
+  for (size_t i = 0; i < culled.size() && (long long)i < g_culled_cap; ++i) { g_culled_out[2 * i] = culled[i].cell; g_culled_out[2 * i + 1] = culled[i].value; }
+  g6_stats[0] = (long long)parse.size(); g6_stats[1] = 0; g6_stats[2] = (long long)fills.size(); g6_stats[3] = 0;
+  for (const vr_fill_job& f : fills)  // what the TMA unit stores: rows of (tx << L) bytes, tile j of the group takes byte j of vals
+    for (int z = 0; z < g.tz; ++z)
+      for (int y = 0; y < g.ty; ++y)
+        for (uint32_t j = 0; j < (1u << f.L); ++j)
+          std::memset(slab + ((int64_t)(f.z + z) * SY + (f.y + y)) * SX + f.x + (int64_t)j * g.tx, (int)((f.vals >> (8 * j)) & 0xFF), (size_t)g.tx);
+  for (const vr_parse_item& it : parse) {
+    if (!it.segChunks) ++g6_stats[1];
+    if (pg.rot == 0) emu6_tile<0>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
+    else if (pg.rot == 1) emu6_tile<1>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
+    else emu6_tile<2>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
+  }
+  return VR_OK;
+}
+// brute force: the chain table of kd_parse6.h equals the sequential saturating chain for every start value
+long long emu_check_chain_lut6(unsigned long long chainDist) {
+  long long bad = 0;
+  for (uint32_t codes = 0; codes < (1u << 14); ++codes) {
+    const uint32_t e = vr6::chain_entry(codes, chainDist);
+    for (int x = 0; x < 256; ++x) {
+      int val = x, L = 7;
+      for (int k = 0; k < 7; ++k) {
+        int c = (codes >> (2 * k)) & 3;
+        if (c == 3) { L = k + 1; break; }
+        val = vr_apply(val, c, (int)((chainDist >> (8 * k)) & 0xFF));
+      }
+      int y = x + ((int)e >> 24);
+      const int lo = (e >> 8) & 0xFF, hi = (e >> 16) & 0xFF;
+      y = y < lo ? lo : y; y = y > hi ? hi : y;
+      if (y != val || (int)(e & 0xFF) != 2 + 2 * L) ++bad;
+    }
+  }
+  return bad;
 }
 }

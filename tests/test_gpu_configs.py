@@ -100,12 +100,11 @@ def _build_streams(ctx, ijk, t=0, tol=1, epochs=2):
     return out, vols
 
 
-def test_config4_full_volume_960_bricks_sharded_over_8_virtual_ranks(ctx):
-    """Config 4 at full size: 2048 x 2048 x 1920, 960 bricks, tolerance 1 / 2 epochs, 1024^2 composite.  Single-texture
-    decode + frame on one device, and the same volume brick-sharded into 8 y-slabs (one per virtual rank) with halo
-    exchange and the sort-last composite.  Properties: slabs == single texture byte for byte; a sample of bricks
-    bit-exact vs levelCut; sort-last frame == single frame (fp32 re-association, < 1/255); rows of the single frame vs
-    the shader restatement on the downloaded volume."""
+@pytest.fixture(scope="module")
+def cfg4(ctx):
+    """Config 4 at full size, shared by the composite and the isosurface test: 2048 x 2048 x 1920, 960 bricks, tolerance
+    1 / 2 epochs, decoded once as a single texture and once brick-sharded into 8 y-slabs (one per virtual rank) whose
+    halo is wide enough for both modes (composite 1 row, isosurface 31 rows at 2048: SURVEY H7)."""
     GI, GJ, GK = synth.GRID
     ijk = [(i, j, k) for k in range(GK) for j in range(GJ) for i in range(GI)]
     streams, vols = _build_streams(ctx, ijk)
@@ -114,22 +113,12 @@ def test_config4_full_volume_960_bricks_sharded_over_8_virtual_ranks(ctx):
     plan = vr.DecodePlan(ctx, [streams[a] for a in ijk], [(i * BX, j * BY, k * BZ) for (i, j, k) in ijk], full)
     plan.run()
     ctx.synchronize()
-    for a in [(0, 0, 0), (3, 4, 7), (7, 7, 7), (5, 2, 8), (2, 6, 14)]:  # constant below, mixing layer, constant above
-        i, j, k = a
-        want = torch.from_numpy(_levelcut(streams[a])).cuda()
-        assert torch.equal(full_t[k * BZ:(k + 1) * BZ, j * BY:(j + 1) * BY, i * BX:(i + 1) * BX], want), a
     W = H = 1024
-    views = [render.default_params(W, H, render.COMPOSITE), render.oblique_params(W, H, render.COMPOSITE)]
-    single = []
-    for p in views:
-        out = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda:0")
-        torch.cuda.synchronize()
-        render.render_device(ctx, full, p, out.data_ptr())
-        ctx.synchronize()
-        single.append(out)
-    # 8 virtual ranks, y-slabs by brick row
+    views = {m: [render.default_params(W, H, m), render.oblique_params(W, H, m)] for m in (render.COMPOSITE, render.ISOSURFACE)}
     n = 8
-    halo = [max(a, b) for a, b in zip(*[sortlast.required_halo(p, G) for p in views])]
+    halos = [sortlast.required_halo(p, G) for m in views for p in views[m]]
+    halo = [max(h[a] for h in halos) for a in range(3)]
+    assert halo[1] >= 31  # the isosurface's look-ahead sample + gradient probes at 2048 (isosurface.frag:18,52-59,121)
     descs, stored = sortlast.slab_layout(G, n, axis=1, halo=halo)
     ops, keep = [], []
     for r in range(n):
@@ -143,22 +132,80 @@ def test_config4_full_volume_960_bricks_sharded_over_8_virtual_ranks(ctx):
         ops.append(sortlast.CudaSlabOps(ctx, sortlast.SortLast(ctx, descs, r), slab, W, H))
     sortlast.exchange_halos_lockstep(ops, descs, stored)
     ctx.synchronize(); torch.cuda.synchronize()
-    for r in range(n):  # owned rows + halo rows == the same rows of the single texture
-        o, e = stored[r]
-        assert torch.equal(keep[r][0], full_t[o[2]:o[2] + e[2], o[1]:o[1] + e[1], o[0]:o[0] + e[0]]), r
+    host = {}
+
+    def host_volume():  # one 7.5 GiB download, shared by the row checks of both tests
+        if "v" not in host:
+            host["v"] = full_t.cpu().numpy()
+        return host["v"]
+
+    yield dict(ijk=ijk, streams=streams, G=G, full_t=full_t, full=full, views=views, descs=descs, stored=stored, ops=ops, keep=keep,
+               W=W, H=H, host_volume=host_volume)
+    for _, pl in keep:
+        pl.close()
+    plan.close()
+
+
+def test_config4_full_volume_960_bricks_sharded_over_8_virtual_ranks(ctx, cfg4):
+    """Config 4, COMPOSITE.  Properties: slabs == single texture byte for byte; a sample of bricks bit-exact vs levelCut;
+    sort-last frame == single frame (fp32 re-association, < 1/255); rows of the single frame vs the shader restatement on
+    the downloaded volume."""
+    c = cfg4
+    full_t, full, streams = c["full_t"], c["full"], c["streams"]
+    for a in [(0, 0, 0), (3, 4, 7), (7, 7, 7), (5, 2, 8), (2, 6, 14)]:  # constant below, mixing layer, constant above
+        i, j, k = a
+        want = torch.from_numpy(_levelcut(streams[a])).cuda()
+        assert torch.equal(full_t[k * BZ:(k + 1) * BZ, j * BY:(j + 1) * BY, i * BX:(i + 1) * BX], want), a
+    W, H = c["W"], c["H"]
+    views = c["views"][render.COMPOSITE]
+    single = []
+    for p in views:
+        out = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda:0")
+        torch.cuda.synchronize()
+        render.render_device(ctx, full, p, out.data_ptr())
+        ctx.synchronize()
+        single.append(out)
+    for r in range(8):  # owned rows + halo rows == the same rows of the single texture
+        o, e = c["stored"][r]
+        assert torch.equal(c["keep"][r][0], full_t[o[2]:o[2] + e[2], o[1]:o[1] + e[1], o[0]:o[0] + e[0]]), r
     for p, one in zip(views, single):
-        frames = sortlast.render_frame_lockstep(ops, p)
+        frames = sortlast.render_frame_lockstep(c["ops"], p)
         torch.cuda.synchronize()
         for f in frames:
             assert float((f - one).abs().max().item()) < 1e-4 < TOL
     # the single-texture frame against the shader restatement, every 64th row, on the decoded volume
-    host = full_t.cpu().numpy()
+    host = c["host_volume"]()
     for p, one in zip(views, single):
         sel, want, _ = _oracle_rows(host, p, 64)
         assert np.abs(one.cpu().numpy()[sel] - want).max() <= TOL
-    for _, pl in keep:
-        pl.close()
-    plan.close()
+
+
+def test_config4_full_volume_isosurface_sharded_over_8_virtual_ranks(ctx, cfg4):
+    """Config 4, ISOSURFACE ("COMPOSITE (and ISOSURFACE)") at full size with the 31-row halo of SURVEY H7: the
+    sort-last first-hit frame of 8 virtual ranks is bit-identical to the single-texture frame (same taps, same
+    arithmetic: isosurface.frag:120-157), for the reference camera and the oblique view whose rays cross the slabs; rows
+    of the single frame against the shader restatement (hit / miss classification equal, hit index within one step,
+    colour <= 2/255 on agreeing hits: SURVEY B.5)."""
+    c = cfg4
+    W, H, full = c["W"], c["H"], c["full"]
+    host = c["host_volume"]()
+    for p in c["views"][render.ISOSURFACE]:
+        one = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda:0")
+        hit = torch.zeros((H, W), dtype=torch.int32, device="cuda:0")
+        torch.cuda.synchronize()
+        render.render_device(ctx, full, p, one.data_ptr(), hit.data_ptr())
+        ctx.synchronize()
+        assert int((hit >= 0).sum().item()) > 1000  # the interface is in view
+        frames = sortlast.render_frame_lockstep(c["ops"], p)
+        torch.cuda.synchronize()
+        for r, f in enumerate(frames):
+            same = (f == one) | (torch.isnan(f) & torch.isnan(one))
+            assert bool(same.all().item()), (r, int((~same).sum().item()))
+        sel, ref, ref_hits = _oracle_rows(host, p, 64)
+        got, gh = one.cpu().numpy()[sel], hit.cpu().numpy()[sel]
+        assert np.array_equal(gh >= 0, ref_hits >= 0) and (gh >= 0).any()
+        assert np.abs(gh - ref_hits).max() <= 1
+        assert np.nanmax(np.abs(got - ref)[gh == ref_hits]) <= 2 * TOL
 
 
 SWEEP = [(1, 6), (2, 4), (2, 2), (2, 1), (5, 1), (5, 0)]  # (maxEpochs, tolerance), SURVEY 8d config 5

@@ -60,6 +60,19 @@ typedef struct vr_fill_job {
   int64_t occCell;   // occupancy cell of the first tile (members follow at +1), < 0 = none
 } vr_fill_job;
 
+// One tile of the persistent kernel's parse queue (kd_decode.cu: kd_decode6_kernel; host: kd_build_worklist6); 48 bytes, read
+// as three 16-byte words.
+typedef struct vr_parse_item {
+  uint32_t brick, tile;  // job index, tile slot (path prefix of Dt bits)
+  uint32_t blk;          // tileLeafBlock[tile]: block of 256 leaf entries
+  uint32_t seg0;         // first 16-byte chunk of the tile's stream segment ...
+  uint32_t segChunks;    // ... and how many to stage in shared memory (0: the segment is too long, parse from global memory)
+  uint32_t pad0;
+  int64_t dst;           // voxel offset of the tile origin inside the destination slab
+  int64_t occCell;       // occupancy cell of the tile, < 0 = none
+  uint64_t pad1;
+} vr_parse_item;
+
 // Stream segment a parse CTA stages in shared memory (VrWinStage): first 16-byte chunk of the brick's stream and the
 // number of chunks; {0, 0} = not staged.  Read as one 8-byte word by the kernel.
 typedef struct vr_stage_range {

@@ -1,0 +1,351 @@
+// kd_parse6.h -- the leaf-subtree parser of the persistent decode kernel (kd_decode.cu), written as host/device code so
+// that tests/emu runs exactly this source thread by thread on the CPU (test harness only).
+//
+// What it parses: one depth-(D0-6) subtree of the preorder 2-bit stream that the reference's VolumeKdtree::levelCut walks
+// with a stack of boxes (/root/reference/volume_renderer/VolumeKdTree_recover.cpp:726-835): 63 inner nodes at most, 64
+// voxels, every voxel followed by its refinement chain (<= 7 symbols, :806-833).  One thread owns one such subtree (its
+// start offset and root value come from the side index, kd_stream.h) and writes the 4x4x4 voxels of its box, x fastest,
+// into a 64-byte block of shared memory; the CTA then stores whole 16-byte x-runs (kd_decode.cu, phase 2).
+//
+// Why it looks the way it does (profiles/r2_parser.md has the instruction counts):
+//  * values: a node's value is one of {parent, sat(parent + d), sat(parent - d), parent} selected by its symbol
+//    (:784-787).  The parent builds that "select word" once (2 fused add-min/max + 2 byte permutes) and each child is ONE
+//    byte permute -- instead of 6 ALU operations per node.
+//  * chains: one look-up in a 16 K-entry table (shared memory) gives the whole chain as x -> min(max(x + A, lo), hi) and
+//    the number of bits the voxel item occupies.
+//  * bit window: the three lowest levels of the tree (an octet: 7 nodes, 8 voxels) are straight-line code, so the
+//    places where the 32-bit window has to be re-aligned are known at compile time: 6 per octet instead of one per
+//    symbol, each branch-free (a refill is two predicated instructions).  Between them a token costs one shift.
+//  * stream words come from shared memory (the tile's segment is staged by a bulk copy) or, for the rare tile whose
+//    segment does not fit, from global memory through the same window type.
+#pragma once
+#include "kd_common.h"
+
+#if defined(__CUDA_ARCH__)
+#define VR6_DEV 1
+#else
+#define VR6_DEV 0
+#endif
+
+namespace vr6 {
+
+// ---- chain table ----------------------------------------------------------------------------------------------------
+// Entry for the 14 bits that follow a voxel's own symbol (7 chain symbols, LSB first):
+//   bits 0-7   number of stream bits of the whole voxel item (own symbol + chain symbols consumed) = 2 + 2 * L
+//   bits 8-15  lo, bits 16-23 hi, bits 24-31 A (signed): the chain maps x to min(max(x + A, lo), hi)
+// (a composition of saturating +-d steps is always of that form).  IDENT = the entry of "no chain" (own symbol 3).
+#define VR6_IDENT 0x00FF0002u
+VR_HD uint32_t chain_entry(uint32_t codes14, uint64_t chainDist) {
+  int A = 0, lo = 0, hi = 255, L = VR_ADD_LEVELS;
+  for (int k = 0; k < VR_ADD_LEVELS; ++k) {
+    const int c = (int)((codes14 >> (2 * k)) & 3);
+    if (c == 3) { L = k + 1; break; }
+    const int d = (int)((chainDist >> (8 * k)) & 0xFF);
+    const int a = c == 1 ? d : (c == 2 ? -d : 0);
+    A += a;
+    lo += a; lo = lo < 0 ? 0 : (lo > 255 ? 255 : lo);
+    hi += a; hi = hi < 0 ? 0 : (hi > 255 ? 255 : hi);
+  }
+  return (uint32_t)(2 + 2 * L) | ((uint32_t)lo << 8) | ((uint32_t)hi << 16) | ((uint32_t)(A & 0xFF) << 24);
+}
+#define VR6_LUT_ENTRIES 16384u
+#define VR6_LUT_BYTES 65536u
+
+// ---- memory policy: "shared" addresses are 32-bit byte addresses (device: the shared window; host emulation: offsets
+// into one array that stands for the CTA's shared memory) -----------------------------------------------------------------
+#if VR6_DEV
+struct Mem {
+  static __device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+  static __device__ __forceinline__ void st8(uint32_t a, uint32_t v) { asm volatile("st.shared.b8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+  static __device__ __forceinline__ void st16(uint32_t a, uint32_t v) { asm volatile("st.shared.b16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
+  static __device__ __forceinline__ void st32(uint32_t a, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+  static __device__ __forceinline__ uint32_t ldg32(const uint32_t* p) { return __ldg(p); }
+  static __device__ __forceinline__ uint32_t funnel(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
+  static __device__ __forceinline__ uint32_t perm(uint32_t a, uint32_t b, uint32_t s) { return __byte_perm(a, b, s); }
+};
+#else
+struct Mem {
+  static inline uint8_t*& base() { static thread_local uint8_t* b = nullptr; return b; }
+  static inline uint32_t lds32(uint32_t a) { uint32_t v; __builtin_memcpy(&v, base() + a, 4); return v; }
+  static inline void st8(uint32_t a, uint32_t v) { base()[a] = (uint8_t)v; }
+  static inline void st16(uint32_t a, uint32_t v) { uint16_t h = (uint16_t)v; __builtin_memcpy(base() + a, &h, 2); }
+  static inline void st32(uint32_t a, uint32_t v) { __builtin_memcpy(base() + a, &v, 4); }
+  static inline uint32_t ldg32(const uint32_t* p) { return *p; }
+  static inline uint32_t funnel(uint32_t lo, uint32_t hi, uint32_t s) { return (uint32_t)(((((uint64_t)hi) << 32) | (uint64_t)lo) >> (s & 31)); }
+  static inline uint32_t perm(uint32_t a, uint32_t b, uint32_t s) {
+    const uint64_t src = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t n = (s >> (4 * k)) & 0xF;
+      uint32_t byte = (uint32_t)(src >> (8 * (n & 7))) & 0xFF;
+      if (n & 8) byte = (byte & 0x80) ? 0xFF : 0x00;
+      r |= byte << (8 * k);
+    }
+    return r;
+  }
+};
+#endif
+
+// ---- bit windows ------------------------------------------------------------------------------------------------------
+// P = absolute bit position in the stream of the next unread symbol; (cur, nxt) = the stream words that hold bits
+// [32 * (P >> 5), +64).  advance_peek(n) consumes n <= 32 bits and returns the next 32 bits; crossing a word boundary is
+// the only conditional part (two moves and a load under one predicate, no branch).
+struct WinShared {  // stream segment staged in shared memory; base = shared address of (virtual) word 0 of the stream
+  uint32_t cur, nxt, P, wi;
+  VR_HD void init(uint32_t base, const uint32_t*, uint32_t sym) {
+    P = sym * 2u;
+    const uint32_t a = base + ((P >> 5) << 2);
+    cur = Mem::lds32(a);
+    nxt = Mem::lds32(a + 4u);
+    wi = a + 8u;
+  }
+  VR_HD uint32_t advance_peek(uint32_t n) {
+    const uint32_t Pn = P + n;
+    if ((P ^ Pn) & 32u) { cur = nxt; nxt = Mem::lds32(wi); wi += 4u; }
+    P = Pn;
+    return Mem::funnel(cur, nxt, P);
+  }
+};
+struct WinGlobal {  // stream words from global memory (tiles whose segment does not fit the staging area)
+  uint32_t cur, nxt, P;
+  const uint32_t* w;
+  VR_HD void init(uint32_t, const uint32_t* words, uint32_t sym) {
+    P = sym * 2u;
+    w = words + (P >> 5);
+    cur = Mem::ldg32(w);
+    nxt = Mem::ldg32(w + 1);
+    w += 2;
+  }
+  VR_HD uint32_t advance_peek(uint32_t n) {
+    const uint32_t Pn = P + n;
+    if ((P ^ Pn) & 32u) { cur = nxt; nxt = Mem::ldg32(w); ++w; }
+    P = Pn;
+    return Mem::funnel(cur, nxt, P);
+  }
+};
+
+// ---- geometry of a 4x4x4 leaf box -------------------------------------------------------------------------------------
+// The six lowest tree levels of the bricks this path accepts split x, y, z cyclically (VolumeKdTree_recover.cpp:151-163 with
+// all three extents still >= 4), so path bit b of a voxel inside its leaf box (bit 0 = last split) carries coordinate bit
+// b / 3 of axis (ROT - b) mod 3, ROT = (D0 - 1) mod 3.  Block layout: byte offset = x + 4 y + 16 z.
+template <int ROT>
+struct Geo {
+  static constexpr int axis(int b) { return ((ROT - b) % 3 + 3) % 3; }
+  static constexpr int bitOff(int b) { return (axis(b) == 0 ? 1 : (axis(b) == 1 ? 4 : 16)) << (b / 3); }
+  static constexpr int off(int path) {  // path: up to 6 bits
+    int o = 0;
+    for (int b = 0; b < 6; ++b) o += ((path >> b) & 1) ? bitOff(b) : 0;
+    return o;
+  }
+  static constexpr int xbit = (ROT + 3) % 3;  // the path bit (0..2) that carries x0: axis(b) == 0  <=>  b == ROT (mod 3)
+};
+
+// All 2^H voxels of the box of a height-H node (H <= 3) at static path position POS take `val`.
+template <int ROT, int H, int POS>
+VR_HD void fill_small(uint32_t base, uint32_t val) {
+  constexpr int xb = Geo<ROT>::xbit;
+  if constexpr (xb < H) {  // the box spans both x0 values: pairs of x neighbours as 16-bit stores
+    const uint32_t v2 = val * 0x0101u;
+#pragma unroll
+    for (int k = 0; k < (1 << H); ++k)
+      if (!((k >> xb) & 1)) Mem::st16(base + (uint32_t)Geo<ROT>::off(POS + k), v2);
+  } else {
+#pragma unroll
+    for (int k = 0; k < (1 << H); ++k) Mem::st8(base + (uint32_t)Geo<ROT>::off(POS + k), val);
+  }
+}
+// Octets [i, i + n) of the leaf box take `val` (pruned nodes above the octets; n = 1, 2, 4).
+template <int ROT>
+VR_HD void fill_octets(uint32_t strip, uint32_t i, uint32_t n, uint32_t val) {
+  for (uint32_t k = i; k < i + n; ++k) {
+    const uint32_t base = strip + ((k & 1u) ? (uint32_t)Geo<ROT>::bitOff(3) : 0u) + ((k & 2u) ? (uint32_t)Geo<ROT>::bitOff(4) : 0u) +
+                          ((k & 4u) ? (uint32_t)Geo<ROT>::bitOff(5) : 0u);
+    fill_small<ROT, 3, 0>(base, val);
+  }
+}
+
+// ---- values -----------------------------------------------------------------------------------------------------------
+// Select word of a node with value n whose children sit at a level with distance d: bytes (n, sat(n+d), sat(n-d), n), so
+// that a child with symbol c (0 same, 1 add, 2 subtract, 3 same-and-stop: VolumeKdTree_recover.cpp:784-787) is byte c.
+VR_HD int imin(int a, int b) { return a < b ? a : b; }
+VR_HD int imax(int a, int b) { return a > b ? a : b; }
+VR_HD uint32_t mkword(uint32_t n, uint32_t d) {
+  const int up = imin((int)n + (int)d, 255), dn = imax((int)n - (int)d, 0);
+  return Mem::perm(n, Mem::perm((uint32_t)up, (uint32_t)dn, 0x0040u), 0x0540u);
+}
+VR_HD uint32_t child(uint32_t word, uint32_t c) { return Mem::perm(word, 0u, c | 0x4440u); }
+
+struct Dist { uint32_t d0, d1, d2, d3, d4, d5; };  // d_h = distanceMap[D0 - h]: applied to nodes at height h
+
+// ---- the octet: straight-line code ------------------------------------------------------------------------------------
+// State threaded through the octet: `bits` = the window shifted so that the next token is at bit 0, `o` = bits consumed
+// since the last re-alignment.  REPEEK marks the static places where the window is re-aligned (see the header comment):
+// before voxels 1, 2, 5, 6 and before the second height-2 node.
+template <class WIN>
+struct Cur {
+  WIN& w;
+  uint32_t bits, o;
+  uint32_t lut;  // shared address of the chain table
+  VR_HD void repeek() { bits = w.advance_peek(o); o = 0; }
+};
+
+template <int ROT, int POS, class WIN>
+VR_HD void voxel(Cur<WIN>& s, uint32_t word, uint32_t base) {
+  if (POS == 1 || POS == 2 || POS == 5 || POS == 6) s.repeek();
+  const uint32_t c = s.bits & 3u;
+  uint32_t e = Mem::lds32(s.lut + (s.bits & 0xFFFCu));
+  e = c == 3u ? VR6_IDENT : e;
+  const int x = (int)child(word, c);
+  const int lo = (int)((e >> 8) & 0xFFu), hi = (int)((e >> 16) & 0xFFu);
+  int v = x + ((int)e >> 24);
+  v = imax(v, lo);
+  v = imin(v, hi);
+  Mem::st8(base + (uint32_t)Geo<ROT>::off(POS), (uint32_t)v);
+  const uint32_t nb = e & 0xFFu;
+  s.bits >>= nb;  // nb <= 16
+  s.o += nb;
+}
+
+template <int ROT, int H, int POS, class WIN>
+struct Node {  // H = 1 or 2
+  static VR_HD void run(Cur<WIN>& s, uint32_t word, const Dist& d, uint32_t base) {
+    if (H == 2 && POS == 4) s.repeek();
+    const uint32_t c = s.bits & 3u;
+    s.bits >>= 2;
+    s.o += 2u;
+    if (c == 3u) {
+      fill_small<ROT, H, POS>(base, word >> 24);
+    } else {
+      const uint32_t cw = mkword(child(word, c), H == 2 ? d.d1 : d.d0);
+      if constexpr (H == 2) {
+        Node<ROT, 1, POS, WIN>::run(s, cw, d, base);
+        Node<ROT, 1, POS + 2, WIN>::run(s, cw, d, base);
+      } else {
+        voxel<ROT, POS, WIN>(s, cw, base);
+        voxel<ROT, POS + 1, WIN>(s, cw, base);
+      }
+    }
+  }
+};
+
+// One leaf subtree.  The window stands on the root's own symbol (known to be an inner node; its value is rootVal).
+template <int ROT, class WIN>
+VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uint32_t strip) {
+  Cur<WIN> s{w, 0u, 2u, lut};  // o = 2: the root's symbol
+  const uint32_t word6 = mkword(rootVal, d.d5);
+  uint32_t word5 = 0, word4 = 0;
+  uint32_t i = 0;  // octet index inside the leaf box (path bits 5..3)
+  for (;;) {
+    s.repeek();
+    if ((i & 3u) == 0u) {  // a height-5 node starts here
+      const uint32_t c = s.bits & 3u;
+      s.bits >>= 2; s.o += 2u;
+      if (c == 3u) {
+        fill_octets<ROT>(strip, i, 4u, word6 >> 24);
+        i += 4u;
+        if (i == 8u) break;
+        continue;
+      }
+      word5 = mkword(child(word6, c), d.d4);
+    }
+    if ((i & 1u) == 0u) {  // a height-4 node
+      const uint32_t c = s.bits & 3u;
+      s.bits >>= 2; s.o += 2u;
+      if (c == 3u) {
+        fill_octets<ROT>(strip, i, 2u, word5 >> 24);
+        i += 2u;
+        if (i == 8u) break;
+        continue;
+      }
+      word4 = mkword(child(word5, c), d.d3);
+    }
+    {  // the octet's root (height 3)
+      const uint32_t c = s.bits & 3u;
+      s.bits >>= 2; s.o += 2u;
+      const uint32_t base = strip + ((i & 1u) ? (uint32_t)Geo<ROT>::bitOff(3) : 0u) + ((i & 2u) ? (uint32_t)Geo<ROT>::bitOff(4) : 0u) +
+                            ((i & 4u) ? (uint32_t)Geo<ROT>::bitOff(5) : 0u);
+      if (c == 3u) {
+        fill_small<ROT, 3, 0>(base, word4 >> 24);
+      } else {
+        const uint32_t word3 = mkword(child(word4, c), d.d2);
+        Node<ROT, 2, 0, WIN>::run(s, word3, d, base);
+        Node<ROT, 2, 4, WIN>::run(s, word3, d, base);
+      }
+    }
+    i += 1u;
+    if (i == 8u) break;
+  }
+}
+
+// Whole leaf box constant (index entry VR_PRUNED).
+VR_HD void fill_leaf(uint32_t strip, uint32_t val) {
+  const uint32_t w = val * 0x01010101u;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) Mem::st32(strip + 4u * (uint32_t)k, w);
+}
+
+#define VR6_STRIP_PITCH 68u  // 64-byte leaf block + 4: the blocks of a warp's 32 lanes start in 32 different banks
+#define VR6_STRIPS_BYTES (256u * VR6_STRIP_PITCH)
+
+// ---- phase 2: leaf blocks -> 16-byte x-runs of the destination --------------------------------------------------------
+// A warp owns 32 consecutive leaf boxes of the tile (its "unit": 2 048 voxels = 128 runs of 16 voxels along x).  Run m
+// (7 bits) = one value of the unit's free coordinate bits: the 3 leaf-index bits that are not tile x bits 2 / 3, and the
+// 4 row bits inside a leaf box (y0, y1, z0, z1).  A run is four 4-byte rows of four x-neighbouring leaf blocks.
+struct P6Geom {
+  int32_t rot;           // (D0 - 1) mod 3
+  uint16_t xs[2];        // strip offset of tile x bits 2, 3 (a leaf-index bit each)
+  uint16_t fs[7];        // strip offset of free bit k
+  uint8_t fAxis[7];      // its axis (1 = y, 2 = z; 0 only for x bit 4 of a 32-wide tile) ...
+  uint8_t fCb[7];        // ... and tile-local coordinate bit
+  uint8_t wAxis[3], wCb[3];  // the warp index (top 3 leaf-index bits) likewise
+};
+// false when the brick's tree does not have the shape this path is written for (kd_decode.cu then takes the generic kernel)
+static inline bool p6_make_geom(const vr_kd_geom& g, P6Geom* out) {
+  if (g.tileBits != 14 || g.leafBits != 6 || g.tx < 16) return false;
+  const int rot = (g.D0 - 1) % 3;
+  for (int b = 0; b < 6; ++b) {
+    const int ax = ((rot - b) % 3 + 3) % 3;
+    if (g.pbAxis[b] != ax || g.pbCoordBit[b] != b / 3) return false;
+  }
+  const int x2 = g.pathBit[0][2], x3 = g.pathBit[0][3];
+  if (x2 < 6 || x2 > 10 || x3 < 6 || x3 > 10) return false;
+  P6Geom p{};
+  p.rot = rot;
+  p.xs[0] = (uint16_t)(VR6_STRIP_PITCH << (x2 - 6));
+  p.xs[1] = (uint16_t)(VR6_STRIP_PITCH << (x3 - 6));
+  int n = 0;
+  for (int b = 0; b < 11; ++b) {  // in-leaf row bits first (lowest), then the leaf-index bits of the unit
+    if (b < 6) {
+      if (g.pbAxis[b] == 0) continue;  // x0, x1: inside a 4-byte row
+      p.fs[n] = (uint16_t)((g.pbAxis[b] == 1 ? 4 : 16) << (b / 3));
+    } else {
+      if (b == x2 || b == x3) continue;
+      p.fs[n] = (uint16_t)(VR6_STRIP_PITCH << (b - 6));
+    }
+    p.fAxis[n] = g.pbAxis[b];
+    p.fCb[n] = g.pbCoordBit[b];
+    ++n;
+  }
+  if (n != 7) return false;
+  for (int j = 0; j < 3; ++j) { p.wAxis[j] = g.pbAxis[11 + j]; p.wCb[j] = g.pbCoordBit[11 + j]; }
+  *out = p;
+  return true;
+}
+// strip offset (relative to the tile's strips) and destination offset (relative to the tile origin) of run m of warp w
+VR_HD void p6_run_addr(const P6Geom& p, uint32_t w, uint32_t m, int64_t rowPitch, int64_t slicePitch, uint32_t* sOff, int64_t* gOff) {
+  uint32_t s = w * 32u * VR6_STRIP_PITCH;
+  int64_t go = 0;
+#pragma unroll
+  for (int k = 0; k < 7; ++k)
+    if ((m >> k) & 1u) {
+      s += p.fs[k];
+      go += (p.fAxis[k] == 0 ? (int64_t)1 : (p.fAxis[k] == 1 ? rowPitch : slicePitch)) << p.fCb[k];
+    }
+#pragma unroll
+  for (int j = 0; j < 3; ++j)
+    if ((w >> j) & 1u) go += (p.wAxis[j] == 0 ? (int64_t)1 : (p.wAxis[j] == 1 ? rowPitch : slicePitch)) << p.wCb[j];
+  *sOff = s;
+  *gOff = go;
+}
+
+}  // namespace vr6

@@ -132,3 +132,82 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
 }
 
 }  // namespace vr
+
+// ---- work lists of the persistent kernel (kd_decode.cu: kd_decode6_kernel) -------------------------------------------------
+// Two queues instead of one CTA list: parse items (one tile each, self-contained so that the CTA needs one 48-byte read per
+// tile) and constant groups (vr_fill_job, stored by the TMA unit).  Both in destination-address order.  Culling as above.
+namespace vr {
+inline void kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const* idx, const int64_t* dstOffset, int64_t rowPitch,
+                               int64_t slicePitch, const int64_t* origins, const int64_t* occBase, const int32_t* tileCell,
+                               const uint8_t* needed, std::vector<vr_occ_set>* culled, uint32_t stageChunksMax,
+                               std::vector<vr_parse_item>* parse, std::vector<vr_fill_job>* fills) {
+  struct PItem { int64_t key; vr_parse_item w; };
+  struct FItem { int64_t key; vr_fill_job f; };
+  std::vector<PItem> pitems;
+  std::vector<FItem> fitems;
+  const uint32_t nt = 1u << g.Dt;
+  for (int b = 0; b < n; ++b) {
+    vr_kd_job hj{};
+    hj.tileLeafBlock = idx[b]->tileLeafBlock.data();
+    hj.tileVal = idx[b]->tileVal.data();
+    const bool occ = occBase && tileCell && occBase[b] >= 0;
+    for (uint32_t t = 0; t < nt; ++t) {
+      const bool isParse = hj.tileLeafBlock[t] != VR_PRUNED;
+      uint64_t vals = 0;
+      int L = 0;
+      if (!isParse) {
+        L = vr_fill_group_of(g, hj, t, &vals);
+        if (L < 0) continue;
+      }
+      if (needed && culled && occ) {
+        const uint32_t members = isParse ? 1u : (1u << L);
+        uint32_t mt[8];
+        bool any = false;
+        for (uint32_t i = 0; i < members; ++i) {
+          uint32_t tm = t;
+          for (int j = 0; j < L && !isParse; ++j) tm |= ((i >> j) & 1u) << g.xrBit[j];
+          mt[i] = tm;
+          any = any || needed[(size_t)b * nt + tm];
+        }
+        if (!any) {
+          for (uint32_t i = 0; i < members; ++i) culled->push_back({occBase[b] + tileCell[mt[i]], (int64_t)idx[b]->tileMax[mt[i]]});
+          continue;
+        }
+      }
+      int ox, oy, oz;
+      vr_tile_origin(g, t, &ox, &oy, &oz);
+      const int64_t key = dstOffset[b] + (int64_t)oz * slicePitch + (int64_t)oy * rowPitch + ox;
+      if (isParse) {
+        vr_parse_item w{};
+        w.brick = (uint32_t)b;
+        w.tile = t;
+        w.blk = hj.tileLeafBlock[t];
+        const uint64_t begin = idx[b]->blockSymBegin[w.blk], end = idx[b]->blockSymEnd[w.blk];
+        // staged range: from the 16-byte chunk of the tile's first symbol to the chunk that holds the word after its last
+        // symbol's word (the window keeps one word of look-ahead)
+        const uint64_t c0 = (begin >> 4) >> 2, c1 = ((((end > begin ? end - 1 : begin) >> 4) + 2) >> 2) + 1;
+        w.seg0 = (uint32_t)c0;
+        w.segChunks = (c1 - c0) <= stageChunksMax ? (uint32_t)(c1 - c0) : 0u;
+        w.dst = key;
+        w.occCell = occ ? occBase[b] + tileCell[t] : -1;
+        pitems.push_back({key, w});
+      } else {
+        vr_fill_job f;
+        f.x = (int32_t)(origins[3 * b] + ox);
+        f.y = (int32_t)(origins[3 * b + 1] + oy);
+        f.z = (int32_t)(origins[3 * b + 2] + oz);
+        f.L = (uint32_t)L;
+        f.vals = vals;
+        f.occCell = occ ? occBase[b] + tileCell[t] : -1;
+        fitems.push_back({key, f});
+      }
+    }
+  }
+  std::sort(pitems.begin(), pitems.end(), [](const PItem& a, const PItem& b) { return a.key < b.key; });
+  std::sort(fitems.begin(), fitems.end(), [](const FItem& a, const FItem& b) { return a.key < b.key; });
+  parse->resize(pitems.size());
+  for (size_t i = 0; i < pitems.size(); ++i) (*parse)[i] = pitems[i].w;
+  fills->resize(fitems.size());
+  for (size_t i = 0; i < fitems.size(); ++i) (*fills)[i] = fitems[i].f;
+}
+}  // namespace vr
