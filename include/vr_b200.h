@@ -177,6 +177,18 @@ int vr_decode_plan_run(vr_decode_plan* plan); /* one kernel launch, asynchronous
 int vr_decode_plan_destroy(vr_decode_plan* plan);
 /* algorithmic bytes of one run: [0] stream bytes read, [1] voxel bytes written, [2] index bytes read */
 int vr_decode_plan_bytes(const vr_decode_plan* plan, int64_t out[3]);
+/* which kernel the plan launches: 0 = persistent warp-specialised kernel (bricks with 4x4x4 leaf boxes such as the
+ * reference's 256x256x128, 16-byte aligned placement), 1 = classic kernel, one CTA per tile (every other shape) */
+int vr_decode_plan_kernel(const vr_decode_plan* plan, int32_t* which);
+/* Debug knobs for A/B measurements; explicit, process-wide, read when a plan is created or run -- the library never
+ * reads the environment.  "decode_kernel": 0 = choose (default), 1 = classic kernel always.  "decode_only": 0 = whole
+ * launch, 1 = parse tiles only, 2 = constant groups only (timing probes; the destination is then incomplete).
+ * "fill_attach": constant groups per parse CTA of the classic kernel (default 2).  Persistent kernel: "unit_store" 2 = a
+ * unit's voxels as 16-byte stores of the lanes instead of one tensor store; "fill_mode" 0 / 2 = tensor stores of the constant
+ * groups without / with (default) an evict-first L2 hint, + 256 * t = pace them by t * 100 ns per group while parse units are
+ * queued; "tma_rows" 8 / 16 / 32 rows per constant-group tensor store; "parse_order" 1 = longest units first. */
+int vr_debug_set(const char* key, int value);
+int vr_debug_get(const char* key, int* value);
 /* End-to-end levelCut: host stream -> host voxels (upload, decode, download; synchronous).
  * cutDepth must equal maxTreeDepth: any other depth crashes the reference and is
  * rejected with VR_ERR_UNSUPPORTED. */

@@ -52,18 +52,6 @@ long long emu_check_chain_lut(unsigned long long chainDist) {
       const int lo = (e >> 8) & 0xFF, hi = (e >> 16) & 0xFF;
       y = y < lo ? lo : y; y = y > hi ? hi : y;
       if (y != val || (int)(e >> 24) != L) ++bad;
-      // the same chain through the two-level table of variant 13 (symbols 0..4, then 5..6 or the identity)
-      const uint32_t m = (codes & (codes >> 1) & 0x1555u) | 0x1000u;
-      const uint32_t e1 = vr_chain_lut_entry((codes & 0x3FFu) | 0x3C00u, chainDist);
-      const uint32_t i2 = (m & 0x155u) ? 0xFu : ((codes >> 10) & 0xFu);
-      const uint32_t e2 = vr_chain_lut_entry(i2 | 0x30u, chainDist >> 40);
-      int z = x + (int)(int8_t)(e1 & 0xFF);
-      const int lo1 = (e1 >> 8) & 0xFF, hi1 = (e1 >> 16) & 0xFF;
-      z = z < lo1 ? lo1 : z; z = z > hi1 ? hi1 : z;
-      z += (int)(int8_t)(e2 & 0xFF);
-      const int lo2 = (e2 >> 8) & 0xFF, hi2 = (e2 >> 16) & 0xFF;
-      z = z < lo2 ? lo2 : z; z = z > hi2 ? hi2 : z;
-      if (z != val || (int)(((unsigned)__builtin_ctz(m)) >> 1) + 1 != L) ++bad;
     }
   }
   return bad;
@@ -72,8 +60,6 @@ int emu_validate(void* p, long long* nodes) {
   int64_t n = 0; int rc = kd_validate(*static_cast<KdStream*>(p), &n); *nodes = n; return rc;
 }
 // prepare + emulate the tile kernel into a slab of dims (SX,SY,SZ) at origin (ox,oy,oz)
-static int g_variant = 0;
-void emu_set_variant(int v) { g_variant = v; }
 // lazy (view-dependent) decode: the next emu_decode call drops the tiles whose byte in `needed` (2^Dt entries) is 0, as the
 // device path does (kd_worklist.h with a kd_cull.h mask), and reports the (cell, max) pairs of the dropped tiles
 static const uint8_t* g_needed = nullptr;
@@ -86,7 +72,7 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   int rc = kd_prepare(s);
   if (rc != VR_OK) return rc;
   const vr_kd_geom& g = s->geom;
-  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 16, 0);  // the windows read a few words (VrWin128: two 16-byte chunks) past the end
+  std::vector<uint32_t> words((s->bits.size() + 3) / 4 + 16, 0);  // the windows read a few words past the end
   std::memcpy(words.data(), s->bits.data(), s->bits.size());
   vr_kd_job job;
   job.words = words.data();
@@ -98,10 +84,8 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
   for (int h = 0; h <= g.leafBits && h < 8; ++h) job.treeDist |= (uint64_t)s->distanceMap[g.D0 - h] << (8 * h);
   for (int k = 1; k <= 7; ++k) job.chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
   job.dstOffset = (oz * SY + oy) * SX + ox;
-  std::vector<uint32_t> lut((1u << 14) + VR_LUT2_ENTRIES);
+  std::vector<uint32_t> lut(1u << 14);
   for (uint32_t i = 0; i < (1u << 14); ++i) lut[i] = vr_chain_lut_entry(i, job.chainDist);
-  for (uint32_t i = 0; i < 1024u; ++i) lut[VR_LUT2_OFF + i] = vr_chain_lut_entry(i | 0x3C00u, job.chainDist);
-  for (uint32_t i = 0; i < 16u; ++i) lut[VR_LUT2_OFF + 1024u + i] = vr_chain_lut_entry(i | 0x30u, job.chainDist >> 40);
   job.chainLut = lut.data();
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   std::vector<uint8_t> strips(lpt * ((1u << g.leafBits) + VR_LEAF_PITCH_PAD));
@@ -151,17 +135,7 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
     std::fill(strips.begin(), strips.end(), 0xEE);
     if (g.fastPath && vec16) {  // mirrors the fast path of kd_decode_tiles_kernel
       for (uint32_t t = 0; t < 256; ++t) {
-        if (g_variant == 1) vr_tile_phase1_v3<true>(job, g, blk, t, strips.data());
-        else if (g_variant == 2) vr_tile_phase1_v2(job, g, blk, t, strips.data());
-        else if (g_variant == 3) vr_tile_phase1_v3<false>(job, g, blk, t, strips.data());
-        else if (g_variant == 4) vr_tile_phase1_v4<true>(job, g, blk, t, strips.data());
-        else if (g_variant == 5) vr_tile_phase1_v4<false, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
-        else if (g_variant == 6) vr_tile_phase1_v4<false>(job, g, blk, t, strips.data());
-        else if (g_variant == 11) vr_tile_phase1_v4<true, uint8_t*, VrWin96>(job, g, blk, t, strips.data());
-        else if (g_variant == 10) vr_tile_phase1_v5<false, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
-        else if (g_variant == 12) vr_tile_phase1_v5<true, uint8_t*, VrWin128>(job, g, blk, t, strips.data());
-        else if (g_variant == 13) vr_tile_phase1_v5_l2<uint8_t*, VrWin32L>(job, g, blk, t, strips.data(), lut.data() + VR_LUT2_OFF, 0u);
-        else vr_tile_phase1_v5<true, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
+        vr_tile_phase1_v5<true, uint8_t*, VrWin32>(job, g, blk, t, strips.data());
       }
       for (uint32_t warp = 0; warp < 8; ++warp)
         for (uint32_t q = 0; q < (1u << g.fbUnit); ++q) vr_unit_phase2_item(g, warp, q, strips.data(), dst, SX, SX * SY);
@@ -174,42 +148,41 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
 }
 
 // ---- the persistent kernel's parser (kd_parse6.h), thread by thread -------------------------------------------------------
-// stageChunks: capacity of the staging area in 16-byte chunks (tiles with longer segments go through WinGlobal, as on the
-// device); needed/culled as in emu_set_lazy.  stats (optional, 4 values): parse tiles, tiles parsed from global memory,
-// constant groups, shared-memory bank-conflict wavefronts of the chain-table look-ups are NOT modelled here.
+// stageChunks: capacity of a warp's staging area in 16-byte chunks (294 on the device; a longer unit is a format error);
+// needed/culled as in emu_set_lazy.  stats (4 values): parse units, longest staged segment in chunks, constant groups, 0.
 }  // extern "C"
 template <int ROT>
-static void emu6_tile(const vr_kd_job& job, const vr_parse_item& it, const vr6::P6Geom& pg, const vr6::Dist& d, std::vector<uint8_t>& smem,
+static void emu6_unit(const vr_kd_job& job, const vr_parse_item& it, const vr6::P6Geom& pg, const vr6::Dist& d, std::vector<uint8_t>& smem,
                       uint32_t lutOff, uint32_t stripOff, uint32_t stageOff, uint8_t* slab, int64_t SX, int64_t SY) {
   vr6::Mem::base() = smem.data();
-  const uint32_t stageBase = stageOff - 16u * it.seg0;  // shared address of virtual word 0 (wraps)
-  if (it.segChunks) std::memcpy(smem.data() + stageOff, reinterpret_cast<const uint8_t*>(job.words) + 16ull * it.seg0, 16ull * it.segChunks);
-  std::fill(smem.begin() + stripOff, smem.begin() + stripOff + VR6_STRIPS_BYTES, 0xEE);
-  for (uint32_t t = 0; t < 256; ++t) {
-    const uint32_t off = job.leafOff[(size_t)it.blk * 256 + t];
-    const uint32_t val = job.leafVal[(size_t)it.blk * 256 + t];
-    const uint32_t strip = stripOff + t * VR6_STRIP_PITCH;
+  const uint32_t stageBase = stageOff - it.segOff;  // shared address of virtual word 0 (wraps)
+  if (it.segChunks) std::memcpy(smem.data() + stageOff, reinterpret_cast<const uint8_t*>(job.words) + it.segOff, 16ull * it.segChunks);
+  std::fill(smem.begin() + stripOff, smem.begin() + stripOff + 32 * VR6_STRIP_PITCH, 0xEE);
+  for (uint32_t lane = 0; lane < 32; ++lane) {
+    const uint32_t off = job.leafOff[(size_t)it.leaf0 + lane];
+    const uint32_t val = job.leafVal[(size_t)it.leaf0 + lane];
+    const uint32_t strip = stripOff + lane * VR6_STRIP_PITCH;
     if (off == VR_PRUNED) { vr6::fill_leaf(strip, val); continue; }
-    if (it.segChunks) {
-      vr6::WinShared w;
-      w.init(stageBase, nullptr, off);
-      vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
-    } else {
-      vr6::WinGlobal w;
-      w.init(0, job.words, off);
-      vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
+    vr6::WinShared w;
+    w.init(stageBase, off);
+    vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
+  }
+  const uint32_t unit = it.tileUnit & 7u;
+  for (uint32_t m = 0; m < 128; ++m) {
+    uint32_t sOff; int64_t gOff;
+    vr6::p6_run_addr(pg, unit, m, SX, SX * SY, &sOff, &gOff);
+    sOff -= unit * 32u * VR6_STRIP_PITCH;  // the warp's strips hold this unit only
+    uint8_t* out = slab + it.dst + gOff;
+    // the same run through the tensor-store path: dense box [z][y][16], placed at the unit's voxel coordinates
+    const uint32_t bo = vr6::p6_box_off(pg, m);
+    const int by = (int)((bo >> 4) & ((1u << pg.boxLy) - 1u)), bz = (int)(bo >> (4 + pg.boxLy));
+    uint8_t* out2 = slab + ((int64_t)(it.uz + bz) * SY + (it.uy + by)) * SX + it.ux;
+    if (out2 != out) { std::memset(out, 0xDD, 16); continue; }  // the two address computations must agree
+    for (uint32_t j = 0; j < 4; ++j) {
+      const uint32_t a = stripOff + sOff + ((j & 1u) ? pg.xs[0] : 0u) + ((j & 2u) ? pg.xs[1] : 0u);
+      std::memcpy(out + 4 * j, smem.data() + a, 4);
     }
   }
-  for (uint32_t w = 0; w < 8; ++w)
-    for (uint32_t m = 0; m < 128; ++m) {
-      uint32_t sOff; int64_t gOff;
-      vr6::p6_run_addr(pg, w, m, SX, SX * SY, &sOff, &gOff);
-      uint8_t* out = slab + it.dst + gOff;
-      for (uint32_t j = 0; j < 4; ++j) {
-        const uint32_t a = stripOff + sOff + ((j & 1u) ? pg.xs[0] : 0u) + ((j & 2u) ? pg.xs[1] : 0u);
-        std::memcpy(out + 4 * j, smem.data() + a, 4);
-      }
-    }
 }
 extern "C" {
 static long long g6_stats[4];
@@ -255,8 +228,9 @@ int emu_decode6(void* p, uint8_t* slab, long long SX, long long SY, long long SZ
       tileCell[t] = (int32_t)((tx0 >> 5) + ncx * ((ty0 >> 5) + ncy * (tz0 >> 4)));
     }
   }
-  kd_build_worklist6(g, 1, &idx, &job.dstOffset, SX, SX * SY, org, g_needed ? &occBase : nullptr, g_needed ? tileCell.data() : nullptr, g_needed,
-                     g_needed ? &culled : nullptr, (uint32_t)(stageChunks > 0 ? stageChunks : 0), &parse, &fills);
+  if (!kd_build_worklist6(g, 1, &idx, &job.dstOffset, SX, SX * SY, org, g_needed ? &occBase : nullptr, g_needed ? tileCell.data() : nullptr, g_needed,
+                          g_needed ? &culled : nullptr, (uint32_t)(stageChunks > 0 ? stageChunks : 0), pg, &parse, nullptr, &fills))
+    return VR_ERR_FORMAT;
   g_culled_n = (long long)culled.size();
   for (size_t i = 0; i < culled.size() && (long long)i < g_culled_cap; ++i) { g_culled_out[2 * i] = culled[i].cell; g_culled_out[2 * i + 1] = culled[i].value; }
   g6_stats[0] = (long long)parse.size(); g6_stats[1] = 0; g6_stats[2] = (long long)fills.size(); g6_stats[3] = 0;
@@ -266,10 +240,9 @@ int emu_decode6(void* p, uint8_t* slab, long long SX, long long SY, long long SZ
         for (uint32_t j = 0; j < (1u << f.L); ++j)
           std::memset(slab + ((int64_t)(f.z + z) * SY + (f.y + y)) * SX + f.x + (int64_t)j * g.tx, (int)((f.vals >> (8 * j)) & 0xFF), (size_t)g.tx);
   for (const vr_parse_item& it : parse) {
-    if (!it.segChunks) ++g6_stats[1];
-    if (pg.rot == 0) emu6_tile<0>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
-    else if (pg.rot == 1) emu6_tile<1>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
-    else emu6_tile<2>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
+    if ((long long)it.segChunks > g6_stats[1]) g6_stats[1] = (long long)it.segChunks;
+    if (pg.rot == 0) emu6_unit<0>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
+    else emu6_unit<1>(job, it, pg, d, smem, lutOff, stripOff, stageOff, slab, SX, SY);
   }
   return VR_OK;
 }

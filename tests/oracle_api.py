@@ -63,7 +63,10 @@ if EMU is not None:
     EMU.emu_get.argtypes = [c_void_p, c_void_p, c_void_p]
     EMU.emu_validate.argtypes = [c_void_p, c_void_p]
     EMU.emu_decode.argtypes = [c_void_p, c_void_p] + [LL] * 6 + [c_int]
-    EMU.emu_set_variant.argtypes = [c_int]
+    EMU.emu_decode6.argtypes = [c_void_p, c_void_p] + [LL] * 6 + [c_int]
+    EMU.emu_decode6_stats.argtypes = [c_void_p]
+    EMU.emu_check_chain_lut6.restype = LL
+    EMU.emu_check_chain_lut6.argtypes = [ctypes.c_ulonglong]
     if hasattr(EMU, "emu_set_lazy"):
         EMU.emu_set_lazy.argtypes = [c_void_p, c_void_p, LL]
         EMU.emu_culled_count.restype = LL

@@ -116,3 +116,45 @@ def test_unaligned_placement_uses_scalar_stores(ctx):
     assert np.array_equal(got[3:19, 5:37, 7:39], _oracle(s))
     got[3:19, 5:37, 7:39] = 0
     assert not got.any()
+
+
+@pytest.mark.parametrize("kernel", ["persistent", "persistent_tensor_stores", "persistent_lane_stores", "classic"])
+def test_slab_of_full_size_bricks_both_kernels(ctx, kernel):
+    """A 2x1x3 grid of 256x256x128 bricks (empty, mixing layer x 3, noise, solid) through the persistent warp-specialised
+    kernel (parse groups + TMA fill warp, kd_decode.cu) and through the classic one-CTA-per-tile kernel: both equal the
+    levelCut restatement voxel for voxel, write nothing outside the bricks, and leave the same exact per-cell maxima."""
+    vr.debug_set("decode_kernel", 0 if kernel.startswith("persistent") else 1)
+    # how a parsed unit's voxels leave the SM: one tensor store per unit, or 16-byte stores of the lanes (default: chosen per plan)
+    vr.debug_set("unit_store", {"persistent_tensor_stores": 1, "persistent_lane_stores": 2}.get(kernel, 0))
+    try:
+        bx, by, bz = 256, 256, 128
+        vols = [synth.constant_brick(value=0), synth.rm_brick(3, 4, 7), synth.rm_brick(2, 4, 7), synth.noise_brick(),
+                synth.rm_brick(3, 4, 8), synth.constant_brick(value=230)]
+        SX, SY, SZ = 2 * bx + 32, by + 32, 3 * bz + 16
+        vol = vr.Volume(ctx, SX, SY, SZ)
+        sentinel = np.full((SZ, SY, SX), 0x5A, np.uint8)
+        vol.upload_brick(sentinel, (0, 0, 0))
+        want = sentinel.copy()
+        streams, origins = [], []
+        for b, v in enumerate(vols):
+            s, _ = vr.Stream.compress(v, 1, 2)
+            s.upload(ctx)
+            streams.append(s)
+            o = (32 + (b % 2) * bx, 32, 16 + (b // 2) * bz)
+            origins.append(o)
+            want[o[2]:o[2] + bz, o[1]:o[1] + by, o[0]:o[0] + bx] = _oracle(s)
+        plan = vr.DecodePlan(ctx, streams, origins, vol)
+        assert plan.kernel() == kernel.split("_")[0]
+        for _ in range(2):  # idempotent
+            plan.run()
+            ctx.synchronize()
+            got = vol.download()
+            assert np.array_equal(got, want)
+        occ = vol.occupancy(0)
+        for b, o in enumerate(origins):  # cells of the decoded bricks: exact maxima of their 32x32x16 voxels
+            blk = want[o[2]:o[2] + bz, o[1]:o[1] + by, o[0]:o[0] + bx].reshape(bz // 16, 16, by // 32, 32, bx // 32, 32).max(axis=(1, 3, 5))
+            assert np.array_equal(occ[o[2] // 16:(o[2] + bz) // 16, o[1] // 32:(o[1] + by) // 32, o[0] // 32:(o[0] + bx) // 32], blk), b
+        plan.close(); vol.close()
+    finally:
+        vr.debug_set("decode_kernel", 0)
+        vr.debug_set("unit_store", 0)

@@ -135,12 +135,15 @@ def test_chain_table_equals_sequential_chain_for_all_inputs():
         assert oa.EMU.emu_check_chain_lut(sum(d << (8 * k) for k, d in enumerate(dist))) == 0
 
 
-@pytest.mark.parametrize("variant,kind", [(0, "rm"), (1, "rm"), (2, "rm"), (3, "rm"), (4, "rm"), (5, "rm"), (6, "rm"), (10, "rm"), (11, "rm"), (12, "rm"), (12, "noise"), (13, "rm"), (13, "noise"), (13, "shell"), (0, "noise"), (0, "shell"), (4, "noise")])
-def test_emulated_fast_path_full_size_brick(variant, kind):
-    """256x256x128 (tiles of 2^14 voxels): exercises the table-driven parsers and the warp-unit gather."""
-    oa.EMU.emu_set_variant(variant)
-    vol = {"rm": lambda: synth.rm_brick(3, 4, 7), "noise": synth.noise_brick,
-           "shell": lambda: synth.shell_brick((256, 256, 128), noise=3)}[kind]()
+def _full_size(kind):
+    return {"rm": lambda: synth.rm_brick(3, 4, 7), "noise": synth.noise_brick,
+            "shell": lambda: synth.shell_brick((256, 256, 128), noise=3)}[kind]()
+
+
+@pytest.mark.parametrize("kind", ["rm", "noise", "shell"])
+def test_emulated_fast_path_full_size_brick(kind):
+    """256x256x128 (tiles of 2^14 voxels): the classic kernel's table-driven parser and its warp-unit gather."""
+    vol = _full_size(kind)
     s, _ = vr.Stream.compress(vol, 1, 2)
     hd = s.header
     dm, bits = s.distance_map, s.bits
@@ -153,4 +156,36 @@ def test_emulated_fast_path_full_size_brick(variant, kind):
     slab[1:129, 1:257, 16:272] = 0xAB
     assert (slab == 0xAB).all()
     oa.EMU.emu_free(h)
-    oa.EMU.emu_set_variant(0)
+
+
+def test_chain_table_of_the_persistent_kernel_for_all_inputs():
+    for dist in ([64, 32, 16, 8, 4, 2, 1], [100, 0, 13, 7, 3, 3, 1], [1, 2, 4, 8, 16, 32, 64]):
+        assert oa.EMU.emu_check_chain_lut6(sum(d << (8 * k) for k, d in enumerate(dist))) == 0
+
+
+@pytest.mark.parametrize("kind,dims", [("rm", (256, 256, 128)), ("noise", (256, 256, 128)), ("shell", (256, 256, 128)),
+                                       ("shell", (128, 128, 64)), ("shell", (256, 128, 128))])
+def test_emulated_persistent_kernel_parser(kind, dims):
+    """kd_parse6.h (the leaf parser of the persistent kernel: select words, chain table, static window re-alignment) and its
+    work lists, lane by lane on the CPU, against the levelCut restatement, with the device's staging capacity of 294 chunks per
+    unit (every unit must fit; too small a capacity is reported as a format error, never decoded wrongly).  256x128x128 is the
+    other leaf-box orientation the kernel is instantiated for (last split along x instead of y)."""
+    X, Y, Z = dims
+    vol = _full_size(kind) if dims == (256, 256, 128) else synth.shell_brick(dims, noise=3)
+    s, _ = vr.Stream.compress(vol, 1, 2)
+    hd = s.header
+    dm, bits = s.distance_map, s.bits
+    h = oa.EMU.emu_from_memory(ctypes.byref(hd), dm.ctypes.data, bits.ctypes.data, bits.size)
+    slab = np.full((Z + 2, Y + 1, X + 32), 0xAB, np.uint8)
+    assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, 294) == 0
+    rc, want = oa.oracle_levelcut(bits, hd.numActiveNodes, dm, hd.origTreeDepth, hd.maxTreeDepth, X, Y, Z)
+    assert rc == 0
+    assert np.array_equal(slab[1:Z + 1, 1:Y + 1, 16:16 + X], want)
+    slab[1:Z + 1, 1:Y + 1, 16:16 + X] = 0xAB
+    assert (slab == 0xAB).all()
+    st = (ctypes.c_longlong * 4)()
+    oa.EMU.emu_decode6_stats(st)
+    assert 0 < st[1] <= 294
+    if kind == "noise":
+        assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, int(st[1]) - 1) == _lib.VR_ERR_FORMAT
+    oa.EMU.emu_free(h)

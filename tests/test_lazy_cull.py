@@ -154,8 +154,9 @@ def test_iso_rule_equals_a_numpy_restatement(layered, iso, step):
     assert 0 < got.sum() < got.size
 
 
-def test_culled_work_list_on_the_cpu_emulation():
-    """The device path's work-list builder with a cull mask (kd_worklist.h), run by the CPU emulation of the decode
+@pytest.mark.parametrize("kernel", ["persistent", "classic"])
+def test_culled_work_list_on_the_cpu_emulation(kernel):
+    """The device path's work-list builders with a cull mask (kd_worklist.h), run by the CPU emulation of the decode
     kernel (tests/emu): tiles the mask keeps are decoded bit-exactly, every member of a kept constant group too, all
     other tiles are never written, and their (cell, exact maximum) pairs are reported for the occupancy grid."""
     import ctypes
@@ -177,7 +178,10 @@ def test_culled_work_list_on_the_cpu_emulation():
     culled = np.zeros((needed.size, 2), np.int64)
     oa.EMU.emu_set_lazy(needed.ctypes.data, culled.ctypes.data, needed.size)
     try:
-        assert oa.EMU.emu_decode(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 1) == 0
+        if kernel == "persistent":
+            assert oa.EMU.emu_decode6(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 294) == 0
+        else:
+            assert oa.EMU.emu_decode(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 1) == 0
         n = oa.EMU.emu_culled_count()
     finally:
         oa.EMU.emu_set_lazy(None, None, 0)

@@ -7,3 +7,8 @@ from . import _lib, render, sortlast, synth  # noqa: F401
 from ._lib import VrError  # noqa: F401
 from .kdtree import Context, DecodePlan, Stream, Volume, VolumeKdtree, load_streams, nibbles_pack, nibbles_unpack  # noqa: F401
 from .loader import VolumeReader  # noqa: F401
+
+
+def debug_set(key, value):
+    """vr_debug_set: explicit A/B knobs of the decode launch ("decode_kernel", "decode_only", "fill_attach")."""
+    _lib.check(_lib.lib.vr_debug_set(key.encode(), int(value)))

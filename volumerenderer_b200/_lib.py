@@ -98,6 +98,9 @@ _SIGS = {
     "vr_decode_plan_run": (c_int, [c_void_p]),
     "vr_decode_plan_destroy": (c_int, [c_void_p]),
     "vr_decode_plan_bytes": (c_int, [c_void_p, POINTER(c_int64)]),
+    "vr_decode_plan_kernel": (c_int, [c_void_p, POINTER(c_int32)]),
+    "vr_debug_set": (c_int, [c_char_p, c_int]),
+    "vr_debug_get": (c_int, [c_char_p, POINTER(c_int)]),
     "vr_kd_levelcut": (c_int, [c_void_p, c_void_p, c_int32, c_void_p]),
     "vr_volume_load_bricks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, POINTER(c_int64), c_void_p, c_void_p,
                                       POINTER(c_int64), c_void_p, POINTER(c_int64)]),

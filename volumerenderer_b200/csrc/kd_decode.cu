@@ -1,23 +1,468 @@
-// kd_decode.cu -- stage 1 of the hot path on the GPU: batched kd-tree stream decode into 8-bit
-// bricks placed inside a device slab.  Replaces the reference's CPU
-// VolumeKdtree::levelCut (/root/reference/volume_renderer/VolumeKdTree_recover.cpp:726-835) and the
-// brick placement of VolumeReader::LoadBricksToTexture (VolumeReader.h:184-205).
+// kd_decode.cu -- stage 1 of the hot path on the GPU: batched kd-tree stream decode into 8-bit bricks placed inside a
+// device slab.  Replaces the reference's CPU VolumeKdtree::levelCut
+// (/root/reference/volume_renderer/VolumeKdTree_recover.cpp:726-835) and the brick placement of
+// VolumeReader::LoadBricksToTexture (VolumeReader.h:184-205).
 //
-// Launch shape: one CTA per (brick, tile); a tile is the box of a depth-Dt tree node (32x32x16 for
-// a 256x256x128 brick), at most 2^14 voxels.  256 parser threads, one per depth-Dl leaf subtree
-// (4x4x4 voxels), walk their stream segments independently (kd_decode_core.h), writing path-ordered
-// strips in shared memory; the CTA then gathers the strips into 16-byte row segments and stores
-// them with 128-bit writes, so every 32-byte DRAM sector of the slab is written exactly once.
+// Two kernels:
+//  * kd_decode6_kernel -- the product path for bricks whose leaf boxes are 4x4x4 (256x256x128 and relatives).  Persistent,
+//    one CTA per SM, warp-specialised: 22 parse warps, each a pipeline of its own over "units" (32 leaf subtrees = an
+//    eighth of a 32x32x16 tile, one lane per leaf subtree: kd_parse6.h; the unit's stream segment and index entries arrive
+//    in shared memory by bulk copies on the warp's mbarrier) and one warp that hands the constant groups to the TMA unit
+//    (cp.async.bulk.tensor from a row image in shared memory).
+//    Parsing is bound by instruction issue, the constant groups by HBM writes; in one CTA per work item (round 1) a CTA in
+//    its fill phase parses nothing and holds its slot until its stores have drained, so the launch cost parse + fill.
+//    Here the fills occupy one warp per SM and no issue slots to speak of, and the two overlap.
+//  * kd_decode_tiles_kernel -- one CTA per work-list entry: any power-of-two brick shape; round 1's default, kept as the
+//    challenger for A/B runs (vr_debug_set("decode_kernel", 1)).
 #include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <cstring>
 
 #include "kd_decode.h"
 #include "kd_decode_core.h"
+#include "kd_parse6.h"
 
 namespace vr {
 
+// =====================================================================================================================
+// persistent kernel
+// =====================================================================================================================
+// Shared memory of the CTA: [chain table 64 KB | per parse warp (7 168 B): staging area 4 704 B (its first 2 KB double as the
+// unit's dense voxel box for the tensor store), leaf blocks 2 176 B, item 64 B, index entries 160 B | TMA row images].
+#define VR6_OFF_LUT 0u
+// The longest possible unit: 32 leaf subtrees of 63 nodes + 64 voxel items of 8 symbols and the 31 nodes above them = 18 431
+// symbols = 4 608 bytes, + 15 bytes of alignment + two words of look-ahead rounded up to chunks (kd_build_worklist6).  Every
+// unit is staged: a parser that reads its stream from global memory waits for HBM on its dependent chain, and next to the
+// write-saturating constant groups that wait grows several-fold (measured: 15 % of the config-3 units took half of all
+// long-scoreboard stalls).
+#define VR6_STAGE_BYTES 4704u
+#define VR6_WARP_STAGE 0u
+#define VR6_BOX_BYTES 2048u                                        // 16 x 16 x 8 voxels of a unit, x fastest
+#define VR6_SMALL_CHUNKS ((VR6_STAGE_BYTES - VR6_BOX_BYTES) / 16u)  // a segment this short is staged behind the box
+#define VR6_WARP_STRIPS VR6_STAGE_BYTES                            // 32 leaf blocks, pitch 68: 2 176 bytes
+#define VR6_WARP_ITEM (VR6_WARP_STRIPS + 32u * VR6_STRIP_PITCH)    // 64 bytes
+#define VR6_WARP_LEAFOFF (VR6_WARP_ITEM + 64u)                     // 128 bytes
+#define VR6_WARP_LEAFVAL (VR6_WARP_LEAFOFF + 128u)                 // 32 bytes
+#define VR6_WARP_BYTES 7168u                                       // 7 104 used; a multiple of 128 (tensor stores read aligned boxes)
+#define VR6_QUEUE_FILL 32u  // the constant groups' counter lives on its own 128-byte line
+#define VR6_BATCH_MAX 4u    // units per queue ticket: one atomic per unit on one address serialises in L2 (38 % of the stalls on
+                            // 262 144 units); short queues take single units, whose costs differ by 10x, for balance
+#define VR6_IMG_TOTAL 8192u  // row images of the constant groups: 8192 / (256 * rows) slots of (32 << 3) x rows bytes
+#define VR6_OFF_IMG ((VR6_LUT_BYTES + VR6_PARSE_WARPS * VR6_WARP_BYTES + 127u) & ~127u)  // tensor stores read 128-byte aligned images
+
+struct Decode6Params {
+  const vr_parse_item* parse;
+  const vr_fill_job* fills;
+  uint32_t nParse, nFill;
+  uint32_t* queue;  // [0] next parse unit, [VR6_QUEUE_FILL] next constant group
+  uint8_t* dst;
+  int64_t rowPitch, slicePitch;
+  const uint32_t* lut;
+  uint8_t* occ;
+  vr6::P6Geom pg;
+  int32_t tx, ty, tz;
+  int32_t only;
+  int32_t fillThrottle;
+  int32_t tmaRows;   // rows per tensor-store box (8, 16 or 32)
+  int32_t tmaOut;    // 1: the units' voxels leave as one tensor store per unit, 0: as 16-byte stores of the lanes
+  uint32_t batch;    // units per parse ticket
+  int32_t fillMode;  // 0 = tensor stores (TMA), 1 = ordinary streaming stores by the fill warp, 2 = tensor stores with an evict-first L2 hint
+  VrFillMaps maps;
+  alignas(64) unsigned char unitMap[128];  // tensor map of the destination with a unit's box
+};
+
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+
+// Timing probe (only == 4): every unit reads the stream and index entries of one of the first 1 024 units, so its loads hit L2;
+// what it decodes is garbage, where it stores is real.
+__device__ __forceinline__ uint32_t src_of(const Decode6Params& p, uint32_t idx) { return p.only == 4 ? (idx & 1023u) : idx; }
+
+// Stages unit `idx` (its 64-byte item, 32 index entries and stream segment) into the warp's shared-memory area with 16-byte
+// asynchronous copies (LDGSTS), all lanes taking part.  Not the TMA unit: its queue is shared with the constant groups' tensor
+// stores, and a unit's load stuck behind a few hundred KB of HBM-bound stores starves the parser (measured: the launch took
+// longer than its two halves one after the other).  ia / ib = the first 32 bytes of the item, valid in lane 0.
+__device__ __forceinline__ void cp16(uint32_t dstS, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dstS), "l"(src) : "memory");
+}
+__device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t wbase, uint32_t lane) {
+  const uint64_t ar = (uint64_t)__shfl_sync(0xFFFFFFFFu, ia.x, 0) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, ia.y, 0) << 32);
+  const uint8_t* arena = reinterpret_cast<const uint8_t*>(ar);
+  const uint32_t segOff = __shfl_sync(0xFFFFFFFFu, ia.z, 0), segChunks = __shfl_sync(0xFFFFFFFFu, ia.w, 0);
+  const uint32_t leafOffOff = __shfl_sync(0xFFFFFFFFu, ib.x, 0), leafValOff = __shfl_sync(0xFFFFFFFFu, ib.y, 0);
+  // (timing probe only == 4: the stream-side half of the item comes from the same few units over and over, see src_of)
+  if (lane < 4u) cp16(wbase + VR6_WARP_ITEM + 16u * lane, reinterpret_cast<const uint8_t*>(p.parse + (lane == 0u ? src_of(p, idx) : idx)) + 16u * lane);
+  else if (lane < 12u) cp16(wbase + VR6_WARP_LEAFOFF + 16u * (lane - 4u), arena + leafOffOff + 16u * (lane - 4u));
+  else if (lane < 14u) cp16(wbase + VR6_WARP_LEAFVAL + 16u * (lane - 12u), arena + leafValOff + 16u * (lane - 12u));
+  const uint32_t st = wbase + VR6_WARP_STAGE + ((p.tmaOut && segChunks <= VR6_SMALL_CHUNKS) ? VR6_BOX_BYTES : 0u);
+  for (uint32_t c = lane; c < segChunks; c += 32u) cp16(st + 16u * c, arena + segOff + 16u * c);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// Pulls everything unit `idx` will stage into L2 -- its stream segment (one 128-byte line per lane), its index entries and its
+// item -- two units ahead of the staging copies: next to the constant groups HBM is write-saturated and a read that misses L2
+// takes several microseconds, longer than a unit takes to parse.  ia / ib valid in lane 0.
+__device__ __forceinline__ void prefetch_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t lane) {
+  const uint64_t ar = (uint64_t)__shfl_sync(0xFFFFFFFFu, ia.x, 0) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, ia.y, 0) << 32);
+  const uint32_t segOff = __shfl_sync(0xFFFFFFFFu, ia.z, 0), segChunks = __shfl_sync(0xFFFFFFFFu, ia.w, 0);
+  const uint32_t leafOffOff = __shfl_sync(0xFFFFFFFFu, ib.x, 0), leafValOff = __shfl_sync(0xFFFFFFFFu, ib.y, 0);
+  for (uint32_t l = lane; l * 8u < segChunks + 7u; l += 32u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + segOff + 128ull * l));
+  if (lane == 29u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafOffOff));
+  if (lane == 30u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafValOff));
+  if (lane == 31u) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint8_t*>(p.parse + idx)));
+}
+
+// One parse warp: its own queue tickets, staging area and leaf blocks -- no barrier with any other warp, so a warp whose unit
+// is empty or heavily pruned moves on while its neighbours are still parsing (with one barrier per tile and group of 8 warps,
+// the warps of a group waited 2.8 issue slots per instruction issued for the slowest of them: profiles/r2_decode.md).
+// Software pipeline over units n: ticket n+3 (atomic) and item n+2 (two 16-byte loads by lane 0) are requested and unit
+// n+1's segment is pulled into L2 while unit n is parsed; unit n+1 is staged while unit n's voxels are stored.
+template <int ROT>
+__device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_t sb, const uint32_t warp, const uint32_t lane) {
+  const uint32_t wbase = sb + VR6_LUT_BYTES + warp * VR6_WARP_BYTES;
+  const uint32_t strips = wbase + VR6_WARP_STRIPS, stageS = wbase + VR6_WARP_STAGE, boxS = wbase + VR6_WARP_STAGE;
+  const uint32_t lutS = sb + VR6_OFF_LUT;
+  const uint32_t xs0 = p.pg.xs[0], xs1 = p.pg.xs[1];
+  const uint32_t myStrip = strips + lane * VR6_STRIP_PITCH;
+  // phase-2 constants of this lane for unit 0 of a tile (the unit index adds a per-unit offset): four 16-byte runs
+  // (tensor-store mode: gRun = the run's place in the unit's dense box in shared memory instead of its offset in the slab)
+  uint32_t sRun[4], gRun[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    uint32_t s;
+    int64_t go;
+    vr6::p6_run_addr(p.pg, 0u, lane + 32u * (uint32_t)k, p.rowPitch, p.slicePitch, &s, &go);
+    sRun[k] = strips + s;
+    gRun[k] = p.tmaOut ? boxS + vr6::p6_box_off(p.pg, lane + 32u * (uint32_t)k) : (uint32_t)go;
+  }
+  uint32_t unitOff[3];  // destination offset of unit bits 0..2
+#pragma unroll
+  for (int j = 0; j < 3; ++j)
+    unitOff[j] = (uint32_t)((p.pg.wAxis[j] == 0 ? (int64_t)1 : (p.pg.wAxis[j] == 1 ? p.rowPitch : p.slicePitch)) << p.pg.wCb[j]);
+
+  // idxA = unit being parsed, idxB = next (item half in b0 / b1), idxC = the one after (item half requested below).  Tickets are
+  // batches of VR6_BATCH consecutive units: (curBase, curPos) = where idxC sits in its batch, nextBase = the batch behind it,
+  // requested a whole batch ahead (lane 0 only).
+  const uint4 z4 = make_uint4(0, 0, 0, 0);
+  uint32_t idxA = 0, idxB = 0, idxC = 0, curBase = 0, curPos = 0, nextBase = 0;
+  uint4 a0 = z4, a1 = z4, b0 = z4, b1 = z4;
+  if (lane == 0) {
+    curBase = atomicAdd(p.queue, p.batch);
+    nextBase = atomicAdd(p.queue, p.batch);
+    // the first three units: positions 0, 1, 2 of the ticket sequence (tickets may hold fewer than three units)
+    idxA = curBase; curPos = 0u;
+    if (curPos + 1u < p.batch) { ++curPos; idxB = curBase + curPos; } else { curBase = nextBase; curPos = 0u; idxB = curBase; nextBase = atomicAdd(p.queue, p.batch); }
+    if (curPos + 1u < p.batch) { ++curPos; idxC = curBase + curPos; } else { curBase = nextBase; curPos = 0u; idxC = curBase; nextBase = atomicAdd(p.queue, p.batch); }
+    if (idxA < p.nParse) { a0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA))); a1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA)) + 1); }
+    if (idxB < p.nParse) { b0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB))); b1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB)) + 1); }
+  }
+  idxA = __shfl_sync(0xFFFFFFFFu, idxA, 0);
+  idxB = __shfl_sync(0xFFFFFFFFu, idxB, 0);
+  idxC = __shfl_sync(0xFFFFFFFFu, idxC, 0);
+  if (idxA < p.nParse) stage_unit(p, idxA, a0, a1, wbase, lane);
+  if (idxB < p.nParse) prefetch_unit(p, idxB, b0, b1, lane);
+  while (idxA < p.nParse) {
+    // requests for later units first, so that they are in flight while this one is parsed
+    uint4 c0 = z4, c1 = z4;
+    uint32_t idxD = 0;
+    if (lane == 0) {
+      if (idxC < p.nParse) { c0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC))); c1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC)) + 1); }
+      if (curPos + 1u < p.batch) { ++curPos; idxD = curBase + curPos; }
+      else { curBase = nextBase; curPos = 0u; idxD = curBase; nextBase = atomicAdd(p.queue, p.batch); }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    const uint4 i0 = lds128(wbase + VR6_WARP_ITEM), i2 = lds128(wbase + VR6_WARP_ITEM + 32u), i3 = lds128(wbase + VR6_WARP_ITEM + 48u);
+    const uint32_t segOff = i0.z, segChunks = i0.w;
+    const uint64_t treeDist = (uint64_t)i2.x | ((uint64_t)i2.y << 32);
+    const int64_t dstOff = (int64_t)((uint64_t)i2.z | ((uint64_t)i2.w << 32));
+    const int32_t occCell = (int32_t)i3.w;
+    const uint32_t unit = lds32(wbase + VR6_WARP_ITEM + 28u) & 7u;  // tileUnit
+    // ---- phase 1: one leaf subtree per lane ----
+    {
+      const uint32_t off = lds32(wbase + VR6_WARP_LEAFOFF + 4u * lane), val = lds8(wbase + VR6_WARP_LEAFVAL + lane);
+      vr6::Dist d;
+      d.d0 = (uint32_t)treeDist & 0xFFu; d.d1 = (uint32_t)(treeDist >> 8) & 0xFFu; d.d2 = (uint32_t)(treeDist >> 16) & 0xFFu;
+      d.d3 = (uint32_t)(treeDist >> 24) & 0xFFu; d.d4 = (uint32_t)(treeDist >> 32) & 0xFFu; d.d5 = (uint32_t)(treeDist >> 40) & 0xFFu;
+      if (off == VR_PRUNED) {
+        vr6::fill_leaf(myStrip, val);
+      } else {
+        vr6::WinShared w;
+        w.init(stageS + ((p.tmaOut && segChunks <= VR6_SMALL_CHUNKS) ? VR6_BOX_BYTES : 0u) - segOff, off);
+        vr6::parse_leaf<ROT>(w, val, d, lutS, myStrip);
+      }
+    }
+    __syncwarp();  // every lane is done with the staged segment, the index entries and the item; the leaf blocks are complete
+    // Unit n+1 is staged while unit n's voxels are stored.  Tensor-store mode: only if its segment fits behind the box; a
+    // longer one needs the whole staging area and has to wait until the TMA unit has read this unit's box (below).
+    const bool nextNow = idxB < p.nParse && (!p.tmaOut || __shfl_sync(0xFFFFFFFFu, b0.w, 0) <= VR6_SMALL_CHUNKS);
+    if (nextNow) stage_unit(p, idxB, b0, b1, wbase, lane);
+    // ---- phase 2: the warp's 32 leaf blocks -> 128 runs of 16 voxels along x, four per lane ----
+    uint8_t* dstUnit = p.dst + dstOff + ((unit & 1u) ? unitOff[0] : 0u) + ((unit & 2u) ? unitOff[1] : 0u) + ((unit & 4u) ? unitOff[2] : 0u);
+    if (p.tmaOut) {  // the box is free once the previous unit's tensor store has read it (issued a whole unit ago)
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      __syncwarp();
+    }
+    // byte maxima through 16-bit lanes: a 16-bit maximum is exact in its HIGH byte, so bytes 1 / 3 come from the words as they
+    // are and bytes 0 / 2 from the words shifted left by 8 (the shift runs on the multiply-add pipe)
+    uint32_t m13 = 0, m02 = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t a = sRun[k];
+      const uint32_t w0 = lds32(a), w1 = lds32(a + xs0), w2 = lds32(a + xs1), w3 = lds32(a + xs0 + xs1);
+      if (p.tmaOut) asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(gRun[k]), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+      else if (p.only != 3) *reinterpret_cast<uint4*>(dstUnit + gRun[k]) = make_uint4(w0, w1, w2, w3);  // (3: timing probe without the voxel stores)
+      m13 = __vmaxu2(__vmaxu2(m13, w0), __vmaxu2(w1, __vmaxu2(w2, w3)));
+      m02 = __vmaxu2(__vmaxu2(m02, w0 * 256u), __vmaxu2(w1 * 256u, __vmaxu2(w2 * 256u, w3 * 256u)));
+    }
+    if (p.tmaOut) {
+      // The unit leaves as ONE tensor store (16 x 16 x 8 box).  Ordinary stores of the lanes wait behind the constant groups'
+      // tensor stores whenever HBM is write-saturated, and since the load/store unit works in order, every shared-memory
+      // access of the SM then waits with them: the launch took fill + parse (profiles/r2_decode.md).  In the TMA queue the
+      // units simply take their turn.
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0 && p.only != 3) {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&p.unitMap[0]), "r"((int)i3.x),
+                     "r"((int)i3.y), "r"((int)i3.z), "r"(boxS)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      if (idxB < p.nParse && !nextNow) {  // a long segment next: it overwrites the box
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        stage_unit(p, idxB, b0, b1, wbase, lane);
+      }
+    }
+    if (p.occ && occCell >= 0) {  // this unit's maximum -> its slot of the tile's occupancy cell
+      uint32_t m = max(max((m13 >> 8) & 0xFFu, m13 >> 24), max((m02 >> 8) & 0xFFu, m02 >> 24));
+      m = __reduce_max_sync(0xFFFFFFFFu, m);
+      if (lane == 0) p.occ[(int64_t)occCell * 8 + unit] = (uint8_t)m;
+    }
+    __syncwarp();  // the leaf blocks are free for the next unit
+    if (idxC < p.nParse) prefetch_unit(p, idxC, c0, c1, lane);  // its item half was requested at the top of this iteration
+    idxA = idxB; idxB = idxC; idxC = __shfl_sync(0xFFFFFFFFu, idxD, 0);
+    b0 = c0; b1 = c1;
+  }
+  if (p.tmaOut && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // before the CTA's shared memory goes away
+}
+
+// The warp that feeds the TMA unit.  A constant group = 2^L x-neighbouring constant tiles (vr_fill_job): a row image of
+// (tx << L) x VR6_TMA_ROWS bytes in shared memory (byte j * tx.. = value of tile j), stored tz * ty / rows times.  Images
+// are cached by (L, values): a slab of mostly empty / mostly solid bricks rewrites them a handful of times per launch.
+__device__ __forceinline__ void fill_warp(const Decode6Params& p, const uint32_t sb, const uint32_t lane) {
+  const uint32_t img0 = sb + VR6_OFF_IMG;
+  const uint32_t ltx = 31u - (uint32_t)__clz(p.tx);
+  const uint32_t rows = (uint32_t)p.tmaRows, imgBytes = 256u * rows, nSlots = VR6_IMG_TOTAL / imgBytes;
+  const uint32_t rowBlocks = (uint32_t)p.ty / rows, per = (uint32_t)p.tz * rowBlocks;
+  uint64_t keyVals[VR6_IMG_SLOTS];
+  uint32_t keyL[VR6_IMG_SLOTS];
+#pragma unroll
+  for (int s = 0; s < VR6_IMG_SLOTS; ++s) { keyVals[s] = 0; keyL[s] = 0xFFFFFFFFu; }
+  uint32_t victim = 0;
+  uint64_t policy = 0;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  for (;;) {
+    uint32_t j0 = 0;
+    if (lane == 0) j0 = atomicAdd(p.queue + VR6_QUEUE_FILL, 8u);
+    j0 = __shfl_sync(0xFFFFFFFFu, j0, 0);
+    if (j0 >= p.nFill) break;
+    const uint32_t n = min(8u, p.nFill - j0);
+    uint4 a = make_uint4(0, 0, 0, 0), b = a;
+    if (lane < n) {
+      a = __ldg(reinterpret_cast<const uint4*>(p.fills + j0 + lane));
+      b = __ldg(reinterpret_cast<const uint4*>(p.fills + j0 + lane) + 1);
+    }
+    for (uint32_t k = 0; k < n; ++k) {
+      const int x = (int)__shfl_sync(0xFFFFFFFFu, a.x, k), y = (int)__shfl_sync(0xFFFFFFFFu, a.y, k), z = (int)__shfl_sync(0xFFFFFFFFu, a.z, k);
+      const uint32_t L = __shfl_sync(0xFFFFFFFFu, a.w, k);
+      const uint64_t vals = (uint64_t)__shfl_sync(0xFFFFFFFFu, b.x, k) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, b.y, k) << 32);
+      const int64_t cell = (int64_t)((uint64_t)__shfl_sync(0xFFFFFFFFu, b.z, k) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, b.w, k) << 32));
+      if (p.occ && cell >= 0 && lane < (1u << L)) {
+        const uint32_t w = (uint32_t)((vals >> (8 * lane)) & 0xFF) * 0x01010101u;
+        *reinterpret_cast<uint2*>(p.occ + (cell + lane) * 8) = make_uint2(w, w);
+      }
+      if (p.fillMode == 1) {  // A/B: the same group as 16-byte streaming stores of this one warp
+        vr_kd_geom gg;
+        gg.tx = p.tx; gg.ty = p.ty; gg.tz = p.tz;
+        vr_group_fill(gg, (int)L, vals, p.dst + (int64_t)z * p.slicePitch + (int64_t)y * p.rowPitch + x, p.rowPitch, p.slicePitch, lane, 32u);
+        continue;
+      }
+      int slotIdx = -1;
+#pragma unroll
+      for (int s = 0; s < VR6_IMG_SLOTS; ++s)
+        if ((uint32_t)s < nSlots && keyL[s] == L && keyVals[s] == vals) slotIdx = s;
+      if (slotIdx < 0) {  // warp-uniform: rewrite the least recently written image once the TMA unit has read it
+        slotIdx = (int)victim;
+        victim = (victim + 1u) % nSlots;
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < VR6_IMG_SLOTS; ++s)
+          if (s == slotIdx) { keyL[s] = L; keyVals[s] = vals; }
+        const uint32_t lW = ltx + L;                             // log2 row bytes of the group
+        const uint32_t pieces = (rows << lW) >> 4;               // 16-byte pieces of the image
+        const uint32_t img = img0 + (uint32_t)slotIdx * imgBytes;
+        for (uint32_t q = lane; q < pieces; q += 32u) {
+          const uint32_t xb = (q << 4) & ((1u << lW) - 1u);
+          const uint32_t w = (uint32_t)((vals >> (8 * (xb >> ltx))) & 0xFF) * 0x01010101u;
+          asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(img + 16u * q), "r"(w) : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+      }
+      const uint32_t img = img0 + (uint32_t)slotIdx * imgBytes;
+      const void* tm = &p.maps.m[L][0];
+      for (uint32_t s = lane; s < per; s += 32u) {
+        const int zz = z + (int)(s / rowBlocks), yy = y + (int)((s % rowBlocks) * rows);
+        if (p.fillMode == 2)
+          asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%1, %2, %3}], [%4], %5;" ::"l"(tm), "r"(x), "r"(yy),
+                       "r"(zz), "r"(img), "l"(policy)
+                       : "memory");
+        else
+          asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tm), "r"(x), "r"(yy), "r"(zz), "r"(img)
+                       : "memory");
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      // pacing (A/B knob): while parse units are still queued, leave a gap after every group so that the parse warps' voxel
+      // stores (ordinary stores, which wait behind the tensor stores when HBM is write-saturated) get through
+      if (p.fillThrottle && *reinterpret_cast<volatile uint32_t*>(p.queue) < p.nParse) __nanosleep(100u * (uint32_t)p.fillThrottle << L >> 3);
+    }
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the stores must have left before the CTA's shared memory goes away
+}
+
+template <int ROT>
+__global__ void __launch_bounds__(VR6_THREADS, 1) kd_decode6_kernel(const __grid_constant__ Decode6Params p) {
+  extern __shared__ __align__(128) uint8_t smem6[];
+  const uint32_t sb = (uint32_t)__cvta_generic_to_shared(smem6);
+  const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+  for (uint32_t i = tid; i < VR6_LUT_BYTES / 16u; i += VR6_THREADS) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.lut) + i);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sb + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  __syncthreads();
+  if (warp >= VR6_PARSE_WARPS) {
+    if (p.only != 1 && p.nFill) fill_warp(p, sb, lane);
+  } else if (p.only != 2 && p.nParse) {
+    parse_warp<ROT>(p, sb, warp, lane);
+  }
+}
+
+uint32_t kd_decode6_stage_chunks(void) { return VR6_STAGE_BYTES / 16u; }
+
+typedef CUresult (*VrEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static VrEncodeFn tensor_map_encoder() {
+  static VrEncodeFn enc = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      f = nullptr;
+    }
+    return (VrEncodeFn)f;
+  }();
+  return enc;
+}
+
+// 3-D uint8 tensor map over the slab with box bx x by x bz (dense in shared memory, x fastest)
+static bool box_map_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int bx, int by, int bz, unsigned char out[128]) {
+  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
+  VrEncodeFn enc = tensor_map_encoder();
+  if (!enc || bx <= 0 || bx > 256 || by <= 0 || by > 256 || bz <= 0 || bz > 256) return false;
+  if (SX % 16 || ((uintptr_t)vol) % 16 || SX >= (int64_t(1) << 32) || SY >= (int64_t(1) << 32) || SZ >= (int64_t(1) << 32)) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)SX, (cuuint64_t)SY, (cuuint64_t)SZ};
+  cuuint64_t strides[2] = {(cuuint64_t)SX, (cuuint64_t)SX * (cuuint64_t)SY};
+  cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, (cuuint32_t)bz};
+  cuuint32_t es[3] = {1, 1, 1};
+  return enc(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, int rows, VrFillMaps* out) {
+  VrEncodeFn enc = tensor_map_encoder();
+  if (!enc || tx < 16 || (tx << 3) > 256 || rows <= 0 || ty % rows) return false;
+  if (SX % 16 || ((uintptr_t)vol) % 16 || SX >= (int64_t(1) << 32) || SY >= (int64_t(1) << 32) || SZ >= (int64_t(1) << 32)) return false;
+  for (int L = 0; L <= 3; ++L) {
+    cuuint64_t dims[3] = {(cuuint64_t)SX, (cuuint64_t)SY, (cuuint64_t)SZ};
+    cuuint64_t strides[2] = {(cuuint64_t)SX, (cuuint64_t)SX * (cuuint64_t)SY};
+    cuuint32_t box[3] = {(cuuint32_t)(tx << L), (cuuint32_t)rows, 1};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = enc(reinterpret_cast<CUtensorMap*>(&out->m[L][0]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+  }
+  return true;
+}
+
+bool kd_decode6_plan(const vr_kd_geom& g, uint8_t* dst, int64_t SX, int64_t SY, int64_t SZ, Decode6Plan* out, int tmaRows) {
+  if (tmaRows != 8 && tmaRows != 16 && tmaRows != 32) return false;
+  out->tmaRows = tmaRows;
+  if (!vr6::p6_make_geom(g, &out->pg)) return false;
+  if (g.tx != 32 || g.ty % tmaRows) return false;                    // image slots are sized for 32-wide tiles
+  if ((int64_t)g.tz * SX * SY + (int64_t)g.ty * SX >= (int64_t(1) << 31)) return false;  // 32-bit run offsets inside a tile
+  if (!kd_fill_maps_create(dst, SX, SY, SZ, g.tx, g.ty, tmaRows, &out->maps)) return false;
+  if ((16u << out->pg.boxLy << out->pg.boxLz) != VR6_BOX_BYTES) return false;
+  if (!box_map_create(dst, SX, SY, SZ, 16, 1 << out->pg.boxLy, 1 << out->pg.boxLz, out->unitMap)) return false;
+  out->smemBytes = (size_t)VR6_OFF_IMG + (size_t)VR6_IMG_TOTAL;
+  return true;
+}
+
+template <int ROT>
+static cudaError_t launch6(const Decode6Params& p, size_t smem, int ctas, cudaStream_t stream) {
+  cudaError_t e = cudaFuncSetAttribute(kd_decode6_kernel<ROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  kd_decode6_kernel<ROT><<<(unsigned)ctas, VR6_THREADS, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t kd_decode6_launch(const vr_kd_geom& g, const Decode6Plan& plan, const vr_kd_job*, const vr_parse_item* parseDev, int nParse,
+                              const vr_fill_job* fillsDev, int nFill, uint32_t* queueDev, const uint32_t* lutDev, uint8_t* dst,
+                              int64_t rowPitch, int64_t slicePitch, uint8_t* occ, int only, cudaStream_t stream, int fillMode, int tmaOut) {
+  if (nParse <= 0 && nFill <= 0) return cudaSuccess;
+  static int numSMs = 0;
+  if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); }
+  Decode6Params p;
+  p.parse = parseDev; p.fills = fillsDev;
+  p.nParse = (uint32_t)(nParse > 0 ? nParse : 0); p.nFill = (uint32_t)(nFill > 0 ? nFill : 0);
+  p.queue = queueDev;
+  p.dst = dst; p.rowPitch = rowPitch; p.slicePitch = slicePitch;
+  p.lut = lutDev; p.occ = occ;
+  p.pg = plan.pg;
+  p.tx = g.tx; p.ty = g.ty; p.tz = g.tz;
+  p.only = only;
+  p.fillMode = fillMode & 0xFF;
+  p.fillThrottle = fillMode >> 8;
+  p.tmaRows = plan.tmaRows;
+  p.tmaOut = tmaOut ? 1 : 0;
+  memcpy(p.unitMap, plan.unitMap, 128);
+  p.maps = plan.maps;
+  cudaError_t e = cudaMemsetAsync(queueDev, 0, VR6_QUEUE_WORDS * sizeof(uint32_t), stream);
+  if (e != cudaSuccess) return e;
+  // enough CTAs for the work: a parse warp takes units one at a time, a fill warp groups eight at a time
+  const int wantP = (int)((p.nParse + VR6_PARSE_WARPS - 1u) / VR6_PARSE_WARPS), wantF = (int)((p.nFill + 7u) / 8u);
+  const int want = wantP > wantF ? wantP : wantF;
+  const int ctas = want < numSMs ? (want > 0 ? want : 1) : numSMs;
+  const uint32_t perWarp = p.nParse / (uint32_t)(ctas * VR6_PARSE_WARPS);
+  p.batch = perWarp >= 8u * VR6_BATCH_MAX ? VR6_BATCH_MAX : (perWarp >= 16u ? 2u : 1u);
+  // rot == 2 (last split along z) puts tile x bit 3 outside a warp's 32 leaf boxes: p6_make_geom never accepts it
+  if (plan.pg.rot == 0) return launch6<0>(p, plan.smemBytes, ctas, stream);
+  if (plan.pg.rot == 1) return launch6<1>(p, plan.smemBytes, ctas, stream);
+  return cudaErrorInvalidValue;
+}
+
+// =====================================================================================================================
+// classic kernel: one CTA per work-list entry
+// =====================================================================================================================
 struct DecodeParams {
   vr_kd_geom g;
   const vr_kd_job* jobs;
@@ -25,27 +470,12 @@ struct DecodeParams {
   int64_t rowPitch;    // slab X
   int64_t slicePitch;  // slab X*Y
   int vec16;
-  const vr_kd_work* work;  // one entry per CTA (kd_worklist.h)
+  const vr_kd_work* work;    // one entry per CTA (kd_worklist.h)
   const vr_fill_job* fills;  // constant groups attached to parse CTAs
-  int variant;  // parser variant of the fast path: 0 = v4 with 3-word window, chain length by ALU (default), 1 = v3 (length by ALU), 2 = v2, 3 = v3, 4 = v4 (length by ALU), 5 = v4 3-word window, 6 = v4
   // occupancy (occupancy.h): when a decode tile is exactly one cell the kernel stores the tile's maximum
   // (8 writer slots per cell: one per warp, so no CTA-wide reduction is needed)
   uint8_t* occ;             // null = off
   const int32_t* tileCell;  // [2^Dt] cell of the tile relative to the cell of the brick's (0,0,0)
-  // stream staging (VrWinStage): ranges[cta] = {first 16-byte chunk, chunks} of the tile's stream segment, copied to
-  // shared memory at byte offset stripBytes by the whole CTA with 128-bit loads before the parsers start
-  const vr_stage_range* ranges;      // null = off
-  uint32_t stripBytes;
-  // attached constant groups stored by the TMA unit (kd_decode.h): row images live at byte offset tmaOff of the dynamic
-  // shared memory, VR_TMA_MAX_ATTACH images of (tx << 3) * VR_TMA_BOX_ROWS bytes
-  int useTma;       // rows of a TMA box (0 = ordinary stores)
-  int skipParse;    // timing experiments: parse entries only issue their attached groups
-  uint32_t tmaOff;
-  VrFillMaps maps;
-  // persistent launch with SM roles (kd_decode_persistent_kernel)
-  int nWork, nParse, fillEvery;
-  uint32_t* queue;
-  uint32_t lutOff;  // variant 13: byte offset of the two-level chain table in the dynamic shared memory
 };
 
 // occupancy cell of tile `tile` of a brick whose (0,0,0) is cell occBase: tiles are 32x32x16 = one cell
@@ -69,60 +499,16 @@ __device__ __forceinline__ void attached_fills(const DecodeParams& p, uint32_t f
   }
 }
 
-// TMA variant of attached_fills: the CTA writes one row image per group ((tx << L) x 8 bytes) into shared memory, warp 0
-// issues the tensor stores (64 per group: 16 slices x 4 row blocks, two per lane) and everybody goes on to parse; the
-// issuing lanes wait for their bulk groups right before the CTA exits.  Must be called by all threads of the CTA.
-__device__ __forceinline__ void attached_fills_tma(const DecodeParams& p, uint32_t first, uint32_t count, uint32_t smemBase) {
-  const uint32_t boxRows = (uint32_t)p.useTma;
-  const uint32_t imgBytes = (uint32_t)(p.g.tx << 3) * boxRows;
-  const uint32_t ltx = (uint32_t)(31 - __clz(p.g.tx));
-  for (uint32_t k = 0; k < count; ++k) {
-    const vr_fill_job* fj = p.fills + first + k;
-    const uint4 a = __ldg(reinterpret_cast<const uint4*>(fj));
-    const uint4 b = __ldg(reinterpret_cast<const uint4*>(fj) + 1);
-    const uint64_t vals = (uint64_t)b.x | ((uint64_t)b.y << 32);
-    const int64_t cell = (int64_t)((uint64_t)b.z | ((uint64_t)b.w << 32));
-    if (p.occ && cell >= 0 && threadIdx.x < (1u << a.w)) {
-      const uint32_t w = (uint32_t)((vals >> (8 * threadIdx.x)) & 0xFF) * 0x01010101u;
-      *reinterpret_cast<uint2*>(p.occ + (cell + threadIdx.x) * 8) = make_uint2(w, w);
-    }
-    const uint32_t lW = ltx + a.w;                                  // log2 row bytes of the group
-    const uint32_t pieces = (boxRows << lW) >> 4;  // 16-byte pieces of the image
-    const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
-    for (uint32_t q = threadIdx.x; q < pieces; q += blockDim.x) {
-      const uint32_t xb = (q << 4) & ((1u << lW) - 1u);
-      const uint32_t w = (uint32_t)((vals >> (8 * (xb >> ltx))) & 0xFF) * 0x01010101u;
-      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(img + 16u * q), "r"(w) : "memory");
-    }
-  }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    const uint32_t rowBlocks = (uint32_t)p.g.ty / boxRows;
-    const uint32_t per = (uint32_t)p.g.tz * rowBlocks;  // stores per group
-    for (uint32_t k = 0; k < count; ++k) {
-      const vr_fill_job* fj = p.fills + first + k;
-      const uint4 a = __ldg(reinterpret_cast<const uint4*>(fj));
-      const void* tm = &p.maps.m[a.w][0];
-      const uint32_t img = smemBase + p.tmaOff + k * imgBytes;
-      for (uint32_t s = threadIdx.x; s < per; s += 32) {
-        const int z = (int)a.z + (int)(s / rowBlocks), y = (int)a.y + (int)((s % rowBlocks) * boxRows);
-        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tm), "r"((int)a.x), "r"(y), "r"(z),
-                     "r"(img)
-                     : "memory");
-      }
-    }
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  }
-}
-__device__ __forceinline__ void attached_fills_tma_wait() {
-  if (threadIdx.x < 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
+  const size_t lpt = size_t(1) << (g.tileBits - g.leafBits);
+  return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
 }
 
-// One work-list entry, executed by a whole CTA (strips = the CTA's dynamic shared memory, sTileBase = one shared word).
-__device__ __forceinline__ void decode_work_item(const DecodeParams& p, const uint32_t item, uint8_t* strips, int64_t& sTileBase) {
+__global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
+  extern __shared__ __align__(128) uint8_t strips[];
+  __shared__ int64_t sTileBase;
   const vr_kd_geom& g = p.g;
-  const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + item);  // {id, L, vals}
+  const uint4 wk = __ldg(reinterpret_cast<const uint4*>(p.work) + blockIdx.x);  // {id, L, vals}
   const uint32_t brick = wk.x >> g.Dt;
   const uint32_t tile = wk.x & ((1u << g.Dt) - 1u);
   const vr_kd_job& job = p.jobs[brick];
@@ -151,61 +537,14 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
     }
     return;
   }
-  // constant groups that ride along with this parse CTA (wk.z = first, wk.w = count | late << 31): half of the CTAs
-  // store them before parsing, the other half afterwards, so that at any time some CTAs of an SM write (HBM bound)
-  // while the others parse (issue bound); with one order for all, the CTAs of a wave would fill and parse in step.
-  const bool late = (wk.w >> 31) != 0;
-  const bool tma = p.useTma && (wk.w & 0x7FFFFFFFu) != 0;  // CTA-uniform
-  if (tma) attached_fills_tma(p, wk.z, wk.w & 0x7FFFFFFFu, (uint32_t)__cvta_generic_to_shared(strips));
-  else if (!late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
-  if (p.skipParse) { if (tma) attached_fills_tma_wait(); else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu); return; }
+  // constant groups that ride along with this parse CTA (wk.z = first, wk.w = count): stored before parsing
+  attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
   const uint32_t blk = __ldg(job.tileLeafBlock + tile);
   const uint32_t items = vr_tile_items(g);
   if (g.fastPath && p.vec16) {
     // fast path: 256 parsers, chains by table look-up, warp-local hand-off to the store phase (no CTA barrier)
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(strips);
-    uint2 rg = make_uint2(0u, 0u);
-    if (p.ranges) rg = __ldg(reinterpret_cast<const uint2*>(p.ranges) + item);
-    if (p.variant == 13) {  // two-level chain table in shared memory, stream staged when the segment fits
-      const uint32_t lutS = sbase + p.lutOff;
-      for (uint32_t i = threadIdx.x; i < VR_LUT2_ENTRIES; i += blockDim.x) {
-        const uint32_t v = __ldg(job.chainLut + VR_LUT2_OFF + i);
-        asm volatile("st.shared.b32 [%0], %1;" ::"r"(lutS + 4u * i), "r"(v) : "memory");
-      }
-      const uint32_t stage = sbase + p.stripBytes;
-      if (rg.y) {
-        const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
-        for (uint32_t j = threadIdx.x; j < rg.y; j += blockDim.x) {
-          const uint4 v = __ldg(src + j);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + 16u * j), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-        }
-      }
-      __syncthreads();
-      const uint32_t* lut2 = reinterpret_cast<const uint32_t*>((uintptr_t)lutS);
-      if (rg.y) vr_tile_phase1_v5_l2<uint32_t, VrWinStageL>(job, g, blk, threadIdx.x, sbase, lut2, stage - 16u * rg.x);
-      else vr_tile_phase1_v5_l2<uint32_t, VrWin32L>(job, g, blk, threadIdx.x, sbase, lut2, 0u);
-    } else if (rg.y) {  // CTA-uniform: stage the tile's stream segment, then parse out of shared memory
-      const uint4* src = reinterpret_cast<const uint4*>(job.words) + rg.x;
-      const uint32_t stage = sbase + p.stripBytes;
-      for (uint32_t j = threadIdx.x; j < rg.y; j += blockDim.x) {
-        const uint4 v = __ldg(src + j);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + 16u * j), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-      }
-      __syncthreads();
-      vr_tile_phase1_v5_staged<true, uint32_t>(job, g, blk, threadIdx.x, sbase, stage - 16u * rg.x);
-    } else if (p.variant == 0) vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 12) vr_tile_phase1_v5<true, uint32_t, VrWin128>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 10) vr_tile_phase1_v5<false, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 11) vr_tile_phase1_v4<true, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 5) vr_tile_phase1_v4<false, uint32_t, VrWin96>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 7) vr_tile_phase1_v4<true, uint32_t, VrWin96, 0>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 8) vr_tile_phase1_v4<true, uint32_t, VrWin96, 1>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 9) vr_tile_phase1_v4<true, uint32_t, VrWin96, 4>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 6) vr_tile_phase1_v4<false>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 1) vr_tile_phase1_v3<true>(job, g, blk, threadIdx.x, sbase);
-    else if (p.variant == 2) vr_tile_phase1_v2(job, g, blk, threadIdx.x, strips);
-    else if (p.variant == 3) vr_tile_phase1_v3<false>(job, g, blk, threadIdx.x, sbase);
-    else vr_tile_phase1_v4<true>(job, g, blk, threadIdx.x, sbase);
+    vr_tile_phase1_v5<true, uint32_t, VrWin32>(job, g, blk, threadIdx.x, sbase);
     __syncwarp();
     int64_t tb = job.dstOffset;  // tile origin, recomputed per thread (no CTA barrier on this path)
     for (int d = 0; d < g.Dt; ++d)
@@ -223,8 +562,6 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
       m = __reduce_max_sync(0xFFFFFFFFu, m);
       if (lane == 0) p.occ[tile_cell(p, job, tile) * 8 + warp] = (uint8_t)m;
     }
-    if (tma) attached_fills_tma_wait();
-    else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
     return;
   }
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
@@ -233,99 +570,11 @@ __device__ __forceinline__ void decode_work_item(const DecodeParams& p, const ui
   uint8_t* dst = p.dst + sTileBase;
   for (uint32_t it = threadIdx.x; it < items; it += blockDim.x)
     vr_tile_phase2_item(g, it, strips, dst, p.rowPitch, p.slicePitch, p.vec16 != 0);
-  if (tma) attached_fills_tma_wait();
-  else if (late) attached_fills(p, wk.z, wk.w & 0x7FFFFFFFu);
-}
-
-size_t kd_decode_smem_bytes(const vr_kd_geom& g) {
-  const size_t lpt = size_t(1) << (g.tileBits - g.leafBits);
-  return lpt * ((size_t(1) << g.leafBits) + VR_LEAF_PITCH_PAD);
-}
-
-__global__ void __launch_bounds__(256, 6) kd_decode_tiles_kernel(const __grid_constant__ DecodeParams p) {
-  extern __shared__ __align__(128) uint8_t strips[];
-  __shared__ int64_t sTileBase;
-  decode_work_item(p, blockIdx.x, strips, sTileBase);
-}
-
-// Persistent variant with SM roles: the work list holds the parse entries first ([0, nParse)) and the constant groups
-// behind them; CTAs on every fillEvery-th SM (by %smid) drain the fill queue first, all others the parse queue first, and
-// either kind helps the other once its own queue is empty.  While HBM is write-saturated a parse CTA's own 16 KB of voxel
-// stores wait behind whatever its SM has queued; confining the fills to a subset of the SMs keeps the other SMs' store
-// queues short (profiles/r1_decode_overlap.md).  queue[0] / queue[1] = next parse / fill entry, zeroed before the launch.
-__global__ void __launch_bounds__(256, 6) kd_decode_persistent_kernel(const __grid_constant__ DecodeParams p) {
-  extern __shared__ __align__(128) uint8_t strips[];
-  __shared__ int64_t sTileBase;
-  __shared__ uint32_t sItem;
-  uint32_t smid;
-  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-  const uint32_t mine = (smid % (uint32_t)p.fillEvery) == 0 ? 1u : 0u;
-  const uint32_t base[2] = {0u, (uint32_t)p.nParse}, count[2] = {(uint32_t)p.nParse, (uint32_t)(p.nWork - p.nParse)};
-  for (;;) {
-    if (threadIdx.x == 0) {
-      uint32_t it = 0xFFFFFFFFu;
-      for (uint32_t t = 0; t < 2 && it == 0xFFFFFFFFu; ++t) {
-        const uint32_t q = mine ^ t;
-        if (count[q] == 0) continue;
-        const uint32_t k = atomicAdd(p.queue + q, 1u);
-        if (k < count[q]) it = base[q] + k;
-      }
-      sItem = it;
-    }
-    __syncthreads();
-    const uint32_t it = sItem;
-    __syncthreads();
-    if (it == 0xFFFFFFFFu) return;
-    decode_work_item(p, it, strips, sTileBase);
-  }
-}
-
-__global__ void __launch_bounds__(256) kd_prefetch_l2_kernel(const uint8_t* const* __restrict__ ptrs, const uint32_t* __restrict__ lines) {
-  const uint8_t* base = ptrs[blockIdx.y];
-  const uint32_t n = lines[blockIdx.y];
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(base + (size_t)i * 128));
-}
-
-cudaError_t kd_prefetch_l2_launch(const uint8_t* const* ptrsDev, const uint32_t* linesDev, int n, cudaStream_t stream) {
-  if (n <= 0) return cudaSuccess;
-  kd_prefetch_l2_kernel<<<dim3(32, (unsigned)n), 256, 0, stream>>>(ptrsDev, linesDev);
-  return cudaGetLastError();
-}
-
-typedef CUresult (*VrEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int tx, int ty, int rows, VrFillMaps* out) {
-  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
-  static VrEncodeFn enc = [] {
-    void* f = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
-      (void)cudaGetLastError();
-      f = nullptr;
-    }
-    return (VrEncodeFn)f;
-  }();
-  if (!enc || tx < 16 || (tx << 3) > 256 || rows <= 0 || ty % rows) return false;
-  if (SX % 16 || ((uintptr_t)vol) % 16 || SX >= (int64_t(1) << 32) || SY >= (int64_t(1) << 32) || SZ >= (int64_t(1) << 32)) return false;
-  for (int L = 0; L <= 3; ++L) {
-    cuuint64_t dims[3] = {(cuuint64_t)SX, (cuuint64_t)SY, (cuuint64_t)SZ};
-    cuuint64_t strides[2] = {(cuuint64_t)SX, (cuuint64_t)SX * (cuuint64_t)SY};
-    cuuint32_t box[3] = {(cuuint32_t)(tx << L), (cuuint32_t)rows, 1};
-    cuuint32_t es[3] = {1, 1, 1};
-    CUresult r = enc(reinterpret_cast<CUtensorMap*>(&out->m[L][0]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, es,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return false;
-  }
-  return true;
 }
 
 cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, const vr_kd_work* workDev, int nWork, uint8_t* dst,
                              int64_t rowPitch, int64_t slicePitch, bool vec16, cudaStream_t stream, uint8_t* occ,
-                             const int32_t* tileCell, const vr_fill_job* fillsDev, const vr_stage_range* rangesDev, int stageBytes,
-                             const VrFillMaps* tmaMaps, int nParse, int fillEvery, uint32_t* queueDev, int tmaRows) {
+                             const int32_t* tileCell, const vr_fill_job* fillsDev) {
   if (nWork <= 0) return cudaSuccess;
   DecodeParams p;
   p.g = g;
@@ -336,50 +585,9 @@ cudaError_t kd_decode_launch(const vr_kd_geom& g, const vr_kd_job* jobsDev, cons
   p.rowPitch = rowPitch;
   p.slicePitch = slicePitch;
   p.vec16 = vec16 ? 1 : 0;
-  p.occ = tileCell ? occ : nullptr; p.tileCell = tileCell;
-  {
-    static int variant = -1;
-    if (variant < 0) { const char* e = getenv("VR_DECODE_VARIANT"); variant = e ? atoi(e) : 0; }
-    p.variant = variant;
-  }
-  p.ranges = stageBytes > 0 ? rangesDev : nullptr;
-  p.stripBytes = (uint32_t)kd_decode_smem_bytes(g);
-  size_t smem = kd_decode_smem_bytes(g) + (p.ranges ? (size_t)stageBytes : 0);
-  p.useTma = 0; p.tmaOff = 0;
-  {
-    static int skip = -1;
-    if (skip < 0) { const char* e = getenv("VR_DECODE_ONLY"); skip = (e && atoi(e) == 3) ? 1 : 0; }
-    p.skipParse = skip;
-  }
-  if (tmaMaps && tmaRows > 0 && fillsDev && vec16 && g.tx >= 16 && (g.tx << 3) <= 256 && g.ty % tmaRows == 0) {
-    p.useTma = tmaRows;
-    p.maps = *tmaMaps;
-    p.tmaOff = (uint32_t)((smem + 127) & ~size_t(127));
-    smem = p.tmaOff + (size_t)VR_TMA_MAX_ATTACH * (size_t)(g.tx << 3) * (size_t)tmaRows;
-  }
-  p.lutOff = 0;
-  if (p.variant == 13) {
-    p.lutOff = (uint32_t)((smem + 15) & ~size_t(15));
-    smem = p.lutOff + 4u * VR_LUT2_ENTRIES + 64;
-  }
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kd_decode_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-  }
-  p.nWork = nWork; p.nParse = nParse; p.fillEvery = fillEvery; p.queue = queueDev;
-  if (fillEvery > 0 && queueDev && nParse >= 0 && nParse <= nWork) {
-    static int numSMs = 0;
-    if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); }
-    if (smem > 48 * 1024) {
-      cudaError_t e = cudaFuncSetAttribute(kd_decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return e;
-    }
-    cudaError_t e = cudaMemsetAsync(queueDev, 0, 2 * sizeof(uint32_t), stream);
-    if (e != cudaSuccess) return e;
-    const int ctas = numSMs * 6 < nWork ? numSMs * 6 : nWork;
-    kd_decode_persistent_kernel<<<(unsigned)ctas, 256, smem, stream>>>(p);
-    return cudaGetLastError();
-  }
+  p.occ = tileCell ? occ : nullptr;
+  p.tileCell = tileCell;
+  const size_t smem = kd_decode_smem_bytes(g);
   kd_decode_tiles_kernel<<<(unsigned)nWork, 256, smem, stream>>>(p);
   return cudaGetLastError();
 }

@@ -60,24 +60,24 @@ typedef struct vr_fill_job {
   int64_t occCell;   // occupancy cell of the first tile (members follow at +1), < 0 = none
 } vr_fill_job;
 
-// One tile of the persistent kernel's parse queue (kd_decode.cu: kd_decode6_kernel; host: kd_build_worklist6); 48 bytes, read
-// as three 16-byte words.
+// One unit of the persistent kernel's parse queue (kd_decode.cu: kd_decode6_kernel; host: kd_build_worklist6 fills the
+// bookkeeping fields, the C ABI layer the device addresses).  A unit = 32 consecutive leaf boxes of a tile (2 048 voxels): the
+// work of one warp.  64 bytes, self-contained: the warp needs nothing else to decode the unit.
 typedef struct vr_parse_item {
-  uint32_t brick, tile;  // job index, tile slot (path prefix of Dt bits)
-  uint32_t blk;          // tileLeafBlock[tile]: block of 256 leaf entries
-  uint32_t seg0;         // first 16-byte chunk of the tile's stream segment ...
-  uint32_t segChunks;    // ... and how many to stage in shared memory (0: the segment is too long, parse from global memory)
-  uint32_t pad0;
-  int64_t dst;           // voxel offset of the tile origin inside the destination slab
-  int64_t occCell;       // occupancy cell of the tile, < 0 = none
-  uint64_t pad1;
+  // --- what the lane that requests the staging copies reads (32 bytes) ---
+  const uint8_t* arena;  // device image of the prepared stream (the packed stream sits at offset 0)
+  uint32_t segOff;       // byte offset of the first 16-byte chunk of the unit's stream segment ...
+  uint32_t segChunks;    // ... and how many chunks to stage in shared memory (0: no live leaf, nothing to parse)
+  uint32_t leafOffOff;   // byte offset inside the arena of the unit's 32 leafOff entries ...
+  uint32_t leafValOff;   // ... and of its 32 leafVal entries
+  uint32_t leaf0;        // index of the unit's first leaf entry = tileLeafBlock[tile] * 256 + 32 * unit
+  uint32_t tileUnit;     // tile << 3 | unit (unit = which eighth of the tile; also the warp slot of the occupancy cell)
+  // --- what every lane reads ---
+  uint64_t treeDist;     // byte h = distanceMap[D0 - h], h = 0..6
+  int64_t dst;           // voxel offset of the TILE origin inside the destination slab
+  int32_t ux, uy, uz;    // voxel coordinates of the UNIT's box in the destination (tensor-store coordinates)
+  int32_t occCell;       // occupancy cell of the tile, < 0 = none
 } vr_parse_item;
-
-// Stream segment a parse CTA stages in shared memory (VrWinStage): first 16-byte chunk of the brick's stream and the
-// number of chunks; {0, 0} = not staged.  Read as one 8-byte word by the kernel.
-typedef struct vr_stage_range {
-  uint32_t first, count;
-} vr_stage_range;
 
 // A tile the lazy decode leaves out (kd_cull.h): its occupancy cell and the exact maximum of its voxels.
 typedef struct vr_occ_set {
@@ -419,91 +419,6 @@ VR_HD uint32_t vr_chain_lut_entry(uint32_t codes14, uint64_t chainDist) {
   return (uint32_t)(A & 0xFF) | ((uint32_t)lo << 8) | ((uint32_t)hi << 16) | ((uint32_t)L << 24);
 }
 
-// Bit window: low bits of `win` are the next symbols; > 32 valid bits after every skip().
-struct VrWindow {
-  const uint32_t* w;  // next word to load
-  uint64_t win;
-  int have;
-  VR_HD void init(const uint32_t* words, uint32_t sym) {
-    w = words + (sym >> 4);
-    const int sh = (int)(sym & 15) * 2;
-    win = (uint64_t)VR_LDG32(w) >> sh;
-    have = 32 - sh;
-    win |= (uint64_t)VR_LDG32(w + 1) << have;
-    have += 32;
-    w += 2;
-  }
-  VR_HD void skip(int nbits) {
-    win >>= nbits;
-    have -= nbits;
-    if (have <= 32) {
-      win |= (uint64_t)VR_LDG32(w) << have;
-      have += 32;
-      ++w;
-    }
-  }
-};
-
-// Leaf-subtree parser, v2: value stack as a byte shift register (top = parent of the next node), whole
-// refinement chains resolved by one table look-up.  Same contract as vr_decode_leaf.
-template <typename Sink>
-VR_HD void vr_decode_leaf_v2(VrWindow& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut, Sink& sink) {
-  const uint32_t total = 1u << leafBits;
-  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
-  uint64_t stack = (uint64_t)ownVal;
-  int h = leafBits - 1;
-  uint32_t v = 0;
-  for (;;) {
-    const int c = (int)(rd.win & 3);
-    const int pv = (int)(stack & 0xFF);
-    if (h > 0) {
-      if (c == 3) {  // constant box of 2^h voxels
-        sink.fill(v, 1u << h, pv);
-        v += 1u << h;
-        rd.skip(2);
-      } else {
-        const int val = vr_apply(pv, c, (int)((treeDist >> (8 * h)) & 0xFF));
-        stack = (stack << 8) | (uint64_t)val;
-        --h;
-        rd.skip(2);
-        continue;
-      }
-    } else {  // voxel + refinement chain
-      const uint32_t e = VR_LDG32(lut + ((uint32_t)(rd.win >> 2) & 0x3FFFu));
-      int val = vr_apply(pv, c, (int)(treeDist & 0xFF));
-      val += (int)(int8_t)(e & 0xFF);
-      const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
-      val = val < lo ? lo : val;
-      val = val > hi ? hi : val;
-      const bool leaf = c == 3;
-      sink.put(v, leaf ? pv : val);
-      v += 1;
-      rd.skip(leaf ? 2 : 2 + 2 * (int)(e >> 24));
-    }
-    if (v == total) break;
-    const int nh = VR_CTZ32(v);
-    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
-    h = nh;
-  }
-  sink.finish(total);
-}
-
-VR_HD void vr_tile_phase1_v2(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, uint8_t* strips) {
-  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
-  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
-  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
-  const int val = job.leafVal[(size_t)blk * lpt + leaf];
-  VrStripSink sink;
-  sink.init(strips + (size_t)leaf * pitch);
-  if (off == VR_PRUNED) {
-    sink.fill(0, 1u << g.leafBits, val);
-    return;
-  }
-  VrWindow rd;
-  rd.init(job.words, off);
-  vr_decode_leaf_v2(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
-}
-
 // Phase 2 over a "unit" = the 2^unitBits voxels whose tile path index shares the top bits `unit`
 // (a warp's 32 leaf subtrees when unitBits = leafBits + 5).  Item q = one 16-byte x-run; the other
 // unitBits-4 free path bits are enumerated by the bits of q in increasing path-bit order.
@@ -576,7 +491,6 @@ VR_HD void vr_st32(uint8_t* addr, uint32_t val) { *reinterpret_cast<uint32_t*>(a
 #endif
 
 struct VrWin32 {
-  static constexpr bool kSmemLut = false;
   const uint32_t* w;  // next word to load
   uint32_t cur, nxt;
   int bo;             // bit offset into cur, 0..31
@@ -599,303 +513,12 @@ struct VrWin32 {
   }
 };
 
-// Same window with one more word of look-ahead: the word loaded by a refill is not part of the window until
-// the NEXT refill (16 symbols later), so the load latency never sits on the parser's dependent chain
-// (profile of VrWin32: a third of the parser's stall samples were on the funnel shift that follows a refill).
-// Reads at most 3 words past the word that holds the last symbol consumed.
-struct VrWin96 {
-  static constexpr bool kSmemLut = false;
-  const uint32_t* w;
-  uint32_t cur, nxt, nn;
-  int bo;
-  VR_HD void init(const uint32_t* words, uint32_t sym) {
-    w = words + (sym >> 4);
-    cur = VR_LDG32(w);
-    nxt = VR_LDG32(w + 1);
-    nn = VR_LDG32(w + 2);
-    w += 3;
-    bo = (int)(sym & 15) * 2;
-  }
-  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
-  VR_HD void skip(int nbits) {
-    bo += nbits;
-    if (bo >= 32) {
-      cur = nxt;
-      nxt = nn;
-      nn = VR_LDG32(w);
-      ++w;
-      bo -= 32;
-    }
-  }
-};
-
-// 128-bit refills: the window proper is still (cur, nxt), but nxt is fed from a four-word register queue that one
-// 16-byte load fills when its last word has moved on -- a whole refill (16 symbols) before the first of the new
-// words is needed, so the load's latency is off the dependent chain, and every 32-byte sector of the stream is requested
-// twice instead of eight times (profiles/r1_decode_overlap.md: the 4-byte refills thrash L1 and wait on L2).
-// words must be 16-byte aligned; reads to the end of the 16-byte chunk after the one holding the last symbol.
-struct alignas(16) VrChunk16 { uint32_t x, y, z, w; };  // uint4 without the CUDA headers (this file also compiles as plain C++)
-struct VrWin128 {
-  static constexpr bool kSmemLut = false;
-  const VrChunk16* w;  // next chunk to load
-  uint32_t cur, nxt;
-  uint32_t b0, b1, b2, b3;  // queue, b0 = next word
-  int left;                 // words left in the queue
-  int bo;
-  VR_HD static VrChunk16 ld(const VrChunk16* p) {
-#if defined(__CUDA_ARCH__)
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-    return VrChunk16{v.x, v.y, v.z, v.w};
-#else
-    return *p;
-#endif
-  }
-  VR_HD uint32_t pop() {
-    const uint32_t r = b0;
-    b0 = b1; b1 = b2; b2 = b3;
-    if (--left == 0) {
-      const VrChunk16 q = ld(w);
-      ++w;
-      b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
-      left = 4;
-    }
-    return r;
-  }
-  VR_HD void init(const uint32_t* words, uint32_t sym) {
-    const uint32_t w0 = sym >> 4;
-    w = reinterpret_cast<const VrChunk16*>(words) + (w0 >> 2);
-    const VrChunk16 q = ld(w);
-    ++w;
-    b0 = q.x; b1 = q.y; b2 = q.z; b3 = q.w;
-    left = 4;
-    for (uint32_t k = 0; k < (w0 & 3u); ++k) (void)pop();
-    cur = pop();
-    nxt = pop();
-    bo = (int)(sym & 15) * 2;
-  }
-  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
-  VR_HD void skip(int nbits) {
-    bo += nbits;
-    if (bo >= 32) {
-      cur = nxt;
-      nxt = pop();
-      bo -= 32;
-    }
-  }
-};
-
-// The tile's whole stream segment staged in shared memory by the CTA (kd_decode.cu): the window refills from shared
-// memory, so the parser's dependent chain never waits on a global load -- its latency under a memory system that the
-// constant fills of the other CTAs keep saturated with writes is what made parsing and filling run one after the other
-// instead of side by side.  sbase = shared byte address of (virtual) word 0 of the stream, i.e. staged address - 4 * first
-// staged word; every word the parser can touch (the segment plus 3 words of look-ahead) is staged.
-struct VrWinStage {
-  static constexpr bool kSmemLut = false;
-  uint32_t sbase;
-  uint32_t wi;  // next word to load
-  uint32_t cur, nxt;
-  int bo;
-  VR_HD static uint32_t lds(uint32_t addr) {
-#if defined(__CUDA_ARCH__)
-    uint32_t v;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-#else
-    (void)addr;
-    return 0;
-#endif
-  }
-  VR_HD void init_staged(uint32_t sb, uint32_t sym) {
-    sbase = sb;
-    wi = sym >> 4;
-    cur = lds(sbase + 4u * wi);
-    nxt = lds(sbase + 4u * wi + 4u);
-    wi += 2;
-    bo = (int)(sym & 15) * 2;
-  }
-  VR_HD uint32_t peek() const { return VR_FUNNEL_R(cur, nxt, bo); }
-  VR_HD void skip(int nbits) {
-    bo += nbits;
-    if (bo >= 32) {
-      cur = nxt;
-      nxt = lds(sbase + 4u * wi);
-      ++wi;
-      bo -= 32;
-    }
-  }
-};
-
-// Two-level chain table (variant 13): the 64 KB table above lives in L1/L2, and under the fills every look-up that misses
-// L1 waits on a busy L2.  A chain's effect x -> min(max(x + A, lo), hi) is closed under composition, so the 7-symbol
-// table splits into symbols 0..4 (1 024 entries) and symbols 5..6 (16 entries, used as the identity when the chain ended
-// earlier): 4 160 bytes that each parse CTA copies into its shared memory.  Layout behind the 16 384-entry table:
-// [VR_LUT2_OFF, +1024) level 1, [+1024, +1040) level 2; entries as vr_chain_lut_entry.
-#define VR_LUT2_OFF 16384u
-#define VR_LUT2_ENTRIES 1040u
-// lut = host pointer to the 1 040 entries (emulation) or, on the device, the shared byte address cast to a pointer
-VR_HD uint32_t vr_lut2_load(const uint32_t* lut, uint32_t idx) {
-#if defined(__CUDA_ARCH__)
-  uint32_t v;
-  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"((uint32_t)(uintptr_t)lut + 4u * idx));
-  return v;
-#else
-  return lut[idx];
-#endif
-}
-struct VrWin32L : VrWin32 {
-  static constexpr bool kSmemLut = true;
-  VR_HD void init2(const uint32_t* words, uint32_t, uint32_t sym) { init(words, sym); }
-};
-struct VrWinStageL : VrWinStage {
-  static constexpr bool kSmemLut = true;
-  VR_HD void init2(const uint32_t*, uint32_t stageBase, uint32_t sym) { init_staged(stageBase, sym); }
-};
-
 // 1 = saturating add, 2 = saturating subtract, 0/3 = unchanged; no branches.
 VR_HD int vr_apply_bf(int parent, int code, int dist) {
   const int s = (code & 1) - (code >> 1);
   int v = parent + s * dist;
   v = v < 0 ? 0 : v;
   return v > 255 ? 255 : v;
-}
-
-template <typename SA>
-struct VrStripSink3 {
-  SA base;
-  uint32_t acc;
-  VR_HD void init(SA b) { base = b; acc = 0; }
-  VR_HD void put(uint32_t v, int val) {
-    acc |= (uint32_t)val << (8 * (v & 3));
-    if ((v & 3) == 3) {
-      VR_ST32(base + (v & ~3u), acc);
-      acc = 0;
-    }
-  }
-  VR_HD void fill(uint32_t v, uint32_t cnt, int val) {
-    const uint32_t word = (uint32_t)val * 0x01010101u;
-    if (cnt >= 4) {
-      for (uint32_t i = 0; i < cnt; i += 4) VR_ST32(base + v + i, word);
-    } else {  // cnt == 2 (cnt == 1 never reaches fill on this path): v is even
-      acc |= (word & 0xFFFFu) << (8 * (v & 3));
-      if (v & 2) { VR_ST32(base + (v & ~3u), acc); acc = 0; }
-    }
-  }
-};
-
-// CHAIN_LEN_ALU: take the chain length from the symbol bits (position of the first 3) instead of the
-// table entry, so the table load is off the parser's critical path.
-template <bool CHAIN_LEN_ALU, typename SA>
-VR_HD void vr_decode_leaf_v3(VrWin32& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
-                             VrStripSink3<SA>& sink) {
-  const uint32_t total = 1u << leafBits;  // leafBits >= 2 on this path
-  const int d0 = (int)(treeDist & 0xFF);
-  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
-  uint64_t stack = (uint64_t)ownVal;
-  int h = leafBits - 1;
-  uint32_t v = 0;
-  for (;;) {
-    uint32_t bits = rd.peek();
-    int c = (int)(bits & 3);
-    const int pv = (int)(stack & 0xFF);
-    if (h > 0) {
-      if (c == 3) {  // constant box of 2^h voxels
-        sink.fill(v, 1u << h, pv);
-        v += 1u << h;
-        rd.skip(2);
-      } else {
-        const int val = vr_apply_bf(pv, c, (int)((treeDist >> (8 * h)) & 0xFF));
-        stack = (stack << 8) | (uint64_t)val;
-        --h;
-        rd.skip(2);
-        continue;
-      }
-    } else {  // left and right voxel of one height-1 node, each with its refinement chain
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        if (t) { bits = rd.peek(); c = (int)(bits & 3); }
-        const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
-        int L;
-        if (CHAIN_LEN_ALU) {
-          const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;
-          L = (VR_CTZ32(m) >> 1) + 1;
-        } else {
-          L = (int)(e >> 24);
-        }
-        const bool leaf = c == 3;
-        rd.skip(leaf ? 2 : 2 + 2 * L);
-        int val = vr_apply_bf(pv, c, d0) + (int)(int8_t)(e & 0xFF);
-        const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
-        val = val < lo ? lo : val;
-        val = val > hi ? hi : val;
-        sink.put(v, leaf ? pv : val);
-        v += 1;
-      }
-    }
-    if (v == total) break;
-    const int nh = VR_CTZ32(v);
-    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
-    h = nh;
-  }
-}
-
-// v4: same arithmetic as v3, different control flow.  In v3 a loop iteration handles EITHER one inner node OR
-// one voxel pair, so the lanes of a warp (each at its own place in its own subtree) sit in different
-// branches most of the time and the warp pays for both bodies every iteration (profile: 20-28 of 32 lanes
-// active, 128 SASS instructions per iteration).  Here every iteration first runs a short descent loop over
-// inner nodes (the cheap body; lanes differ only in trip count, 1-5), after which all lanes are at a leaf
-// event -- a voxel pair, or occasionally a pruned box -- and execute the expensive pair body together.
-template <bool CHAIN_LEN_ALU, typename SA, typename WIN>
-VR_HD void vr_decode_leaf_v4(WIN& rd, int leafBits, int ownVal, uint64_t treeDist, const uint32_t* lut,
-                             VrStripSink3<SA>& sink) {
-  const uint32_t total = 1u << leafBits;  // leafBits >= 2 on this path
-  const int d0 = (int)(treeDist & 0xFF);
-  rd.skip(2);  // the root's own symbol (known internal); its effect is already in ownVal
-  uint64_t stack = (uint64_t)ownVal;
-  int h = leafBits - 1;
-  uint32_t v = 0;
-  for (;;) {
-    uint32_t bits = rd.peek();
-    int c = (int)(bits & 3);
-    while (h > 0 && c != 3) {  // descend through inner nodes
-      const int val = vr_apply_bf((int)(stack & 0xFF), c, (int)((treeDist >> (8 * h)) & 0xFF));
-      stack = (stack << 8) | (uint64_t)val;
-      --h;
-      rd.skip(2);
-      bits = rd.peek();
-      c = (int)(bits & 3);
-    }
-    const int pv = (int)(stack & 0xFF);
-    if (h > 0) {  // constant box of 2^h voxels
-      sink.fill(v, 1u << h, pv);
-      v += 1u << h;
-      rd.skip(2);
-    } else {  // left and right voxel of one height-1 node, each with its refinement chain
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        if (t) { bits = rd.peek(); c = (int)(bits & 3); }
-        const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
-        int L;
-        if (CHAIN_LEN_ALU) {
-          const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;
-          L = (VR_CTZ32(m) >> 1) + 1;
-        } else {
-          L = (int)(e >> 24);
-        }
-        const bool leaf = c == 3;
-        rd.skip(leaf ? 2 : 2 + 2 * L);
-        int val = vr_apply_bf(pv, c, d0) + (int)(int8_t)(e & 0xFF);
-        const int lo = (int)((e >> 8) & 0xFF), hi = (int)((e >> 16) & 0xFF);
-        val = val < lo ? lo : val;
-        val = val > hi ? hi : val;
-        sink.put(v, leaf ? pv : val);
-        v += 1;
-      }
-    }
-    if (v == total) break;
-    const int nh = VR_CTZ32(v);
-    stack >>= 8 * (nh - h);  // pop back to the parent of the next node
-    h = nh;
-  }
 }
 
 // v5: the three lowest levels of a leaf subtree (7 inner nodes, 8 voxels: an "octet") as straight-line code.
@@ -929,25 +552,6 @@ struct VrSub<0, POS, CHAIN_LEN_ALU, SA, WIN> {  // one voxel with its refinement
   static VR_HD void run(WIN& rd, int pv, uint64_t treeDist, const uint32_t* lut, SA base, uint32_t& acc) {
     const uint32_t bits = rd.peek();
     const int c = (int)(bits & 3);
-    if constexpr (WIN::kSmemLut) {  // two-level table in shared memory (VR_LUT2_*)
-      const uint32_t m = ((bits >> 2) & (bits >> 3) & 0x1555u) | 0x1000u;  // bit 2k: chain symbol k is a terminator
-      const int L = (VR_CTZ32(m) >> 1) + 1;
-      const uint32_t e1 = vr_lut2_load(lut, (bits >> 2) & 0x3FFu);
-      const uint32_t i2 = (m & 0x155u) ? 0xFu : ((bits >> 12) & 0xFu);  // chain ended within symbols 0..4: identity
-      const uint32_t e2 = vr_lut2_load(lut, 1024u + i2);
-      const bool leaf = c == 3;
-      rd.skip(leaf ? 2 : 2 + 2 * L);
-      int val = vr_apply_bf(pv, c, (int)(treeDist & 0xFF)) + (int)(int8_t)(e1 & 0xFF);
-      const int lo1 = (int)((e1 >> 8) & 0xFF), hi1 = (int)((e1 >> 16) & 0xFF);
-      val = val < lo1 ? lo1 : val;
-      val = val > hi1 ? hi1 : val;
-      val += (int)(int8_t)(e2 & 0xFF);
-      const int lo2 = (int)((e2 >> 8) & 0xFF), hi2 = (int)((e2 >> 16) & 0xFF);
-      val = val < lo2 ? lo2 : val;
-      val = val > hi2 ? hi2 : val;
-      acc |= (uint32_t)(leaf ? pv : val) << (8 * (POS & 3));
-      if ((POS & 3) == 3) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
-    } else {
     const uint32_t e = VR_LDG32(lut + ((bits >> 2) & 0x3FFFu));
     int L;
     if (CHAIN_LEN_ALU) {
@@ -964,7 +568,6 @@ struct VrSub<0, POS, CHAIN_LEN_ALU, SA, WIN> {  // one voxel with its refinement
     val = val > hi ? hi : val;
     acc |= (uint32_t)(leaf ? pv : val) << (8 * (POS & 3));
     if ((POS & 3) == 3) { VR_ST32(base + (POS & ~3), acc); acc = 0; }
-    }
   }
 };
 
@@ -1006,7 +609,7 @@ VR_HD void vr_decode_leaf_v5(WIN& rd, int leafBits, int ownVal, uint64_t treeDis
   }
 }
 
-template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32, int PF = VR_PREFETCH_LINES>
+template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32>
 VR_HD void vr_tile_phase1_v5(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
   const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
   const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
@@ -1021,85 +624,4 @@ VR_HD void vr_tile_phase1_v5(const vr_kd_job& job, const vr_kd_geom& g, uint32_t
   WIN rd;
   rd.init(job.words, off);
   vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
-}
-
-// v5 parser with the two-level chain table in shared memory; WIN = VrWin32L (stream from global memory) or VrWinStageL
-// (staged segment, stageBase as below); lut2 = the 1 040 entries (vr_lut2_load)
-template <typename SA, typename WIN>
-VR_HD void vr_tile_phase1_v5_l2(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips, const uint32_t* lut2,
-                                uint32_t stageBase) {
-  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
-  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
-  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
-  const int val = job.leafVal[(size_t)blk * lpt + leaf];
-  const SA base = strips + leaf * pitch;
-  if (off == VR_PRUNED) {
-    const uint32_t word = (uint32_t)val * 0x01010101u;
-    for (uint32_t i = 0; i < (1u << g.leafBits); i += 4) VR_ST32(base + i, word);
-    return;
-  }
-  WIN rd;
-  rd.init2(job.words, stageBase, off);
-  vr_decode_leaf_v5<true, SA, WIN>(rd, g.leafBits, val, job.treeDist, lut2, base);
-}
-
-// v5 parser over a staged segment (VrWinStage): stageBase = shared byte address of virtual word 0
-template <bool CHAIN_LEN_ALU, typename SA>
-VR_HD void vr_tile_phase1_v5_staged(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips, uint32_t stageBase) {
-  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
-  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
-  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
-  const int val = job.leafVal[(size_t)blk * lpt + leaf];
-  const SA base = strips + leaf * pitch;
-  if (off == VR_PRUNED) {
-    const uint32_t word = (uint32_t)val * 0x01010101u;
-    for (uint32_t i = 0; i < (1u << g.leafBits); i += 4) VR_ST32(base + i, word);
-    return;
-  }
-  VrWinStage rd;
-  rd.init_staged(stageBase, off);
-  vr_decode_leaf_v5<CHAIN_LEN_ALU, SA, VrWinStage>(rd, g.leafBits, val, job.treeDist, job.chainLut, base);
-}
-
-template <bool CHAIN_LEN_ALU, typename SA, typename WIN = VrWin32, int PF = VR_PREFETCH_LINES>
-VR_HD void vr_tile_phase1_v4(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
-  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
-  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
-  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
-  const int val = job.leafVal[(size_t)blk * lpt + leaf];
-  VrStripSink3<SA> sink;
-  sink.init(strips + leaf * pitch);
-  if (off == VR_PRUNED) {
-    sink.fill(0, 1u << g.leafBits, val);
-    return;
-  }
-#if defined(__CUDA_ARCH__)
-  // The segment of one leaf subtree is 50-160 bytes of the stream that nobody has touched yet: without help every
-  // 32-byte sector is a DRAM round trip in the middle of the dependent parse (a warp paid ~50 of them per tile, one
-  // after the other).  Ask for the lines now, all lanes at once, so that they are under way while the parse starts.
-  {
-    const char* q = reinterpret_cast<const char*>(job.words + (off >> 4));
-    for (int k = 0; k < PF; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + 128 * k));
-  }
-#endif
-  WIN rd;
-  rd.init(job.words, off);
-  vr_decode_leaf_v4<CHAIN_LEN_ALU, SA, WIN>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
-}
-
-template <bool CHAIN_LEN_ALU, typename SA>
-VR_HD void vr_tile_phase1_v3(const vr_kd_job& job, const vr_kd_geom& g, uint32_t blk, uint32_t leaf, SA strips) {
-  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
-  const uint32_t pitch = (1u << g.leafBits) + VR_LEAF_PITCH_PAD;
-  const uint32_t off = job.leafOff[(size_t)blk * lpt + leaf];
-  const int val = job.leafVal[(size_t)blk * lpt + leaf];
-  VrStripSink3<SA> sink;
-  sink.init(strips + leaf * pitch);
-  if (off == VR_PRUNED) {
-    sink.fill(0, 1u << g.leafBits, val);
-    return;
-  }
-  VrWin32 rd;
-  rd.init(job.words, off);
-  vr_decode_leaf_v3<CHAIN_LEN_ALU, SA>(rd, g.leafBits, val, job.treeDist, job.chainLut, sink);
 }

@@ -16,8 +16,8 @@
 //  * bit window: the three lowest levels of the tree (an octet: 7 nodes, 8 voxels) are straight-line code, so the
 //    places where the 32-bit window has to be re-aligned are known at compile time: 6 per octet instead of one per
 //    symbol, each branch-free (a refill is two predicated instructions).  Between them a token costs one shift.
-//  * stream words come from shared memory (the tile's segment is staged by a bulk copy) or, for the rare tile whose
-//    segment does not fit, from global memory through the same window type.
+//  * stream words come from shared memory: the unit's segment (at most 4.6 KB) is staged by asynchronous copies, so the
+//    parser's dependent chain never waits on global memory.
 #pragma once
 #include "kd_common.h"
 
@@ -25,6 +25,11 @@
 #define VR6_DEV 1
 #else
 #define VR6_DEV 0
+#endif
+#if defined(__CUDACC__)
+#define VR6_CE __host__ __device__ constexpr
+#else
+#define VR6_CE constexpr
 #endif
 
 namespace vr6 {
@@ -61,7 +66,11 @@ struct Mem {
   static __device__ __forceinline__ void st32(uint32_t a, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
   static __device__ __forceinline__ uint32_t ldg32(const uint32_t* p) { return __ldg(p); }
   static __device__ __forceinline__ uint32_t funnel(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
-  static __device__ __forceinline__ uint32_t perm(uint32_t a, uint32_t b, uint32_t s) { return __byte_perm(a, b, s); }
+  static __device__ __forceinline__ uint32_t perm(uint32_t a, uint32_t b, uint32_t s) {  // prmt as is (__byte_perm masks the selector first)
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
+    return r;
+  }
 };
 #else
 struct Mem {
@@ -88,11 +97,12 @@ struct Mem {
 
 // ---- bit windows ------------------------------------------------------------------------------------------------------
 // P = absolute bit position in the stream of the next unread symbol; (cur, nxt) = the stream words that hold bits
-// [32 * (P >> 5), +64).  advance_peek(n) consumes n <= 32 bits and returns the next 32 bits; crossing a word boundary is
-// the only conditional part (two moves and a load under one predicate, no branch).
+// [32 * (P >> 5), +64).  advance_peek(n) consumes (n & 0xFF) <= 32 bits and returns the next 32 bits; crossing a word boundary
+// is the only conditional part (two moves and a load under one predicate, no branch).  Only bits 0..5 of P are ever looked at
+// (the word address is tracked separately), so n may carry garbage above bit 7.
 struct WinShared {  // stream segment staged in shared memory; base = shared address of (virtual) word 0 of the stream
   uint32_t cur, nxt, P, wi;
-  VR_HD void init(uint32_t base, const uint32_t*, uint32_t sym) {
+  VR_HD void init(uint32_t base, uint32_t sym) {
     P = sym * 2u;
     const uint32_t a = base + ((P >> 5) << 2);
     cur = Mem::lds32(a);
@@ -106,33 +116,15 @@ struct WinShared {  // stream segment staged in shared memory; base = shared add
     return Mem::funnel(cur, nxt, P);
   }
 };
-struct WinGlobal {  // stream words from global memory (tiles whose segment does not fit the staging area)
-  uint32_t cur, nxt, P;
-  const uint32_t* w;
-  VR_HD void init(uint32_t, const uint32_t* words, uint32_t sym) {
-    P = sym * 2u;
-    w = words + (P >> 5);
-    cur = Mem::ldg32(w);
-    nxt = Mem::ldg32(w + 1);
-    w += 2;
-  }
-  VR_HD uint32_t advance_peek(uint32_t n) {
-    const uint32_t Pn = P + n;
-    if ((P ^ Pn) & 32u) { cur = nxt; nxt = Mem::ldg32(w); ++w; }
-    P = Pn;
-    return Mem::funnel(cur, nxt, P);
-  }
-};
-
 // ---- geometry of a 4x4x4 leaf box -------------------------------------------------------------------------------------
 // The six lowest tree levels of the bricks this path accepts split x, y, z cyclically (VolumeKdTree_recover.cpp:151-163 with
 // all three extents still >= 4), so path bit b of a voxel inside its leaf box (bit 0 = last split) carries coordinate bit
 // b / 3 of axis (ROT - b) mod 3, ROT = (D0 - 1) mod 3.  Block layout: byte offset = x + 4 y + 16 z.
 template <int ROT>
 struct Geo {
-  static constexpr int axis(int b) { return ((ROT - b) % 3 + 3) % 3; }
-  static constexpr int bitOff(int b) { return (axis(b) == 0 ? 1 : (axis(b) == 1 ? 4 : 16)) << (b / 3); }
-  static constexpr int off(int path) {  // path: up to 6 bits
+  static VR6_CE int axis(int b) { return ((ROT - b) % 3 + 3) % 3; }
+  static VR6_CE int bitOff(int b) { return (axis(b) == 0 ? 1 : (axis(b) == 1 ? 4 : 16)) << (b / 3); }
+  static VR6_CE int off(int path) {  // path: up to 6 bits
     int o = 0;
     for (int b = 0; b < 6; ++b) o += ((path >> b) & 1) ? bitOff(b) : 0;
     return o;
@@ -171,9 +163,21 @@ VR_HD int imin(int a, int b) { return a < b ? a : b; }
 VR_HD int imax(int a, int b) { return a > b ? a : b; }
 VR_HD uint32_t mkword(uint32_t n, uint32_t d) {
   const int up = imin((int)n + (int)d, 255), dn = imax((int)n - (int)d, 0);
-  return Mem::perm(n, Mem::perm((uint32_t)up, (uint32_t)dn, 0x0040u), 0x0540u);
+  // bytes 1, 2 by one permute, bytes 0 and 3 by a multiply-add: the integer pipe that carries every logic operation, shift
+  // and min/max of this parser is the kernel's bottleneck (68 % busy in ncu), the multiply-add pipe is nearly idle
+  return n * 0x01000001u + Mem::perm((uint32_t)up, (uint32_t)dn, 0x1401u);
 }
 VR_HD uint32_t child(uint32_t word, uint32_t c) { return Mem::perm(word, 0u, c | 0x4440u); }
+// the same from the window itself: selector = (bits & 3) | 0x4440 in one three-input logic operation
+VR_HD uint32_t child_of_bits(uint32_t word, uint32_t bits) {
+#if VR6_DEV
+  uint32_t sel;
+  asm("lop3.b32 %0, %1, 3, %2, 0xEA;" : "=r"(sel) : "r"(bits), "r"(0x4440u));
+  return Mem::perm(word, 0u, sel);
+#else
+  return Mem::perm(word, 0u, (bits & 3u) | 0x4440u);
+#endif
+}
 
 struct Dist { uint32_t d0, d1, d2, d3, d4, d5; };  // d_h = distanceMap[D0 - h]: applied to nodes at height h
 
@@ -186,37 +190,72 @@ struct Cur {
   WIN& w;
   uint32_t bits, o;
   uint32_t lut;  // shared address of the chain table
+  // o may carry garbage above bit 7 (voxel() adds whole table entries): the window only ever looks at bits 0..5 of its position
   VR_HD void repeek() { bits = w.advance_peek(o); o = 0; }
 };
+
+// Chain-table entry of the voxel item at the front of `bits`; the identity entry when the voxel's own symbol is 3.
+VR_HD uint32_t item_entry(uint32_t lut, uint32_t bits) {
+#if VR6_DEV
+  uint32_t e;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b32 t;\n"
+      "lop3.b32 t, %2, 3, 0, 0x0C;\n"   // ~bits & 3: zero iff the symbol is 3
+      "setp.ne.u32 p, t, 0;\n"
+      "mov.b32 %0, %3;\n"
+      "@p ld.shared.b32 %0, [%1];\n"
+      "}\n"
+      : "=r"(e)
+      : "r"(lut + (bits & 0xFFFCu)), "r"(bits), "n"(VR6_IDENT));
+  return e;
+#else
+  return (bits & 3u) == 3u ? VR6_IDENT : Mem::lds32(lut + (bits & 0xFFFCu));
+#endif
+}
+VR_HD bool is3(uint32_t bits) {  // front symbol == 3, as one logic operation with a predicate result
+#if VR6_DEV
+  uint32_t t;
+  asm("lop3.b32 %0, %1, 3, 0, 0x0C;" : "=r"(t) : "r"(bits));  // ~bits & 3
+  return t == 0u;
+#else
+  return (bits & 3u) == 3u;
+#endif
+}
+VR_HD uint32_t shr_wrap(uint32_t v, uint32_t n) {  // v >> (n & 31): a funnel shift takes the count modulo 32, so no mask is needed
+#if VR6_DEV
+  return __funnelshift_r(v, 0u, n);
+#else
+  return v >> (n & 31u);
+#endif
+}
 
 template <int ROT, int POS, class WIN>
 VR_HD void voxel(Cur<WIN>& s, uint32_t word, uint32_t base) {
   if (POS == 1 || POS == 2 || POS == 5 || POS == 6) s.repeek();
-  const uint32_t c = s.bits & 3u;
-  uint32_t e = Mem::lds32(s.lut + (s.bits & 0xFFFCu));
-  e = c == 3u ? VR6_IDENT : e;
-  const int x = (int)child(word, c);
-  const int lo = (int)((e >> 8) & 0xFFu), hi = (int)((e >> 16) & 0xFFu);
+  const uint32_t e = item_entry(s.lut, s.bits);
+  const int x = (int)child_of_bits(word, s.bits);
+  const int lo = (int)Mem::perm(e, 0u, 0x4441u), hi = (int)Mem::perm(e, 0u, 0x4442u);
   int v = x + ((int)e >> 24);
   v = imax(v, lo);
   v = imin(v, hi);
   Mem::st8(base + (uint32_t)Geo<ROT>::off(POS), (uint32_t)v);
-  const uint32_t nb = e & 0xFFu;
-  s.bits >>= nb;  // nb <= 16
-  s.o += nb;
+  s.bits = shr_wrap(s.bits, e);  // low byte of e = bits of the item (<= 16)
+  s.o += e;                      // only the low byte counts: repeek() masks
 }
 
 template <int ROT, int H, int POS, class WIN>
 struct Node {  // H = 1 or 2
   static VR_HD void run(Cur<WIN>& s, uint32_t word, const Dist& d, uint32_t base) {
     if (H == 2 && POS == 4) s.repeek();
-    const uint32_t c = s.bits & 3u;
+    const uint32_t bits0 = s.bits;
     s.bits >>= 2;
     s.o += 2u;
-    if (c == 3u) {
+    if (is3(bits0)) {
       fill_small<ROT, H, POS>(base, word >> 24);
     } else {
-      const uint32_t cw = mkword(child(word, c), H == 2 ? d.d1 : d.d0);
+      const uint32_t cw = mkword(child_of_bits(word, bits0), H == 2 ? d.d1 : d.d0);
       if constexpr (H == 2) {
         Node<ROT, 1, POS, WIN>::run(s, cw, d, base);
         Node<ROT, 1, POS + 2, WIN>::run(s, cw, d, base);
@@ -298,11 +337,13 @@ struct P6Geom {
   uint8_t fAxis[7];      // its axis (1 = y, 2 = z; 0 only for x bit 4 of a 32-wide tile) ...
   uint8_t fCb[7];        // ... and tile-local coordinate bit
   uint8_t wAxis[3], wCb[3];  // the warp index (top 3 leaf-index bits) likewise
+  uint8_t boxLy, boxLz;      // a unit's box is 16 x 2^boxLy x 2^boxLz voxels (16 x 16 x 8 for 256x256x128 bricks)
 };
 // false when the brick's tree does not have the shape this path is written for (kd_decode.cu then takes the generic kernel)
 static inline bool p6_make_geom(const vr_kd_geom& g, P6Geom* out) {
   if (g.tileBits != 14 || g.leafBits != 6 || g.tx < 16) return false;
   const int rot = (g.D0 - 1) % 3;
+  if (rot == 2) return false;  // tile x bit 3 would be path bit 11: not inside a warp's unit
   for (int b = 0; b < 6; ++b) {
     const int ax = ((rot - b) % 3 + 3) % 3;
     if (g.pbAxis[b] != ax || g.pbCoordBit[b] != b / 3) return false;
@@ -327,9 +368,28 @@ static inline bool p6_make_geom(const vr_kd_geom& g, P6Geom* out) {
     ++n;
   }
   if (n != 7) return false;
+  for (int k = 0; k < 7; ++k) {  // the free bits are the low y and z bits of the unit's box, each axis without gaps
+    if (p.fAxis[k] == 1) { if (p.fCb[k] != p.boxLy) return false; ++p.boxLy; }
+    else if (p.fAxis[k] == 2) { if (p.fCb[k] != p.boxLz) return false; ++p.boxLz; }
+    else return false;
+  }
   for (int j = 0; j < 3; ++j) { p.wAxis[j] = g.pbAxis[11 + j]; p.wCb[j] = g.pbCoordBit[11 + j]; }
   *out = p;
   return true;
+}
+// offset of run m inside the unit's dense box [z][y][16 x] (what the tensor store of a unit reads)
+VR_HD uint32_t p6_box_off(const P6Geom& p, uint32_t m) {
+  uint32_t o = 0;
+#pragma unroll
+  for (int k = 0; k < 7; ++k)
+    if ((m >> k) & 1u) o += (p.fAxis[k] == 1 ? 16u : (16u << p.boxLy)) << p.fCb[k];
+  return o;
+}
+// voxel coordinates of unit u's box relative to the tile origin
+VR_HD void p6_unit_origin(const P6Geom& p, uint32_t u, int32_t o[3]) {
+  o[0] = o[1] = o[2] = 0;
+  for (int j = 0; j < 3; ++j)
+    if ((u >> j) & 1u) o[p.wAxis[j]] += 1 << p.wCb[j];
 }
 // strip offset (relative to the tile's strips) and destination offset (relative to the tile origin) of run m of warp w
 VR_HD void p6_run_addr(const P6Geom& p, uint32_t w, uint32_t m, int64_t rowPitch, int64_t slicePitch, uint32_t* sOff, int64_t* gOff) {

@@ -57,10 +57,8 @@ namespace vr {
 int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out) {
   auto it = ctx->chainLuts.find(chainDist);
   if (it != ctx->chainLuts.end()) { *out = it->second; return VR_OK; }
-  std::vector<uint32_t> host((1u << 14) + VR_LUT2_ENTRIES);
+  std::vector<uint32_t> host(1u << 14);
   for (uint32_t i = 0; i < (1u << 14); ++i) host[i] = vr_chain_lut_entry(i, chainDist);
-  for (uint32_t i = 0; i < 1024u; ++i) host[VR_LUT2_OFF + i] = vr_chain_lut_entry(i | 0x3C00u, chainDist);         // symbols 0..4
-  for (uint32_t i = 0; i < 16u; ++i) host[VR_LUT2_OFF + 1024u + i] = vr_chain_lut_entry(i | 0x30u, chainDist >> 40);  // symbols 5..6
   uint32_t* dev = nullptr;
   CU(cudaMalloc((void**)&dev, host.size() * 4));
   cudaError_t e = cudaMemcpyAsync(dev, host.data(), host.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
@@ -146,6 +144,7 @@ int vr_volume_dims(const vr_volume* v, int64_t d[3]) {
 }
 int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host) {
   if (!ctx || !v || !host) return fail(VR_ERR_ARG, "null");
+  if (v->is_partial()) return fail(VR_ERR_STATE, "vr_volume_download: the volume was decoded lazily for one frame; run its plan in full first");
   CU(cudaSetDevice(ctx->device));
   CU(cudaMemcpyAsync(host, v->dev, (size_t)(v->SX * v->SY * v->SZ), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -174,14 +173,127 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
 void vr_decode_plan::lazy_free() {
-  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.rangesDev) cudaSetDevice(ctx->device);
-  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev); cudaFree(lazy.rangesDev);
+  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.parseDev) cudaSetDevice(ctx->device);
+  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev); cudaFree(lazy.parseDev);
   lazy = Lazy();
 }
 
-extern "C" { static int env_int(const char* name, int dflt); }
+// Debug knobs (vr_debug_set): explicit, process-wide, read when a plan is created / run.  Nothing in the library reads the
+// environment.  decode_kernel: 0 = persistent kernel where the brick shape allows it (default), 1 = classic kernel always.
+// decode_only: 0 = everything, 1 = parse tiles only, 2 = constant groups only (timing probes: the slab is then incomplete).
+namespace {
+struct DebugKnobs { int decodeKernel = 0, decodeOnly = 0, fillAttach = 2, fillMode = 2, tmaRows = 8, parseOrder = 0, unitStore = 0; } g_dbg;
+}
+extern "C" int vr_debug_set(const char* key, int value) {
+  if (!key) return fail(VR_ERR_ARG, "vr_debug_set: null key");
+  const std::string k(key);
+  if (k == "decode_kernel") g_dbg.decodeKernel = value;
+  else if (k == "decode_only") g_dbg.decodeOnly = value;
+  else if (k == "fill_attach") g_dbg.fillAttach = value;
+  else if (k == "fill_mode") g_dbg.fillMode = value;
+  else if (k == "tma_rows") g_dbg.tmaRows = value;
+  else if (k == "parse_order") g_dbg.parseOrder = value;
+  else if (k == "unit_store") g_dbg.unitStore = value;  // 0 / 1 = one tensor store per unit (default), 2 = 16-byte stores of the lanes
+  else return fail(VR_ERR_ARG, "vr_debug_set: unknown key");
+  return VR_OK;
+}
+extern "C" int vr_debug_get(const char* key, int* value) {
+  if (!key || !value) return fail(VR_ERR_ARG, "vr_debug_get: null");
+  const std::string k(key);
+  if (k == "decode_kernel") *value = g_dbg.decodeKernel;
+  else if (k == "decode_only") *value = g_dbg.decodeOnly;
+  else if (k == "fill_attach") *value = g_dbg.fillAttach;
+  else if (k == "fill_mode") *value = g_dbg.fillMode;
+  else if (k == "tma_rows") *value = g_dbg.tmaRows;
+  else if (k == "parse_order") *value = g_dbg.parseOrder;
+  else if (k == "unit_store") *value = g_dbg.unitStore;
+  else return fail(VR_ERR_ARG, "vr_debug_get: unknown key");
+  return VR_OK;
+}
 
 namespace vr {
+int context_chain_lut6(vr_context* ctx, uint64_t chainDist, const uint32_t** out) {
+  auto it = ctx->chainLuts6.find(chainDist);
+  if (it != ctx->chainLuts6.end()) { *out = it->second; return VR_OK; }
+  std::vector<uint32_t> host(VR6_LUT_ENTRIES);
+  for (uint32_t i = 0; i < VR6_LUT_ENTRIES; ++i) host[i] = vr6::chain_entry(i, chainDist);
+  uint32_t* dev = nullptr;
+  CU(cudaMalloc((void**)&dev, host.size() * 4));
+  cudaError_t e = cudaMemcpyAsync(dev, host.data(), host.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) { cudaFree(dev); return fail_cuda(e, "upload chain table"); }
+  ctx->chainLuts6[chainDist] = dev;
+  *out = dev;
+  return VR_OK;
+}
+
+template <typename T>
+static cudaError_t upload_vec(const std::vector<T>& v, T** dev) {
+  *dev = nullptr;
+  if (v.empty()) return cudaSuccess;
+  cudaError_t e = cudaMalloc((void**)dev, sizeof(T) * v.size());
+  if (e == cudaSuccess) e = cudaMemcpy(*dev, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(*dev); *dev = nullptr; }
+  return e;
+}
+
+// The work lists of one launch over the plan's bricks (all of them, or -- needed != null -- only the tiles a frame can read:
+// kd_cull.h).  Persistent kernel: parse items + constant groups; classic kernel: CTA list + attached groups.
+static int plan_build_lists(vr_decode_plan* p, const uint8_t* needed, std::vector<vr_occ_set>* culled, vr_parse_item** parseDev, int* nParse,
+                            vr_kd_work** workDev, int* nWork, vr_fill_job** fillsDev, int* nFill, int* tmaOut) {
+  const vr_kd_geom& g = p->geom;
+  const vr_volume* d = p->dst;
+  const int n = p->n;
+  std::vector<const KdIndex*> idx((size_t)n);
+  for (int i = 0; i < n; ++i) idx[(size_t)i] = &p->streams[(size_t)i]->kd.index;
+  const int64_t* ob = p->occFused ? p->occBase.data() : nullptr;
+  const int32_t* tc = p->occFused ? p->tileCellHost.data() : nullptr;
+  std::vector<vr_fill_job> fills;
+  *parseDev = nullptr; *workDev = nullptr; *fillsDev = nullptr; *nParse = 0; *nWork = 0; *nFill = 0; *tmaOut = 0;
+  cudaError_t e = cudaSuccess;
+  if (p->persistent6) {
+    std::vector<vr_parse_item> parse;
+    std::vector<uint32_t> brickOf;
+    if (!kd_build_worklist6(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->origins.data(), ob, tc, needed, culled,
+                            kd_decode6_stage_chunks(), p->p6.pg, &parse, &brickOf, &fills, g_dbg.parseOrder != 0))
+      return fail(VR_ERR_FORMAT, "a unit of the stream is longer than the grammar allows");
+    for (size_t i = 0; i < parse.size(); ++i) {  // device addresses of the brick's prepared stream
+      vr_parse_item& it = parse[i];
+      const vr_stream* s = p->streams[(size_t)brickOf[i]];
+      it.arena = s->devImage;
+      it.segOff += (uint32_t)s->offWords;
+      it.leafOffOff = (uint32_t)(s->offLeafOff + 4ull * it.leaf0);
+      it.leafValOff = (uint32_t)(s->offLeafVal + (uint64_t)it.leaf0);
+      it.treeDist = p->treeDist[(size_t)brickOf[i]];
+    }
+    // a unit's voxels leave as one tensor store (kd_decode.cu: parse_warp); measured faster than 16-byte stores of the lanes on
+    // all three workloads (slab 0.247 / 0.268 ms, config-3 layer 0.670 / 0.700, noise 0.265 / 0.288: profiles/r2_decode.md)
+    *tmaOut = g_dbg.unitStore == 2 ? 0 : 1;
+    e = upload_vec(parse, parseDev);
+    *nParse = (int)parse.size();
+  } else {
+    std::vector<vr_kd_work> work;
+    kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, 0, &work, &fills, std::min(g_dbg.fillAttach, 64),
+                      p->origins.data(), 0, ob, tc, needed, culled, needed ? 0 : g_dbg.decodeOnly);
+    e = upload_vec(work, workDev);
+    *nWork = (int)work.size();
+  }
+  if (e == cudaSuccess) e = upload_vec(fills, fillsDev);
+  *nFill = (int)fills.size();
+  if (e != cudaSuccess) { cudaFree(*parseDev); cudaFree(*workDev); *parseDev = nullptr; *workDev = nullptr; return fail_cuda(e, "upload work list"); }
+  return VR_OK;
+}
+
+static cudaError_t plan_launch(vr_decode_plan* p, const vr_parse_item* parseDev, int nParse, const vr_kd_work* workDev, int nWork,
+                               const vr_fill_job* fillsDev, int nFill, bool occ, int only, int tmaOut) {
+  vr_volume* d = p->dst;
+  if (p->persistent6)
+    return kd_decode6_launch(p->geom, p->p6, p->jobsDev, parseDev, nParse, fillsDev, nFill, p->queueDev, p->lut6Dev, d->dev, d->SX, d->SX * d->SY,
+                             occ ? d->occRaw : nullptr, only, p->ctx->stream, g_dbg.fillMode, tmaOut);
+  return kd_decode_launch(p->geom, p->jobsDev, workDev, nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
+                          occ ? p->tileCellDev : nullptr, fillsDev);
+}
+
 int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], const int stepReach[3]) {
   vr_decode_plan::Lazy& lz = p->lazy;
   if (lz.built && lz.mode == mode && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2] &&
@@ -204,39 +316,24 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
   std::vector<uint8_t> solid;
   cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, mode, thr,
              reach, stepReach, needed.data(), &solid);
-  std::vector<vr_kd_work> work;
-  std::vector<vr_fill_job> fills;
+  if (cudaSetDevice(p->ctx->device) != cudaSuccess) return fail(VR_ERR_CUDA, "cudaSetDevice");
   std::vector<vr_occ_set> culled;
-  std::vector<vr_stage_range> ranges;
-  kd_build_worklist(g, n, idx.data(), p->dstOffset.data(), d->SX, d->SX * d->SY, p->vec16, env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                    std::min(env_int("VR_FILL_ATTACH", 2), p->tma ? VR_TMA_MAX_ATTACH : 64), p->origins.data(), env_int("VR_FILL_LATE", 0), ob.data(), tc.data(), needed.data(), &culled,
-                    &ranges, p->stageBytes);
+  int rc = plan_build_lists(p, needed.data(), &culled, &lz.parseDev, &lz.nParse, &lz.workDev, &lz.nWork, &lz.fillJobsDev, &lz.nFill, &lz.tmaOut);
+  if (rc != VR_OK) return rc;
   lz.tilesTotal = (int64_t)n * nt;
   lz.tilesWritten = lz.tilesTotal - (int64_t)culled.size();
   lz.bytesVoxels = lz.tilesWritten * ((int64_t)g.tx * g.ty * g.tz);
   lz.bytesStream = 0;
-  for (const vr_kd_work& w : work)
-    if (w.L == VR_WORK_PARSE) {
-      const KdIndex& ix = *idx[(size_t)(w.id >> g.Dt)];
-      const uint32_t blk = ix.tileLeafBlock[w.id & (nt - 1u)];
+  for (int b = 0; b < n; ++b)
+    for (uint32_t t = 0; t < nt; ++t) {
+      const KdIndex& ix = *idx[(size_t)b];
+      const uint32_t blk = ix.tileLeafBlock[t];
+      if (blk == VR_PRUNED || !needed[(size_t)b * nt + t]) continue;
       lz.bytesStream += ((int64_t)ix.blockSymEnd[blk] - (int64_t)ix.blockSymBegin[blk] + 3) / 4;
     }
-  if (cudaSetDevice(p->ctx->device) != cudaSuccess) return fail(VR_ERR_CUDA, "cudaSetDevice");
   cudaError_t e = cudaSuccess;
-  lz.nWork = (int)work.size(); lz.nFill = (int)fills.size(); lz.nOccSet = (int)culled.size();
-  if (lz.nWork) {
-    e = cudaMalloc((void**)&lz.workDev, sizeof(vr_kd_work) * work.size());
-    if (e == cudaSuccess) e = cudaMemcpy(lz.workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
-  }
-  if (e == cudaSuccess && lz.nFill) {
-    e = cudaMalloc((void**)&lz.fillJobsDev, sizeof(vr_fill_job) * fills.size());
-    if (e == cudaSuccess) e = cudaMemcpy(lz.fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
-  }
-  if (e == cudaSuccess && p->stageBytes > 0 && !ranges.empty()) {
-    e = cudaMalloc((void**)&lz.rangesDev, sizeof(vr_stage_range) * ranges.size());
-    if (e == cudaSuccess) e = cudaMemcpy(lz.rangesDev, ranges.data(), sizeof(vr_stage_range) * ranges.size(), cudaMemcpyHostToDevice);
-  }
-  if (e == cudaSuccess && lz.nOccSet) {
+  lz.nOccSet = (int)culled.size();
+  if (lz.nOccSet) {
     static_assert(sizeof(vr_occ_set) == 16, "pairs of int64");
     e = cudaMalloc((void**)&lz.occSetDev, sizeof(vr_occ_set) * culled.size());
     if (e == cudaSuccess) e = cudaMemcpy(lz.occSetDev, culled.data(), sizeof(vr_occ_set) * culled.size(), cudaMemcpyHostToDevice);
@@ -259,28 +356,22 @@ int plan_lazy_run(vr_decode_plan* p) {
   if (!lz.built) return fail(VR_ERR_STATE, "lazy work list not built");
   if (!(d->occRaw && d->occEpoch == p->occEpoch && d->skipping)) return fail(VR_ERR_STATE, "occupancy grid of the destination changed");
   cudaError_t e = cudaSetDevice(p->ctx->device);
-  if (e == cudaSuccess)
-    e = kd_decode_launch(p->geom, p->jobsDev, lz.workDev, lz.nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, d->occRaw,
-                         p->tileCellDev, lz.fillJobsDev, lz.rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr, -1, 0, nullptr,
-                         p->tmaRows);
+  if (e == cudaSuccess) e = plan_launch(p, lz.parseDev, lz.nParse, lz.workDev, lz.nWork, lz.fillJobsDev, lz.nFill, true, 0, lz.tmaOut);
   if (e == cudaSuccess) e = occ_set_cells_launch(d->occRaw, lz.occSetDev, lz.nOccSet, p->ctx->stream);
   if (e != cudaSuccess) return fail_cuda(e, "lazy decode launch");
   d->occDilDirty = true;
-  if (lz.nOccSet) d->partialOwner = p;
+  if (lz.nOccSet) d->partial.insert(p);
   return VR_OK;
 }
 }  // namespace vr
 
 extern "C" {
 
-static int env_int(const char* name, int dflt) {
-  const char* e = getenv(name);
-  return e ? atoi(e) : dflt;
-}
-
 int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n, const int64_t* origins,
                           vr_volume* dst, vr_decode_plan** out) {
   if (!ctx || !streams || n <= 0 || !origins || !dst || !out) return fail(VR_ERR_ARG, "vr_decode_plan_create: bad argument");
+  for (int i = 0; i < n; ++i)
+    if (!streams[i]) return fail(VR_ERR_ARG, "vr_decode_plan_create: null stream");
   CU(cudaSetDevice(ctx->device));
   const vr_kd_geom& g = streams[0]->kd.geom;
   std::vector<vr_kd_job> jobs((size_t)n);
@@ -289,9 +380,12 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   p->ctx = ctx; p->geom = g; p->n = n; p->dst = dst;
   // the kernel keeps the occupancy grid current when every decode tile is exactly one cell (32x32x16)
   bool occFused = dst->skipping && g.fastPath && g.tx == 32 && g.ty == 32 && g.tz == 16 && volume_occ_alloc(dst) == VR_OK;
+  bool sameChain = true;
+  uint64_t chain0 = 0;
+  p->treeDist.resize((size_t)n);
   for (int i = 0; i < n; ++i) {
     vr_stream* s = streams[i];
-    if (!s || !s->devImage || s->device != ctx->device) { delete p; return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
+    if (!s->devImage || s->device != ctx->device) { delete p; return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
     const vr_kd_header& h = s->kd.hdr;
     if (h.X != g.X || h.Y != g.Y || h.Z != g.Z) { delete p; return fail(VR_ERR_ARG, "all streams of a plan must share one brick shape"); }
     const int64_t ox = origins[3 * i], oy = origins[3 * i + 1], oz = origins[3 * i + 2];
@@ -308,6 +402,9 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
     j.treeDist = 0; j.chainDist = 0;
     for (int hh = 0; hh <= g.leafBits && hh < 8; ++hh) j.treeDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 - hh)] << (8 * hh);
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) j.chainDist |= (uint64_t)s->kd.distanceMap[(size_t)(g.D0 + k)] << (8 * (k - 1));
+    p->treeDist[(size_t)i] = j.treeDist;
+    if (i == 0) chain0 = j.chainDist;
+    else if (j.chainDist != chain0) sameChain = false;
     j.dstOffset = (oz * dst->SY + oy) * dst->SX + ox;
     j.occBase = -1;
     if (occFused) {
@@ -316,7 +413,7 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
       else j.occBase = (l[0] >> 5) + (int64_t)dst->nc[0] * ((l[1] >> 5) + (int64_t)dst->nc[1] * (l[2] >> 4));
     }
     { int rc = context_chain_lut(ctx, j.chainDist, &j.chainLut); if (rc != VR_OK) { delete p; return rc; } }
-    int chainSum = 0;  // the table packs the net offset in 8 signed bits: 64+32+...+1 = 127 for every reference stream
+    int chainSum = 0;  // the tables pack the net offset in 8 signed bits: 64+32+...+1 = 127 for every reference stream
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) chainSum += s->kd.distanceMap[(size_t)(g.D0 + k)];
     if (chainSum > 127) p->geom.fastPath = 0;
     p->bytesStream += s->kd.streamBytes() + 88 + h.maxTreeDepth + 1;
@@ -327,84 +424,35 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   p->occFused = occFused && vec16 && p->geom.fastPath;
   p->occEpoch = dst->occEpoch;
   if (!p->occFused) for (auto& j : jobs) j.occBase = -1;
-  std::vector<vr_stream*> jobStream(streams, streams + n);
-  std::vector<int32_t> tileCellHost;
+  p->streams.assign(streams, streams + n);
+  p->origins.assign(origins, origins + 3 * (size_t)n);
+  p->dstOffset.resize((size_t)n); p->occBase.resize((size_t)n);
+  for (int i = 0; i < n; ++i) { p->dstOffset[(size_t)i] = jobs[(size_t)i].dstOffset; p->occBase[(size_t)i] = jobs[(size_t)i].occBase; }
   if (p->occFused) {
-    std::vector<int32_t>& tc = tileCellHost;
+    std::vector<int32_t>& tc = p->tileCellHost;
     tc.resize(size_t(1) << g.Dt);
     for (uint32_t t = 0; t < tc.size(); ++t) {
       int ox, oy, oz;
       vr_tile_origin(g, t, &ox, &oy, &oz);
       tc[t] = (ox >> 5) + dst->nc[0] * ((oy >> 5) + dst->nc[1] * (oz >> 4));
     }
-    cudaError_t et = cudaMalloc((void**)&p->tileCellDev, tc.size() * 4);
-    if (et == cudaSuccess) et = cudaMemcpy(p->tileCellDev, tc.data(), tc.size() * 4, cudaMemcpyHostToDevice);
-    if (et != cudaSuccess) { cudaFree(p->tileCellDev); delete p; return fail_cuda(et, "upload tile cells"); }
+    cudaError_t et = upload_vec(tc, &p->tileCellDev);
+    if (et != cudaSuccess) { delete p; return fail_cuda(et, "upload tile cells"); }
   }
-  cudaError_t e;
-  {
-    std::vector<const KdIndex*> idx((size_t)n);
-    std::vector<int64_t> offs((size_t)n);
-    for (int i = 0; i < n; ++i) { idx[(size_t)i] = &jobStream[(size_t)i]->kd.index; offs[(size_t)i] = jobs[(size_t)i].dstOffset; }
-    std::vector<vr_kd_work> work;
-    std::vector<vr_fill_job> fills;
-    std::vector<vr_stage_range> ranges;
-    // experiment, off by default (VR_STAGE_KB = 8 / 16 turns it on): parse CTAs copy their tile's stream segment into shared
-    // memory first (VrWinStage).  Measured on the 120-brick slab: 8 KB 0.263 ms, 16 KB 0.275 ms against 0.267 ms without --
-    // the parser is bound by instruction issue, not by the latency of its stream loads, and the larger shared-memory
-    // footprint costs L1 hits of the chain table (profiles/r1_ab_stage.txt)
-    p->stageBytes = (vec16 && p->geom.fastPath && (kd_decode_smem_bytes(g) % 16) == 0) ? 1024 * env_int("VR_STAGE_KB", 0) : 0;
-    // experiment VR_FILL_TMA = 1: the constant groups attached to parse CTAs are stored by the TMA unit
-    p->tmaRows = env_int("VR_TMA_ROWS", 8);
-    p->tma = env_int("VR_FILL_TMA", 0) != 0 && vec16 && p->geom.fastPath &&
-             kd_fill_maps_create(dst->dev, dst->SX, dst->SY, dst->SZ, g.tx, g.ty, p->tmaRows, &p->tmaMaps);
-    std::vector<int64_t> ob((size_t)n);
-    for (int i = 0; i < n; ++i) ob[(size_t)i] = jobs[(size_t)i].occBase;
-    p->persistFillEvery = (vec16 && p->geom.fastPath) ? env_int("VR_DECODE_PERSIST", 0) : 0;
-    const bool persist = p->persistFillEvery > 0;  // parse entries first, no attached groups: two queues
-    kd_build_worklist(g, n, idx.data(), offs.data(), dst->SX, dst->SX * dst->SY, vec16, persist ? 1 : env_int("VR_DECODE_ORDER", 0), &work, &fills,
-                      persist ? 0 : std::min(env_int("VR_FILL_ATTACH", 2), p->tma ? VR_TMA_MAX_ATTACH : 64), origins, env_int("VR_FILL_LATE", 0), p->occFused ? ob.data() : nullptr,
-                      p->occFused ? tileCellHost.data() : nullptr, nullptr, nullptr, &ranges, p->stageBytes,
-                      env_int("VR_DECODE_ONLY", 0));
-    p->nWork = (int)work.size();
-    p->nFill = (int)fills.size();
-    p->nParse = 0;
-    for (const vr_kd_work& w : work) p->nParse += w.L == VR_WORK_PARSE ? 1 : 0;
-    if (persist && cudaMalloc((void**)&p->queueDev, 2 * sizeof(uint32_t)) != cudaSuccess) { (void)cudaGetLastError(); p->persistFillEvery = 0; }
-    p->streams = jobStream; p->origins.assign(origins, origins + 3 * (size_t)n); p->dstOffset = offs; p->occBase = ob;
-    p->tileCellHost = tileCellHost;
-    e = cudaMalloc((void**)&p->workDev, sizeof(vr_kd_work) * std::max<size_t>(work.size(), 1));
-    if (e == cudaSuccess) e = cudaMemcpy(p->workDev, work.data(), sizeof(vr_kd_work) * work.size(), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && p->nFill) {
-      e = cudaMalloc((void**)&p->fillJobsDev, sizeof(vr_fill_job) * fills.size());
-      if (e == cudaSuccess) e = cudaMemcpy(p->fillJobsDev, fills.data(), sizeof(vr_fill_job) * fills.size(), cudaMemcpyHostToDevice);
-    }
-    if (e == cudaSuccess && p->stageBytes > 0 && !ranges.empty()) {
-      e = cudaMalloc((void**)&p->rangesDev, sizeof(vr_stage_range) * ranges.size());
-      if (e == cudaSuccess) e = cudaMemcpy(p->rangesDev, ranges.data(), sizeof(vr_stage_range) * ranges.size(), cudaMemcpyHostToDevice);
-    }
-    if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); cudaFree(p->rangesDev); delete p; return fail_cuda(e, "upload work list"); }
+  // which kernel: the persistent one wherever the brick shape, the destination and the streams allow it
+  p->persistent6 = g_dbg.decodeKernel == 0 && vec16 && p->geom.fastPath && sameChain &&
+                   kd_decode6_plan(p->geom, dst->dev, dst->SX, dst->SY, dst->SZ, &p->p6, g_dbg.tmaRows);
+  if (p->persistent6) {
+    int rc = context_chain_lut6(ctx, chain0, &p->lut6Dev);
+    if (rc == VR_OK && cudaMalloc((void**)&p->queueDev, VR6_QUEUE_WORDS * sizeof(uint32_t)) != cudaSuccess) rc = fail(VR_ERR_CUDA, "cudaMalloc(queue)");
+    if (rc != VR_OK) { vr_decode_plan_destroy(p); return rc; }
   }
-  if (env_int("VR_L2_PREFETCH", 0)) {  // experiment: pull the plan's streams into L2 (evict-last) before every decode launch
-    std::vector<const uint8_t*> ptrs;
-    std::vector<uint32_t> lines;
-    for (vr_stream* s : jobStream) {
-      bool seen = false;
-      for (const uint8_t* q : ptrs) seen = seen || q == s->devImage;
-      if (!seen) { ptrs.push_back(s->devImage); lines.push_back((uint32_t)((s->imageBytes + 127) / 128)); }
-    }
-    p->nPrefetch = (int)ptrs.size();
-    e = cudaMalloc((void**)&p->pfPtrsDev, sizeof(void*) * ptrs.size());
-    if (e == cudaSuccess) e = cudaMemcpy(p->pfPtrsDev, ptrs.data(), sizeof(void*) * ptrs.size(), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&p->pfLinesDev, 4 * lines.size());
-    if (e == cudaSuccess) e = cudaMemcpy(p->pfLinesDev, lines.data(), 4 * lines.size(), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) { p->nPrefetch = 0; (void)cudaGetLastError(); }
-  }
-  e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
-  if (e != cudaSuccess) { cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "cudaMalloc(jobs)"); }
-  e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+  int rc = plan_build_lists(p, nullptr, nullptr, &p->parseDev, &p->nParse, &p->workDev, &p->nWork, &p->fillJobsDev, &p->nFill, &p->tmaOut);
+  if (rc != VR_OK) { vr_decode_plan_destroy(p); return rc; }
+  cudaError_t e = cudaMalloc((void**)&p->jobsDev, sizeof(vr_kd_job) * (size_t)n);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(p->jobsDev, jobs.data(), sizeof(vr_kd_job) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // jobs is a stack-lifetime buffer
-  if (e != cudaSuccess) { cudaFree(p->jobsDev); cudaFree(p->workDev); cudaFree(p->fillJobsDev); cudaFree(p->tileCellDev); delete p; return fail_cuda(e, "upload jobs"); }
+  if (e != cudaSuccess) { vr_decode_plan_destroy(p); return fail_cuda(e, "upload jobs"); }
   *out = p;
   return VR_OK;
 }
@@ -413,13 +461,10 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
-  if (p->nPrefetch) CU(kd_prefetch_l2_launch(p->pfPtrsDev, p->pfLinesDev, p->nPrefetch, p->ctx->stream));
-  CU(kd_decode_launch(p->geom, p->jobsDev, p->workDev, p->nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream,
-                      occ ? d->occRaw : nullptr, occ ? p->tileCellDev : nullptr, p->fillJobsDev, p->rangesDev, p->stageBytes, p->tma ? &p->tmaMaps : nullptr, p->nParse,
-                      p->queueDev ? p->persistFillEvery : 0, p->queueDev, p->tmaRows));
+  CU(plan_launch(p, p->parseDev, p->nParse, p->workDev, p->nWork, p->fillJobsDev, p->nFill, occ, g_dbg.decodeOnly, p->tmaOut));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
-  if (d->partialOwner == p) d->partialOwner = nullptr;  // every tile of the plan holds its voxels again
+  d->partial.erase(p);  // every tile of the plan holds its voxels again
   return VR_OK;
 }
 int vr_decode_plan_destroy(vr_decode_plan* p) {
@@ -427,12 +472,18 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaSetDevice(p->ctx->device);
   cudaFree(p->jobsDev);
   cudaFree(p->workDev);
+  cudaFree(p->parseDev);
   cudaFree(p->fillJobsDev);
   cudaFree(p->tileCellDev);
-  cudaFree(p->rangesDev);
-  cudaFree(p->pfPtrsDev); cudaFree(p->pfLinesDev); cudaFree(p->queueDev);
+  cudaFree(p->queueDev);
   p->lazy_free();
+  if (p->dst && p->dst->partial.erase(p)) p->dst->partialOrphan = true;  // its stale tiles stay stale
   delete p;
+  return VR_OK;
+}
+int vr_decode_plan_kernel(const vr_decode_plan* p, int32_t* which) {
+  if (!p || !which) return fail(VR_ERR_ARG, "null");
+  *which = p->persistent6 ? 0 : 1;
   return VR_OK;
 }
 int vr_decode_plan_bytes(const vr_decode_plan* p, int64_t out[3]) {
@@ -505,6 +556,7 @@ int vr_kd_compress_volume(vr_context* ctx, const vr_volume* vol, const int64_t o
   if (origin[0] < 0 || origin[1] < 0 || origin[2] < 0 || X <= 0 || Y <= 0 || Z <= 0 || origin[0] + X > vol->SX || origin[1] + Y > vol->SY ||
       origin[2] + Z > vol->SZ)
     return fail(VR_ERR_ARG, "vr_kd_compress_volume: brick outside the volume");
+  if (vol->is_partial()) return fail(VR_ERR_STATE, "vr_kd_compress_volume: the volume was decoded lazily for one frame; run its plan in full first");
   CU(cudaSetDevice(ctx->device));
   const uint8_t* p = vol->dev + (origin[2] * vol->SY + origin[1]) * vol->SX + origin[0];
   return build_common(ctx, p, X, Y, Z, vol->SX, vol->SX * vol->SY, tol, epochs, out, stats, fixed_point_iterations);

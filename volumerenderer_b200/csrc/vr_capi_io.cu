@@ -154,7 +154,7 @@ int vr_volume_load_bricks(vr_context* ctx, vr_volume* v, int64_t numBricks, int6
   cudaError_t se = cudaStreamSynchronize(ctx->stream);  // the staging ring is freed on return
   if (rc == VR_OK && se != cudaSuccess) { ce = se; rc = VR_ERR_CUDA; }
   v->occValid = false;  // reduced lazily at the next render (occupancy.h)
-  v->partialOwner = nullptr;
+  if (copied * (int64_t)(brick_dims[0] * brick_dims[1] * brick_dims[2]) >= v->SX * v->SY * v->SZ) { v->partial.clear(); v->partialOrphan = false; }  // every voxel rewritten
   if (stats) { stats[0] = copied; stats[1] = copied * brickBytes; }
   if (rc == VR_ERR_CUDA) return fail_cuda(ce, "vr_volume_load_bricks: copy");
   if (rc == VR_ERR_IO) return fail(rc, ("cannot read brick file " + (failedBrick >= 0 ? paths[(size_t)failedBrick] : std::string("?"))).c_str());

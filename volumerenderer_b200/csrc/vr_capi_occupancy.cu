@@ -57,6 +57,7 @@ int volume_occ_view(vr_context* ctx, const vr_volume* cv, int thr, OccView* out)
   int rc = volume_occ_alloc(v);
   if (rc != VR_OK) return rc;
   if (!v->occValid) {
+    if (v->is_partial()) return fail(VR_ERR_STATE, "occupancy rebuild: the volume was decoded lazily for one frame (stale tiles); run its plan in full first");
     const int64_t lo[3] = {0, 0, 0}, ext[3] = {v->SX, v->SY, v->SZ};
     CU(occ_reduce_box_launch(v->dev, v->SX, v->SY, v->SZ, lo, ext, v->occRaw, v->nc[0], v->nc[1], v->nc[2], v->shift, ctx->stream));
     v->occValid = true; v->occDilDirty = true;
@@ -122,6 +123,8 @@ int vr_volume_set_skipping(vr_volume* v, int enable) {
 int vr_volume_invalidate(vr_volume* v) {
   if (!v) return fail(VR_ERR_ARG, "null");
   v->occValid = false;
+  v->partial.clear();  // the caller vouches for the stored voxels
+  v->partialOrphan = false;
   return VR_OK;
 }
 

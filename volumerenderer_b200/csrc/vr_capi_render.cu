@@ -65,7 +65,7 @@ int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params*
   if (!ctx || !vol || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render: null argument");
   if (params->mode != VR_MODE_COMPOSITE && params->mode != VR_MODE_ISOSURFACE && params->mode != VR_MODE_ISOSURFACE_COMPRESSED)
     return fail(VR_ERR_ARG, "vr_render: unknown mode");
-  if (vol->partialOwner && !allowPartial)
+  if (vol->is_partial() && !allowPartial)
     return fail(VR_ERR_STATE, "vr_render: the volume was decoded lazily for one frame (vr_render_compressed_lazy); run its plan in full first");
   RenderParams P;
   if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");

@@ -126,6 +126,7 @@ int vr_sortlast_halo(const vr_render_params* p, const int64_t global[3], int64_t
   SlabGeom g;                                                                                       \
   std::memset(&g, 0, sizeof(g));                                                                    \
   if (need_slab) { if (!slab) return fail(VR_ERR_ARG, "null slab"); int rc_ = slab_geom(sl, slab, &g); if (rc_ != VR_OK) return rc_; } \
+  if (need_slab && slab->is_partial()) return fail(VR_ERR_STATE, "the slab was decoded lazily for one frame; run its plan in full first"); \
   CU(cudaSetDevice(ctx->device));                                                                   \
   OccView occ;                                                                                      \
   std::memset(&occ, 0, sizeof(occ));                                                                \
@@ -180,6 +181,7 @@ static int box_copy(vr_context* ctx, const vr_volume* v, const int64_t o[3], con
   const int64_t S[3] = {v->SX, v->SY, v->SZ};
   for (int a = 0; a < 3; ++a)
     if (o[a] < 0 || e[a] <= 0 || o[a] + e[a] > S[a]) return fail(VR_ERR_ARG, "box outside the slab");
+  if (pack && v->is_partial()) return fail(VR_ERR_STATE, "vr_volume_pack_box: the volume was decoded lazily for one frame; run its plan in full first");
   CU(cudaSetDevice(ctx->device));
   cudaMemcpy3DParms p;
   std::memset(&p, 0, sizeof(p));

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <map>
+#include <set>
 #include <vector>
 #include "../../include/vr_b200.h"
 #include "kd_decode.h"
@@ -19,7 +20,8 @@ struct vr_context {
   cudaEvent_t ev[16][2] = {};
   cudaEvent_t evOrder = nullptr;  // recorded by vr_context_wait_for(other = this)
   vr::KdBuilder* builder = nullptr;  // scratch of the GPU stream producer (kd_build.h), created on first use
-  std::map<uint64_t, uint32_t*> chainLuts;  // chainDist -> device table of 16384 entries
+  std::map<uint64_t, uint32_t*> chainLuts;   // chainDist -> device table of 16384 entries (classic kernel: vr_chain_lut_entry)
+  std::map<uint64_t, uint32_t*> chainLuts6;  // same for the persistent kernel (vr6::chain_entry)
 };
 
 // Device image of a prepared stream: one arena, sections 16-byte aligned:
@@ -54,9 +56,14 @@ struct vr_volume {
   uint8_t* occLvl = nullptr;      // per level-0 cell: highest void level for threshold occLvlThr (occupancy.h)
   int occLvlThr = -2;             // -2 = occLvl is stale
   int occEpoch = 0;               // bumped whenever the grids are freed (plans remember the epoch they were built for)
-  // set by a lazy decode (vr_render_compressed_lazy): only the tiles that frame could read hold valid voxels, so
-  // vr_render refuses the volume until the owning plan has been run in full again
-  const void* partialOwner = nullptr;
+  // Plans whose last run was lazy (vr_render_compressed_lazy): the tiles their frame could not read hold stale voxels,
+  // so every entry point that reads stored voxels (vr_render, vr_volume_download, vr_kd_compress_volume, vr_volume_pack_box,
+  // vr_partial_*, occupancy rebuilds from the voxels) refuses the volume until each of these plans has been run in full
+  // again.  partialOrphan: such a plan was destroyed while its tiles were stale (cleared by vr_volume_invalidate or by a
+  // load that covers the whole volume).
+  std::set<const void*> partial;
+  bool partialOrphan = false;
+  bool is_partial() const { return partialOrphan || !partial.empty(); }
   void occ_free();
 };
 
@@ -64,35 +71,38 @@ struct vr_decode_plan {
   vr_context* ctx = nullptr;
   vr_kd_geom geom;
   vr_kd_job* jobsDev = nullptr;
-  vr_kd_work* workDev = nullptr;  // CTA work list of the launch (kd_worklist.h)
-  int nWork = 0;
-  vr_fill_job* fillJobsDev = nullptr;  // constant groups attached to parse CTAs (kd_worklist.h)
-  int nFill = 0;
   int n = 0;
   vr_volume* dst = nullptr;
   bool vec16 = false;
   bool occFused = false;  // every tile of every job is one occupancy cell: the kernel keeps occRaw current
   int occEpoch = 0;
   int32_t* tileCellDev = nullptr;  // [2^Dt] tile -> cell offset for dst's grid
-  const uint8_t** pfPtrsDev = nullptr; uint32_t* pfLinesDev = nullptr; int nPrefetch = 0;  // unique stream arenas (L2 prefetch)
-  int persistFillEvery = 0, nParse = 0; uint32_t* queueDev = nullptr;  // persistent launch with SM roles (kd_decode.h)
-  int tmaRows = 8;
-  bool tma = false;                // attached constant groups go through the TMA unit (kd_decode.h)
-  vr::VrFillMaps tmaMaps;
-  vr_stage_range* rangesDev = nullptr;      // per CTA: stream segment staged in shared memory (kd_worklist.h); null = off
-  int stageBytes = 0;
+  // persistent kernel (kd_decode.h): two device-side queues
+  bool persistent6 = false;
+  vr::Decode6Plan p6;
+  vr_parse_item* parseDev = nullptr;
+  int nParse = 0;
+  int tmaOut = 0;  // the units' voxels leave through the TMA unit (launches dominated by constant groups)
+  uint32_t* queueDev = nullptr;
+  const uint32_t* lut6Dev = nullptr;
+  // classic kernel: one CTA per entry (kd_worklist.h)
+  vr_kd_work* workDev = nullptr;
+  int nWork = 0;
+  vr_fill_job* fillJobsDev = nullptr;  // constant groups (persistent: the fill queue; classic: attached to parse CTAs)
+  int nFill = 0;
   int64_t bytesStream = 0, bytesVoxels = 0, bytesIndex = 0;
   // host copies kept for the lazy (view-dependent) work list, kd_cull.h
   std::vector<vr_stream*> streams;
   std::vector<int64_t> origins, dstOffset, occBase;
+  std::vector<uint64_t> treeDist;
   std::vector<int32_t> tileCellHost;
   struct Lazy {
     bool built = false;
     int mode = 0, thr = 0, reach[3] = {0, 0, 0}, stepReach[3] = {0, 0, 0};   // cache key
     uint8_t* solidDev = nullptr;  // per occupancy cell of dst: 1 = "solid-high" look-up cell (kd_cull.h), isosurface only
+    vr_parse_item* parseDev = nullptr; int nParse = 0; int tmaOut = 0;
     vr_kd_work* workDev = nullptr; int nWork = 0;
     vr_fill_job* fillJobsDev = nullptr; int nFill = 0;
-    vr_stage_range* rangesDev = nullptr;
     int64_t* occSetDev = nullptr; int nOccSet = 0;  // (cell, max) pairs of the tiles left out
     int64_t tilesTotal = 0, tilesWritten = 0, bytesVoxels = 0, bytesStream = 0;
   } lazy;

@@ -311,6 +311,13 @@ class DecodePlan:
         check(lib.vr_decode_plan_bytes(self.h, out))
         return {"stream": out[0], "voxels": out[1], "index": out[2]}
 
+    def kernel(self):
+        """'persistent' (warp-specialised kernel, kd_decode.cu) or 'classic' (one CTA per tile)."""
+        from ctypes import c_int32
+        w = c_int32(0)
+        check(lib.vr_decode_plan_kernel(self.h, byref(w)))
+        return "persistent" if w.value == 0 else "classic"
+
     def close(self):
         if self.h:
             lib.vr_decode_plan_destroy(self.h)
