@@ -18,7 +18,7 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 // One CTA per SM: 22 parse warps (one lane per leaf subtree, kd_parse6.h; a warp's work item is a "unit" = 32 leaf boxes = an
 // eighth of a tile) + one warp that feeds the TMA unit with constant groups.  Work comes from two device-side queues (parse
 // units / constant groups, both in destination-address order); a unit's stream segment and its 32 index entries are staged
-// in shared memory by bulk copies that complete on the warp's own mbarrier -- no barrier between warps.
+// in shared memory by the warp's own 16-byte asynchronous copies (cp.async groups) -- no barrier between warps.
 #define VR6_PARSE_WARPS 22
 #define VR6_QUEUE_WORDS 64  // the two queue counters, 128 bytes apart
 #define VR6_THREADS (VR6_PARSE_WARPS * 32 + 32)
