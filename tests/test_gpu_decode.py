@@ -158,3 +158,21 @@ def test_slab_of_full_size_bricks_both_kernels(ctx, kernel):
     finally:
         vr.debug_set("decode_kernel", 0)
         vr.debug_set("unit_store", 0)
+
+
+def test_handles_may_be_released_in_any_order(ctx):
+    """A host with a garbage collector frees the volume before the plan as often as after it: the plan is detached,
+    refuses to run (VR_ERR_STATE) and can still be destroyed."""
+    brick = synth.shell_brick((64, 64, 32), noise=4)
+    s, _ = vr.Stream.compress_device(ctx, brick, 1, 2)
+    s.upload(ctx)
+    vol = vr.Volume(ctx, 64, 64, 32)
+    plan, plan2 = vr.DecodePlan(ctx, [s], [(0, 0, 0)], vol), vr.DecodePlan(ctx, [s], [(0, 0, 0)], vol)
+    plan.run(); ctx.synchronize()
+    plan2.close()  # plan before volume
+    vol.close()    # volume before plan
+    with pytest.raises(_lib.VrError) as e:
+        plan.run()
+    assert e.value.code == _lib.VR_ERR_STATE
+    plan.close()
+    s.close()

@@ -76,7 +76,14 @@ def test_lazy_frame_is_bit_identical_and_leaves_culled_tiles_untouched(ctx, laye
         with pytest.raises(_lib.VrError) as ei:
             render.render_to_host(ctx, vol, p)
         assert ei.value.code == _lib.VR_ERR_STATE
-        got = vol.download()
+        with pytest.raises(_lib.VrError) as ei:
+            vol.download()
+        assert ei.value.code == _lib.VR_ERR_STATE
+        vr.debug_set("read_partial", 1)  # look at the stale tiles on purpose
+        try:
+            got = vol.download()
+        finally:
+            vr.debug_set("read_partial", 0)
         written = 0
         for b in range(needed.shape[0]):
             for t in range(needed.shape[1]):

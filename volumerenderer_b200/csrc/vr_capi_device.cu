@@ -127,6 +127,7 @@ int vr_volume_wrap(vr_context* ctx, void* p, int64_t SX, int64_t SY, int64_t SZ,
 }
 int vr_volume_destroy(vr_volume* v) {
   if (!v) return VR_OK;
+  for (vr_decode_plan* p : v->plans) p->dst = nullptr;
   v->occ_free();
   if (v->owned && v->dev) { cudaSetDevice(v->device); cudaFree(v->dev); }
   delete v;
@@ -142,9 +143,11 @@ int vr_volume_dims(const vr_volume* v, int64_t d[3]) {
   d[0] = v->SX; d[1] = v->SY; d[2] = v->SZ;
   return VR_OK;
 }
+namespace { int g_read_partial = 0; }  // vr_debug_set("read_partial", 1): tests look at the tiles a lazy frame left alone
 int vr_volume_download(vr_context* ctx, const vr_volume* v, uint8_t* host) {
   if (!ctx || !v || !host) return fail(VR_ERR_ARG, "null");
-  if (v->is_partial()) return fail(VR_ERR_STATE, "vr_volume_download: the volume was decoded lazily for one frame; run its plan in full first");
+  if (v->is_partial() && !g_read_partial)
+    return fail(VR_ERR_STATE, "vr_volume_download: the volume was decoded lazily for one frame; run its plan in full first");
   CU(cudaSetDevice(ctx->device));
   CU(cudaMemcpyAsync(host, v->dev, (size_t)(v->SX * v->SY * v->SZ), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -173,7 +176,7 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
 void vr_decode_plan::lazy_free() {
-  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.parseDev) cudaSetDevice(ctx->device);
+  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.parseDev) cudaSetDevice(device);
   cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev); cudaFree(lazy.parseDev);
   lazy = Lazy();
 }
@@ -194,6 +197,7 @@ extern "C" int vr_debug_set(const char* key, int value) {
   else if (k == "tma_rows") g_dbg.tmaRows = value;
   else if (k == "parse_order") g_dbg.parseOrder = value;
   else if (k == "unit_store") g_dbg.unitStore = value;  // 0 / 1 = one tensor store per unit (default), 2 = 16-byte stores of the lanes
+  else if (k == "read_partial") g_read_partial = value;  // vr_volume_download of a partially decoded volume (tests)
   else return fail(VR_ERR_ARG, "vr_debug_set: unknown key");
   return VR_OK;
 }
@@ -207,6 +211,7 @@ extern "C" int vr_debug_get(const char* key, int* value) {
   else if (k == "tma_rows") *value = g_dbg.tmaRows;
   else if (k == "parse_order") *value = g_dbg.parseOrder;
   else if (k == "unit_store") *value = g_dbg.unitStore;
+  else if (k == "read_partial") *value = g_read_partial;
   else return fail(VR_ERR_ARG, "vr_debug_get: unknown key");
   return VR_OK;
 }
@@ -377,7 +382,8 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   std::vector<vr_kd_job> jobs((size_t)n);
   bool vec16 = (g.tx >= 16) && (dst->SX % 16 == 0) && (((uintptr_t)dst->dev) % 16 == 0);
   vr_decode_plan* p = new vr_decode_plan;
-  p->ctx = ctx; p->geom = g; p->n = n; p->dst = dst;
+  p->ctx = ctx; p->device = ctx->device; p->geom = g; p->n = n; p->dst = dst;
+  dst->plans.insert(p);
   // the kernel keeps the occupancy grid current when every decode tile is exactly one cell (32x32x16)
   bool occFused = dst->skipping && g.fastPath && g.tx == 32 && g.ty == 32 && g.tz == 16 && volume_occ_alloc(dst) == VR_OK;
   bool sameChain = true;
@@ -458,6 +464,7 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
 }
 int vr_decode_plan_run(vr_decode_plan* p) {
   if (!p) return fail(VR_ERR_ARG, "null plan");
+  if (!p->dst) return fail(VR_ERR_STATE, "vr_decode_plan_run: the plan's destination volume was destroyed");
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
@@ -469,7 +476,7 @@ int vr_decode_plan_run(vr_decode_plan* p) {
 }
 int vr_decode_plan_destroy(vr_decode_plan* p) {
   if (!p) return VR_OK;
-  cudaSetDevice(p->ctx->device);
+  cudaSetDevice(p->device);  // not through p->ctx: the host may have closed the context first
   cudaFree(p->jobsDev);
   cudaFree(p->workDev);
   cudaFree(p->parseDev);
@@ -477,7 +484,10 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->tileCellDev);
   cudaFree(p->queueDev);
   p->lazy_free();
-  if (p->dst && p->dst->partial.erase(p)) p->dst->partialOrphan = true;  // its stale tiles stay stale
+  if (p->dst) {
+    if (p->dst->partial.erase(p)) p->dst->partialOrphan = true;  // its stale tiles stay stale
+    p->dst->plans.erase(p);
+  }
   delete p;
   return VR_OK;
 }

@@ -140,6 +140,7 @@ int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_par
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,
                          int32_t* hit_dev, uint64_t* samples_dev) {
   if (!plan || !params) return fail(VR_ERR_ARG, "null plan");
+  if (!plan->dst) return fail(VR_ERR_STATE, "vr_render_compressed: the plan's destination volume was destroyed");
   int rc = vr_decode_plan_run(plan);
   if (rc != VR_OK) return rc;
   // the stream index bounds every tile from both sides, so the isosurface march can also skip look-up cells in which
@@ -162,6 +163,7 @@ int vr_render_compressed_lazy(vr_context* ctx, vr_decode_plan* plan, const vr_re
                               int32_t* hit_dev, uint64_t* samples_dev, int64_t stats[4]) {
   if (!ctx || !plan || !params || !out_rgba_dev) return fail(VR_ERR_ARG, "vr_render_compressed_lazy: null argument");
   if (ctx != plan->ctx) return fail(VR_ERR_ARG, "vr_render_compressed_lazy: the plan belongs to another context");
+  if (!plan->dst) return fail(VR_ERR_STATE, "vr_render_compressed_lazy: the plan's destination volume was destroyed");
   vr_volume* d = plan->dst;
   int thr = 0, mode = 0;
   if (skip_threshold_of(params, &thr, &mode) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");

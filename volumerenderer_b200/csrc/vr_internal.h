@@ -64,11 +64,15 @@ struct vr_volume {
   std::set<const void*> partial;
   bool partialOrphan = false;
   bool is_partial() const { return partialOrphan || !partial.empty(); }
+  // Plans that decode into this volume.  vr_volume_destroy detaches them (their dst becomes null and they fail with
+  // VR_ERR_STATE from then on), so a host that releases its handles in any order -- a garbage collector does -- is safe.
+  std::set<struct vr_decode_plan*> plans;
   void occ_free();
 };
 
 struct vr_decode_plan {
   vr_context* ctx = nullptr;
+  int device = 0;
   vr_kd_geom geom;
   vr_kd_job* jobsDev = nullptr;
   int n = 0;
