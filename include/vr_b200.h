@@ -222,6 +222,20 @@ int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* par
 /* Same, result copied to HOST buffers; synchronous. */
 int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_host,
                       int32_t* hit_host, uint64_t* samples_host);
+/* The frame of vr_render_to_host without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  vr_render_to_host allocates and frees its device-side frame per call; this entry point marches into a
+ * file-scope __device__ array of VR_STATIC_SCRATCH_BYTES that is part of the library image (every GPU that loads the
+ * library holds it until the process exits) and calls no cudaMalloc / cudaFree.  The caller still passes the volume and
+ * the host outputs; same arguments, same results (frame and hit indices bit for bit, same sample count; the march runs
+ * without the occupancy grid, whose construction allocates).  width * height above VR_STATIC_MAX_PIXELS fails with
+ * VR_ERR_UNSUPPORTED.  All calls share the array, which keeps the last call's contents (the sample counter is cleared
+ * per call): calls that overlap on one GPU race on it.  Synchronous.  csrc/vr_capi_noalloc.cu. */
+#define VR_STATIC_MAX_PIXELS 2097152 /* 2 Mi pixels: 1600 x 1200 (main.cpp:27) fits */
+#define VR_STATIC_SCRATCH_BYTES (VR_STATIC_MAX_PIXELS * 20 + 256) /* RGBA float32 + hit indices + sample counter = 40 MiB */
+int vr_render_to_host_static(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_host,
+                             int32_t* hit_host, uint64_t* samples_host);
+int64_t vr_static_scratch_max_pixels(void);
 /* ISOSURFACE_COMPRESSED / any mode straight from streams: run the decode plan, then march its
  * destination volume, all on the device with no host round trip. */
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,

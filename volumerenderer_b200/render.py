@@ -22,7 +22,7 @@ _lib.lib.vr_render_defaults.restype = ctypes.c_int
 _lib.lib.vr_render_defaults.argtypes = [ctypes.POINTER(RenderParams)]
 _lib.lib.vr_camera_basis.restype = ctypes.c_int
 _lib.lib.vr_camera_basis.argtypes = [ctypes.POINTER(RenderParams), ctypes.POINTER(c_float)]
-for _n in ("vr_render", "vr_render_to_host", "vr_render_compressed"):
+for _n in ("vr_render", "vr_render_to_host", "vr_render_to_host_static", "vr_render_compressed"):
     getattr(_lib.lib, _n).restype = ctypes.c_int
     getattr(_lib.lib, _n).argtypes = [c_void_p, c_void_p, ctypes.POINTER(RenderParams), c_void_p, c_void_p, c_void_p]
 _lib.lib.vr_render_compressed_lazy.restype = ctypes.c_int
@@ -33,7 +33,10 @@ _lib.lib.vr_lazy_tile_mask.argtypes = [ctypes.POINTER(c_void_p), c_int32, ctypes
                                        ctypes.POINTER(RenderParams), c_void_p, c_void_p, ctypes.POINTER(c_int32)]
 _lib.lib.vr_stream_tile_bounds.restype = ctypes.c_int
 _lib.lib.vr_stream_tile_bounds.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, ctypes.POINTER(c_int32)]
-_lib.EXPORTED[:] = sorted(set(_lib.EXPORTED) | {"vr_render_defaults", "vr_camera_basis", "vr_render",
+_lib.lib.vr_static_scratch_max_pixels.restype = ctypes.c_int64
+_lib.lib.vr_static_scratch_max_pixels.argtypes = []
+_lib.EXPORTED[:] = sorted(set(_lib.EXPORTED) | {"vr_render_defaults", "vr_camera_basis", "vr_render", "vr_render_to_host_static",
+                                                "vr_static_scratch_max_pixels",
                                                 "vr_render_to_host", "vr_render_compressed", "vr_render_compressed_lazy",
                                                 "vr_lazy_tile_mask", "vr_stream_tile_bounds"})
 
@@ -84,6 +87,22 @@ def render_to_host(ctx, volume, p, want_hits=False, want_samples=True):
                                 hits.ctypes.data if want_hits else None,
                                 ctypes.cast(byref(samples), c_void_p) if want_samples else None))
     return out, samples.value, hits
+
+
+def render_to_host_static(ctx, volume, p, want_hits=False, want_samples=True):
+    """render_to_host through vr_render_to_host_static: no device allocation, frame marched into the library's static
+    scratch array (at most static_max_pixels() pixels; calls that overlap on one GPU race on it)."""
+    out = np.empty((p.height, p.width, 4), np.float32)
+    hits = np.empty((p.height, p.width), np.int32) if want_hits else None
+    samples = c_uint64(0)
+    check(lib.vr_render_to_host_static(ctx.h, volume.h, byref(p), out.ctypes.data,
+                                       hits.ctypes.data if want_hits else None,
+                                       ctypes.cast(byref(samples), c_void_p) if want_samples else None))
+    return out, samples.value, hits
+
+
+def static_max_pixels():
+    return int(lib.vr_static_scratch_max_pixels())
 
 
 def render_device(ctx, volume, p, out_ptr, hit_ptr=None, samples_ptr=None):
