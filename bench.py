@@ -178,12 +178,131 @@ def frame_check_multi(args, ctx, vol, ops, descs, stored, frame, peers, p, rank,
     return res
 
 
+def _median_ms(ctx, fn, iters=7, warm=2, slot=15):
+    for _ in range(warm):
+        fn()
+    ctx.synchronize()
+    ms = []
+    for _ in range(iters):
+        ctx.timer_begin(slot); fn(); ctx.timer_end(slot)
+        ms.append(ctx.timer_ms(slot))
+    return float(np.median(ms))
+
+
+def bench_extras(ctx, vr, render, vol, plan, threads, peak, local):
+    """N = 1, after the headline region: further frames of the rm_yslab slab (isosurface,
+    lazy isosurface_compressed straight from the streams, oblique camera), fetched samples beside march steps, and the
+    stream-dense decode workloads -- the config-3 layer (64 bricks of k = 7, 5.3 bits/voxel: BASELINE config 3) and 16
+    incompressible noise bricks -- with the same algorithmic-bytes formula and the same CUDA-event timing as `roofline`."""
+    import torch
+    from volumerenderer_b200 import synth
+    dev = f"cuda:{local}"
+    out = torch.empty((IMG, IMG, 4), dtype=torch.float32, device=dev)
+    hit = torch.empty((IMG, IMG), dtype=torch.int32, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+
+    def count(v, p, fetched):
+        vr.debug_set("count_fetched", 1 if fetched else 0)
+        try:
+            cnt.zero_(); torch.cuda.synchronize()
+            render.render_device(ctx, v, p, out.data_ptr(), None, cnt.data_ptr()); ctx.synchronize()
+            return int(cnt.item())
+        finally:
+            vr.debug_set("count_fetched", 0)
+
+    def frames(v, tag_params):
+        res = {}
+        for tag, p in tag_params:
+            ms = _median_ms(ctx, lambda: render.render_device(ctx, v, p, out.data_ptr(), hit.data_ptr()))
+            steps, fetched = count(v, p, False), count(v, p, True)
+            res[tag] = {"ms": ms, "frames_per_s": 1e3 / ms, "samples_per_frame": steps, "fetched_samples": fetched,
+                        "gsamples_per_s": steps / ms / 1e6}
+        return res
+
+    plan.run(); ctx.synchronize()
+    views = [("composite_reference", render.default_params(IMG, IMG, render.COMPOSITE)),
+             ("isosurface_reference", render.default_params(IMG, IMG, render.ISOSURFACE)),
+             ("composite_oblique", render.oblique_params(IMG, IMG, render.COMPOSITE)),
+             ("isosurface_oblique", render.oblique_params(IMG, IMG, render.ISOSURFACE))]
+    ex = {"frames_rm_yslab": frames(vol, views)}
+    # isosurface_compressed: decode + frame in one call; lazy = only the tiles the frame can read are decoded
+    pc = render.default_params(IMG, IMG, render.ISOSURFACE_COMPRESSED)
+    st = {}
+    full_ms = _median_ms(ctx, lambda: render.render_compressed_device(ctx, plan, pc, out.data_ptr(), hit.data_ptr()))
+    lazy_ms = _median_ms(ctx, lambda: st.update(render.render_compressed_lazy_device(ctx, plan, pc, out.data_ptr(), hit.data_ptr())))
+    plan.run(); ctx.synchronize()  # the slab is complete again
+    ex["isosurface_compressed_rm_yslab"] = {"full_decode_plus_frame_ms": full_ms, "lazy_decode_plus_frame_ms": lazy_ms,
+                                            "frames_per_s_lazy": 1e3 / lazy_ms, "tiles": st.get("tiles"), "tiles_written": st.get("tiles_written")}
+
+    def dense(name, vols, origins, dims):
+        t0 = time.time()
+        streams = [vr.Stream.compress_device(ctx, v, 1, 2)[0] for v in vols]
+        t_build = time.time() - t0
+        t0 = time.time()
+        with ThreadPoolExecutor(max_workers=threads) as pool:
+            list(pool.map(lambda s: s.prepare(), streams))
+        t_prep = time.time() - t0
+        for s in streams:
+            s.upload(ctx)
+        v = vr.Volume(ctx, *dims)
+        pl = vr.DecodePlan(ctx, streams, origins, v)
+        by = pl.bytes()
+        ms = _median_ms(ctx, pl.run, iters=11, warm=3)
+        algo = by["stream"] + by["voxels"]
+        nodes = sum(s.header.numActiveNodes for s in streams)
+        r = {"workload": name, "kernel": "kd_decode6_kernel" if pl.kernel() == "persistent" else "kd_decode_tiles_kernel",
+             "bound": "hbm", "achieved": algo / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": algo / ms / 1e6 / peak, "ms": ms,
+             "algorithmic_bytes": algo, "stream_bytes": by["stream"], "voxel_bytes": by["voxels"], "index_bytes": by["index"],
+             "bits_per_voxel": 2.0 * nodes / by["voxels"], "gvoxels_per_s": by["voxels"] / ms / 1e6, "bricks": len(streams),
+             "setup": {"gpu_producer_s": t_build, "host_index_walk_s": t_prep, "threads": threads}}
+        return r, streams, v, pl
+
+    ijk = [(i, j, 7) for j in range(8) for i in range(8)]
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        vols = list(pool.map(lambda a: synth.rm_brick(*a), ijk))
+    r3, streams3, v3, pl3 = dense("config-3 layer: 64 bricks 256x256x128 of k = 7 (2048x2048x128)", vols,
+                                  [(i * BX, j * BY, 0) for (i, j, k) in ijk], (8 * BX, 8 * BY, BZ))
+    del vols
+    st3 = {}
+    f_full = _median_ms(ctx, lambda: render.render_compressed_device(ctx, pl3, pc, out.data_ptr(), hit.data_ptr()))
+    f_lazy = _median_ms(ctx, lambda: st3.update(render.render_compressed_lazy_device(ctx, pl3, pc, out.data_ptr(), hit.data_ptr())))
+    pl3.run(); ctx.synchronize()
+    f_march = _median_ms(ctx, lambda: render.render_device(ctx, v3, pc, out.data_ptr(), hit.data_ptr()))
+    ex["config3"] = {"decode_ms": r3["ms"], "decode_gvoxels_per_s": r3["gvoxels_per_s"], "frame_ms": f_march,
+                     "isosurface_compressed_full_ms": f_full, "isosurface_compressed_lazy_ms": f_lazy,
+                     "frames_per_s_lazy": 1e3 / f_lazy, "tiles": st3.get("tiles"), "tiles_written": st3.get("tiles_written"),
+                     "image": [IMG, IMG], "isoValue": "40/255"}
+    # host index walk of one mixing-layer stream on one thread (what vr_stream_prepare costs for a legacy container)
+    one = vr.Stream.from_memory(streams3[27].header, streams3[27].distance_map, streams3[27].bits)
+    t0 = time.time(); one.prepare(); host_ms = (time.time() - t0) * 1e3
+    ex["index_build"] = {"host_ms_per_brick": host_ms, "host_threads_per_brick": 1, "bricks_in_parallel": threads,
+                         "brick": "rm brick (3, 3, 7)", "nodes": int(one.header.numActiveNodes), "device_ms_per_brick": None}
+    one.close()
+    pl3.close(); v3.close()
+    for s in streams3:
+        s.close()
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        vols = list(pool.map(lambda b: synth.noise_brick(seed=0xB200 + b), range(16)))
+    rn, streamsn, vn, pln = dense("noise: 16 incompressible bricks 256x256x128 (1024x1024x128)", vols,
+                                  [((b % 4) * BX, (b // 4) * BY, 0) for b in range(16)], (4 * BX, 4 * BY, BZ))
+    pln.close(); vn.close()
+    for s in streamsn:
+        s.close()
+    ex["roofline_dense"] = {"config3": r3, "noise": rn, "frac": min(r3["frac"], rn["frac"]),
+                            "note": "same formula and events as `roofline` (stream read once + voxels written once, over the "
+                                    "measured HBM copy peak); the parser is bound by instruction issue, not by HBM"}
+    return ex
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     import volumerenderer_b200 as vr
     from volumerenderer_b200 import render
     rank, world, local = dist_setup(args.gpus)
+    for kv in args.debug:
+        k, _, v = kv.partition("=")
+        vr.debug_set(k, int(v))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -453,10 +572,13 @@ def run_ours(args):
             dist.barrier(); dist.destroy_process_group()
         return
     peak, peak_src = peaks()
+    extras = None
+    if world == 1 and not args.no_extras:
+        extras = bench_extras(ctx, vr, render, vol, plan, threads, peak, local)
     d_ms, m_ms = float(np.median(dec_ms)), float(np.median(mar_ms))  # eager probe steps; the first ones absorb rank skew
     dec_bytes = by["stream"] + by["voxels"]
     mar_bytes = 8 * samples // world + 16 * IMG * IMG  # per rank (N > 1: an even share of all ranks' fetches)
-    roof_dec = {"kernel": "kd_decode_tiles_kernel", "bound": "hbm", "achieved": dec_bytes / d_ms / 1e6, "peak": peak, "unit": "GB/s",
+    roof_dec = {"kernel": "kd_decode6_kernel" if plan.kernel() == "persistent" else "kd_decode_tiles_kernel", "bound": "hbm", "achieved": dec_bytes / d_ms / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": dec_bytes / d_ms / 1e6 / peak, "traffic": None, "ms": d_ms, "algorithmic_bytes": dec_bytes,
                 "index_bytes": by["index"], "peak_source": peak_src,
                 "write_fraction": by["voxels"] / dec_bytes,
@@ -502,8 +624,12 @@ def run_ours(args):
         # own kernels per step: decode, 3 occupancy refresh, march; N > 1 over NCCL: partial, resolve, finish instead of march;
         # N > 1 over peer windows (rank 0, one neighbour): decode, halo put + wait + box reduce, 3 occupancy, partial, gather put +
         # wait, resolve, reduce-scatter put + wait + combine, all-gather put + wait, finish = 17
-        "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "frame_check": frame_check, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
+        "debug_knobs": args.debug or None, "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "frame_check": frame_check, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
     }
+    if extras:
+        line["roofline_dense"] = extras.pop("roofline_dense")
+        line["index_build"] = extras.pop("index_build")
+        line["extras"] = extras
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(budget_s=20.0, steps=1)
     emit(line)
@@ -638,6 +764,9 @@ def main():
                     help="N > 1: sort-last exchange over peer-memory windows (copy kernels, or fused into the march kernels) or NCCL")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
                     help="strictly sequential steps (decode, then frame) instead of decode(t+1) overlapping frame(t) on two slabs")
+    ap.add_argument("--debug", action="append", default=[], metavar="KEY=VALUE",
+                    help="A/B runs: vr_debug_set(KEY, VALUE) before anything is created (e.g. decode_split=1, decode_only=2: timing probes)")
+    ap.add_argument("--no-extras", action="store_true", help="N = 1: skip the extra frames and the stream-dense decode workloads")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of replaying a captured CUDA graph")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that print to fd 1 (NCCL's version banner, ...) are

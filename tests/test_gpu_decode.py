@@ -118,7 +118,7 @@ def test_unaligned_placement_uses_scalar_stores(ctx):
     assert not got.any()
 
 
-@pytest.mark.parametrize("kernel", ["persistent", "persistent_tensor_stores", "persistent_lane_stores", "classic"])
+@pytest.mark.parametrize("kernel", ["persistent", "persistent_tensor_stores", "persistent_lane_stores", "persistent_split", "classic"])
 def test_slab_of_full_size_bricks_both_kernels(ctx, kernel):
     """A 2x1x3 grid of 256x256x128 bricks (empty, mixing layer x 3, noise, solid) through the persistent warp-specialised
     kernel (parse groups + TMA fill warp, kd_decode.cu) and through the classic one-CTA-per-tile kernel: both equal the
@@ -126,6 +126,7 @@ def test_slab_of_full_size_bricks_both_kernels(ctx, kernel):
     vr.debug_set("decode_kernel", 0 if kernel.startswith("persistent") else 1)
     # how a parsed unit's voxels leave the SM: one tensor store per unit, or 16-byte stores of the lanes (default: chosen per plan)
     vr.debug_set("unit_store", {"persistent_tensor_stores": 1, "persistent_lane_stores": 2}.get(kernel, 0))
+    vr.debug_set("decode_split", 1 if kernel == "persistent_split" else 0)  # constant groups as a kernel of their own, side stream
     try:
         bx, by, bz = 256, 256, 128
         vols = [synth.constant_brick(value=0), synth.rm_brick(3, 4, 7), synth.rm_brick(2, 4, 7), synth.noise_brick(),
@@ -158,6 +159,7 @@ def test_slab_of_full_size_bricks_both_kernels(ctx, kernel):
     finally:
         vr.debug_set("decode_kernel", 0)
         vr.debug_set("unit_store", 0)
+        vr.debug_set("decode_split", 0)
 
 
 def test_handles_may_be_released_in_any_order(ctx):

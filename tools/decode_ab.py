@@ -69,6 +69,7 @@ def main():
     ap.add_argument("--tma-rows", type=int, default=8)
     ap.add_argument("--unit-store", type=int, default=0, help="persistent kernel: 0 choose, 1 tensor store per unit, 2 16-byte stores of the lanes")
     ap.add_argument("--parse-order", type=int, default=0, help="0 address order, 1 longest segments first")
+    ap.add_argument("--split", type=int, default=0, help="persistent kernel: 1 = constant groups as a kernel of their own on a side stream")
     ap.add_argument("--probes", action="store_true", help="persistent kernel: two more timing probes (results are not valid voxels)")
     args = ap.parse_args()
     peak, _ = bench.peaks()
@@ -76,6 +77,7 @@ def main():
     vr.debug_set("tma_rows", args.tma_rows)
     vr.debug_set("parse_order", args.parse_order)
     vr.debug_set("unit_store", args.unit_store)
+    vr.debug_set("decode_split", args.split)
     ctx = vr.Context(0)
     threads = min(32, os.cpu_count() or 8)
     for name in args.workloads.split(","):
@@ -94,7 +96,7 @@ def main():
                     plan = vr.DecodePlan(ctx, streams, origins, vol)  # the classic kernel filters its work list at creation
                 ms, mn = timed(ctx, plan.run, args.iters)
                 algo = by["stream"] + by["voxels"]
-                print(json.dumps({"workload": name, "kernel": plan.kernel(), "fill_mode": args.fill_mode, "tma_rows": args.tma_rows, "parse_order": args.parse_order, "unit_store": args.unit_store, "part": part, "ms": ms, "min_ms": mn,
+                print(json.dumps({"workload": name, "kernel": plan.kernel(), "fill_mode": args.fill_mode, "tma_rows": args.tma_rows, "parse_order": args.parse_order, "unit_store": args.unit_store, "split": args.split, "part": part, "ms": ms, "min_ms": mn,
                                   "gvoxel_s": by["voxels"] / ms / 1e6 if only == 0 else None,
                                   "algo_GBps": algo / ms / 1e6 if only == 0 else None,
                                   "frac_of_hbm_peak": algo / ms / 1e6 / peak if only == 0 else None,

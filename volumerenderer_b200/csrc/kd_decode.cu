@@ -257,8 +257,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
 // The warp that feeds the TMA unit.  A constant group = 2^L x-neighbouring constant tiles (vr_fill_job): a row image of
 // (tx << L) x VR6_TMA_ROWS bytes in shared memory (byte j * tx.. = value of tile j), stored tz * ty / rows times.  Images
 // are cached by (L, values): a slab of mostly empty / mostly solid bricks rewrites them a handful of times per launch.
-__device__ __forceinline__ void fill_warp(const Decode6Params& p, const uint32_t sb, const uint32_t lane) {
-  const uint32_t img0 = sb + VR6_OFF_IMG;
+__device__ __forceinline__ void fill_warp(const Decode6Params& p, const uint32_t img0, const uint32_t lane) {
   const uint32_t ltx = 31u - (uint32_t)__clz(p.tx);
   const uint32_t rows = (uint32_t)p.tmaRows, imgBytes = 256u * rows, nSlots = VR6_IMG_TOTAL / imgBytes;
   const uint32_t rowBlocks = (uint32_t)p.ty / rows, per = (uint32_t)p.tz * rowBlocks;
@@ -344,16 +343,26 @@ __global__ void __launch_bounds__(VR6_THREADS, 1) kd_decode6_kernel(const __grid
   extern __shared__ __align__(128) uint8_t smem6[];
   const uint32_t sb = (uint32_t)__cvta_generic_to_shared(smem6);
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
-  for (uint32_t i = tid; i < VR6_LUT_BYTES / 16u; i += VR6_THREADS) {
+  for (uint32_t i = tid; i < VR6_LUT_BYTES / 16u; i += blockDim.x) {
     const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.lut) + i);
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sb + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
   __syncthreads();
   if (warp >= VR6_PARSE_WARPS) {
-    if (p.only != 1 && p.nFill) fill_warp(p, sb, lane);
+    if (p.only != 1 && p.nFill) fill_warp(p, sb + VR6_OFF_IMG, lane);
   } else if (p.only != 2 && p.nParse) {
     parse_warp<ROT>(p, sb, warp, lane);
   }
+}
+
+// The constant groups as a launch of their own (split mode): one warp per CTA, 8 KB of shared memory, next to the parse
+// CTAs of the kernel above (launched without its fill warp and without the image area, so that both fit one SM).  A parse
+// CTA holds 56 K registers until its last warp is done; as one kernel, those registers stay taken while the fill warp drains
+// its HBM-bound queue, and a frame's march CTAs (a second stream) find no room.  As two kernels the parse CTAs leave when the
+// parsing is done and the march runs beside the fills.
+__global__ void __launch_bounds__(32, 1) kd_fill6_kernel(const __grid_constant__ Decode6Params p) {
+  extern __shared__ __align__(128) uint8_t smem6[];
+  fill_warp(p, (uint32_t)__cvta_generic_to_shared(smem6), threadIdx.x);
 }
 
 uint32_t kd_decode6_stage_chunks(void) { return VR6_STAGE_BYTES / 16u; }
@@ -419,16 +428,17 @@ bool kd_decode6_plan(const vr_kd_geom& g, uint8_t* dst, int64_t SX, int64_t SY, 
 }
 
 template <int ROT>
-static cudaError_t launch6(const Decode6Params& p, size_t smem, int ctas, cudaStream_t stream) {
+static cudaError_t launch6(const Decode6Params& p, size_t smem, int ctas, int threads, cudaStream_t stream) {
   cudaError_t e = cudaFuncSetAttribute(kd_decode6_kernel<ROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  kd_decode6_kernel<ROT><<<(unsigned)ctas, VR6_THREADS, smem, stream>>>(p);
+  kd_decode6_kernel<ROT><<<(unsigned)ctas, (unsigned)threads, smem, stream>>>(p);
   return cudaGetLastError();
 }
 
 cudaError_t kd_decode6_launch(const vr_kd_geom& g, const Decode6Plan& plan, const vr_kd_job*, const vr_parse_item* parseDev, int nParse,
                               const vr_fill_job* fillsDev, int nFill, uint32_t* queueDev, const uint32_t* lutDev, uint8_t* dst,
-                              int64_t rowPitch, int64_t slicePitch, uint8_t* occ, int only, cudaStream_t stream, int fillMode, int tmaOut) {
+                              int64_t rowPitch, int64_t slicePitch, uint8_t* occ, int only, cudaStream_t stream, int fillMode, int tmaOut,
+                              const Decode6Side* side) {
   if (nParse <= 0 && nFill <= 0) return cudaSuccess;
   static int numSMs = 0;
   if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); }
@@ -456,9 +466,32 @@ cudaError_t kd_decode6_launch(const vr_kd_geom& g, const Decode6Plan& plan, cons
   const uint32_t perWarp = p.nParse / (uint32_t)(ctas * VR6_PARSE_WARPS);
   p.batch = perWarp >= 8u * VR6_BATCH_MAX ? VR6_BATCH_MAX : (perWarp >= 16u ? 2u : 1u);
   // rot == 2 (last split along z) puts tile x bit 3 outside a warp's 32 leaf boxes: p6_make_geom never accepts it
-  if (plan.pg.rot == 0) return launch6<0>(p, plan.smemBytes, ctas, stream);
-  if (plan.pg.rot == 1) return launch6<1>(p, plan.smemBytes, ctas, stream);
-  return cudaErrorInvalidValue;
+  if (plan.pg.rot != 0 && plan.pg.rot != 1) return cudaErrorInvalidValue;
+  if (side && side->stream && (only == 0 || only == 1 || only == 2) && p.nParse && p.nFill && p.fillMode != 1) {
+    // split mode: constant groups on the side stream (fork / join by events, capturable), parse CTAs without the fill warp
+    // (timing probes only == 1 / 2: one of the two kernels alone)
+    if (only != 1) {
+      e = cudaEventRecord(side->fork, stream);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(side->stream, side->fork, 0);
+      if (e != cudaSuccess) return e;
+      Decode6Params pf = p;
+      pf.only = 2;
+      const int fillCtas = wantF < numSMs ? (wantF > 0 ? wantF : 1) : numSMs;
+      kd_fill6_kernel<<<(unsigned)fillCtas, 32, VR6_IMG_TOTAL, side->stream>>>(pf);
+      e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaEventRecord(side->join, side->stream);
+      if (e != cudaSuccess) return e;
+    }
+    if (only != 2) {
+      p.only = 1;
+      const int parseCtas = wantP < numSMs ? (wantP > 0 ? wantP : 1) : numSMs;
+      e = plan.pg.rot == 0 ? launch6<0>(p, VR6_OFF_IMG, parseCtas, VR6_PARSE_WARPS * 32, stream) : launch6<1>(p, VR6_OFF_IMG, parseCtas, VR6_PARSE_WARPS * 32, stream);
+      if (e != cudaSuccess) return e;
+    }
+    return only != 1 ? cudaStreamWaitEvent(stream, side->join, 0) : cudaSuccess;
+  }
+  if (plan.pg.rot == 0) return launch6<0>(p, plan.smemBytes, ctas, VR6_THREADS, stream);
+  return launch6<1>(p, plan.smemBytes, ctas, VR6_THREADS, stream);
 }
 
 // =====================================================================================================================

@@ -33,11 +33,14 @@ struct Decode6Plan {
 // false: this geometry / destination cannot take the persistent kernel
 bool kd_decode6_plan(const vr_kd_geom& g, uint8_t* dst, int64_t SX, int64_t SY, int64_t SZ, Decode6Plan* out, int tmaRows = 8);
 uint32_t kd_decode6_stage_chunks(void);  // staging capacity per unit in 16-byte chunks (host work list: kd_build_worklist6)
+// Split mode (side != null): the constant groups run as a kernel of their own on side->stream, forked from and joined to
+// `stream` by the two events (all three owned by the caller, one set per context).
+struct Decode6Side { cudaStream_t stream; cudaEvent_t fork, join; };
 // queueDev: VR6_QUEUE_WORDS words, zeroed by the launch.  lutDev: vr6::chain_entry table (16 384 entries).
 cudaError_t kd_decode6_launch(const vr_kd_geom& g, const Decode6Plan& plan, const vr_kd_job* jobsDev, const vr_parse_item* parseDev, int nParse,
                               const vr_fill_job* fillsDev, int nFill, uint32_t* queueDev, const uint32_t* lutDev, uint8_t* dst,
                               int64_t rowPitch, int64_t slicePitch, uint8_t* occ, int only, cudaStream_t stream, int fillMode = 0,
-                              int tmaOut = 0);
+                              int tmaOut = 0, const Decode6Side* side = nullptr);
 // only (timing probes, vr_debug_set("decode_only")): 0 = everything, 1 = parse tiles, 2 = constant groups.
 
 // ---- classic kernel: one CTA per work-list entry (kd_worklist.h) -----------------------------------------------------------

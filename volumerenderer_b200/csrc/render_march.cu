@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
             const int k = occ_skip<false>(occ, v, p, dirStep, inv, 299 - i);
             if (k >= 0) {
               for (int j = 0; j < k; ++j) p = add(p, dirStep);
-              i += k; n += 1 + k;
+              i += k; n += (unsigned)((1 + k) & P.skipCountMask);
               continue;
             }
           }
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) march_kernel(const __grid_constant__ Rend
             const int k = occ_skip<false>(occ, v, pn, dirStep, inv, 299 - i);
             if (k >= 0) {
               for (int j = 0; j < k; ++j) p = add(p, dirStep);
-              i += k; n += 1 + k;
+              i += k; n += (unsigned)((1 + k) & P.skipCountMask);
               continue;
             }
           }

@@ -13,6 +13,8 @@ struct RenderParams {
   float step[3];
   float iso;
   int W, H, mode;  // mode 0 composite, 1 isosurface
+  int skipCountMask;  // -1: skipped lattice positions count as samples (the reference's march steps); 0: only fetching steps
+                      // count (vr_debug_set("count_fetched", 1); plain march only)
 };
 // occ.dil == null: march every sample; otherwise skip void cells (occupancy.h), same frame bit for bit
 cudaError_t render_launch(const RenderParams& P, const OccView& occ, const uint8_t* vol, int X, int Y, int Z, float4* out,

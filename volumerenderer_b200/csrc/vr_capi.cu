@@ -54,6 +54,10 @@ int vr_context_destroy(vr_context* c) {
   for (auto& e : c->ev) for (auto& k : e) if (k) cudaEventDestroy(k);
   if (c->evOrder) cudaEventDestroy(c->evOrder);
   for (auto& kv : c->chainLuts) cudaFree(kv.second);
+  for (auto& kv : c->chainLuts6) cudaFree(kv.second);
+  if (c->side.stream) cudaStreamDestroy(c->side.stream);
+  if (c->side.fork) cudaEventDestroy(c->side.fork);
+  if (c->side.join) cudaEventDestroy(c->side.join);
   vr::kd_builder_destroy(c->builder);
   delete c;
   return VR_OK;

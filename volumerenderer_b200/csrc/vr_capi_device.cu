@@ -185,7 +185,7 @@ void vr_decode_plan::lazy_free() {
 // environment.  decode_kernel: 0 = persistent kernel where the brick shape allows it (default), 1 = classic kernel always.
 // decode_only: 0 = everything, 1 = parse tiles only, 2 = constant groups only (timing probes: the slab is then incomplete).
 namespace {
-struct DebugKnobs { int decodeKernel = 0, decodeOnly = 0, fillAttach = 2, fillMode = 2, tmaRows = 8, parseOrder = 0, unitStore = 0; } g_dbg;
+struct DebugKnobs { int decodeKernel = 0, decodeOnly = 0, fillAttach = 2, fillMode = 2, tmaRows = 8, parseOrder = 0, unitStore = 0, decodeSplit = 0; } g_dbg;
 }
 extern "C" int vr_debug_set(const char* key, int value) {
   if (!key) return fail(VR_ERR_ARG, "vr_debug_set: null key");
@@ -197,6 +197,8 @@ extern "C" int vr_debug_set(const char* key, int value) {
   else if (k == "tma_rows") g_dbg.tmaRows = value;
   else if (k == "parse_order") g_dbg.parseOrder = value;
   else if (k == "unit_store") g_dbg.unitStore = value;  // 0 / 1 = one tensor store per unit (default), 2 = 16-byte stores of the lanes
+  else if (k == "decode_split") g_dbg.decodeSplit = value;  // 1: constant groups as a kernel of their own on a side stream
+  else if (k == "count_fetched") vr::g_count_fetched = value;  // samples_dev counts fetching march steps only (plain march)
   else if (k == "read_partial") g_read_partial = value;  // vr_volume_download of a partially decoded volume (tests)
   else return fail(VR_ERR_ARG, "vr_debug_set: unknown key");
   return VR_OK;
@@ -211,6 +213,8 @@ extern "C" int vr_debug_get(const char* key, int* value) {
   else if (k == "tma_rows") *value = g_dbg.tmaRows;
   else if (k == "parse_order") *value = g_dbg.parseOrder;
   else if (k == "unit_store") *value = g_dbg.unitStore;
+  else if (k == "decode_split") *value = g_dbg.decodeSplit;
+  else if (k == "count_fetched") *value = vr::g_count_fetched;
   else if (k == "read_partial") *value = g_read_partial;
   else return fail(VR_ERR_ARG, "vr_debug_get: unknown key");
   return VR_OK;
@@ -294,7 +298,8 @@ static cudaError_t plan_launch(vr_decode_plan* p, const vr_parse_item* parseDev,
   vr_volume* d = p->dst;
   if (p->persistent6)
     return kd_decode6_launch(p->geom, p->p6, p->jobsDev, parseDev, nParse, fillsDev, nFill, p->queueDev, p->lut6Dev, d->dev, d->SX, d->SX * d->SY,
-                             occ ? d->occRaw : nullptr, only, p->ctx->stream, g_dbg.fillMode, tmaOut);
+                             occ ? d->occRaw : nullptr, only, p->ctx->stream, g_dbg.fillMode, tmaOut,
+                             g_dbg.decodeSplit && p->ctx->side.stream ? &p->ctx->side : nullptr);
   return kd_decode_launch(p->geom, p->jobsDev, workDev, nWork, d->dev, d->SX, d->SX * d->SY, p->vec16, p->ctx->stream, occ ? d->occRaw : nullptr,
                           occ ? p->tileCellDev : nullptr, fillsDev);
 }
@@ -391,12 +396,12 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   p->treeDist.resize((size_t)n);
   for (int i = 0; i < n; ++i) {
     vr_stream* s = streams[i];
-    if (!s->devImage || s->device != ctx->device) { delete p; return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
+    if (!s->devImage || s->device != ctx->device) { vr_decode_plan_destroy(p); return fail(VR_ERR_STATE, "stream not uploaded to this device"); }
     const vr_kd_header& h = s->kd.hdr;
-    if (h.X != g.X || h.Y != g.Y || h.Z != g.Z) { delete p; return fail(VR_ERR_ARG, "all streams of a plan must share one brick shape"); }
+    if (h.X != g.X || h.Y != g.Y || h.Z != g.Z) { vr_decode_plan_destroy(p); return fail(VR_ERR_ARG, "all streams of a plan must share one brick shape"); }
     const int64_t ox = origins[3 * i], oy = origins[3 * i + 1], oz = origins[3 * i + 2];
     if (ox < 0 || oy < 0 || oz < 0 || ox + h.X > dst->SX || oy + h.Y > dst->SY || oz + h.Z > dst->SZ) {
-      delete p; return fail(VR_ERR_ARG, "brick placement outside the destination volume");
+      vr_decode_plan_destroy(p); return fail(VR_ERR_ARG, "brick placement outside the destination volume");
     }
     if (ox % 16) vec16 = false;
     vr_kd_job& j = jobs[(size_t)i];
@@ -418,7 +423,7 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
       if ((l[0] & 31) || (l[1] & 31) || (l[2] & 15)) occFused = false;
       else j.occBase = (l[0] >> 5) + (int64_t)dst->nc[0] * ((l[1] >> 5) + (int64_t)dst->nc[1] * (l[2] >> 4));
     }
-    { int rc = context_chain_lut(ctx, j.chainDist, &j.chainLut); if (rc != VR_OK) { delete p; return rc; } }
+    { int rc = context_chain_lut(ctx, j.chainDist, &j.chainLut); if (rc != VR_OK) { vr_decode_plan_destroy(p); return rc; } }
     int chainSum = 0;  // the tables pack the net offset in 8 signed bits: 64+32+...+1 = 127 for every reference stream
     for (int k = 1; k <= VR_ADD_LEVELS; ++k) chainSum += s->kd.distanceMap[(size_t)(g.D0 + k)];
     if (chainSum > 127) p->geom.fastPath = 0;
@@ -443,7 +448,7 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
       tc[t] = (ox >> 5) + dst->nc[0] * ((oy >> 5) + dst->nc[1] * (oz >> 4));
     }
     cudaError_t et = upload_vec(tc, &p->tileCellDev);
-    if (et != cudaSuccess) { delete p; return fail_cuda(et, "upload tile cells"); }
+    if (et != cudaSuccess) { vr_decode_plan_destroy(p); return fail_cuda(et, "upload tile cells"); }
   }
   // which kernel: the persistent one wherever the brick shape, the destination and the streams allow it
   p->persistent6 = g_dbg.decodeKernel == 0 && vec16 && p->geom.fastPath && sameChain &&
@@ -451,6 +456,12 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
   if (p->persistent6) {
     int rc = context_chain_lut6(ctx, chain0, &p->lut6Dev);
     if (rc == VR_OK && cudaMalloc((void**)&p->queueDev, VR6_QUEUE_WORDS * sizeof(uint32_t)) != cudaSuccess) rc = fail(VR_ERR_CUDA, "cudaMalloc(queue)");
+    if (rc == VR_OK && !ctx->side.stream) {  // split launch (kd_decode.h): one side stream + two events per context
+      cudaError_t es = cudaStreamCreateWithFlags(&ctx->side.stream, cudaStreamNonBlocking);
+      if (es == cudaSuccess) es = cudaEventCreateWithFlags(&ctx->side.fork, cudaEventDisableTiming);
+      if (es == cudaSuccess) es = cudaEventCreateWithFlags(&ctx->side.join, cudaEventDisableTiming);
+      if (es != cudaSuccess) rc = fail_cuda(es, "side stream of the decode launch");
+    }
     if (rc != VR_OK) { vr_decode_plan_destroy(p); return rc; }
   }
   int rc = plan_build_lists(p, nullptr, nullptr, &p->parseDev, &p->nParse, &p->workDev, &p->nWork, &p->fillJobsDev, &p->nFill, &p->tmaOut);

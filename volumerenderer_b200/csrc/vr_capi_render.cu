@@ -15,6 +15,7 @@ using namespace vr;
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
 
 namespace vr {
+int g_count_fetched = 0;  // vr_debug_set("count_fetched")
 int make_render_params(const vr_render_params* in, RenderParams* P) {
   if (in->width <= 0 || in->height <= 0) return VR_ERR_ARG;
   double f[3] = {in->front[0], in->front[1], in->front[2]}, up[3] = {in->up[0], in->up[1], in->up[2]};
@@ -37,6 +38,7 @@ int make_render_params(const vr_render_params* in, RenderParams* P) {
   P->iso = in->isoValue;
   P->W = in->width; P->H = in->height;
   P->mode = in->mode == VR_MODE_COMPOSITE ? 0 : 1;
+  P->skipCountMask = g_count_fetched ? 0 : -1;
   return VR_OK;
 }
 // Largest voxel value m whose sample can never reach the mode's threshold (occupancy.h): composite skips

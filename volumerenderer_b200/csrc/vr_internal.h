@@ -22,6 +22,7 @@ struct vr_context {
   vr::KdBuilder* builder = nullptr;  // scratch of the GPU stream producer (kd_build.h), created on first use
   std::map<uint64_t, uint32_t*> chainLuts;   // chainDist -> device table of 16384 entries (classic kernel: vr_chain_lut_entry)
   std::map<uint64_t, uint32_t*> chainLuts6;  // same for the persistent kernel (vr6::chain_entry)
+  vr::Decode6Side side{};  // side stream + fork / join events of the split decode launch (kd_decode.h), created with the first plan
 };
 
 // Device image of a prepared stream: one arena, sections 16-byte aligned:
@@ -114,6 +115,7 @@ struct vr_decode_plan {
 };
 
 namespace vr {
+extern int g_count_fetched;  // vr_debug_set("count_fetched"), vr_capi_render.cu
 int fail(int code, const char* msg);
 int fail_cuda(cudaError_t e, const char* where);
 int stream_build_image(vr_stream* s);  // prepare + pack host image
