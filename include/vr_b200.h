@@ -175,6 +175,14 @@ int vr_decode_plan_create(vr_context* ctx, vr_stream* const* streams, int32_t n,
                           vr_volume* dst, vr_decode_plan** out);
 int vr_decode_plan_run(vr_decode_plan* plan); /* one kernel launch, asynchronous */
 int vr_decode_plan_destroy(vr_decode_plan* plan);
+/* Random-access decode (levelCutRecursive at an arbitrary node, HashedKdtree.cpp:254-336): decode only the
+ * tiles with needed[b * tiles + t] != 0 (tiles = vr_stream_index_info out[0], kd path order; tile boxes from
+ * vr_lazy_tile_mask).  Those tiles hold exactly the voxels levelCut produces there; every other tile is left alone, except
+ * constant tiles in the x-aligned fill group of a needed tile, which receive their (correct) voxels too.  The occupancy
+ * grid receives the exact maxima of the tiles left out.  Afterwards the destination is PARTIAL (see
+ * vr_render_compressed_lazy).  Needs 32x32x16 tiles aligned with the destination's occupancy cells.  Streams opened with a
+ * tile subset must hold every non-constant tile asked for (VR_ERR_STATE otherwise).  stats as vr_render_compressed_lazy. */
+int vr_decode_plan_run_tiles(vr_decode_plan* plan, const uint8_t* needed, int64_t stats[4]);
 /* algorithmic bytes of one run: [0] stream bytes read, [1] voxel bytes written, [2] index bytes read */
 int vr_decode_plan_bytes(const vr_decode_plan* plan, int64_t out[3]);
 /* which kernel the plan launches: 0 = persistent warp-specialised kernel (bricks with 4x4x4 leaf boxes such as the
@@ -264,6 +272,30 @@ int vr_lazy_tile_mask(vr_stream* const* streams, int32_t n, const int64_t* origi
 /* Exact minimum / maximum of the voxels levelCut would produce in every decode tile, read off the stream index
  * (implies prepare; nothing is decoded).  2^Dt entries each in tile (kd path) order; tile_dims (optional) = tile extent. */
 int vr_stream_tile_bounds(vr_stream* s, uint8_t* mins, uint8_t* maxs, int64_t cap, int32_t tile_dims[3]);
+
+/* ---- indexed ("random-access") container -------------------------------------------------------------
+ * What HashedKdtree.cpp:96-214 (build), :254-336 (levelCutRecursive), :406-507 (compress), :528-545 (save) was reaching
+ * for: decode any part of a brick without parsing what lies in front of it.  The reference's Morton-keyed hash with
+ * collision overflow and a std::random_device seed (HashedKdtree.h:82-84) crashes and is not reproduced;
+ * the container keeps the stream of VolumeKdtree::save bit for bit and stores the decode index of vr_stream_prepare and
+ * the exact per-tile bounds beside it (layout: csrc/kd_kdx.cpp).  Deterministic: a pure function of the stream.
+ *   vr_stream_save_indexed    writes it (prepares the index first if the stream has none).
+ *   vr_stream_open_indexed    opens it WITHOUT walking the stream.  tile_mask (optional, 2^Dt bytes in tile order, see
+ *                             vr_stream_index_info) reads only the byte ranges of those tiles from disk; such a stream
+ *                             decodes through vr_decode_plan_run_tiles / vr_render_compressed_lazy only, and only the
+ *                             tiles it holds.  verify != 0 checks the stream checksum (full opens).
+ *                             bytes_read (optional) = bytes fetched from the file.
+ *   vr_stream_from_memory_indexed  the same from a buffer holding the file image.
+ *   vr_stream_index_info      out[0] tiles per brick (2^Dt), [1] live (non-constant) tiles, [2] leaf subtrees per tile,
+ *                             [3] 1 when only a tile subset is resident, [4] index bytes, [5] longest leaf segment (symbols).
+ *   vr_stream_index_section   read-only view of one index array (implies prepare): 1 tileLeafBlock u32, 2 tileVal u8,
+ *                             3 tileMin u8, 4 tileMax u8, 5 blockSymBegin u32, 6 blockSymEnd u32, 7 leafOff u32, 8 leafVal u8. */
+int vr_stream_save_indexed(vr_stream* s, const char* path);
+int vr_stream_open_indexed(const char* path, const uint8_t* tile_mask, int32_t verify, vr_stream** out, int64_t* bytes_read);
+int vr_stream_from_memory_indexed(const uint8_t* image, int64_t nbytes, const uint8_t* tile_mask, int32_t verify, vr_stream** out);
+int vr_stream_serialize_indexed(vr_stream* s, uint8_t* out, int64_t cap, int64_t* nbytes); /* out may be NULL to query the size */
+int vr_stream_index_info(vr_stream* s, int64_t out[6]);
+int vr_stream_index_section(vr_stream* s, int32_t which, const void** data, int64_t* nbytes);
 
 /* ---- sort-last rendering of a volume sharded over GPUs (no counterpart in the reference, which
  * renders one texture on one GPU, main.cpp:290,404) ------------------------------------

@@ -41,6 +41,9 @@ class Context {
   Context& operator=(const Context&) = delete;
   vr_context* handle() const { return h_; }
   void synchronize() { check(vr_context_synchronize(h_)); }
+  // Process-wide context on device 0, created on first use: what reference-shaped calls that carry no context
+  // (levelCut(cutDepth, out), VolumeReader's four-argument constructor) run on -- the role of the one GL context of main.cpp.
+  static Context& shared() { static Context c(0); return c; }
  private:
   vr_context* h_ = nullptr;
 };
@@ -57,7 +60,10 @@ class VolumeKdtree {
   vr_build_stats stats{};            // what build() prints in the reference (:76,120,129)
 
   VolumeKdtree() {}
-  VolumeKdtree(std::vector<byte>& inData, int64_t x, int64_t y, int64_t z) : X(x), Y(y), Z(z), data_(&inData) {}
+  // :103.  ctx (optional) binds the device context levelCut / build(true-on-device) use; default = Context::shared().
+  VolumeKdtree(std::vector<byte>& inData, int64_t x, int64_t y, int64_t z, Context* ctx = nullptr) : X(x), Y(y), Z(z), data_(&inData), ctx_(ctx) {}
+  explicit VolumeKdtree(Context* ctx) : ctx_(ctx) {}
+  void setContext(Context* ctx) { ctx_ = ctx; }
   ~VolumeKdtree() { vr_stream_destroy(s_); }
   VolumeKdtree(const VolumeKdtree&) = delete;
   VolumeKdtree& operator=(const VolumeKdtree&) = delete;
@@ -84,7 +90,9 @@ class VolumeKdtree {
     check(vr_stream_open(filename.c_str(), &s_));
     refresh();
   }
-  // Stage 1 on the GPU (:134).  cutDepth must be maxTreeDepth (any other depth crashes the reference).
+  // Stage 1 on the GPU (:134, call site main.cpp:281), same two arguments as the reference; runs on the context bound at
+  // construction (or the shared one).  cutDepth must be maxTreeDepth (any other depth crashes the reference).
+  void levelCut(int cutDepth, std::vector<byte>& outData) { levelCut(cutDepth, outData, ctx_ ? *ctx_ : Context::shared()); }
   void levelCut(int cutDepth, std::vector<byte>& outData, Context& ctx) {
     need();
     outData.resize((size_t)(X * Y * Z));
@@ -129,6 +137,7 @@ class VolumeKdtree {
   std::vector<byte>* data_ = nullptr;
   const std::vector<byte>* output_ = nullptr;
   vr_stream* s_ = nullptr;
+  Context* ctx_ = nullptr;
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -143,7 +152,7 @@ class VolumeReader {
  public:
   dim3D brickDims = {0, 0, 0};
   std::function<std::string(int, int)> findSourceFile;  // (brick, timestep) -> path
-  std::map<int, std::vector<int64_t>>* brickMap = nullptr;  // brick -> (i, j, k) on the brick grid
+  std::map<int, dim3D>* brickMap = nullptr;  // brick -> (i, j, k) on the brick grid: the reference's type (VolumeReader.h:45)
   std::vector<T> data;
   dim3D dataDims = {0, 0, 0};
   vr_volume* volume = nullptr;  // replaces `GLuint textureId`
@@ -151,9 +160,16 @@ class VolumeReader {
   VolumeReader() {
     findSourceFile = [](int, int) -> std::string { throw std::runtime_error("findSourceFile function not defined"); };
   }
+  // VolumeReader.h:68-70, argument for argument; ctx (optional) = the device context of toGPU uploads, default Context::shared()
+  VolumeReader(const dim3D brick, const dim3D /*grid*/, std::function<std::string(int, int)> findFileFunct, std::map<int, dim3D>* bMap,
+               Context* ctx = nullptr)
+      : findSourceFile(findFileFunct), brickMap(bMap), ctx_(ctx) {
+    for (int a = 0; a < 3; ++a) brickDims[a] = brick[a];
+  }
+  // the same with a map of vectors (hosts that cannot hold arrays in a std::map)
   VolumeReader(const dim3D brick, const dim3D /*grid*/, std::function<std::string(int, int)> findFileFunct,
                std::map<int, std::vector<int64_t>>* bMap, Context* ctx = nullptr)
-      : findSourceFile(findFileFunct), brickMap(bMap), ctx_(ctx) {
+      : findSourceFile(findFileFunct), brickMapVec_(bMap), ctx_(ctx) {
     for (int a = 0; a < 3; ++a) brickDims[a] = brick[a];
   }
   ~VolumeReader() { vr_volume_destroy(volume); }
@@ -172,11 +188,13 @@ class VolumeReader {
     const int64_t GX = I * X, GY = J * Y;
     std::vector<int64_t> ijk((size_t)numBricks * 3);
     for (int b = 0; b < (int)numBricks; ++b) {
-      if (!brickMap || !brickMap->count(b)) throw std::runtime_error("brick map has no entry for brick " + std::to_string(b));
-      for (int a = 0; a < 3; ++a) ijk[(size_t)b * 3 + a] = (*brickMap)[b][a];
+      if (brickMap && brickMap->count(b)) { for (int a = 0; a < 3; ++a) ijk[(size_t)b * 3 + a] = (*brickMap)[b][a]; }
+      else if (brickMapVec_ && brickMapVec_->count(b)) { for (int a = 0; a < 3; ++a) ijk[(size_t)b * 3 + a] = (*brickMapVec_)[b][(size_t)a]; }
+      else throw std::runtime_error("brick map has no entry for brick " + std::to_string(b));
     }
     dataDims[0] = GX; dataDims[1] = GY; dataDims[2] = K * Z;
-    if (toGPU && ctx_) {
+    if (toGPU && !ctx_) ctx_ = &Context::shared();
+    if (toGPU) {
       // pipelined path (vr_volume_load_bricks): file reads overlap the H2D copies, bricks go straight to their place in
       // the slab; the assembled host array (`data`) is only filled when the caller keeps it (dealloc == false)
       static_assert(sizeof(T) == 1, "the device slab is 8-bit (GL_RED / GL_UNSIGNED_BYTE in the reference)");
@@ -208,7 +226,7 @@ class VolumeReader {
   // glTexImage3D(GL_TEXTURE_3D, GL_RED, GL_UNSIGNED_BYTE) of VolumeReader.h:114-127 -> one device slab
   void transferToGPU(bool dealloc = true) {
     static_assert(sizeof(T) == 1, "the device slab is 8-bit (GL_RED / GL_UNSIGNED_BYTE in the reference)");
-    if (!ctx_) throw Error(VR_ERR_STATE, "transferToGPU: no vr::Context given");
+    if (!ctx_) ctx_ = &Context::shared();
     vr_volume_destroy(volume); volume = nullptr;
     check(vr_volume_create(ctx_->handle(), dataDims[0], dataDims[1], dataDims[2], &volume));
     check(vr_volume_upload_brick(ctx_->handle(), volume, reinterpret_cast<const uint8_t*>(data.data()), dataDims[0], dataDims[1],
@@ -238,6 +256,7 @@ class VolumeReader {
   }
   std::vector<T> temp_;
   std::string path_;
+  std::map<int, std::vector<int64_t>>* brickMapVec_ = nullptr;
   Context* ctx_ = nullptr;
 };
 

@@ -23,8 +23,8 @@ int main(int argc, char** argv) {
   const std::string dir = argv[2];
   try {
     vr::dim3D BRICK_DIM = {32, 32, 16}, VOLUME_GRID = {2, 2, 2};  // main.cpp:78-79 in miniature
-    std::map<int, std::vector<int64_t>> brickMap;                 // fillVolumeBrickMap, main.cpp:599-619
-    for (int b = 0; b < 8; ++b) brickMap[b] = {b % 2, (b / 2) % 2, b / 4};
+    std::map<int, vr::dim3D> brickMap;                            // main.cpp:81, filled as fillVolumeBrickMap does (main.cpp:599-619)
+    for (int b = 0; b < 8; ++b) { brickMap[b][0] = b % 2; brickMap[b][1] = (b / 2) % 2; brickMap[b][2] = b / 4; }
     auto findBrickBinaryFile = [&](int brick, int timestep) { return dir + "/brick_" + std::to_string(brick) + "_t" + std::to_string(timestep) + ".raw"; };
     vr::Context* ctx = gpu ? new vr::Context(0) : nullptr;
     vr::VolumeReader<vr::byte> volume(BRICK_DIM, VOLUME_GRID, findBrickBinaryFile, &brickMap, ctx);
@@ -73,7 +73,12 @@ int main(int argc, char** argv) {
                                                  gpuTree.numActiveNodes == myTree.numActiveNodes && gpuTree.stats.maxError == myTree.stats.maxError));
     }
     std::vector<vr::byte> treeData;
-    myTree.levelCut(myTree.maxTreeDepth, treeData, *ctx);  // main.cpp:280-281
+    myTree.levelCut(myTree.maxTreeDepth, treeData);  // main.cpp:280-281, the reference's two-argument call (shared device context)
+    {
+      std::vector<vr::byte> again;
+      myTree.levelCut(myTree.maxTreeDepth, again, *ctx);  // explicit context: same voxels
+      std::printf("levelcut_ctx_equal=%d\n", (int)(again == treeData));
+    }
     std::printf("decoded=%u maxerr_measured=%d\n", fnv(treeData.data(), treeData.size()), myTree.measureMaxError());
     try { std::vector<vr::byte> o; myTree.levelCut(10, o, *ctx); std::puts("cut10=nothrow"); }
     catch (const vr::Error& e) { std::printf("cut10=error%d\n", e.code); }

@@ -87,6 +87,7 @@ def test_cpp_pipeline_gpu(exe, scene):
     rc, want = oa.oracle_levelcut(s.bits, hd.numActiveNodes, s.distance_map, hd.origTreeDepth, hd.maxTreeDepth, 64, 64, 32)
     assert rc == 0 and int(kv["decoded"]) == fnv_fast(want)
     assert int(kv["maxerr_measured"]) == int(np.abs(want.astype(int) - full.astype(int)).max())
+    assert kv["levelcut_ctx_equal"] == "1"                 # two-argument levelCut (shared context) == explicit context
     assert kv["cut10"] == "error5"                         # VR_ERR_UNSUPPORTED; the reference segfaults
     assert kv["gpu_build_equal"] == "1"                    # VolumeKdtree::build(Context&): GPU producer, same stream
     # LoadBricksToTexture(toGPU=true): pipelined loader, same placement on the host copy and in the device slab

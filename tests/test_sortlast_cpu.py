@@ -51,6 +51,30 @@ def test_visibility_orders():
         sortlast.SortLast(None, d2, 0)
 
 
+def _desc(glob, lo, hi):
+    d = sortlast.SlabDesc()
+    d.global_[:] = glob
+    d.origin[:] = lo
+    d.own_lo[:] = lo
+    d.own_hi[:] = hi
+    return d
+
+
+def test_only_grid_partitions_are_accepted():
+    """Disjoint boxes that tile the texture but are not a grid have no front-to-back order valid for every ray (a +x+y ray
+    can leave Q = [1,2]x[0,1] and enter P = [0,2]x[1,2] although P sorts before Q): vr_sortlast_create must refuse them."""
+    G = (64, 64, 32)
+    bad = [_desc(G, (0, 32, 0), (64, 64, 32)), _desc(G, (32, 0, 0), (64, 32, 32)), _desc(G, (0, 0, 0), (32, 32, 32))]
+    with pytest.raises(Exception) as e:
+        sortlast.SortLast(None, bad, 0)
+    assert "grid" in str(e.value)
+    good = [_desc(G, (0, 0, 0), (32, 32, 32)), _desc(G, (32, 0, 0), (64, 32, 32)), _desc(G, (0, 32, 0), (32, 64, 32)),
+            _desc(G, (32, 32, 0), (64, 64, 32))]
+    sl = sortlast.SortLast(None, good, 0)
+    assert sl.order(0) == [0, 2, 1, 3] or sl.order(0) == [0, 1, 2, 3]
+    assert sl.order(3)[0] == 3 and sl.order(3)[-1] == 0
+
+
 @pytest.mark.parametrize("n,axis", [(2, 1), (4, 1), (3, 2)])
 @pytest.mark.parametrize("mode", [render.COMPOSITE, render.ISOSURFACE])
 def test_lockstep_matches_single_texture_oracle(n, axis, mode):

@@ -54,6 +54,12 @@ _SIGS = {
     "vr_stream_open": (c_int, [c_char_p, POINTER(c_void_p)]),
     "vr_stream_save": (c_int, [c_void_p, c_char_p]),
     "vr_stream_destroy": (c_int, [c_void_p]),
+    "vr_stream_save_indexed": (c_int, [c_void_p, c_char_p]),
+    "vr_stream_open_indexed": (c_int, [c_char_p, c_void_p, c_int32, POINTER(c_void_p), POINTER(c_int64)]),
+    "vr_stream_from_memory_indexed": (c_int, [c_void_p, c_int64, c_void_p, c_int32, POINTER(c_void_p)]),
+    "vr_stream_serialize_indexed": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64)]),
+    "vr_stream_index_info": (c_int, [c_void_p, POINTER(c_int64)]),
+    "vr_stream_index_section": (c_int, [c_void_p, c_int32, POINTER(c_void_p), POINTER(c_int64)]),
     "vr_stream_get_header": (c_int, [c_void_p, POINTER(StreamHeader)]),
     "vr_stream_get_distance_map": (c_int, [c_void_p, c_void_p, c_int32]),
     "vr_stream_get_bits": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_int64)]),
@@ -96,6 +102,7 @@ _SIGS = {
     "vr_volume_occupancy_download": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, POINTER(c_int32)]),
     "vr_decode_plan_create": (c_int, [c_void_p, POINTER(c_void_p), c_int32, POINTER(c_int64), c_void_p, POINTER(c_void_p)]),
     "vr_decode_plan_run": (c_int, [c_void_p]),
+    "vr_decode_plan_run_tiles": (c_int, [c_void_p, c_void_p, POINTER(c_int64)]),
     "vr_decode_plan_destroy": (c_int, [c_void_p]),
     "vr_decode_plan_bytes": (c_int, [c_void_p, POINTER(c_int64)]),
     "vr_decode_plan_kernel": (c_int, [c_void_p, POINTER(c_int32)]),

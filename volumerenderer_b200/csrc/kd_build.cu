@@ -222,6 +222,75 @@ __global__ void pack_kernel(const uint8_t* sym, int64_t nSym, uint8_t* bits, int
   bits[j] = (uint8_t)b;
 }
 
+// ---- decode index from the producer's own offsets ("the index for free") ---------------------
+// The offsets of offset_level_kernel are exactly what the host walk of kd_stream.cpp (kd_prepare) recovers from the finished
+// stream; the decoded value of every node follows from the codes top-down.  val[i] = value levelCut carries at node i
+// (VolumeKdTree_recover.cpp:743,784-787); nodes under a pruned ancestor inherit the ancestor's value, which is what the
+// decode writes into their boxes (:759-766).
+__global__ void val_level_kernel(const uint8_t* codes, const uint32_t* off, uint8_t* val, int64_t start, int64_t n, int dist) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t i = start + k;
+  const int parent = val[(i - 1) >> 1];
+  val[i] = (uint8_t)(off[i] == KB_NOT_EMITTED ? parent : vr_apply(parent, codes[i], dist));
+}
+// final voxel values: the leaf's value with its refinement chain applied (:815-818 for depths > origTreeDepth)
+__global__ void final_kernel(const uint8_t* leafCode, const uint32_t* leafOff, const uint8_t* leafVal, const uint32_t* chain, Dist7 dist, uint8_t* fin,
+                             int64_t n) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int v = leafVal[i];
+  if (leafOff[i] != KB_NOT_EMITTED && leafCode[i] != 3) {
+    const uint32_t ch = chain[i], cnt = ch >> 16;
+    for (uint32_t q = 0; q < cnt; ++q) {
+      const int c = (int)((ch >> (2 * q)) & 3u);
+      if (c == 3) break;
+      v = vr_apply(v, c, dist.d[q]);
+    }
+  }
+  fin[i] = (uint8_t)v;
+}
+// one thread: tiles in path order, live tiles numbered as they come (kd_stream.cpp IndexVisitor::node)
+__global__ void index_tiles_kernel(const uint8_t* codes, const uint32_t* off, const uint8_t* val, int64_t firstTile, int64_t nTiles,
+                                   uint32_t* tileLeafBlock, uint32_t* tileBegin, uint8_t* tileVal, uint32_t* numLive) {
+  uint32_t live = 0;
+  for (int64_t t = 0; t < nTiles; ++t) {
+    const int64_t i = firstTile + t;
+    const bool isLive = off[i] != KB_NOT_EMITTED && codes[i] != 3;
+    tileLeafBlock[t] = isLive ? live++ : VR_PRUNED;
+    tileBegin[t] = isLive ? off[i] : 0u;
+    tileVal[t] = isLive ? (uint8_t)0 : val[i];
+  }
+  *numLive = live;
+}
+__global__ void index_leaves_kernel(const uint8_t* codes, const uint32_t* off, const uint8_t* val, int64_t firstLeafNode, int64_t nLeafNodes,
+                                    int lptLog2, const uint32_t* tileLeafBlock, uint32_t* leafOff, uint8_t* leafVal) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= nLeafNodes) return;
+  const uint32_t blk = tileLeafBlock[k >> lptLog2];
+  if (blk == VR_PRUNED) return;
+  const int64_t j = firstLeafNode + k;
+  const int64_t o = ((int64_t)blk << lptLog2) + (k & ((int64_t(1) << lptLog2) - 1));
+  const bool em = off[j] != KB_NOT_EMITTED && codes[j] != 3;
+  leafOff[o] = em ? off[j] : VR_PRUNED;
+  leafVal[o] = val[j];
+}
+// exact bounds of the decoded voxels of every tile: one CTA per tile
+__global__ void tile_bounds_kernel(const uint8_t* fin, int tileBits, uint8_t* tileMin, uint8_t* tileMax) {
+  __shared__ uint32_t smn[TB / 32], smx[TB / 32];
+  const int64_t base = (int64_t)blockIdx.x << tileBits, cnt = int64_t(1) << tileBits;
+  uint32_t mn = 255, mx = 0;
+  for (int64_t i = threadIdx.x; i < cnt; i += blockDim.x) { const uint32_t v = fin[base + i]; mn = min(mn, v); mx = max(mx, v); }
+  mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+  mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+  if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < TB / 32; ++w) { mn = min(mn, smn[w]); mx = max(mx, smx[w]); }
+    tileMin[blockIdx.x] = (uint8_t)mn; tileMax[blockIdx.x] = (uint8_t)mx;
+  }
+}
+
 inline unsigned grid_for(int64_t n) { return (unsigned)((n + TB - 1) / TB); }
 
 }  // namespace
@@ -239,11 +308,14 @@ struct KdBuilder {
   int64_t capSym = 0;
   void* cubTemp = nullptr;
   size_t cubBytes = 0;
+  uint8_t* idxTiles = nullptr;    // per tile: tileLeafBlock u32 | tileBegin u32 | tileVal | tileMin | tileMax
+  int64_t capTiles = 0;
   double* scalarsDev = nullptr;   // 8 doubles / counters
   double* scalarsHost = nullptr;  // pinned mirror
   void release() {
     for (void* p : {(void*)temp, (void*)mn, (void*)mx, (void*)codes, (void*)lvl[0], (void*)lvl[1], (void*)lvl[2], (void*)items, (void*)prefix,
-                    (void*)dec, (void*)blockSum, (void*)superSum, (void*)chain, (void*)sym, (void*)bits, cubTemp, (void*)scalarsDev})
+                    (void*)dec, (void*)blockSum, (void*)superSum, (void*)chain, (void*)sym, (void*)bits, cubTemp, (void*)scalarsDev,
+                    (void*)idxTiles})
       if (p) cudaFree(p);
     if (scalarsHost) cudaFreeHost(scalarsHost);
     *this = KdBuilder();
@@ -290,7 +362,7 @@ cudaError_t fetch(KdBuilder* b, int k, cudaStream_t s) {
 
 int kd_build_device(KdBuilder* b, const uint8_t* volDev, int64_t X, int64_t Y, int64_t Z, int64_t rowPitch, int64_t slicePitch,
                     int tolerance, int maxEpochs, cudaStream_t stream, KdStream* out, KdBuildStats* stats, cudaError_t* errOut,
-                    int64_t* iterStats) {
+                    int64_t* iterStats, bool withIndex) {
   cudaError_t err = cudaSuccess;
   struct ErrGuard { cudaError_t& e; cudaError_t* o; ~ErrGuard() { if (o) *o = e; } } guard{err, errOut};
   if (!b || !volDev || !out) return VR_ERR_ARG;
@@ -470,6 +542,56 @@ int kd_build_device(KdBuilder* b, const uint8_t* volDev, int64_t X, int64_t Y, i
   pack_kernel<<<grid_for(nBytes), TB, 0, stream>>>(b->sym, numActive, b->bits, nBytes);
   KB_CHECK(cudaGetLastError());
 
+  // ---- decode index (kd_stream.h KdIndex) from the offsets above: no walk of the finished stream ----
+  KdIndex ix;
+  const bool emitIndex = withIndex && numActive < (int64_t)VR_PRUNED;
+  if (emitIndex) {
+    const int64_t nTiles = int64_t(1) << g.Dt, nLeafNodes = int64_t(1) << g.Dl;
+    const int lptLog2 = g.tileBits - g.leafBits;
+    if (nTiles > b->capTiles) {
+      if (b->idxTiles) cudaFree(b->idxTiles);
+      b->idxTiles = nullptr; b->capTiles = 0;
+      KB_CHECK(cudaMalloc((void**)&b->idxTiles, (size_t)nTiles * 11 + 64));
+      b->capTiles = nTiles;
+    }
+    uint32_t* tileLeafBlockDev = reinterpret_cast<uint32_t*>(b->idxTiles);
+    uint32_t* tileBeginDev = tileLeafBlockDev + nTiles;
+    uint8_t *tileValDev = b->idxTiles + 8 * nTiles, *tileMinDev = tileValDev + nTiles, *tileMaxDev = tileMinDev + nTiles;
+    uint8_t *val = b->mn, *fin = b->mx;  // the pyramid's min / max arrays are free by now
+    uint32_t* leafOffDev = b->chain;     // read by final_kernel first, then overwritten (stream order)
+    uint8_t* leafValDev = b->dec;
+    uint32_t* numLiveDev = reinterpret_cast<uint32_t*>(b->scalarsDev);
+    KB_CHECK(cudaMemcpyAsync(val, distanceMap.data(), 1, cudaMemcpyHostToDevice, stream));  // root = distanceMap[0] (:743)
+    for (int d = 1; d <= D0; ++d) {
+      const int64_t n = int64_t(1) << d;
+      val_level_kernel<<<grid_for(n), TB, 0, stream>>>(b->codes, off, val, n - 1, n, (int)distanceMap[(size_t)d]);
+    }
+    final_kernel<<<grid_for(numLeaves), TB, 0, stream>>>(leafCode, off + firstLeaf, val + firstLeaf, b->chain, dist7, fin, numLeaves);
+    index_tiles_kernel<<<1, 1, 0, stream>>>(b->codes, off, val, nTiles - 1, nTiles, tileLeafBlockDev, tileBeginDev, tileValDev, numLiveDev);
+    tile_bounds_kernel<<<(unsigned)nTiles, TB, 0, stream>>>(fin, g.tileBits, tileMinDev, tileMaxDev);
+    index_leaves_kernel<<<grid_for(nLeafNodes), TB, 0, stream>>>(b->codes, off, val, nLeafNodes - 1, nLeafNodes, lptLog2, tileLeafBlockDev, leafOffDev,
+                                                                 leafValDev);
+    KB_CHECK(cudaGetLastError());
+    std::vector<uint32_t> tileBegin((size_t)nTiles);
+    ix.tileLeafBlock.resize((size_t)nTiles); ix.tileVal.resize((size_t)nTiles); ix.tileMin.resize((size_t)nTiles); ix.tileMax.resize((size_t)nTiles);
+    KB_CHECK(cudaMemcpyAsync(ix.tileLeafBlock.data(), tileLeafBlockDev, (size_t)nTiles * 4, cudaMemcpyDeviceToHost, stream));
+    KB_CHECK(cudaMemcpyAsync(tileBegin.data(), tileBeginDev, (size_t)nTiles * 4, cudaMemcpyDeviceToHost, stream));
+    KB_CHECK(cudaMemcpyAsync(ix.tileVal.data(), tileValDev, (size_t)nTiles, cudaMemcpyDeviceToHost, stream));
+    KB_CHECK(cudaMemcpyAsync(ix.tileMin.data(), tileMinDev, (size_t)nTiles, cudaMemcpyDeviceToHost, stream));
+    KB_CHECK(cudaMemcpyAsync(ix.tileMax.data(), tileMaxDev, (size_t)nTiles, cudaMemcpyDeviceToHost, stream));
+    KB_CHECK(fetch(b, 1, stream));
+    uint32_t numLive;
+    std::memcpy(&numLive, b->scalarsHost, sizeof(numLive));
+    const size_t nLeafEntries = (size_t)numLive << lptLog2;
+    ix.leafOff.resize(nLeafEntries); ix.leafVal.resize(nLeafEntries);
+    if (nLeafEntries) {
+      KB_CHECK(cudaMemcpyAsync(ix.leafOff.data(), leafOffDev, nLeafEntries * 4, cudaMemcpyDeviceToHost, stream));
+      KB_CHECK(cudaMemcpyAsync(ix.leafVal.data(), leafValDev, nLeafEntries, cudaMemcpyDeviceToHost, stream));
+      KB_CHECK(cudaStreamSynchronize(stream));
+    }
+    kd_index_finish(g, tileBegin, numActive, &ix);
+  }
+
   if (stats) {
     KB_CHECK(cudaMemsetAsync(b->scalarsDev + 5, 0, 3 * sizeof(double), stream));
     leaf_err_kernel<<<grid_for(numLeaves), TB, 0, stream>>>(leafTruth, recon, numLeaves, maxErrDev, sumsDev, sumsDev + 1);
@@ -499,6 +621,7 @@ int kd_build_device(KdBuilder* b, const uint8_t* volDev, int64_t X, int64_t Y, i
   KB_CHECK(cudaMemcpyAsync(s.bits.data(), b->bits, (size_t)nBytes, cudaMemcpyDeviceToHost, stream));
   KB_CHECK(cudaStreamSynchronize(stream));
   if (iterStats) { iterStats[0] = itTotal; iterStats[1] = itWorst; }
+  if (emitIndex) s.index = std::move(ix);
   *out = std::move(s);
   return VR_OK;
 }

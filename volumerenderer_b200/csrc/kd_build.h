@@ -16,8 +16,10 @@ void kd_builder_destroy(KdBuilder* b);
 // pitch `rowPitch` and slice pitch `slicePitch` (a tight brick: X and X*Y).  Synchronises `stream` several times
 // per level (the gradient descent branches on the level's error).  *err receives the CUDA error on VR_ERR_CUDA.
 // iterStats (optional, 2 entries): scan iterations of the running-mean fixed point (total, worst level).
+// withIndex: also emit out->index (the decode index of kd_prepare, byte for byte) from the producer's own symbol offsets, so
+// the finished stream is never walked on the host.
 int kd_build_device(KdBuilder* b, const uint8_t* volDev, int64_t X, int64_t Y, int64_t Z, int64_t rowPitch, int64_t slicePitch,
                     int tolerance, int maxEpochs, cudaStream_t stream, KdStream* out, KdBuildStats* stats, cudaError_t* err,
-                    int64_t* iterStats);
+                    int64_t* iterStats, bool withIndex = true);
 
 }  // namespace vr

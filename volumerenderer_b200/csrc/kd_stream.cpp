@@ -9,7 +9,7 @@
 
 namespace vr {
 
-static int check_header(const vr_kd_header& h, vr_kd_geom* g) {
+int kd_check_header(const vr_kd_header& h, vr_kd_geom* g) {
   if (h.X <= 0 || h.Y <= 0 || h.Z <= 0 || h.numActiveNodes <= 0) return VR_ERR_FORMAT;
   if (vr_kd_make_geom(h.X, h.Y, h.Z, g) != 0) return VR_ERR_FORMAT;
   if (h.origTreeDepth != g->D0 || h.maxTreeDepth != g->Dmax) return VR_ERR_FORMAT;
@@ -23,7 +23,7 @@ int kd_from_memory(const vr_kd_header* hdr, const uint8_t* distanceMap, const ui
                    int64_t nbytes, KdStream* out) {
   if (!hdr || !distanceMap || !bits || !out) return VR_ERR_ARG;
   vr_kd_geom g;
-  int rc = check_header(*hdr, &g);
+  int rc = kd_check_header(*hdr, &g);
   if (rc != VR_OK) return rc;
   int64_t need = (hdr->numActiveNodes + 3) / 4;
   if (nbytes < need) return VR_ERR_FORMAT;  // longer is fine: open() of the reference over-sizes by 8
@@ -62,6 +62,7 @@ int kd_open(const char* path, KdStream* out) {
 int kd_save(const KdStream& s, const char* path) {
   if (!path) return VR_ERR_ARG;
   if (s.bits.empty()) return VR_ERR_STATE;  // "ERROR! No tree to save." (:527-531)
+  if (!s.residentTiles.empty()) return VR_ERR_STATE;  // opened with a tile subset: not the whole stream
   FILE* f = std::fopen(path, "wb");
   if (!f) return VR_ERR_IO;
   size_t ok = std::fwrite(&s.hdr, sizeof(s.hdr), 1, f);
@@ -175,14 +176,46 @@ struct IndexVisitor {
 };
 }  // namespace
 
+// longest parser segment: distance between successive live leaf offsets / block ends
+static void finish_segments(const vr_kd_geom& g, KdIndex* ixp) {
+  KdIndex& ix = *ixp;
+  ix.numLiveTiles = (int64_t)ix.blockSymBegin.size();
+  int64_t maxSeg = 0;
+  const uint32_t lpt = 1u << (g.tileBits - g.leafBits);
+  for (int64_t b = 0; b < ix.numLiveTiles; ++b) {
+    int64_t prev = -1;
+    for (uint32_t l = 0; l < lpt; ++l) {
+      uint32_t o = ix.leafOff[b * lpt + l];
+      if (o == VR_PRUNED) continue;
+      if (prev >= 0 && (int64_t)o - prev > maxSeg) maxSeg = (int64_t)o - prev;
+      prev = o;
+    }
+    if (prev >= 0 && (int64_t)ix.blockSymEnd[b] - prev > maxSeg) maxSeg = (int64_t)ix.blockSymEnd[b] - prev;
+  }
+  ix.maxSymbolsPerLeaf = maxSeg;
+}
+
+void kd_index_finish(const vr_kd_geom& g, const std::vector<uint32_t>& tileBegin, int64_t numActiveNodes, KdIndex* ix) {
+  ix->blockSymBegin.clear();
+  ix->blockSymEnd.clear();
+  for (size_t t = 0; t < ix->tileLeafBlock.size(); ++t) {  // blocks are numbered in path order
+    if (ix->tileLeafBlock[t] == VR_PRUNED) continue;
+    if (!ix->blockSymBegin.empty()) ix->blockSymEnd.push_back(tileBegin[t]);
+    ix->blockSymBegin.push_back(tileBegin[t]);
+  }
+  if (!ix->blockSymBegin.empty()) ix->blockSymEnd.push_back((uint32_t)numActiveNodes);
+  finish_segments(g, ix);
+  ix->built = true;
+}
+
 int kd_validate(const KdStream& s, int64_t* nodesConsumed) {
-  if (s.bits.empty()) return VR_ERR_STATE;
+  if (s.bits.empty() || !s.residentTiles.empty()) return VR_ERR_STATE;
   CountVisitor cv;
   return walk(s, cv, nodesConsumed);
 }
 
 int kd_prepare(KdStream* s) {
-  if (!s || s->bits.empty()) return VR_ERR_STATE;
+  if (!s || s->bits.empty() || !s->residentTiles.empty()) return VR_ERR_STATE;
   if (s->hdr.numActiveNodes >= (int64_t)VR_PRUNED) return VR_ERR_UNSUPPORTED;
   const vr_kd_geom& g = s->geom;
   KdIndex ix;
@@ -196,21 +229,7 @@ int kd_prepare(KdStream* s) {
   int rc = walk(*s, iv, &consumed);
   if (rc != VR_OK) return rc;
   if (iv.curBlock >= 0) ix.blockSymEnd.push_back((uint32_t)consumed);
-  ix.numLiveTiles = (int64_t)ix.blockSymBegin.size();
-  // longest parser segment: distance between successive live leaf offsets / block ends
-  int64_t maxSeg = 0;
-  const uint32_t lpt = iv.leavesPerTile;
-  for (int64_t b = 0; b < ix.numLiveTiles; ++b) {
-    int64_t prev = -1;
-    for (uint32_t l = 0; l < lpt; ++l) {
-      uint32_t o = ix.leafOff[b * lpt + l];
-      if (o == VR_PRUNED) continue;
-      if (prev >= 0 && (int64_t)o - prev > maxSeg) maxSeg = (int64_t)o - prev;
-      prev = o;
-    }
-    if (prev >= 0 && (int64_t)ix.blockSymEnd[b] - prev > maxSeg) maxSeg = (int64_t)ix.blockSymEnd[b] - prev;
-  }
-  ix.maxSymbolsPerLeaf = maxSeg;
+  finish_segments(g, &ix);
   ix.built = true;
   s->index = std::move(ix);
   return VR_OK;

@@ -38,6 +38,9 @@ struct KdStream {
   std::vector<uint8_t> bits;         // ceil(numActiveNodes/4) bytes (trailing slack tolerated)
   vr_kd_geom geom{};
   KdIndex index;
+  // Indexed container opened with a tile subset (kd_kdx.cpp): residentTiles[t] != 0 -> the symbols of tile t are in
+  // `bits`; the rest of `bits` is zero.  Empty = the whole stream is resident (every other way of making a stream).
+  std::vector<uint8_t> residentTiles;
 
   int64_t voxels() const { return hdr.X * hdr.Y * hdr.Z; }
   int64_t streamBytes() const { return (hdr.numActiveNodes + 3) / 4; }
@@ -65,6 +68,19 @@ int kd_validate(const KdStream& s, int64_t* nodesConsumed);
 
 // Builds s->index (sequential walk, O(numActiveNodes)).
 int kd_prepare(KdStream* s);
+// Derives blockSymBegin / blockSymEnd / numLiveTiles / maxSymbolsPerLeaf from tileLeafBlock + leafOff (what kd_prepare does
+// after its walk); `tileBegin[t]` = symbol offset of live tile t.  Used by producers that know the offsets already.
+void kd_index_finish(const vr_kd_geom& g, const std::vector<uint32_t>& tileBegin, int64_t numActiveNodes, KdIndex* ix);
+int kd_check_header(const vr_kd_header& h, vr_kd_geom* g);
+
+// Indexed ("random-access") container, SURVEY 8f-4 -- what HashedKdtree.cpp:96-214,406-507 was reaching for: the stream
+// plus its decode index and exact per-tile bounds in one deterministic file, so that opening needs no walk of the stream
+// and single tiles can be fetched from disk.  Layout in kd_kdx.cpp.
+int kdx_serialize(KdStream* s, std::vector<uint8_t>* out);  // prepares the index if needed
+int kdx_save(KdStream* s, const char* path);
+// tileMask (optional, 2^Dt bytes): read only the stream bytes of these tiles.  verify: check the stream checksum (full opens only).
+int kdx_from_memory(const uint8_t* buf, int64_t nbytes, const uint8_t* tileMask, bool verify, KdStream* out);
+int kdx_open(const char* path, const uint8_t* tileMask, bool verify, KdStream* out, int64_t* bytesRead);
 
 // CPU compressor: the reference's build() algorithm (VolumeKdTree_recover.cpp:17-140) restated;
 // produces byte-identical streams.  `volume` is not modified (the reference empties its input).

@@ -59,6 +59,7 @@ int vr_context_destroy(vr_context* c) {
   if (c->side.fork) cudaEventDestroy(c->side.fork);
   if (c->side.join) cudaEventDestroy(c->side.join);
   vr::kd_builder_destroy(c->builder);
+  cudaFree(c->frameDev); cudaFree(c->frameHitDev); cudaFree(c->frameCountDev);
   delete c;
   return VR_OK;
 }
@@ -136,6 +137,79 @@ int vr_stream_save(const vr_stream* s, const char* path) {
   int rc = kd_save(s->kd, path);
   return rc == VR_OK ? VR_OK : fail(rc, "vr_stream_save failed (no tree to save, or I/O error)");
 }
+// ---- indexed container (kd_kdx.cpp) ----------------------------------------------------------------
+int vr_stream_save_indexed(vr_stream* s, const char* path) {
+  if (!s || !path) return fail(VR_ERR_ARG, "vr_stream_save_indexed: null argument");
+  int rc = kdx_save(&s->kd, path);
+  return rc == VR_OK ? VR_OK : fail(rc, "vr_stream_save_indexed failed (no tree, tile subset, stream does not parse, or I/O error)");
+}
+int vr_stream_serialize_indexed(vr_stream* s, uint8_t* out, int64_t cap, int64_t* nbytes) {
+  if (!s || !nbytes) return fail(VR_ERR_ARG, "vr_stream_serialize_indexed: null argument");
+  std::vector<uint8_t> buf;
+  int rc = kdx_serialize(&s->kd, &buf);
+  if (rc != VR_OK) return fail(rc, "vr_stream_serialize_indexed failed");
+  *nbytes = (int64_t)buf.size();
+  if (!out) return VR_OK;
+  if (cap < (int64_t)buf.size()) return fail(VR_ERR_ARG, "vr_stream_serialize_indexed: buffer too small");
+  std::memcpy(out, buf.data(), buf.size());
+  return VR_OK;
+}
+static int kdx_fail(int rc) {
+  return fail(rc, rc == VR_ERR_IO ? "indexed container missing or truncated" : "bad indexed container (magic, geometry, index or checksum)");
+}
+int vr_stream_open_indexed(const char* path, const uint8_t* tile_mask, int32_t verify, vr_stream** out, int64_t* bytes_read) {
+  if (!path || !out) return fail(VR_ERR_ARG, "vr_stream_open_indexed: null argument");
+  vr_stream* s = new vr_stream;
+  int rc = kdx_open(path, tile_mask, verify != 0, &s->kd, bytes_read);
+  if (rc != VR_OK) { delete s; return kdx_fail(rc); }
+  *out = s;
+  return VR_OK;
+}
+int vr_stream_from_memory_indexed(const uint8_t* image, int64_t nbytes, const uint8_t* tile_mask, int32_t verify, vr_stream** out) {
+  if (!image || !out) return fail(VR_ERR_ARG, "vr_stream_from_memory_indexed: null argument");
+  vr_stream* s = new vr_stream;
+  int rc = kdx_from_memory(image, nbytes, tile_mask, verify != 0, &s->kd);
+  if (rc != VR_OK) { delete s; return kdx_fail(rc); }
+  *out = s;
+  return VR_OK;
+}
+static int ensure_index(vr_stream* s) {
+  if (s->kd.index.built) return VR_OK;
+  int rc = kd_prepare(&s->kd);
+  return rc == VR_OK ? VR_OK : fail(rc, "stream does not parse");
+}
+int vr_stream_index_info(vr_stream* s, int64_t out[6]) {
+  if (!s || !out) return fail(VR_ERR_ARG, "vr_stream_index_info: null argument");
+  int rc = ensure_index(s);
+  if (rc != VR_OK) return rc;
+  const KdIndex& ix = s->kd.index;
+  out[0] = (int64_t)ix.tileLeafBlock.size();
+  out[1] = ix.numLiveTiles;
+  out[2] = int64_t(1) << (s->kd.geom.tileBits - s->kd.geom.leafBits);
+  out[3] = s->kd.residentTiles.empty() ? 0 : 1;
+  out[4] = (int64_t)(ix.tileLeafBlock.size() * 7 + ix.blockSymBegin.size() * 8 + ix.leafOff.size() * 5);
+  out[5] = ix.maxSymbolsPerLeaf;
+  return VR_OK;
+}
+int vr_stream_index_section(vr_stream* s, int32_t which, const void** data, int64_t* nbytes) {
+  if (!s || !data || !nbytes) return fail(VR_ERR_ARG, "vr_stream_index_section: null argument");
+  int rc = ensure_index(s);
+  if (rc != VR_OK) return rc;
+  const KdIndex& ix = s->kd.index;
+  switch (which) {
+    case 1: *data = ix.tileLeafBlock.data(); *nbytes = (int64_t)ix.tileLeafBlock.size() * 4; break;
+    case 2: *data = ix.tileVal.data(); *nbytes = (int64_t)ix.tileVal.size(); break;
+    case 3: *data = ix.tileMin.data(); *nbytes = (int64_t)ix.tileMin.size(); break;
+    case 4: *data = ix.tileMax.data(); *nbytes = (int64_t)ix.tileMax.size(); break;
+    case 5: *data = ix.blockSymBegin.data(); *nbytes = (int64_t)ix.blockSymBegin.size() * 4; break;
+    case 6: *data = ix.blockSymEnd.data(); *nbytes = (int64_t)ix.blockSymEnd.size() * 4; break;
+    case 7: *data = ix.leafOff.data(); *nbytes = (int64_t)ix.leafOff.size() * 4; break;
+    case 8: *data = ix.leafVal.data(); *nbytes = (int64_t)ix.leafVal.size(); break;
+    default: return fail(VR_ERR_ARG, "vr_stream_index_section: sections are numbered 1..8");
+  }
+  return VR_OK;
+}
+
 int vr_stream_destroy(vr_stream* s) {
   if (!s) return VR_OK;
   s->release();

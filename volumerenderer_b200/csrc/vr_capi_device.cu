@@ -175,17 +175,18 @@ int vr_volume_upload_brick(vr_context* ctx, vr_volume* v, const uint8_t* brick, 
 }  // extern "C"
 
 // ---- stage 1: decode plans ----------------------------------------------------------------------------
-void vr_decode_plan::lazy_free() {
-  if (lazy.workDev || lazy.fillJobsDev || lazy.occSetDev || lazy.solidDev || lazy.parseDev) cudaSetDevice(device);
-  cudaFree(lazy.workDev); cudaFree(lazy.fillJobsDev); cudaFree(lazy.occSetDev); cudaFree(lazy.solidDev); cudaFree(lazy.parseDev);
-  lazy = Lazy();
+void vr_decode_plan::lazy_free(Lazy* which) {
+  Lazy& lz = which ? *which : lazy;
+  if (lz.workDev || lz.fillJobsDev || lz.occSetDev || lz.solidDev || lz.parseDev) cudaSetDevice(device);
+  cudaFree(lz.workDev); cudaFree(lz.fillJobsDev); cudaFree(lz.occSetDev); cudaFree(lz.solidDev); cudaFree(lz.parseDev);
+  lz = Lazy();
 }
 
 // Debug knobs (vr_debug_set): explicit, process-wide, read when a plan is created / run.  Nothing in the library reads the
 // environment.  decode_kernel: 0 = persistent kernel where the brick shape allows it (default), 1 = classic kernel always.
 // decode_only: 0 = everything, 1 = parse tiles only, 2 = constant groups only (timing probes: the slab is then incomplete).
 namespace {
-struct DebugKnobs { int decodeKernel = 0, decodeOnly = 0, fillAttach = 2, fillMode = 2, tmaRows = 8, parseOrder = 0, unitStore = 0, decodeSplit = 0; } g_dbg;
+struct DebugKnobs { int decodeKernel = 0, decodeOnly = 0, fillAttach = 2, fillMode = 2, tmaRows = 8, parseOrder = 0, unitStore = 0, decodeSplit = 0, producerIndex = 1; } g_dbg;
 }
 extern "C" int vr_debug_set(const char* key, int value) {
   if (!key) return fail(VR_ERR_ARG, "vr_debug_set: null key");
@@ -198,6 +199,7 @@ extern "C" int vr_debug_set(const char* key, int value) {
   else if (k == "parse_order") g_dbg.parseOrder = value;
   else if (k == "unit_store") g_dbg.unitStore = value;  // 0 / 1 = one tensor store per unit (default), 2 = 16-byte stores of the lanes
   else if (k == "decode_split") g_dbg.decodeSplit = value;  // 1: constant groups as a kernel of their own on a side stream
+  else if (k == "producer_index") g_dbg.producerIndex = value;  // 0: vr_kd_compress_device leaves the index to the host walk
   else if (k == "count_fetched") vr::g_count_fetched = value;  // samples_dev counts fetching march steps only (plain march)
   else if (k == "read_partial") g_read_partial = value;  // vr_volume_download of a partially decoded volume (tests)
   else return fail(VR_ERR_ARG, "vr_debug_set: unknown key");
@@ -214,6 +216,7 @@ extern "C" int vr_debug_get(const char* key, int* value) {
   else if (k == "parse_order") *value = g_dbg.parseOrder;
   else if (k == "unit_store") *value = g_dbg.unitStore;
   else if (k == "decode_split") *value = g_dbg.decodeSplit;
+  else if (k == "producer_index") *value = g_dbg.producerIndex;
   else if (k == "count_fetched") *value = vr::g_count_fetched;
   else if (k == "read_partial") *value = g_read_partial;
   else return fail(VR_ERR_ARG, "vr_debug_get: unknown key");
@@ -304,28 +307,23 @@ static cudaError_t plan_launch(vr_decode_plan* p, const vr_parse_item* parseDev,
                           occ ? p->tileCellDev : nullptr, fillsDev);
 }
 
-int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], const int stepReach[3]) {
-  vr_decode_plan::Lazy& lz = p->lazy;
-  if (lz.built && lz.mode == mode && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2] &&
-      lz.stepReach[0] == stepReach[0] && lz.stepReach[1] == stepReach[1] && lz.stepReach[2] == stepReach[2])
-    return VR_OK;
-  if (!p->occFused) return fail(VR_ERR_STATE, "lazy decode needs tiles that coincide with occupancy cells");
-  p->lazy_free();
+// Work lists of the tiles in `needed` (n * 2^Dt bytes) plus the (cell, max) pairs of the others, into *lzp.
+// Streams opened with a tile subset (kd_kdx.cpp) must hold every live tile the lists parse.
+static int plan_build_culled(vr_decode_plan* p, const uint8_t* neededPtr, const std::vector<uint8_t>& solid, vr_decode_plan::Lazy* lzp) {
+  vr_decode_plan::Lazy& lz = *lzp;
   const vr_kd_geom& g = p->geom;
-  const vr_volume* d = p->dst;
   const uint32_t nt = 1u << g.Dt;
   const int n = p->n;
   std::vector<const KdIndex*> idx((size_t)n);
   for (int i = 0; i < n; ++i) idx[(size_t)i] = &p->streams[(size_t)i]->kd.index;
-  CullGrid cg;
-  for (int a = 0; a < 3; ++a) cg.nc[a] = d->nc[a];
-  cg.lg[0] = VR_OCC_LX; cg.lg[1] = VR_OCC_LY; cg.lg[2] = VR_OCC_LZ;
-  std::vector<uint8_t> needed((size_t)n * nt);
-  const std::vector<int64_t>& ob = p->occBase;
-  const std::vector<int32_t>& tc = p->tileCellHost;
-  std::vector<uint8_t> solid;
-  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, mode, thr,
-             reach, stepReach, needed.data(), &solid);
+  for (int b = 0; b < n; ++b) {
+    const std::vector<uint8_t>& res = p->streams[(size_t)b]->kd.residentTiles;
+    if (res.empty()) continue;
+    for (uint32_t t = 0; t < nt; ++t)
+      if (neededPtr[(size_t)b * nt + t] && !res[t] && idx[(size_t)b]->tileLeafBlock[t] != VR_PRUNED)
+        return fail(VR_ERR_STATE, "a tile this launch must parse is not resident (stream opened with a tile subset)");
+  }
+  struct NeededView { const uint8_t* p; const uint8_t* data() const { return p; } const uint8_t& operator[](size_t i) const { return p[i]; } } needed{neededPtr};
   if (cudaSetDevice(p->ctx->device) != cudaSuccess) return fail(VR_ERR_CUDA, "cudaSetDevice");
   std::vector<vr_occ_set> culled;
   int rc = plan_build_lists(p, needed.data(), &culled, &lz.parseDev, &lz.nParse, &lz.workDev, &lz.nWork, &lz.fillJobsDev, &lz.nFill, &lz.tmaOut);
@@ -352,7 +350,34 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
     e = cudaMalloc((void**)&lz.solidDev, solid.size());
     if (e == cudaSuccess) e = cudaMemcpy(lz.solidDev, solid.data(), solid.size(), cudaMemcpyHostToDevice);
   }
-  if (e != cudaSuccess) { p->lazy_free(); return fail_cuda(e, "upload lazy work list"); }
+  if (e != cudaSuccess) { p->lazy_free(&lz); return fail_cuda(e, "upload lazy work list"); }
+  return VR_OK;
+}
+
+int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], const int stepReach[3]) {
+  vr_decode_plan::Lazy& lz = p->lazy;
+  if (lz.built && lz.mode == mode && lz.thr == thr && lz.reach[0] == reach[0] && lz.reach[1] == reach[1] && lz.reach[2] == reach[2] &&
+      lz.stepReach[0] == stepReach[0] && lz.stepReach[1] == stepReach[1] && lz.stepReach[2] == stepReach[2])
+    return VR_OK;
+  if (!p->occFused) return fail(VR_ERR_STATE, "lazy decode needs tiles that coincide with occupancy cells");
+  p->lazy_free();
+  const vr_kd_geom& g = p->geom;
+  const vr_volume* d = p->dst;
+  const uint32_t nt = 1u << g.Dt;
+  const int n = p->n;
+  std::vector<const KdIndex*> idx((size_t)n);
+  for (int i = 0; i < n; ++i) idx[(size_t)i] = &p->streams[(size_t)i]->kd.index;
+  CullGrid cg;
+  for (int a = 0; a < 3; ++a) cg.nc[a] = d->nc[a];
+  cg.lg[0] = VR_OCC_LX; cg.lg[1] = VR_OCC_LY; cg.lg[2] = VR_OCC_LZ;
+  std::vector<uint8_t> needed((size_t)n * nt);
+  const std::vector<int64_t>& ob = p->occBase;
+  const std::vector<int32_t>& tc = p->tileCellHost;
+  std::vector<uint8_t> solid;
+  cull_tiles(cg, n, nt, idx.data(), [&](int b, uint32_t t) -> int64_t { return ob[(size_t)b] < 0 ? -1 : ob[(size_t)b] + tc[t]; }, mode, thr,
+             reach, stepReach, needed.data(), &solid);
+  int rc = plan_build_culled(p, needed.data(), solid, &lz);
+  if (rc != VR_OK) return rc;
   lz.mode = mode; lz.thr = thr;
   for (int a = 0; a < 3; ++a) { lz.reach[a] = reach[a]; lz.stepReach[a] = stepReach[a]; }
   lz.built = true;
@@ -360,8 +385,8 @@ int plan_lazy_prepare(vr_decode_plan* p, int mode, int thr, const int reach[3], 
 }
 
 // One lazy pass: decode what the frame can read, record the maxima of the rest.
-int plan_lazy_run(vr_decode_plan* p) {
-  vr_decode_plan::Lazy& lz = p->lazy;
+int plan_lazy_run(vr_decode_plan* p, vr_decode_plan::Lazy* which) {
+  vr_decode_plan::Lazy& lz = which ? *which : p->lazy;
   vr_volume* d = p->dst;
   if (!lz.built) return fail(VR_ERR_STATE, "lazy work list not built");
   if (!(d->occRaw && d->occEpoch == p->occEpoch && d->skipping)) return fail(VR_ERR_STATE, "occupancy grid of the destination changed");
@@ -478,11 +503,28 @@ int vr_decode_plan_run(vr_decode_plan* p) {
   if (!p->dst) return fail(VR_ERR_STATE, "vr_decode_plan_run: the plan's destination volume was destroyed");
   CU(cudaSetDevice(p->ctx->device));
   vr_volume* d = p->dst;
+  for (const vr_stream* s : p->streams)
+    if (!s->kd.residentTiles.empty())
+      return fail(VR_ERR_STATE, "vr_decode_plan_run: a stream holds a tile subset only (vr_stream_open_indexed with a mask); use vr_decode_plan_run_tiles");
   const bool occ = p->occFused && d->occRaw && d->occEpoch == p->occEpoch && d->skipping;
   CU(plan_launch(p, p->parseDev, p->nParse, p->workDev, p->nWork, p->fillJobsDev, p->nFill, occ, g_dbg.decodeOnly, p->tmaOut));
   if (occ) d->occDilDirty = true;  // cells of the decoded bricks are current; validity of the rest is unchanged
   else d->occValid = false;
   d->partial.erase(p);  // every tile of the plan holds its voxels again
+  return VR_OK;
+}
+int vr_decode_plan_run_tiles(vr_decode_plan* p, const uint8_t* needed, int64_t stats[4]) {
+  if (!p || !needed) return fail(VR_ERR_ARG, "vr_decode_plan_run_tiles: null argument");
+  if (!p->dst) return fail(VR_ERR_STATE, "vr_decode_plan_run_tiles: the plan's destination volume was destroyed");
+  if (!p->occFused) return fail(VR_ERR_STATE, "vr_decode_plan_run_tiles needs 32x32x16 tiles that coincide with the destination's occupancy cells");
+  CU(cudaSetDevice(p->ctx->device));
+  p->lazy_free(&p->subset);
+  int rc = plan_build_culled(p, needed, std::vector<uint8_t>(), &p->subset);
+  if (rc != VR_OK) return rc;
+  p->subset.built = true;
+  rc = plan_lazy_run(p, &p->subset);
+  if (rc != VR_OK) return rc;
+  if (stats) { stats[0] = p->subset.tilesTotal; stats[1] = p->subset.tilesWritten; stats[2] = p->subset.bytesVoxels; stats[3] = p->subset.bytesStream; }
   return VR_OK;
 }
 int vr_decode_plan_destroy(vr_decode_plan* p) {
@@ -495,6 +537,7 @@ int vr_decode_plan_destroy(vr_decode_plan* p) {
   cudaFree(p->tileCellDev);
   cudaFree(p->queueDev);
   p->lazy_free();
+  p->lazy_free(&p->subset);
   if (p->dst) {
     if (p->dst->partial.erase(p)) p->dst->partialOrphan = true;  // its stale tiles stay stale
     p->dst->plans.erase(p);
@@ -540,7 +583,7 @@ static int build_common(vr_context* ctx, const uint8_t* volDev, int64_t X, int64
   vr_stream* s = new vr_stream;
   KdBuildStats st;
   cudaError_t ce = cudaSuccess;
-  int rc = kd_build_device(ctx->builder, volDev, X, Y, Z, rowPitch, slicePitch, tol, epochs, ctx->stream, &s->kd, &st, &ce, iters);
+  int rc = kd_build_device(ctx->builder, volDev, X, Y, Z, rowPitch, slicePitch, tol, epochs, ctx->stream, &s->kd, &st, &ce, iters, g_dbg.producerIndex != 0);
   if (rc != VR_OK) {
     delete s;
     if (rc == VR_ERR_CUDA) return fail_cuda(ce, "vr_kd_compress_device");

@@ -118,25 +118,33 @@ int vr_render(vr_context* ctx, const vr_volume* vol, const vr_render_params* par
 int vr_render_to_host(vr_context* ctx, const vr_volume* vol, const vr_render_params* params, float* out_rgba_host,
                       int32_t* hit_host, uint64_t* samples_host) {
   if (!ctx || !params || !out_rgba_host) return fail(VR_ERR_ARG, "vr_render_to_host: null argument");
+  if (params->width <= 0 || params->height <= 0) return fail(VR_ERR_ARG, "vr_render_to_host: empty frame");
   CU(cudaSetDevice(ctx->device));
   const size_t px = (size_t)params->width * (size_t)params->height;
-  float* d = nullptr; int32_t* dh = nullptr; uint64_t* ds = nullptr;
-  CU(cudaMalloc((void**)&d, px * 16));
-  int rc = VR_OK;
-  cudaError_t e = cudaSuccess;
-  if (hit_host) e = cudaMalloc((void**)&dh, px * 4);
-  if (e == cudaSuccess && samples_host) { e = cudaMalloc((void**)&ds, 8); if (e == cudaSuccess) e = cudaMemsetAsync(ds, 0, 8, ctx->stream); }
-  if (e != cudaSuccess) rc = fail_cuda(e, "cudaMalloc(render outputs)");
-  if (rc == VR_OK) rc = vr_render(ctx, vol, params, d, dh, ds);
-  if (rc == VR_OK) {
-    e = cudaMemcpyAsync(out_rgba_host, d, px * 16, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess && hit_host) e = cudaMemcpyAsync(hit_host, dh, px * 4, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess && samples_host) e = cudaMemcpyAsync(samples_host, ds, 8, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) rc = fail_cuda(e, "render download");
+  // the device-side frame lives in the context and only grows (one Draw() per frame, main.cpp:404, allocates nothing)
+  if (px > ctx->framePixels) {
+    cudaFree(ctx->frameDev); ctx->frameDev = nullptr; ctx->framePixels = 0;
+    CU(cudaMalloc((void**)&ctx->frameDev, px * 16));
+    ctx->framePixels = px;
   }
-  cudaFree(d); cudaFree(dh); cudaFree(ds);
-  return rc;
+  if (hit_host && px > ctx->frameHitPixels) {
+    cudaFree(ctx->frameHitDev); ctx->frameHitDev = nullptr; ctx->frameHitPixels = 0;
+    CU(cudaMalloc((void**)&ctx->frameHitDev, px * 4));
+    ctx->frameHitPixels = px;
+  }
+  if (samples_host && !ctx->frameCountDev) CU(cudaMalloc((void**)&ctx->frameCountDev, 8));
+  float* d = ctx->frameDev;
+  int32_t* dh = hit_host ? ctx->frameHitDev : nullptr;
+  uint64_t* ds = samples_host ? ctx->frameCountDev : nullptr;
+  if (ds) CU(cudaMemsetAsync(ds, 0, 8, ctx->stream));
+  int rc = vr_render(ctx, vol, params, d, dh, ds);
+  if (rc != VR_OK) return rc;
+  cudaError_t e = cudaMemcpyAsync(out_rgba_host, d, px * 16, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && hit_host) e = cudaMemcpyAsync(hit_host, dh, px * 4, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && samples_host) e = cudaMemcpyAsync(samples_host, ds, 8, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) return fail_cuda(e, "render download");
+  return VR_OK;
 }
 
 int vr_render_compressed(vr_context* ctx, vr_decode_plan* plan, const vr_render_params* params, float* out_rgba_dev,

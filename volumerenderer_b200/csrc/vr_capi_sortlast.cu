@@ -60,6 +60,25 @@ int vr_sortlast_create(vr_context* ctx, const vr_slab_desc* slabs, int32_t n, in
     }
   }
   if (vol != tot) return fail(VR_ERR_ARG, "owned boxes do not cover the texture");
+  // ... and they must form a GRID: per axis one set of cut planes shared by all boxes, every box one cell of it, n = product
+  // of the cell counts.  Only then is the lexicographic order below a visibility order for every ray (three boxes
+  // [0,2]x[1,2], [1,2]x[0,1], [0,1]x[0,1] tile a square, but a +x+y ray can leave the second and enter the first).
+  {
+    int64_t cells = 1;
+    for (int a = 0; a < 3; ++a) {
+      std::vector<int64_t> cuts;
+      for (int r = 0; r < n; ++r) { cuts.push_back(slabs[r].own_lo[a]); cuts.push_back(slabs[r].own_hi[a]); }
+      std::sort(cuts.begin(), cuts.end());
+      cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+      for (int r = 0; r < n; ++r) {
+        const auto lo = std::lower_bound(cuts.begin(), cuts.end(), slabs[r].own_lo[a]);
+        if (*(lo + 1) != slabs[r].own_hi[a])
+          return fail(VR_ERR_ARG, "owned boxes are not a grid partition (a box spans a cut plane of another): no front-to-back order exists for every ray");
+      }
+      cells *= (int64_t)cuts.size() - 1;
+    }
+    if (cells != n) return fail(VR_ERR_ARG, "owned boxes are not a grid partition: no front-to-back order exists for every ray");
+  }
   vr_sortlast* sl = new vr_sortlast;
   sl->device = ctx ? ctx->device : -1; sl->n = n; sl->rank = rank;
   sl->slabs.assign(slabs, slabs + n);

@@ -22,6 +22,10 @@ struct vr_context {
   vr::KdBuilder* builder = nullptr;  // scratch of the GPU stream producer (kd_build.h), created on first use
   std::map<uint64_t, uint32_t*> chainLuts;   // chainDist -> device table of 16384 entries (classic kernel: vr_chain_lut_entry)
   std::map<uint64_t, uint32_t*> chainLuts6;  // same for the persistent kernel (vr6::chain_entry)
+  // device-side frame of vr_render_to_host (RGBA, hit indices, sample counter): kept between calls, grown on demand, so
+  // that one Draw() per frame (main.cpp:404) costs no cudaMalloc / cudaFree
+  float* frameDev = nullptr; int32_t* frameHitDev = nullptr; uint64_t* frameCountDev = nullptr;
+  size_t framePixels = 0, frameHitPixels = 0;
   vr::Decode6Side side{};  // side stream + fork / join events of the split decode launch (kd_decode.h), created with the first plan
 };
 
@@ -111,7 +115,8 @@ struct vr_decode_plan {
     int64_t* occSetDev = nullptr; int nOccSet = 0;  // (cell, max) pairs of the tiles left out
     int64_t tilesTotal = 0, tilesWritten = 0, bytesVoxels = 0, bytesStream = 0;
   } lazy;
-  void lazy_free();
+  Lazy subset;  // lists of the last vr_decode_plan_run_tiles
+  void lazy_free(Lazy* which = nullptr);
 };
 
 namespace vr {
@@ -134,6 +139,6 @@ int render_volume(vr_context* ctx, const vr_volume* vol, const vr_render_params*
 int skip_threshold_of(const vr_render_params* params, int* thr, int* mode);  // occupancy threshold of the frame's mode
 // (re)builds plan->lazy for (thr, reach): the work list without the tiles the frame cannot read (kd_cull.h)
 int plan_lazy_prepare(vr_decode_plan* plan, int mode, int thr, const int reach[3], const int stepReach[3]);
-int plan_lazy_run(vr_decode_plan* plan);  // decode launch over the lazy list + maxima of the tiles left out
+int plan_lazy_run(vr_decode_plan* plan, vr_decode_plan::Lazy* which = nullptr);  // decode launch over the lazy list + maxima of the tiles left out
 void volume_occ_written(vr_context* ctx, vr_volume* v, const int64_t lo[3], const int64_t ext[3]);  // a box of voxels was overwritten
 }

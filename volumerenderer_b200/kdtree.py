@@ -127,6 +127,61 @@ class Stream:
     def save(self, path):
         check(lib.vr_stream_save(self.h, str(path).encode()))
 
+    # ---- indexed ("random-access") container, csrc/kd_kdx.cpp ----
+    def save_indexed(self, path):
+        check(lib.vr_stream_save_indexed(self.h, str(path).encode()))
+
+    def serialize_indexed(self):
+        """The bytes save_indexed() writes, as a uint8 array."""
+        n = c_int64()
+        check(lib.vr_stream_serialize_indexed(self.h, None, 0, byref(n)))
+        out = np.empty(n.value, np.uint8)
+        check(lib.vr_stream_serialize_indexed(self.h, out.ctypes.data, out.size, byref(n)))
+        return out
+
+    @classmethod
+    def open_indexed(cls, path, tile_mask=None, verify=False):
+        """Opens an indexed container without walking the stream.  tile_mask (uint8[tiles]): fetch only those tiles' symbols.
+        Returns the Stream; .bytes_read = bytes fetched from the file."""
+        m = None if tile_mask is None else np.ascontiguousarray(tile_mask, dtype=np.uint8)
+        h = c_void_p()
+        nread = c_int64()
+        check(lib.vr_stream_open_indexed(str(path).encode(), None if m is None else m.ctypes.data, int(bool(verify)), byref(h), byref(nread)))
+        s = cls(h)
+        s.bytes_read = nread.value
+        return s
+
+    @classmethod
+    def from_memory_indexed(cls, image, tile_mask=None, verify=False):
+        a = np.ascontiguousarray(image, dtype=np.uint8)
+        m = None if tile_mask is None else np.ascontiguousarray(tile_mask, dtype=np.uint8)
+        h = c_void_p()
+        check(lib.vr_stream_from_memory_indexed(a.ctypes.data, a.size, None if m is None else m.ctypes.data, int(bool(verify)), byref(h)))
+        return cls(h)
+
+    def index_info(self):
+        out = (c_int64 * 6)()
+        check(lib.vr_stream_index_info(self.h, out))
+        return {"tiles": out[0], "live_tiles": out[1], "leaves_per_tile": out[2], "subset": bool(out[3]), "index_bytes": out[4],
+                "max_symbols_per_leaf": out[5]}
+
+    _SECTIONS = {"tileLeafBlock": (1, np.uint32), "tileVal": (2, np.uint8), "tileMin": (3, np.uint8), "tileMax": (4, np.uint8),
+                 "blockSymBegin": (5, np.uint32), "blockSymEnd": (6, np.uint32), "leafOff": (7, np.uint32), "leafVal": (8, np.uint8)}
+
+    def index_section(self, name):
+        """Copy of one array of the decode index (names as in csrc/kd_stream.h KdIndex)."""
+        which, dt = self._SECTIONS[name]
+        p = c_void_p()
+        n = c_int64()
+        check(lib.vr_stream_index_section(self.h, which, byref(p), byref(n)))
+        if n.value == 0:
+            return np.zeros(0, dt)
+        raw = np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8)), shape=(n.value,)).copy()
+        return raw.view(dt)
+
+    def index_arrays(self):
+        return {k: self.index_section(k) for k in self._SECTIONS}
+
     @property
     def header(self):
         hd = _lib.StreamHeader()
@@ -305,6 +360,13 @@ class DecodePlan:
 
     def run(self):
         check(lib.vr_decode_plan_run(self.h))
+
+    def run_tiles(self, needed):
+        """Random-access decode: only the tiles with needed[brick, tile] != 0 (vr_decode_plan_run_tiles).  Returns stats."""
+        m = np.ascontiguousarray(needed, dtype=np.uint8)
+        st = (c_int64 * 4)()
+        check(lib.vr_decode_plan_run_tiles(self.h, m.ctypes.data, st))
+        return {"tiles": st[0], "tiles_written": st[1], "voxel_bytes": st[2], "stream_bytes": st[3]}
 
     def bytes(self):
         out = (c_int64 * 3)()
