@@ -273,6 +273,19 @@ int vr_lazy_tile_mask(vr_stream* const* streams, int32_t n, const int64_t* origi
  * (implies prepare; nothing is decoded).  2^Dt entries each in tile (kd path) order; tile_dims (optional) = tile extent. */
 int vr_stream_tile_bounds(vr_stream* s, uint8_t* mins, uint8_t* maxs, int64_t cap, int32_t tile_dims[3]);
 
+/* ---- MidRangeTree::save / open (MidRangeTree.cpp:753-786, 788-833; layout SURVEY A.3) ---------------------------------
+ * File = the 88-byte header, distanceMap, distanceMap_range (maxTreeDepth+1 bytes each), tree.bits, tree_range.bits
+ * (tree_nbytes each).  vr_mrt_save writes what the reference's save() writes, byte for byte.  vr_mrt_open reads such a
+ * file: the midpoint stream comes back as a decodable stream handle -- MidRangeTree::levelCut == VolumeKdtree::levelCut on it,
+ * MidRangeTree.cpp:908-1017 -- and the range stream and its distance map as plain bytes (they feed convertToByteArray,
+ * vr_nibbles_pack).  The reference's own open() mis-sizes both arrays by 4 bytes (one int64 missing from its header sum,
+ * :815) and so reads tree_range misaligned (SURVEY C-3); that is not reproduced.  Call vr_mrt_open with NULL output
+ * buffers first to learn tree_nbytes (the returned stream must still be destroyed). */
+int vr_mrt_save(const char* path, const vr_stream_header* hdr, const uint8_t* distanceMap, const uint8_t* distanceMap_range,
+                const uint8_t* tree_bits, const uint8_t* range_bits, int64_t tree_nbytes);
+int vr_mrt_open(const char* path, vr_stream** mid_out, uint8_t* distanceMap_range_out, int32_t dm_cap, uint8_t* range_bits_out,
+                int64_t cap, int64_t* tree_nbytes);
+
 /* ---- indexed ("random-access") container -------------------------------------------------------------
  * What HashedKdtree.cpp:96-214 (build), :254-336 (levelCutRecursive), :406-507 (compress), :528-545 (save) was reaching
  * for: decode any part of a brick without parsing what lies in front of it.  The reference's Morton-keyed hash with

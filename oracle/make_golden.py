@@ -48,5 +48,40 @@ def main():
         oa.REF.ref_kd_free(s["h"])
 
 
+MRT_CASES = [
+    ("mrt_shell_32x32x16_t1e2", lambda: synth.shell_brick((32, 32, 16), noise=4), 1, 2),
+    ("mrt_odd_16x8x4_t1e2", lambda: synth.shell_brick((16, 8, 4), noise=9), 1, 2),
+]
+
+
+def main_mrt():
+    """tests/golden/mrt/*.npz: the file MidRangeTree::save of the unmodified reference writes, the class's public arrays and
+    MidRangeTree::levelCut's output."""
+    out_dir = os.path.join(ROOT, "tests", "golden", "mrt")
+    os.makedirs(out_dir, exist_ok=True)
+    LL = oa.c_longlong
+    for name, gen, tol, ep in MRT_CASES:
+        vol = gen()
+        Z, Y, X = vol.shape
+        h = oa.REF.ref_mrt_build(vol.ctypes.data, X, Y, Z, tol, ep, 0)
+        m = (LL * 7)()
+        oa.REF.ref_mrt_meta(h, m)
+        dm = np.zeros(m[0] + 1, np.uint8); dmr = np.zeros(m[0] + 1, np.uint8)
+        bits = np.zeros(m[6], np.uint8); bitsr = np.zeros(m[6], np.uint8)
+        oa.REF.ref_mrt_get(h, dm.ctypes.data, dmr.ctypes.data, bits.ctypes.data, bitsr.ctypes.data)
+        dec = np.zeros((Z, Y, X), np.uint8)
+        oa.REF.ref_mrt_levelcut(h, dec.ctypes.data)
+        with tempfile.TemporaryDirectory() as td:
+            p = os.path.join(td, "t.mrt")
+            oa.REF.ref_mrt_save(h, p.encode())
+            blob = np.fromfile(p, np.uint8)
+        oa.REF.ref_mrt_free(h)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), volume=vol, container=blob, dmap=dm, dmap_range=dmr, bits=bits, bits_range=bitsr,
+                            decoded=dec, meta=np.array(list(m), np.int64))
+        print(name, "nodes", m[5], "file bytes", blob.size)
+
+
 if __name__ == "__main__":
-    main()
+    if "--mrt-only" not in sys.argv:
+        main()
+    main_mrt()

@@ -65,3 +65,11 @@ long long ref_mrt_bytearray(void* hv, unsigned char* out) {
   return (long long)o.size();
 }
 }
+
+extern "C" {
+// MidRangeTree::save (MidRangeTree.cpp:753-786) of the unmodified reference
+void ref_mrt_save(void* hv, const char* path) {
+  CoutMute m;
+  static_cast<RefMrt*>(hv)->t->save(path);
+}
+}

@@ -47,6 +47,8 @@ if REF is not None:
     REF.ref_mrt_levelcut.argtypes = [c_void_p, c_void_p]
     REF.ref_mrt_bytearray.restype = LL
     REF.ref_mrt_bytearray.argtypes = [c_void_p, c_void_p]
+    if hasattr(REF, "ref_mrt_save"):
+        REF.ref_mrt_save.argtypes = [c_void_p, ctypes.c_char_p]
 
 if EMU is not None:
     LL = c_longlong

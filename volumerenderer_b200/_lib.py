@@ -71,6 +71,8 @@ _SIGS = {
     "vr_nibbles_pack": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, POINTER(c_int64)]),
     "vr_nibbles_unpack": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "vr_stream_from_nibbles": (c_int, [POINTER(StreamHeader), c_void_p, c_void_p, c_int64, POINTER(c_void_p), c_void_p]),
+    "vr_mrt_save": (c_int, [c_char_p, POINTER(StreamHeader), c_void_p, c_void_p, c_void_p, c_void_p, c_int64]),
+    "vr_mrt_open": (c_int, [c_char_p, POINTER(c_void_p), c_void_p, c_int32, c_void_p, c_int64, POINTER(c_int64)]),
     "vr_kd_compress": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
     "vr_peer_create": (c_int, [c_void_p, c_int32, c_int32, c_int64, POINTER(c_void_p)]),
     "vr_peer_destroy": (c_int, [c_void_p]),

@@ -82,6 +82,11 @@ int kdx_save(KdStream* s, const char* path);
 int kdx_from_memory(const uint8_t* buf, int64_t nbytes, const uint8_t* tileMask, bool verify, KdStream* out);
 int kdx_open(const char* path, const uint8_t* tileMask, bool verify, KdStream* out, int64_t* bytesRead);
 
+// MidRangeTree::save / open container (kd_mrt.cpp): midpoint stream + range stream in one file.
+int mrt_save(const vr_kd_header& hdr, const uint8_t* dm, const uint8_t* dmRange, const uint8_t* treeBits, const uint8_t* rangeBits,
+             int64_t treeSize, const char* path);
+int mrt_open(const char* path, KdStream* mid, std::vector<uint8_t>* dmRange, std::vector<uint8_t>* rangeBits);
+
 // CPU compressor: the reference's build() algorithm (VolumeKdTree_recover.cpp:17-140) restated;
 // produces byte-identical streams.  `volume` is not modified (the reference empties its input).
 struct KdBuildStats {

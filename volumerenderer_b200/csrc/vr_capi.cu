@@ -284,6 +284,31 @@ int vr_stream_from_nibbles(const vr_stream_header* hdr, const uint8_t* dm, const
   return vr_stream_from_memory(hdr, dm, mid.data(), (int64_t)mid.size(), out);
 }
 
+// ---- MidRangeTree::save / open (kd_mrt.cpp) -----------------------------------------------------------
+int vr_mrt_save(const char* path, const vr_stream_header* hdr, const uint8_t* dm, const uint8_t* dm_range, const uint8_t* tree_bits,
+                const uint8_t* range_bits, int64_t tree_nbytes) {
+  if (!path || !hdr) return fail(VR_ERR_ARG, "vr_mrt_save: null argument");
+  int rc = mrt_save(*reinterpret_cast<const vr_kd_header*>(hdr), dm, dm_range, tree_bits, range_bits, tree_nbytes, path);
+  return rc == VR_OK ? VR_OK : fail(rc, "vr_mrt_save failed (no tree to save, bad depth, or I/O error)");
+}
+int vr_mrt_open(const char* path, vr_stream** mid_out, uint8_t* dm_range_out, int32_t dm_cap, uint8_t* range_bits_out, int64_t cap,
+                int64_t* tree_nbytes) {
+  if (!path || !mid_out || !tree_nbytes) return fail(VR_ERR_ARG, "vr_mrt_open: null argument");
+  vr_stream* s = new vr_stream;
+  std::vector<uint8_t> dmr, rb;
+  int rc = mrt_open(path, &s->kd, &dmr, &rb);
+  if (rc != VR_OK) { delete s; return fail(rc, rc == VR_ERR_IO ? "Tree File does not exist or is short" : "bad MidRangeTree file"); }
+  *tree_nbytes = (int64_t)rb.size();
+  if ((dm_range_out && dm_cap < (int32_t)dmr.size()) || (range_bits_out && cap < (int64_t)rb.size())) {
+    delete s;
+    return fail(VR_ERR_ARG, "vr_mrt_open: output buffer too small");
+  }
+  if (dm_range_out) std::memcpy(dm_range_out, dmr.data(), dmr.size());
+  if (range_bits_out) std::memcpy(range_bits_out, rb.data(), rb.size());
+  *mid_out = s;
+  return VR_OK;
+}
+
 int vr_kd_compress(const uint8_t* brick, int64_t X, int64_t Y, int64_t Z, int tol, int epochs, vr_stream** out,
                    vr_build_stats* stats) {
   if (!brick || !out) return fail(VR_ERR_ARG, "null");

@@ -245,6 +245,30 @@ def load_streams(paths, ctx=None, threads=0):
     return [Stream(c_void_p(out[i])) for i in range(n)]
 
 
+def mrt_save(path, header, distance_map, distance_map_range, tree_bits, range_bits):
+    """MidRangeTree::save (MidRangeTree.cpp:753-786): byte-identical file from the class's public fields."""
+    dm = np.ascontiguousarray(distance_map, dtype=np.uint8)
+    dmr = np.ascontiguousarray(distance_map_range, dtype=np.uint8)
+    tb = np.ascontiguousarray(tree_bits, dtype=np.uint8)
+    rb = np.ascontiguousarray(range_bits, dtype=np.uint8)
+    assert tb.size == rb.size and dm.size == dmr.size == header.maxTreeDepth + 1
+    check(lib.vr_mrt_save(str(path).encode(), byref(header), dm.ctypes.data, dmr.ctypes.data, tb.ctypes.data, rb.ctypes.data, tb.size))
+
+
+def mrt_open(path):
+    """MidRangeTree::open without its 4-byte misalignment: (midpoint Stream, distanceMap_range, tree_range bits)."""
+    h = c_void_p()
+    n = c_int64()
+    check(lib.vr_mrt_open(str(path).encode(), byref(h), None, 0, None, 0, byref(n)))
+    lib.vr_stream_destroy(h)
+    dmr = np.zeros(64, np.uint8)
+    rb = np.zeros(n.value, np.uint8)
+    h = c_void_p()
+    check(lib.vr_mrt_open(str(path).encode(), byref(h), dmr.ctypes.data, dmr.size, rb.ctypes.data, rb.size, byref(n)))
+    s = Stream(h)
+    return s, dmr[: s.header.maxTreeDepth + 1].copy(), rb
+
+
 def nibbles_pack(tree_bits, range_bits, n):
     """MidRangeTree::convertToByteArray (MidRangeTree.cpp:1095-1128): the 4-bit/node stream of n nodes."""
     t = np.ascontiguousarray(tree_bits, np.uint8); r = np.ascontiguousarray(range_bits, np.uint8)
