@@ -275,8 +275,25 @@ def bench_extras(ctx, vr, render, vol, plan, threads, peak, local):
     # host index walk of one mixing-layer stream on one thread (what vr_stream_prepare costs for a legacy container)
     one = vr.Stream.from_memory(streams3[27].header, streams3[27].distance_map, streams3[27].bits)
     t0 = time.time(); one.prepare(); host_ms = (time.time() - t0) * 1e3
+    # the same index emitted by the GPU producer from its own symbol offsets (csrc/kd_build.cu): producer time with and without it
+    brick337 = synth.rm_brick(3, 3, 7)
+
+    def producer_ms(with_index):
+        vr.debug_set("producer_index", 1 if with_index else 0)
+        try:
+            ts = []
+            for _ in range(3):
+                t0 = time.time(); sx, _ = vr.Stream.compress_device(ctx, brick337, 1, 2); ts.append((time.time() - t0) * 1e3); sx.close()
+            return float(np.median(ts))
+        finally:
+            vr.debug_set("producer_index", 1)
+    p_with, p_without = producer_ms(True), producer_ms(False)
     ex["index_build"] = {"host_ms_per_brick": host_ms, "host_threads_per_brick": 1, "bricks_in_parallel": threads,
-                         "brick": "rm brick (3, 3, 7)", "nodes": int(one.header.numActiveNodes), "device_ms_per_brick": None}
+                         "brick": "rm brick (3, 3, 7)", "nodes": int(one.header.numActiveNodes),
+                         "device_ms_per_brick": max(p_with - p_without, 0.0),
+                         "device": "index emitted by the GPU stream producer from its own symbol offsets (no walk of the stream); "
+                                   "producer alone %.2f ms, with index %.2f ms per brick; streams from elsewhere: host walk, or none at all "
+                                   "for indexed containers (e2e.cold)" % (p_without, p_with)}
     one.close()
     pl3.close(); v3.close()
     for s in streams3:
@@ -338,7 +355,7 @@ def run_ours(args):
                 dist.all_gather_object(allh, mine)
                 return allh
             peer = sortlast.PeerExchange(ctx, rank, world, IMG, IMG, halo_bytes=sortlast.halo_staging_bytes(descs, stored),
-                                         handles=gather_handles)
+                                         handles=gather_handles, halo_buffers=2)
             exch = peer
         else:
             exch = sortlast.TorchDistExchange()
@@ -418,7 +435,37 @@ def run_ours(args):
     # still decodes its 120 bricks and draws one frame of a freshly decoded slab; a pair of steps is one graph replay.
     pair = None
     peerF = None
-    if args.pipeline and (world == 1 or peer is not None):
+    inter = None
+    schedule = "sequential"
+    if args.pipeline and world > 1 and peer is not None and args.exchange == "peer" and args.schedule == "interleaved":
+        # N > 1 default: ONE stream, the stages of frame(t) and decode(t+1) interleaved so that every device-side wait of the
+        # exchange sits behind a long kernel of the other stage (sortlast.InterleavedSteps)
+        try:
+            vol2 = vr.Volume(ctx, *se).set_cell_origin(so)
+            plan2 = vr.DecodePlan(ctx, streams, origins, vol2)
+            ops2 = sortlast.CudaSlabOps(ctx, sl, vol2, IMG, IMG, count_samples=False)
+            opsA = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=False)
+            inter = sortlast.InterleavedSteps(peer, [plan, plan2], [opsA, ops2], descs, stored, p)
+            barrier()
+            inter.prologue()
+            for _ in range(4):
+                inter.step()
+            barrier()
+            if not args.no_graph:
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2, stream=main_stream):
+                    inter.step(); inter.step()
+                g2.replay(); barrier()
+                pair = g2.replay
+            else:
+                pair = lambda: (inter.step(), inter.step())
+            schedule = "interleaved"
+        except Exception as e:
+            pair, inter = None, None
+            sys.stderr.write(f"bench.py: interleaved steps unavailable ({type(e).__name__}: {e}); sequential steps\n")
+            torch.cuda.synchronize()
+    elif args.pipeline and (world == 1 or peer is not None):
+        schedule = "two-stream"
         try:
             f_stream = torch.cuda.Stream(priority=-1)
             ctxF = vr.Context(local, cuda_stream=f_stream.cuda_stream)
@@ -459,6 +506,7 @@ def run_ours(args):
                 pair = step_pair
         except Exception as e:
             pair = None
+            schedule = "sequential"
             sys.stderr.write(f"bench.py: pipelined steps unavailable ({type(e).__name__}: {e}); sequential steps\n")
             torch.cuda.synchronize()
     barrier()
@@ -469,6 +517,11 @@ def run_ours(args):
         for it in range(args.steps // 2):
             pair()
         todo = args.steps & 1
+    if inter is not None and pair is not None:
+        for it in range(todo):
+            inter.step()
+        todo = 0
+        inter.drain()  # the last issued frame is waited for inside the timed region
     for it in range(todo):
         if graph is not None:
             graph.replay()
@@ -567,6 +620,63 @@ def run_ours(args):
     torch.cuda.synchronize()
     e2e_ms = reduce_max((time.time() - te) * 1e3 / e2e_steps)
 
+    # ---- cold end to end (N = 1): every step opens the timestep's containers from files (page cache), indexes them,
+    # pins + uploads, plans, decodes, draws, reads the frame back -- nothing is reused between steps.  Two container
+    # formats: the reference's .bin (vr_streams_load walks every stream on the host threads to build the decode index) and
+    # the indexed container of csrc/kd_kdx.cpp (the index is in the file: no walk).
+    cold = None
+    if world == 1 and not args.no_extras:
+        import shutil
+        import tempfile
+        tmp = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        try:
+            files = {"bin": [], "kdx": []}
+            maps = []
+            for t, (ss, us) in enumerate(((streams, uniq), (streams1, uniq1))):
+                order = list(us.keys())
+                maps.append([order.index(id(x)) for x in ss])
+                for fmt in files:
+                    pl = []
+                    for m, key in enumerate(order):
+                        f = os.path.join(tmp, f"t{t}_{m}.{fmt}")
+                        (us[key].save if fmt == "bin" else us[key].save_indexed)(f)
+                        pl.append(f)
+                    files[fmt].append(pl)
+
+            def cold_step(fmt, t, tm):
+                t0 = time.time()
+                ss = vr.load_streams(files[fmt][t], ctx, threads)       # open (+ host walk for .bin), pin, H2D
+                t1 = time.time()
+                pl = vr.DecodePlan(ctx, [ss[m] for m in maps[t]], origins, vol)  # work lists (host) + uploads
+                t2 = time.time()
+                pl.run()
+                img = frame()
+                ctx.download(host_img.data_ptr(), img.data_ptr(), d2h)
+                ctx.synchronize()
+                t3 = time.time()
+                pl.close()
+                for x in ss:
+                    x.close()
+                tm.append((t1 - t0, t2 - t1, t3 - t2, time.time() - t0))
+
+            cold = {}
+            for fmt in ("kdx", "bin"):
+                tm = []
+                cold_step(fmt, 0, [])
+                for i in range(4):
+                    cold_step(fmt, i & 1, tm)
+                a = np.median(np.asarray(tm), axis=0) * 1e3
+                cold[{"kdx": "indexed_container", "bin": "reference_container"}[fmt]] = {
+                    "ms_per_step": float(a[3]), "open_index_pin_upload_ms": float(a[0]), "plan_ms": float(a[1]), "decode_frame_d2h_ms": float(a[2]),
+                    "value": voxels_all / float(a[3]) / 1e6, "unit": "GVoxel/s",
+                    "file_bytes_per_step": int(np.mean([sum(os.path.getsize(f) for f in files[fmt][t]) for t in range(2)]))}
+            cold["host_threads"] = threads
+            cold["note"] = ("every step: vr_streams_load of the timestep's files (page cache) -> vr_decode_plan_create -> decode -> frame -> D2H; "
+                            "nothing reused between steps; reference_container = VolumeKdtree::save files, index built by the host walk; "
+                            "indexed_container = csrc/kd_kdx.cpp files, no walk")
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+
     if rank != 0:
         if world > 1:
             dist.barrier(); dist.destroy_process_group()
@@ -610,9 +720,14 @@ def run_ours(args):
                                  + ("over peer-memory windows on NVLink (halo planes, all-gather T_seg 4 MiB/rank, reduce-scatter of the "
                                     "(C,A) terms + finished stripes to every rank)" if peer is not None else
                                     "over NCCL (halo send/recv, all-gather T_seg 4 MiB/rank, all-reduce (C,A) 8 MiB)")),
-                   "step": ("pipelined: two slabs; step t decodes one while the frame of step t-1 is drawn from the other on a second "
-                            "stream; every step = 120 bricks decoded + 1 frame of a freshly decoded slab" if pair is not None else
-                            "sequential: decode, then frame, on one stream")},
+                   "step": {"two-stream": "pipelined: two slabs; step t decodes one while the frame of step t-1 is drawn from the other on a "
+                                          "second stream; every step = 120 bricks decoded + 1 frame of a freshly decoded slab",
+                            "interleaved": "interleaved on one stream: two slabs; step t draws the frame of the slab decoded by step t-1 and "
+                                           "decodes the next one, stage by stage (pass 1 | decode | halo put | resolve | halo unpack | sum), so the "
+                                           "exchange's waits sit behind the other stage's kernels; every step = 120 bricks decoded + halo "
+                                           "exchange + 1 frame of a freshly decoded slab",
+                            "sequential": "sequential: decode, then frame, on one stream"}[schedule if pair is not None else "sequential"],
+                   "schedule": schedule if pair is not None else "sequential"},
         "stages": {"decode_ms": d_ms, "march_ms": m_ms, "decode_gvoxels_per_s": voxels_rank / d_ms / 1e6,
                    "frames_per_s": 1e3 / m_ms, "gsamples_per_s": samples / m_ms / 1e6, "samples_per_frame": samples},
         "roofline": dominant, "roofline_decode": roof_dec, "roofline_march": roof_mar,
@@ -620,7 +735,8 @@ def run_ours(args):
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                 "mode": "streaming: timesteps t=0/t=1 alternate, H2D of the next timestep overlaps decode+frame of the current",
                 "serial": {"value": voxels_all / serial_ms / 1e6, "ms_per_step": serial_ms,
-                           "h2d_bytes_per_step": int(h2d_sets[0])}},
+                           "h2d_bytes_per_step": int(h2d_sets[0])},
+                "cold": cold},
         # own kernels per step: decode, 3 occupancy refresh, march; N > 1 over NCCL: partial, resolve, finish instead of march;
         # N > 1 over peer windows (rank 0, one neighbour): decode, halo put + wait + box reduce, 3 occupancy, partial, gather put +
         # wait, resolve, reduce-scatter put + wait + combine, all-gather put + wait, finish = 17
@@ -764,6 +880,8 @@ def main():
                     help="N > 1: sort-last exchange over peer-memory windows (copy kernels, or fused into the march kernels) or NCCL")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
                     help="strictly sequential steps (decode, then frame) instead of decode(t+1) overlapping frame(t) on two slabs")
+    ap.add_argument("--schedule", default="interleaved", choices=["interleaved", "two-stream"],
+                    help="N > 1 with the peer exchange: how decode(t+1) and frame(t) share the GPU (one stream, stages interleaved; or two streams)")
     ap.add_argument("--debug", action="append", default=[], metavar="KEY=VALUE",
                     help="A/B runs: vr_debug_set(KEY, VALUE) before anything is created (e.g. decode_split=1, decode_only=2: timing probes)")
     ap.add_argument("--no-extras", action="store_true", help="N = 1: skip the extra frames and the stream-dense decode workloads")

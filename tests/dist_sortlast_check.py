@@ -14,6 +14,65 @@ import volumerenderer_b200 as vr  # noqa: E402
 from volumerenderer_b200 import render, sortlast, synth  # noqa: E402
 
 
+class _OwnedBoxWriter:
+    """Stands in for a decode plan in interleaved_steps_check: run() rewrites the slab (owned box of `full`, halo zeroed)."""
+
+    def __init__(self, vol, full, desc, origin, extent):
+        self.vol, self.e = vol, extent
+        lo, hi = list(desc.own_lo), list(desc.own_hi)
+        self.box = np.ascontiguousarray(full[lo[2]:hi[2], lo[1]:hi[1], lo[0]:hi[0]])
+        self.at = [lo[a] - origin[a] for a in range(3)]
+        self.zero = np.zeros((extent[2], extent[1], extent[0]), np.uint8)
+
+    def run(self):
+        self.vol.upload_brick(self.zero, (0, 0, 0))
+        self.vol.upload_brick(self.box, self.at)
+
+
+def interleaved_steps_check(ctx, rank, world, full):
+    """sortlast.InterleavedSteps (frame(t) and decode(t+1) + halo(t+1) interleaved on one stream, two halo staging areas, the
+    frame waited for one step later): two alternating volumes, every frame against the staged frame of the same volume."""
+    Z, Y, X = full.shape
+    W, H = 160, 120
+    other = np.ascontiguousarray(full[::-1, :, ::-1])  # the second timestep
+    p = render.oblique_params(W, H, render.COMPOSITE, step=(1 / 96, 1 / 96, 1 / 128))
+    descs, stored = sortlast.slab_layout((X, Y, Z), world, axis=1, halo=sortlast.required_halo(p, (X, Y, Z)))
+    o, e = stored[rank]
+
+    def gather_handles(mine):
+        allh = [None] * world
+        dist.all_gather_object(allh, mine)
+        return allh
+    peer = sortlast.PeerExchange(ctx, rank, world, W, H, halo_bytes=sortlast.halo_staging_bytes(descs, stored), handles=gather_handles,
+                                 halo_buffers=2)
+    sl = sortlast.SortLast(ctx, descs, rank)
+    vols = [vr.Volume(ctx, *e).set_cell_origin(o) for _ in range(2)]
+    ops = [sortlast.CudaSlabOps(ctx, sl, v, W, H) for v in vols]
+    plans = [_OwnedBoxWriter(vols[k], (full, other)[k], descs[rank], o, e) for k in range(2)]
+    want = []
+    for k in range(2):  # staged frames of the two timesteps
+        plans[k].run()
+        peer.exchange_halos(ops[k], descs, stored)
+        want.append(peer.render_frame(ops[k], p).clone())
+        torch.cuda.synchronize()
+    dist.barrier()
+    assert float((want[0] - want[1]).abs().max()) > 0.05, "the two timesteps must differ"
+    inter = sortlast.InterleavedSteps(peer, plans, ops, descs, stored, p)
+    got = []
+    inter.prologue()
+    for _ in range(7):
+        inter.step(consume=lambda f: got.append(f.clone()))
+    got.append(inter.drain().clone())
+    torch.cuda.synchronize()
+    assert not peer.timed_out(), hex(peer.last_error)
+    assert len(got) == 7
+    for t, f in enumerate(got):
+        d = float((f - want[t & 1]).abs().max())
+        assert d == 0.0, (rank, t, d)
+    dist.barrier()
+    peer.close()
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -61,6 +120,7 @@ def main():
             err = float(np.nanmax(np.abs(got - want)))
             worst = max(worst, err)
             assert err <= (2e-5 if mode == render.COMPOSITE else 2.0 / 255.0), (rank, mode, err)
+    interleaved_steps_check(ctx, rank, world, full)
     dist.barrier()
     if rank == 0:
         print(f"SORTLAST_NCCL_OK world={world} worst_abs_err={worst:.3g}")

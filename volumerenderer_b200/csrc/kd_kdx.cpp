@@ -235,4 +235,17 @@ int kdx_open(const char* path, const uint8_t* tileMask, bool verify, KdStream* o
   return rc;
 }
 
+// VolumeKdtree::open on either container: the indexed one is recognised by its magic (a plain container starts with
+// rootMin = 0,0,0: eight zero bytes) and opened without the walk.
+int kd_open_any(const char* path, KdStream* out) {
+  if (!path || !out) return VR_ERR_ARG;
+  FILE* f = std::fopen(path, "rb");
+  if (!f) return VR_ERR_IO;
+  char magic[8] = {0};
+  const size_t got = std::fread(magic, 1, 8, f);
+  std::fclose(f);
+  if (got == 8 && std::memcmp(magic, KDX_MAGIC, 8) == 0) return kdx_open(path, nullptr, false, out, nullptr);
+  return kd_open(path, out);
+}
+
 }  // namespace vr

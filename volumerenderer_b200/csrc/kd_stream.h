@@ -81,6 +81,7 @@ int kdx_save(KdStream* s, const char* path);
 // tileMask (optional, 2^Dt bytes): read only the stream bytes of these tiles.  verify: check the stream checksum (full opens only).
 int kdx_from_memory(const uint8_t* buf, int64_t nbytes, const uint8_t* tileMask, bool verify, KdStream* out);
 int kdx_open(const char* path, const uint8_t* tileMask, bool verify, KdStream* out, int64_t* bytesRead);
+int kd_open_any(const char* path, KdStream* out);  // plain or indexed container, by magic
 
 // MidRangeTree::save / open container (kd_mrt.cpp): midpoint stream + range stream in one file.
 int mrt_save(const vr_kd_header& hdr, const uint8_t* dm, const uint8_t* dmRange, const uint8_t* treeBits, const uint8_t* rangeBits,

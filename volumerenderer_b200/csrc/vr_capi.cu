@@ -127,7 +127,7 @@ int vr_stream_from_memory(const vr_stream_header* hdr, const uint8_t* dm, const 
 int vr_stream_open(const char* path, vr_stream** out) {
   if (!out) return fail(VR_ERR_ARG, "null out");
   vr_stream* s = new vr_stream;
-  int rc = kd_open(path, &s->kd);
+  int rc = kd_open_any(path, &s->kd);  // VolumeKdtree::open; an indexed container (kd_kdx.cpp) is recognised by its magic
   if (rc != VR_OK) { delete s; return fail(rc, rc == VR_ERR_IO ? "Tree File does not exist or is short" : "bad tree file"); }
   *out = s;
   return VR_OK;

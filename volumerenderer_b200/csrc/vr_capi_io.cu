@@ -184,7 +184,7 @@ int vr_streams_load(vr_context* ctx, const char* const* paths, int32_t n, int32_
         const int i = next.fetch_add(1);
         if (i >= n || abort.load()) return;
         vr_stream* s = new vr_stream;
-        int rc = kd_open(paths[i], &s->kd);
+        int rc = kd_open_any(paths[i], &s->kd);  // an indexed container (kd_kdx.cpp) brings its index: no walk
         if (rc == VR_OK) rc = stream_build_image(s);
         std::lock_guard<std::mutex> lk(mu);
         if (rc != VR_OK) { s->release(); delete s; state[(size_t)i] = -rc; abort.store(true); }

@@ -247,7 +247,7 @@ class PeerExchange:
 
     GATHER, RED_IN, RED_OUT, HALO = 0, 1, 2, 3
 
-    def __init__(self, ctx, rank, n, W, H, halo_bytes=0, handles=None):
+    def __init__(self, ctx, rank, n, W, H, halo_bytes=0, handles=None, halo_buffers=1):
         import torch
         self.torch, self.ctx, self.rank, self.n, self.P = torch, ctx, int(rank), int(n), int(W) * int(H)
         P = self.P
@@ -257,7 +257,8 @@ class PeerExchange:
         self.off_total = self.off_red_in + 16 * P          # n stripes of 16P/n bytes (largest payload: rgba float4)
         self.off_halo = self.off_total + 16 * P
         self.halo_bytes = (int(halo_bytes) + 15) // 16 * 16
-        self.bytes = self.off_halo + self.halo_bytes
+        self.halo_buffers = int(halo_buffers)  # staging areas used in turn (InterleavedSteps alternates two)
+        self.bytes = self.off_halo + self.halo_bytes * self.halo_buffers
         self.h = c_void_p()
         check(lib.vr_peer_create(ctx.h, self.rank, self.n, self.bytes, byref(self.h)))
         self.device = torch.device("cuda", ctx.device if hasattr(ctx, "device") else torch.cuda.current_device())
@@ -399,9 +400,12 @@ class PeerExchange:
             pass
         return res
 
-    def exchange_halos(self, ops, descs, stored, defer_receive=False):
+    def exchange_halos(self, ops, descs, stored, defer_receive=False, buf=0):
         """Halo boxes: the owner packs a box and stores it into the staging area of the rank that needs it; that rank
-        waits on the device and unpacks into its slab (which also refreshes the occupancy of the box)."""
+        waits on the device and unpacks into its slab (which also refreshes the occupancy of the box).
+        buf: which of the halo_buffers staging areas this exchange uses (same on all ranks)."""
+        assert 0 <= buf < self.halo_buffers
+        base = self.off_halo + buf * self.halo_bytes
         rank, my_o = self.rank, stored[self.rank][0]
         offs = {}            # running staging offset per destination, identical on all ranks
         copies, keep, recvs = [], [], []
@@ -411,14 +415,15 @@ class PeerExchange:
             offs[dst] = o + nb
             assert o + nb <= self.halo_bytes, "halo staging area too small"
             if src == rank:
-                buf = ops.pack_box([lo[a] - stored[src][0][a] for a in range(3)], ext, pad16=True)
-                keep.append(buf)
-                copies.append((dst, self.off_halo + o, buf.data_ptr(), nb))
+                pk = ops.pack_box([lo[a] - stored[src][0][a] for a in range(3)], ext, pad16=True)
+                keep.append(pk)
+                copies.append((dst, base + o, pk.data_ptr(), nb))
             elif dst == rank:
-                recvs.append((src, [lo[a] - my_o[a] for a in range(3)], ext, o))
+                recvs.append((src, [lo[a] - my_o[a] for a in range(3)], ext, base + o))
         if copies:
             self._put(self.HALO, copies)
-        self._keep = keep  # until the next call: the put kernel reads them asynchronously
+        self._keep = getattr(self, "_keep_prev", None), keep  # the put kernel reads them asynchronously: held for two calls
+        self._keep_prev = keep
         if defer_receive:
             return recvs
         self.receive_halos(ops, recvs)
@@ -428,7 +433,7 @@ class PeerExchange:
         if recvs:
             self._wait(self.HALO, sorted({r[0] for r in recvs}))
             for _, o3, ext, o in recvs:
-                ops.unpack_box_ptr(o3, ext, self._base() + self.off_halo + o)
+                ops.unpack_box_ptr(o3, ext, self._base() + o)
 
     def timed_out(self):
         e = c_int32(0)
@@ -440,6 +445,60 @@ class PeerExchange:
         if self.h:
             lib.vr_peer_destroy(self.h)
             self.h = c_void_p()
+
+
+class InterleavedSteps:
+    """Steady state of a time-varying sharded volume on ONE stream (N > 1, peer-memory exchange): step t draws the COMPOSITE
+    frame of the slab decoded by step t-1 and decodes the next timestep into the other slab, with the stages of the two
+    interleaved so that every device-side wait sits behind a long kernel of the other stage:
+
+        partial(t) + put T_seg  |  wait frame(t-1)  |  DECODE(t+1)  |  halo pack + put (t+1)  |  wait T_seg, resolve(t), put terms
+        |  wait halo, unpack (t+1)  |  wait terms, sum + colour map + broadcast (t)            [frame(t) is waited for in step t+1]
+
+    The all-gather's latency and the skew between ranks' pass 1 hide behind the decode, the reduce-scatter's behind the halo
+    unpack, the broadcast's behind the next step's pass 1.  No second stream, no concurrency between kernels is needed (a
+    persistent decode launch leaves no room for it).  Two halo staging areas alternate: a neighbour can be a whole step ahead.
+    Write-after-read on the windows: a rank's next store into an area follows a wait that the area's reader preceded in its
+    own stream order (gather: put(t+1) follows wait terms(t), whose signal follows the reader's resolve(t); terms: put(t+1)
+    follows wait T_seg(t+1), whose signal follows the reader's sum(t); frame: the sum of t+1 follows wait terms(t+1), whose
+    signal follows the reader's wait frame(t); halo area b: put(t+2) follows wait terms(t), whose signal follows unpack(t))."""
+
+    def __init__(self, peer, plans, ops, descs, stored, params):
+        assert peer.halo_buffers >= 2 and len(plans) == 2 and len(ops) == 2 and params.mode == COMPOSITE
+        self.peer, self.plans, self.ops, self.descs, self.stored, self.p = peer, plans, ops, descs, stored, params
+        self.pending = None   # generator of the frame whose broadcast has not been waited for
+        self.k = 0            # slab the next step draws
+        self.t = 0
+
+    def prologue(self):
+        """Decode slab 0 and complete its halo: the state every step expects on entry."""
+        self.plans[0].run()
+        self.peer.exchange_halos(self.ops[0], self.descs, self.stored, buf=0)
+        self.k, self.t = 0, 1
+
+    def step(self, consume=None):
+        """One step: frame of slab k (issued, not yet waited for) + decode and halo of slab 1-k.  consume(frame): called with
+        the previous step's finished frame (a view of this rank's window) as soon as it has been waited for; whatever reads
+        it must be enqueued on the context's stream inside the callback -- later the peers may overwrite it."""
+        k, peer = self.k, self.peer
+        gen = peer.frame_stages_hybrid(self.ops[k], self.p)
+        next(gen)                                         # pass 1 + store T_seg into every window
+        prev = next(self.pending) if self.pending is not None else None   # wait for the previous frame's stripes
+        if consume is not None and prev is not None:
+            consume(prev)
+        self.plans[1 - k].run()                           # decode of the next timestep
+        recvs = peer.exchange_halos(self.ops[1 - k], self.descs, self.stored, defer_receive=True, buf=self.t & 1)
+        next(gen)                                         # wait T_seg, resolve, store terms into the stripe owners
+        peer.receive_halos(self.ops[1 - k], recvs)        # wait halo planes, unpack (+ occupancy of the box)
+        next(gen)                                         # wait terms, sum + colour map + stripes into every window
+        self.pending = gen
+        self.k, self.t = 1 - k, self.t + 1
+
+    def drain(self):
+        """Wait for the last issued frame; returns it."""
+        out = next(self.pending) if self.pending is not None else None
+        self.pending = None
+        return out
 
 
 def frame_steps(ops, params):
