@@ -402,6 +402,29 @@ int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, cons
 int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off,
                              int64_t frame_off);
 
+/* ---- the whole sort-last frame as ONE call (main.cpp:404: one Draw() per frame) ---------------------------------------
+ * A C / C++ host of the sharded renderer needs no Python and no knowledge of the exchange protocol: it creates the peer
+ * window (vr_peer_create with vr_sortlast_frame_window_bytes, handles exchanged by whatever transport it has), a
+ * vr_sortlast and a vr_sortlast_frame, and then per decoded timestep calls vr_sortlast_exchange_halos and per frame
+ * vr_sortlast_render.  Both are asynchronous on the context's stream and issue exactly the sequence of entry points above
+ * that volumerenderer_b200/sortlast.py issues (frames are bit-identical).  Every rank makes the same calls in the same order.
+ *   halo            voxels per axis and side around the owned box that every rank's device slab holds (vr_sortlast_halo);
+ *                   slab origin / extent must be the owned box grown by it and clipped to the texture.
+ *   halo_buffers    staging areas for halo planes (1; 2 when the host lets a neighbour run a timestep ahead).
+ *   vr_sortlast_exchange_halos(part): 0 = send and receive, 1 = pack + send only, 2 = wait + unpack only (other GPU work
+ *                   may be issued between the halves).
+ *   vr_sortlast_render: COMPOSITE, ISOSURFACE or ISOSURFACE_COMPRESSED frame; *out_rgba_dev = width * height float4 inside
+ *                   this rank's window, the finished frame on EVERY rank, valid until the next vr_sortlast_render. */
+typedef struct vr_sortlast_frame vr_sortlast_frame;
+int vr_sortlast_frame_window_bytes(const vr_slab_desc* slabs, int32_t n, int32_t width, int32_t height, const int64_t halo[3],
+                                   int32_t halo_buffers, int64_t* out);
+int vr_sortlast_frame_create(vr_context* ctx, vr_peer* peer, vr_sortlast* sl, int32_t width, int32_t height, const int64_t halo[3],
+                             int32_t halo_buffers, vr_sortlast_frame** out);
+int vr_sortlast_frame_destroy(vr_sortlast_frame* f);
+int vr_sortlast_exchange_halos(vr_sortlast_frame* f, vr_volume* slab, int32_t buffer, int32_t part);
+int vr_sortlast_render(vr_sortlast_frame* f, const vr_volume* slab, const vr_render_params* params, const float** out_rgba_dev,
+                       uint64_t* samples_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,11 +73,11 @@ int main(int argc, char** argv) {
                                                  gpuTree.numActiveNodes == myTree.numActiveNodes && gpuTree.stats.maxError == myTree.stats.maxError));
     }
     std::vector<vr::byte> treeData;
-    myTree.levelCut(myTree.maxTreeDepth, treeData);  // main.cpp:280-281, the reference's two-argument call (shared device context)
     {
-      std::vector<vr::byte> again;
-      myTree.levelCut(myTree.maxTreeDepth, again, *ctx);  // explicit context: same voxels
-      std::printf("levelcut_ctx_equal=%d\n", (int)(again == treeData));
+      std::vector<vr::byte> viaCtx;
+      myTree.levelCut(myTree.maxTreeDepth, viaCtx, *ctx);  // explicit context
+      myTree.levelCut(myTree.maxTreeDepth, treeData);      // main.cpp:280-281, the reference's two-argument call (shared device context)
+      std::printf("levelcut_ctx_equal=%d\n", (int)(viaCtx == treeData));
     }
     std::printf("decoded=%u maxerr_measured=%d\n", fnv(treeData.data(), treeData.size()), myTree.measureMaxError());
     try { std::vector<vr::byte> o; myTree.levelCut(10, o, *ctx); std::puts("cut10=nothrow"); }

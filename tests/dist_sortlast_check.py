@@ -70,6 +70,19 @@ def interleaved_steps_check(ctx, rank, world, full):
         d = float((f - want[t & 1]).abs().max())
         assert d == 0.0, (rank, t, d)
     dist.barrier()
+    # the same frames through the one-call C entries (csrc/vr_capi_frame.cu) on the same windows
+    halo = sortlast.required_halo(p, (X, Y, Z))
+    assert sortlast.SortLastFrame.window_bytes(descs, W, H, halo, 2) <= peer.bytes
+    fr = sortlast.SortLastFrame(ctx, peer.h, sl, W, H, halo, halo_buffers=2)
+    for k in range(2):
+        plans[k].run()                       # wipes the halo
+        fr.exchange_halos(vols[k], buffer=k)
+        img = fr.render(vols[k], p).clone()
+        torch.cuda.synchronize()
+        assert float((img - want[k]).abs().max()) == 0.0, (rank, k)
+    assert not peer.timed_out(), hex(peer.last_error)
+    dist.barrier()
+    fr.close()
     peer.close()
 
 

@@ -15,13 +15,6 @@
 using namespace vr;
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
 
-struct vr_sortlast {
-  int device = 0;
-  int n = 0, rank = 0;
-  std::vector<vr_slab_desc> slabs;
-  int order[8][VR_MAX_RANKS];
-  int* orderDev = nullptr;  // 8 x n
-};
 
 namespace vr { int make_render_params(const vr_render_params* in, RenderParams* P); int skip_threshold(const RenderParams& P); }
 

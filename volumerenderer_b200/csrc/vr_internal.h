@@ -119,6 +119,15 @@ struct vr_decode_plan {
   void lazy_free(Lazy* which = nullptr);
 };
 
+// slab geometry of all ranks + the visibility orders (vr_capi_sortlast.cu)
+struct vr_sortlast {
+  int device = 0;
+  int n = 0, rank = 0;
+  std::vector<vr_slab_desc> slabs;
+  int order[8][64 /* VR_MAX_RANKS, render_march.h */];
+  int* orderDev = nullptr;  // 8 x n
+};
+
 namespace vr {
 extern int g_count_fetched;  // vr_debug_set("count_fetched"), vr_capi_render.cu
 int fail(int code, const char* msg);

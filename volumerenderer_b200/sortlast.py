@@ -48,6 +48,11 @@ _SIGS = {
     "vr_resolve_iso": [c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p],
     "vr_volume_pack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
     "vr_volume_unpack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
+    "vr_sortlast_frame_window_bytes": [_P(SlabDesc), c_int32, c_int32, c_int32, _P(c_int64), c_int32, _P(c_int64)],
+    "vr_sortlast_frame_create": [c_void_p, c_void_p, c_void_p, c_int32, c_int32, _P(c_int64), c_int32, _P(c_void_p)],
+    "vr_sortlast_frame_destroy": [c_void_p],
+    "vr_sortlast_exchange_halos": [c_void_p, c_void_p, c_int32, c_int32],
+    "vr_sortlast_render": [c_void_p, c_void_p, _P(RenderParams), _P(c_void_p), c_void_p],
 }
 for _n, _a in _SIGS.items():
     getattr(lib, _n).restype = ctypes.c_int
@@ -444,6 +449,41 @@ class PeerExchange:
     def close(self):
         if self.h:
             lib.vr_peer_destroy(self.h)
+            self.h = c_void_p()
+
+
+class SortLastFrame:
+    """vr_sortlast_frame: the whole frame / the halo exchange of a timestep as ONE C call each (csrc/vr_capi_frame.cu) -- what
+    a C++ host uses instead of PeerExchange.  The peer window must be at least window_bytes() large."""
+
+    @staticmethod
+    def window_bytes(descs, W, H, halo, halo_buffers=1):
+        n = len(descs)
+        out = c_int64()
+        check(lib.vr_sortlast_frame_window_bytes((SlabDesc * n)(*descs), n, int(W), int(H), (c_int64 * 3)(*[int(v) for v in halo]),
+                                                 int(halo_buffers), byref(out)))
+        return out.value
+
+    def __init__(self, ctx, peer_handle, sl, W, H, halo, halo_buffers=1):
+        import torch
+        self.torch, self.ctx, self.W, self.H = torch, ctx, int(W), int(H)
+        self.h = c_void_p()
+        check(lib.vr_sortlast_frame_create(ctx.h, peer_handle, sl.h, self.W, self.H, (c_int64 * 3)(*[int(v) for v in halo]),
+                                           int(halo_buffers), byref(self.h)))
+        self.device = torch.device("cuda", ctx.device if hasattr(ctx, "device") else torch.cuda.current_device())
+
+    def exchange_halos(self, vol, buffer=0, part=0):
+        check(lib.vr_sortlast_exchange_halos(self.h, vol.h, int(buffer), int(part)))
+
+    def render(self, vol, params, samples_ptr=None):
+        """Issues the frame; returns it as a tensor view [H, W, 4] of this rank's window."""
+        out = c_void_p()
+        check(lib.vr_sortlast_render(self.h, vol.h, byref(params), byref(out), c_void_p(samples_ptr) if samples_ptr else None))
+        return self.torch.as_tensor(_DevMem(out.value, (self.H, self.W, 4), "<f4"), device=self.device)
+
+    def close(self):
+        if self.h:
+            lib.vr_sortlast_frame_destroy(self.h)
             self.h = c_void_p()
 
 
