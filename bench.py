@@ -334,9 +334,9 @@ def run_ours(args):
     t_setup = time.time()
     bricks, streams, _ = build_streams(vr, rank, threads)
     uniq = {id(s): s for s in streams}
-    for s in uniq.values():
-        s.pin()
-        s.upload(ctx)
+    # the timestep's stream images in ONE pinned buffer + ONE device buffer: a timestep is one H2D copy (vr_stream_arena)
+    arena0 = vr.StreamArena(ctx, list(uniq.values()))
+    arena0.upload(ctx)
     p = render.default_params(IMG, IMG, render.COMPOSITE)
     peer = None
     if world > 1:
@@ -568,8 +568,7 @@ def run_ours(args):
         return ms
 
     def serial_step():
-        for s in uniq.values():
-            s.upload(ctx)
+        arena0.upload(ctx)
         plan.run()
         img = frame()
         if rank == 0:
@@ -588,25 +587,24 @@ def run_ours(args):
     _, streams1, _ = build_streams(vr, rank, threads, t=1)
     uniq1 = {id(s): s for s in streams1}
     ctx_copy = vr.Context(local)  # its own CUDA stream
-    for s in uniq1.values():
-        s.pin(); s.upload(ctx_copy)
+    arena1 = vr.StreamArena(ctx_copy, list(uniq1.values()))
+    arena1.upload(ctx_copy)
     ctx_copy.synchronize()
     plans = [plan, vr.DecodePlan(ctx, streams1, origins, vol)]
     sets = [list(uniq.values()), list(uniq1.values())]
+    arenas = [arena0, arena1]
     host_imgs = [host_img, torch.empty((IMG, IMG, 4), dtype=torch.float32).pin_memory()]
-    h2d_sets = [sum(sum(s.device_bytes()) for s in ss) for ss in sets]
+    h2d_sets = [a.nbytes for a in arenas]  # what one upload copies
     h2d = sum(h2d_sets) / 2.0
 
     def streaming(n):
-        for s in sets[0]:
-            s.upload(ctx_copy)
+        arenas[0].upload(ctx_copy)
         for i in range(n):
             cur, nxt = i & 1, 1 - (i & 1)
             ctx.wait_for(ctx_copy)      # this step's streams have arrived
             ctx_copy.wait_for(ctx)      # the decode that last read the other set's device images is done
             if i + 1 < n:
-                for s in sets[nxt]:
-                    s.upload(ctx_copy)
+                arenas[nxt].upload(ctx_copy)   # ONE copy per timestep
             plans[cur].run()
             img = frame()
             if rank == 0:
@@ -619,6 +617,26 @@ def run_ours(args):
     streaming(e2e_steps)
     torch.cuda.synchronize()
     e2e_ms = reduce_max((time.time() - te) * 1e3 / e2e_steps)
+
+    # ---- what the host side of this box delivers: every rank copies its timestep arena H2D at the same time, nothing else
+    # running (the e2e legs above are bound by this link at every N)
+    ctx_copy.synchronize(); ctx.synchronize()
+    barrier()
+    reps = 10
+    tp = time.time()
+    for _ in range(reps):
+        arenas[0].upload(ctx_copy)
+    ctx_copy.synchronize()
+    my_gbs = arenas[0].nbytes * reps / (time.time() - tp) / 1e9
+    if world > 1:
+        tt = torch.tensor([my_gbs, -my_gbs, my_gbs], device=f"cuda:{local}", dtype=torch.float64)
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        h2d_probe = {"per_rank_gbs_max": float(mx[0].item()), "per_rank_gbs_min": float(-mx[1].item()), "aggregate_gbs": float(sm[2].item())}
+    else:
+        h2d_probe = {"per_rank_gbs_max": my_gbs, "per_rank_gbs_min": my_gbs, "aggregate_gbs": my_gbs}
+    h2d_probe["bytes_per_copy"] = arenas[0].nbytes
+    h2d_probe["note"] = "all ranks at once, 10 copies of the timestep arena (pinned) each, wall clock"
 
     # ---- cold end to end (N = 1): every step opens the timestep's containers from files (page cache), indexes them,
     # pins + uploads, plans, decodes, draws, reads the frame back -- nothing is reused between steps.  Two container
@@ -733,14 +751,15 @@ def run_ours(args):
         "roofline": dominant, "roofline_decode": roof_dec, "roofline_march": roof_mar,
         "e2e": {"value": voxels_all / e2e_ms / 1e6, "unit": "GVoxel/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                "mode": "streaming: timesteps t=0/t=1 alternate, H2D of the next timestep overlaps decode+frame of the current",
+                "mode": "streaming: timesteps t=0/t=1 alternate, H2D of the next timestep (one copy of its arena) overlaps decode+frame of the current",
+                "h2d_gbs": h2d * world / e2e_ms / 1e6, "h2d_probe": h2d_probe,
                 "serial": {"value": voxels_all / serial_ms / 1e6, "ms_per_step": serial_ms,
                            "h2d_bytes_per_step": int(h2d_sets[0])},
                 "cold": cold},
         # own kernels per step: decode, 3 occupancy refresh, march; N > 1 over NCCL: partial, resolve, finish instead of march;
         # N > 1 over peer windows (rank 0, one neighbour): decode, halo put + wait + box reduce, 3 occupancy, partial, gather put +
-        # wait, resolve, reduce-scatter put + wait + combine, all-gather put + wait, finish = 17
-        "debug_knobs": args.debug or None, "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "frame_check": frame_check, "gpu_launches": (5 if world == 1 else (17 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
+        # wait, T_in pass + wait, resolve, terms put + wait, sum + colour map + stripes, wait = 19
+        "debug_knobs": args.debug or None, "exchange": None if world == 1 else args.exchange, "cuda_graph": graph is not None, "pipelined": pair is not None, "frame_check": frame_check, "gpu_launches": (5 if world == 1 else (19 if peer is not None else 7)) * args.steps, "clocks": clocks, "setup_s": t_setup,
     }
     if extras:
         line["roofline_dense"] = extras.pop("roofline_dense")

@@ -94,10 +94,21 @@ int vr_stream_pin(vr_stream* s);
 int vr_stream_upload(vr_context* ctx, vr_stream* s);
 
 /* VolumeKdtree::open for a whole timestep (main.cpp:276-284 opens one tree per brick): `threads` host threads (0 = all
- * cores) open and parse the n container files and build their decode index while the calling thread pins and uploads
- * the streams in order as they become ready (ctx may be NULL: open + prepare only).  out receives n streams; on any
- * failure every stream is destroyed and the first error is returned (VR_ERR_IO missing / short file, VR_ERR_FORMAT). */
+ * cores) open the n container files -- plain containers are walked to build their decode index, indexed containers
+ * (vr_stream_save_indexed) bring it along -- and write the device images straight into the context's pinned staging
+ * buffer (kept between calls); then ONE device allocation and ONE H2D copy carry the whole set (ctx may be NULL: open +
+ * prepare only).  out receives n streams that share the allocation; on any failure every stream is destroyed and the
+ * first error is returned (VR_ERR_IO missing / short file, VR_ERR_FORMAT). */
 int vr_streams_load(vr_context* ctx, const char* const* paths, int32_t n, int32_t threads, vr_stream** out);
+/* The prepared images of n streams (a timestep) moved into ONE pinned host buffer and ONE device buffer, so that a
+ * timestep travels with one H2D copy instead of one per stream (VolumeReader::transferToGPU, VolumeReader.h:114-138, is
+ * one glTexImage3D of the assembled array).  Create the arena BEFORE the decode plans of these streams (their device
+ * addresses change).  The buffers live until the arena handle and every stream in it have been destroyed. */
+typedef struct vr_stream_arena vr_stream_arena;
+int vr_stream_arena_create(vr_context* ctx, vr_stream* const* streams, int32_t n, vr_stream_arena** out);
+int vr_stream_arena_upload(vr_context* ctx, vr_stream_arena* a); /* asynchronous on the context stream */
+int vr_stream_arena_bytes(const vr_stream_arena* a, int64_t* bytes);
+int vr_stream_arena_destroy(vr_stream_arena* a);
 
 /* ---- MidRangeTree's 4-bit/node shader stream (MidRangeTree::convertToByteArray, MidRangeTree.cpp:1095-1128) ----
  * byte k = tree[2k]<<6 | range[2k]<<4 | tree[2k+1]<<2 | range[2k+1]; length = next power of two >= ceil(n/2),
@@ -401,6 +412,18 @@ int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, cons
                               uint64_t* samples_dev);
 int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off,
                              int64_t frame_off);
+
+/* The all-gather of T_seg replaced by two stripe exchanges (what a rank needs of the others' T_seg is one number per
+ * pixel, the transmittance T_in in front of its own segment): every rank puts stripe j of its T_seg into rank j's window at
+ * gather_off + rank * 4*W*H/n; vr_peer_tin_composite (on rank j, after the wait) walks the segments of its stripe's pixels
+ * front to back -- the same order table and fp32 products as vr_resolve_composite -- and stores into EVERY rank r's window,
+ * at tin_off + 4 * pixel, the T_in of r's segment (-1 = the ray terminated in front of it), then raises `slot`;
+ * vr_resolve_composite_tin is pass 2 on that buffer (tin_dev = own window + tin_off) and this rank's own T_seg.  Same
+ * frame bit for bit, 2 (n-1)/n image-sized transfers per rank instead of n-1. */
+int vr_peer_tin_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_render_params* params,
+                          int64_t gather_off, int64_t tin_off);
+int vr_resolve_composite_tin(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                             const float* tin_dev, const float* tseg_dev, const float* cseg_dev, float* contrib_dev, uint64_t* samples_dev);
 
 /* ---- the whole sort-last frame as ONE call (main.cpp:404: one Draw() per frame) ---------------------------------------
  * A C / C++ host of the sharded renderer needs no Python and no knowledge of the exchange protocol: it creates the peer

@@ -94,3 +94,63 @@ def test_streams_load_uploads_and_decodes(ctx, tmp_path):
     for (ox, oy, oz), dec in zip(origins, want):
         assert np.array_equal(got[oz:oz + bz, oy:oy + by, ox:ox + bx], dec)
     plan.close(); vol.close()
+
+
+def _six_bricks(tmp_path, indexed):
+    bx, by, bz = 64, 64, 32
+    paths, want, origins, streams = [], [], [], []
+    for b in range(6):
+        i, k = b % 3, b // 3
+        brick = synth.rm_region(640 + i * bx, 900, 930 + k * bz, bx, by, bz) if b != 4 else synth.constant_brick((bx, by, bz), 61)
+        s, _ = vr.Stream.compress(brick, 1, 2)
+        p = tmp_path / (f"tree{b}.kdx" if indexed(b) else f"tree{b}.bin")
+        (s.save_indexed if indexed(b) else s.save)(p)
+        paths.append(p)
+        hd = s.header
+        rc, dec = oa.oracle_levelcut(s.bits, hd.numActiveNodes, s.distance_map, hd.origTreeDepth, hd.maxTreeDepth, bx, by, bz)
+        assert rc == 0
+        want.append(dec); origins.append((i * bx, 0, k * bz)); streams.append(s)
+    return (bx, by, bz), paths, want, origins, streams
+
+
+def _decodes(ctx, dims, streams, origins, want):
+    bx, by, bz = dims
+    vol = vr.Volume(ctx, 3 * bx, by, 2 * bz)
+    plan = vr.DecodePlan(ctx, streams, origins, vol)
+    plan.run()
+    got = vol.download()
+    for (ox, oy, oz), dec in zip(origins, want):
+        assert np.array_equal(got[oz:oz + bz, oy:oy + by, ox:ox + bx], dec)
+    plan.close(); vol.close()
+
+
+def test_streams_load_mixed_containers_repeatedly(ctx, tmp_path):
+    """Plain and indexed containers in one load (one allocation + one H2D copy per call, the pinned staging buffer reused):
+    three loads in a row, earlier sets still decodable after later loads (they own their device memory)."""
+    dims, paths, want, origins, _ = _six_bricks(tmp_path, lambda b: b % 2 == 0)
+    sets = [vr.load_streams(paths, ctx, threads=3) for _ in range(3)]
+    for ss in sets:
+        _decodes(ctx, dims, ss, origins, want)
+    for s in sets[1]:
+        s.close()
+    _decodes(ctx, dims, sets[0], origins, want)
+    # a loaded stream can still be saved / validated / moved to a fresh upload
+    s = sets[2][1]
+    assert s.validate() == s.header.numActiveNodes
+    s.pin(); s.upload(ctx)
+    _decodes(ctx, dims, sets[2], origins, want)
+
+
+def test_stream_arena_one_copy_per_timestep(ctx, tmp_path):
+    dims, paths, want, origins, streams = _six_bricks(tmp_path, lambda b: False)
+    shared = streams + [streams[0]]  # a stream may appear twice in a plan (constant bricks share one)
+    arena = vr.StreamArena(ctx, shared)
+    assert arena.nbytes >= sum(sum(s.device_bytes()) for s in streams)
+    arena.upload(ctx)
+    _decodes(ctx, dims, streams, origins, want)
+    arena.upload(ctx)  # again: every step of a streaming loop
+    _decodes(ctx, dims, streams, origins, want)
+    arena.close()      # the buffers live on with the streams
+    _decodes(ctx, dims, streams, origins, want)
+    streams[2].upload(ctx)  # a single stream can still be re-uploaded on its own (into its slice)
+    _decodes(ctx, dims, streams, origins, want)

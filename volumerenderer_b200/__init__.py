@@ -5,7 +5,7 @@ Importing this package loads the CUDA library; it raises if the library was not 
 """
 from . import _lib, render, sortlast, synth  # noqa: F401
 from ._lib import VrError  # noqa: F401
-from .kdtree import Context, DecodePlan, Stream, Volume, VolumeKdtree, load_streams, mrt_open, mrt_save, nibbles_pack, nibbles_unpack  # noqa: F401
+from .kdtree import Context, DecodePlan, Stream, StreamArena, Volume, VolumeKdtree, load_streams, mrt_open, mrt_save, nibbles_pack, nibbles_unpack  # noqa: F401
 from .loader import VolumeReader  # noqa: F401
 
 

@@ -113,6 +113,10 @@ _SIGS = {
     "vr_kd_levelcut": (c_int, [c_void_p, c_void_p, c_int32, c_void_p]),
     "vr_volume_load_bricks": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32, POINTER(c_int64), c_void_p, c_void_p,
                                       POINTER(c_int64), c_void_p, POINTER(c_int64)]),
+    "vr_stream_arena_create": (c_int, [c_void_p, POINTER(c_void_p), c_int32, POINTER(c_void_p)]),
+    "vr_stream_arena_upload": (c_int, [c_void_p, c_void_p]),
+    "vr_stream_arena_bytes": (c_int, [c_void_p, POINTER(c_int64)]),
+    "vr_stream_arena_destroy": (c_int, [c_void_p]),
     "vr_streams_load": (c_int, [c_void_p, POINTER(c_char_p), c_int32, c_int32, POINTER(c_void_p)]),
 }
 FIND_SOURCE_FILE = ctypes.CFUNCTYPE(c_void_p, c_int32, c_int32, c_void_p)  # returns the address of a NUL-terminated path

@@ -62,6 +62,13 @@ cudaError_t partial_composite_peer_launch(const RenderParams& P, const SlabGeom&
 cudaError_t resolve_composite_peer_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol,
                                           const float* tsegAll, const int* order, const float* cseg, const PeerTargets& t,
                                           long long redOff, unsigned long long* sampleCount, cudaStream_t stream);
+// T_in exchange (replaces the all-gather of T_seg): the stripe owner walks its pixels' segments front to back and stores to every
+// rank r the transmittance in front of r's segment (-1: terminated in front) at window[r] + tinOff; then the pass-2 kernel on T_in
+cudaError_t tin_stripe_peer_launch(const RenderParams& P, const int* order, const PeerTargets& t, long long gatherOff, long long tinOff,
+                                   cudaStream_t stream);
+cudaError_t resolve_composite_tin_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, const float* tin,
+                                         const float* tseg, int n, int rank, const int* order, const float* cseg, float2* contrib,
+                                         unsigned long long* sampleCount, cudaStream_t stream);
 // pass 3 (stripe owner): sum of the n terms in rank order + colour map -> RGBA of the stripe into every window + frameOff
 cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff,
                                          cudaStream_t stream);

@@ -272,6 +272,83 @@ __global__ void __launch_bounds__(256) resolve_composite_peer_kernel(const __gri
   peer_signal(t);
 }
 
+// ---- the all-gather of T_seg replaced by two stripe exchanges ---------------------------------------------------------
+// What a rank needs from the other ranks' T_seg is one number per pixel: the transmittance T_in in front of its own
+// segment (or the fact that the ray has terminated in front of it).  So instead of every rank storing its whole T_seg into
+// every window (n - 1 image-sized transfers per rank), stripe j of every rank's T_seg goes to rank j, which walks the
+// segments of its pixels front to back exactly as resolve_pixel does (same order table, same fp32 products) and stores to
+// every rank r the T_in of r's segment: 2 (n - 1) / n image-sized transfers per rank in total.
+// Encoding: T_in >= 0 = the transmittance in front of the segment; -1 = the ray terminated in a slab in front.
+__global__ void __launch_bounds__(256) tin_stripe_peer_kernel(const __grid_constant__ RenderParams P, const int* __restrict__ order,
+                                                              const __grid_constant__ PeerTargets t, long long gatherOff, long long tinOff) {
+  const long long stripe = ((long long)P.W * P.H) / t.n;
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < stripe) {
+    const long long pix = (long long)t.rank * stripe + k;
+    const float* in = reinterpret_cast<const float*>(t.base[t.rank] + gatherOff);  // n stripes, rank-major
+    V3 vUV;
+    if (ray_setup(P, (int)(pix % P.W), (int)(pix / P.W), &vUV)) {
+      V3 dir, dirStep;
+      ray_dir(P, vUV, &dir, &dirStep);
+      const int oct = (dirStep.x < 0.0f ? 1 : 0) | (dirStep.y < 0.0f ? 2 : 0) | (dirStep.z < 0.0f ? 4 : 0);
+      const int* ord = order + oct * t.n;
+      float T = 1.0f;
+      bool crossed = false;
+      for (int q = 0; q < t.n; ++q) {
+        const int r = __ldg(ord + q);
+        reinterpret_cast<float*>(t.base[r] + tinOff)[pix] = crossed ? -1.0f : T;
+        T = fmul(T, in[(long long)r * stripe + k]);
+        if (!crossed && fsub(1.0f, T) > 0.99f) crossed = true;
+      }
+    } else {
+      for (int r = 0; r < t.n; ++r) reinterpret_cast<float*>(t.base[r] + tinOff)[pix] = -1.0f;  // the ray misses the cube: no terms
+    }
+  }
+  peer_signal(t);
+}
+
+// resolve_pixel with T_in given instead of all ranks' T_seg (same decisions, same arithmetic)
+template <bool OCC>
+__global__ void __launch_bounds__(256) resolve_composite_tin_kernel(const __grid_constant__ RenderParams P,
+                                                                    const __grid_constant__ SlabGeom g,
+                                                                    const __grid_constant__ OccView occ,
+                                                                    const uint8_t* __restrict__ vol, const float* __restrict__ tin,
+                                                                    const float* __restrict__ tseg, int nRanks, int rank,
+                                                                    const int* __restrict__ order, const float* __restrict__ cseg,
+                                                                    float2* __restrict__ contrib,
+                                                                    unsigned long long* __restrict__ sampleCount) {
+  int px, py;
+  unsigned n = 0;
+  if (pixel_of_thread(P, &px, &py)) {
+    const long long pix = (long long)py * P.W + px;
+    float2 term = make_float2(0.0f, 0.0f);
+    const float Tin = __ldg(tin + pix);
+    V3 vUV;
+    if (Tin >= 0.0f && ray_setup(P, px, py, &vUV)) {
+      V3 dir, dirStep;
+      ray_dir(P, vUV, &dir, &dirStep);
+      const float Tseg = __ldg(tseg + pix);
+      const float Tout = fmul(Tin, Tseg);
+      if (fsub(1.0f, Tout) > 0.99f) {           // the ray terminates inside this segment
+        if (Tin == 1.0f) {                      // nothing in front: pass 1 already ran the reference recurrence from A = 0
+          term = make_float2(__ldg(cseg + pix), fsub(1.0f, Tseg));
+        } else {                                // replay it with the reference recurrence from A_in
+          Vol v = make_vol(g, vol);
+          float C = 0.0f, A = fsub(1.0f, Tin);
+          march_segment<OCC>(v, occ, vUV, dirStep, &C, &A, &n);
+          term = make_float2(C, A);
+        }
+      } else {
+        term.x = fmul(Tin, __ldg(cseg + pix));
+        const int oct = (dirStep.x < 0.0f ? 1 : 0) | (dirStep.y < 0.0f ? 2 : 0) | (dirStep.z < 0.0f ? 4 : 0);
+        if (__ldg(order + oct * nRanks + nRanks - 1) == rank) term.y = fsub(1.0f, Tout);  // no termination anywhere: last slab closes alpha
+      }
+    }
+    contrib[pix] = term;
+  }
+  count_samples(sampleCount, n);
+}
+
 // One thread per pixel of this rank's stripe: the ranks' terms in rank order, then the colour map (finish_composite_kernel).
 __global__ void __launch_bounds__(256) finish_composite_peer_kernel(const __grid_constant__ RenderParams P,
                                                                     const __grid_constant__ PeerTargets t, long long redOff, long long frameOff) {
@@ -363,6 +440,19 @@ cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTarget
                                          cudaStream_t stream) {
   const long long stripe = ((long long)P.W * P.H) / t.n;
   finish_composite_peer_kernel<<<dim3((unsigned)((stripe + 255) / 256), 1), 256, 0, stream>>>(P, t, redOff, frameOff);
+  return cudaGetLastError();
+}
+cudaError_t tin_stripe_peer_launch(const RenderParams& P, const int* order, const PeerTargets& t, long long gatherOff, long long tinOff,
+                                   cudaStream_t stream) {
+  const long long stripe = ((long long)P.W * P.H) / t.n;
+  tin_stripe_peer_kernel<<<dim3((unsigned)((stripe + 255) / 256), 1), 256, 0, stream>>>(P, order, t, gatherOff, tinOff);
+  return cudaGetLastError();
+}
+cudaError_t resolve_composite_tin_launch(const RenderParams& P, const SlabGeom& g, const OccView& occ, const uint8_t* vol, const float* tin,
+                                         const float* tseg, int n, int rank, const int* order, const float* cseg, float2* contrib,
+                                         unsigned long long* sampleCount, cudaStream_t stream) {
+  if (occ.pyr) resolve_composite_tin_kernel<true><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tin, tseg, n, rank, order, cseg, contrib, sampleCount);
+  else resolve_composite_tin_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tin, tseg, n, rank, order, cseg, contrib, sampleCount);
   return cudaGetLastError();
 }
 cudaError_t finish_composite_launch(const RenderParams& P, const float2* sum, float4* out, cudaStream_t stream) {

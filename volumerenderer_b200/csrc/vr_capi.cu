@@ -60,6 +60,8 @@ int vr_context_destroy(vr_context* c) {
   if (c->side.join) cudaEventDestroy(c->side.join);
   vr::kd_builder_destroy(c->builder);
   cudaFree(c->frameDev); cudaFree(c->frameHitDev); cudaFree(c->frameCountDev);
+  if (c->stagingDone) { cudaEventSynchronize(c->stagingDone); cudaEventDestroy(c->stagingDone); }
+  if (c->stagingHost) cudaFreeHost(c->stagingHost);
   delete c;
   return VR_OK;
 }

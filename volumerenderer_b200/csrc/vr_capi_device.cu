@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <new>
 
 #include "../../include/vr_b200.h"
@@ -20,15 +21,27 @@ using namespace vr;
 
 static inline size_t align16(size_t v) { return (v + 15) & ~size_t(15); }
 
+vr::ArenaMem::~ArenaMem() {
+  if (host) cudaFreeHost(host);
+  if (dev) { if (device >= 0) cudaSetDevice(device); cudaFree(dev); }
+}
+void vr_stream::drop_host() {
+  if (hostImage && hostOwned) { if (pinned) cudaFreeHost(hostImage); else delete[] hostImage; }
+  hostImage = nullptr; pinned = false; hostOwned = true;
+  if (devOwned || !devImage) arena.reset();
+}
+void vr_stream::drop_dev() {
+  if (devImage && devOwned) { if (device >= 0) cudaSetDevice(device); cudaFree(devImage); }
+  devImage = nullptr; devOwned = true;
+  if (hostOwned || !hostImage) arena.reset();
+}
 void vr_stream::release() {
-  if (devImage) { if (device >= 0) cudaSetDevice(device); cudaFree(devImage); devImage = nullptr; }
-  if (hostImage) { if (pinned) cudaFreeHost(hostImage); else delete[] hostImage; hostImage = nullptr; }
-  pinned = false;
+  drop_dev();
+  drop_host();
 }
 
 namespace vr {
-int stream_build_image(vr_stream* s) {
-  if (s->hostImage) return VR_OK;
+int stream_image_layout(vr_stream* s) {
   if (!s->kd.index.built) {
     int rc = kd_prepare(&s->kd);
     if (rc != VR_OK) return fail(rc, "vr_stream_prepare: stream does not parse");
@@ -41,14 +54,29 @@ int stream_build_image(vr_stream* s) {
   s->offTileVal = s->offLeafOff + align16(ix.leafOff.size() * 4);
   s->offLeafVal = s->offTileVal + align16(ix.tileVal.size());
   s->imageBytes = s->offLeafVal + align16(ix.leafVal.size());
+  return VR_OK;
+}
+void stream_image_write(const vr_stream* s, uint8_t* dst) {
+  const KdIndex& ix = s->kd.index;
+  // zero only the gaps: the pad behind the stream and the alignment tails of the sections
+  auto put = [&](size_t off, const void* src, size_t n, size_t end) {
+    if (n) std::memcpy(dst + off, src, n);
+    std::memset(dst + off + n, 0, end - (off + n));
+  };
+  put(s->offWords, s->kd.bits.data(), (size_t)s->kd.streamBytes(), s->offTile);
+  put(s->offTile, ix.tileLeafBlock.data(), ix.tileLeafBlock.size() * 4, s->offLeafOff);
+  put(s->offLeafOff, ix.leafOff.data(), ix.leafOff.size() * 4, s->offTileVal);
+  put(s->offTileVal, ix.tileVal.data(), ix.tileVal.size(), s->offLeafVal);
+  put(s->offLeafVal, ix.leafVal.data(), ix.leafVal.size(), s->imageBytes);
+}
+int stream_build_image(vr_stream* s) {
+  if (s->hostImage) return VR_OK;
+  int rc = stream_image_layout(s);
+  if (rc != VR_OK) return rc;
   s->hostImage = new (std::nothrow) uint8_t[s->imageBytes];
   if (!s->hostImage) return fail(VR_ERR_ARG, "out of host memory");
-  std::memset(s->hostImage, 0, s->imageBytes);
-  std::memcpy(s->hostImage + s->offWords, s->kd.bits.data(), (size_t)s->kd.streamBytes());
-  std::memcpy(s->hostImage + s->offTile, ix.tileLeafBlock.data(), ix.tileLeafBlock.size() * 4);
-  if (!ix.leafOff.empty()) std::memcpy(s->hostImage + s->offLeafOff, ix.leafOff.data(), ix.leafOff.size() * 4);
-  std::memcpy(s->hostImage + s->offTileVal, ix.tileVal.data(), ix.tileVal.size());
-  if (!ix.leafVal.empty()) std::memcpy(s->hostImage + s->offLeafVal, ix.leafVal.data(), ix.leafVal.size());
+  s->hostOwned = true;
+  stream_image_write(s, s->hostImage);
   return VR_OK;
 }
 }  // namespace vr
@@ -91,9 +119,10 @@ int vr_stream_pin(vr_stream* s) {
   uint8_t* p = nullptr;
   CU(cudaHostAlloc((void**)&p, s->imageBytes, cudaHostAllocDefault));
   std::memcpy(p, s->hostImage, s->imageBytes);
-  delete[] s->hostImage;
+  s->drop_host();
   s->hostImage = p;
   s->pinned = true;
+  s->hostOwned = true;
   return VR_OK;
 }
 int vr_stream_upload(vr_context* ctx, vr_stream* s) {
@@ -101,9 +130,67 @@ int vr_stream_upload(vr_context* ctx, vr_stream* s) {
   int rc = stream_build_image(s);
   if (rc != VR_OK) return rc;
   CU(cudaSetDevice(ctx->device));
-  if (s->devImage && s->device != ctx->device) { cudaSetDevice(s->device); cudaFree(s->devImage); s->devImage = nullptr; cudaSetDevice(ctx->device); }
-  if (!s->devImage) { CU(cudaMalloc((void**)&s->devImage, s->imageBytes)); s->device = ctx->device; }
+  if (s->devImage && s->device != ctx->device) { s->drop_dev(); cudaSetDevice(ctx->device); }
+  if (!s->devImage) { CU(cudaMalloc((void**)&s->devImage, s->imageBytes)); s->device = ctx->device; s->devOwned = true; }
   CU(cudaMemcpyAsync(s->devImage, s->hostImage, s->imageBytes, cudaMemcpyHostToDevice, ctx->stream));
+  return VR_OK;
+}
+
+// ---- stream arenas: the images of a timestep in one pinned buffer and one device buffer, ONE copy per upload ----------
+struct vr_stream_arena {
+  std::shared_ptr<vr::ArenaMem> mem;
+  size_t used = 0;
+  int nStreams = 0;
+};
+int vr_stream_arena_create(vr_context* ctx, vr_stream* const* streams, int32_t n, vr_stream_arena** out) {
+  if (!ctx || !streams || n <= 0 || !out) return fail(VR_ERR_ARG, "vr_stream_arena_create: bad argument");
+  std::vector<vr_stream*> uniq;
+  for (int i = 0; i < n; ++i) {
+    if (!streams[i]) return fail(VR_ERR_ARG, "vr_stream_arena_create: null stream");
+    if (std::find(uniq.begin(), uniq.end(), streams[i]) == uniq.end()) uniq.push_back(streams[i]);
+  }
+  size_t total = 0;
+  std::vector<size_t> off(uniq.size());
+  for (size_t i = 0; i < uniq.size(); ++i) {
+    int rc = stream_image_layout(uniq[i]);
+    if (rc != VR_OK) return rc;
+    off[i] = total;
+    total += (uniq[i]->imageBytes + 255) & ~size_t(255);
+  }
+  CU(cudaSetDevice(ctx->device));
+  auto mem = std::make_shared<vr::ArenaMem>();
+  mem->device = ctx->device; mem->bytes = total;
+  CU(cudaHostAlloc((void**)&mem->host, total, cudaHostAllocDefault));
+  CU(cudaMalloc((void**)&mem->dev, total));
+  for (size_t i = 0; i < uniq.size(); ++i) {
+    vr_stream* s = uniq[i];
+    if (s->hostImage) std::memcpy(mem->host + off[i], s->hostImage, s->imageBytes);
+    else stream_image_write(s, mem->host + off[i]);
+    s->drop_host();
+    s->drop_dev();
+    s->hostImage = mem->host + off[i]; s->pinned = true; s->hostOwned = false;
+    s->devImage = mem->dev + off[i]; s->device = ctx->device; s->devOwned = false;
+    s->arena = mem;
+  }
+  vr_stream_arena* a = new vr_stream_arena;
+  a->mem = mem; a->used = total; a->nStreams = (int)uniq.size();
+  *out = a;
+  return VR_OK;
+}
+int vr_stream_arena_upload(vr_context* ctx, vr_stream_arena* a) {
+  if (!ctx || !a) return fail(VR_ERR_ARG, "vr_stream_arena_upload: null argument");
+  if (ctx->device != a->mem->device) return fail(VR_ERR_ARG, "vr_stream_arena_upload: the arena lives on another device");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(a->mem->dev, a->mem->host, a->used, cudaMemcpyHostToDevice, ctx->stream));
+  return VR_OK;
+}
+int vr_stream_arena_bytes(const vr_stream_arena* a, int64_t* bytes) {
+  if (!a || !bytes) return fail(VR_ERR_ARG, "null");
+  *bytes = (int64_t)a->used;
+  return VR_OK;
+}
+int vr_stream_arena_destroy(vr_stream_arena* a) {
+  delete a;  // the buffers live until the last stream that points into them is destroyed
   return VR_OK;
 }
 

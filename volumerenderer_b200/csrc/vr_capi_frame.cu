@@ -5,8 +5,9 @@
 // include/vr_b200.h on the context's stream -- the same sequence sortlast.PeerExchange issues, so frames are bit-identical.
 //
 // Window layout (bytes; P = width * height, n ranks), identical on all ranks:
-//   [0, 4Pn)            gather: the n ranks' T_seg (composite) -- slot 0
-//   [4Pn, 4Pn + 16P)    stripes-in: n stripes of this rank's stripe of the terms being combined -- slot 1
+//   [0, 4Pn)            gather: this rank's stripe of the n ranks' T_seg in its first 4P bytes (composite) -- slot 0
+//   [4Pn, 4Pn + 16P)    stripes-in: n stripes of this rank's stripe of the terms being combined -- slot 1; composite terms use
+//                       8P of it, the other half holds T_in (slot 4)
 //   [.., + 16P)         total: the combined buffer / the finished RGBA frame -- slot 2
 //   [.., + B * halo)    B halo staging areas -- slot 3
 #include <cuda_runtime.h>
@@ -23,7 +24,7 @@ using namespace vr;
 #define RC(call) do { int rc_ = (call); if (rc_ != VR_OK) return rc_; } while (0)
 
 namespace {
-enum { SLOT_GATHER = 0, SLOT_RED_IN = 1, SLOT_RED_OUT = 2, SLOT_HALO = 3 };
+enum { SLOT_GATHER = 0, SLOT_RED_IN = 1, SLOT_RED_OUT = 2, SLOT_HALO = 3, SLOT_TIN = 4 };
 inline int64_t pad16(int64_t v) { return (v + 15) / 16 * 16; }
 
 struct HaloBox { int src, dst; int64_t lo[3], ext[3], bytes; };
@@ -219,15 +220,21 @@ int vr_sortlast_render(vr_sortlast_frame* f, const vr_volume* slab, const vr_ren
   all_ranks(f, &everyone);
   const int n = f->n;
   if (params->mode == VR_MODE_COMPOSITE) {
-    // pass 1, all-gather of T_seg by stores, pass 2, terms to the stripe owners, sum + colour map + stripes to every window
+    // pass 1; T_seg stripes to their owners, which hand every rank the transmittance in front of its segment
+    // (vr_peer_tin_composite: two stripe exchanges instead of an all-gather of whole images); pass 2; terms to the stripe
+    // owners; sum + colour map + stripes to every window
     RC(vr_partial_composite(f->ctx, f->sl, slab, params, f->cseg, f->tseg, samples_dev));
-    const int64_t nb = 4 * f->P;
-    std::vector<int64_t> off((size_t)n), bytes((size_t)n, nb);
+    const int64_t s4 = 4 * f->P / n;
+    std::vector<int64_t> off((size_t)n), bytes((size_t)n, s4);
     std::vector<const void*> ptr((size_t)n);
-    for (int r = 0; r < n; ++r) { off[(size_t)r] = f->offGather + f->rank * nb; ptr[(size_t)r] = f->tseg; }
+    for (int j = 0; j < n; ++j) { off[(size_t)j] = f->offGather + f->rank * s4; ptr[(size_t)j] = (const uint8_t*)f->tseg + j * s4; }
     RC(vr_peer_put(f->peer, SLOT_GATHER, n, everyone.data(), off.data(), ptr.data(), bytes.data()));
     RC(vr_peer_wait(f->peer, SLOT_GATHER, n, everyone.data()));
-    RC(vr_resolve_composite(f->ctx, f->sl, slab, params, reinterpret_cast<const float*>(f->base + f->offGather), f->cseg, f->contrib, samples_dev));
+    const int64_t offTin = f->offRedIn + 8 * f->P;  // the half of the stripes-in area the composite terms do not use
+    RC(vr_peer_tin_composite(f->ctx, f->peer, SLOT_TIN, f->sl, params, f->offGather, offTin));
+    RC(vr_peer_wait(f->peer, SLOT_TIN, n, everyone.data()));
+    RC(vr_resolve_composite_tin(f->ctx, f->sl, slab, params, reinterpret_cast<const float*>(f->base + offTin), f->tseg, f->cseg, f->contrib,
+                                samples_dev));
     const int64_t sb = 8 * f->P / n;
     for (int j = 0; j < n; ++j) { off[(size_t)j] = f->offRedIn + f->rank * sb; ptr[(size_t)j] = (const uint8_t*)f->contrib + j * sb; bytes[(size_t)j] = sb; }
     RC(vr_peer_put(f->peer, SLOT_RED_IN, n, everyone.data(), off.data(), ptr.data(), bytes.data()));

@@ -15,6 +15,7 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -170,49 +171,66 @@ int vr_streams_load(vr_context* ctx, const char* const* paths, int32_t n, int32_
   if (threads <= 0) threads = 4;
   if (threads > n) threads = n;
   if (ctx) CU(cudaSetDevice(ctx->device));
-  // workers: open (VolumeKdtree::open) + grammar walk / decode index + host image, any order; the calling thread
-  // uploads stream i as soon as streams 0..i are ready, so H2D copies overlap the parsing of the later files
-  std::vector<int> state((size_t)n, 0);  // 0 = pending, 1 = ready, < 0 = -error
-  std::mutex mu;
-  std::condition_variable cv;
-  std::atomic<int> next(0);
-  std::atomic<bool> abort(false);
-  std::vector<std::thread> pool;
-  for (int w = 0; w < threads; ++w)
-    pool.emplace_back([&]() {
-      for (;;) {
-        const int i = next.fetch_add(1);
-        if (i >= n || abort.load()) return;
-        vr_stream* s = new vr_stream;
-        int rc = kd_open_any(paths[i], &s->kd);  // an indexed container (kd_kdx.cpp) brings its index: no walk
-        if (rc == VR_OK) rc = stream_build_image(s);
-        std::lock_guard<std::mutex> lk(mu);
-        if (rc != VR_OK) { s->release(); delete s; state[(size_t)i] = -rc; abort.store(true); }
-        else { out[i] = s; state[(size_t)i] = 1; }
-        cv.notify_all();
-      }
-    });
+  // Phase 1, workers: open (VolumeKdtree::open; an indexed container brings its index, a plain one is walked) and lay out the
+  // device image.  Phase 2, workers again: write every image straight into its slice of the context's pinned staging buffer.
+  // Then ONE device allocation and ONE H2D copy for the whole set (a timestep): the streams share the allocation.
+  std::vector<int> err((size_t)n, VR_OK);
+  auto run_pool = [&](auto&& fn) {
+    std::atomic<int> next(0);
+    std::vector<std::thread> pool;
+    for (int w = 0; w < threads; ++w)
+      pool.emplace_back([&]() {
+        for (;;) {
+          const int i = next.fetch_add(1);
+          if (i >= n) return;
+          fn(i);
+        }
+      });
+    for (auto& t : pool) t.join();
+  };
+  run_pool([&](int i) {
+    vr_stream* s = new vr_stream;
+    int rc = kd_open_any(paths[i], &s->kd);
+    if (rc == VR_OK) rc = ctx ? stream_image_layout(s) : stream_build_image(s);
+    if (rc != VR_OK) { delete s; err[(size_t)i] = rc; return; }
+    out[i] = s;
+  });
   int rc = VR_OK, bad = -1;
-  for (int i = 0; i < n && rc == VR_OK; ++i) {
-    {
-      std::unique_lock<std::mutex> lk(mu);
-      cv.wait(lk, [&] { return state[(size_t)i] != 0 || abort.load(); });
-      if (state[(size_t)i] < 0) { rc = -state[(size_t)i]; bad = i; break; }
-      if (state[(size_t)i] == 0) {  // another file failed: find it
-        for (int k = 0; k < n; ++k) if (state[(size_t)k] < 0) { rc = -state[(size_t)k]; bad = k; }
-        if (rc == VR_OK) rc = VR_ERR_IO;
-        break;
+  for (int i = 0; i < n && rc == VR_OK; ++i)
+    if (err[(size_t)i] != VR_OK) { rc = err[(size_t)i]; bad = i; }
+  std::string cudaMsg;
+  if (rc == VR_OK && ctx) {
+    std::vector<size_t> off((size_t)n);
+    size_t total = 0;
+    for (int i = 0; i < n; ++i) { off[(size_t)i] = total; total += (out[i]->imageBytes + 255) & ~size_t(255); }
+    cudaError_t e = cudaSuccess;
+    if (!ctx->stagingDone) e = cudaEventCreateWithFlags(&ctx->stagingDone, cudaEventDisableTiming);
+    else e = cudaEventSynchronize(ctx->stagingDone);  // the previous load's copy has left the staging buffer
+    if (e == cudaSuccess && total > ctx->stagingBytes) {
+      if (ctx->stagingHost) cudaFreeHost(ctx->stagingHost);
+      ctx->stagingHost = nullptr; ctx->stagingBytes = 0;
+      const size_t want = total + total / 4;  // room to grow: pinning is the expensive part of a cold load
+      e = cudaHostAlloc((void**)&ctx->stagingHost, want, cudaHostAllocDefault);
+      if (e == cudaSuccess) ctx->stagingBytes = want;
+    }
+    auto mem = std::make_shared<vr::ArenaMem>();
+    mem->device = ctx->device; mem->bytes = total;
+    if (e == cudaSuccess) e = cudaMalloc((void**)&mem->dev, total);
+    if (e == cudaSuccess) {
+      uint8_t* stage = ctx->stagingHost;
+      run_pool([&](int i) { stream_image_write(out[i], stage + off[(size_t)i]); });
+      e = cudaMemcpyAsync(mem->dev, stage, total, cudaMemcpyHostToDevice, ctx->stream);
+      if (e == cudaSuccess) e = cudaEventRecord(ctx->stagingDone, ctx->stream);
+    }
+    if (e != cudaSuccess) { rc = VR_ERR_CUDA; bad = -2; cudaMsg = std::string("vr_streams_load: ") + cudaGetErrorString(e); }
+    else
+      for (int i = 0; i < n; ++i) {
+        vr_stream* s = out[i];
+        s->devImage = mem->dev + off[(size_t)i]; s->device = ctx->device; s->devOwned = false; s->arena = mem;
       }
-    }
-    if (ctx) {
-      int urc = vr_stream_pin(out[i]);
-      if (urc == VR_OK) urc = vr_stream_upload(ctx, out[i]);
-      if (urc != VR_OK) { rc = urc; bad = -2; abort.store(true); }
-    }
   }
-  for (auto& t : pool) t.join();
   if (rc != VR_OK) {
-    std::string msg = bad == -2 ? std::string(vr_last_error()) : "vr_streams_load: cannot open / parse " + std::string(bad >= 0 ? paths[bad] : "?");
+    std::string msg = bad == -2 ? cudaMsg : "vr_streams_load: cannot open / parse " + std::string(bad >= 0 ? paths[bad] : "?");
     if (ctx) cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < n; ++i) { vr_stream_destroy(out[i]); out[i] = nullptr; }
     return fail(rc, msg.c_str());

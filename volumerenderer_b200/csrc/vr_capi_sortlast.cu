@@ -248,6 +248,33 @@ int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, cons
   return VR_OK;
 }
 
+int vr_peer_tin_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_sortlast* sl, const vr_render_params* params,
+                          int64_t gather_off, int64_t tin_off) {
+  if (!peer) return fail(VR_ERR_ARG, "null argument");
+  const vr_volume* slab = nullptr;
+  SL_PROLOGUE(false)
+  { int rc_ = order_on_device(ctx, const_cast<vr_sortlast*>(sl)); if (rc_ != VR_OK) return rc_; }
+  PeerTargets t;
+  int64_t wb = 0;
+  { int rc_ = peer_targets(peer, slot, &t, &wb); if (rc_ != VR_OK) return rc_; }
+  const int64_t npix = (int64_t)P.W * P.H;
+  if (t.n != sl->n || t.rank != sl->rank || npix % t.n || ((4 * npix / t.n) & 15) || gather_off < 0 || tin_off < 0 || (gather_off & 15) ||
+      (tin_off & 15) || gather_off + 4 * npix > wb || tin_off + 4 * npix > wb)
+    return fail(VR_ERR_ARG, "vr_peer_tin_composite: window too small, ranks differ or image not divisible into stripes");
+  CU(tin_stripe_peer_launch(P, sl->orderDev, t, gather_off, tin_off, ctx->stream));
+  return VR_OK;
+}
+
+int vr_resolve_composite_tin(vr_context* ctx, const vr_sortlast* sl, const vr_volume* slab, const vr_render_params* params,
+                             const float* tin, const float* tseg, const float* cseg, float* contrib, uint64_t* samples) {
+  if (!tin || !tseg || !cseg || !contrib) return fail(VR_ERR_ARG, "null buffer");
+  SL_PROLOGUE(true)
+  { int rc_ = order_on_device(ctx, const_cast<vr_sortlast*>(sl)); if (rc_ != VR_OK) return rc_; }
+  CU(resolve_composite_tin_launch(P, g, occ, slab->dev, tin, tseg, sl->n, sl->rank, sl->orderDev, cseg, reinterpret_cast<float2*>(contrib),
+                                  reinterpret_cast<unsigned long long*>(samples), ctx->stream));
+  return VR_OK;
+}
+
 int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off, int64_t frame_off) {
   if (!ctx || !peer || !params) return fail(VR_ERR_ARG, "null argument");
   RenderParams P;

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <map>
+#include <memory>
 #include <set>
 #include <vector>
 #include "../../include/vr_b200.h"
@@ -12,6 +13,19 @@
 namespace vr { struct KdBuilder; void kd_builder_destroy(KdBuilder*); }
 
 struct vr_peer;
+
+namespace vr {
+// One pinned host buffer and / or one device buffer that holds the images of several streams back to back (a timestep):
+// vr_stream_arena_* (one H2D copy per timestep) and vr_streams_load (one allocation + one copy per load).  Streams keep it
+// alive through a shared_ptr; their hostImage / devImage point inside it and are not theirs to free.
+struct ArenaMem {
+  uint8_t* host = nullptr;
+  uint8_t* dev = nullptr;
+  size_t bytes = 0;
+  int device = -1;
+  ~ArenaMem();
+};
+}  // namespace vr
 
 struct vr_context {
   int device = 0;
@@ -26,6 +40,8 @@ struct vr_context {
   // that one Draw() per frame (main.cpp:404) costs no cudaMalloc / cudaFree
   float* frameDev = nullptr; int32_t* frameHitDev = nullptr; uint64_t* frameCountDev = nullptr;
   size_t framePixels = 0, frameHitPixels = 0;
+  // pinned staging of vr_streams_load (grow-only; stagingDone = the last copy out of it has finished)
+  uint8_t* stagingHost = nullptr; size_t stagingBytes = 0; cudaEvent_t stagingDone = nullptr;
   vr::Decode6Side side{};  // side stream + fork / join events of the split decode launch (kd_decode.h), created with the first plan
 };
 
@@ -40,7 +56,11 @@ struct vr_stream {
   size_t wordsBytes = 0;          // stream section (algorithmic stream bytes, padded)
   uint8_t* devImage = nullptr;
   int device = -1;
+  std::shared_ptr<vr::ArenaMem> arena;    // set when hostImage and / or devImage live inside a shared arena
+  bool hostOwned = true, devOwned = true;  // false: the pointer belongs to `arena`
   void release();
+  void drop_host();  // forget / free the host image
+  void drop_dev();   // forget / free the device image
 };
 
 struct vr_volume {
@@ -133,6 +153,8 @@ extern int g_count_fetched;  // vr_debug_set("count_fetched"), vr_capi_render.cu
 int fail(int code, const char* msg);
 int fail_cuda(cudaError_t e, const char* where);
 int stream_build_image(vr_stream* s);  // prepare + pack host image
+int stream_image_layout(vr_stream* s);                 // prepare + section offsets / imageBytes (no allocation)
+void stream_image_write(const vr_stream* s, uint8_t* dst);  // the image (imageBytes) into dst
 int context_chain_lut(vr_context* ctx, uint64_t chainDist, const uint32_t** out);
 struct OccView;
 struct PeerTargets;

@@ -245,6 +245,37 @@ def load_streams(paths, ctx=None, threads=0):
     return [Stream(c_void_p(out[i])) for i in range(n)]
 
 
+class StreamArena:
+    """vr_stream_arena: the images of a timestep's streams in one pinned buffer + one device buffer; upload() is ONE copy.
+    Create it before the DecodePlans of these streams."""
+
+    def __init__(self, ctx, streams):
+        self.streams = list(streams)
+        n = len(self.streams)
+        self.h = c_void_p()
+        check(lib.vr_stream_arena_create(ctx.h, (c_void_p * n)(*[s.h for s in self.streams]), n, byref(self.h)))
+
+    def upload(self, ctx):
+        check(lib.vr_stream_arena_upload(ctx.h, self.h))
+
+    @property
+    def nbytes(self):
+        b = c_int64()
+        check(lib.vr_stream_arena_bytes(self.h, byref(b)))
+        return b.value
+
+    def close(self):
+        if self.h:
+            lib.vr_stream_arena_destroy(self.h)
+            self.h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def mrt_save(path, header, distance_map, distance_map_range, tree_bits, range_bits):
     """MidRangeTree::save (MidRangeTree.cpp:753-786): byte-identical file from the class's public fields."""
     dm = np.ascontiguousarray(distance_map, dtype=np.uint8)

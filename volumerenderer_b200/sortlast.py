@@ -48,6 +48,8 @@ _SIGS = {
     "vr_resolve_iso": [c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p],
     "vr_volume_pack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
     "vr_volume_unpack_box": [c_void_p, c_void_p, _P(c_int64), _P(c_int64), c_void_p],
+    "vr_peer_tin_composite": [c_void_p, c_void_p, c_int32, c_void_p, _P(RenderParams), c_int64, c_int64],
+    "vr_resolve_composite_tin": [c_void_p, c_void_p, c_void_p, _P(RenderParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "vr_sortlast_frame_window_bytes": [_P(SlabDesc), c_int32, c_int32, c_int32, _P(c_int64), c_int32, _P(c_int64)],
     "vr_sortlast_frame_create": [c_void_p, c_void_p, c_void_p, c_int32, c_int32, _P(c_int64), c_int32, _P(c_void_p)],
     "vr_sortlast_frame_destroy": [c_void_p],
@@ -169,6 +171,11 @@ class CudaSlabOps:
         assert tseg_all.is_contiguous() and tseg_all.shape[0] == self.sl.n
         check(lib.vr_resolve_composite(self.ctx.h, self.sl.h, self.vol.h, byref(p), c_void_p(tseg_all.data_ptr()),
                                        c_void_p(cseg.data_ptr()), c_void_p(self.contrib.data_ptr()), self._cnt()))
+        return self.contrib
+
+    def resolve_composite_tin(self, p, tin_ptr, tseg, cseg):
+        check(lib.vr_resolve_composite_tin(self.ctx.h, self.sl.h, self.vol.h, byref(p), c_void_p(int(tin_ptr)), c_void_p(tseg.data_ptr()),
+                                           c_void_p(cseg.data_ptr()), c_void_p(self.contrib.data_ptr()), self._cnt()))
         return self.contrib
 
     def finish_composite(self, p, total):
@@ -372,18 +379,26 @@ class PeerExchange:
         self._wait(self.RED_OUT, everyone)
         yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
 
+    TIN = 4
+
     def frame_stages_hybrid(self, ops, params):
-        """COMPOSITE frame, the default: plain march kernels, the two image-sized hand-overs as coalesced copy kernels
-        into the peers' windows, and the last pass (sum of the ranks' terms + colour map) as ONE kernel that stores the
-        finished stripe into every window: 3 compute + 2 copy + 3 wait launches."""
+        """COMPOSITE frame, the default: plain march kernels; stripe j of T_seg goes to rank j, which hands every rank the
+        transmittance in front of its segment (vr_peer_tin_composite) -- two stripe exchanges instead of an all-gather of
+        whole images; the (C, A) terms go to the stripe owners, whose last pass (sum + colour map) stores the finished
+        stripe into every window.  4 compute + 2 copy + 4 wait launches, five stages.  T_in lives in the unused half of the stripes-in
+        area (composite terms need 8P of its 16P bytes)."""
         assert params.mode == COMPOSITE
         everyone = list(range(self.n))
         cseg, tseg = ops.partial_composite(params)
-        nb = 4 * self.P
-        self._put(self.GATHER, [(r, self.off_gather + self.rank * nb, tseg.data_ptr(), nb) for r in everyone])
+        s4 = 4 * self.P // self.n
+        self._put(self.GATHER, [(j, self.off_gather + self.rank * s4, tseg.data_ptr() + j * s4, s4) for j in everyone])
         yield None
         self._wait(self.GATHER, everyone)
-        contrib = ops.resolve_composite(params, self._view(self.off_gather, (self.n,) + tuple(tseg.shape), tseg.dtype), cseg)
+        off_tin = self.off_red_in + 8 * self.P
+        check(lib.vr_peer_tin_composite(self.ctx.h, self.h, self.TIN, ops.sl.h, byref(params), self.off_gather, off_tin))
+        yield None
+        self._wait(self.TIN, everyone)
+        contrib = ops.resolve_composite_tin(params, self._base() + off_tin, tseg, cseg)
         sb = 8 * self.P // self.n
         self._put(self.RED_IN, [(j, self.off_red_in + self.rank * sb, contrib.data_ptr() + j * sb, sb) for j in everyone])
         yield None
@@ -492,15 +507,17 @@ class InterleavedSteps:
     frame of the slab decoded by step t-1 and decodes the next timestep into the other slab, with the stages of the two
     interleaved so that every device-side wait sits behind a long kernel of the other stage:
 
-        partial(t) + put T_seg  |  wait frame(t-1)  |  DECODE(t+1)  |  halo pack + put (t+1)  |  wait T_seg, resolve(t), put terms
-        |  wait halo, unpack (t+1)  |  wait terms, sum + colour map + broadcast (t)            [frame(t) is waited for in step t+1]
+        partial(t) + put T_seg stripes  |  wait frame(t-1)  |  DECODE(t+1)  |  wait stripes, T_in to every rank  |  halo pack + put (t+1)
+        |  wait T_in, resolve(t), put terms  |  wait halo, unpack (t+1)  |  wait terms, sum + colour map + broadcast (t)
+                                                                                           [frame(t) is waited for in step t+1]
 
-    The all-gather's latency and the skew between ranks' pass 1 hide behind the decode, the reduce-scatter's behind the halo
-    unpack, the broadcast's behind the next step's pass 1.  No second stream, no concurrency between kernels is needed (a
+    The first exchange's latency and the skew between ranks' pass 1 hide behind the decode, the T_in round trip behind the halo
+    pack, the reduce-scatter's behind the halo unpack, the broadcast's behind the next step's pass 1.  No second stream, no concurrency between kernels is needed (a
     persistent decode launch leaves no room for it).  Two halo staging areas alternate: a neighbour can be a whole step ahead.
     Write-after-read on the windows: a rank's next store into an area follows a wait that the area's reader preceded in its
-    own stream order (gather: put(t+1) follows wait terms(t), whose signal follows the reader's resolve(t); terms: put(t+1)
-    follows wait T_seg(t+1), whose signal follows the reader's sum(t); frame: the sum of t+1 follows wait terms(t+1), whose
+    own stream order (T_seg stripes: put(t+1) follows wait terms(t), whose signal follows the owner's T_in pass (t); T_in: the owner's
+    pass (t+1) follows its wait stripes(t+1), whose signal follows the reader's resolve(t); terms: put(t+1) follows wait T_in(t+1),
+    whose signal follows the owner's wait stripes(t+1) and so its sum(t); frame: the sum of t+1 follows wait terms(t+1), whose
     signal follows the reader's wait frame(t); halo area b: put(t+2) follows wait terms(t), whose signal follows unpack(t))."""
 
     def __init__(self, peer, plans, ops, descs, stored, params):
@@ -522,13 +539,14 @@ class InterleavedSteps:
         it must be enqueued on the context's stream inside the callback -- later the peers may overwrite it."""
         k, peer = self.k, self.peer
         gen = peer.frame_stages_hybrid(self.ops[k], self.p)
-        next(gen)                                         # pass 1 + store T_seg into every window
+        next(gen)                                         # pass 1 + T_seg stripes to their owners
         prev = next(self.pending) if self.pending is not None else None   # wait for the previous frame's stripes
         if consume is not None and prev is not None:
             consume(prev)
         self.plans[1 - k].run()                           # decode of the next timestep
+        next(gen)                                         # wait T_seg stripes, T_in of my stripe to every rank
         recvs = peer.exchange_halos(self.ops[1 - k], self.descs, self.stored, defer_receive=True, buf=self.t & 1)
-        next(gen)                                         # wait T_seg, resolve, store terms into the stripe owners
+        next(gen)                                         # wait T_in, resolve, store terms into the stripe owners
         peer.receive_halos(self.ops[1 - k], recvs)        # wait halo planes, unpack (+ occupancy of the box)
         next(gen)                                         # wait terms, sum + colour map + stripes into every window
         self.pending = gen
