@@ -445,7 +445,7 @@ def run_ours(args):
             plan2 = vr.DecodePlan(ctx, streams, origins, vol2)
             ops2 = sortlast.CudaSlabOps(ctx, sl, vol2, IMG, IMG, count_samples=False)
             opsA = sortlast.CudaSlabOps(ctx, sl, vol, IMG, IMG, count_samples=False)
-            inter = sortlast.InterleavedSteps(peer, [plan, plan2], [opsA, ops2], descs, stored, p)
+            inter = sortlast.InterleavedSteps(peer, [plan, plan2], [opsA, ops2], descs, stored, p, frame_to=0)
             barrier()
             inter.prologue()
             for _ in range(4):
@@ -735,8 +735,9 @@ def run_ours(args):
                    "l2": "inputs+outputs per step (>= 1 GB) exceed the 126 MB L2; no explicit flush",
                    "multi_gpu": ("single slab, plain march" if world == 1 else
                                  f"texture = {world} y-slabs (2048x{256 * world}x1920); decode has no collective; frame = sort-last composite "
-                                 + ("over peer-memory windows on NVLink (halo planes, all-gather T_seg 4 MiB/rank, reduce-scatter of the "
-                                    "(C,A) terms + finished stripes to every rank)" if peer is not None else
+                                 + ("over peer-memory windows on NVLink (halo planes; T_seg stripes to their owners and T_in back, 2 x 4 MiB x "
+                                    "(n-1)/n per rank; (C,A) terms to the stripe owners; finished stripes to rank 0"
+                                    + (")" if inter is not None else " and every other rank)") if peer is not None else
                                     "over NCCL (halo send/recv, all-gather T_seg 4 MiB/rank, all-reduce (C,A) 8 MiB)")),
                    "step": {"two-stream": "pipelined: two slabs; step t decodes one while the frame of step t-1 is drawn from the other on a "
                                           "second stream; every step = 120 bricks decoded + 1 frame of a freshly decoded slab",

@@ -412,6 +412,10 @@ int vr_peer_resolve_composite(vr_context* ctx, vr_peer* peer, int32_t slot, cons
                               uint64_t* samples_dev);
 int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off,
                              int64_t frame_off);
+/* the same with the finished stripes stored into (and `slot` raised at) rank dst_rank only -- a frame that one rank displays
+ * or reads back; dst_rank < 0 = every rank.  Only dst_rank waits for `slot` then. */
+int vr_peer_finish_composite_to(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off,
+                                int64_t frame_off, int32_t dst_rank);
 
 /* The all-gather of T_seg replaced by two stripe exchanges (what a rank needs of the others' T_seg is one number per
  * pixel, the transmittance T_in in front of its own segment): every rank puts stripe j of its T_seg into rank j's window at

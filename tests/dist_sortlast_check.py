@@ -70,6 +70,23 @@ def interleaved_steps_check(ctx, rank, world, full):
         d = float((f - want[t & 1]).abs().max())
         assert d == 0.0, (rank, t, d)
     dist.barrier()
+    # the finished frame delivered to rank 0 only (vr_peer_finish_composite_to): the other ranks neither receive nor wait
+    inter = sortlast.InterleavedSteps(peer, plans, ops, descs, stored, p, frame_to=0)
+    got = []
+    inter.prologue()
+    for _ in range(5):
+        inter.step(consume=lambda f: got.append(f.clone()))
+    last = inter.drain()
+    torch.cuda.synchronize()
+    assert not peer.timed_out(), hex(peer.last_error)
+    if rank == 0:
+        got.append(last.clone())
+        assert len(got) == 5
+        for t, f in enumerate(got):
+            assert float((f - want[t & 1]).abs().max()) == 0.0, (rank, t)
+    else:
+        assert last is None and not got
+    dist.barrier()
     # the same frames through the one-call C entries (csrc/vr_capi_frame.cu) on the same windows
     halo = sortlast.required_halo(p, (X, Y, Z))
     assert sortlast.SortLastFrame.window_bytes(descs, W, H, halo, 2) <= peer.bytes

@@ -88,6 +88,7 @@ _SIGS = {
     "vr_peer_partial_composite": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "vr_peer_resolve_composite": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
     "vr_peer_finish_composite": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, c_int64]),
+    "vr_peer_finish_composite_to": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, c_int64, c_int32]),
     "vr_kd_compress_device": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p), POINTER(BuildStats)]),
     "vr_kd_compress_volume": (c_int, [c_void_p, c_void_p, POINTER(c_int64), c_int64, c_int64, c_int64, c_int, c_int, POINTER(c_void_p),
                                       POINTER(BuildStats), POINTER(c_int64)]),

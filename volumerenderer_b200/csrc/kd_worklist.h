@@ -132,6 +132,11 @@ inline bool kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const*
   std::vector<PItem> pitems;
   std::vector<FItem> fitems;
   const uint32_t nt = 1u << g.Dt;
+  {
+    size_t live = 0;
+    for (int b = 0; b < n; ++b) live += (size_t)idx[b]->numLiveTiles;
+    pitems.reserve(live * 8);
+  }
   for (int b = 0; b < n; ++b) {
     vr_kd_job hj{};
     hj.tileLeafBlock = idx[b]->tileLeafBlock.data();
@@ -167,16 +172,23 @@ inline bool kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const*
         const uint32_t blk = hj.tileLeafBlock[t];
         const uint32_t* lo = idx[b]->leafOff.data() + (size_t)blk * 256;
         const uint64_t tileEnd = idx[b]->blockSymEnd[blk];
+        // first / last live leaf of every unit in one pass over the tile's 256 entries
+        uint64_t uFirst[8], uLast[8];
+        bool uAny[8];
+        for (uint32_t u = 0; u < 8; ++u) {
+          uAny[u] = false; uFirst[u] = 0; uLast[u] = 0;
+          for (uint32_t l = 32u * u; l < 32u * u + 32u; ++l)
+            if (lo[l] != VR_PRUNED) { if (!uAny[u]) { uFirst[u] = lo[l]; uAny[u] = true; } uLast[u] = lo[l]; }
+        }
         for (uint32_t u = 0; u < 8; ++u) {
           vr_parse_item w{};
           w.tileUnit = (t << 3) | u;
           w.leaf0 = blk * 256u + 32u * u;
           // the unit's symbols lie between its first live leaf and the next live leaf behind it (or the end of the tile)
-          uint64_t begin = ~0ull, end = tileEnd, last = 0;
-          for (uint32_t l = 32u * u; l < 32u * u + 32u; ++l)
-            if (lo[l] != VR_PRUNED) { if (begin == ~0ull) begin = lo[l]; last = lo[l]; }
-          for (uint32_t l = 32u * u + 32u; l < 256u; ++l)
-            if (lo[l] != VR_PRUNED) { end = lo[l]; break; }
+          uint64_t begin = uAny[u] ? uFirst[u] : ~0ull, end = tileEnd;
+          const uint64_t last = uLast[u];
+          for (uint32_t v = u + 1u; v < 8u; ++v)
+            if (uAny[v]) { end = uFirst[v]; break; }
           // ... and a leaf subtree is at most 63 nodes + 64 voxel items of 8 symbols long
           if (begin != ~0ull && last + 575u < end) end = last + 575u;
           if (begin != ~0ull) {
@@ -211,14 +223,17 @@ inline bool kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const*
   // Parse units in address order.  (heavyFirst = longest segments first, in classes of 1 KB: measured slower -- the two
   // 16-byte halves of a 32-byte sector belong to units four tickets apart, and in address order L2 merges them before they
   // reach DRAM: 0.70 ms against 0.87 ms on the config-3 layer.)
-  std::sort(pitems.begin(), pitems.end(), [heavyFirst](const PItem& a, const PItem& b) {
-    const uint32_t ca = heavyFirst ? a.w.segChunks >> 6 : 0u, cb = heavyFirst ? b.w.segChunks >> 6 : 0u;
-    return ca != cb ? ca > cb : a.key < b.key;
-  });
+  // (sorted through an index array: the records are 80 bytes)
+  std::vector<std::pair<int64_t, uint32_t>> ord(pitems.size());
+  for (size_t i = 0; i < pitems.size(); ++i) {
+    const int64_t cls = heavyFirst ? (int64_t)(0xFFFFu - (pitems[i].w.segChunks >> 6)) : 0;
+    ord[i] = {(cls << 47) + pitems[i].key, (uint32_t)i};
+  }
+  std::sort(ord.begin(), ord.end());
   std::sort(fitems.begin(), fitems.end(), [](const FItem& a, const FItem& b) { return a.key < b.key; });
   parse->resize(pitems.size());
   if (parseBrick) parseBrick->resize(pitems.size());
-  for (size_t i = 0; i < pitems.size(); ++i) { (*parse)[i] = pitems[i].w; if (parseBrick) (*parseBrick)[i] = pitems[i].brick; }
+  for (size_t i = 0; i < ord.size(); ++i) { (*parse)[i] = pitems[ord[i].second].w; if (parseBrick) (*parseBrick)[i] = pitems[ord[i].second].brick; }
   fills->resize(fitems.size());
   for (size_t i = 0; i < fitems.size(); ++i) (*fills)[i] = fitems[i].f;
   return true;

@@ -70,6 +70,6 @@ cudaError_t resolve_composite_tin_launch(const RenderParams& P, const SlabGeom& 
                                          const float* tseg, int n, int rank, const int* order, const float* cseg, float2* contrib,
                                          unsigned long long* sampleCount, cudaStream_t stream);
 // pass 3 (stripe owner): sum of the n terms in rank order + colour map -> RGBA of the stripe into every window + frameOff
-cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff,
+cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff, int dstOnly,
                                          cudaStream_t stream);
 }  // namespace vr

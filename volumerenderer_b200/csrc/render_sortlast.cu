@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(256) partial_composite_kernel(const __grid_con
 
 // Last CTA of the grid publishes: every CTA has fenced its stores (system scope: they go to peer memory) before it
 // takes a ticket, so whoever draws the last ticket knows all of them are visible before the flags are.
-__device__ __forceinline__ void peer_signal(const PeerTargets& t) {
+// only >= 0: raise the flag at that one rank (a result that a single rank consumes)
+__device__ __forceinline__ void peer_signal(const PeerTargets& t, int only = -1) {
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -115,6 +116,7 @@ __device__ __forceinline__ void peer_signal(const PeerTargets& t) {
       *t.ticket = 0;
       __threadfence_system();
       for (int r = 0; r < t.n; ++r) {
+        if (only >= 0 && r != only) continue;
         const uint32_t v = *t.sent[r] + 1u;
         *t.sent[r] = v;
         *reinterpret_cast<volatile uint32_t*>(t.flag[r]) = v;
@@ -351,7 +353,8 @@ __global__ void __launch_bounds__(256) resolve_composite_tin_kernel(const __grid
 
 // One thread per pixel of this rank's stripe: the ranks' terms in rank order, then the colour map (finish_composite_kernel).
 __global__ void __launch_bounds__(256) finish_composite_peer_kernel(const __grid_constant__ RenderParams P,
-                                                                    const __grid_constant__ PeerTargets t, long long redOff, long long frameOff) {
+                                                                    const __grid_constant__ PeerTargets t, long long redOff, long long frameOff,
+                                                                    int dstOnly) {
   const long long stripe = ((long long)P.W * P.H) / t.n;
   const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < stripe) {
@@ -367,9 +370,10 @@ __global__ void __launch_bounds__(256) finish_composite_peer_kernel(const __grid
     V3 vUV;
     if (ray_setup(P, (int)(pix % P.W), (int)(pix / P.W), &vUV))
       rgba = make_float4(clamp01(fsub(1.0f, s.x)), clamp01(fsub(1.0f, s.x)), 1.0f, clamp01(s.y));
-    for (int r = 0; r < t.n; ++r) reinterpret_cast<float4*>(t.base[r] + frameOff)[pix] = rgba;
+    if (dstOnly >= 0) reinterpret_cast<float4*>(t.base[dstOnly] + frameOff)[pix] = rgba;
+    else for (int r = 0; r < t.n; ++r) reinterpret_cast<float4*>(t.base[r] + frameOff)[pix] = rgba;
   }
-  peer_signal(t);
+  peer_signal(t, dstOnly);
 }
 
 __global__ void __launch_bounds__(256) finish_composite_kernel(const __grid_constant__ RenderParams P,
@@ -436,10 +440,10 @@ cudaError_t resolve_composite_peer_launch(const RenderParams& P, const SlabGeom&
   else resolve_composite_peer_kernel<false><<<pixel_grid(P), 256, 0, stream>>>(P, g, occ, vol, tsegAll, order, cseg, t, redOff, sampleCount);
   return cudaGetLastError();
 }
-cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff,
+cudaError_t finish_composite_peer_launch(const RenderParams& P, const PeerTargets& t, long long redOff, long long frameOff, int dstOnly,
                                          cudaStream_t stream) {
   const long long stripe = ((long long)P.W * P.H) / t.n;
-  finish_composite_peer_kernel<<<dim3((unsigned)((stripe + 255) / 256), 1), 256, 0, stream>>>(P, t, redOff, frameOff);
+  finish_composite_peer_kernel<<<dim3((unsigned)((stripe + 255) / 256), 1), 256, 0, stream>>>(P, t, redOff, frameOff, dstOnly);
   return cudaGetLastError();
 }
 cudaError_t tin_stripe_peer_launch(const RenderParams& P, const int* order, const PeerTargets& t, long long gatherOff, long long tinOff,

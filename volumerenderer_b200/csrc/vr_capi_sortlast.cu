@@ -276,6 +276,10 @@ int vr_resolve_composite_tin(vr_context* ctx, const vr_sortlast* sl, const vr_vo
 }
 
 int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off, int64_t frame_off) {
+  return vr_peer_finish_composite_to(ctx, peer, slot, params, red_off, frame_off, -1);
+}
+int vr_peer_finish_composite_to(vr_context* ctx, vr_peer* peer, int32_t slot, const vr_render_params* params, int64_t red_off, int64_t frame_off,
+                                int32_t dst_rank) {
   if (!ctx || !peer || !params) return fail(VR_ERR_ARG, "null argument");
   RenderParams P;
   if (make_render_params(params, &P) != VR_OK) return fail(VR_ERR_ARG, "degenerate camera or image size");
@@ -286,7 +290,8 @@ int vr_peer_finish_composite(vr_context* ctx, vr_peer* peer, int32_t slot, const
   const int64_t npix = (int64_t)P.W * P.H;
   if (npix % t.n || red_off < 0 || frame_off < 0 || (frame_off & 15) || red_off + 8 * npix > wb || frame_off + 16 * npix > wb)
     return fail(VR_ERR_ARG, "vr_peer_finish_composite: window too small or image not divisible into stripes");
-  CU(finish_composite_peer_launch(P, t, red_off, frame_off, ctx->stream));
+  if (dst_rank >= t.n) return fail(VR_ERR_ARG, "vr_peer_finish_composite_to: no such rank");
+  CU(finish_composite_peer_launch(P, t, red_off, frame_off, dst_rank < 0 ? -1 : dst_rank, ctx->stream));
   return VR_OK;
 }
 

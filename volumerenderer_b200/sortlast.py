@@ -381,8 +381,9 @@ class PeerExchange:
 
     TIN = 4
 
-    def frame_stages_hybrid(self, ops, params):
-        """COMPOSITE frame, the default: plain march kernels; stripe j of T_seg goes to rank j, which hands every rank the
+    def frame_stages_hybrid(self, ops, params, frame_to=None):
+        """frame_to = r: the finished frame goes to rank r only (the last value is None on the others).
+        COMPOSITE frame, the default: plain march kernels; stripe j of T_seg goes to rank j, which hands every rank the
         transmittance in front of its segment (vr_peer_tin_composite) -- two stripe exchanges instead of an all-gather of
         whole images; the (C, A) terms go to the stripe owners, whose last pass (sum + colour map) stores the finished
         stripe into every window.  4 compute + 2 copy + 4 wait launches, five stages.  T_in lives in the unused half of the stripes-in
@@ -403,8 +404,12 @@ class PeerExchange:
         self._put(self.RED_IN, [(j, self.off_red_in + self.rank * sb, contrib.data_ptr() + j * sb, sb) for j in everyone])
         yield None
         self._wait(self.RED_IN, everyone)
-        check(lib.vr_peer_finish_composite(self.ctx.h, self.h, self.RED_OUT, byref(params), self.off_red_in, self.off_total))
+        check(lib.vr_peer_finish_composite_to(self.ctx.h, self.h, self.RED_OUT, byref(params), self.off_red_in, self.off_total,
+                                              -1 if frame_to is None else int(frame_to)))
         yield None
+        if frame_to is not None and frame_to != self.rank:
+            yield None
+            return
         self._wait(self.RED_OUT, everyone)
         yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
 
@@ -520,9 +525,10 @@ class InterleavedSteps:
     whose signal follows the owner's wait stripes(t+1) and so its sum(t); frame: the sum of t+1 follows wait terms(t+1), whose
     signal follows the reader's wait frame(t); halo area b: put(t+2) follows wait terms(t), whose signal follows unpack(t))."""
 
-    def __init__(self, peer, plans, ops, descs, stored, params):
+    def __init__(self, peer, plans, ops, descs, stored, params, frame_to=None):
         assert peer.halo_buffers >= 2 and len(plans) == 2 and len(ops) == 2 and params.mode == COMPOSITE
         self.peer, self.plans, self.ops, self.descs, self.stored, self.p = peer, plans, ops, descs, stored, params
+        self.frame_to = frame_to  # None: every rank receives the finished frame; r: rank r only
         self.pending = None   # generator of the frame whose broadcast has not been waited for
         self.k = 0            # slab the next step draws
         self.t = 0
@@ -538,7 +544,7 @@ class InterleavedSteps:
         the previous step's finished frame (a view of this rank's window) as soon as it has been waited for; whatever reads
         it must be enqueued on the context's stream inside the callback -- later the peers may overwrite it."""
         k, peer = self.k, self.peer
-        gen = peer.frame_stages_hybrid(self.ops[k], self.p)
+        gen = peer.frame_stages_hybrid(self.ops[k], self.p, frame_to=self.frame_to)
         next(gen)                                         # pass 1 + T_seg stripes to their owners
         prev = next(self.pending) if self.pending is not None else None   # wait for the previous frame's stripes
         if consume is not None and prev is not None:
