@@ -438,7 +438,7 @@ def run_ours(args):
     inter = None
     schedule = "sequential"
     if args.pipeline and world > 1 and peer is not None and args.exchange == "peer" and args.schedule == "interleaved":
-        # N > 1 default: ONE stream, the stages of frame(t) and decode(t+1) interleaved so that every device-side wait of the
+        # --schedule interleaved (measured slightly slower than two streams on 2 and 8 GPUs, profiles/r2_schedule_ab.md): ONE stream, the stages of frame(t) and decode(t+1) interleaved so that every device-side wait of the
         # exchange sits behind a long kernel of the other stage (sortlast.InterleavedSteps)
         try:
             vol2 = vr.Volume(ctx, *se).set_cell_origin(so)
@@ -481,7 +481,7 @@ def run_ours(args):
                 with torch.cuda.stream(f_stream):
                     if world > 1:
                         peerF.exchange_halos(opsF[k], descs, stored)
-                        return peerF.render_frame(opsF[k], p, fused=args.exchange == "peer-fused")
+                        return peerF.render_frame(opsF[k], p, fused=args.exchange == "peer-fused", frame_to=0)
                     render.render_device(ctxF, vols[k], p, outs[k].data_ptr())
                     return outs[k]
 
@@ -737,7 +737,7 @@ def run_ours(args):
                                  f"texture = {world} y-slabs (2048x{256 * world}x1920); decode has no collective; frame = sort-last composite "
                                  + ("over peer-memory windows on NVLink (halo planes; T_seg stripes to their owners and T_in back, 2 x 4 MiB x "
                                     "(n-1)/n per rank; (C,A) terms to the stripe owners; finished stripes to rank 0"
-                                    + (")" if inter is not None else " and every other rank)") if peer is not None else
+                                    " in the timed steps)" if peer is not None else
                                     "over NCCL (halo send/recv, all-gather T_seg 4 MiB/rank, all-reduce (C,A) 8 MiB)")),
                    "step": {"two-stream": "pipelined: two slabs; step t decodes one while the frame of step t-1 is drawn from the other on a "
                                           "second stream; every step = 120 bricks decoded + 1 frame of a freshly decoded slab",
@@ -900,7 +900,7 @@ def main():
                     help="N > 1: sort-last exchange over peer-memory windows (copy kernels, or fused into the march kernels) or NCCL")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
                     help="strictly sequential steps (decode, then frame) instead of decode(t+1) overlapping frame(t) on two slabs")
-    ap.add_argument("--schedule", default="interleaved", choices=["interleaved", "two-stream"],
+    ap.add_argument("--schedule", default="two-stream", choices=["interleaved", "two-stream"],
                     help="N > 1 with the peer exchange: how decode(t+1) and frame(t) share the GPU (one stream, stages interleaved; or two streams)")
     ap.add_argument("--debug", action="append", default=[], metavar="KEY=VALUE",
                     help="A/B runs: vr_debug_set(KEY, VALUE) before anything is created (e.g. decode_split=1, decode_only=2: timing probes)")

@@ -381,25 +381,36 @@ class PeerExchange:
 
     TIN = 4
 
-    def frame_stages_hybrid(self, ops, params, frame_to=None):
-        """frame_to = r: the finished frame goes to rank r only (the last value is None on the others).
-        COMPOSITE frame, the default: plain march kernels; stripe j of T_seg goes to rank j, which hands every rank the
-        transmittance in front of its segment (vr_peer_tin_composite) -- two stripe exchanges instead of an all-gather of
-        whole images; the (C, A) terms go to the stripe owners, whose last pass (sum + colour map) stores the finished
-        stripe into every window.  4 compute + 2 copy + 4 wait launches, five stages.  T_in lives in the unused half of the stripes-in
-        area (composite terms need 8P of its 16P bytes)."""
+    def frame_stages_hybrid(self, ops, params, frame_to=None, t_in=None):
+        """COMPOSITE frame, the default: plain march kernels, the hand-overs as coalesced copy kernels into the peers' windows,
+        the last pass (sum of the ranks' terms + colour map) as ONE kernel that stores the finished stripes.  Five stages.
+        t_in (default: n >= 4): instead of an all-gather of T_seg (n - 1 image-sized transfers per rank), stripe j of T_seg goes
+        to rank j, which hands every rank the transmittance in front of its segment (vr_peer_tin_composite): 2 (n-1)/n
+        transfers and one more round trip -- measured slower on 2 GPUs (0.30 vs 0.28 ms per frame), faster on 8.  T_in lives
+        in the unused half of the stripes-in area (composite terms need 8P of its 16P bytes).
+        frame_to = r: the finished frame goes to rank r only (the last value is None on the others)."""
         assert params.mode == COMPOSITE
         everyone = list(range(self.n))
+        if t_in is None:
+            t_in = self.n >= 4
         cseg, tseg = ops.partial_composite(params)
-        s4 = 4 * self.P // self.n
-        self._put(self.GATHER, [(j, self.off_gather + self.rank * s4, tseg.data_ptr() + j * s4, s4) for j in everyone])
-        yield None
-        self._wait(self.GATHER, everyone)
-        off_tin = self.off_red_in + 8 * self.P
-        check(lib.vr_peer_tin_composite(self.ctx.h, self.h, self.TIN, ops.sl.h, byref(params), self.off_gather, off_tin))
-        yield None
-        self._wait(self.TIN, everyone)
-        contrib = ops.resolve_composite_tin(params, self._base() + off_tin, tseg, cseg)
+        if t_in:
+            s4 = 4 * self.P // self.n
+            self._put(self.GATHER, [(j, self.off_gather + self.rank * s4, tseg.data_ptr() + j * s4, s4) for j in everyone])
+            yield None
+            self._wait(self.GATHER, everyone)
+            off_tin = self.off_red_in + 8 * self.P
+            check(lib.vr_peer_tin_composite(self.ctx.h, self.h, self.TIN, ops.sl.h, byref(params), self.off_gather, off_tin))
+            yield None
+            self._wait(self.TIN, everyone)
+            contrib = ops.resolve_composite_tin(params, self._base() + off_tin, tseg, cseg)
+        else:
+            nb = 4 * self.P
+            self._put(self.GATHER, [(r, self.off_gather + self.rank * nb, tseg.data_ptr(), nb) for r in everyone])
+            yield None
+            yield None
+            self._wait(self.GATHER, everyone)
+            contrib = ops.resolve_composite(params, self._view(self.off_gather, (self.n,) + tuple(tseg.shape), tseg.dtype), cseg)
         sb = 8 * self.P // self.n
         self._put(self.RED_IN, [(j, self.off_red_in + self.rank * sb, contrib.data_ptr() + j * sb, sb) for j in everyone])
         yield None
@@ -413,7 +424,7 @@ class PeerExchange:
         self._wait(self.RED_OUT, everyone)
         yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
 
-    def render_frame(self, ops, params, fused=False):
+    def render_frame(self, ops, params, fused=False, frame_to=None):
         """The frame of one rank (one process per GPU).  fused=True (COMPOSITE only) lets the march kernels store into
         the peers' windows themselves; measured slower than the staged copies on 2 x B200 (0.334 vs 0.287 ms per
         1024^2 frame: 32-byte stores in the 8x4 pixel-tile order and a system-scope fence per CTA inside the compute
@@ -421,7 +432,7 @@ class PeerExchange:
         if params.mode != COMPOSITE:
             return render_frame(ops, self, params)
         res = None
-        for res in (self.frame_stages(ops, params) if fused else self.frame_stages_hybrid(ops, params)):
+        for res in (self.frame_stages(ops, params) if fused else self.frame_stages_hybrid(ops, params, frame_to=frame_to)):
             pass
         return res
 
