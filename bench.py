@@ -720,6 +720,15 @@ def run_ours(args):
         try:
             t = json.load(open(tr))
             roof_dec["traffic"] = t.get("decode"); roof_mar["traffic"] = t.get("march")
+            # not measured by this run: one `ncu --set full` capture per kernel of this build (tools/profile_step.sh), committed
+            roof_dec["traffic_source"] = roof_mar["traffic_source"] = t.get("source")
+            if t.get("march_ncu"):
+                # what bounds the march is instruction issue and L1, not HBM (its DRAM traffic is a few % of the algorithmic
+                # bytes): the HBM figure above is SURVEY 8d's uniformity number, these are the kernel's own limits
+                roof_mar["bound_note"] = "issue / L1-bound kernel; the HBM fraction is SURVEY 8d's uniformity figure, not its roofline"
+                roof_mar["ncu"] = t["march_ncu"]
+            if t.get("decode_ncu"):
+                roof_dec["ncu"] = t["decode_ncu"]
         except Exception:
             pass
     dominant = roof_dec if d_ms >= m_ms else roof_mar

@@ -4,7 +4,7 @@
 //   build :17-140, buildRecursive :143-201 (midrange pyramid), compressGradientDescent :206-384,
 //   encodeNodeEstimate :415-455, encodeNode :457-502, pruneTreeRecursive :596-629,
 //   convertToPreorder :631-724.
-// The output must be byte-identical to the reference's stream (tests/test_compress_parity.py), so
+// The output must be byte-identical to the reference's stream (tests/test_host_codec.py: golden containers written by the unmodified reference, and live against oracle/_ref), so
 // every data-dependent decision keeps the reference's order of evaluation, including its quirks:
 //   * `currentError` is never reset: it carries over between epochs and levels (SURVEY C-1) and
 //     is accumulated by sequential double additions, which we keep sequential;
