@@ -110,21 +110,34 @@ __global__ void __launch_bounds__(256) occ_pyr_high_kernel(uint8_t* __restrict__
   }
 }
 
-__global__ void occ_levels_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ lvl, const __grid_constant__ OccView L) {
+// lvl[c] for the march (occupancy.h): VR_OCC_SOLID, or R = the largest radius such that every cell within Chebyshev distance R
+// of c (in cells; cells outside the grid count as void -- the march clips its boxes to the stored voxels) is void for L.thr.
+// Chebyshev distance to the nearest non-void cell, separably: along x, then min over y' of max(|dy|, .), then the same along z.
+__global__ void occ_dist_x_kernel(const uint8_t* __restrict__ pyr0, uint8_t* __restrict__ gx, const __grid_constant__ OccView L) {
   const long long n = (long long)L.nx * L.ny * L.nz;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const int cx = (int)(i % L.nx), cy = (int)((i / L.nx) % L.ny), cz = (int)(i / ((long long)L.nx * L.ny));
-  int out = VR_OCC_SOLID;
-  if ((int)pyr[L.off[0] + i] <= L.thr) {
-    out = 0;
-    for (int s = 1; s < L.nlev; ++s) {
-      const int nxl = ((L.nx - 1) >> s) + 1, nyl = ((L.ny - 1) >> s) + 1;
-      if ((int)pyr[L.off[s] + ((long long)(cz >> s) * nyl + (cy >> s)) * nxl + (cx >> s)] > L.thr) break;
-      out = s;
-    }
+  const int cx = (int)(i % L.nx);
+  const uint8_t* row = pyr0 + (i - cx);
+  int g = VR_OCC_DIST_CAP;
+  for (int d = 0; d < VR_OCC_DIST_CAP; ++d)
+    if ((cx - d >= 0 && (int)row[cx - d] > L.thr) || (cx + d < L.nx && (int)row[cx + d] > L.thr)) { g = d; break; }
+  gx[i] = (uint8_t)g;
+}
+// stride = distance between neighbours along the axis, c / nc = coordinate and extent along it; out = min over d of max(d, in[c +- d])
+__global__ void occ_dist_axis_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, const __grid_constant__ OccView L, int axis, int finish) {
+  const long long n = (long long)L.nx * L.ny * L.nz;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = axis == 1 ? (int)((i / L.nx) % L.ny) : (int)(i / ((long long)L.nx * L.ny));
+  const int nc = axis == 1 ? L.ny : L.nz;
+  const long long stride = axis == 1 ? L.nx : (long long)L.nx * L.ny;
+  int best = in[i];
+  for (int d = 1; d < best; ++d) {
+    if (c - d >= 0) best = min(best, max(d, (int)in[i - d * stride]));
+    if (c + d < nc) best = min(best, max(d, (int)in[i + d * stride]));
   }
-  lvl[i] = (uint8_t)out;
+  out[i] = finish ? (uint8_t)(best == 0 ? VR_OCC_SOLID : best - 1) : (uint8_t)best;
 }
 
 }  // namespace
@@ -160,7 +173,11 @@ cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, c
 
 cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& L, cudaStream_t stream) {
   const long long n = (long long)L.nx * L.ny * L.nz;
-  occ_levels_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(pyr, lvl, L);
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  uint8_t *gx = lvl + n, *gy = lvl + 2 * n;  // scratch behind lvl (the array holds 3 n bytes)
+  occ_dist_x_kernel<<<blocks, 256, 0, stream>>>(pyr + L.off[0], gx, L);
+  occ_dist_axis_kernel<<<blocks, 256, 0, stream>>>(gx, gy, L, 1, 0);
+  occ_dist_axis_kernel<<<blocks, 256, 0, stream>>>(gy, lvl, L, 2, 1);
   return cudaGetLastError();
 }
 

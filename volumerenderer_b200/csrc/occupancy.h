@@ -22,10 +22,11 @@ namespace vr {
 #define VR_OCC_MAX_LEVELS 12
 
 #define VR_OCC_SOLID 0xFF
+#define VR_OCC_DIST_CAP 64  // lvl[] radii are capped below this many cells
 
 struct OccView {        // what the march kernels read (null pyr = no skipping)
   const uint8_t* pyr;
-  const uint8_t* lvl;   // per level-0 cell, for this thr: VR_OCC_SOLID, or the highest level whose enclosing cell is void
+  const uint8_t* lvl;   // per level-0 cell, for this thr: VR_OCC_SOLID, or the radius R (cells, Chebyshev) of the largest void cube of cells around it
   int nlev;
   int off[VR_OCC_MAX_LEVELS];  // byte offset of level l inside pyr
   int nx, ny, nz;       // level-0 cells; level l has ((n - 1) >> l) + 1 cells per axis
@@ -43,7 +44,9 @@ cudaError_t occ_set_cells_launch(uint8_t* raw, const int64_t* pairsDev, int n, c
 cudaError_t occ_merge_solid_launch(uint8_t* lvl, const uint8_t* solidDev, int n, cudaStream_t stream);
 // all pyramid levels from raw (two launches)
 cudaError_t occ_pyramid_launch(const uint8_t* raw, uint8_t* pyr, const OccView& layout, cudaStream_t stream);
-// lvl[c] for layout.thr (one thread per level-0 cell climbs the octree once, instead of every ray doing it)
+// lvl[c] for layout.thr: radius of the largest cube of void cells around c (three separable passes over level 0 of pyr; lvl holds
+// 3 x cells bytes, the last two thirds are scratch) -- a ray leaves such a cube in one skip, where octree cells made it stop at
+// every aligned boundary
 cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& layout, cudaStream_t stream);
 
 }  // namespace vr

@@ -139,8 +139,8 @@ __device__ __forceinline__ bool ray_setup(const RenderParams& P, int px, int py,
 // ---- empty-space skipping (occupancy.h) -------------------------------------------------------------
 // q = position whose 8 taps decide the sample (composite: the sample itself; isosurface: the look-ahead
 // p + dirStep).  Returns -1 when the cell's bound does not prove the sample void; otherwise the number
-// k >= 0 of FURTHER lattice steps q + j*d (j = 1..k) that provably stay inside the largest void octree
-// cell around q (and inside the texture), capped by `budget`.  inv = 1/d per axis.  The estimate uses
+// k >= 0 of FURTHER lattice steps q + j*d (j = 1..k) that provably stay inside the largest void cube of cells
+// around q's cell (and inside the texture), capped by `budget`.  inv = 1/d per axis.  The estimate uses
 // real-number geometry with a margin far above the accumulated rounding of the lattice (300 additions of
 // magnitude <= 1: < 2e-5); the positions themselves are still produced by the caller's repeated additions.
 template <bool SLAB>
@@ -150,19 +150,19 @@ __device__ __forceinline__ int occ_skip(const OccView& o, const Vol& v, V3 q, V3
   int bz = clampi((int)floorf(fsub(fmul(q.z, v.fZ), 0.5f)), 0, v.GZ - 1);
   if (SLAB) { bx = clampi(bx - v.ox, 0, v.SX - 1); by = clampi(by - v.oy, 0, v.SY - 1); bz = clampi(bz - v.oz, 0, v.SZ - 1); }
   const int cx = (bx + o.sx) >> VR_OCC_LX, cy = (by + o.sy) >> VR_OCC_LY, cz = (bz + o.sz) >> VR_OCC_LZ;
-  const int l = (int)__ldg(o.lvl + (cz * o.ny + cy) * o.nx + cx);  // highest void octree level around the cell
-  if (l == VR_OCC_SOLID) return -1;
-  if (l < 2) return 0;  // a cell or two: about one step, not worth the geometry
-  // the level-l cell as a box of base texels in global voxel coordinates, clipped to the stored box
+  const int R = (int)__ldg(o.lvl + (cz * o.ny + cy) * o.nx + cx);  // radius (cells) of the void cube of cells around the cell
+  if (R == VR_OCC_SOLID) return -1;
+  if (R < 1) return 0;  // a single cell: about one step, not worth the geometry
+  // the cube of cells [c - R, c + R] as a box of base texels in global voxel coordinates, clipped to the stored box
   const float kMargin = 1.0e-4f;
   float t = 1.0e9f;
-  const int cl[3] = {cx >> l, cy >> l, cz >> l}, sh[3] = {o.sx, o.sy, o.sz}, lg[3] = {VR_OCC_LX + l, VR_OCC_LY + l, VR_OCC_LZ + l};
+  const int cc[3] = {cx, cy, cz}, sh[3] = {o.sx, o.sy, o.sz}, lg[3] = {VR_OCC_LX, VR_OCC_LY, VR_OCC_LZ};
   const int S[3] = {v.SX, v.SY, v.SZ}, org[3] = {SLAB ? v.ox : 0, SLAB ? v.oy : 0, SLAB ? v.oz : 0}, G[3] = {v.GX, v.GY, v.GZ};
   const float qq[3] = {q.x, q.y, q.z}, dd[3] = {d.x, d.y, d.z}, ii[3] = {inv.x, inv.y, inv.z}, rG[3] = {1.0f / v.fX, 1.0f / v.fY, 1.0f / v.fZ};
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
-    const int lo = max((cl[a] << lg[a]) - sh[a], 0) + org[a];
-    const int hi = (int)min((long long)((cl[a] + 1ll) << lg[a]) - sh[a], (long long)S[a]) + org[a];
+    const int lo = max(((cc[a] - R) << lg[a]) - sh[a], 0) + org[a];
+    const int hi = min(((cc[a] + R + 1) << lg[a]) - sh[a], S[a]) + org[a];
     const float plo = lo == 0 ? 0.0f : ((float)lo + 0.5f) * rG[a];
     const float phi = hi >= G[a] ? 1.0f : ((float)hi + 0.5f) * rG[a];
     if (dd[a] > 0.0f) t = fminf(t, (phi - kMargin - qq[a]) * ii[a]);

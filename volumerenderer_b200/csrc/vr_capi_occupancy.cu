@@ -44,7 +44,7 @@ int volume_occ_alloc(vr_volume* v) {
   CU(cudaSetDevice(v->device));
   CU(cudaMalloc((void**)&v->occRaw, n * VR_OCC_SLOTS));
   CU(cudaMalloc((void**)&v->occPyr, total));
-  CU(cudaMalloc((void**)&v->occLvl, n));
+  CU(cudaMalloc((void**)&v->occLvl, 3 * n));  // radii + two scratch passes (occ_levels_launch)
   v->occValid = false; v->occDilDirty = true;
   return VR_OK;
 }
