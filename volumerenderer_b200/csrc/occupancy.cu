@@ -124,6 +124,46 @@ __global__ void occ_dist_x_kernel(const uint8_t* __restrict__ pyr0, uint8_t* __r
     if ((cx - d >= 0 && (int)row[cx - d] > L.thr) || (cx + d < L.nx && (int)row[cx + d] > L.thr)) { g = d; break; }
   gx[i] = (uint8_t)g;
 }
+// The hot path's first two passes in one launch, one CTA per z-slice of cells (nx * ny cells in shared memory): dilation of the
+// raw maxima into level 0 of pyr (what occ_pyr_low_kernel writes there), distance along x, then along y.
+__global__ void __launch_bounds__(256) occ_dilate_dist_xy_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ pyr0, uint8_t* __restrict__ gy,
+                                                                 const __grid_constant__ OccView L) {
+  extern __shared__ uint8_t sm_occ[];
+  const int cells = L.nx * L.ny, cz = blockIdx.x;
+  uint8_t *solid = sm_occ, *gx = sm_occ + cells;
+  for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+    const int cx = i % L.nx, cy = i / L.nx;
+    unsigned m = 0;
+    for (int dz = 0; dz < 2; ++dz)
+      for (int dy = 0; dy < 2; ++dy)
+        for (int dx = 0; dx < 2; ++dx) {
+          const int x = min(cx + dx, L.nx - 1), y = min(cy + dy, L.ny - 1), z = min(cz + dz, L.nz - 1);
+          m = max(m, raw_max(raw, ((long long)z * L.ny + y) * L.nx + x));
+        }
+    pyr0[(long long)cz * cells + i] = (uint8_t)m;
+    solid[i] = (int)m > L.thr;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+    const int cx = i % L.nx;
+    const uint8_t* row = solid + (i - cx);
+    int g = VR_OCC_DIST_CAP;
+    for (int d = 0; d < VR_OCC_DIST_CAP; ++d)
+      if ((cx - d >= 0 && row[cx - d]) || (cx + d < L.nx && row[cx + d])) { g = d; break; }
+    gx[i] = (uint8_t)g;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+    const int cy = i / L.nx;
+    int best = gx[i];
+    for (int d = 1; d < best; ++d) {
+      if (cy - d >= 0) best = min(best, max(d, (int)gx[i - d * L.nx]));
+      if (cy + d < L.ny) best = min(best, max(d, (int)gx[i + d * L.nx]));
+    }
+    gy[(long long)cz * cells + i] = (uint8_t)best;
+  }
+}
+
 // stride = distance between neighbours along the axis, c / nc = coordinate and extent along it; out = min over d of max(d, in[c +- d])
 __global__ void occ_dist_axis_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, const __grid_constant__ OccView L, int axis, int finish) {
   const long long n = (long long)L.nx * L.ny * L.nz;
@@ -179,6 +219,19 @@ cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& L
   occ_dist_axis_kernel<<<blocks, 256, 0, stream>>>(gx, gy, L, 1, 0);
   occ_dist_axis_kernel<<<blocks, 256, 0, stream>>>(gy, lvl, L, 2, 1);
   return cudaGetLastError();
+}
+
+// Level 0 of pyr from raw AND lvl for L.thr in two launches (what a freshly decoded timestep needs before its frame); false when
+// a slice of cells does not fit in shared memory (the caller then takes occ_pyramid_launch + occ_levels_launch).
+bool occ_refresh_launch(const uint8_t* raw, uint8_t* pyr, uint8_t* lvl, const OccView& L, cudaStream_t stream, cudaError_t* err) {
+  const long long n = (long long)L.nx * L.ny * L.nz;
+  const size_t smem = 2 * (size_t)L.nx * L.ny;
+  if (smem > 40 * 1024) return false;
+  uint8_t* gy = lvl + 2 * n;
+  occ_dilate_dist_xy_kernel<<<(unsigned)L.nz, 256, smem, stream>>>(raw, pyr + L.off[0], gy, L);
+  occ_dist_axis_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(gy, lvl, L, 2, 1);
+  *err = cudaGetLastError();
+  return true;
 }
 
 cudaError_t occ_reduce_box_launch(const uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, const int64_t lo[3], const int64_t ext[3],

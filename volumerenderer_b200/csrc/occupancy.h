@@ -22,7 +22,7 @@ namespace vr {
 #define VR_OCC_MAX_LEVELS 12
 
 #define VR_OCC_SOLID 0xFF
-#define VR_OCC_DIST_CAP 64  // lvl[] radii are capped below this many cells
+#define VR_OCC_DIST_CAP 16  // lvl[] radii are capped below this many cells (step of the rm_yslab bench: 0.364 ms at 16, 0.366 at 32, 0.372 at 64)
 
 struct OccView {        // what the march kernels read (null pyr = no skipping)
   const uint8_t* pyr;
@@ -48,5 +48,8 @@ cudaError_t occ_pyramid_launch(const uint8_t* raw, uint8_t* pyr, const OccView& 
 // 3 x cells bytes, the last two thirds are scratch) -- a ray leaves such a cube in one skip, where octree cells made it stop at
 // every aligned boundary
 cudaError_t occ_levels_launch(const uint8_t* pyr, uint8_t* lvl, const OccView& layout, cudaStream_t stream);
+// level 0 of pyr (the dilated maxima) and lvl in two launches -- the per-timestep refresh; the octree levels above 0 are then stale
+// (nothing on the render path reads them; vr_volume_occupancy_download rebuilds them on demand).  false = grid too wide, not launched
+bool occ_refresh_launch(const uint8_t* raw, uint8_t* pyr, uint8_t* lvl, const OccView& layout, cudaStream_t stream, cudaError_t* err);
 
 }  // namespace vr

@@ -49,7 +49,7 @@ int volume_occ_alloc(vr_volume* v) {
   return VR_OK;
 }
 
-int volume_occ_view(vr_context* ctx, const vr_volume* cv, int thr, OccView* out) {
+int volume_occ_view(vr_context* ctx, const vr_volume* cv, int thr, OccView* out, bool wantPyramid) {
   std::memset(out, 0, sizeof(*out));
   vr_volume* v = const_cast<vr_volume*>(cv);  // the grids are a cache of the voxel data
   if (!v->skipping || thr < 0) return VR_OK;
@@ -67,14 +67,24 @@ int volume_occ_view(vr_context* ctx, const vr_volume* cv, int thr, OccView* out)
   out->nx = v->nc[0]; out->ny = v->nc[1]; out->nz = v->nc[2];
   out->sx = v->shift[0]; out->sy = v->shift[1]; out->sz = v->shift[2];
   out->thr = thr;
-  if (v->occDilDirty) {
-    CU(occ_pyramid_launch(v->occRaw, v->occPyr, *out, ctx->stream));
+  if (v->occDilDirty || v->occLvlThr != thr) {
+    // a freshly decoded timestep (or a new threshold): dilated level 0 + void radii in two launches; the octree levels above
+    // level 0 are only built when somebody asks for them (wantPyramid: vr_volume_occupancy_download)
+    cudaError_t e = cudaSuccess;
+    if (occ_refresh_launch(v->occRaw, v->occPyr, v->occLvl, *out, ctx->stream, &e)) {
+      CU(e);
+      if (v->occDilDirty) v->occPyrHigh = false;
+    } else {
+      CU(occ_pyramid_launch(v->occRaw, v->occPyr, *out, ctx->stream));
+      CU(occ_levels_launch(v->occPyr, v->occLvl, *out, ctx->stream));
+      v->occPyrHigh = true;
+    }
     v->occDilDirty = false;
-    v->occLvlThr = -2;
-  }
-  if (v->occLvlThr != thr) {
-    CU(occ_levels_launch(v->occPyr, v->occLvl, *out, ctx->stream));
     v->occLvlThr = thr;
+  }
+  if (wantPyramid && !v->occPyrHigh) {
+    CU(occ_pyramid_launch(v->occRaw, v->occPyr, *out, ctx->stream));
+    v->occPyrHigh = true;
   }
   out->pyr = v->occPyr;
   out->lvl = v->occLvl;
@@ -131,7 +141,7 @@ int vr_volume_invalidate(vr_volume* v) {
 int vr_volume_occupancy_download(vr_context* ctx, const vr_volume* v, int32_t which, uint8_t* out_host, int64_t cap, int32_t dims[3]) {
   if (!ctx || !v || !dims) return fail(VR_ERR_ARG, "null");
   OccView ov;
-  int rc = volume_occ_view(ctx, v, 0, &ov);
+  int rc = volume_occ_view(ctx, v, 0, &ov, which >= 2);
   if (rc != VR_OK) return rc;
   if (!ov.pyr) return fail(VR_ERR_STATE, "skipping is disabled for this volume");
   if (which < 0 || which > ov.nlev) return fail(VR_ERR_ARG, "no such level");

@@ -78,8 +78,9 @@ struct vr_volume {
   uint8_t *occRaw = nullptr, *occPyr = nullptr;  // raw: 8 writer slots per cell; pyr: dilated level 0 + octree of maxima
   bool occValid = false;          // occRaw bounds every stored voxel
   bool occDilDirty = true;        // occPyr needs recomputing from occRaw
-  uint8_t* occLvl = nullptr;      // per level-0 cell: highest void level for threshold occLvlThr (occupancy.h)
+  uint8_t* occLvl = nullptr;      // per level-0 cell: radius of the void cube of cells around it for threshold occLvlThr (occupancy.h)
   int occLvlThr = -2;             // -2 = occLvl is stale
+  bool occPyrHigh = false;        // the octree levels above level 0 of occPyr are current (built on demand)
   int occEpoch = 0;               // bumped whenever the grids are freed (plans remember the epoch they were built for)
   // Plans whose last run was lazy (vr_render_compressed_lazy): the tiles their frame could not read hold stale voxels,
   // so every entry point that reads stored voxels (vr_render, vr_volume_download, vr_kd_compress_volume, vr_volume_pack_box,
@@ -161,7 +162,7 @@ struct PeerTargets;
 // fills t for a fused kernel that signals `slot` at every rank (vr_capi_peer.cu); windowBytes = usable window size
 int peer_targets(struct ::vr_peer* p, int slot, PeerTargets* t, int64_t* windowBytes);
 int volume_occ_alloc(vr_volume* v);                       // allocate the grids for the current cellOrigin
-int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out);  // build / refresh as needed; out->dil = null when off
+int volume_occ_view(vr_context* ctx, const vr_volume* v, int thr, OccView* out, bool wantPyramid = false);  // build / refresh as needed; out->dil = null when off
 // the march of vr_render without the partial-volume check (lazy path)
 // solidMaskDev (optional, one byte per occupancy cell): look-up cells where the iso crossing test cannot fire because
 // every reachable voxel is >= isoValue (kd_cull.h); the march skips the fetch there as it does in void cells
