@@ -341,6 +341,8 @@ def run_ours(args):
     peer = None
     if world > 1:
         from volumerenderer_b200 import sortlast
+        if args.tin_min_ranks is not None:
+            sortlast.PeerExchange.T_IN_MIN_RANKS = args.tin_min_ranks
         G = (GI * BX, BY * world, GK * BZ)
         descs, stored = sortlast.slab_layout(G, world, axis=1, halo=sortlast.required_halo(p, G))
         so, se = stored[rank]
@@ -911,6 +913,7 @@ def main():
                     help="strictly sequential steps (decode, then frame) instead of decode(t+1) overlapping frame(t) on two slabs")
     ap.add_argument("--schedule", default="two-stream", choices=["interleaved", "two-stream"],
                     help="N > 1 with the peer exchange: how decode(t+1) and frame(t) share the GPU (one stream, stages interleaved; or two streams)")
+    ap.add_argument("--tin-min-ranks", type=int, default=None, help="A/B: rank count from which the T_in stripe exchange replaces the all-gather of T_seg")
     ap.add_argument("--debug", action="append", default=[], metavar="KEY=VALUE",
                     help="A/B runs: vr_debug_set(KEY, VALUE) before anything is created (e.g. decode_split=1, decode_only=2: timing probes)")
     ap.add_argument("--no-extras", action="store_true", help="N = 1: skip the extra frames and the stream-dense decode workloads")

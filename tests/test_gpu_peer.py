@@ -95,7 +95,7 @@ def test_frame_over_peer_windows(full, n, axis, mode):
         c.close()
 
 
-@pytest.mark.parametrize("n", [1, 2, 4])
+@pytest.mark.parametrize("n", [1, 2, 4, 8])
 @pytest.mark.parametrize("mode", [render.COMPOSITE, render.ISOSURFACE])
 def test_whole_frame_through_the_c_entry(full, n, mode):
     """vr_sortlast_exchange_halos + vr_sortlast_render (csrc/vr_capi_frame.cu): one C call per timestep / per frame, every

@@ -380,11 +380,13 @@ class PeerExchange:
         yield self._view(self.off_total, (params.height, params.width, 4), self.torch.float32)
 
     TIN = 4
+    T_IN_MIN_RANKS = 5  # from this many ranks up the T_in stripe exchange replaces the all-gather of T_seg (measured: slower on 2,
+                        # equal on 4 -- 0.511 vs 0.509 ms per step -- faster on 8 GPUs)
 
     def frame_stages_hybrid(self, ops, params, frame_to=None, t_in=None):
         """COMPOSITE frame, the default: plain march kernels, the hand-overs as coalesced copy kernels into the peers' windows,
         the last pass (sum of the ranks' terms + colour map) as ONE kernel that stores the finished stripes.  Five stages.
-        t_in (default: n >= 4): instead of an all-gather of T_seg (n - 1 image-sized transfers per rank), stripe j of T_seg goes
+        t_in (default: n > 4): instead of an all-gather of T_seg (n - 1 image-sized transfers per rank), stripe j of T_seg goes
         to rank j, which hands every rank the transmittance in front of its segment (vr_peer_tin_composite): 2 (n-1)/n
         transfers and one more round trip -- measured slower on 2 GPUs (0.30 vs 0.28 ms per frame), faster on 8.  T_in lives
         in the unused half of the stripes-in area (composite terms need 8P of its 16P bytes).
@@ -392,7 +394,7 @@ class PeerExchange:
         assert params.mode == COMPOSITE
         everyone = list(range(self.n))
         if t_in is None:
-            t_in = self.n >= 4
+            t_in = self.n >= self.T_IN_MIN_RANKS
         cseg, tseg = ops.partial_composite(params)
         if t_in:
             s4 = 4 * self.P // self.n
