@@ -13,6 +13,8 @@
 //    byte permute -- instead of 6 ALU operations per node.
 //  * chains: one look-up in a 16 K-entry table (shared memory) gives the whole chain as x -> min(max(x + A, lo), hi) and
 //    the number of bits the voxel item occupies.
+//  * the two voxels of a height-1 node are finished together in 16-bit lanes (voxel_pair): 10 instead of 14 instructions
+//    on the integer pipe.
 //  * bit window: the three lowest levels of the tree (an octet: 7 nodes, 8 voxels) are straight-line code, so the
 //    places where the 32-bit window has to be re-aligned are known at compile time: 6 per octet instead of one per
 //    symbol, each branch-free (a refill is two predicated instructions).  Between them a token costs one shift.
@@ -245,6 +247,75 @@ VR_HD void voxel(Cur<WIN>& s, uint32_t word, uint32_t base) {
   s.o += e;                      // only the low byte counts: repeek() masks
 }
 
+// Both voxels of a height-1 node at once: the two chains are looked up one after the other (the second item starts where the
+// first one ends), the arithmetic runs in 16-bit lanes -- one permute each gathers (x0, x1), (A0, A1) sign-extended,
+// (lo0, lo1), (hi0, hi1) from the select word and the two table entries, one fused add-max and one min finish both.
+// 10 instructions instead of 14 on the pipe that bounds the parser (VR6_PAIR=0 keeps the one-by-one version for A/B).
+#ifndef VR6_PAIR
+#define VR6_PAIR 1
+#endif
+VR_HD uint32_t addmax_s16x2(uint32_t a, uint32_t b, uint32_t c) {  // per 16-bit lane: max(a + b, c), signed
+#if VR6_DEV
+  return __viaddmax_s16x2(a, b, c);
+#else
+  uint32_t r = 0;
+  for (int k = 0; k < 2; ++k) {
+    const int x = (int16_t)(a >> (16 * k)) + (int16_t)(b >> (16 * k)), y = (int16_t)(c >> (16 * k));
+    r |= ((uint32_t)(uint16_t)(int16_t)(x > y ? x : y)) << (16 * k);
+  }
+  return r;
+#endif
+}
+VR_HD uint32_t min_s16x2(uint32_t a, uint32_t b) {
+#if VR6_DEV
+  return __vmins2(a, b);
+#else
+  uint32_t r = 0;
+  for (int k = 0; k < 2; ++k) {
+    const int x = (int16_t)(a >> (16 * k)), y = (int16_t)(b >> (16 * k));
+    r |= ((uint32_t)(uint16_t)(int16_t)(x < y ? x : y)) << (16 * k);
+  }
+  return r;
+#endif
+}
+template <int ROT, int POS, class WIN>
+VR_HD void voxel_pair(Cur<WIN>& s, uint32_t word, uint32_t base) {
+  if (POS == 2 || POS == 6) s.repeek();
+  const uint32_t bits0 = s.bits;
+  const uint32_t e0 = item_entry(s.lut, bits0);
+  s.bits = shr_wrap(bits0, e0);
+  s.o += e0;
+  if (POS == 0 || POS == 4) s.repeek();  // before voxels 1 and 5
+  const uint32_t bits1 = s.bits;
+  const uint32_t e1 = item_entry(s.lut, bits1);
+  s.bits = shr_wrap(bits1, e1);
+  s.o += e1;
+  // selector of (x0, 0, x1, 0): the two symbols in nibbles 0 and 2, nibbles 1 and 3 = byte 4 (zero)
+#if VR6_DEV
+  uint32_t sel;
+  asm("{\n"
+      ".reg .b32 t;\n"
+      "lop3.b32 t, %2, 0x300, 0x4040, 0xEA;\n"  // (a & b) | c
+      "lop3.b32 %0, %1, 3, t, 0xEA;\n"
+      "}\n"
+      : "=r"(sel)
+      : "r"(bits0), "r"(bits1 * 256u));
+#else
+  const uint32_t sel = (bits0 & 3u) | ((bits1 * 256u) & 0x300u) | 0x4040u;
+#endif
+  const uint32_t X = Mem::perm(word, 0u, sel);
+  const uint32_t A = Mem::perm(e0, e1, 0xF7B3u);   // (A0, sign, A1, sign)
+  const uint32_t LO = Mem::perm(e0, e1, 0x8581u);  // (lo0, 0, lo1, 0): nibble 8 = sign of the length byte = 0
+  const uint32_t HI = Mem::perm(e0, e1, 0x8682u);
+  const uint32_t V = min_s16x2(addmax_s16x2(X, A, LO), HI);
+  if constexpr (Geo<ROT>::xbit == 0) {  // x neighbours: one 16-bit store
+    Mem::st16(base + (uint32_t)Geo<ROT>::off(POS), Mem::perm(V, 0u, 0x4420u));
+  } else {
+    Mem::st8(base + (uint32_t)Geo<ROT>::off(POS), V);
+    Mem::st8(base + (uint32_t)Geo<ROT>::off(POS + 1), V >> 16);
+  }
+}
+
 template <int ROT, int H, int POS, class WIN>
 struct Node {  // H = 1 or 2
   static VR_HD void run(Cur<WIN>& s, uint32_t word, const Dist& d, uint32_t base) {
@@ -260,8 +331,12 @@ struct Node {  // H = 1 or 2
         Node<ROT, 1, POS, WIN>::run(s, cw, d, base);
         Node<ROT, 1, POS + 2, WIN>::run(s, cw, d, base);
       } else {
+#if VR6_PAIR
+        voxel_pair<ROT, POS, WIN>(s, cw, base);
+#else
         voxel<ROT, POS, WIN>(s, cw, base);
         voxel<ROT, POS + 1, WIN>(s, cw, base);
+#endif
       }
     }
   }
