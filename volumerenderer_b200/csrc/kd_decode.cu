@@ -90,6 +90,17 @@ __device__ __forceinline__ uint32_t src_of(const Decode6Params& p, uint32_t idx)
 // asynchronous copies (LDGSTS), all lanes taking part.  Not the TMA unit: its queue is shared with the constant groups' tensor
 // stores, and a unit's load stuck behind a few hundred KB of HBM-bound stores starves the parser (measured: the launch took
 // longer than its two halves one after the other).  ia / ib = the first 32 bytes of the item, valid in lane 0.
+// A queue ticket = n consecutive units; the counter counts tickets.  atom.inc on purpose: an atomicAdd() by one lane is
+// rewritten (by ptxas, inline PTX included) into its warp-aggregated form, which reads the result back with a shuffle
+// right behind the atomic -- the warp then waits out the whole round trip to L2 (several microseconds while the constant
+// groups saturate HBM: 22 % of the parse warps' stall samples on the bench slab, profiles/r2_ticket_ab.md) although the
+// ticket is not needed before the next unit.  A wrapping increment cannot be aggregated (with a bound of 2^32 - 1 ptxas turns it
+// back into an add, hence 2^31 - 1: never reached).
+__device__ __forceinline__ uint32_t take_ticket(uint32_t* q) {  // first unit = ticket * p.batch, multiplied where it is used
+  uint32_t r;
+  asm volatile("atom.global.inc.u32 %0, [%1], 0x7FFFFFFF;" : "=r"(r) : "l"(q) : "memory");
+  return r;
+}
 __device__ __forceinline__ void cp16(uint32_t dstS, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dstS), "l"(src) : "memory");
 }
@@ -148,21 +159,31 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     unitOff[j] = (uint32_t)((p.pg.wAxis[j] == 0 ? (int64_t)1 : (p.pg.wAxis[j] == 1 ? p.rowPitch : p.slicePitch)) << p.pg.wCb[j]);
 
   // idxA = unit being parsed, idxB = next (item half in b0 / b1), idxC = the one after (item half requested below).  Tickets are
-  // batches of VR6_BATCH consecutive units: (curBase, curPos) = where idxC sits in its batch, nextBase = the batch behind it,
+  // batches of p.batch consecutive units: (curBase, curPos) = where idxC sits in its batch, nextBase = the TICKET of the batch behind it,
   // requested a whole batch ahead (lane 0 only).
   const uint4 z4 = make_uint4(0, 0, 0, 0);
   uint32_t idxA = 0, idxB = 0, idxC = 0, curBase = 0, curPos = 0, nextBase = 0;
   uint4 a0 = z4, a1 = z4, b0 = z4, b1 = z4;
+  // The first tickets of a warp are static (ticket k * W + gw, W = parse warps of the grid; 3 of them when a ticket is one
+  // unit, else 2), the counter hands out the ones behind them: the first units start without a round trip to L2.
+  const uint32_t W = gridDim.x * VR6_PARSE_WARPS, gw = blockIdx.x * VR6_PARSE_WARPS + warp;
+  const uint32_t tOff = (p.batch == 1u ? 3u : 2u) * W;  // nextBase holds ticket - tOff (what the counter returns)
   if (lane == 0) {
-    curBase = atomicAdd(p.queue, p.batch);
-    nextBase = atomicAdd(p.queue, p.batch);
+    curBase = gw * p.batch;
+    nextBase = W + gw - tOff;
     // the first three units: positions 0, 1, 2 of the ticket sequence (tickets may hold fewer than three units)
     idxA = curBase; curPos = 0u;
-    if (curPos + 1u < p.batch) { ++curPos; idxB = curBase + curPos; } else { curBase = nextBase; curPos = 0u; idxB = curBase; nextBase = atomicAdd(p.queue, p.batch); }
-    if (curPos + 1u < p.batch) { ++curPos; idxC = curBase + curPos; } else { curBase = nextBase; curPos = 0u; idxC = curBase; nextBase = atomicAdd(p.queue, p.batch); }
+    if (curPos + 1u < p.batch) { ++curPos; idxB = curBase + curPos; } else { curBase = (nextBase + tOff) * p.batch; curPos = 0u; idxB = curBase; nextBase = 2u * W + gw - tOff; }
+    if (curPos + 1u < p.batch) { ++curPos; idxC = curBase + curPos; } else { curBase = (nextBase + tOff) * p.batch; curPos = 0u; idxC = curBase; nextBase = take_ticket(p.queue); }
     if (idxA < p.nParse) { a0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA))); a1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA)) + 1); }
     if (idxB < p.nParse) { b0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB))); b1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB)) + 1); }
   }
+  // the chain table, while those requests are in flight (the parse warps only: the fill warp does not wait for it)
+  for (uint32_t i = threadIdx.x; i < VR6_LUT_BYTES / 16u; i += VR6_PARSE_WARPS * 32u) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.lut) + i);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sb + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(VR6_PARSE_WARPS * 32) : "memory");
   idxA = __shfl_sync(0xFFFFFFFFu, idxA, 0);
   idxB = __shfl_sync(0xFFFFFFFFu, idxB, 0);
   idxC = __shfl_sync(0xFFFFFFFFu, idxC, 0);
@@ -175,7 +196,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     if (lane == 0) {
       if (idxC < p.nParse) { c0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC))); c1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC)) + 1); }
       if (curPos + 1u < p.batch) { ++curPos; idxD = curBase + curPos; }
-      else { curBase = nextBase; curPos = 0u; idxD = curBase; nextBase = atomicAdd(p.queue, p.batch); }
+      else { curBase = (nextBase + tOff) * p.batch; curPos = 0u; idxD = curBase; nextBase = take_ticket(p.queue); }
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
@@ -268,11 +289,12 @@ __device__ __forceinline__ void fill_warp(const Decode6Params& p, const uint32_t
   uint32_t victim = 0;
   uint64_t policy = 0;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  // tickets of 8 groups; the first one is static (the CTA's index), the next one is requested while this one is worked on
+  uint32_t tk = blockIdx.x - gridDim.x;  // ticket - gridDim.x, as the counter returns it
   for (;;) {
-    uint32_t j0 = 0;
-    if (lane == 0) j0 = atomicAdd(p.queue + VR6_QUEUE_FILL, 8u);
-    j0 = __shfl_sync(0xFFFFFFFFu, j0, 0);
+    const uint32_t j0 = (__shfl_sync(0xFFFFFFFFu, tk, 0) + gridDim.x) * 8u;
     if (j0 >= p.nFill) break;
+    if (lane == 0) tk = take_ticket(p.queue + VR6_QUEUE_FILL);
     const uint32_t n = min(8u, p.nFill - j0);
     uint4 a = make_uint4(0, 0, 0, 0), b = a;
     if (lane < n) {
@@ -343,11 +365,6 @@ __global__ void __launch_bounds__(VR6_THREADS, 1) kd_decode6_kernel(const __grid
   extern __shared__ __align__(128) uint8_t smem6[];
   const uint32_t sb = (uint32_t)__cvta_generic_to_shared(smem6);
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
-  for (uint32_t i = tid; i < VR6_LUT_BYTES / 16u; i += blockDim.x) {
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.lut) + i);
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sb + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-  }
-  __syncthreads();
   if (warp >= VR6_PARSE_WARPS) {
     if (p.only != 1 && p.nFill) fill_warp(p, sb + VR6_OFF_IMG, lane);
   } else if (p.only != 2 && p.nParse) {
