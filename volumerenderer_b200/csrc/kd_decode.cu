@@ -46,7 +46,8 @@ namespace vr {
 #define VR6_WARP_ITEM (VR6_WARP_STRIPS + 32u * VR6_STRIP_PITCH)    // 64 bytes
 #define VR6_WARP_LEAFOFF (VR6_WARP_ITEM + 64u)                     // 128 bytes
 #define VR6_WARP_LEAFVAL (VR6_WARP_LEAFOFF + 128u)                 // 32 bytes
-#define VR6_WARP_BYTES 7168u                                       // 7 104 used; a multiple of 128 (tensor stores read aligned boxes)
+#define VR6_WARP_MBAR (VR6_WARP_LEAFVAL + 32u)                     // 8 bytes: completion of the staging copies
+#define VR6_WARP_BYTES 7168u                                       // 7 112 used; a multiple of 128 (tensor stores read aligned boxes)
 #define VR6_QUEUE_FILL 32u  // the constant groups' counter lives on its own 128-byte line
 #define VR6_BATCH_MAX 4u    // units per queue ticket: one atomic per unit on one address serialises in L2 (38 % of the stalls on
                             // 262 144 units); short queues take single units, whose costs differ by 10x, for balance
@@ -104,7 +105,12 @@ __device__ __forceinline__ uint32_t take_ticket(uint32_t* q) {  // first unit = 
 __device__ __forceinline__ void cp16(uint32_t dstS, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dstS), "l"(src) : "memory");
 }
-__device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t wbase, uint32_t lane) {
+// Completion of a unit's staging copies is tracked by the warp's mbarrier (one noinc arrival per lane once its copies have
+// landed), not by cp.async groups: groups of asynchronous copies and bulk (TMA) groups count on ONE scoreboard in this part
+// (cp.async.wait_group N and cp.async.bulk.wait_group[.read] N assemble to the same DEPBAR.LE SB0, N), so a wait for the
+// staging would also wait for the previous unit's tensor store and the other way round.
+__device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t wbase, uint32_t segS,
+                                           uint32_t barS, uint32_t lane) {
   const uint64_t ar = (uint64_t)__shfl_sync(0xFFFFFFFFu, ia.x, 0) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, ia.y, 0) << 32);
   const uint8_t* arena = reinterpret_cast<const uint8_t*>(ar);
   const uint32_t segOff = __shfl_sync(0xFFFFFFFFu, ia.z, 0), segChunks = __shfl_sync(0xFFFFFFFFu, ia.w, 0);
@@ -113,9 +119,19 @@ __device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx,
   if (lane < 4u) cp16(wbase + VR6_WARP_ITEM + 16u * lane, reinterpret_cast<const uint8_t*>(p.parse + (lane == 0u ? src_of(p, idx) : idx)) + 16u * lane);
   else if (lane < 12u) cp16(wbase + VR6_WARP_LEAFOFF + 16u * (lane - 4u), arena + leafOffOff + 16u * (lane - 4u));
   else if (lane < 14u) cp16(wbase + VR6_WARP_LEAFVAL + 16u * (lane - 12u), arena + leafValOff + 16u * (lane - 12u));
-  const uint32_t st = wbase + VR6_WARP_STAGE + ((p.tmaOut && segChunks <= VR6_SMALL_CHUNKS) ? VR6_BOX_BYTES : 0u);
-  for (uint32_t c = lane; c < segChunks; c += 32u) cp16(st + 16u * c, arena + segOff + 16u * c);
-  asm volatile("cp.async.commit_group;" ::: "memory");
+  for (uint32_t c = lane; c < segChunks; c += 32u) cp16(segS + 16u * c, arena + segOff + 16u * c);
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(barS) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t barS, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "W6_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra W6_%=;\n"
+      "}\n" ::"r"(barS),
+      "r"(parity)
+      : "memory");
 }
 // Pulls everything unit `idx` will stage into L2 -- its stream segment (one 128-byte line per lane), its index entries and its
 // item -- two units ahead of the staging copies: next to the constant groups HBM is write-saturated and a read that misses L2
@@ -138,12 +154,12 @@ __device__ __forceinline__ void prefetch_unit(const Decode6Params& p, uint32_t i
 template <int ROT>
 __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_t sb, const uint32_t warp, const uint32_t lane) {
   const uint32_t wbase = sb + VR6_LUT_BYTES + warp * VR6_WARP_BYTES;
-  const uint32_t strips = wbase + VR6_WARP_STRIPS, stageS = wbase + VR6_WARP_STAGE, boxS = wbase + VR6_WARP_STAGE;
+  const uint32_t strips = wbase + VR6_WARP_STRIPS, stageS = wbase + VR6_WARP_STAGE, barS = wbase + VR6_WARP_MBAR;
   const uint32_t lutS = sb + VR6_OFF_LUT;
   const uint32_t xs0 = p.pg.xs[0], xs1 = p.pg.xs[1];
   const uint32_t myStrip = strips + lane * VR6_STRIP_PITCH;
   // phase-2 constants of this lane for unit 0 of a tile (the unit index adds a per-unit offset): four 16-byte runs
-  // (tensor-store mode: gRun = the run's place in the unit's dense box in shared memory instead of its offset in the slab)
+  // (tensor-store mode: gRun = the run's place in the unit's dense box instead of its offset in the slab)
   uint32_t sRun[4], gRun[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -151,7 +167,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     int64_t go;
     vr6::p6_run_addr(p.pg, 0u, lane + 32u * (uint32_t)k, p.rowPitch, p.slicePitch, &s, &go);
     sRun[k] = strips + s;
-    gRun[k] = p.tmaOut ? boxS + vr6::p6_box_off(p.pg, lane + 32u * (uint32_t)k) : (uint32_t)go;
+    gRun[k] = p.tmaOut ? vr6::p6_box_off(p.pg, lane + 32u * (uint32_t)k) : (uint32_t)go;
   }
   uint32_t unitOff[3];  // destination offset of unit bits 0..2
 #pragma unroll
@@ -178,6 +194,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     if (idxA < p.nParse) { a0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA))); a1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxA)) + 1); }
     if (idxB < p.nParse) { b0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB))); b1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxB)) + 1); }
   }
+  if (lane == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], 32;" ::"r"(barS) : "memory");  // visible to the warp after the barrier below
   // the chain table, while those requests are in flight (the parse warps only: the fill warp does not wait for it)
   for (uint32_t i = threadIdx.x; i < VR6_LUT_BYTES / 16u; i += VR6_PARSE_WARPS * 32u) {
     const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.lut) + i);
@@ -187,7 +204,19 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
   idxA = __shfl_sync(0xFFFFFFFFu, idxA, 0);
   idxB = __shfl_sync(0xFFFFFFFFu, idxB, 0);
   idxC = __shfl_sync(0xFFFFFFFFu, idxC, 0);
-  if (idxA < p.nParse) stage_unit(p, idxA, a0, a1, wbase, lane);
+  // The staging area is two regions, R0 = [0, 2 048) and R1 = [2 048, 4 704).  A unit's segment sits in one of them and its
+  // voxel box (2 048 B) is later written over it, so the OTHER region is free while the unit is parsed: the next unit is
+  // staged there half-way through the parsing (its copies then have the rest of the unit to land), not after it.  A
+  // segment longer than its region ("big": starts at 0 and reaches into R1; noise-like data) falls back to staging
+  // after the parsing (if the next segment fits R1) or after the tensor store has read the box.
+  uint32_t curOff = 0, parity = 0;
+  bool curBig = false;
+  if (idxA < p.nParse) {
+    const uint32_t bytesA = 16u * __shfl_sync(0xFFFFFFFFu, a0.w, 0);
+    curOff = bytesA <= VR6_STAGE_BYTES - VR6_BOX_BYTES ? VR6_BOX_BYTES : 0u;
+    curBig = bytesA > VR6_STAGE_BYTES - VR6_BOX_BYTES;
+    stage_unit(p, idxA, a0, a1, wbase, stageS + curOff, barS, lane);
+  }
   if (idxB < p.nParse) prefetch_unit(p, idxB, b0, b1, lane);
   while (idxA < p.nParse) {
     // requests for later units first, so that they are in flight while this one is parsed
@@ -198,39 +227,59 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
       if (curPos + 1u < p.batch) { ++curPos; idxD = curBase + curPos; }
       else { curBase = (nextBase + tOff) * p.batch; curPos = 0u; idxD = curBase; nextBase = take_ticket(p.queue); }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
+    mbar_wait(barS, parity);  // this unit's segment, index entries and item are in shared memory
+    parity ^= 1u;
     const uint4 i0 = lds128(wbase + VR6_WARP_ITEM), i2 = lds128(wbase + VR6_WARP_ITEM + 32u), i3 = lds128(wbase + VR6_WARP_ITEM + 48u);
-    const uint32_t segOff = i0.z, segChunks = i0.w;
+    const uint32_t segOff = i0.z;
     const uint64_t treeDist = (uint64_t)i2.x | ((uint64_t)i2.y << 32);
     const int64_t dstOff = (int64_t)((uint64_t)i2.z | ((uint64_t)i2.w << 32));
     const int32_t occCell = (int32_t)i3.w;
     const uint32_t unit = lds32(wbase + VR6_WARP_ITEM + 28u) & 7u;  // tileUnit
-    // ---- phase 1: one leaf subtree per lane ----
-    {
-      const uint32_t off = lds32(wbase + VR6_WARP_LEAFOFF + 4u * lane), val = lds8(wbase + VR6_WARP_LEAFVAL + lane);
-      vr6::Dist d;
-      d.d0 = (uint32_t)treeDist & 0xFFu; d.d1 = (uint32_t)(treeDist >> 8) & 0xFFu; d.d2 = (uint32_t)(treeDist >> 16) & 0xFFu;
-      d.d3 = (uint32_t)(treeDist >> 24) & 0xFFu; d.d4 = (uint32_t)(treeDist >> 32) & 0xFFu; d.d5 = (uint32_t)(treeDist >> 40) & 0xFFu;
-      if (off == VR_PRUNED) {
-        vr6::fill_leaf(myStrip, val);
-      } else {
-        vr6::WinShared w;
-        w.init(stageS + ((p.tmaOut && segChunks <= VR6_SMALL_CHUNKS) ? VR6_BOX_BYTES : 0u) - segOff, off);
-        vr6::parse_leaf<ROT>(w, val, d, lutS, myStrip);
+    const uint32_t off = lds32(wbase + VR6_WARP_LEAFOFF + 4u * lane), val = lds8(wbase + VR6_WARP_LEAFVAL + lane);
+    // where the next unit's segment can go
+    const bool haveB = idxB < p.nParse;
+    const uint32_t bytesB = 16u * __shfl_sync(0xFFFFFFFFu, b0.w, 0);
+    const uint32_t otherOff = curOff ? 0u : VR6_BOX_BYTES, otherCap = curOff ? VR6_BOX_BYTES : VR6_STAGE_BYTES - VR6_BOX_BYTES;
+    const bool fitsOther = haveB && bytesB <= otherCap;
+    const bool early = fitsOther && !curBig;
+    // ---- phase 1: one leaf subtree per lane, first half ----
+    vr6::Dist d;
+    d.d0 = (uint32_t)treeDist & 0xFFu; d.d1 = (uint32_t)(treeDist >> 8) & 0xFFu; d.d2 = (uint32_t)(treeDist >> 16) & 0xFFu;
+    d.d3 = (uint32_t)(treeDist >> 24) & 0xFFu; d.d4 = (uint32_t)(treeDist >> 32) & 0xFFu; d.d5 = (uint32_t)(treeDist >> 40) & 0xFFu;
+    vr6::WinShared w;
+    uint32_t wo = 2u;  // bits consumed since the window's last re-alignment: the root's symbol
+    const uint32_t word6 = vr6::mkword(val, d.d5);
+    if (off == VR_PRUNED) {
+      vr6::fill_leaf(myStrip, val);
+    } else {
+      w.init(stageS + curOff - segOff, off);
+      vr6::parse_leaf_half<ROT, 0>(w, wo, word6, d, lutS, myStrip);
+    }
+    __syncwarp();  // every lane has read its index entry and the item
+    if (early) {   // the other region held the previous unit's box: its tensor store (issued half a unit ago) must have read it
+      if (p.tmaOut) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
       }
+      stage_unit(p, idxB, b0, b1, wbase, stageS + otherOff, barS, lane);
     }
-    __syncwarp();  // every lane is done with the staged segment, the index entries and the item; the leaf blocks are complete
-    // Unit n+1 is staged while unit n's voxels are stored.  Tensor-store mode: only if its segment fits behind the box; a
-    // longer one needs the whole staging area and has to wait until the TMA unit has read this unit's box (below).
-    const bool nextNow = idxB < p.nParse && (!p.tmaOut || __shfl_sync(0xFFFFFFFFu, b0.w, 0) <= VR6_SMALL_CHUNKS);
-    if (nextNow) stage_unit(p, idxB, b0, b1, wbase, lane);
+    // ---- second half ----
+    if (off != VR_PRUNED) vr6::parse_leaf_half<ROT, 4>(w, wo, word6, d, lutS, myStrip);
+    __syncwarp();  // every lane is done with the staged segment; the leaf blocks are complete
+    bool staged = early;
+    if (!staged && fitsOther) {  // this unit's segment was big; now that it is consumed the other region is free
+      if (p.tmaOut) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+      }
+      stage_unit(p, idxB, b0, b1, wbase, stageS + otherOff, barS, lane);
+      staged = true;
+    }
     // ---- phase 2: the warp's 32 leaf blocks -> 128 runs of 16 voxels along x, four per lane ----
+    // (tensor-store mode: into the unit's box, which takes the place of its segment; no tensor store is reading that
+    // region: every staging above waited for the stores before it, and the one store since then read the other region)
     uint8_t* dstUnit = p.dst + dstOff + ((unit & 1u) ? unitOff[0] : 0u) + ((unit & 2u) ? unitOff[1] : 0u) + ((unit & 4u) ? unitOff[2] : 0u);
-    if (p.tmaOut) {  // the box is free once the previous unit's tensor store has read it (issued a whole unit ago)
-      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      __syncwarp();
-    }
+    const uint32_t boxS = stageS + curOff;
     // byte maxima through 16-bit lanes: a 16-bit maximum is exact in its HIGH byte, so bytes 1 / 3 come from the words as they
     // are and bytes 0 / 2 from the words shifted left by 8 (the shift runs on the multiply-add pipe)
     uint32_t m13 = 0, m02 = 0;
@@ -238,7 +287,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     for (int k = 0; k < 4; ++k) {
       const uint32_t a = sRun[k];
       const uint32_t w0 = lds32(a), w1 = lds32(a + xs0), w2 = lds32(a + xs1), w3 = lds32(a + xs0 + xs1);
-      if (p.tmaOut) asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(gRun[k]), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+      if (p.tmaOut) asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(boxS + gRun[k]), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
       else if (p.only != 3) *reinterpret_cast<uint4*>(dstUnit + gRun[k]) = make_uint4(w0, w1, w2, w3);  // (3: timing probe without the voxel stores)
       m13 = __vmaxu2(__vmaxu2(m13, w0), __vmaxu2(w1, __vmaxu2(w2, w3)));
       m02 = __vmaxu2(__vmaxu2(m02, w0 * 256u), __vmaxu2(w1 * 256u, __vmaxu2(w2 * 256u, w3 * 256u)));
@@ -256,12 +305,16 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
                      : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
-      if (idxB < p.nParse && !nextNow) {  // a long segment next: it overwrites the box
+    }
+    if (haveB && !staged) {  // the next segment needs more than the other region: from offset 0, once this unit's box has been read
+      if (p.tmaOut) {
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
-        stage_unit(p, idxB, b0, b1, wbase, lane);
       }
+      stage_unit(p, idxB, b0, b1, wbase, stageS, barS, lane);
     }
+    curOff = staged ? otherOff : 0u;
+    curBig = !staged && bytesB > VR6_BOX_BYTES;
     if (p.occ && occCell >= 0) {  // this unit's maximum -> its slot of the tile's occupancy cell
       uint32_t m = max(max((m13 >> 8) & 0xFFu, m13 >> 24), max((m02 >> 8) & 0xFFu, m02 >> 24));
       m = __reduce_max_sync(0xFFFFFFFFu, m);

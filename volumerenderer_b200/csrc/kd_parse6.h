@@ -342,13 +342,15 @@ struct Node {  // H = 1 or 2
   }
 };
 
-// One leaf subtree.  The window stands on the root's own symbol (known to be an inner node; its value is rootVal).
-template <int ROT, class WIN>
-VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uint32_t strip) {
-  Cur<WIN> s{w, 0u, 2u, lut};  // o = 2: the root's symbol
-  const uint32_t word6 = mkword(rootVal, d.d5);
+// One leaf subtree, in two halves (octets 0-3 = the first height-5 node, octets 4-7 = the second) so that the kernel can do
+// warp-wide work between them (kd_decode.cu stages the next unit there).  The window stands on the root's own symbol
+// (known to be an inner node; its value is rootVal) when the first half starts; `o` = bits consumed since the window's last
+// re-alignment (2 = the root's symbol) is carried from one half to the next.
+template <int ROT, int I0, class WIN>
+VR_HD void parse_leaf_half(WIN& w, uint32_t& o, uint32_t word6, const Dist& d, uint32_t lut, uint32_t strip) {
+  Cur<WIN> s{w, 0u, o, lut};
   uint32_t word5 = 0, word4 = 0;
-  uint32_t i = 0;  // octet index inside the leaf box (path bits 5..3)
+  uint32_t i = (uint32_t)I0;  // octet index inside the leaf box (path bits 5..3)
   for (;;) {
     s.repeek();
     if ((i & 3u) == 0u) {  // a height-5 node starts here
@@ -356,9 +358,7 @@ VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uin
       s.bits >>= 2; s.o += 2u;
       if (c == 3u) {
         fill_octets<ROT>(strip, i, 4u, word6 >> 24);
-        i += 4u;
-        if (i == 8u) break;
-        continue;
+        break;
       }
       word5 = mkword(child(word6, c), d.d4);
     }
@@ -368,7 +368,7 @@ VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uin
       if (c == 3u) {
         fill_octets<ROT>(strip, i, 2u, word5 >> 24);
         i += 2u;
-        if (i == 8u) break;
+        if (i == (uint32_t)I0 + 4u) break;
         continue;
       }
       word4 = mkword(child(word5, c), d.d3);
@@ -387,8 +387,16 @@ VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uin
       }
     }
     i += 1u;
-    if (i == 8u) break;
+    if (i == (uint32_t)I0 + 4u) break;
   }
+  o = s.o;
+}
+template <int ROT, class WIN>
+VR_HD void parse_leaf(WIN& w, uint32_t rootVal, const Dist& d, uint32_t lut, uint32_t strip) {
+  uint32_t o = 2u;  // the root's symbol
+  const uint32_t word6 = mkword(rootVal, d.d5);
+  parse_leaf_half<ROT, 0, WIN>(w, o, word6, d, lut, strip);
+  parse_leaf_half<ROT, 4, WIN>(w, o, word6, d, lut, strip);
 }
 
 // Whole leaf box constant (index entry VR_PRUNED).
