@@ -103,17 +103,20 @@ struct Mem {
 // is the only conditional part (two moves and a load under one predicate, no branch).  Only bits 0..5 of P are ever looked at
 // (the word address is tracked separately), so n may carry garbage above bit 7.
 struct WinShared {  // stream segment staged in shared memory; base = shared address of (virtual) word 0 of the stream
-  uint32_t cur, nxt, P, wi;
+  // nn = the word behind nxt, loaded one boundary ahead: the load of a refill is then not on the parser's dependent chain
+  // (window -> table look-up -> shift -> window ...), where it cost a shared-memory round trip at every boundary
+  uint32_t cur, nxt, nn, P, wi;
   VR_HD void init(uint32_t base, uint32_t sym) {
     P = sym * 2u;
     const uint32_t a = base + ((P >> 5) << 2);
     cur = Mem::lds32(a);
     nxt = Mem::lds32(a + 4u);
-    wi = a + 8u;
+    nn = Mem::lds32(a + 8u);
+    wi = a + 12u;
   }
   VR_HD uint32_t advance_peek(uint32_t n) {
     const uint32_t Pn = P + n;
-    if ((P ^ Pn) & 32u) { cur = nxt; nxt = Mem::lds32(wi); wi += 4u; }
+    if ((P ^ Pn) & 32u) { cur = nxt; nxt = nn; nn = Mem::lds32(wi); wi += 4u; }
     P = Pn;
     return Mem::funnel(cur, nxt, P);
   }
