@@ -41,7 +41,6 @@ namespace vr {
 #define VR6_STAGE_BYTES 4704u
 #define VR6_WARP_STAGE 0u
 #define VR6_BOX_BYTES 2048u                                        // 16 x 16 x 8 voxels of a unit, x fastest
-#define VR6_SMALL_CHUNKS ((VR6_STAGE_BYTES - VR6_BOX_BYTES) / 16u)  // a segment this short is staged behind the box
 #define VR6_WARP_STRIPS VR6_STAGE_BYTES                            // 32 leaf blocks, pitch 68: 2 176 bytes
 #define VR6_WARP_ITEM (VR6_WARP_STRIPS + 32u * VR6_STRIP_PITCH)    // 64 bytes
 #define VR6_WARP_LEAFOFF (VR6_WARP_ITEM + 64u)                     // 128 bytes
@@ -66,7 +65,6 @@ struct Decode6Params {
   vr6::P6Geom pg;
   int32_t tx, ty, tz;
   int32_t only;
-  int32_t fillThrottle;
   int32_t tmaRows;   // rows per tensor-store box (8, 16 or 32)
   int32_t tmaOut;    // 1: the units' voxels leave as one tensor store per unit, 0: as 16-byte stores of the lanes
   uint32_t batch;    // units per parse ticket
@@ -405,9 +403,6 @@ __device__ __forceinline__ void fill_warp(const Decode6Params& p, const uint32_t
                        : "memory");
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      // pacing (A/B knob): while parse units are still queued, leave a gap after every group so that the parse warps' voxel
-      // stores (ordinary stores, which wait behind the tensor stores when HBM is write-saturated) get through
-      if (p.fillThrottle && *reinterpret_cast<volatile uint32_t*>(p.queue) < p.nParse) __nanosleep(100u * (uint32_t)p.fillThrottle << L >> 3);
     }
   }
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the stores must have left before the CTA's shared memory goes away
@@ -522,7 +517,6 @@ cudaError_t kd_decode6_launch(const vr_kd_geom& g, const Decode6Plan& plan, cons
   p.tx = g.tx; p.ty = g.ty; p.tz = g.tz;
   p.only = only;
   p.fillMode = fillMode & 0xFF;
-  p.fillThrottle = fillMode >> 8;
   p.tmaRows = plan.tmaRows;
   p.tmaOut = tmaOut ? 1 : 0;
   memcpy(p.unitMap, plan.unitMap, 128);
