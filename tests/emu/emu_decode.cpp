@@ -148,35 +148,42 @@ int emu_decode(void* p, uint8_t* slab, long long SX, long long SY, long long SZ,
 }
 
 // ---- the persistent kernel's parser (kd_parse6.h), thread by thread -------------------------------------------------------
-// stageChunks: capacity of a warp's staging area in 16-byte chunks (294 on the device; a longer unit is a format error);
+// stageChunks: capacity of a warp's staging area in 16-byte chunks (304 on the device; a longer unit is a format error);
 // needed/culled as in emu_set_lazy.  stats (4 values): parse units, longest staged segment in chunks, constant groups, 0.
 }  // extern "C"
 template <int ROT>
 static void emu6_unit(const vr_kd_job& job, const vr_parse_item& it, const vr6::P6Geom& pg, const vr6::Dist& d, std::vector<uint8_t>& smem,
                       uint32_t lutOff, uint32_t stripOff, uint32_t stageOff, uint8_t* slab, int64_t SX, int64_t SY) {
   vr6::Mem::base() = smem.data();
-  const uint32_t stageBase = stageOff - it.segOff;  // shared address of virtual word 0 (wraps)
-  if (it.segChunks) std::memcpy(smem.data() + stageOff, reinterpret_cast<const uint8_t*>(job.words) + it.segOff, 16ull * it.segChunks);
+  const uint32_t unit = it.tileUnit & 7u;
+  const uint32_t runLen = 1u << pg.runLog, nRuns = 32u >> pg.runLog;
+  // the runs' segments, one behind the other (as stage_unit of kd_decode.cu places them)
+  for (uint32_t r = 0; r < nRuns; ++r) {
+    const uint32_t pk = it.run[r].packed;
+    if (VR_RUN_CHUNKS(pk))
+      std::memcpy(smem.data() + stageOff + 16u * VR_RUN_SMEM(pk), reinterpret_cast<const uint8_t*>(job.words) + it.run[r].segOff, 16ull * VR_RUN_CHUNKS(pk));
+  }
   std::fill(smem.begin() + stripOff, smem.begin() + stripOff + 32 * VR6_STRIP_PITCH, 0xEE);
   for (uint32_t lane = 0; lane < 32; ++lane) {
-    const uint32_t off = job.leafOff[(size_t)it.leaf0 + lane];
-    const uint32_t val = job.leafVal[(size_t)it.leaf0 + lane];
+    const uint32_t r = lane >> pg.runLog, pk = it.run[r].packed;
+    const uint32_t leaf = it.leaf0 + VR_RUN_LEAF(pk) + (lane & (runLen - 1u));
+    if (VR_RUN_LEAF(pk) + (lane & (runLen - 1u)) != vr6::p6_leaf_of(pg, unit, lane)) { std::memset(slab, 0xCC, 64); return; }  // the work list and the geometry must agree
+    const uint32_t off = job.leafOff[(size_t)leaf];
+    const uint32_t val = job.leafVal[(size_t)leaf];
     const uint32_t strip = stripOff + lane * VR6_STRIP_PITCH;
     if (off == VR_PRUNED) { vr6::fill_leaf(strip, val); continue; }
     vr6::WinShared w;
-    w.init(stageBase, off);
+    w.init(stageOff + 16u * VR_RUN_SMEM(pk) - it.run[r].segOff, off);  // shared address of virtual word 0 of the stream (wraps)
     vr6::parse_leaf<ROT>(w, val, d, lutOff, strip);
   }
-  const uint32_t unit = it.tileUnit & 7u;
   for (uint32_t m = 0; m < 128; ++m) {
     uint32_t sOff; int64_t gOff;
     vr6::p6_run_addr(pg, unit, m, SX, SX * SY, &sOff, &gOff);
-    sOff -= unit * 32u * VR6_STRIP_PITCH;  // the warp's strips hold this unit only
     uint8_t* out = slab + it.dst + gOff;
-    // the same run through the tensor-store path: dense box [z][y][16], placed at the unit's voxel coordinates
+    // the same run through the tensor-store path: dense box [z][y][32], placed at the unit's voxel coordinates
     const uint32_t bo = vr6::p6_box_off(pg, m);
-    const int by = (int)((bo >> 4) & ((1u << pg.boxLy) - 1u)), bz = (int)(bo >> (4 + pg.boxLy));
-    uint8_t* out2 = slab + ((int64_t)(it.uz + bz) * SY + (it.uy + by)) * SX + it.ux;
+    const int bx = (int)(bo & 31u), by = (int)((bo >> 5) & ((1u << pg.boxLy) - 1u)), bz = (int)(bo >> (5 + pg.boxLy));
+    uint8_t* out2 = slab + ((int64_t)(it.uz + bz) * SY + (it.uy + by)) * SX + it.ux + bx;
     if (out2 != out) { std::memset(out, 0xDD, 16); continue; }  // the two address computations must agree
     for (uint32_t j = 0; j < 4; ++j) {
       const uint32_t a = stripOff + sOff + ((j & 1u) ? pg.xs[0] : 0u) + ((j & 2u) ? pg.xs[1] : 0u);

@@ -167,7 +167,7 @@ def test_chain_table_of_the_persistent_kernel_for_all_inputs():
                                        ("shell", (128, 128, 64)), ("shell", (256, 128, 128))])
 def test_emulated_persistent_kernel_parser(kind, dims):
     """kd_parse6.h (the leaf parser of the persistent kernel: select words, chain table, static window re-alignment) and its
-    work lists, lane by lane on the CPU, against the levelCut restatement, with the device's staging capacity of 294 chunks per
+    work lists, lane by lane on the CPU, against the levelCut restatement, with the device's staging capacity of 304 chunks per
     unit (every unit must fit; too small a capacity is reported as a format error, never decoded wrongly).  256x128x128 is the
     other leaf-box orientation the kernel is instantiated for (last split along x instead of y)."""
     X, Y, Z = dims
@@ -177,7 +177,7 @@ def test_emulated_persistent_kernel_parser(kind, dims):
     dm, bits = s.distance_map, s.bits
     h = oa.EMU.emu_from_memory(ctypes.byref(hd), dm.ctypes.data, bits.ctypes.data, bits.size)
     slab = np.full((Z + 2, Y + 1, X + 32), 0xAB, np.uint8)
-    assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, 294) == 0
+    assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, 304) == 0
     rc, want = oa.oracle_levelcut(bits, hd.numActiveNodes, dm, hd.origTreeDepth, hd.maxTreeDepth, X, Y, Z)
     assert rc == 0
     assert np.array_equal(slab[1:Z + 1, 1:Y + 1, 16:16 + X], want)
@@ -185,7 +185,7 @@ def test_emulated_persistent_kernel_parser(kind, dims):
     assert (slab == 0xAB).all()
     st = (ctypes.c_longlong * 4)()
     oa.EMU.emu_decode6_stats(st)
-    assert 0 < st[1] <= 294
+    assert 0 < st[1] <= 304
     if kind == "noise":
         assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, int(st[1]) - 1) == _lib.VR_ERR_FORMAT
     oa.EMU.emu_free(h)

@@ -179,7 +179,7 @@ def test_culled_work_list_on_the_cpu_emulation(kernel):
     oa.EMU.emu_set_lazy(needed.ctypes.data, culled.ctypes.data, needed.size)
     try:
         if kernel == "persistent":
-            assert oa.EMU.emu_decode6(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 294) == 0
+            assert oa.EMU.emu_decode6(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 304) == 0
         else:
             assert oa.EMU.emu_decode(h, slab.ctypes.data, X, Y, Z, 0, 0, 0, 1) == 0
         n = oa.EMU.emu_culled_count()

@@ -18,7 +18,6 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
-#include <cstdlib>
 #include <cstring>
 
 #include "kd_decode.h"
@@ -30,28 +29,32 @@ namespace vr {
 // =====================================================================================================================
 // persistent kernel
 // =====================================================================================================================
-// Shared memory of the CTA: [chain table 64 KB | per parse warp (7 168 B): staging area 4 704 B (its first 2 KB double as the
-// unit's dense voxel box for the tensor store), leaf blocks 2 176 B, item 64 B, index entries 160 B | TMA row images].
+// Shared memory of the CTA: [chain table 64 KB | 22 staging areas of 4 864 B (two regions; a unit's dense voxel box for the
+// tensor store is written over its own segment) | 22 x (leaf blocks 2 176 B, item 64 B, index entries 192 B) | 22 mbarriers |
+// TMA row images 6 KB] = 227 KB to the byte.
 #define VR6_OFF_LUT 0u
-// The longest possible unit: 32 leaf subtrees of 63 nodes + 64 voxel items of 8 symbols and the 31 nodes above them = 18 431
-// symbols = 4 608 bytes, + 15 bytes of alignment + two words of look-ahead rounded up to chunks (kd_build_worklist6).  Every
-// unit is staged: a parser that reads its stream from global memory waits for HBM on its dependent chain, and next to the
-// write-saturating constant groups that wait grows several-fold (measured: 15 % of the config-3 units took half of all
-// long-scoreboard stalls).
-#define VR6_STAGE_BYTES 4704u
-#define VR6_WARP_STAGE 0u
-#define VR6_BOX_BYTES 2048u                                        // 16 x 16 x 8 voxels of a unit, x fastest
-#define VR6_WARP_STRIPS VR6_STAGE_BYTES                            // 32 leaf blocks, pitch 68: 2 176 bytes
+// The longest possible unit: 32 leaf subtrees of 63 nodes + 64 voxel items of 8 symbols = 575 symbols each.  A unit is 2 or 4
+// runs of consecutive leaf subtrees; a run of 8 is at most 4 600 symbols = 1 150 bytes, staged as at most 74 16-byte chunks
+// (alignment in front, one word of look-ahead behind: kd_build_worklist6): 296 chunks per unit, and real data gets there (a
+// Richtmyer-Meshkov brick has units of 296).  Every unit is staged: a parser that reads its stream from global memory waits
+// for HBM on its dependent chain, and next to the write-saturating constant groups that wait grows several-fold (measured:
+// 15 % of the config-3 units took half of all long-scoreboard stalls).
+#define VR6_STAGE_BYTES 4864u                                      // 304 chunks; a multiple of 128 (tensor stores read aligned boxes)
+#define VR6_BOX_BYTES 2048u                                        // 32 x 8 x 8 voxels of a unit, x fastest
+#define VR6_OFF_STAGE VR6_LUT_BYTES
+#define VR6_OFF_MISC (VR6_OFF_STAGE + VR6_PARSE_WARPS * VR6_STAGE_BYTES)
+#define VR6_WARP_STRIPS 0u                                         // 32 leaf blocks, pitch 68: 2 176 bytes
 #define VR6_WARP_ITEM (VR6_WARP_STRIPS + 32u * VR6_STRIP_PITCH)    // 64 bytes
 #define VR6_WARP_LEAFOFF (VR6_WARP_ITEM + 64u)                     // 128 bytes
-#define VR6_WARP_LEAFVAL (VR6_WARP_LEAFOFF + 128u)                 // 32 bytes
-#define VR6_WARP_MBAR (VR6_WARP_LEAFVAL + 32u)                     // 8 bytes: completion of the staging copies
-#define VR6_WARP_BYTES 7168u                                       // 7 112 used; a multiple of 128 (tensor stores read aligned boxes)
+#define VR6_WARP_LEAFVAL (VR6_WARP_LEAFOFF + 128u)                 // 64 bytes: one 16-byte chunk per run
+#define VR6_MISC_BYTES (VR6_WARP_LEAFVAL + 64u)                    // 2 432, a multiple of 16
+#define VR6_OFF_MBAR (VR6_OFF_MISC + VR6_PARSE_WARPS * VR6_MISC_BYTES)  // 8 bytes per warp: completion of the staging copies
 #define VR6_QUEUE_FILL 32u  // the constant groups' counter lives on its own 128-byte line
 #define VR6_BATCH_MAX 4u    // units per queue ticket: one atomic per unit on one address serialises in L2 (38 % of the stalls on
                             // 262 144 units); short queues take single units, whose costs differ by 10x, for balance
-#define VR6_IMG_TOTAL 8192u  // row images of the constant groups: 8192 / (256 * rows) slots of (32 << 3) x rows bytes
-#define VR6_OFF_IMG ((VR6_LUT_BYTES + VR6_PARSE_WARPS * VR6_WARP_BYTES + 127u) & ~127u)  // tensor stores read 128-byte aligned images
+#define VR6_IMG_TOTAL 6144u  // row images of the constant groups: 6144 / (256 * rows) slots of (32 << 3) x rows bytes
+#define VR6_OFF_IMG ((VR6_OFF_MBAR + VR6_PARSE_WARPS * 8u + 127u) & ~127u)  // tensor stores read 128-byte aligned images
+static_assert(VR6_OFF_IMG + VR6_IMG_TOTAL <= 232448u, "shared memory of one CTA");
 
 struct Decode6Params {
   const vr_parse_item* parse;
@@ -107,17 +110,36 @@ __device__ __forceinline__ void cp16(uint32_t dstS, const void* src) {
 // landed), not by cp.async groups: groups of asynchronous copies and bulk (TMA) groups count on ONE scoreboard in this part
 // (cp.async.wait_group N and cp.async.bulk.wait_group[.read] N assemble to the same DEPBAR.LE SB0, N), so a wait for the
 // staging would also wait for the previous unit's tensor store and the other way round.
-__device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t wbase, uint32_t segS,
-                                           uint32_t barS, uint32_t lane) {
+// ia / ib = the first two 16-byte quarters of the unit's item (valid in lane 0), ir = its run descriptors (lane r holds run r).
+__device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, const uint2& ir, uint32_t wbase,
+                                           uint32_t segS, uint32_t barS, uint32_t lane) {
   const uint64_t ar = (uint64_t)__shfl_sync(0xFFFFFFFFu, ia.x, 0) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, ia.y, 0) << 32);
   const uint8_t* arena = reinterpret_cast<const uint8_t*>(ar);
-  const uint32_t segOff = __shfl_sync(0xFFFFFFFFu, ia.z, 0), segChunks = __shfl_sync(0xFFFFFFFFu, ia.w, 0);
   const uint32_t leafOffOff = __shfl_sync(0xFFFFFFFFu, ib.x, 0), leafValOff = __shfl_sync(0xFFFFFFFFu, ib.y, 0);
+  const uint32_t runLog = p.pg.runLog, nRuns = 32u >> runLog, cprLog = runLog - 2u;  // (1 << cprLog) 16-byte chunks of leafOff entries per run
+  // lanes 0-3: the item's first 64 bytes; 4-11: the 32 leafOff entries (lane order = run after run); 12..: one 16-byte chunk
+  // of leafVal entries per run
+  const uint32_t myRun = lane < 12u ? ((lane - 4u) & 7u) >> cprLog : (lane - 12u) & 3u;
+  const uint32_t leafRel = VR_RUN_LEAF(__shfl_sync(0xFFFFFFFFu, ir.y, myRun));
   // (timing probe only == 4: the stream-side half of the item comes from the same few units over and over, see src_of)
   if (lane < 4u) cp16(wbase + VR6_WARP_ITEM + 16u * lane, reinterpret_cast<const uint8_t*>(p.parse + (lane == 0u ? src_of(p, idx) : idx)) + 16u * lane);
-  else if (lane < 12u) cp16(wbase + VR6_WARP_LEAFOFF + 16u * (lane - 4u), arena + leafOffOff + 16u * (lane - 4u));
-  else if (lane < 14u) cp16(wbase + VR6_WARP_LEAFVAL + 16u * (lane - 12u), arena + leafValOff + 16u * (lane - 12u));
-  for (uint32_t c = lane; c < segChunks; c += 32u) cp16(segS + 16u * c, arena + segOff + 16u * c);
+  else if (lane < 12u) cp16(wbase + VR6_WARP_LEAFOFF + 16u * (lane - 4u), arena + leafOffOff + 4u * leafRel + 16u * ((lane - 4u) & ((1u << cprLog) - 1u)));
+  else if (lane < 12u + nRuns) cp16(wbase + VR6_WARP_LEAFVAL + 16u * (lane - 12u), arena + ((leafValOff + leafRel) & ~15u));
+  // The runs' chunks sit one behind the other in the staging region (run r from chunk s_r on: the work list stores the
+  // running total in every slot, unused ones included), so ONE loop over the unit's chunks copies them all: chunk c of the
+  // region comes from arena offset 16 c + D_r, r = the last run that starts at or before c.
+  const uint32_t total = __shfl_sync(0xFFFFFFFFu, ia.z, 0);
+  const uint32_t k1 = __shfl_sync(0xFFFFFFFFu, ir.y, 1), k2 = __shfl_sync(0xFFFFFFFFu, ir.y, 2), k3 = __shfl_sync(0xFFFFFFFFu, ir.y, 3);
+  const uint32_t s1 = VR_RUN_SMEM(k1), s2 = VR_RUN_SMEM(k2), s3 = VR_RUN_SMEM(k3);
+  const uint32_t D0 = __shfl_sync(0xFFFFFFFFu, ir.x, 0), D1 = __shfl_sync(0xFFFFFFFFu, ir.x, 1) - 16u * s1,
+                 D2 = __shfl_sync(0xFFFFFFFFu, ir.x, 2) - 16u * s2, D3 = __shfl_sync(0xFFFFFFFFu, ir.x, 3) - 16u * s3;
+#pragma unroll 1
+  for (uint32_t c = lane; c < total; c += 32u) {
+    uint32_t D = c >= s1 ? D1 : D0;
+    D = c >= s2 ? D2 : D;
+    D = c >= s3 ? D3 : D;
+    cp16(segS + 16u * c, arena + (uint32_t)(16u * c + D));
+  }
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(barS) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t barS, uint32_t parity) {
@@ -134,14 +156,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t barS, uint32_t parity) {
 // Pulls everything unit `idx` will stage into L2 -- its stream segment (one 128-byte line per lane), its index entries and its
 // item -- two units ahead of the staging copies: next to the constant groups HBM is write-saturated and a read that misses L2
 // takes several microseconds, longer than a unit takes to parse.  ia / ib valid in lane 0.
-__device__ __forceinline__ void prefetch_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, uint32_t lane) {
+__device__ __forceinline__ void prefetch_unit(const Decode6Params& p, uint32_t idx, const uint4& ia, const uint4& ib, const uint2& ir, uint32_t lane) {
   const uint64_t ar = (uint64_t)__shfl_sync(0xFFFFFFFFu, ia.x, 0) | ((uint64_t)__shfl_sync(0xFFFFFFFFu, ia.y, 0) << 32);
-  const uint32_t segOff = __shfl_sync(0xFFFFFFFFu, ia.z, 0), segChunks = __shfl_sync(0xFFFFFFFFu, ia.w, 0);
   const uint32_t leafOffOff = __shfl_sync(0xFFFFFFFFu, ib.x, 0), leafValOff = __shfl_sync(0xFFFFFFFFu, ib.y, 0);
-  for (uint32_t l = lane; l * 8u < segChunks + 7u; l += 32u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + segOff + 128ull * l));
-  if (lane == 29u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafOffOff));
-  if (lane == 30u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafValOff));
+  // eight lanes per run: one 128-byte line of its segment each, and the lines of its index entries
+  const uint32_t r = lane >> 3, j = lane & 7u;
+  const uint32_t so = __shfl_sync(0xFFFFFFFFu, ir.x, r), pk = __shfl_sync(0xFFFFFFFFu, ir.y, r);
+  if (r < (32u >> p.pg.runLog)) {
+    const uint32_t sc = VR_RUN_CHUNKS(pk);
+#pragma unroll 1
+    for (uint32_t l = j; l * 8u < sc + 7u && sc; l += 8u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + so + 128ull * l));
+    if (j == 6u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafOffOff + 4u * VR_RUN_LEAF(pk)));
+    if (j == 7u) asm volatile("prefetch.global.L2 [%0];" ::"l"(ar + leafValOff + VR_RUN_LEAF(pk)));
+  }
   if (lane == 31u) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint8_t*>(p.parse + idx)));
+  if (lane == 30u) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const uint8_t*>(p.parse + idx) + 95));
 }
 
 // One parse warp: its own queue tickets, staging area and leaf blocks -- no barrier with any other warp, so a warp whose unit
@@ -151,8 +180,8 @@ __device__ __forceinline__ void prefetch_unit(const Decode6Params& p, uint32_t i
 // n+1's segment is pulled into L2 while unit n is parsed; unit n+1 is staged while unit n's voxels are stored.
 template <int ROT>
 __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_t sb, const uint32_t warp, const uint32_t lane) {
-  const uint32_t wbase = sb + VR6_LUT_BYTES + warp * VR6_WARP_BYTES;
-  const uint32_t strips = wbase + VR6_WARP_STRIPS, stageS = wbase + VR6_WARP_STAGE, barS = wbase + VR6_WARP_MBAR;
+  const uint32_t wbase = sb + VR6_OFF_MISC + warp * VR6_MISC_BYTES;
+  const uint32_t strips = wbase + VR6_WARP_STRIPS, stageS = sb + VR6_OFF_STAGE + warp * VR6_STAGE_BYTES, barS = sb + VR6_OFF_MBAR + 8u * warp;
   const uint32_t lutS = sb + VR6_OFF_LUT;
   const uint32_t xs0 = p.pg.xs[0], xs1 = p.pg.xs[1];
   const uint32_t myStrip = strips + lane * VR6_STRIP_PITCH;
@@ -202,6 +231,13 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
   idxA = __shfl_sync(0xFFFFFFFFu, idxA, 0);
   idxB = __shfl_sync(0xFFFFFFFFu, idxB, 0);
   idxC = __shfl_sync(0xFFFFFFFFu, idxC, 0);
+  // run descriptors of the units (lane r: run r), loaded with the item halves: curR = the unit being parsed, bR / cR = the next two
+  const uint2 z2 = make_uint2(0, 0);
+  uint2 curR = z2, bR = z2;
+  if (lane < 4u) {
+    if (idxA < p.nParse) curR = __ldg(reinterpret_cast<const uint2*>(&p.parse[src_of(p, idxA)].run[lane]));
+    if (idxB < p.nParse) bR = __ldg(reinterpret_cast<const uint2*>(&p.parse[src_of(p, idxB)].run[lane]));
+  }
   // The staging area is two regions, R0 = [0, 2 048) and R1 = [2 048, 4 704).  A unit's segment sits in one of them and its
   // voxel box (2 048 B) is later written over it, so the OTHER region is free while the unit is parsed: the next unit is
   // staged there half-way through the parsing (its copies then have the rest of the unit to land), not after it.  A
@@ -210,16 +246,18 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
   uint32_t curOff = 0, parity = 0;
   bool curBig = false;
   if (idxA < p.nParse) {
-    const uint32_t bytesA = 16u * __shfl_sync(0xFFFFFFFFu, a0.w, 0);
+    const uint32_t bytesA = 16u * __shfl_sync(0xFFFFFFFFu, a0.z, 0);
     curOff = bytesA <= VR6_STAGE_BYTES - VR6_BOX_BYTES ? VR6_BOX_BYTES : 0u;
     curBig = bytesA > VR6_STAGE_BYTES - VR6_BOX_BYTES;
-    stage_unit(p, idxA, a0, a1, wbase, stageS + curOff, barS, lane);
+    stage_unit(p, idxA, a0, a1, curR, wbase, stageS + curOff, barS, lane);
   }
-  if (idxB < p.nParse) prefetch_unit(p, idxB, b0, b1, lane);
+  if (idxB < p.nParse) prefetch_unit(p, idxB, b0, b1, bR, lane);
   while (idxA < p.nParse) {
     // requests for later units first, so that they are in flight while this one is parsed
     uint4 c0 = z4, c1 = z4;
+    uint2 cR = z2;
     uint32_t idxD = 0;
+    if (lane < 4u && idxC < p.nParse) cR = __ldg(reinterpret_cast<const uint2*>(&p.parse[src_of(p, idxC)].run[lane]));
     if (lane == 0) {
       if (idxC < p.nParse) { c0 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC))); c1 = __ldg(reinterpret_cast<const uint4*>(p.parse + src_of(p, idxC)) + 1); }
       if (curPos + 1u < p.batch) { ++curPos; idxD = curBase + curPos; }
@@ -227,16 +265,19 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     }
     mbar_wait(barS, parity);  // this unit's segment, index entries and item are in shared memory
     parity ^= 1u;
-    const uint4 i0 = lds128(wbase + VR6_WARP_ITEM), i2 = lds128(wbase + VR6_WARP_ITEM + 32u), i3 = lds128(wbase + VR6_WARP_ITEM + 48u);
-    const uint32_t segOff = i0.z;
+    const uint4 i2 = lds128(wbase + VR6_WARP_ITEM + 32u), i3 = lds128(wbase + VR6_WARP_ITEM + 48u);
     const uint64_t treeDist = (uint64_t)i2.x | ((uint64_t)i2.y << 32);
     const int64_t dstOff = (int64_t)((uint64_t)i2.z | ((uint64_t)i2.w << 32));
     const int32_t occCell = (int32_t)i3.w;
     const uint32_t unit = lds32(wbase + VR6_WARP_ITEM + 28u) & 7u;  // tileUnit
-    const uint32_t off = lds32(wbase + VR6_WARP_LEAFOFF + 4u * lane), val = lds8(wbase + VR6_WARP_LEAFVAL + lane);
+    // this lane's leaf box: run lane >> runLog of the unit, entry lane of the staged index entries (lane order = run after run)
+    const uint32_t myRun = lane >> p.pg.runLog;
+    const uint32_t runSeg = __shfl_sync(0xFFFFFFFFu, curR.x, myRun), runPk = __shfl_sync(0xFFFFFFFFu, curR.y, myRun);
+    const uint32_t off = lds32(wbase + VR6_WARP_LEAFOFF + 4u * lane);
+    const uint32_t val = lds8(wbase + VR6_WARP_LEAFVAL + 16u * myRun + (VR_RUN_LEAF(runPk) & 15u) + (lane & ((1u << p.pg.runLog) - 1u)));
     // where the next unit's segment can go
     const bool haveB = idxB < p.nParse;
-    const uint32_t bytesB = 16u * __shfl_sync(0xFFFFFFFFu, b0.w, 0);
+    const uint32_t bytesB = 16u * __shfl_sync(0xFFFFFFFFu, b0.z, 0);
     const uint32_t otherOff = curOff ? 0u : VR6_BOX_BYTES, otherCap = curOff ? VR6_BOX_BYTES : VR6_STAGE_BYTES - VR6_BOX_BYTES;
     const bool fitsOther = haveB && bytesB <= otherCap;
     const bool early = fitsOther && !curBig;
@@ -250,7 +291,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     if (off == VR_PRUNED) {
       vr6::fill_leaf(myStrip, val);
     } else {
-      w.init(stageS + curOff - segOff, off);
+      w.init(stageS + curOff + 16u * VR_RUN_SMEM(runPk) - runSeg, off);
       vr6::parse_leaf_half<ROT, 0>(w, wo, word6, d, lutS, myStrip);
     }
     __syncwarp();  // every lane has read its index entry and the item
@@ -259,7 +300,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
       }
-      stage_unit(p, idxB, b0, b1, wbase, stageS + otherOff, barS, lane);
+      stage_unit(p, idxB, b0, b1, bR, wbase, stageS + otherOff, barS, lane);
     }
     // ---- second half ----
     if (off != VR_PRUNED) vr6::parse_leaf_half<ROT, 4>(w, wo, word6, d, lutS, myStrip);
@@ -270,7 +311,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
       }
-      stage_unit(p, idxB, b0, b1, wbase, stageS + otherOff, barS, lane);
+      stage_unit(p, idxB, b0, b1, bR, wbase, stageS + otherOff, barS, lane);
       staged = true;
     }
     // ---- phase 2: the warp's 32 leaf blocks -> 128 runs of 16 voxels along x, four per lane ----
@@ -291,7 +332,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
       m02 = __vmaxu2(__vmaxu2(m02, w0 * 256u), __vmaxu2(w1 * 256u, __vmaxu2(w2 * 256u, w3 * 256u)));
     }
     if (p.tmaOut) {
-      // The unit leaves as ONE tensor store (16 x 16 x 8 box).  Ordinary stores of the lanes wait behind the constant groups'
+      // The unit leaves as ONE tensor store (32 x 8 x 8 box: 64 rows of whole sectors).  Ordinary stores of the lanes wait behind the constant groups'
       // tensor stores whenever HBM is write-saturated, and since the load/store unit works in order, every shared-memory
       // access of the SM then waits with them: the launch took fill + parse (profiles/r2_decode.md).  In the TMA queue the
       // units simply take their turn.
@@ -309,7 +350,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
       }
-      stage_unit(p, idxB, b0, b1, wbase, stageS, barS, lane);
+      stage_unit(p, idxB, b0, b1, bR, wbase, stageS, barS, lane);
     }
     curOff = staged ? otherOff : 0u;
     curBig = !staged && bytesB > VR6_BOX_BYTES;
@@ -319,9 +360,10 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
       if (lane == 0) p.occ[(int64_t)occCell * 8 + unit] = (uint8_t)m;
     }
     __syncwarp();  // the leaf blocks are free for the next unit
-    if (idxC < p.nParse) prefetch_unit(p, idxC, c0, c1, lane);  // its item half was requested at the top of this iteration
+    if (idxC < p.nParse) prefetch_unit(p, idxC, c0, c1, cR, lane);  // its item half was requested at the top of this iteration
     idxA = idxB; idxB = idxC; idxC = __shfl_sync(0xFFFFFFFFu, idxD, 0);
     b0 = c0; b1 = c1;
+    curR = bR; bR = cR;
   }
   if (p.tmaOut && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // before the CTA's shared memory goes away
 }
@@ -480,14 +522,14 @@ bool kd_fill_maps_create(uint8_t* vol, int64_t SX, int64_t SY, int64_t SZ, int t
 }
 
 bool kd_decode6_plan(const vr_kd_geom& g, uint8_t* dst, int64_t SX, int64_t SY, int64_t SZ, Decode6Plan* out, int tmaRows) {
-  if (tmaRows != 8 && tmaRows != 16 && tmaRows != 32) return false;
+  if (tmaRows != 8 && tmaRows != 16) return false;  // (32 rows = 8 KB per image: no slot)
   out->tmaRows = tmaRows;
   if (!vr6::p6_make_geom(g, &out->pg)) return false;
   if (g.tx != 32 || g.ty % tmaRows) return false;                    // image slots are sized for 32-wide tiles
   if ((int64_t)g.tz * SX * SY + (int64_t)g.ty * SX >= (int64_t(1) << 31)) return false;  // 32-bit run offsets inside a tile
   if (!kd_fill_maps_create(dst, SX, SY, SZ, g.tx, g.ty, tmaRows, &out->maps)) return false;
-  if ((16u << out->pg.boxLy << out->pg.boxLz) != VR6_BOX_BYTES) return false;
-  if (!box_map_create(dst, SX, SY, SZ, 16, 1 << out->pg.boxLy, 1 << out->pg.boxLz, out->unitMap)) return false;
+  if (((uint32_t)VR6_UNIT_X << out->pg.boxLy << out->pg.boxLz) != VR6_BOX_BYTES) return false;
+  if (!box_map_create(dst, SX, SY, SZ, VR6_UNIT_X, 1 << out->pg.boxLy, 1 << out->pg.boxLz, out->unitMap)) return false;
   out->smemBytes = (size_t)VR6_OFF_IMG + (size_t)VR6_IMG_TOTAL;
   return true;
 }

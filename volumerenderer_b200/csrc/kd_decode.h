@@ -22,11 +22,11 @@ size_t kd_decode_smem_bytes(const vr_kd_geom& g);
 #define VR6_PARSE_WARPS 22
 #define VR6_QUEUE_WORDS 64  // the two queue counters, 128 bytes apart
 #define VR6_THREADS (VR6_PARSE_WARPS * 32 + 32)
-#define VR6_IMG_SLOTS 4  // at most (rows = 8)
+#define VR6_IMG_SLOTS 3  // at most (rows = 8)
 struct Decode6Plan {
   vr6::P6Geom pg;
   VrFillMaps maps;
-  alignas(64) unsigned char unitMap[128];  // tensor map with a unit's box (16 x 16 x 8 for 256x256x128 bricks)
+  alignas(64) unsigned char unitMap[128];  // tensor map with a unit's box (32 x 8 x 8 for 256x256x128 bricks)
   int tmaRows;
   size_t smemBytes;
 };

@@ -61,22 +61,37 @@ typedef struct vr_fill_job {
 } vr_fill_job;
 
 // One unit of the persistent kernel's parse queue (kd_decode.cu: kd_decode6_kernel; host: kd_build_worklist6 fills the
-// bookkeeping fields, the C ABI layer the device addresses).  A unit = 32 consecutive leaf boxes of a tile (2 048 voxels): the
-// work of one warp.  64 bytes, self-contained: the warp needs nothing else to decode the unit.
+// bookkeeping fields, the C ABI layer the device addresses).  A unit = 32 leaf boxes of a tile that together span the tile's
+// whole x extent (32 x 8 x 8 voxels = 2 048, the work of one warp): its voxel box then leaves as 64 rows of 32 bytes --
+// whole sectors.  (Units of 32 CONSECUTIVE leaf boxes are 16 voxels wide: 128 half-sector rows per box, which cost the
+// TMA unit twice the time and wrote every sector in two halves: profiles/r2_step_final.md.)  In stream order the 32 leaf
+// boxes are 2 or 4 runs of consecutive ones (vr6::P6Geom), each with its own staged stream segment.  96 bytes,
+// self-contained: the warp needs nothing else to decode the unit.
+typedef struct vr_parse_run {
+  uint32_t segOff;  // byte offset inside the arena of the first 16-byte chunk of the run's stream segment
+  uint32_t packed;  // bits 0-8 chunks to stage (0: no live leaf in the run), 9-16 first leaf of the run relative to the tile's
+                    // first, 17-25 where the run's chunks go in the staging region (in chunks)
+} vr_parse_run;
+#define VR_RUN_PACK(chunks, leafRel, smemChunk) ((uint32_t)(chunks) | ((uint32_t)(leafRel) << 9) | ((uint32_t)(smemChunk) << 17))
+#define VR_RUN_CHUNKS(p) ((p) & 0x1FFu)
+#define VR_RUN_LEAF(p) (((p) >> 9) & 0xFFu)
+#define VR_RUN_SMEM(p) (((p) >> 17) & 0x1FFu)
 typedef struct vr_parse_item {
   // --- what the lane that requests the staging copies reads (32 bytes) ---
   const uint8_t* arena;  // device image of the prepared stream (the packed stream sits at offset 0)
-  uint32_t segOff;       // byte offset of the first 16-byte chunk of the unit's stream segment ...
-  uint32_t segChunks;    // ... and how many chunks to stage in shared memory (0: no live leaf, nothing to parse)
-  uint32_t leafOffOff;   // byte offset inside the arena of the unit's 32 leafOff entries ...
-  uint32_t leafValOff;   // ... and of its 32 leafVal entries
-  uint32_t leaf0;        // index of the unit's first leaf entry = tileLeafBlock[tile] * 256 + 32 * unit
+  uint32_t segChunks;    // chunks to stage in shared memory, all runs together (0: no live leaf, nothing to parse)
+  uint32_t pad0;
+  uint32_t leafOffOff;   // byte offset inside the arena of the TILE's 256 leafOff entries ...
+  uint32_t leafValOff;   // ... and of its 256 leafVal entries
+  uint32_t leaf0;        // index of the tile's first leaf entry = tileLeafBlock[tile] * 256
   uint32_t tileUnit;     // tile << 3 | unit (unit = which eighth of the tile; also the warp slot of the occupancy cell)
   // --- what every lane reads ---
   uint64_t treeDist;     // byte h = distanceMap[D0 - h], h = 0..6
   int64_t dst;           // voxel offset of the TILE origin inside the destination slab
   int32_t ux, uy, uz;    // voxel coordinates of the UNIT's box in the destination (tensor-store coordinates)
   int32_t occCell;       // occupancy cell of the tile, < 0 = none
+  // --- the runs (lanes 0..3 read one each) ---
+  vr_parse_run run[4];
 } vr_parse_item;
 
 // A tile the lazy decode leaves out (kd_cull.h): its occupancy cell and the exact maximum of its voxels.

@@ -412,63 +412,102 @@ VR_HD void fill_leaf(uint32_t strip, uint32_t val) {
 #define VR6_STRIP_PITCH 68u  // 64-byte leaf block + 4: the blocks of a warp's 32 lanes start in 32 different banks
 #define VR6_STRIPS_BYTES (256u * VR6_STRIP_PITCH)
 
-// ---- phase 2: leaf blocks -> 16-byte x-runs of the destination --------------------------------------------------------
-// A warp owns 32 consecutive leaf boxes of the tile (its "unit": 2 048 voxels = 128 runs of 16 voxels along x).  Run m
-// (7 bits) = one value of the unit's free coordinate bits: the 3 leaf-index bits that are not tile x bits 2 / 3, and the
-// 4 row bits inside a leaf box (y0, y1, z0, z1).  A run is four 4-byte rows of four x-neighbouring leaf blocks.
+// ---- units and phase 2: leaf blocks -> 16-byte x-runs of the destination -------------------------------------------------
+// A tile (14 path bits) has 256 leaf boxes, leaf-index bit k = path bit 6 + k.  A warp's unit = the 32 leaf boxes that share
+// the three "unit" bits; the five "lane" bits are the three leaf-index bits that carry tile x bits 2, 3, 4 plus the two lowest
+// other ones, so that the unit's box is 32 (all of x) x 8 x 8 voxels.  Lane l <-> the leaf box whose lane bits spell l.  The
+// lane bits that form a block from path bit 6 upwards enumerate consecutive leaf boxes of the stream: a unit is 32 >> runLog
+// runs of (1 << runLog) consecutive leaf boxes.
+// The unit's 2 048 voxels = 128 runs of 16 voxels along x.  Run m (7 bits) = one value of the unit's free coordinate bits:
+// the 4 row bits inside a leaf box (y0, y1, z0, z1) and the 3 lane bits that are not tile x bits 2 / 3 (one of them is x
+// bit 4).  A run is four 4-byte rows of four x-neighbouring leaf blocks.
 struct P6Geom {
   int32_t rot;           // (D0 - 1) mod 3
-  uint16_t xs[2];        // strip offset of tile x bits 2, 3 (a leaf-index bit each)
+  uint16_t xs[2];        // strip offset of tile x bits 2, 3 (a lane bit each)
   uint16_t fs[7];        // strip offset of free bit k
-  uint8_t fAxis[7];      // its axis (1 = y, 2 = z; 0 only for x bit 4 of a 32-wide tile) ...
+  uint8_t fAxis[7];      // its axis (0 = x: tile x bit 4, 1 = y, 2 = z) ...
   uint8_t fCb[7];        // ... and tile-local coordinate bit
-  uint8_t wAxis[3], wCb[3];  // the warp index (top 3 leaf-index bits) likewise
-  uint8_t boxLy, boxLz;      // a unit's box is 16 x 2^boxLy x 2^boxLz voxels (16 x 16 x 8 for 256x256x128 bricks)
+  uint8_t wAxis[3], wCb[3];  // the unit bits likewise
+  uint8_t boxLy, boxLz;      // a unit's box is 32 x 2^boxLy x 2^boxLz voxels (32 x 8 x 8 for 256x256x128 bricks)
+  uint8_t laneBit[5];        // leaf-index bit of lane bit k (ascending)
+  uint8_t unitBit[3];        // leaf-index bit of unit bit j (ascending)
+  uint8_t runLog;            // log2 of the run length: 3 (4 runs of 8) or 4 (2 runs of 16)
 };
+#define VR6_UNIT_X 32
+// leaf index (0..255, relative to the tile's first) of lane l of unit u
+VR_HD uint32_t p6_leaf_of(const P6Geom& p, uint32_t u, uint32_t l) {
+  uint32_t r = 0;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) r |= ((l >> k) & 1u) << p.laneBit[k];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) r |= ((u >> j) & 1u) << p.unitBit[j];
+  return r;
+}
 // false when the brick's tree does not have the shape this path is written for (kd_decode.cu then takes the generic kernel)
 static inline bool p6_make_geom(const vr_kd_geom& g, P6Geom* out) {
-  if (g.tileBits != 14 || g.leafBits != 6 || g.tx < 16) return false;
+  if (g.tileBits != 14 || g.leafBits != 6 || g.tx != VR6_UNIT_X) return false;
   const int rot = (g.D0 - 1) % 3;
-  if (rot == 2) return false;  // tile x bit 3 would be path bit 11: not inside a warp's unit
   for (int b = 0; b < 6; ++b) {
     const int ax = ((rot - b) % 3 + 3) % 3;
     if (g.pbAxis[b] != ax || g.pbCoordBit[b] != b / 3) return false;
   }
-  const int x2 = g.pathBit[0][2], x3 = g.pathBit[0][3];
-  if (x2 < 6 || x2 > 10 || x3 < 6 || x3 > 10) return false;
   P6Geom p{};
   p.rot = rot;
-  p.xs[0] = (uint16_t)(VR6_STRIP_PITCH << (x2 - 6));
-  p.xs[1] = (uint16_t)(VR6_STRIP_PITCH << (x3 - 6));
+  // lane bits: the x bits of the tile's leaf index and the two lowest others
+  bool isLane[8] = {false, false, false, false, false, false, false, false};
+  int nx = 0, nother = 0;
+  for (int k = 0; k < 8; ++k)
+    if (g.pbAxis[6 + k] == 0) { isLane[k] = true; ++nx; }
+  if (nx != 3) return false;
+  for (int k = 0; k < 8 && nother < 2; ++k)
+    if (!isLane[k]) { isLane[k] = true; ++nother; }
+  int nl = 0, nu = 0;
+  for (int k = 0; k < 8; ++k) {
+    if (isLane[k]) p.laneBit[nl++] = (uint8_t)k;
+    else p.unitBit[nu++] = (uint8_t)k;
+  }
+  if (nl != 5 || nu != 3) return false;
+  int run = 0;
+  while (run < 5 && p.laneBit[run] == run) ++run;
+  if (run < 3) return false;  // more than 4 runs per unit: not worth staging
+  p.runLog = (uint8_t)(run > 4 ? 4 : run);  // (5 = one run of 32; handled as two of 16)
+  auto lanePos = [&](int leafBit) { for (int k = 0; k < 5; ++k) if (p.laneBit[k] == leafBit) return k; return -1; };
+  const int x2 = g.pathBit[0][2] - 6, x3 = g.pathBit[0][3] - 6, x4 = g.pathBit[0][4] - 6;
+  if (lanePos(x2) < 0 || lanePos(x3) < 0 || lanePos(x4) < 0) return false;
+  p.xs[0] = (uint16_t)(VR6_STRIP_PITCH << lanePos(x2));
+  p.xs[1] = (uint16_t)(VR6_STRIP_PITCH << lanePos(x3));
   int n = 0;
-  for (int b = 0; b < 11; ++b) {  // in-leaf row bits first (lowest), then the leaf-index bits of the unit
-    if (b < 6) {
-      if (g.pbAxis[b] == 0) continue;  // x0, x1: inside a 4-byte row
-      p.fs[n] = (uint16_t)((g.pbAxis[b] == 1 ? 4 : 16) << (b / 3));
-    } else {
-      if (b == x2 || b == x3) continue;
-      p.fs[n] = (uint16_t)(VR6_STRIP_PITCH << (b - 6));
-    }
+  for (int b = 0; b < 6; ++b) {  // in-leaf row bits first (lowest) ...
+    if (g.pbAxis[b] == 0) continue;  // x0, x1: inside a 4-byte row
+    p.fs[n] = (uint16_t)((g.pbAxis[b] == 1 ? 4 : 16) << (b / 3));
     p.fAxis[n] = g.pbAxis[b];
     p.fCb[n] = g.pbCoordBit[b];
     ++n;
   }
+  for (int k = 0; k < 5; ++k) {  // ... then the lane bits that are not x bits 2 / 3
+    const int lb = p.laneBit[k];
+    if (lb == x2 || lb == x3) continue;
+    p.fs[n] = (uint16_t)(VR6_STRIP_PITCH << k);
+    p.fAxis[n] = g.pbAxis[6 + lb];
+    p.fCb[n] = g.pbCoordBit[6 + lb];
+    ++n;
+  }
   if (n != 7) return false;
-  for (int k = 0; k < 7; ++k) {  // the free bits are the low y and z bits of the unit's box, each axis without gaps
+  for (int k = 0; k < 7; ++k) {  // the free bits are x bit 4 and the low y and z bits of the unit's box, each axis without gaps
     if (p.fAxis[k] == 1) { if (p.fCb[k] != p.boxLy) return false; ++p.boxLy; }
     else if (p.fAxis[k] == 2) { if (p.fCb[k] != p.boxLz) return false; ++p.boxLz; }
-    else return false;
+    else if (p.fCb[k] != 4) return false;
   }
-  for (int j = 0; j < 3; ++j) { p.wAxis[j] = g.pbAxis[11 + j]; p.wCb[j] = g.pbCoordBit[11 + j]; }
+  for (int j = 0; j < 3; ++j) { p.wAxis[j] = g.pbAxis[6 + p.unitBit[j]]; p.wCb[j] = g.pbCoordBit[6 + p.unitBit[j]]; }
   *out = p;
   return true;
 }
-// offset of run m inside the unit's dense box [z][y][16 x] (what the tensor store of a unit reads)
+// offset of run m inside the unit's dense box [z][y][32 x] (what the tensor store of a unit reads)
 VR_HD uint32_t p6_box_off(const P6Geom& p, uint32_t m) {
   uint32_t o = 0;
 #pragma unroll
   for (int k = 0; k < 7; ++k)
-    if ((m >> k) & 1u) o += (p.fAxis[k] == 1 ? 16u : (16u << p.boxLy)) << p.fCb[k];
+    if ((m >> k) & 1u) o += p.fAxis[k] == 0 ? 16u : ((p.fAxis[k] == 1 ? (uint32_t)VR6_UNIT_X : ((uint32_t)VR6_UNIT_X << p.boxLy)) << p.fCb[k]);
   return o;
 }
 // voxel coordinates of unit u's box relative to the tile origin
@@ -477,9 +516,9 @@ VR_HD void p6_unit_origin(const P6Geom& p, uint32_t u, int32_t o[3]) {
   for (int j = 0; j < 3; ++j)
     if ((u >> j) & 1u) o[p.wAxis[j]] += 1 << p.wCb[j];
 }
-// strip offset (relative to the tile's strips) and destination offset (relative to the tile origin) of run m of warp w
+// strip offset (relative to the unit's 32 strips, lane order) and destination offset (relative to the tile origin) of run m of unit w
 VR_HD void p6_run_addr(const P6Geom& p, uint32_t w, uint32_t m, int64_t rowPitch, int64_t slicePitch, uint32_t* sOff, int64_t* gOff) {
-  uint32_t s = w * 32u * VR6_STRIP_PITCH;
+  uint32_t s = 0;
   int64_t go = 0;
 #pragma unroll
   for (int k = 0; k < 7; ++k)

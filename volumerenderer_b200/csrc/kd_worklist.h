@@ -118,7 +118,7 @@ inline void kd_build_worklist(const vr_kd_geom& g, int n, const KdIndex* const* 
 
 // ---- work lists of the persistent kernel (kd_decode.cu: kd_decode6_kernel) -------------------------------------------------
 // Two queues instead of one CTA list: parse items (one unit = an eighth of a tile = one warp's work each, self-contained
-// 64-byte records) and constant groups (vr_fill_job, stored by the TMA unit).  Both in destination-address order.  Culling as above.
+// 96-byte records) and constant groups (vr_fill_job, stored by the TMA unit).  Both in destination-address order.  Culling as above.
 namespace vr {
 // Returns false when a unit's segment exceeds stageChunksMax (cannot happen for a well-formed stream and the kernel's capacity;
 // the caller then takes the classic kernel).
@@ -172,33 +172,40 @@ inline bool kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const*
         const uint32_t blk = hj.tileLeafBlock[t];
         const uint32_t* lo = idx[b]->leafOff.data() + (size_t)blk * 256;
         const uint64_t tileEnd = idx[b]->blockSymEnd[blk];
-        // first / last live leaf of every unit in one pass over the tile's 256 entries
-        uint64_t uFirst[8], uLast[8];
-        bool uAny[8];
-        for (uint32_t u = 0; u < 8; ++u) {
-          uAny[u] = false; uFirst[u] = 0; uLast[u] = 0;
-          for (uint32_t l = 32u * u; l < 32u * u + 32u; ++l)
-            if (lo[l] != VR_PRUNED) { if (!uAny[u]) { uFirst[u] = lo[l]; uAny[u] = true; } uLast[u] = lo[l]; }
-        }
+        // offset of the first live leaf at or behind every leaf index (the end of a run's symbols), in one backward pass
+        uint64_t nextLive[257];
+        nextLive[256] = tileEnd;
+        for (int l = 255; l >= 0; --l) nextLive[l] = lo[l] != VR_PRUNED ? (uint64_t)lo[l] : nextLive[l + 1];
+        const uint32_t runLen = 1u << pg.runLog, nRuns = 32u >> pg.runLog;
         for (uint32_t u = 0; u < 8; ++u) {
           vr_parse_item w{};
           w.tileUnit = (t << 3) | u;
-          w.leaf0 = blk * 256u + 32u * u;
-          // the unit's symbols lie between its first live leaf and the next live leaf behind it (or the end of the tile)
-          uint64_t begin = uAny[u] ? uFirst[u] : ~0ull, end = tileEnd;
-          const uint64_t last = uLast[u];
-          for (uint32_t v = u + 1u; v < 8u; ++v)
-            if (uAny[v]) { end = uFirst[v]; break; }
-          // ... and a leaf subtree is at most 63 nodes + 64 voxel items of 8 symbols long
-          if (begin != ~0ull && last + 575u < end) end = last + 575u;
-          if (begin != ~0ull) {
-            // staged range: from the 16-byte chunk of the first symbol to the chunk that holds the word after the last
-            // symbol's word (the window keeps one word of look-ahead)
-            const uint64_t c0 = (begin >> 4) >> 2, c1 = ((((end > begin ? end - 1 : begin) >> 4) + 2) >> 2) + 1;
-            if (c1 - c0 > stageChunksMax) return false;
-            w.segOff = (uint32_t)(16u * c0);  // the packed stream sits at offset 0 of the arena
-            w.segChunks = (uint32_t)(c1 - c0);
+          w.leaf0 = blk * 256u;
+          uint32_t total = 0;
+          for (uint32_t r = 0; r < nRuns; ++r) {
+            const uint32_t base = vr6::p6_leaf_of(pg, u, r << pg.runLog);
+            // the run's symbols lie between its first live leaf and the next live leaf behind it (or the end of the tile)
+            uint64_t begin = ~0ull, last = 0;
+            for (uint32_t l = base; l < base + runLen; ++l)
+              if (lo[l] != VR_PRUNED) { if (begin == ~0ull) begin = lo[l]; last = lo[l]; }
+            uint32_t chunks = 0, segOff = 0;
+            if (begin != ~0ull) {
+              uint64_t end = nextLive[base + runLen];
+              // ... and a leaf subtree is at most 63 nodes + 64 voxel items of 8 symbols long
+              if (last + 575u < end) end = last + 575u;
+              // staged range: from the 16-byte chunk of the first symbol to the chunk that holds the word after the last
+              // symbol's word (the window keeps one word of look-ahead)
+              const uint64_t c0 = (begin >> 4) >> 2, c1 = ((((end > begin ? end - 1 : begin) >> 4) + 2) >> 2) + 1;
+              chunks = (uint32_t)(c1 - c0);
+              segOff = (uint32_t)(16u * c0);  // the packed stream sits at offset 0 of the arena
+            }
+            w.run[r].segOff = segOff;
+            w.run[r].packed = VR_RUN_PACK(chunks, base, total);
+            total += chunks;
           }
+          for (uint32_t r = nRuns; r < 4u; ++r) w.run[r].packed = VR_RUN_PACK(0u, 0u, total);  // (stage_unit's one loop over all runs)
+          if (total > stageChunksMax) return false;
+          w.segChunks = total;
           w.dst = key;
           int32_t uo[3];
           vr6::p6_unit_origin(pg, u, uo);
@@ -223,7 +230,7 @@ inline bool kd_build_worklist6(const vr_kd_geom& g, int n, const KdIndex* const*
   // Parse units in address order.  (heavyFirst = longest segments first, in classes of 1 KB: measured slower -- the two
   // 16-byte halves of a 32-byte sector belong to units four tickets apart, and in address order L2 merges them before they
   // reach DRAM: 0.70 ms against 0.87 ms on the config-3 layer.)
-  // (sorted through an index array: the records are 80 bytes)
+  // (sorted through an index array: the records are 112 bytes)
   std::vector<std::pair<int64_t, uint32_t>> ord(pitems.size());
   for (size_t i = 0; i < pitems.size(); ++i) {
     const int64_t cls = heavyFirst ? (int64_t)(0xFFFFu - (pitems[i].w.segChunks >> 6)) : 0;

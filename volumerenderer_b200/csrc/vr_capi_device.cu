@@ -360,7 +360,7 @@ static int plan_build_lists(vr_decode_plan* p, const uint8_t* needed, std::vecto
       vr_parse_item& it = parse[i];
       const vr_stream* s = p->streams[(size_t)brickOf[i]];
       it.arena = s->devImage;
-      it.segOff += (uint32_t)s->offWords;
+      for (int r = 0; r < 4; ++r) it.run[r].segOff += (uint32_t)s->offWords;
       it.leafOffOff = (uint32_t)(s->offLeafOff + 4ull * it.leaf0);
       it.leafValOff = (uint32_t)(s->offLeafVal + (uint64_t)it.leaf0);
       it.treeDist = p->treeDist[(size_t)brickOf[i]];
