@@ -212,8 +212,8 @@ int emu_decode6(void* p, uint8_t* slab, long long SX, long long SY, long long SZ
   uint64_t chainDist = 0;
   for (int k = 1; k <= 7; ++k) chainDist |= (uint64_t)s->distanceMap[g.D0 + k] << (8 * (k - 1));
   job.dstOffset = (oz * SY + oy) * SX + ox;
-  vr6::Dist d{s->distanceMap[g.D0], s->distanceMap[g.D0 - 1], s->distanceMap[g.D0 - 2], s->distanceMap[g.D0 - 3], s->distanceMap[g.D0 - 4],
-              s->distanceMap[g.D0 - 5]};
+  vr6::Dist d{vr6::dist2(s->distanceMap[g.D0]), vr6::dist2(s->distanceMap[g.D0 - 1]), vr6::dist2(s->distanceMap[g.D0 - 2]),
+              vr6::dist2(s->distanceMap[g.D0 - 3]), vr6::dist2(s->distanceMap[g.D0 - 4]), vr6::dist2(s->distanceMap[g.D0 - 5])};
   const uint32_t lutOff = 0, stripOff = VR6_LUT_BYTES, stageOff = VR6_LUT_BYTES + ((VR6_STRIPS_BYTES + 15u) & ~15u);
   std::vector<uint8_t> smem(stageOff + 16ull * (size_t)(stageChunks > 0 ? stageChunks : 1) + 64);
   for (uint32_t i = 0; i < VR6_LUT_ENTRIES; ++i) { const uint32_t e = vr6::chain_entry(i, chainDist); std::memcpy(smem.data() + lutOff + 4 * i, &e, 4); }

@@ -125,20 +125,15 @@ __device__ __forceinline__ void stage_unit(const Decode6Params& p, uint32_t idx,
   if (lane < 4u) cp16(wbase + VR6_WARP_ITEM + 16u * lane, reinterpret_cast<const uint8_t*>(p.parse + (lane == 0u ? src_of(p, idx) : idx)) + 16u * lane);
   else if (lane < 12u) cp16(wbase + VR6_WARP_LEAFOFF + 16u * (lane - 4u), arena + leafOffOff + 4u * leafRel + 16u * ((lane - 4u) & ((1u << cprLog) - 1u)));
   else if (lane < 12u + nRuns) cp16(wbase + VR6_WARP_LEAFVAL + 16u * (lane - 12u), arena + ((leafValOff + leafRel) & ~15u));
-  // The runs' chunks sit one behind the other in the staging region (run r from chunk s_r on: the work list stores the
-  // running total in every slot, unused ones included), so ONE loop over the unit's chunks copies them all: chunk c of the
-  // region comes from arena offset 16 c + D_r, r = the last run that starts at or before c.
-  const uint32_t total = __shfl_sync(0xFFFFFFFFu, ia.z, 0);
-  const uint32_t k1 = __shfl_sync(0xFFFFFFFFu, ir.y, 1), k2 = __shfl_sync(0xFFFFFFFFu, ir.y, 2), k3 = __shfl_sync(0xFFFFFFFFu, ir.y, 3);
-  const uint32_t s1 = VR_RUN_SMEM(k1), s2 = VR_RUN_SMEM(k2), s3 = VR_RUN_SMEM(k3);
-  const uint32_t D0 = __shfl_sync(0xFFFFFFFFu, ir.x, 0), D1 = __shfl_sync(0xFFFFFFFFu, ir.x, 1) - 16u * s1,
-                 D2 = __shfl_sync(0xFFFFFFFFu, ir.x, 2) - 16u * s2, D3 = __shfl_sync(0xFFFFFFFFu, ir.x, 3) - 16u * s3;
+  // the segments: the lanes of a run (8 or 16) copy that run's chunks, 128 or 256 contiguous bytes per step; the runs sit one
+  // behind the other in the staging region
+  {
+    const uint32_t cr = lane >> runLog, j = lane & ((1u << runLog) - 1u);
+    const uint32_t so = __shfl_sync(0xFFFFFFFFu, ir.x, cr), pk = __shfl_sync(0xFFFFFFFFu, ir.y, cr);
+    const uint32_t sc = VR_RUN_CHUNKS(pk), sm = segS + 16u * VR_RUN_SMEM(pk);
+    const uint8_t* src = arena + so;
 #pragma unroll 1
-  for (uint32_t c = lane; c < total; c += 32u) {
-    uint32_t D = c >= s1 ? D1 : D0;
-    D = c >= s2 ? D2 : D;
-    D = c >= s3 ? D3 : D;
-    cp16(segS + 16u * c, arena + (uint32_t)(16u * c + D));
+    for (uint32_t c = j; c < sc; c += 1u << runLog) cp16(sm + 16u * c, src + 16u * c);
   }
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(barS) : "memory");
 }
@@ -283,8 +278,9 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     const bool early = fitsOther && !curBig;
     // ---- phase 1: one leaf subtree per lane, first half ----
     vr6::Dist d;
-    d.d0 = (uint32_t)treeDist & 0xFFu; d.d1 = (uint32_t)(treeDist >> 8) & 0xFFu; d.d2 = (uint32_t)(treeDist >> 16) & 0xFFu;
-    d.d3 = (uint32_t)(treeDist >> 24) & 0xFFu; d.d4 = (uint32_t)(treeDist >> 32) & 0xFFu; d.d5 = (uint32_t)(treeDist >> 40) & 0xFFu;
+    d.d0 = vr6::dist2((uint32_t)treeDist & 0xFFu); d.d1 = vr6::dist2((uint32_t)(treeDist >> 8) & 0xFFu);
+    d.d2 = vr6::dist2((uint32_t)(treeDist >> 16) & 0xFFu); d.d3 = vr6::dist2((uint32_t)(treeDist >> 24) & 0xFFu);
+    d.d4 = vr6::dist2((uint32_t)(treeDist >> 32) & 0xFFu); d.d5 = vr6::dist2((uint32_t)(treeDist >> 40) & 0xFFu);
     vr6::WinShared w;
     uint32_t wo = 2u;  // bits consumed since the window's last re-alignment: the root's symbol
     const uint32_t word6 = vr6::mkword(val, d.d5);

@@ -166,11 +166,20 @@ VR_HD void fill_octets(uint32_t strip, uint32_t i, uint32_t n, uint32_t val) {
 // that a child with symbol c (0 same, 1 add, 2 subtract, 3 same-and-stop: VolumeKdTree_recover.cpp:784-787) is byte c.
 VR_HD int imin(int a, int b) { return a < b ? a : b; }
 VR_HD int imax(int a, int b) { return a > b ? a : b; }
-VR_HD uint32_t mkword(uint32_t n, uint32_t d) {
-  const int up = imin((int)n + (int)d, 255), dn = imax((int)n - (int)d, 0);
-  // bytes 1, 2 by one permute, bytes 0 and 3 by a multiply-add: the integer pipe that carries every logic operation, shift
-  // and min/max of this parser is the kernel's bottleneck (68 % busy in ncu), the multiply-add pipe is nearly idle
-  return n * 0x01000001u + Mem::perm((uint32_t)up, (uint32_t)dn, 0x1401u);
+// d2 = the level's distance packed for 16-bit lanes: d in the low half, -d in the high half (dist2()).
+VR_HD uint32_t dist2(uint32_t d) { return d + ((0u - d) << 16); }
+VR_HD uint32_t mkword(uint32_t n, uint32_t d2) {
+  // (n, n) + (d, -d) in 16-bit lanes, capped at (255, 32767) and floored at 0 -- ONE fused add-min-relu gives sat(n+d) and
+  // sat(n-d); one permute places them between two copies of n.  The copies come from a multiply (the multiply-add pipe is
+  // nearly idle; the integer pipe that carries every logic operation, shift and min/max of this parser is its bottleneck).
+  const uint32_t n2 = n * 0x00010001u;
+#if VR6_DEV
+  const uint32_t t = __viaddmin_s16x2_relu(n2, d2, 0x7FFF00FFu);
+#else
+  const int up = imin((int)n + (int)(d2 & 0xFFFFu), 255), dn = imax((int)n - (int)(d2 & 0xFFFFu), 0);
+  const uint32_t t = (uint32_t)up | ((uint32_t)dn << 16);
+#endif
+  return Mem::perm(n2, t, 0x0640u);  // bytes (n, up, dn, n)
 }
 VR_HD uint32_t child(uint32_t word, uint32_t c) { return Mem::perm(word, 0u, c | 0x4440u); }
 // the same from the window itself: selector = (bits & 3) | 0x4440 in one three-input logic operation
@@ -184,7 +193,7 @@ VR_HD uint32_t child_of_bits(uint32_t word, uint32_t bits) {
 #endif
 }
 
-struct Dist { uint32_t d0, d1, d2, d3, d4, d5; };  // d_h = distanceMap[D0 - h]: applied to nodes at height h
+struct Dist { uint32_t d0, d1, d2, d3, d4, d5; };  // d_h = dist2(distanceMap[D0 - h]): applied to nodes at height h
 
 // ---- the octet: straight-line code ------------------------------------------------------------------------------------
 // State threaded through the octet: `bits` = the window shifted so that the next token is at bit 0, `o` = bits consumed
