@@ -6,10 +6,11 @@
 // Two kernels:
 //  * kd_decode6_kernel -- the product path for bricks whose leaf boxes are 4x4x4 (256x256x128 and relatives).  Persistent,
 //    one CTA per SM, warp-specialised: 22 parse warps, each a pipeline of its own over "units" (32 leaf subtrees = an
-//    eighth of a 32x32x16 tile, one lane per leaf subtree: kd_parse6.h; the unit's stream segment and index entries arrive
-//    in shared memory by 16-byte asynchronous copies (cp.async) of the warp's own lanes, its voxels leave as one tensor
-//    store) and one warp that hands the constant groups to the TMA unit (cp.async.bulk.tensor from a row image in
-//    shared memory).
+//    eighth of a 32x32x16 tile that spans the tile's whole x extent, 32 x 8 x 8 voxels, one lane per leaf subtree:
+//    kd_parse6.h; the unit's stream segments (2 or 4 runs of consecutive leaf subtrees) and index entries arrive in shared
+//    memory by 16-byte asynchronous copies (cp.async) of the warp's own lanes half a unit ahead, its voxels leave as one
+//    tensor store of 64 whole-sector rows) and one warp that hands the constant groups to the TMA unit
+//    (cp.async.bulk.tensor from a row image in shared memory).
 //    Parsing is bound by instruction issue, the constant groups by HBM writes; in one CTA per work item (round 1) a CTA in
 //    its fill phase parses nothing and holds its slot until its stores have drained, so the launch cost parse + fill.
 //    Here the fills occupy one warp per SM and no issue slots to speak of, and the two overlap.

@@ -7,10 +7,10 @@
 // start offset and root value come from the side index, kd_stream.h) and writes the 4x4x4 voxels of its box, x fastest,
 // into a 64-byte block of shared memory; the CTA then stores whole 16-byte x-runs (kd_decode.cu, phase 2).
 //
-// Why it looks the way it does (profiles/r2_parser.md has the instruction counts):
+// Why it looks the way it does (profiles/r2_step_final.md has the instruction counts and the A/B runs):
 //  * values: a node's value is one of {parent, sat(parent + d), sat(parent - d), parent} selected by its symbol
-//    (:784-787).  The parent builds that "select word" once (2 fused add-min/max + 2 byte permutes) and each child is ONE
-//    byte permute -- instead of 6 ALU operations per node.
+//    (:784-787).  The parent builds that "select word" once (one fused add-min-relu in 16-bit lanes + one byte permute +
+//    one multiply) and each child is ONE byte permute -- instead of 6 ALU operations per node.
 //  * chains: one look-up in a 16 K-entry table (shared memory) gives the whole chain as x -> min(max(x + A, lo), hi) and
 //    the number of bits the voxel item occupies.
 //  * the two voxels of a height-1 node are finished together in 16-bit lanes (voxel_pair): 10 instead of 14 instructions
@@ -18,8 +18,8 @@
 //  * bit window: the three lowest levels of the tree (an octet: 7 nodes, 8 voxels) are straight-line code, so the
 //    places where the 32-bit window has to be re-aligned are known at compile time: 6 per octet instead of one per
 //    symbol, each branch-free (a refill is two predicated instructions).  Between them a token costs one shift.
-//  * stream words come from shared memory: the unit's segment (at most 4.6 KB) is staged by asynchronous copies, so the
-//    parser's dependent chain never waits on global memory.
+//  * stream words come from shared memory: the unit's segments (at most 4.7 KB) are staged by asynchronous copies, so the
+//    parser's dependent chain never waits on global memory; the window keeps a third word loaded one boundary ahead.
 #pragma once
 #include "kd_common.h"
 
