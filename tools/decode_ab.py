@@ -64,9 +64,9 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--workloads", default="slab,config3,noise")
     ap.add_argument("--check", action="store_true", help="compare the two kernels' slabs byte for byte")
-    ap.add_argument("--fill-mode", type=int, default=0, help="persistent kernel: 0 tensor stores, 1 streaming stores of the fill warp, 2 tensor stores + evict-first")
+    ap.add_argument("--fill-mode", type=int, default=2, help="persistent kernel: 0 tensor stores, 1 streaming stores of the fill warp, 2 tensor stores + evict-first")
     ap.add_argument("--kernels", default="persistent,classic")
-    ap.add_argument("--tma-rows", type=int, default=8)
+    ap.add_argument("--tma-rows", type=int, default=8, help="rows per tensor-store box of the constant groups: 8 or 16 (anything else: the classic kernel)")
     ap.add_argument("--unit-store", type=int, default=0, help="persistent kernel: 0 choose, 1 tensor store per unit, 2 16-byte stores of the lanes")
     ap.add_argument("--parse-order", type=int, default=0, help="0 address order, 1 longest segments first")
     ap.add_argument("--split", type=int, default=0, help="persistent kernel: 1 = constant groups as a kernel of their own on a side stream")
