@@ -234,7 +234,7 @@ __device__ __forceinline__ void parse_warp(const Decode6Params& p, const uint32_
     if (idxA < p.nParse) curR = __ldg(reinterpret_cast<const uint2*>(&p.parse[src_of(p, idxA)].run[lane]));
     if (idxB < p.nParse) bR = __ldg(reinterpret_cast<const uint2*>(&p.parse[src_of(p, idxB)].run[lane]));
   }
-  // The staging area is two regions, R0 = [0, 2 048) and R1 = [2 048, 4 704).  A unit's segment sits in one of them and its
+  // The staging area is two regions, R0 = [0, 2 048) and R1 = [2 048, 4 864).  A unit's segments sit in one of them and its
   // voxel box (2 048 B) is later written over it, so the OTHER region is free while the unit is parsed: the next unit is
   // staged there half-way through the parsing (its copies then have the rest of the unit to land), not after it.  A
   // segment longer than its region ("big": starts at 0 and reaches into R1; noise-like data) falls back to staging
