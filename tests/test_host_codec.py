@@ -189,3 +189,39 @@ def test_emulated_persistent_kernel_parser(kind, dims):
     if kind == "noise":
         assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, int(st[1]) - 1) == _lib.VR_ERR_FORMAT
     oa.EMU.emu_free(h)
+
+
+@pytest.mark.parametrize("dims", [(64, 64, 32), (64, 32, 32)])
+def test_longest_possible_units_fit_the_staging_area(dims):
+    """A hand-made stream in which no node is pruned and every voxel carries the longest refinement chain (8 symbols per
+    voxel item): the units of the persistent kernel are then as long as the grammar allows.  They must fit the staging
+    capacity of 304 chunks (kd_decode.cu: at most 4 runs x 74 chunks), and the parser must decode them like the levelCut
+    restatement.  Both leaf-box orientations."""
+    X, Y, Z = dims
+    s, _ = vr.Stream.compress(synth.shell_brick(dims, noise=3), 1, 2)  # header and distance map of a brick of this shape
+    hd, dm = s.header, s.distance_map.copy()
+    D0 = hd.origTreeDepth
+    rng = np.random.default_rng(7)
+    syms = np.empty(((1 << D0) - 1) + (8 << D0), np.uint8)
+    pos, stack = 0, [0]
+    while stack:  # preorder of the complete tree; symbols 0..2 only (3 would prune a node / end a chain)
+        d = stack.pop()
+        if d == D0:
+            syms[pos:pos + 8] = rng.integers(0, 3, 8); pos += 8
+        else:
+            syms[pos] = rng.integers(0, 3); pos += 1
+            stack += [d + 1, d + 1]
+    assert pos == syms.size
+    sy = np.concatenate([syms, np.zeros((-syms.size) % 4, np.uint8)]).reshape(-1, 4)
+    packed = np.concatenate([(sy[:, 0] | (sy[:, 1] << 2) | (sy[:, 2] << 4) | (sy[:, 3] << 6)).astype(np.uint8), np.zeros(64, np.uint8)])
+    hd.numActiveNodes = syms.size
+    rc, want = oa.oracle_levelcut(packed, hd.numActiveNodes, dm, hd.origTreeDepth, hd.maxTreeDepth, X, Y, Z)
+    assert rc == 0
+    h = oa.EMU.emu_from_memory(ctypes.byref(hd), dm.ctypes.data, packed.ctypes.data, packed.size)
+    slab = np.full((Z + 2, Y + 1, X + 32), 0xAB, np.uint8)
+    assert oa.EMU.emu_decode6(h, slab.ctypes.data, X + 32, Y + 1, Z + 2, 16, 1, 1, 304) == 0
+    assert np.array_equal(slab[1:Z + 1, 1:Y + 1, 16:16 + X], want)
+    st = (ctypes.c_longlong * 4)()
+    oa.EMU.emu_decode6_stats(st)
+    assert 288 <= st[1] <= 296  # 18 431 symbols = 4 608 bytes per unit, plus the alignment of its 2 or 4 runs
+    oa.EMU.emu_free(h)
